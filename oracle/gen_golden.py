@@ -1,0 +1,141 @@
+"""Generate tests/golden/*.npz by running the REFERENCE ITSELF (imported read-only from
+/root/reference/src) on small seeded inputs.  Run in the build container only:
+
+    python oracle/gen_golden.py
+
+The GPU box has no /root/reference; tests read the committed .npz files.  TEST INFRASTRUCTURE.
+"""
+from __future__ import annotations
+
+import os
+import random
+import sys
+
+import numpy as np
+
+REF_SRC = "/root/reference/src"
+OUT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests", "golden")
+
+
+def _import_reference():
+    sys.path.insert(0, REF_SRC)
+    import vector_db.indexing.hnsw as ref_hnsw
+    import vector_db.inference.pq as ref_pq
+    from vector_db.storage import InMemoryNodeStorage
+    from vector_db.types import Node
+    from vector_db.util.distance import euclidean_vector_distance
+    from vector_db.util.math import top_k_indices_sorted
+    return ref_hnsw, ref_pq, InMemoryNodeStorage, Node, euclidean_vector_distance, top_k_indices_sorted
+
+
+def gen_exact(ref_dist, topk_sorted):
+    rng = np.random.default_rng(1234)
+    X = rng.standard_normal((300, 24)).astype(np.float32)
+    X[17] = X[5]                      # a duplicate row: (dist,id) tie-break must pick the smaller id
+    ids = np.arange(300, dtype=np.int64) * 3 + 7
+    Q = rng.standard_normal((12, 24)).astype(np.float32)
+    Q[0] = X[5]                       # self query -> distance exactly 0 (test_hnsw.py:103-111)
+    k = 10
+    D = np.empty((12, k), np.float32)
+    I = np.empty((12, k), np.int64)
+    full = np.empty((12, 300), np.float32)
+    for qi in range(12):
+        pairs = [(ref_dist(Q[qi], X[i]), int(ids[i])) for i in range(300)]   # test_hnsw.py:128-134
+        full[qi] = [p[0] for p in pairs]
+        pairs.sort()
+        D[qi] = [p[0] for p in pairs[:k]]
+        I[qi] = [p[1] for p in pairs[:k]]
+    scores = rng.standard_normal(50).astype(np.float32)
+    np.savez_compressed(os.path.join(OUT, "exact_l2.npz"), X=X, ids=ids, Q=Q, D=D, I=I, full=full,
+                        scores=scores, top7=topk_sorted(scores, 7))
+
+
+def gen_pq(ref_pq):
+    # KATs restated from tests/inference/test_pq.py:78-116
+    svc = ref_pq.ProductQuantizationService(k=3, chunks=2, dim=4)
+    kat_c = np.array([[0.0, 0.0], [1.0, 1.0], [2.0, 2.0]], dtype=np.float32)
+    kat1 = svc._find_nearest_centroid(np.array([0.9, 1.1], dtype=np.float32), kat_c)
+    cents = [np.array([[0.0, 0.0], [1.0, 1.0], [2.0, 2.0]], dtype=np.float32),
+             np.array([[0.0, 0.0], [1.0, 1.0], [2.0, 2.0]], dtype=np.float32)]
+    kat2 = svc._compress_embedding(np.array([0.9, 1.1, 2.1, 1.9], dtype=np.float32), cents)
+
+    # full compress(): centroids + codes from ONE reference run (SURVEY.md 8c determinism note)
+    np.random.seed(777)
+    rng = np.random.default_rng(777)
+    X = rng.standard_normal((1500, 32)).astype(np.float32)
+    svc = ref_pq.ProductQuantizationService(k=32, chunks=8, dim=32)
+    codes = svc.compress(X)
+    cents = np.stack([np.asarray(c, dtype=np.float32) for c in svc.centroids])    # (m,K,dsub)
+    chunked = svc._chunk_embeddings(X[:5])
+    chunk_kat = np.array([[np.asarray(v) for v in ch] for ch in chunked], dtype=np.float32)
+    # encode of held-out rows with the SAME centroids through the reference's per-row path
+    Y = rng.standard_normal((400, 32)).astype(np.float32)
+    codes_y = np.array([svc._compress_embedding(y, svc.centroids) for y in Y], dtype=np.int64)
+    np.savez_compressed(os.path.join(OUT, "pq.npz"), X=X, codes=codes, centroids=cents, Y=Y,
+                        codes_y=codes_y, chunk_kat=chunk_kat, kat1=np.int64(kat1), kat2=kat2)
+
+
+def gen_hnsw(ref_hnsw, Storage, Node, tag, n, dim, M, efc, nq, ef, k, seed):
+    rng = np.random.default_rng(seed)
+    X = rng.standard_normal((n, dim)).astype(np.float32)
+    Q = rng.standard_normal((nq, dim)).astype(np.float32)
+    Q[0] = X[3]
+    counter = {"n": 0}
+    real = ref_hnsw.euclidean_vector_distance
+
+    def counting(a, b):
+        counter["n"] += 1
+        return real(a, b)
+
+    ref_hnsw.euclidean_vector_distance = counting
+    try:
+        idx = ref_hnsw.HNSW(M=M, ef_construction=efc, rng=random.Random(42), storage=Storage())
+        for i in range(n):
+            idx.insert_node(Node(id=i, embedding=X[i]))
+        build_evals = counter["n"]
+        # flatten graph: (node, level, pos) -> neighbour
+        rows = []
+        for nid, node in idx.node_store.items():
+            for lvl, lst in node.neighbors.items():
+                for pos, nb in enumerate(lst):
+                    rows.append((nid, lvl, pos, nb))
+        graph = np.array(rows, dtype=np.int64)
+        node_levels = np.array([max(idx.node_store[i].neighbors.keys()) for i in range(n)], np.int32)
+        D = np.full((nq, k), np.inf, np.float32)
+        I = np.full((nq, k), -1, np.int64)
+        evals = np.zeros(nq, np.int64)
+        for qi in range(nq):
+            counter["n"] = 0
+            res = idx.search(Q[qi], k=k, ef=ef)
+            evals[qi] = counter["n"]
+            for j, (node, d) in enumerate(res):
+                D[qi, j], I[qi, j] = d, node.id
+        # filtered search (hnsw.py:96,127): allow only ids divisible by 3
+        allowed = {i for i in range(n) if i % 3 == 0}
+        Df = np.full((nq, k), np.inf, np.float32)
+        If = np.full((nq, k), -1, np.int64)
+        for qi in range(nq):
+            res = idx.search(Q[qi], k=k, ef=ef, filter_ids=allowed)
+            for j, (node, d) in enumerate(res):
+                Df[qi, j], If[qi, j] = d, node.id
+    finally:
+        ref_hnsw.euclidean_vector_distance = real
+    np.savez_compressed(os.path.join(OUT, f"hnsw_{tag}.npz"), X=X, Q=Q, graph=graph,
+                        node_levels=node_levels, entry=np.int64(idx.entry_node_id),
+                        max_level=np.int64(idx.max_level), M=np.int64(M), efc=np.int64(efc),
+                        ef=np.int64(ef), k=np.int64(k), D=D, I=I, evals=evals, Df=Df, If=If,
+                        build_evals=np.int64(build_evals))
+
+
+def main():
+    os.makedirs(OUT, exist_ok=True)
+    ref_hnsw, ref_pq, Storage, Node, ref_dist, topk_sorted = _import_reference()
+    gen_exact(ref_dist, topk_sorted)
+    gen_pq(ref_pq)
+    gen_hnsw(ref_hnsw, Storage, Node, "small", n=400, dim=16, M=8, efc=50, nq=24, ef=50, k=10, seed=11)
+    gen_hnsw(ref_hnsw, Storage, Node, "medium", n=2000, dim=48, M=16, efc=100, nq=32, ef=64, k=10, seed=12)
+    print("golden fixtures written to", os.path.abspath(OUT))
+
+
+if __name__ == "__main__":
+    main()

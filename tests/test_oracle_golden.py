@@ -1,0 +1,118 @@
+"""Pins the CPU oracle (oracle/*.py) against fixtures produced by the reference itself
+(oracle/gen_golden.py) and against the reference tests' known answers."""
+import os
+
+import numpy as np
+
+from oracle import oracle as O
+from oracle.hnsw_oracle import HnswOracle, search_arrays
+
+
+def _load(golden_dir, name):
+    return np.load(os.path.join(golden_dir, name))
+
+
+def test_l2_distance_and_exact_topk_match_reference(golden_dir):
+    g = _load(golden_dir, "exact_l2.npz")
+    X, ids, Q = g["X"], g["ids"], g["Q"]
+    for qi in range(Q.shape[0]):
+        for i in (0, 5, 17, 299):
+            assert O.l2_distance(Q[qi], X[i]) == g["full"][qi, i]
+    D, I = O.exact_l2_topk(X, ids, Q, 10)
+    np.testing.assert_array_equal(I, g["I"])
+    np.testing.assert_allclose(D, g["D"], rtol=1e-6, atol=0)
+    assert D[0, 0] == 0.0 and I[0, 0] == ids[5] and I[0, 1] == ids[17]   # duplicate row: smaller id first
+    for qi in range(3):
+        pw = O.exact_l2_topk_pairwise(X, ids, Q[qi], 10)
+        assert [p[1] for p in pw] == list(g["I"][qi])
+    Dg, Ig = O.exact_l2_topk_gemm(X, ids, Q, 10)
+    np.testing.assert_array_equal(Ig, g["I"])
+
+
+def test_exact_topk_short_database_pads():
+    X = np.eye(3, 4, dtype=np.float32)
+    D, I = O.exact_l2_topk(X, np.array([4, 2, 9]), X[:1], 5)
+    assert list(I[0]) == [4, 2, 9, -1, -1] and D[0, 0] == 0 and np.isinf(D[0, 3])
+
+
+def test_topk_largest_sorted_matches_reference(golden_dir):
+    g = _load(golden_dir, "exact_l2.npz")
+    np.testing.assert_array_equal(O.topk_largest_sorted(g["scores"], 7), g["top7"])
+
+
+def test_cosine_topk_is_largest_first():
+    rng = np.random.default_rng(0)
+    X = rng.standard_normal((200, 8)).astype(np.float32)
+    S, I = O.exact_cosine_topk(X, np.arange(200), X[:4] * 3.0, 5)
+    assert list(I[:, 0]) == [0, 1, 2, 3]
+    assert np.all(np.diff(S, axis=1) <= 0) and np.allclose(S[:, 0], 1.0, atol=1e-6)
+
+
+def test_pq_kats_and_codes_match_reference(golden_dir):
+    g = _load(golden_dir, "pq.npz")
+    # tests/inference/test_pq.py:78-90 and :92-116
+    c = np.array([[0, 0], [1, 1], [2, 2]], dtype=np.float32)
+    assert O.pq_nearest_centroid(np.array([0.9, 1.1], np.float32), c) == 1 == int(g["kat1"])
+    assert list(O.pq_encode_loop(np.array([[0.9, 1.1, 2.1, 1.9]], np.float32), [c, c])[0]) == [1, 2]
+    assert list(g["kat2"]) == [1, 2]
+    cents = list(g["centroids"])
+    np.testing.assert_array_equal(O.pq_chunk(g["X"][:5], 8), g["chunk_kat"])
+    np.testing.assert_array_equal(O.pq_encode(g["Y"], cents), g["codes_y"])
+    np.testing.assert_array_equal(O.pq_encode_loop(g["Y"][:50], cents), g["codes_y"][:50])
+    # compress() labels the training rows with the FINAL centroids (pq.py:103-106)
+    np.testing.assert_array_equal(O.pq_encode(g["X"], cents), g["codes"])
+
+
+def test_adc_restatement_consistent_with_decode(golden_dir):
+    g = _load(golden_dir, "pq.npz")
+    cents = list(g["centroids"])
+    Q = g["Y"][:6]
+    codes = g["codes"]
+    lut = O.adc_lut(Q, cents)
+    D, I = O.adc_scan_topk(codes, lut, 8)
+    recon = np.concatenate([cents[j][codes[:, j]] for j in range(len(cents))], axis=1)
+    ref = ((Q[:, None, :] - recon[None, :, :]) ** 2).sum(axis=2)
+    np.testing.assert_allclose(D, np.sort(ref, axis=1)[:, :8], rtol=2e-5)
+    assert np.all(np.diff(D, axis=1) >= 0)
+
+
+def _rebuild(g):
+    M, efc = int(g["M"]), int(g["efc"])
+    X = g["X"]
+    o = HnswOracle(M, efc)
+    for i in range(X.shape[0]):
+        o.insert(i, X[i])
+    return o
+
+
+def _graph_rows(o):
+    rows = []
+    for nid, d in o.links.items():
+        for lvl, lst in d.items():
+            for pos, nb in enumerate(lst):
+                rows.append((nid, lvl, pos, nb))
+    return np.array(sorted(rows), dtype=np.int64)
+
+
+def test_hnsw_oracle_reproduces_reference_graph_and_search(golden_dir):
+    for name in ("hnsw_small.npz", "hnsw_medium.npz"):
+        g = _load(golden_dir, name)
+        o = _rebuild(g)
+        assert o.entry == int(g["entry"]) and o.max_level == int(g["max_level"])
+        assert o.n_evals == int(g["build_evals"])
+        np.testing.assert_array_equal(_graph_rows(o), np.array(sorted(map(tuple, g["graph"])), dtype=np.int64))
+        k, ef = int(g["k"]), int(g["ef"])
+        allowed = {i for i in range(g["X"].shape[0]) if i % 3 == 0}
+        arr = o.export_arrays()
+        for qi in range(g["Q"].shape[0]):
+            o.n_evals = 0
+            res = o.search(g["Q"][qi], k, ef)
+            assert o.n_evals == int(g["evals"][qi])
+            assert [r[1] for r in res] == [int(x) for x in g["I"][qi] if x >= 0]
+            np.testing.assert_array_equal(np.array([r[0] for r in res], np.float32), g["D"][qi][:len(res)])
+            resf = o.search(g["Q"][qi], k, ef, allowed)
+            assert [r[1] for r in resf] == [int(x) for x in g["If"][qi] if x >= 0]
+            ra, ev = search_arrays(g["X"], arr["adj0"], arr["up_ptr"], arr["adj_up"], int(arr["entry_row"]),
+                                   int(arr["max_level"]), g["Q"][qi], k, ef)
+            assert [int(arr["ids"][r[1]]) for r in ra] == [r[1] for r in res] and ev == int(g["evals"][qi])
+        assert g["D"][0, 0] < 1e-6 and g["I"][0, 0] == 3     # self query, test_hnsw.py:103-111
