@@ -1,0 +1,152 @@
+/* vdb_b200.h -- C ABI of the B200-native search core (libvdb_b200.so).
+ *
+ * Drop-in boundary for the hot path of GProgrammer1/Vector-DB.  The reference has no FFI of its
+ * own (pure Python); each entry point below names the reference call site (file:line, relative to
+ * the reference repo root) whose arithmetic it replaces.  The Python shim in vector_db_b200/
+ * binds these with ctypes; INTEGRATION.md shows the stub a reference maintainer would add.
+ *
+ * Conventions
+ *   - Plain pointers and sizes only; no torch / C++ types.  Pointers marked [dev] are CUDA device
+ *     pointers (the shim passes tensor.data_ptr()), [host] are host pointers.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).  All work is
+ *     enqueued on it; nothing synchronises unless stated.
+ *   - The library keeps no persistent allocations: scratch memory is passed in as `ws`/`ws_bytes`
+ *     and sized by the matching *_workspace() query.
+ *   - Return 0 on success, a VDB_ERR_* code otherwise; vdb_last_error() returns a thread-local
+ *     human-readable message.  There is NO CPU fallback: without a CUDA device every compute entry
+ *     point fails with VDB_ERR_CUDA.
+ *   - Top-k outputs are ordered by (distance, index) ascending -- the tuple order of
+ *     tests/indexing/test_hnsw.py:128-134 and src/vector_db/indexing/hnsw.py:366 -- and padded
+ *     with (+inf, -1) when fewer than k results exist.  L2 distances are NON-squared
+ *     (src/vector_db/util/distance.py:3-4).  Row indices are positions in the device arrays; when
+ *     an `ids` table is given, outputs are translated to external ids.
+ */
+#ifndef VDB_B200_H
+#define VDB_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VDB_OK 0
+#define VDB_ERR_INVALID 1    /* bad argument (shim raises ValueError) */
+#define VDB_ERR_CUDA 2       /* CUDA runtime failure / no device (RuntimeError) */
+#define VDB_ERR_WORKSPACE 3  /* workspace too small (RuntimeError) */
+#define VDB_ERR_UNSUPPORTED 4/* shape outside the kernels' envelope (ValueError) */
+#define VDB_ERR_OVERFLOW 5   /* a bounded on-chip structure overflowed; retry with the bigger variant */
+
+#define VDB_METRIC_L2 0
+#define VDB_METRIC_COSINE 1
+
+const char* vdb_last_error(void);
+int vdb_abi_version(void);
+/* number of kernels this library launched from the calling process so far (bench.py gpu_launches) */
+uint64_t vdb_launch_count(void);
+
+/* ---- a9/a10 storage staging ---------------------------------------------------------------
+ * De-interleave `n` records of the reference's layer-1 memmap layout
+ * {int64 id; float32 embedding[D]} (stride 8+4D, src/vector_db/storage.py:135-144) from PINNED
+ * host memory into SoA device arrays with two strided DMA copies.  */
+int vdb_stage_aos_h2d(const void* host_records /*[host,pinned]*/, int64_t n, int D,
+                      int64_t* ids /*[dev] n*/, float* vecs /*[dev] n*D*/, void* stream);
+
+/* Per-row squared norms and the bf16 mirror used by the tensor-core scan.
+ * Either output may be NULL. */
+int vdb_prepare_rows(const float* vecs /*[dev] N*D*/, int64_t N, int D,
+                     float* sqnorm /*[dev] N*/, void* bf16_mirror /*[dev] N*D bf16*/, void* stream);
+
+/* ---- a1/a3 exact scan, fp32 direct-difference form ------------------------------------------
+ * Replaces the per-pair loop euclidean_vector_distance + sort of
+ * tests/indexing/test_hnsw.py:128-134 / src/vector_db/indexing/ivf.py:176-199.
+ * metric L2: out_d = sqrt(sum((q-x)^2)), ascending.  metric COSINE (no reference implementation;
+ * largest-first order of src/vector_db/util/math.py:3-5): out_d = q.x/(|q||x|), descending.
+ * `ids` may be NULL (outputs are row indices).  `row_mask` (optional bitmap, bit r of word r/32)
+ * restricts results to set rows (the filter_ids of hnsw.py:96,127).  N < 2^32. */
+size_t vdb_exact_topk_f32_workspace(int Q, int64_t N, int k);
+int vdb_exact_topk_f32(const float* q /*[dev] Q*D*/, int Q, const float* db /*[dev] N*D*/,
+                       const int64_t* ids /*[dev] N or NULL*/, const uint32_t* row_mask /*[dev] or NULL*/,
+                       int64_t N, int D, int k, int metric,
+                       float* out_d /*[dev] Q*k*/, int64_t* out_i /*[dev] Q*k*/,
+                       void* ws, size_t ws_bytes, void* stream);
+
+/* Exact fp32 rerank of per-query candidate rows (cand[q][r], -1 = empty; duplicates allowed and
+ * collapsed): the direct-difference distance of util/distance.py:3-4 and the (dist,id) order.
+ * out_kth (optional) receives the k-th returned distance per query (+inf if fewer). */
+int vdb_rerank_f32(const float* q, int Q, const float* db, const int64_t* ids, int64_t N, int D,
+                   const int32_t* cand /*[dev] Q*R*/, int R, int k, int metric,
+                   float* out_d, int64_t* out_i, void* stream);
+
+/* ---- a11 PQ encode -------------------------------------------------------------------------
+ * codes[i][j] = argmin_c sqrt(sum((C_j[c]-x_ij)^2)), first minimum wins
+ * (src/vector_db/inference/pq.py:77-89).  codebooks laid out [m][K][dsub] fp32, K <= 256,
+ * codes uint8 [N][m]. */
+int vdb_pq_encode(const float* x /*[dev] N*D*/, int64_t N, int D, int m, int K,
+                  const float* codebooks /*[dev] m*K*dsub*/, uint8_t* codes /*[dev] N*m*/, void* stream);
+
+/* ---- a12 PQ training (Lloyd iterations of scipy kmeans2 as called at pq.py:11) ------------------
+ * One assignment + mean-update round for all m sub-spaces at once; an empty cluster keeps its
+ * centroid.  `labels` int32 [m][N] receives the assignment made BEFORE the update (kmeans2's
+ * return convention).  ws: m*K*(dsub+1) floats. */
+size_t vdb_pq_kmeans_workspace(int m, int K, int dsub);
+int vdb_pq_kmeans_step(const float* x, int64_t N, int D, int m, int K, float* codebooks /*in/out*/,
+                       int32_t* labels /*[dev] m*N or NULL*/, void* ws, size_t ws_bytes, void* stream);
+
+/* ---- a13 ADC scan (no reference symbol; sub-space layout pq.py:48-62, distance pq.py:77-80) ----
+ * lut[q][j][c] = sum_t (q_jt - C_j[c][t])^2, fp32 [Q][m][K]. */
+int vdb_pq_lut(const float* q /*[dev] Q*D*/, int Q, int D, int m, int K, const float* codebooks,
+               float* lut /*[dev] Q*m*K*/, void* stream);
+/* d(q,i) = sum_j lut[q][j][codes[i][j]] (fp32, j ascending); the R smallest by (d, row).
+ * K must be 256 (nbits=8).  out_i are row indices (int64), or ids[row] when ids != NULL. */
+size_t vdb_pq_adc_topk_workspace(int Q, int64_t N, int m, int R);
+int vdb_pq_adc_topk(const uint8_t* codes /*[dev] N*m*/, int64_t N, int m, const float* lut, int Q, int R,
+                    const int64_t* ids, float* out_d /*[dev] Q*R*/, int64_t* out_i /*[dev] Q*R*/,
+                    void* ws, size_t ws_bytes, void* stream);
+
+/* ---- a4/a5/a6 batched HNSW search -------------------------------------------------------------
+ * One CTA per query: greedy descent on levels max_level..1 (hnsw.py:289-328, strict '<'), then the
+ * best-first beam of hnsw.py:79-134 on level 0 with the same termination rule
+ * (len(found) >= ef and d > worst), result order (dist,row) and result-only filtering.
+ * Graph layout: adj0 int32 [N][deg0] (-1 padded, deg0 = 2M); upper levels: node r with top level
+ * L_r owns rows up_ptr[r] .. up_ptr[r]+L_r-1 of adj_up int32 [*][deg_up] (level l at up_ptr[r]+l-1).
+ * `alive` (optional bitmap): cleared rows are tombstones -- marked visited, never evaluated
+ * (hnsw.py:116-121).  `filter` (optional bitmap): only set rows may enter the result list.
+ * out_stats (optional) uint32 [Q][2] = {distance evaluations, expansions}.  ef <= 1024.
+ * The visited set is an open-addressing hash: hash_slots = 0 sizes it automatically (shared memory
+ * when it fits, else global memory inside ws); a power of two forces that many slots in global
+ * memory.  After the stream has drained, the first int32 of ws is non-zero if any query filled its
+ * visited table (its result may be truncated): retry with a larger hash_slots. */
+size_t vdb_hnsw_search_workspace(int Q, int ef, int deg0);
+int vdb_hnsw_search(const float* q, int Q, const float* db, int64_t N, int D,
+                    const int32_t* adj0, int deg0, const int32_t* adj_up, int deg_up,
+                    const int32_t* up_ptr, int32_t entry_row, int max_level, int ef, int k,
+                    const uint32_t* alive, const uint32_t* filter, int hash_slots,
+                    float* out_d /*[dev] Q*k*/, int32_t* out_rows /*[dev] Q*k*/, uint32_t* out_stats,
+                    void* ws, size_t ws_bytes, void* stream);
+
+/* ---- a7 HNSW construction ----------------------------------------------------------------------
+ * Sequential-semantics insert of rows first..first+count-1 (their vectors already in `db`, their
+ * levels drawn by the host from random.Random, hnsw.py:66-68,160) by ONE CTA, reproducing
+ * hnsw.py:143-225: greedy descent, ef_construction beam per level, M closest as links, reverse
+ * links with closest-cap truncation.  state int32[4] = {entry_row, max_level, evals_lo, evals_hi} is
+ * read and updated (evals = running count of distance evaluations, for parity checks against the
+ * reference's call count).  First int32 of ws = visited-table overflow flag as in vdb_hnsw_search. */
+size_t vdb_hnsw_insert_workspace(int efc, int deg0);
+int vdb_hnsw_insert(const float* db, int64_t N, int D, int32_t* adj0, int deg0, int32_t* adj_up,
+                    int deg_up, const int32_t* up_ptr, const int32_t* levels /*[dev] N*/,
+                    int32_t first, int32_t count, int M, int efc, int32_t* state /*[dev] 4*/,
+                    const uint32_t* alive, void* ws, size_t ws_bytes, void* stream);
+
+/* ---- e: multi-GPU merge -----------------------------------------------------------------------
+ * lists: L sorted lists per query, d [L][Q][k] / i [L][Q][k] (the all-gathered per-shard results);
+ * selects the k best by (d, list, position) -- equal to (d,id) order when shard l owns smaller ids
+ * than shard l+1.  descending != 0 selects the largest (cosine similarities). */
+int vdb_merge_topk(const float* d, const int64_t* i, int L, int Q, int k, int descending,
+                   float* out_d, int64_t* out_i, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VDB_B200_H */

@@ -1,0 +1,165 @@
+// Shared device/host helpers for the vector_db_b200 search core (sm_100a only).
+//
+//  * error plumbing for the C-ABI (thread-local last-error string, VDB_* codes)
+//  * order-preserving (score,index) -> u64 key packing: ascending key == ascending (score, idx),
+//    the (dist, id) tuple order the reference sorts by (tests/indexing/test_hnsw.py:128-134,
+//    src/vector_db/indexing/hnsw.py:366)
+//  * BlockSelect: CTA-wide streaming top-R in shared memory (threshold filter + pending area +
+//    bitonic compaction) used by every scan kernel and by the merge kernels
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "../../include/vdb_b200.h"
+
+namespace vdb {
+
+// ------------------------------------------------------------------ errors
+void set_error(const char* fmt, ...);
+int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
+
+#define VDB_CUDA(expr)                                                          \
+    do {                                                                        \
+        cudaError_t _e = (expr);                                                \
+        if (_e != cudaSuccess) return ::vdb::cuda_fail(_e, #expr, __FILE__, __LINE__); \
+    } while (0)
+
+#define VDB_REQUIRE(cond, code, ...)                                            \
+    do {                                                                        \
+        if (!(cond)) { ::vdb::set_error(__VA_ARGS__); return (code); }          \
+    } while (0)
+
+int sm_count();
+int max_smem_optin();
+void count_launch(int n);
+
+// ------------------------------------------------------------------ keys
+typedef unsigned long long u64;
+#define VDB_KEY_MAX 0xFFFFFFFFFFFFFFFFull
+
+// float -> uint32 such that unsigned order == float order (-inf < ... < -0 < +0 < ... < +inf < NaN)
+__host__ __device__ __forceinline__ uint32_t f32_to_ordered(float f) {
+#ifdef __CUDA_ARCH__
+    uint32_t u = __float_as_uint(f);
+#else
+    uint32_t u; memcpy(&u, &f, 4);
+#endif
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__host__ __device__ __forceinline__ float ordered_to_f32(uint32_t u) {
+    u = (u & 0x80000000u) ? (u & 0x7FFFFFFFu) : ~u;
+#ifdef __CUDA_ARCH__
+    return __uint_as_float(u);
+#else
+    float f; memcpy(&f, &u, 4); return f;
+#endif
+}
+__host__ __device__ __forceinline__ u64 pack_key(float score, uint32_t idx) {
+    return ((u64)f32_to_ordered(score) << 32) | (u64)idx;
+}
+__host__ __device__ __forceinline__ float key_score(u64 k) { return ordered_to_f32((uint32_t)(k >> 32)); }
+__host__ __device__ __forceinline__ uint32_t key_index(u64 k) { return (uint32_t)(k & 0xFFFFFFFFull); }
+
+__host__ __device__ __forceinline__ int next_pow2(int v) {
+    int p = 1;
+    while (p < v) p <<= 1;
+    return p;
+}
+
+#ifdef __CUDACC__
+// ------------------------------------------------------------------ warp helpers
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// 128-bit streaming load that does not allocate in L1 (read-once code / vector streams)
+__device__ __forceinline__ uint4 ld_stream_u4(const uint4* p) {
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
+__device__ __forceinline__ float4 ld_stream_f4(const float4* p) {
+    float4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+    return r;
+}
+
+// ------------------------------------------------------------------ CTA-wide bitonic sort (ascending), n = power of two
+__device__ __forceinline__ void block_bitonic_sort(u64* buf, int n) {
+    for (int k = 2; k <= n; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int i = threadIdx.x; i < n; i += blockDim.x) {
+                int p = i ^ j;
+                if (p > i) {
+                    u64 a = buf[i], b = buf[p];
+                    bool up = ((i & k) == 0);
+                    if ((a > b) == up) { buf[i] = b; buf[p] = a; }
+                }
+            }
+            __syncthreads();
+        }
+    }
+}
+
+// ------------------------------------------------------------------ BlockSelect
+// Streaming "keep the R smallest keys" over a shared-memory array of C = 2^c entries.
+//   [0, R)       best-so-far (sorted after every compaction)
+//   [R, C)       pending area; threads append with an atomic counter
+// Protocol: between two CTA-uniform calls to maybe_compact() the CTA may push at most `burst`
+// keys; maybe_compact() sorts when fewer than `burst` pending slots remain, so push() never
+// overflows.  Keys are unique (score,index) pairs, so `key < thr` is an exact filter.
+struct BlockSelect {
+    u64* buf;   // shared, C entries
+    int* cnt;   // shared, pending count
+    u64* thr;   // shared, current R-th best key (VDB_KEY_MAX until R keys were seen)
+    int C, R, burst;
+
+    __device__ __forceinline__ void init(u64* b, int* c, u64* t, int C_, int R_, int burst_) {
+        buf = b; cnt = c; thr = t; C = C_; R = R_; burst = burst_;
+        for (int i = threadIdx.x; i < C; i += blockDim.x) buf[i] = VDB_KEY_MAX;
+        if (threadIdx.x == 0) { *cnt = 0; *thr = VDB_KEY_MAX; }
+        // caller must __syncthreads()
+    }
+    __device__ __forceinline__ u64 threshold() const { return *thr; }
+    __device__ __forceinline__ void push(u64 key) {
+        if (key < *thr) {
+            int p = atomicAdd(cnt, 1);
+            buf[R + p] = key;
+        }
+    }
+    // CTA-uniform, called by ALL threads after they issued their pushes of this burst.  The
+    // barrier-with-OR makes the decision uniform: the thread that pushed last sees the full count.
+    __device__ __forceinline__ void maybe_compact() {
+        int pending = *(volatile int*)cnt;
+        if (__syncthreads_or(pending + burst > C - R)) compact_after_barrier();
+    }
+    // requires: a barrier since the last push
+    __device__ __forceinline__ void compact_after_barrier() {
+        block_bitonic_sort(buf, C);
+        if (threadIdx.x == 0) { *cnt = 0; *thr = buf[R - 1]; }
+        __syncthreads();
+    }
+    __device__ __forceinline__ void finalize() {   // leaves buf[0..R) sorted ascending
+        __syncthreads();
+        compact_after_barrier();
+    }
+};
+
+__host__ __device__ __forceinline__ int select_capacity(int R, int burst) {
+    int c = next_pow2(R + 2 * burst);
+    return c < 256 ? 256 : c;
+}
+
+// (exact_f32.cu) select the k best of L keys per query and translate them to (value, id)
+int finalize_keys(const u64* keys, int Q, int L, int k, const int64_t* ids, int64_t idx_offset, int negate,
+                  float* out_d, int64_t* out_i, cudaStream_t st);
+#endif  // __CUDACC__
+
+}  // namespace vdb

@@ -1,0 +1,124 @@
+// Runtime plumbing of libvdb_b200.so: error strings, launch accounting, storage staging
+// (reference layer-1 memmap AoS -> SoA in HBM) and the per-row preparation kernel
+// (squared norms + bf16 mirror) that feeds the tensor-core scan.
+#include <stdarg.h>
+
+#include <atomic>
+
+#include "common.cuh"
+
+namespace vdb {
+
+static thread_local char g_err[512] = "";
+std::atomic<uint64_t> g_launches{0};
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int cuda_fail(cudaError_t e, const char* what, const char* file, int line) {
+    set_error("CUDA error %s (%s) at %s:%d in %s", cudaGetErrorName(e), cudaGetErrorString(e), file, line, what);
+    return VDB_ERR_CUDA;
+}
+
+void count_launch(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
+
+int sm_count() {
+    static int n = 0;
+    if (n == 0) {
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    }
+    return n;
+}
+
+int max_smem_optin() {
+    static int n = 0;
+    if (n == 0) {
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess) return 227 * 1024;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev) != cudaSuccess || n <= 0)
+            n = 227 * 1024;
+    }
+    return n;
+}
+
+// ---------------------------------------------------------------------------------------------
+// sqnorm[r] = sum_t x[r][t]^2 (fp32, lane-strided + shuffle tree) ; mirror[r][t] = bf16_rn(x[r][t])
+// One warp per row; 128-bit loads when D % 4 == 0.  HBM-bound: reads N*D*4, writes N*D*2 + N*4.
+__global__ void prepare_rows_kernel(const float* __restrict__ x, int64_t N, int D,
+                                    float* __restrict__ sqnorm, __nv_bfloat16* __restrict__ mirror) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t r = (((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5); r < N; r += warps) {
+        const float* row = x + r * D;
+        float acc = 0.f;
+        if ((D & 3) == 0) {
+            const float4* row4 = reinterpret_cast<const float4*>(row);
+            for (int t = lane; t < (D >> 2); t += 32) {
+                float4 v = ld_stream_f4(row4 + t);
+                acc = fmaf(v.x, v.x, acc); acc = fmaf(v.y, v.y, acc);
+                acc = fmaf(v.z, v.z, acc); acc = fmaf(v.w, v.w, acc);
+                if (mirror) {
+                    __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y);
+                    __nv_bfloat162 hi = __floats2bfloat162_rn(v.z, v.w);
+                    uint2 pk;
+                    pk.x = *reinterpret_cast<uint32_t*>(&lo);
+                    pk.y = *reinterpret_cast<uint32_t*>(&hi);
+                    *reinterpret_cast<uint2*>(mirror + r * D + 4 * t) = pk;
+                }
+            }
+        } else {
+            for (int t = lane; t < D; t += 32) {
+                float v = row[t];
+                acc = fmaf(v, v, acc);
+                if (mirror) mirror[r * D + t] = __float2bfloat16_rn(v);
+            }
+        }
+        acc = warp_sum(acc);
+        if (sqnorm && lane == 0) sqnorm[r] = acc;
+    }
+}
+
+}  // namespace vdb
+
+using namespace vdb;
+
+extern "C" {
+
+const char* vdb_last_error(void) { return vdb::g_err; }
+int vdb_abi_version(void) { return 1; }
+uint64_t vdb_launch_count(void) { return vdb::g_launches.load(); }
+
+int vdb_stage_aos_h2d(const void* host_records, int64_t n, int D, int64_t* ids, float* vecs, void* stream) {
+    VDB_REQUIRE(n >= 0 && D > 0, VDB_ERR_INVALID, "vdb_stage_aos_h2d: bad n=%lld D=%d", (long long)n, D);
+    if (n == 0) return VDB_OK;
+    VDB_REQUIRE(host_records && vecs, VDB_ERR_INVALID, "vdb_stage_aos_h2d: null pointer");
+    const size_t stride = 8 + 4 * (size_t)D;
+    const char* base = static_cast<const char*>(host_records);
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (ids) VDB_CUDA(cudaMemcpy2DAsync(ids, 8, base, stride, 8, (size_t)n, cudaMemcpyHostToDevice, s));
+    VDB_CUDA(cudaMemcpy2DAsync(vecs, 4 * (size_t)D, base + 8, stride, 4 * (size_t)D, (size_t)n,
+                               cudaMemcpyHostToDevice, s));
+    return VDB_OK;
+}
+
+int vdb_prepare_rows(const float* vecs, int64_t N, int D, float* sqnorm, void* bf16_mirror, void* stream) {
+    VDB_REQUIRE(N >= 0 && D > 0, VDB_ERR_INVALID, "vdb_prepare_rows: bad N=%lld D=%d", (long long)N, D);
+    if (N == 0) return VDB_OK;
+    VDB_REQUIRE(vecs != nullptr, VDB_ERR_INVALID, "vdb_prepare_rows: null input");
+    int blocks = sm_count() * 8;
+    int64_t need = (N + 7) / 8;
+    if (need < blocks) blocks = (int)need;
+    prepare_rows_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        vecs, N, D, sqnorm, static_cast<__nv_bfloat16*>(bf16_mirror));
+    count_launch(1);
+    VDB_CUDA(cudaGetLastError());
+    return VDB_OK;
+}
+
+}  // extern "C"

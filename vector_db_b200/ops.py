@@ -1,0 +1,195 @@
+"""Typed wrappers over the C ABI: torch CUDA tensors in, torch CUDA tensors out.
+
+Every function enqueues on torch's current stream and returns device tensors without
+synchronising (unless stated).  All compute happens in libvdb_b200.so; torch is used for
+device memory and streams only.
+"""
+from __future__ import annotations
+
+import threading
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import METRIC_COSINE, METRIC_L2, check, load, ptr
+
+_tls = threading.local()
+
+
+def _ws(name: str, nbytes: int, device) -> torch.Tensor:
+    """Per-thread, per-purpose grow-only workspace (search calls may come from many threads)."""
+    pool = getattr(_tls, "pool", None)
+    if pool is None:
+        pool = _tls.pool = {}
+    key = (name, device.index)
+    w = pool.get(key)
+    if w is None:
+        w = pool[key] = _lib.Workspace()
+    return w.get(nbytes, device)
+
+
+def _metric(metric) -> int:
+    if metric in (METRIC_L2, "l2", "L2", "euclidean"):
+        return METRIC_L2
+    if metric in (METRIC_COSINE, "cos", "cosine"):
+        return METRIC_COSINE
+    raise ValueError(f"unknown metric {metric!r}")
+
+
+def _f32(t: torch.Tensor, name: str) -> torch.Tensor:
+    if not t.is_cuda:
+        raise ValueError(f"{name} must be a CUDA tensor")
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t.contiguous()
+
+
+def prepare_rows(vecs: torch.Tensor, want_norm=True, want_bf16=True):
+    vecs = _f32(vecs, "vecs")
+    n, d = vecs.shape
+    sq = torch.empty(n, dtype=torch.float32, device=vecs.device) if want_norm else None
+    mir = torch.empty((n, d), dtype=torch.bfloat16, device=vecs.device) if want_bf16 else None
+    check(load().vdb_prepare_rows(ptr(vecs), n, d, ptr(sq), ptr(mir), _lib.stream_ptr(vecs.device)))
+    return sq, mir
+
+
+def exact_topk_f32(q: torch.Tensor, db: torch.Tensor, k: int, metric=METRIC_L2, ids: Optional[torch.Tensor] = None,
+                   row_mask: Optional[torch.Tensor] = None, n_rows: Optional[int] = None
+                   ) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Exact fp32 scan.  Returns (values f32 [Q,k], ids i64 [Q,k])."""
+    q = _f32(q, "q")
+    db = _f32(db, "db") if db.numel() else db
+    Q, D = q.shape
+    N = db.shape[0] if n_rows is None else int(n_rows)
+    dev = q.device
+    out_d = torch.empty((Q, k), dtype=torch.float32, device=dev)
+    out_i = torch.empty((Q, k), dtype=torch.int64, device=dev)
+    lib = load()
+    nbytes = lib.vdb_exact_topk_f32_workspace(Q, N, k)
+    ws = _ws("exact", nbytes, dev)
+    check(lib.vdb_exact_topk_f32(ptr(q), Q, ptr(db), ptr(ids), ptr(row_mask), N, D, k, _metric(metric), ptr(out_d),
+                                 ptr(out_i), ptr(ws), ws.numel(), _lib.stream_ptr(dev)))
+    return out_d, out_i
+
+
+def rerank_f32(q: torch.Tensor, db: torch.Tensor, cand: torch.Tensor, k: int, metric=METRIC_L2,
+               ids: Optional[torch.Tensor] = None, n_rows: Optional[int] = None):
+    q = _f32(q, "q")
+    Q, D = q.shape
+    cand = cand.to(torch.int32).contiguous()
+    R = cand.shape[1]
+    N = db.shape[0] if n_rows is None else int(n_rows)
+    out_d = torch.empty((Q, k), dtype=torch.float32, device=q.device)
+    out_i = torch.empty((Q, k), dtype=torch.int64, device=q.device)
+    check(load().vdb_rerank_f32(ptr(q), Q, ptr(db), ptr(ids), N, D, ptr(cand), R, k, _metric(metric), ptr(out_d),
+                                ptr(out_i), _lib.stream_ptr(q.device)))
+    return out_d, out_i
+
+
+def pq_encode(x: torch.Tensor, codebooks: torch.Tensor) -> torch.Tensor:
+    """x [N,D] fp32, codebooks [m,K,dsub] fp32 -> codes uint8 [N,m]."""
+    x = _f32(x, "x")
+    codebooks = _f32(codebooks, "codebooks")
+    n, d = x.shape
+    m, K, dsub = codebooks.shape
+    if m * dsub != d:
+        raise ValueError(f"codebooks {tuple(codebooks.shape)} do not tile dim {d}")
+    codes = torch.empty((n, m), dtype=torch.uint8, device=x.device)
+    check(load().vdb_pq_encode(ptr(x), n, d, m, K, ptr(codebooks), ptr(codes), _lib.stream_ptr(x.device)))
+    return codes
+
+
+def pq_kmeans_step(x: torch.Tensor, codebooks: torch.Tensor, labels: Optional[torch.Tensor] = None) -> None:
+    """One Lloyd round for all sub-spaces, in place on `codebooks` [m,K,dsub]."""
+    n, d = x.shape
+    m, K, dsub = codebooks.shape
+    lib = load()
+    nbytes = lib.vdb_pq_kmeans_workspace(m, K, dsub)
+    ws = _ws("kmeans", nbytes, x.device)
+    check(lib.vdb_pq_kmeans_step(ptr(x), n, d, m, K, ptr(codebooks), ptr(labels), ptr(ws), ws.numel(),
+                                 _lib.stream_ptr(x.device)))
+
+
+def pq_lut(q: torch.Tensor, codebooks: torch.Tensor) -> torch.Tensor:
+    """LUT [Q,m,K] fp32 of squared sub-space distances."""
+    q = _f32(q, "q")
+    codebooks = _f32(codebooks, "codebooks")
+    Q, d = q.shape
+    m, K, dsub = codebooks.shape
+    lut = torch.empty((Q, m, K), dtype=torch.float32, device=q.device)
+    check(load().vdb_pq_lut(ptr(q), Q, d, m, K, ptr(codebooks), ptr(lut), _lib.stream_ptr(q.device)))
+    return lut
+
+
+def pq_adc_topk(codes: torch.Tensor, lut: torch.Tensor, R: int, ids: Optional[torch.Tensor] = None,
+                n_rows: Optional[int] = None):
+    """codes uint8 [N,m], lut fp32 [Q,m,256] -> (d f32 [Q,R], idx i64 [Q,R]) by (d,row) ascending."""
+    if lut.shape[2] != 256:
+        raise ValueError("ADC scan needs 256-entry LUT rows (nbits=8); pad the codebooks")
+    Q, m = lut.shape[0], lut.shape[1]
+    N = codes.shape[0] if n_rows is None else int(n_rows)
+    dev = lut.device
+    out_d = torch.empty((Q, R), dtype=torch.float32, device=dev)
+    out_i = torch.empty((Q, R), dtype=torch.int64, device=dev)
+    lib = load()
+    nbytes = lib.vdb_pq_adc_topk_workspace(Q, N, m, R)
+    if nbytes == 0 and Q > 0:
+        raise ValueError(f"ADC scan: m={m} R={R} do not fit shared memory")
+    ws = _ws("adc", nbytes, dev)
+    check(lib.vdb_pq_adc_topk(ptr(codes), N, m, ptr(lut), Q, R, ptr(ids), ptr(out_d), ptr(out_i), ptr(ws),
+                              ws.numel(), _lib.stream_ptr(dev)))
+    return out_d, out_i
+
+
+def merge_topk(d: torch.Tensor, i: torch.Tensor, descending: bool = False):
+    """d,i [L,Q,k] (per-shard sorted lists) -> merged (d [Q,k], i [Q,k])."""
+    L, Q, k = d.shape
+    d = d.contiguous()
+    i = i.contiguous()
+    out_d = torch.empty((Q, k), dtype=torch.float32, device=d.device)
+    out_i = torch.empty((Q, k), dtype=torch.int64, device=d.device)
+    check(load().vdb_merge_topk(ptr(d), ptr(i), L, Q, k, int(descending), ptr(out_d), ptr(out_i),
+                                _lib.stream_ptr(d.device)))
+    return out_d, out_i
+
+
+def hnsw_search(q: torch.Tensor, db: torch.Tensor, n_rows: int, adj0: torch.Tensor, adj_up: torch.Tensor,
+                up_ptr: torch.Tensor, entry_row: int, max_level: int, ef: int, k: int,
+                alive: Optional[torch.Tensor] = None, flt: Optional[torch.Tensor] = None, want_stats: bool = False):
+    """Batched graph search.  Returns (dist f32 [Q,k], rows i32 [Q,k], stats u32 [Q,2] | None).
+    Synchronises once to read the visited-table overflow flag and retries with a larger table."""
+    q = _f32(q, "q")
+    Q, D = q.shape
+    dev = q.device
+    out_d = torch.empty((Q, k), dtype=torch.float32, device=dev)
+    out_r = torch.empty((Q, k), dtype=torch.int32, device=dev)
+    stats = torch.zeros((Q, 2), dtype=torch.int32, device=dev) if want_stats else None
+    lib = load()
+    deg0 = adj0.shape[1]
+    deg_up = adj_up.shape[1] if adj_up is not None and adj_up.dim() == 2 else deg0 // 2
+    nbytes = lib.vdb_hnsw_search_workspace(Q, ef, deg0)
+    hash_slots = 0
+    for _ in range(4):
+        ws = _ws("hnsw", nbytes, dev)
+        check(lib.vdb_hnsw_search(ptr(q), Q, ptr(db), n_rows, D, ptr(adj0), deg0, ptr(adj_up), deg_up, ptr(up_ptr),
+                                  entry_row, max_level, ef, k, ptr(alive), ptr(flt), hash_slots, ptr(out_d),
+                                  ptr(out_r), ptr(stats), ptr(ws), ws.numel(), _lib.stream_ptr(dev)))
+        if int(ws[:4].view(torch.int32).item()) == 0:
+            return out_d, out_r, stats
+        # a visited table filled up: force a (4x) larger table in global memory and retry
+        base = 1024
+        want = (ef + 32) * deg0 * 5 // 4
+        while base < want:
+            base *= 2
+        hash_slots = base * 4 if hash_slots == 0 else hash_slots * 4
+        nbytes = 256 + 8 * torch.cuda.get_device_properties(dev).multi_processor_count * hash_slots * 4
+    raise _lib.VdbError("hnsw_search: visited table overflow persists")
+
+
+def tc_supported(Q: int, N: int, D: int, k: int) -> bool:
+    """True when the tcgen05 tensor-core scan covers this shape (see vdb_exact_topk_tc)."""
+    lib = load()
+    if not hasattr(lib, "vdb_exact_topk_tc"):
+        return False
+    return D % 64 == 0 and D <= 1024 and k <= 64 and N >= 4096 and Q >= 1
