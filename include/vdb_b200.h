@@ -46,6 +46,14 @@ int vdb_abi_version(void);
 /* number of kernels this library launched from the calling process so far (bench.py gpu_launches) */
 uint64_t vdb_launch_count(void);
 
+/* Per-kernel timing for bench.py: while enabled, every launch of a dominant kernel is bracketed by
+ * CUDA events on its own stream.  vdb_profile_read() waits for the slot's events, returns the
+ * number of launches and their summed duration, and clears the slot.
+ * Slots: 0 exact fp32 scan, 1 exact tensor-core scan, 2 ADC scan, 3 PQ encode, 4 HNSW search,
+ * 5 rerank, 6 top-k finalise/merge, 7 HNSW insert. */
+void vdb_profile_enable(int on);
+int vdb_profile_read(int slot, int* launches, float* total_ms);
+
 /* ---- a9/a10 storage staging ---------------------------------------------------------------
  * De-interleave `n` records of the reference's layer-1 memmap layout
  * {int64 id; float32 embedding[D]} (stride 8+4D, src/vector_db/storage.py:135-144) from PINNED

@@ -75,6 +75,26 @@ def gen_pq(ref_pq):
                         codes_y=codes_y, chunk_kat=chunk_kat, kat1=np.int64(kat1), kat2=kat2)
 
 
+def gen_pq8(ref_pq):
+    """dsub = 8: numpy's pairwise_sum switches to its 8-accumulator tree at n >= 8, the case the CUDA
+    encode kernel has to reproduce bit for bit (BASELINE configs use dsub = 8)."""
+    np.random.seed(4242)
+    rng = np.random.default_rng(4242)
+    X = rng.standard_normal((1200, 64)).astype(np.float32)
+    svc = ref_pq.ProductQuantizationService(k=64, chunks=8, dim=64)
+    codes = svc.compress(X)
+    cents = np.stack([np.asarray(c, dtype=np.float32) for c in svc.centroids])
+    Y = rng.standard_normal((600, 64)).astype(np.float32)
+    codes_y = np.array([svc._compress_embedding(y, svc.centroids) for y in Y], dtype=np.int64)
+    # dsub = 12 exercises the tree + remainder loop
+    svc12 = ref_pq.ProductQuantizationService(k=16, chunks=2, dim=24)
+    X12 = rng.standard_normal((300, 24)).astype(np.float32)
+    codes12 = svc12.compress(X12)
+    cents12 = np.stack([np.asarray(c, dtype=np.float32) for c in svc12.centroids])
+    np.savez_compressed(os.path.join(OUT, "pq8.npz"), X=X, codes=codes, centroids=cents, Y=Y, codes_y=codes_y,
+                        X12=X12, codes12=codes12, centroids12=cents12)
+
+
 def gen_hnsw(ref_hnsw, Storage, Node, tag, n, dim, M, efc, nq, ef, k, seed):
     rng = np.random.default_rng(seed)
     X = rng.standard_normal((n, dim)).astype(np.float32)
@@ -132,6 +152,7 @@ def main():
     ref_hnsw, ref_pq, Storage, Node, ref_dist, topk_sorted = _import_reference()
     gen_exact(ref_dist, topk_sorted)
     gen_pq(ref_pq)
+    gen_pq8(ref_pq)
     gen_hnsw(ref_hnsw, Storage, Node, "small", n=400, dim=16, M=8, efc=50, nq=24, ef=50, k=10, seed=11)
     gen_hnsw(ref_hnsw, Storage, Node, "medium", n=2000, dim=48, M=16, efc=100, nq=32, ef=64, k=10, seed=12)
     print("golden fixtures written to", os.path.abspath(OUT))

@@ -1,0 +1,142 @@
+"""GPU parity: exact scan / rerank / merge through the C ABI vs the oracle and the golden vectors."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+def _dev():
+    return torch.device("cuda", 0)
+
+
+def _t(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).to(_dev())
+
+
+def _check_topk(D, I, Dref, Iref, rtol=1e-5):
+    """ids equal except where the reference distances tie within fp32 tolerance."""
+    D, I = D.cpu().numpy(), I.cpu().numpy()
+    np.testing.assert_allclose(D, Dref, rtol=rtol, atol=1e-6)
+    bad = np.argwhere(I != Iref)
+    for qi, j in bad:
+        # a mismatch is only acceptable inside a run of (near-)equal distances
+        assert abs(Dref[qi, j] - D[qi, j]) <= rtol * max(1.0, abs(Dref[qi, j]))
+        assert I[qi, j] in Iref[qi] or np.isclose(D[qi, j], Dref[qi, -1], rtol=rtol)
+    assert len(bad) <= 0.001 * I.size + 2
+
+
+def test_golden_exact_l2(golden_dir):
+    from vector_db_b200 import ops
+    g = np.load(os.path.join(golden_dir, "exact_l2.npz"))
+    D, I = ops.exact_topk_f32(_t(g["Q"]), _t(g["X"]), 10, "l2", ids=_t(g["ids"]))
+    np.testing.assert_array_equal(I.cpu().numpy(), g["I"])
+    np.testing.assert_allclose(D.cpu().numpy(), g["D"], rtol=1e-5, atol=0)
+    assert D[0, 0].item() == 0.0                                   # self query (test_hnsw.py:103-111)
+    assert I[0, 0].item() == g["ids"][5] and I[0, 1].item() == g["ids"][17]   # duplicate row: smaller id first
+
+
+@pytest.mark.parametrize("n,d,q,k", [(20000, 96, 33, 10), (5000, 50, 7, 100), (3000, 384, 1, 5), (777, 13, 20, 3)])
+def test_exact_l2_vs_oracle(n, d, q, k):
+    from vector_db_b200 import ops
+    rng = np.random.default_rng(n + d)
+    X = rng.standard_normal((n, d)).astype(np.float32)
+    Q = rng.standard_normal((q, d)).astype(np.float32)
+    ids = rng.permutation(n * 2)[:n].astype(np.int64)
+    Dref, Iref = O.exact_l2_topk(X, ids, Q, k)
+    D, I = ops.exact_topk_f32(_t(Q), _t(X), k, "l2", ids=_t(ids))
+    _check_topk(D, I, Dref, Iref)
+
+
+def test_exact_cosine_vs_oracle():
+    from vector_db_b200 import ops
+    rng = np.random.default_rng(5)
+    X = rng.standard_normal((9000, 64)).astype(np.float32) * rng.uniform(0.1, 5, (9000, 1)).astype(np.float32)
+    Q = rng.standard_normal((19, 64)).astype(np.float32)
+    ids = np.arange(9000, dtype=np.int64)
+    Sref, Iref = O.exact_cosine_topk(X, ids, Q, 10)
+    S, I = ops.exact_topk_f32(_t(Q), _t(X), 10, "cosine", ids=_t(ids))
+    np.testing.assert_allclose(S.cpu().numpy(), Sref, rtol=1e-4, atol=1e-6)
+    assert (I.cpu().numpy() == Iref).mean() > 0.995
+    assert np.all(np.diff(S.cpu().numpy(), axis=1) <= 0)
+
+
+def test_exact_short_db_pads_and_mask():
+    from vector_db_b200 import ops
+    X = np.eye(3, 8, dtype=np.float32)
+    D, I = ops.exact_topk_f32(_t(X[:1]), _t(X), 5, "l2", ids=_t(np.array([4, 2, 9], dtype=np.int64)))
+    assert I[0].tolist() == [4, 2, 9, -1, -1] and D[0, 0].item() == 0 and torch.isinf(D[0, 3])
+    rng = np.random.default_rng(1)
+    Y = rng.standard_normal((4000, 32)).astype(np.float32)
+    Q = rng.standard_normal((5, 32)).astype(np.float32)
+    allowed = np.arange(0, 4000, 3)
+    words = np.zeros((4000 + 31) // 32, dtype=np.uint32)
+    np.bitwise_or.at(words, allowed >> 5, np.uint32(1) << (allowed & 31).astype(np.uint32))
+    D, I = ops.exact_topk_f32(_t(Q), _t(Y), 10, "l2", row_mask=_t(words.view(np.int32)))
+    Dref, Iref = O.exact_l2_topk(Y[allowed], allowed, Q, 10)
+    _check_topk(D, I, Dref, Iref)
+
+
+def test_rerank_and_merge():
+    from vector_db_b200 import ops
+    rng = np.random.default_rng(2)
+    X = rng.standard_normal((6000, 40)).astype(np.float32)
+    Q = rng.standard_normal((9, 40)).astype(np.float32)
+    cand = rng.integers(0, 6000, (9, 300)).astype(np.int32)
+    cand[:, 7] = -1
+    cand[:, 8] = cand[:, 9]                                          # duplicates collapse
+    D, I = ops.rerank_f32(_t(Q), _t(X), _t(cand), 10, "l2")
+    for qi in range(9):
+        rows = np.unique(cand[qi][cand[qi] >= 0])
+        Dref, Iref = O.exact_l2_topk(X[rows], rows, Q[qi:qi + 1], 10)
+        np.testing.assert_array_equal(I[qi].cpu().numpy(), Iref[0])
+        np.testing.assert_allclose(D[qi].cpu().numpy(), Dref[0], rtol=1e-5)
+    # merge: split the db in 4 id-ordered shards, search each, merge == global search
+    ids = np.arange(6000, dtype=np.int64)
+    parts_d, parts_i = [], []
+    for s in range(4):
+        sl = slice(s * 1500, (s + 1) * 1500)
+        d, i = ops.exact_topk_f32(_t(Q), _t(X[sl]), 10, "l2", ids=_t(ids[sl]))
+        parts_d.append(d)
+        parts_i.append(i)
+    md, mi = ops.merge_topk(torch.stack(parts_d), torch.stack(parts_i))
+    Dref, Iref = O.exact_l2_topk(X, ids, Q, 10)
+    _check_topk(md, mi, Dref, Iref)
+
+
+def test_exact_index_host_api_and_util():
+    from vector_db_b200.indexing import ExactIndex
+    from vector_db_b200.util import euclidean_vector_distance, top_k_indices_sorted
+    rng = np.random.default_rng(3)
+    X = rng.standard_normal((5000, 24)).astype(np.float32)
+    idx = ExactIndex(24, "l2", engine="f32")
+    idx.add(range(100, 5100), X)
+    D, I = idx.search(X[:4], 3)
+    assert I[:, 0].tolist() == [100, 101, 102, 103] and np.all(D[:, 0] == 0)
+    D2, I2 = idx.search(X[:4], 3, filter_ids={100, 2000, 2001})
+    assert set(I2[0].tolist()) == {100, 2000, 2001}
+    d = euclidean_vector_distance(X[0], X[1])
+    assert isinstance(d, np.float32) and np.isclose(d, O.l2_distance(X[0], X[1]), rtol=1e-6)
+    s = rng.standard_normal(3000).astype(np.float32)
+    np.testing.assert_array_equal(top_k_indices_sorted(s, 7), O.topk_largest_sorted(s, 7))
+
+
+def test_large_scan_properties():
+    """Size-independent properties at a size the oracle cannot finish quickly: self-queries come back
+    first with distance 0, results are sorted, and a sharded search merges to the same answer."""
+    from vector_db_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(7)
+    X = torch.randn((200_000, 128), device=_dev(), generator=g)
+    qrows = torch.arange(0, 200_000, 3125, device=_dev())
+    Q = X[qrows].clone()
+    D, I = ops.exact_topk_f32(Q, X, 10, "l2")
+    assert torch.equal(I[:, 0], qrows) and torch.all(D[:, 0] == 0)
+    assert torch.all(D[:, 1:] >= D[:, :-1])
+    d1, i1 = ops.exact_topk_f32(Q, X[:100_000], 10, "l2")
+    d2, i2 = ops.exact_topk_f32(Q, X[100_000:], 10, "l2")
+    md, mi = ops.merge_topk(torch.stack([d1, d2]), torch.stack([i1, i2 + 100_000]))
+    assert torch.equal(mi, I) and torch.equal(md, D)

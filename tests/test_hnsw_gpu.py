@@ -1,0 +1,160 @@
+"""GPU parity: HNSW build + search vs graphs / results produced by the reference itself
+(tests/golden/hnsw_*.npz) and vs the oracle restatement; plus the reference's own property tests
+(tests/indexing/test_hnsw.py) re-stated against the GPU class."""
+import os
+import pickle
+import random
+
+import numpy as np
+import pytest
+import torch
+
+from oracle.hnsw_oracle import HnswOracle
+
+pytestmark = pytest.mark.gpu
+
+
+def _nodes(X, ids=None):
+    from vector_db_b200.types import Node
+    ids = range(X.shape[0]) if ids is None else ids
+    return [Node(id=int(i), embedding=X[j]) for j, i in enumerate(ids)]
+
+
+def _graph_rows(index):
+    rows = []
+    for nid in index.node_store:
+        for lvl, lst in index.node_store[nid].neighbors.items():
+            for pos, nb in enumerate(lst):
+                rows.append((nid, lvl, pos, nb))
+    return np.array(sorted(rows), dtype=np.int64)
+
+
+def _golden_graph_dict(g):
+    store = {}
+    n = g["X"].shape[0]
+    for i in range(n):
+        store[i] = {"id": i, "neighbors": {l: [] for l in range(int(g["node_levels"][i]) + 1)}}
+    for nid, lvl, pos, nb in sorted(map(tuple, g["graph"])):
+        store[int(nid)]["neighbors"].setdefault(int(lvl), []).append(int(nb))
+    M = int(g["M"])
+    return {"M": M, "M_max": M, "M_max0": 2 * M, "ef_construction": int(g["efc"]), "max_level": int(g["max_level"]),
+            "entry_node_id": int(g["entry"]), "node_store": store}
+
+
+@pytest.mark.parametrize("name", ["hnsw_small.npz", "hnsw_medium.npz"])
+def test_search_on_reference_graph_matches_reference(golden_dir, name):
+    """Import the graph the reference built; GPU traversal must return the reference's ids, distances
+    and distance-evaluation counts, with and without filter_ids."""
+    from vector_db_b200.indexing import HNSW
+    g = np.load(os.path.join(golden_dir, name))
+    X = g["X"]
+    idx = HNSW(M=int(g["M"]), ef_construction=int(g["efc"]), rng=random.Random(42))
+    for node in _nodes(X):
+        idx.storage.save(node)
+    idx.load_graph(_golden_graph_dict(g))
+    assert idx.entry_node_id == int(g["entry"]) and idx.max_level == int(g["max_level"])
+    k, ef = int(g["k"]), int(g["ef"])
+    D, I, st = idx.search_batch(g["Q"], k, ef=ef, return_stats=True)
+    np.testing.assert_array_equal(I, g["I"])
+    np.testing.assert_allclose(D, g["D"], rtol=1e-5, atol=1e-6)
+    np.testing.assert_array_equal(st[:, 0], g["evals"])
+    allowed = {i for i in range(X.shape[0]) if i % 3 == 0}
+    Df, If = idx.search_batch(g["Q"], k, ef=ef, filter_ids=allowed)
+    np.testing.assert_array_equal(If, g["If"])
+    np.testing.assert_allclose(Df, g["Df"], rtol=1e-5, atol=1e-6)
+    res = idx.search(g["Q"][0], k=k, ef=ef)                      # single-query API, self query
+    assert res[0][0].id == 3 and res[0][1] < 1e-6 and isinstance(res[0][1], np.float32)
+
+
+@pytest.mark.parametrize("name", ["hnsw_small.npz", "hnsw_medium.npz"])
+def test_gpu_build_equals_reference_graph(golden_dir, name):
+    """Sequential-semantics insert kernel + random.Random(42) level draws == the reference's graph,
+    link order included, and the same number of distance evaluations."""
+    from vector_db_b200.indexing import HNSW
+    g = np.load(os.path.join(golden_dir, name))
+    idx = HNSW(M=int(g["M"]), ef_construction=int(g["efc"]), rng=random.Random(42))
+    nodes = _nodes(g["X"])
+    idx.build_index(nodes[:100])
+    for node in nodes[100:130]:
+        idx.insert_node(node)                                      # one-at-a-time path
+    idx.build_index(nodes[130:])
+    assert idx.entry_node_id == int(g["entry"]) and idx.max_level == int(g["max_level"])
+    np.testing.assert_array_equal(_graph_rows(idx), np.array(sorted(map(tuple, g["graph"])), dtype=np.int64))
+    assert idx.distance_evaluations() == int(g["build_evals"])
+    D, I = idx.search_batch(g["Q"], int(g["k"]), ef=int(g["ef"]))
+    np.testing.assert_array_equal(I, g["I"])
+
+
+def test_reference_property_tests_restated(tmp_path):
+    """tests/indexing/test_hnsw.py: init state, idempotent insert, recall vs brute force,
+    level-0 reachability, delete, pickle round trip."""
+    from vector_db_b200.indexing import HNSW
+    from vector_db_b200.types import Node
+    idx = HNSW(M=8, ef_construction=50, rng=random.Random(42))
+    assert idx.entry_node_id is None and idx.max_level == -1 and len(idx.node_store) == 0   # :19-29
+    assert idx.search(np.zeros(16, np.float32), k=3) == []
+    rs = np.random.RandomState(0)
+    X = rs.rand(100, 16).astype(np.float32)
+    idx.build_index(_nodes(X))
+    assert len(idx.node_store) == 100 and idx.node_store[5].id == 5
+    before = idx.node_store[7].neighbors
+    idx.insert_node(Node(id=7, embedding=X[7]))                                            # :309-327
+    assert idx.node_store[7].neighbors == before and len(idx.node_store) == 100
+    hits = 0
+    for _ in range(10):                                                                    # :113-153
+        q = rs.rand(16).astype(np.float32)
+        got = {n.id for n, _ in idx.search(q, k=5, ef=50)}
+        truth = {i for _, i in sorted((float(np.linalg.norm(q - X[i])), i) for i in range(100))[:5]}
+        hits += len(got & truth) / 5 >= 0.7
+    assert hits >= 8
+    seen, stack = {idx.entry_node_id}, [idx.entry_node_id]                                # :155-185
+    while stack:
+        for nb in idx.node_store[stack.pop()].neighbors.get(0, []):
+            if nb not in seen:
+                seen.add(nb)
+                stack.append(nb)
+    assert len(seen) >= 90
+    nb10 = idx.node_store[10].neighbors
+    idx.delete_node(10)                                                                    # :187-218
+    assert 10 not in idx.node_store and len(idx.node_store) == 99
+    for lvl, lst in nb10.items():
+        for nb in lst:
+            assert 10 not in idx.node_store[nb].neighbors.get(lvl, [])
+    assert all(n.id != 10 for n, _ in idx.search(X[10], k=5, ef=50))
+    entry = idx.entry_node_id
+    idx.delete_node(entry)
+    assert idx.entry_node_id is not None and idx.entry_node_id != entry
+    assert len(idx.search(X[3], k=5, ef=50)) == 5
+    # pickle round trip in the reference's schema (:220-256)
+    idx.index_file = tmp_path / "g.index.pkl"
+    idx.save_index()
+    data = pickle.load(open(idx.index_file, "rb"))
+    assert set(data) == {"M", "M_max", "M_max0", "ef_construction", "max_level", "entry_node_id", "node_store"}
+    idx2 = HNSW(M=8, ef_construction=50, rng=random.Random(42), storage=idx.storage, index_file=idx.index_file)
+    assert idx2.entry_node_id == idx.entry_node_id and idx2.max_level == idx.max_level
+    a = [(n.id, float(d)) for n, d in idx.search(X[3], k=5, ef=50)]
+    b = [(n.id, float(d)) for n, d in idx2.search(X[3], k=5, ef=50)]
+    assert a == b
+
+
+def test_oracle_and_gpu_agree_on_larger_graph():
+    """N beyond the golden files: the oracle restatement (pinned to the reference) builds the graph,
+    the GPU builds it too; graphs, results and eval counts must agree."""
+    from vector_db_b200.indexing import HNSW
+    rng = np.random.default_rng(99)
+    X = rng.standard_normal((3000, 64)).astype(np.float32)
+    Q = rng.standard_normal((40, 64)).astype(np.float32)
+    o = HnswOracle(12, 80)
+    for i in range(3000):
+        o.insert(i, X[i])
+    idx = HNSW(M=12, ef_construction=80, rng=random.Random(42))
+    idx.build_index(_nodes(X))
+    ref_rows = sorted((nid, lvl, pos, nb) for nid, d in o.links.items() for lvl, lst in d.items()
+                      for pos, nb in enumerate(lst))
+    np.testing.assert_array_equal(_graph_rows(idx), np.array(ref_rows, dtype=np.int64))
+    D, I, st = idx.search_batch(Q, 10, ef=100, return_stats=True)
+    for qi in range(40):
+        o.n_evals = 0
+        res = o.search(Q[qi], 10, 100)
+        assert [r[1] for r in res] == I[qi].tolist()
+        assert o.n_evals == st[qi, 0]

@@ -116,3 +116,10 @@ def test_hnsw_oracle_reproduces_reference_graph_and_search(golden_dir):
                                    int(arr["max_level"]), g["Q"][qi], k, ef)
             assert [int(arr["ids"][r[1]]) for r in ra] == [r[1] for r in res] and ev == int(g["evals"][qi])
         assert g["D"][0, 0] < 1e-6 and g["I"][0, 0] == 3     # self query, test_hnsw.py:103-111
+
+
+def test_pq_dsub8_and_dsub12_codes_match_reference(golden_dir):
+    g = _load(golden_dir, "pq8.npz")
+    np.testing.assert_array_equal(O.pq_encode(g["Y"], list(g["centroids"])), g["codes_y"])
+    np.testing.assert_array_equal(O.pq_encode(g["X"], list(g["centroids"])), g["codes"])
+    np.testing.assert_array_equal(O.pq_encode(g["X12"], list(g["centroids12"])), g["codes12"])

@@ -1,0 +1,97 @@
+"""GPU parity: PQ encode (bit-exact vs the reference's codes), k-means step, LUT and ADC scan."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _t(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).to(DEV)
+
+
+def test_encode_bit_exact_vs_reference_codes(golden_dir):
+    from vector_db_b200 import ops
+    g = np.load(os.path.join(golden_dir, "pq.npz"))           # dsub = 4 (plain loop order)
+    cb = _t(g["centroids"])
+    np.testing.assert_array_equal(ops.pq_encode(_t(g["Y"]), cb).cpu().numpy(), g["codes_y"])
+    np.testing.assert_array_equal(ops.pq_encode(_t(g["X"]), cb).cpu().numpy(), g["codes"])
+    g8 = np.load(os.path.join(golden_dir, "pq8.npz"))          # dsub = 8 (numpy's 8-way tree)
+    cb8 = _t(g8["centroids"])
+    np.testing.assert_array_equal(ops.pq_encode(_t(g8["Y"]), cb8).cpu().numpy(), g8["codes_y"])
+    np.testing.assert_array_equal(ops.pq_encode(_t(g8["X"]), cb8).cpu().numpy(), g8["codes"])
+    np.testing.assert_array_equal(ops.pq_encode(_t(g8["X12"]), _t(g8["centroids12"])).cpu().numpy(), g8["codes12"])
+
+
+def test_service_kats_and_compress_contract(golden_dir):
+    from vector_db_b200.inference.pq import ProductQuantizationService as PQ
+    svc = PQ(k=3, chunks=2, dim=4)
+    c = np.array([[0, 0], [1, 1], [2, 2]], dtype=np.float32)
+    assert svc._find_nearest_centroid(np.array([0.9, 1.1], np.float32), c) == 1          # test_pq.py:78-90
+    out = svc._compress_embedding(np.array([0.9, 1.1, 2.1, 1.9], np.float32), [c, c])   # test_pq.py:92-116
+    assert out.dtype == np.int64 and out.tolist() == [1, 2]
+    rng = np.random.default_rng(0)
+    X = rng.random((500, 32), dtype=np.float32)
+    svc = PQ(k=16, chunks=4, dim=32)
+    np.random.seed(1)
+    codes = svc.compress(X)                                                               # test_pq.py:118-176
+    assert codes.shape == (500, 4) and codes.dtype == np.int64 and codes.min() >= 0 and codes.max() < 16
+    assert len(svc.centroids) == 4 and all(cc.shape == (16, 8) and cc.dtype == np.float32 for cc in svc.centroids)
+    np.testing.assert_array_equal(codes, O.pq_encode(X, svc.centroids))
+    with pytest.raises(ValueError):
+        PQ(k=600, chunks=4, dim=32).compress(X)
+
+
+def test_kmeans_matches_lloyd_restatement():
+    from vector_db_b200.inference.pq import ProductQuantizationService as PQ
+    rng = np.random.default_rng(3)
+    centers = rng.standard_normal((8, 8)).astype(np.float32) * 4
+    X = (centers[rng.integers(0, 8, 3000)] + 0.3 * rng.standard_normal((3000, 8))).astype(np.float32)
+    init = rng.choice(3000, 8, replace=False)
+    svc = PQ(k=8, chunks=2, dim=8)
+    cents = svc.fit(X, init_rows=init, iters=25)
+    for j in range(2):
+        ref, _ = O.kmeans_lloyd(X[:, 4 * j:4 * j + 4], X[init, 4 * j:4 * j + 4], 25)
+        np.testing.assert_allclose(cents[j], ref, rtol=1e-3, atol=1e-3)
+
+
+@pytest.mark.parametrize("n,m,dsub,q,R", [(30000, 16, 4, 9, 10), (20000, 48, 2, 5, 10), (20000, 48, 2, 3, 700),
+                                         (5000, 5, 3, 2, 17), (100, 8, 4, 6, 10), (9000, 32, 2, 1, 64)])
+def test_lut_and_adc_vs_oracle(n, m, dsub, q, R):
+    from vector_db_b200 import ops
+    rng = np.random.default_rng(n + m)
+    d = m * dsub
+    cents = [rng.standard_normal((256, dsub)).astype(np.float32) for _ in range(m)]
+    codes = rng.integers(0, 256, (n, m)).astype(np.uint8)
+    Q = rng.standard_normal((q, d)).astype(np.float32)
+    lut_ref = O.adc_lut(Q, cents)
+    lut = ops.pq_lut(_t(Q), _t(np.stack(cents)))
+    np.testing.assert_array_equal(lut.cpu().numpy(), lut_ref)          # same fp32 operation order
+    R_eff = min(R, n)
+    Dref, Iref = O.adc_scan_topk(codes, lut_ref, R_eff)
+    D, I = ops.pq_adc_topk(_t(codes), lut, R_eff)
+    np.testing.assert_array_equal(D.cpu().numpy(), Dref)
+    np.testing.assert_array_equal(I.cpu().numpy(), Iref)
+
+
+def test_pq_index_end_to_end_recall_with_rerank(golden_dir):
+    from vector_db_b200.inference.pq import PQIndex
+    g = np.load(os.path.join(golden_dir, "pq8.npz"))
+    cents = list(g["centroids"])                                       # K = 64 < 256: LUT rows padded
+    X = g["X"]
+    idx = PQIndex(cents, keep_vectors=True)
+    idx.add(X, ids=np.arange(1200) + 5000)
+    Q = g["Y"][:16]
+    D, I = idx.search(Q, 10)
+    Dref, Iref = O.adc_scan_topk(g["codes"], O.adc_lut(Q, cents), 10, ids=np.arange(1200) + 5000)
+    np.testing.assert_array_equal(I, Iref)
+    np.testing.assert_array_equal(D, Dref)
+    De, Ie = idx.search(Q, 10, shortlist=1200, rerank=True)            # full shortlist -> exact answer
+    Dx, Ix = O.exact_l2_topk(X, np.arange(1200) + 5000, Q, 10)
+    np.testing.assert_array_equal(Ie, Ix)
+    np.testing.assert_allclose(De, Dx, rtol=1e-5)

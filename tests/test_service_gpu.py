@@ -1,0 +1,72 @@
+"""GPU: IndexingService + MMapNodeStorage drop-in behaviour (tests/services/test_indexing_service.py,
+tests/inference/test_mmap_vector_store.py restated) and the memmap -> pinned -> HBM staging path."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _cfg(tmp_path, extra=""):
+    p = tmp_path / "config.yaml"
+    p.write_text("index:\n  M: 8\n  ef_construction: 50\n  flush_threshold: 20\n" + extra +
+                 "vector_db:\n  dimension: 16\n  capacity: 256\n")
+    return str(p)
+
+
+def test_indexing_service_dropin(tmp_path):
+    from vector_db_b200.services import IndexingService
+    from vector_db_b200.storage import MMapNodeStorage
+    from vector_db_b200.types import Node
+    st = MMapNodeStorage(tmp_path / "db.embeddings.npy", tmp_path / "db.metadata.npy", dim=16, capacity=256)
+    svc = IndexingService(st, _cfg(tmp_path))
+    assert not svc.is_index_loaded() and svc.get_index_size() == 0
+    assert svc.index.M == 8 and svc.index.ef_construction == 50 and svc.flush_threshold == 20
+    rng = np.random.default_rng(0)
+    X = rng.random((40, 16), dtype=np.float32)
+    for i in range(40):
+        svc.insert_node(Node(id=i, embedding=X[i], content=f"doc {i}", metadata={"parity": i % 2}))
+    assert svc.get_index_size() == 40
+    assert svc.index_file.exists() and not svc._index_modified          # flush_threshold reached -> saved
+    res = svc.search(X[5], k=3, ef=50, pq_chunks=4, custom_arg=1)        # extra kwargs ignored (hnsw.py:338)
+    assert len(res) == 3 and res[0][0].id == 5 and res[0][1] < 1e-6
+    assert res[0][0].content == "doc 5" and res[0][0].metadata == {"parity": 1}
+    even = {i for i in range(40) if i % 2 == 0}
+    assert all(n.id in even for n, _ in svc.search(X[5], k=5, ef=50, filter_ids=even))
+    assert svc.search(X[5], k=5, filter_ids=set()) == []
+    svc.delete_node(5)
+    assert svc._index_modified and all(n.id != 5 for n, _ in svc.search(X[5], k=5, ef=50))
+    svc.force_save_index()
+    st.close()
+    st2 = MMapNodeStorage(tmp_path / "db.embeddings.npy", tmp_path / "db.metadata.npy", dim=16, capacity=256)
+    svc2 = IndexingService(st2, _cfg(tmp_path, "  ef_search: 64\n"))
+    assert svc2.is_index_loaded() and svc2.get_index_size() == 39 and svc2.ef_search == 64
+    a = [(n.id, float(d)) for n, d in svc.search(X[7], k=5, ef=64)]
+    b = [(n.id, float(d)) for n, d in svc2.search(X[7], k=5)]
+    assert a == b
+
+
+def test_stage_memmap_to_hbm(tmp_path):
+    from vector_db_b200.storage import MMapNodeStorage
+    from vector_db_b200.types import Node
+    dim = 24
+    st = MMapNodeStorage(tmp_path / "s.embeddings.npy", tmp_path / "s.metadata.npy", dim=dim, capacity=300)
+    rng = np.random.default_rng(1)
+    X = rng.standard_normal((200, dim)).astype(np.float32)
+    # write layer 1 directly (vectorised) the way a bulk loader would, then reopen to index it
+    st.embeddings["id"][:200] = np.arange(200) * 7
+    st.embeddings["embedding"][:200] = X
+    st.embeddings.flush()
+    st.close()
+    st = MMapNodeStorage(tmp_path / "s.embeddings.npy", tmp_path / "s.metadata.npy", dim=dim, capacity=300)
+    assert st.size() == 200
+    st.delete(21)                                   # slot 3 becomes a hole (id 0, zero vector)
+    ids, vecs = st.stage_to_device(chunk_records=64)
+    keep = np.array([i for i in range(200) if i != 3])
+    np.testing.assert_array_equal(ids.cpu().numpy(), keep * 7)
+    np.testing.assert_array_equal(vecs.cpu().numpy(), X[keep])
+    from vector_db_b200.indexing import ExactIndex
+    idx = ExactIndex(dim, engine="f32")
+    idx.add_device(ids, vecs)
+    D, I = idx.search(X[10:12], 1)
+    assert I[:, 0].tolist() == [70, 77] and np.all(D[:, 0] == 0)

@@ -23,6 +23,8 @@ SIGNATURES = {
     "vdb_last_error": (C.c_char_p, []),
     "vdb_abi_version": (_i, []),
     "vdb_launch_count": (C.c_uint64, []),
+    "vdb_profile_enable": (None, [_i]),
+    "vdb_profile_read": (_i, [_i, C.POINTER(C.c_int), C.POINTER(C.c_float)]),
     "vdb_stage_aos_h2d": (_i, [_p, _i64, _i, _p, _p, _p]),
     "vdb_prepare_rows": (_i, [_p, _i64, _i, _p, _p, _p]),
     "vdb_exact_topk_f32_workspace": (_sz, [_i, _i64, _i]),
@@ -98,6 +100,21 @@ def require_cuda() -> torch.device:
     if not torch.cuda.is_available():
         raise VdbError("vector_db_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
     return torch.device("cuda", torch.cuda.current_device())
+
+
+PROF_SLOTS = {"exact_f32": 0, "exact_tc": 1, "adc_scan": 2, "pq_encode": 3, "hnsw_search": 4, "rerank": 5,
+              "finalize": 6, "hnsw_insert": 7}
+
+
+def profile_enable(on: bool) -> None:
+    load().vdb_profile_enable(int(on))
+
+
+def profile_read(slot: str):
+    """(launches, total_ms) of a kernel slot since the last read; waits for its events."""
+    n, ms = C.c_int(0), C.c_float(0.0)
+    check(load().vdb_profile_read(PROF_SLOTS[slot], C.byref(n), C.byref(ms)))
+    return n.value, ms.value
 
 
 def launch_count() -> int:

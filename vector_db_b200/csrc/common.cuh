@@ -36,6 +36,16 @@ int sm_count();
 int max_smem_optin();
 void count_launch(int n);
 
+// Optional per-kernel timing (bench.py): when enabled, a ProfScope brackets ONE kernel launch with a
+// pair of CUDA events on the launching stream; vdb_profile_read() sums and clears a slot.
+enum ProfSlot { kProfExactF32 = 0, kProfExactTC = 1, kProfAdcScan = 2, kProfPqEncode = 3, kProfHnswSearch = 4,
+                kProfRerank = 5, kProfFinalize = 6, kProfHnswInsert = 7, kProfSlots = 8 };
+struct ProfScope {
+    int slot; cudaStream_t st; bool on;
+    ProfScope(int slot_, cudaStream_t st_);
+    ~ProfScope();
+};
+
 // ------------------------------------------------------------------ keys
 typedef unsigned long long u64;
 #define VDB_KEY_MAX 0xFFFFFFFFFFFFFFFFull

@@ -347,6 +347,7 @@ int finalize_keys(const u64* keys, int Q, int L, int k, const int64_t* ids, int6
     size_t smem = (size_t)C * 8;
     VDB_REQUIRE(smem <= (size_t)max_smem_optin() - 1024, VDB_ERR_UNSUPPORTED, "top-k too large for finalize (k=%d)", k);
     VDB_CUDA(cudaFuncSetAttribute(finalize_keys_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    ProfScope prof(kProfFinalize, st);
     finalize_keys_kernel<<<Q, 256, smem, st>>>(keys, L, k, C, ids, idx_offset, negate, out_d, out_i);
     count_launch(1);
     VDB_CUDA(cudaGetLastError());
@@ -359,6 +360,7 @@ static int launch_scan(const ScanPlan& p, const float* q, int Q, const float* db
     auto kern = exact_scan_f32_kernel<TQ, METRIC>;
     VDB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem));
     dim3 grid(p.groups, p.slices);
+    ProfScope prof(kProfExactF32, st);
     kern<<<grid, kScanThreads, p.smem, st>>>(q, Q, db, mask, N, D, k, p.C, p.slice_rows, partial, p.slices);
     count_launch(1);
     VDB_CUDA(cudaGetLastError());
@@ -420,6 +422,7 @@ int vdb_rerank_f32(const float* q, int Q, const float* db, const int64_t* ids, i
     size_t smem = (size_t)C * 8 + (size_t)D * 4;
     VDB_REQUIRE(smem <= (size_t)max_smem_optin() - 1024, VDB_ERR_UNSUPPORTED, "R=%d D=%d exceed shared memory", R, D);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
+    ProfScope prof(kProfRerank, st);
     if (metric == VDB_METRIC_L2) {
         VDB_CUDA(cudaFuncSetAttribute(rerank_f32_kernel<VDB_METRIC_L2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         rerank_f32_kernel<VDB_METRIC_L2><<<Q, 256, smem, st>>>(q, db, ids, N, D, cand, R, k, C, out_d, out_i);

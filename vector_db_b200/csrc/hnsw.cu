@@ -513,6 +513,7 @@ int vdb_hnsw_search(const float* q, int Q, const float* db, int64_t N, int D, co
         ghash = reinterpret_cast<uint32_t*>(static_cast<char*>(ws) + 256);
     }
     VDB_CUDA(cudaMemsetAsync(flag, 0, 4, st));
+    ProfScope prof(kProfHnswSearch, st);
     hnsw_search_kernel<<<grid, kHnswThreads, smem, st>>>(g, q, Q, entry_row, max_level, ef, k, filter, CC, NM, H, ghash,
                                                          out_d, out_rows, out_stats, flag);
     count_launch(1);
@@ -552,6 +553,7 @@ int vdb_hnsw_insert(const float* db, int64_t N, int D, int32_t* adj0, int deg0, 
     }
     VDB_CUDA(cudaFuncSetAttribute(hnsw_insert_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     VDB_CUDA(cudaMemsetAsync(flag, 0, 4, st));
+    ProfScope prof(kProfHnswInsert, st);
     hnsw_insert_kernel<<<1, kHnswThreads, smem, st>>>(g, levels, first, count, M, efc, state, CC, NM, H, ghash, flag);
     count_launch(1);
     VDB_CUDA(cudaGetLastError());

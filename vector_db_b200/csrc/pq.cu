@@ -361,6 +361,7 @@ static int launch_adc(const AdcPlan& p, const uint8_t* codes, int64_t N, int m, 
         VDB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem));         \
         kern<<<p.grid, kAdcThreads, p.smem, st>>>(codes, N, m, lut, Q, R, p.C, p.slice_rows, p.S, p.groups, partial); \
     }
+    ProfScope prof(kProfAdcScan, st);
     const bool aligned4 = (m % 4 == 0) && ((reinterpret_cast<uintptr_t>(codes) & 15) == 0);
     if (aligned4 && m == 16) VDB_ADC_CASE(4)
     else if (aligned4 && m == 32) VDB_ADC_CASE(8)
@@ -399,6 +400,7 @@ int vdb_pq_encode(const float* x, int64_t N, int D, int m, int K, const float* c
         VDB_CUDA(cudaFuncSetAttribute(pq_encode_kernel<DSV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
         pq_encode_kernel<DSV><<<grid, kEncThreads, smem, st>>>(x, N, D, m, K, dsub, codebooks, codes);      \
     }
+    ProfScope prof(kProfPqEncode, st);
     switch (dsub) {
         case 1: VDB_ENC_CASE(1) break;
         case 2: VDB_ENC_CASE(2) break;

@@ -4,6 +4,9 @@
 #include <stdarg.h>
 
 #include <atomic>
+#include <mutex>
+#include <utility>
+#include <vector>
 
 #include "common.cuh"
 
@@ -25,6 +28,24 @@ int cuda_fail(cudaError_t e, const char* what, const char* file, int line) {
 }
 
 void count_launch(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
+
+static std::atomic<int> g_prof_on{0};
+static std::mutex g_prof_mu;
+static std::vector<std::pair<cudaEvent_t, cudaEvent_t>> g_prof[kProfSlots];
+
+ProfScope::ProfScope(int slot_, cudaStream_t st_) : slot(slot_), st(st_), on(g_prof_on.load() != 0) {
+    if (!on) return;
+    cudaEvent_t a, b;
+    if (cudaEventCreate(&a) != cudaSuccess || cudaEventCreate(&b) != cudaSuccess) { on = false; return; }
+    cudaEventRecord(a, st);
+    std::lock_guard<std::mutex> lk(g_prof_mu);
+    g_prof[slot].push_back({a, b});
+}
+ProfScope::~ProfScope() {
+    if (!on) return;
+    std::lock_guard<std::mutex> lk(g_prof_mu);
+    cudaEventRecord(g_prof[slot].back().second, st);
+}
 
 int sm_count() {
     static int n = 0;
@@ -93,6 +114,28 @@ extern "C" {
 const char* vdb_last_error(void) { return vdb::g_err; }
 int vdb_abi_version(void) { return 1; }
 uint64_t vdb_launch_count(void) { return vdb::g_launches.load(); }
+
+void vdb_profile_enable(int on) { vdb::g_prof_on.store(on); }
+
+int vdb_profile_read(int slot, int* launches, float* total_ms) {
+    VDB_REQUIRE(slot >= 0 && slot < kProfSlots && launches && total_ms, VDB_ERR_INVALID, "vdb_profile_read: bad slot");
+    std::lock_guard<std::mutex> lk(vdb::g_prof_mu);
+    float sum = 0.f;
+    int n = 0;
+    for (auto& pr : vdb::g_prof[slot]) {
+        float ms = 0.f;
+        if (cudaEventSynchronize(pr.second) == cudaSuccess && cudaEventElapsedTime(&ms, pr.first, pr.second) == cudaSuccess) {
+            sum += ms;
+            ++n;
+        }
+        cudaEventDestroy(pr.first);
+        cudaEventDestroy(pr.second);
+    }
+    vdb::g_prof[slot].clear();
+    *launches = n;
+    *total_ms = sum;
+    return VDB_OK;
+}
 
 int vdb_stage_aos_h2d(const void* host_records, int64_t n, int D, int64_t* ids, float* vecs, void* stream) {
     VDB_REQUIRE(n >= 0 && D > 0, VDB_ERR_INVALID, "vdb_stage_aos_h2d: bad n=%lld D=%d", (long long)n, D);
