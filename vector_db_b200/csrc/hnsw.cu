@@ -385,10 +385,10 @@ hnsw_insert_kernel(Graph g, const int32_t* __restrict__ levels, int32_t first, i
         const int lvl = levels[node];
         __syncthreads();
         for (int t = tid; t < g.D; t += kHnswThreads) m.qs[t] = g.db[(size_t)node * g.D + t];
-        const int entry = state[0], top = state[1];
+        const int entry = ((volatile int32_t*)state)[0], top = ((volatile int32_t*)state)[1];
         __syncthreads();
         if (entry < 0) {                       // first node: becomes the entry point, no links
-            if (tid == 0) { state[0] = node; state[1] = lvl; }
+            if (tid == 0) { state[0] = node; state[1] = lvl; __threadfence(); }
             __syncthreads();
             continue;
         }
@@ -404,6 +404,7 @@ hnsw_insert_kernel(Graph g, const int32_t* __restrict__ levels, int32_t first, i
             int deg;
             int32_t* mine = nbr_list_rw(g, node, level, &deg);
             for (int t = tid; t < deg; t += kHnswThreads) mine[t] = t < nsel ? (int32_t)key_index(found[t]) : -1;
+            __threadfence();
             __syncthreads();
             for (int sidx = 0; sidx < nsel; ++sidx) {
                 const int nb = (int)key_index(found[sidx]);
@@ -411,7 +412,7 @@ hnsw_insert_kernel(Graph g, const int32_t* __restrict__ levels, int32_t first, i
                 int32_t* lst = nbr_list_rw(g, nb, level, &cap);
                 const int len = __syncthreads_count(tid < cap && __ldcg(lst + tid) >= 0);
                 if (len < cap) {
-                    if (tid == 0) lst[len] = node;
+                    if (tid == 0) { lst[len] = node; __threadfence(); }
                     __syncthreads();
                 } else {
                     // truncate to the `cap` closest of (old links + new node), measured from nb
@@ -443,6 +444,7 @@ hnsw_insert_kernel(Graph g, const int32_t* __restrict__ levels, int32_t first, i
                     __syncthreads();
                     const int keep = valid < cap ? valid : cap;
                     for (int t = tid; t < cap; t += kHnswThreads) lst[t] = t < keep ? (int32_t)key_index(m.news[t]) : -1;
+                    __threadfence();
                     __syncthreads();
                 }
             }
@@ -450,7 +452,7 @@ hnsw_insert_kernel(Graph g, const int32_t* __restrict__ levels, int32_t first, i
             __syncthreads();
         }
         total_evals += evals;
-        if (tid == 0 && lvl > top) { state[0] = node; state[1] = lvl; }
+        if (tid == 0 && lvl > top) { state[0] = node; state[1] = lvl; __threadfence(); }
         __syncthreads();
     }
     if (tid == 0) { state[2] = (int32_t)(uint32_t)(total_evals & 0xFFFFFFFFull); state[3] = (int32_t)(uint32_t)(total_evals >> 32); }
