@@ -37,11 +37,11 @@ def test_indexing_service_dropin(tmp_path):
     svc.delete_node(5)
     assert svc._index_modified and all(n.id != 5 for n, _ in svc.search(X[5], k=5, ef=50))
     svc.force_save_index()
+    a = [(n.id, float(d)) for n, d in svc.search(X[7], k=5, ef=64)]
     st.close()
     st2 = MMapNodeStorage(tmp_path / "db.embeddings.npy", tmp_path / "db.metadata.npy", dim=16, capacity=256)
     svc2 = IndexingService(st2, _cfg(tmp_path, "  ef_search: 64\n"))
     assert svc2.is_index_loaded() and svc2.get_index_size() == 39 and svc2.ef_search == 64
-    a = [(n.id, float(d)) for n, d in svc.search(X[7], k=5, ef=64)]
     b = [(n.id, float(d)) for n, d in svc2.search(X[7], k=5)]
     assert a == b
 
