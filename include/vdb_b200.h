@@ -87,6 +87,26 @@ int vdb_rerank_f32(const float* q, int Q, const float* db, const int64_t* ids, i
                    const int32_t* cand /*[dev] Q*R*/, int R, int k, int metric,
                    float* out_d, int64_t* out_i, void* stream);
 
+/* ---- a3 exact scan on tcgen05 tensor cores ------------------------------------------------
+ * Coarse pass: bf16 x bf16 -> fp32 GEMM tiles (TMA-fed tcgen05.mma, accumulators in TMEM) with
+ * a fused epilogue that turns each accumulator row into scores (L2: |x|^2 - 2 q.x, cosine:
+ * -q.x/|x|), reduces them to per-bin minima (bin = VDB_TC_BIN consecutive rows) and keeps the
+ * `nbins` best bins per (query, db slice).  The caller (vdb_exact_topk_tc) merges slices, reranks
+ * every row of the selected bins in fp32 and certifies the result with a rigorous bf16 error
+ * bound; uncertified queries are re-run through vdb_exact_topk_f32.
+ * Requirements: D % 64 == 0, operands of one query tile fit shared memory (D <= 384), k <= 16;
+ * vdb_exact_topk_tc_supported() answers for a shape.  */
+#define VDB_TC_BIN 8
+int vdb_exact_topk_tc_supported(int Q, int64_t N, int D, int k);
+size_t vdb_exact_topk_tc_workspace(int Q, int64_t N, int D, int k);
+int vdb_exact_topk_tc(const float* q /*[dev] Q*D fp32*/, int Q,
+                      const float* db /*[dev] N*D fp32*/, const void* db_bf16 /*[dev] N*D bf16*/,
+                      const float* db_sqnorm /*[dev] N*/, float db_max_norm,
+                      const int64_t* ids /*[dev] or NULL*/, int64_t N, int D, int k, int metric,
+                      float* out_d, int64_t* out_i,
+                      int32_t* out_uncertified /*[dev] Q+1: count, then the query indices that could not be certified*/,
+                      void* ws, size_t ws_bytes, void* stream);
+
 /* ---- a11 PQ encode -------------------------------------------------------------------------
  * codes[i][j] = argmin_c sqrt(sum((C_j[c]-x_ij)^2)), first minimum wins
  * (src/vector_db/inference/pq.py:77-89).  codebooks laid out [m][K][dsub] fp32, K <= 256,

@@ -1,0 +1,84 @@
+"""GPU parity: tensor-core exact scan (tcgen05 coarse pass + fp32 rerank + certificate) vs the fp32
+scan kernel (itself pinned to the oracle / golden vectors in test_exact_gpu.py) and vs the oracle."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _prep(X):
+    from vector_db_b200 import ops
+    sq, mir = ops.prepare_rows(X)
+    return sq, mir, float(sq.max().sqrt().item())
+
+
+@pytest.mark.parametrize("n,d,q,k,metric", [(50_000, 384, 300, 10, "l2"), (20_011, 128, 129, 10, "l2"),
+                                             (33_000, 64, 7, 5, "l2"), (50_000, 384, 260, 10, "cosine"),
+                                             (8_200, 256, 128, 16, "cosine")])
+def test_tc_matches_fp32_scan(n, d, q, k, metric):
+    from vector_db_b200 import ops
+    g = torch.Generator(device=DEV).manual_seed(n + d)
+    X = torch.randn((n, d), device=DEV, generator=g)
+    Q = torch.randn((q, d), device=DEV, generator=g)
+    Q[0] = X[17]                                       # self query
+    if metric == "l2":
+        X[40] = X[17]                                  # duplicate row -> (dist,id) tie
+    assert ops.tc_supported(q, n, d, k)
+    sq, mir, mx = _prep(X)
+    D, I, n_bad = ops.exact_topk_tc(Q, X, mir, sq, mx, k, metric, return_uncertified=True)
+    Dr, Ir = ops.exact_topk_f32(Q, X, k, metric)
+    assert torch.equal(I, Ir), f"{(I != Ir).sum().item()} ids differ"
+    assert torch.equal(D, Dr)                          # final values come from the same fp32 arithmetic
+    assert n_bad <= max(2, q // 20), f"{n_bad} of {q} queries fell back to the fp32 scan"
+    if metric == "l2":
+        assert D[0, 0].item() == 0.0 and I[0, 0].item() == 17 and I[0, 1].item() == 40
+
+
+def test_tc_vs_oracle_and_ids():
+    from vector_db_b200 import ops
+    rng = np.random.default_rng(5)
+    X = rng.standard_normal((12_000, 192)).astype(np.float32)
+    Q = rng.standard_normal((40, 192)).astype(np.float32)
+    ids = (np.arange(12_000, dtype=np.int64) * 5 + 3)
+    Xd, Qd = torch.from_numpy(X).to(DEV), torch.from_numpy(Q).to(DEV)
+    sq, mir, mx = _prep(Xd)
+    D, I = ops.exact_topk_tc(Qd, Xd, mir, sq, mx, 10, "l2", ids=torch.from_numpy(ids).to(DEV))
+    Dref, Iref = O.exact_l2_topk(X, ids, Q, 10)
+    np.testing.assert_array_equal(I.cpu().numpy(), Iref)
+    np.testing.assert_allclose(D.cpu().numpy(), Dref, rtol=1e-5)
+
+
+def test_tc_adversarial_near_duplicates_fall_back_not_fail():
+    """Rows that differ from the query by less than bf16 resolution: the coarse pass cannot rank them,
+    the certificate must notice (or the shortlist must contain them) -- the answer stays exact."""
+    from vector_db_b200 import ops
+    g = torch.Generator(device=DEV).manual_seed(1)
+    base = torch.randn((1, 128), device=DEV, generator=g)
+    X = base + 1e-3 * torch.randn((20_000, 128), device=DEV, generator=g)      # a tight cluster
+    Q = base + 1e-3 * torch.randn((64, 128), device=DEV, generator=g)
+    sq, mir, mx = _prep(X)
+    D, I, n_bad = ops.exact_topk_tc(Q, X, mir, sq, mx, 10, "l2", return_uncertified=True)
+    Dr, Ir = ops.exact_topk_f32(Q, X, 10, "l2")
+    assert torch.equal(I, Ir) and torch.equal(D, Dr)
+    assert n_bad > 0          # this data cannot be certified from a bf16 pass
+
+
+def test_exact_index_uses_tensor_cores_when_it_can():
+    from vector_db_b200 import _lib
+    from vector_db_b200.indexing import ExactIndex
+    rng = np.random.default_rng(3)
+    X = rng.standard_normal((30_000, 128)).astype(np.float32)
+    idx = ExactIndex(128, "l2")
+    idx.add(range(30_000), X)
+    _lib.profile_enable(True)
+    _lib.profile_read("exact_tc")
+    D, I = idx.search(X[:50], 10)
+    n, ms = _lib.profile_read("exact_tc")
+    _lib.profile_enable(False)
+    assert n == 1 and I[:, 0].tolist() == list(range(50)) and np.all(D[:, 0] == 0)
+    Dref, Iref = O.exact_l2_topk(X, np.arange(30_000), X[:50], 10)
+    np.testing.assert_array_equal(I, Iref)

@@ -189,7 +189,38 @@ def hnsw_search(q: torch.Tensor, db: torch.Tensor, n_rows: int, adj0: torch.Tens
 
 def tc_supported(Q: int, N: int, D: int, k: int) -> bool:
     """True when the tcgen05 tensor-core scan covers this shape (see vdb_exact_topk_tc)."""
+    if Q <= 0 or N < 4096:
+        return False          # tiny databases: the fp32 scan is already launch-bound
+    return bool(load().vdb_exact_topk_tc_supported(int(Q), int(N), int(D), int(k)))
+
+
+def exact_topk_tc(q: torch.Tensor, db: torch.Tensor, db_bf16: torch.Tensor, db_sqnorm: torch.Tensor, max_norm: float,
+                  k: int, metric=METRIC_L2, ids: Optional[torch.Tensor] = None, n_rows: Optional[int] = None,
+                  return_uncertified: bool = False):
+    """Exact top-k through the tensor-core coarse scan + fp32 rerank + certificate.  Queries the
+    certificate rejects are re-run through the exact fp32 scan, so the result is always exact.
+    Synchronises once (reads the uncertified count)."""
+    q = _f32(q, "q")
+    Q, D = q.shape
+    N = db.shape[0] if n_rows is None else int(n_rows)
+    dev = q.device
+    m = _metric(metric)
+    out_d = torch.empty((Q, k), dtype=torch.float32, device=dev)
+    out_i = torch.empty((Q, k), dtype=torch.int64, device=dev)
+    uncert = torch.empty((Q + 1,), dtype=torch.int32, device=dev)
     lib = load()
-    if not hasattr(lib, "vdb_exact_topk_tc"):
-        return False
-    return D % 64 == 0 and D <= 1024 and k <= 64 and N >= 4096 and Q >= 1
+    nbytes = lib.vdb_exact_topk_tc_workspace(Q, N, D, k)
+    if nbytes == 0:
+        raise ValueError(f"tensor-core scan does not support Q={Q} N={N} D={D} k={k}")
+    ws = _ws("exact_tc", nbytes, dev)
+    check(lib.vdb_exact_topk_tc(ptr(q), Q, ptr(db), ptr(db_bf16), ptr(db_sqnorm), float(max_norm), ptr(ids), N, D, k, m,
+                                ptr(out_d), ptr(out_i), ptr(uncert), ptr(ws), ws.numel(), _lib.stream_ptr(dev)))
+    n_bad = int(uncert[0].item())
+    if n_bad:
+        bad = uncert[1:1 + n_bad].long()
+        fd, fi = exact_topk_f32(q.index_select(0, bad), db, k, m, ids=ids, n_rows=N)
+        out_d.index_copy_(0, bad, fd)
+        out_i.index_copy_(0, bad, fi)
+    if return_uncertified:
+        return out_d, out_i, n_bad
+    return out_d, out_i
