@@ -197,7 +197,7 @@ def run_ours(args):
     for _ in range(max(args.warmup, 3)):
         out = step_device()
     barrier()
-    engine = "exact_tc" if ops.tc_supported(N_QUERIES, N_ROWS, DIM, K) and args.engine != "f32" else "exact_f32"
+    engine = "exact_tc" if ops.tc_supported(N_QUERIES, N_ROWS, DIM, K, "cosine") and args.engine != "f32" else "exact_f32"
 
     # ---- timed region: device-resident inputs
     _lib.profile_enable(True)

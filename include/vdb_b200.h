@@ -88,24 +88,33 @@ int vdb_rerank_f32(const float* q, int Q, const float* db, const int64_t* ids, i
                    float* out_d, int64_t* out_i, void* stream);
 
 /* ---- a3 exact scan on tcgen05 tensor cores ------------------------------------------------
- * Coarse pass: bf16 x bf16 -> fp32 GEMM tiles (TMA-fed tcgen05.mma, accumulators in TMEM) with
- * a fused epilogue that turns each accumulator row into scores (L2: |x|^2 - 2 q.x, cosine:
- * -q.x/|x|), reduces them to per-bin minima (bin = VDB_TC_BIN consecutive rows) and keeps the
- * `nbins` best bins per (query, db slice).  The caller (vdb_exact_topk_tc) merges slices, reranks
- * every row of the selected bins in fp32 and certifies the result with a rigorous bf16 error
- * bound; uncertified queries are re-run through vdb_exact_topk_f32.
- * Requirements: D % 64 == 0, operands of one query tile fit shared memory (D <= 384), k <= 16;
- * vdb_exact_topk_tc_supported() answers for a shape.  */
+ * Coarse pass: bf16 x bf16 -> fp32 GEMM tiles (TMA-fed tcgen05.mma, accumulators in TMEM) over a
+ * per-metric OPERAND MIRROR of the rows, built so that the accumulator is the ranking score
+ * itself: L2 rows hold bf16(-2x) plus a three-way bf16 split of |x|^2 in three extra K columns
+ * (score = |x|^2 - 2 q.x), cosine rows hold bf16(-x/|x|) (score = -q.x/|x|).  The fused epilogue
+ * reduces every accumulator row to per-bin minima (bin = VDB_TC_BIN consecutive rows) and keeps
+ * the best bins per (query, db slice) in registers.  vdb_exact_topk_tc merges the slices, reranks
+ * every row of the selected bins in fp32 (the reference's direct-difference arithmetic) and
+ * certifies the result with a rigorous bf16 error bound; the indices of queries it cannot certify
+ * are returned so the caller re-runs them through vdb_exact_topk_f32.
+ * Requirements: D % 8 == 0, one query tile's operand fits shared memory (D <= 512), k <= 16;
+ * vdb_exact_topk_tc_supported() answers for a shape.
+ * Mirror layout: bf16 [N][vdb_tc_row_elems(D, metric)], 16-byte aligned. */
 #define VDB_TC_BIN 8
-int vdb_exact_topk_tc_supported(int Q, int64_t N, int D, int k);
-size_t vdb_exact_topk_tc_workspace(int Q, int64_t N, int D, int k);
+int vdb_exact_topk_tc_supported(int Q, int64_t N, int D, int k, int metric);
+int vdb_tc_row_elems(int D, int metric);
+int vdb_tc_prepare_rows(const float* vecs /*[dev] N*D*/, int64_t N, int D, int metric,
+                        float* sqnorm /*[dev] N or NULL*/, void* mirror /*[dev] N*row_elems bf16*/, void* stream);
+size_t vdb_exact_topk_tc_workspace(int Q, int64_t N, int D, int k, int metric);
 int vdb_exact_topk_tc(const float* q /*[dev] Q*D fp32*/, int Q,
-                      const float* db /*[dev] N*D fp32*/, const void* db_bf16 /*[dev] N*D bf16*/,
-                      const float* db_sqnorm /*[dev] N*/, float db_max_norm,
+                      const float* db /*[dev] N*D fp32*/, const void* mirror /*[dev] see above*/,
+                      float db_max_norm /* max |x| over the rows, used by the L2 certificate */,
                       const int64_t* ids /*[dev] or NULL*/, int64_t N, int D, int k, int metric,
                       float* out_d, int64_t* out_i,
                       int32_t* out_uncertified /*[dev] Q+1: count, then the query indices that could not be certified*/,
                       void* ws, size_t ws_bytes, void* stream);
+/* bench/debug only: bit 0 = skip the epilogue arithmetic of the coarse pass (results are then invalid) */
+void vdb_debug_set_tc_flags(int flags);
 
 /* ---- a11 PQ encode -------------------------------------------------------------------------
  * codes[i][j] = argmin_c sqrt(sum((C_j[c]-x_ij)^2)), first minimum wins

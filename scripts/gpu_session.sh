@@ -25,9 +25,15 @@ if [[ "$what" == *bench* || "$what" == *all* ]]; then
 fi
 if [[ "$what" == *ncu* || "$what" == *all* ]]; then
   if python bench.py --steps 2 --warmup 3 > gpurun_out/ncu_plain.log 2>&1; then
-    timeout -k 10 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv \
+    timeout -k 10 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv \
       --log-file gpurun_out/launches.csv python bench.py --steps 2 --warmup 3 > gpurun_out/ncu_run.log 2>&1
     echo "--- ncu launch list rc=$?"; tail -n 5 gpurun_out/launches.csv
   fi
+fi
+if [[ "$what" == *full* ]]; then
+  # one --set full capture of the dominant kernel (KERNEL regex, default the tensor-core scan)
+  timeout -k 10 1200 ncu --set full --clock-control none --import-source on -k "regex:${KERNEL:-exact_tc_kernel}" \
+    -s ${SKIP:-3} -c 1 -f -o "gpurun_out/${PROF:-prof_exact_tc}" ${CMD:-python bench.py --steps 2 --warmup 3} > gpurun_out/ncu_full.log 2>&1
+  echo "--- ncu full rc=$?"; tail -n 5 gpurun_out/ncu_full.log
 fi
 echo "=== done ($(date +%T))"

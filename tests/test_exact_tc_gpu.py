@@ -10,10 +10,10 @@ pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
 
 
-def _prep(X):
+def _prep(X, metric="l2"):
     from vector_db_b200 import ops
-    sq, mir = ops.prepare_rows(X)
-    return sq, mir, float(sq.max().sqrt().item())
+    mir, sq = ops.tc_prepare_rows(X, metric)
+    return mir, float(sq.max().sqrt().item())
 
 
 @pytest.mark.parametrize("n,d,q,k,metric", [(50_000, 384, 300, 10, "l2"), (20_011, 128, 129, 10, "l2"),
@@ -27,9 +27,9 @@ def test_tc_matches_fp32_scan(n, d, q, k, metric):
     Q[0] = X[17]                                       # self query
     if metric == "l2":
         X[40] = X[17]                                  # duplicate row -> (dist,id) tie
-    assert ops.tc_supported(q, n, d, k)
-    sq, mir, mx = _prep(X)
-    D, I, n_bad = ops.exact_topk_tc(Q, X, mir, sq, mx, k, metric, return_uncertified=True)
+    assert ops.tc_supported(q, n, d, k, metric)
+    mir, mx = _prep(X, metric)
+    D, I, n_bad = ops.exact_topk_tc(Q, X, mir, mx, k, metric, return_uncertified=True)
     Dr, Ir = ops.exact_topk_f32(Q, X, k, metric)
     assert torch.equal(I, Ir), f"{(I != Ir).sum().item()} ids differ"
     assert torch.equal(D, Dr)                          # final values come from the same fp32 arithmetic
@@ -45,8 +45,8 @@ def test_tc_vs_oracle_and_ids():
     Q = rng.standard_normal((40, 192)).astype(np.float32)
     ids = (np.arange(12_000, dtype=np.int64) * 5 + 3)
     Xd, Qd = torch.from_numpy(X).to(DEV), torch.from_numpy(Q).to(DEV)
-    sq, mir, mx = _prep(Xd)
-    D, I = ops.exact_topk_tc(Qd, Xd, mir, sq, mx, 10, "l2", ids=torch.from_numpy(ids).to(DEV))
+    mir, mx = _prep(Xd)
+    D, I = ops.exact_topk_tc(Qd, Xd, mir, mx, 10, "l2", ids=torch.from_numpy(ids).to(DEV))
     Dref, Iref = O.exact_l2_topk(X, ids, Q, 10)
     np.testing.assert_array_equal(I.cpu().numpy(), Iref)
     np.testing.assert_allclose(D.cpu().numpy(), Dref, rtol=1e-5)
@@ -60,8 +60,8 @@ def test_tc_adversarial_near_duplicates_fall_back_not_fail():
     base = torch.randn((1, 128), device=DEV, generator=g)
     X = base + 1e-3 * torch.randn((20_000, 128), device=DEV, generator=g)      # a tight cluster
     Q = base + 1e-3 * torch.randn((64, 128), device=DEV, generator=g)
-    sq, mir, mx = _prep(X)
-    D, I, n_bad = ops.exact_topk_tc(Q, X, mir, sq, mx, 10, "l2", return_uncertified=True)
+    mir, mx = _prep(X)
+    D, I, n_bad = ops.exact_topk_tc(Q, X, mir, mx, 10, "l2", return_uncertified=True)
     Dr, Ir = ops.exact_topk_f32(Q, X, 10, "l2")
     assert torch.equal(I, Ir) and torch.equal(D, Dr)
     assert n_bad > 0          # this data cannot be certified from a bf16 pass

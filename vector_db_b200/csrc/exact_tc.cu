@@ -1,18 +1,21 @@
 // Exact top-k on the 5th-gen tensor cores: bf16 coarse scan (tcgen05.mma fed by TMA, accumulators in
-// TMEM) with a fused score + per-bin-minimum + per-row top-bins epilogue, followed by an exact fp32
-// rerank of every row in the selected bins and a RIGOROUS certificate.  Queries whose certificate
-// fails are reported so the caller can re-run them through the fp32 scan (exact_f32.cu).
+// TMEM) whose accumulator IS the ranking score, with a fused per-bin-minimum + per-row best-bins
+// epilogue kept in registers, followed by an exact fp32 rerank of every row in the selected bins and
+// a RIGOROUS certificate.  Queries whose certificate fails are reported so the caller can re-run
+// them through the fp32 scan (exact_f32.cu).
 //
 // Replaces: the all-pairs distance + sort of tests/indexing/test_hnsw.py:128-134 /
 // src/vector_db/indexing/ivf.py:176-199 (arithmetic: src/vector_db/util/distance.py:3-4).
 //
 // Why the answer is still exact.  The reference computes sqrt(sum((q-x)^2)) in fp32.  The coarse
-// pass ranks by c(x) = |x|^2 - 2 q~.x~ (q~, x~ = bf16 roundings), whose error against the true
+// pass ranks by c(x) = |x|^2 - 2 q~.x~ (q~, x~ = bf16 roundings; |x|^2 enters the MMA as an exact
+// three-way bf16 split against ones in the query operand), whose error against the true
 // t(x) = |x|^2 - 2 q.x is bounded by eps = 2 * (2^-8 * 1.01 + 2^-13) * |q| * max|x| (Cauchy-Schwarz
-// on the two roundings + fp32 accumulation).  The kernel keeps, per query, the NB bins (8 consecutive
-// rows) with the smallest bin minimum; every row outside them has c(x) >= tau (the largest kept bin
-// minimum), hence t(x) >= tau - eps.  All 8*NB rows inside them are re-scored exactly.  If
+// on the two roundings + fp32 accumulation).  The kernel keeps, per query, the bins (8 consecutive
+// rows) with the smallest bin minimum; every row outside them has c(x) >= tau (see
+// select_bins_kernel), hence t(x) >= tau - eps.  All rows inside them are re-scored exactly.  If
 // tau - eps > t_k (the k-th exact score) no outside row can enter the top-k: certified.
+// Cosine: c(x) = q~ . bf16(-x/|x|), t(x) = -q.x/|x|, eps = (2^-8 * 1.01 + 2^-13) * |q|.
 #include <cuda.h>
 
 #include "common.cuh"
@@ -22,7 +25,7 @@ namespace vdb {
 
 using namespace sm100;
 
-constexpr int kTcThreads = 256;
+constexpr int kTcThreads = 384;          // warp 0 TMA, 1 MMA, 2 TMEM alloc, 3 spare, 4-11 epilogue (two groups)
 constexpr int kTileM = 128;              // queries per CTA tile
 constexpr int kTileN = 256;              // database rows per accumulator tile
 constexpr int kBlockK = 64;              // bf16 elements per 128-byte swizzled row
@@ -31,52 +34,79 @@ constexpr int kABytes = kTileM * kBlockK * 2;    // 16 KB per A k-block
 constexpr int kBBytes = kTileN * kBlockK * 2;    // 32 KB per B stage
 constexpr int kBin = VDB_TC_BIN;
 constexpr int kMaxStages = 8;
+constexpr int kNBL = 16;                 // bins kept per (query, slice, epilogue group)
+constexpr int kNBFinal = 32;             // bins reranked per query
+constexpr int kGroups = 2;               // epilogue groups == accumulator stages
 
 struct TcSmemLayout {
-    int a_off, b_off, heap_off, coef_off, bar_off, total;
+    int a_off, b_off, bar_off, total;
 };
 
-__host__ __device__ inline TcSmemLayout tc_layout(int num_kb, int stages, int NB) {
+__host__ __device__ inline TcSmemLayout tc_layout(int num_kb, int stages) {
     TcSmemLayout L;
     L.a_off = 0;
     L.b_off = L.a_off + num_kb * kABytes;
-    L.heap_off = L.b_off + stages * kBBytes;
-    L.coef_off = L.heap_off + NB * kTileM * 8;
-    L.bar_off = L.coef_off + kTileN * 4;
+    L.bar_off = L.b_off + stages * kBBytes;
     L.total = L.bar_off + (2 * kMaxStages + 8) * 8 + 16;
     return L;
 }
 
-// max-heap (by key) of NB entries for one row, entries strided by kTileM; replace the root.
-__device__ __forceinline__ void heap_replace_root(u64* h, int NB, u64 key) {
-    int e = 0;
-    while (true) {
-        int c = 2 * e + 1;
-        if (c >= NB) break;
-        u64 kc = h[c * kTileM];
-        if (c + 1 < NB) {
-            u64 k2 = h[(c + 1) * kTileM];
-            if (k2 > kc) { kc = k2; c = c + 1; }
-        }
-        if (kc <= key) break;
-        h[e * kTileM] = kc;
-        e = c;
+// Sorted (ascending) register list of the kNBL best (score, bin) pairs of one query row.
+struct BinList {
+    float s[kNBL];
+    uint32_t b[kNBL];
+    __device__ __forceinline__ void reset() {
+#pragma unroll
+        for (int i = 0; i < kNBL; ++i) { s[i] = INFINITY; b[i] = 0xFFFFFFFFu; }
     }
-    h[e * kTileM] = key;
+    __device__ __forceinline__ float tau() const { return s[kNBL - 1]; }
+    // requires score < tau(): bubble the new pair to its place, the old worst falls off the end
+    __device__ __forceinline__ void insert(float score, uint32_t bin) {
+#pragma unroll
+        for (int i = 0; i < kNBL; ++i) {
+            const bool lt = score < s[i];
+            const float ts = s[i];
+            const uint32_t tb = b[i];
+            s[i] = lt ? score : ts;
+            b[i] = lt ? bin : tb;
+            score = lt ? ts : score;
+            bin = lt ? tb : bin;
+        }
+    }
+};
+
+__device__ __forceinline__ float min8(const float* v) {
+    return fminf(fminf(fminf(v[0], v[1]), fminf(v[2], v[3])), fminf(fminf(v[4], v[5]), fminf(v[6], v[7])));
 }
 
-template <int METRIC>
+// One 32-column chunk of one accumulator row: the columns ARE the scores (the operand mirror is
+// built so that q~ . b~ = |x|^2 - 2 q.x  or  -q.x/|x|).  Fast path: one min over the chunk against
+// the row's current threshold; only chunks that beat it look at their four bins.
+__device__ __forceinline__ void consume_chunk(float (&v)[32], int n_valid, uint32_t bin0, BinList& list) {
+    if (n_valid < 32) {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = (i < n_valid) ? v[i] : INFINITY;
+    }
+    const float m0 = min8(v), m1 = min8(v + 8), m2 = min8(v + 16), m3 = min8(v + 24);
+    const float cm = fminf(fminf(m0, m1), fminf(m2, m3));
+    if (cm < list.tau()) {
+        if (m0 < list.tau()) list.insert(m0, bin0);
+        if (m1 < list.tau()) list.insert(m1, bin0 + 1);
+        if (m2 < list.tau()) list.insert(m2, bin0 + 2);
+        if (m3 < list.tau()) list.insert(m3, bin0 + 3);
+    }
+}
+
+// flags: bit 0 = debug, skip the epilogue arithmetic (measures the TMA + MMA pipeline alone)
 __global__ void __launch_bounds__(kTcThreads, 1)
 exact_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-                const float* __restrict__ coef, int Q, int64_t N, int num_kb, int stages, int NB, int m_tiles, int S,
-                int tiles_per_slice, int tiles_total, u64* __restrict__ partial) {
+                int Q, int64_t N, int Dp, int num_kb, int stages, int m_tiles, int S,
+                int tiles_per_slice, int tiles_total, int flags, u64* __restrict__ partial) {
     extern __shared__ __align__(1024) unsigned char smem[];   // 128B-swizzled operand tiles need 1024 B alignment
     if ((smem_u32(smem) & 1023u) != 0) __trap();
-    const TcSmemLayout L = tc_layout(num_kb, stages, NB);
+    const TcSmemLayout L = tc_layout(num_kb, stages);
     unsigned char* sA = smem + L.a_off;
     unsigned char* sB = smem + L.b_off;
-    u64* heap = reinterpret_cast<u64*>(smem + L.heap_off);
-    float* coefS = reinterpret_cast<float*>(smem + L.coef_off);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L.bar_off);
     uint64_t* full = bars;                         // [stages]
     uint64_t* empty = bars + kMaxStages;           // [stages]
@@ -88,6 +118,8 @@ exact_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int units = m_tiles * S;
+    // UMMAs in the last k-block: columns past Dp are zero-filled by TMA, skip the all-zero K steps
+    const int last_steps = (Dp - (num_kb - 1) * kBlockK + kUmmaK - 1) / kUmmaK;
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&map_a);
@@ -140,7 +172,7 @@ exact_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                 mbar_wait(a_full, ui & 1);
                 tc_fence_after();
                 for (int t = t0; t < t1; ++t) {
-                    mbar_wait(&tmem_empty[as], aph ^ 1);          // epilogue drained this accumulator
+                    mbar_wait(&tmem_empty[as], aph ^ 1);          // epilogue group `as` drained this accumulator
                     tc_fence_after();
                     const uint32_t d_tmem = tmem_base + (uint32_t)(as * kTileN);
                     for (int kb = 0; kb < num_kb; ++kb) {
@@ -148,8 +180,8 @@ exact_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                         tc_fence_after();
                         const uint64_t da = make_desc_k_sw128(smem_u32(sA + kb * kABytes));
                         const uint64_t db = make_desc_k_sw128(smem_u32(sB + st * kBBytes));
-#pragma unroll
-                        for (int k = 0; k < kBlockK / kUmmaK; ++k)
+                        const int steps = (kb == num_kb - 1) ? last_steps : kBlockK / kUmmaK;
+                        for (int k = 0; k < steps; ++k)
                             umma_bf16(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((kb | k) != 0));
                         umma_commit(&empty[st]);                   // smem stage reusable once these MMAs retire
                         if (++st == stages) { st = 0; ph ^= 1; }
@@ -162,62 +194,47 @@ exact_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
             }
         }
     } else if (warp >= 4) {
-        // ================= epilogue: TMEM -> scores -> bin minima -> per-row top-NB bins =================
+        // ====== epilogue: group eg owns accumulator stage eg, i.e. every other tile this CTA computes ======
+        const int eg = (warp - 4) >> 2;
         const int ew = warp & 3;                       // TMEM lane quarter this warp may touch
         const int row = ew * 32 + lane;                // accumulator row == query within the tile
-        const int et = threadIdx.x - 128;              // 0..127
-        u64* my_heap = heap + row;
-        const u64 empty_key = pack_key(INFINITY, 0xFFFFFFFFu);
-        int as = 0, aph = 0;
+        const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(eg * kTileN);
+        BinList list;
+        int tile_counter = 0, phase = 0;
         for (int u = blockIdx.x; u < units; u += gridDim.x) {
             const int mt = u % m_tiles, s = u / m_tiles;
             const int t0 = s * tiles_per_slice;
             const int t1 = min(tiles_total, t0 + tiles_per_slice);
-            for (int e = 0; e < NB; ++e) my_heap[e * kTileM] = empty_key;
-            float tau = INFINITY;
-            for (int t = t0; t < t1; ++t) {
-                float* cs = coefS;
-                {
-                    const int64_t r0 = (int64_t)t * kTileN + et, r1 = r0 + 128;
-                    const float oob = (METRIC == VDB_METRIC_L2) ? INFINITY : 0.f;
-                    cs[et] = r0 < N ? __ldg(coef + r0) : oob;
-                    cs[et + 128] = r1 < N ? __ldg(coef + r1) : oob;
-                }
-                named_bar_sync(1, 128);
-                mbar_wait(&tmem_full[as], aph);
+            list.reset();
+            for (int t = t0; t < t1; ++t, ++tile_counter) {
+                if ((tile_counter & 1) != eg) continue;
+                mbar_wait(&tmem_full[eg], phase);
+                phase ^= 1;
                 tc_fence_after();
-                const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * kTileN);
-#pragma unroll 1
-                for (int ch = 0; ch < kTileN / 32; ++ch) {
-                    float v[32];
-                    tmem_ld_x32(taddr + (uint32_t)(ch * 32), v);
-                    tmem_ld_wait();
+                if (!(flags & 1)) {
+                    const int64_t left = N - (int64_t)t * kTileN;
+                    const int n_valid = left < kTileN ? (int)left : kTileN;
+                    const uint32_t bin_base = (uint32_t)t * (kTileN / kBin);
+                    float va[32], vb[32];
+                    tmem_ld_x32(taddr, va);
 #pragma unroll
-                    for (int b = 0; b < 32 / kBin; ++b) {
-                        float m = INFINITY;
-#pragma unroll
-                        for (int e = 0; e < kBin; ++e) {
-                            const float c = cs[ch * 32 + b * kBin + e];
-                            const float sc = (METRIC == VDB_METRIC_L2) ? fmaf(-2.f, v[b * kBin + e], c) : v[b * kBin + e] * c;
-                            m = fminf(m, sc);
-                        }
-                        if (m < tau) {
-                            const uint32_t bin = (uint32_t)t * (kTileN / kBin) + (uint32_t)(ch * (32 / kBin) + b);
-                            heap_replace_root(my_heap, NB, pack_key(m, bin));
-                            tau = key_score(my_heap[0]);
-                        }
+                    for (int ch = 0; ch < kTileN / 32; ch += 2) {
+                        tmem_ld_wait(va);
+                        tmem_ld_x32(taddr + (uint32_t)((ch + 1) * 32), vb);
+                        consume_chunk(va, n_valid - ch * 32, bin_base + (uint32_t)(ch * 4), list);
+                        tmem_ld_wait(vb);
+                        if (ch + 2 < kTileN / 32) tmem_ld_x32(taddr + (uint32_t)((ch + 2) * 32), va);
+                        consume_chunk(vb, n_valid - (ch + 1) * 32, bin_base + (uint32_t)((ch + 1) * 4), list);
                     }
                 }
                 tc_fence_before();
-                mbar_arrive(&tmem_empty[as]);
-                as ^= 1;
-                if (as == 0) aph ^= 1;
-                named_bar_sync(1, 128);                            // everyone is done with this tile's coefficients
+                mbar_arrive(&tmem_empty[eg]);
             }
             const int q = mt * kTileM + row;
             if (q < Q) {
-                u64* dst = partial + ((size_t)q * S + s) * NB;
-                for (int e = 0; e < NB; ++e) dst[e] = my_heap[e * kTileM];
+                u64* dst = partial + (((size_t)q * S + s) * kGroups + eg) * kNBL;
+#pragma unroll
+                for (int e = 0; e < kNBL; ++e) dst[e] = pack_key(list.s[e], list.b[e]);
             }
         }
     }
@@ -230,56 +247,87 @@ exact_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
 // ------------------------------------------------------------------------------------------
 // helper kernels around the coarse pass
 
-__global__ void f32_to_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ y, int64_t n) {
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
-        y[i] = __float2bfloat16_rn(x[i]);
-}
-
-// cosine epilogue coefficient: -1/|x| (0 for zero rows, which can never be a meaningful neighbour)
-__global__ void cosine_coef_kernel(const float* __restrict__ sqnorm, float* __restrict__ coef, int64_t n) {
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-        float s = sqnorm[i];
-        coef[i] = s > 0.f ? -1.f / sqrtf(s) : 0.f;
+// Query operand: bf16(q) padded to Dp columns; for L2 the three columns after D hold 1.0 so that
+// the MMA adds the (hi, mid, lo) bf16 split of |x|^2 stored in the same columns of the row mirror.
+__global__ void tc_query_operand_kernel(const float* __restrict__ q, __nv_bfloat16* __restrict__ y, int Q, int D, int Dp,
+                                        int metric) {
+    const int64_t total = (int64_t)Q * Dp;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = i / Dp;
+        const int c = (int)(i - r * Dp);
+        float v = 0.f;
+        if (c < D) v = q[r * D + c];
+        else if (metric == VDB_METRIC_L2 && c < D + 3) v = 1.f;
+        y[i] = __float2bfloat16_rn(v);
     }
 }
 
-// Per query: merge the S per-slice bin lists, keep the NB best bins, expand them to candidate rows
-// and record tau (see the certificate in the file header).  One CTA per query.
+// Row operand ("mirror"), one warp per row, built once per index mutation:
+//   L2     : bf16(-2 x) = -2 bf16(x) in columns [0,D), bf16 split (hi, mid, lo) of |x|^2 in D..D+2, zeros up to Dp
+//   cosine : bf16(-x/|x|) (zero rows stay zero)
+// so that the fp32 accumulator of q~ . row~ is the ranking score itself.  Also emits sqnorm.
+__global__ void tc_row_operand_kernel(const float* __restrict__ x, int64_t N, int D, int Dp, int metric,
+                                      float* __restrict__ sqnorm, __nv_bfloat16* __restrict__ mirror) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t r = (((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5); r < N; r += warps) {
+        const float* row = x + r * D;
+        float acc = 0.f;
+        for (int t = lane; t < D; t += 32) { const float v = row[t]; acc = fmaf(v, v, acc); }
+        acc = warp_sum(acc);
+        if (sqnorm && lane == 0) sqnorm[r] = acc;
+        __nv_bfloat16* out = mirror + r * Dp;
+        if (metric == VDB_METRIC_L2) {
+            for (int t = lane; t < D; t += 32) out[t] = __float2bfloat16_rn(-2.f * row[t]);
+            if (lane == 0) {
+                const __nv_bfloat16 h = __float2bfloat16_rn(acc);
+                const float r1 = acc - __bfloat162float(h);
+                const __nv_bfloat16 m = __float2bfloat16_rn(r1);
+                const __nv_bfloat16 l = __float2bfloat16_rn(r1 - __bfloat162float(m));
+                out[D] = h; out[D + 1] = m; out[D + 2] = l;
+            }
+            for (int t = D + 3 + lane; t < Dp; t += 32) out[t] = __float2bfloat16_rn(0.f);
+        } else {
+            const float rinv = acc > 0.f ? -1.f / sqrtf(acc) : 0.f;
+            for (int t = lane; t < D; t += 32) out[t] = __float2bfloat16_rn(row[t] * rinv);
+            for (int t = D + lane; t < Dp; t += 32) out[t] = __float2bfloat16_rn(0.f);
+        }
+    }
+}
+
+// Per query: merge the L per-(slice, group) bin lists, keep the NB best bins, expand them to
+// candidate rows and record tau (see the certificate in the file header): every bin that is NOT a
+// candidate has a coarse minimum >= tau, either because it ranks behind the NB-th merged bin or
+// because it was dropped from a full list, whose worst entry bounds it.  One CTA per query.
 __global__ void __launch_bounds__(256)
-select_bins_kernel(const u64* __restrict__ partial, int S, int NB, int C, int64_t N, int32_t* __restrict__ cand,
+select_bins_kernel(const u64* __restrict__ partial, int L, int NBL, int NB, int C, int64_t N, int32_t* __restrict__ cand,
                    float* __restrict__ tau_out) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     u64* buf = reinterpret_cast<u64*>(smem_raw);
-    __shared__ int some_slice_full;
-    const int q = blockIdx.x, total = S * NB;
-    const u64 empty_key = pack_key(INFINITY, 0xFFFFFFFFu);
-    if (threadIdx.x == 0) some_slice_full = 0;
+    __shared__ unsigned tau_bits;          // ordered-float minimum over the full lists' worst entries
+    const int q = blockIdx.x, total = L * NBL;
+    if (threadIdx.x == 0) tau_bits = f32_to_ordered(INFINITY);
     __syncthreads();
-    for (int i = threadIdx.x; i < C; i += blockDim.x) buf[i] = i < total ? partial[(size_t)q * total + i] : VDB_KEY_MAX;
-    for (int s = threadIdx.x; s < S; s += blockDim.x) {
-        bool full = true;
-        for (int e = 0; e < NB; ++e) full &= partial[(size_t)q * total + (size_t)s * NB + e] != empty_key;
-        if (full) some_slice_full = 1;
+    for (int i = threadIdx.x; i < C; i += blockDim.x) {
+        u64 key = VDB_KEY_MAX;
+        if (i < total) {
+            key = partial[(size_t)q * total + i];
+            if (key_index(key) == 0xFFFFFFFFu) key = VDB_KEY_MAX;                  // empty slot
+            else if ((i % NBL) == NBL - 1) atomicMin(&tau_bits, (unsigned)(key >> 32));   // worst entry of a full list
+        }
+        buf[i] = key;
     }
     __syncthreads();
     block_bitonic_sort(buf, C);
-    // empty_key sorts after every real key (score +inf, idx max) and before VDB_KEY_MAX padding
-    __shared__ int valid_s;
     if (threadIdx.x == 0) {
-        int valid = 0;
-        while (valid < total && valid <= NB && buf[valid] < empty_key) ++valid;   // only need to know <= NB or more
-        valid_s = valid;
-        float tau;
-        if (valid <= NB && !some_slice_full) tau = INFINITY;          // every bin of every slice is a candidate
-        else tau = key_score(buf[NB - 1]);
+        float tau = ordered_to_f32(tau_bits);
+        if (NB - 1 < C && buf[NB - 1] != VDB_KEY_MAX) tau = fminf(tau, key_score(buf[NB - 1]));
         tau_out[q] = tau;
     }
-    __syncthreads();
-    const int valid = valid_s < NB ? valid_s : NB;
     for (int i = threadIdx.x; i < NB * kBin; i += blockDim.x) {
         const int j = i / kBin, e = i - j * kBin;
         int32_t r = -1;
-        if (j < valid) {
+        if (j < C && buf[j] != VDB_KEY_MAX) {
             int64_t row = (int64_t)key_index(buf[j]) * kBin + e;
             if (row < N) r = (int32_t)row;
         }
@@ -362,24 +410,24 @@ static int make_map(CUtensorMap* map, const void* base, int64_t rows, int D, int
 }
 
 struct TcPlan {
-    int num_kb, stages, NB, m_tiles, S, tiles_per_slice, tiles_total, grid;
+    int Dp, num_kb, stages, m_tiles, S, tiles_per_slice, tiles_total, grid;
     size_t smem;
 };
 
-static int tc_pick_nb(int k) { return k <= 16 ? 32 : 0; }
+static int tc_row_elems(int D, int metric) { return metric == VDB_METRIC_L2 ? D + 16 : D; }
 
-static bool plan_tc(int Q, int64_t N, int D, int k, TcPlan* p) {
-    if (D % kBlockK != 0 || D <= 0 || Q <= 0 || N <= 0) return false;
-    p->NB = tc_pick_nb(k);
-    if (p->NB == 0) return false;
-    p->num_kb = D / kBlockK;
+static bool plan_tc(int Q, int64_t N, int D, int k, int metric, TcPlan* p) {
+    if (D % 8 != 0 || D <= 0 || Q <= 0 || N <= 0) return false;
+    if (k > 16) return false;                       // kNBFinal bins of kBin rows must hold k results with margin
+    p->Dp = tc_row_elems(D, metric);
+    p->num_kb = (p->Dp + kBlockK - 1) / kBlockK;
     const int smem_max = max_smem_optin();
     int stages = kMaxStages;
     // + 1024: the 1024-byte aligned extern array makes the compiler reserve 1 KB of static shared memory
-    while (stages >= 2 && tc_layout(p->num_kb, stages, p->NB).total + 1024 > smem_max) --stages;
+    while (stages >= 2 && tc_layout(p->num_kb, stages).total + 1024 > smem_max) --stages;
     if (stages < 2) return false;
     p->stages = stages;
-    p->smem = (size_t)tc_layout(p->num_kb, stages, p->NB).total;
+    p->smem = (size_t)tc_layout(p->num_kb, stages).total;
     p->m_tiles = (Q + kTileM - 1) / kTileM;
     int64_t tiles_total = (N + kTileN - 1) / kTileN;
     if (tiles_total > (1 << 24)) return false;
@@ -406,21 +454,22 @@ static bool plan_tc(int Q, int64_t N, int D, int k, TcPlan* p) {
 }
 
 struct TcWorkspace {
-    size_t qbf16, coef, partial, cand, tau, total;
+    size_t qbf16, partial, cand, tau, total;
 };
 
-static TcWorkspace tc_workspace(const TcPlan& p, int Q, int64_t N, int D) {
+static TcWorkspace tc_workspace(const TcPlan& p, int Q) {
     TcWorkspace w;
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
-    w.qbf16 = take((size_t)Q * D * 2);
-    w.coef = take((size_t)N * 4);
-    w.partial = take((size_t)Q * p.S * p.NB * 8);
-    w.cand = take((size_t)Q * p.NB * kBin * 4);
+    w.qbf16 = take((size_t)Q * p.Dp * 2);
+    w.partial = take((size_t)Q * p.S * kGroups * kNBL * 8);
+    w.cand = take((size_t)Q * kNBFinal * kBin * 4);
     w.tau = take((size_t)Q * 4);
     w.total = off;
     return w;
 }
+
+static int g_tc_flags = 0;
 
 }  // namespace vdb
 
@@ -428,70 +477,77 @@ using namespace vdb;
 
 extern "C" {
 
-int vdb_exact_topk_tc_supported(int Q, int64_t N, int D, int k) {
+void vdb_debug_set_tc_flags(int flags) { g_tc_flags = flags; }
+
+int vdb_exact_topk_tc_supported(int Q, int64_t N, int D, int k, int metric) {
     TcPlan p;
-    return plan_tc(Q, N, D, k, &p) && N < (1ll << 31) ? 1 : 0;
+    return plan_tc(Q, N, D, k, metric, &p) && N < (1ll << 31) ? 1 : 0;
 }
 
-size_t vdb_exact_topk_tc_workspace(int Q, int64_t N, int D, int k) {
-    TcPlan p;
-    if (!plan_tc(Q, N, D, k, &p)) return 0;
-    return tc_workspace(p, Q, N, D).total;
+int vdb_tc_row_elems(int D, int metric) { return tc_row_elems(D, metric); }
+
+int vdb_tc_prepare_rows(const float* vecs, int64_t N, int D, int metric, float* sqnorm, void* mirror, void* stream) {
+    VDB_REQUIRE(N >= 0 && D > 0 && D % 8 == 0, VDB_ERR_INVALID, "vdb_tc_prepare_rows: bad N=%lld D=%d", (long long)N, D);
+    VDB_REQUIRE(metric == VDB_METRIC_L2 || metric == VDB_METRIC_COSINE, VDB_ERR_INVALID, "unknown metric %d", metric);
+    if (N == 0) return VDB_OK;
+    VDB_REQUIRE(vecs && mirror, VDB_ERR_INVALID, "vdb_tc_prepare_rows: null pointer");
+    int blocks = sm_count() * 8;
+    int64_t need = (N + 7) / 8;
+    if (need < blocks) blocks = (int)need;
+    tc_row_operand_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        vecs, N, D, tc_row_elems(D, metric), metric, sqnorm, static_cast<__nv_bfloat16*>(mirror));
+    count_launch(1);
+    VDB_CUDA(cudaGetLastError());
+    return VDB_OK;
 }
 
-int vdb_exact_topk_tc(const float* q, int Q, const float* db, const void* db_bf16, const float* db_sqnorm,
-                      float db_max_norm, const int64_t* ids, int64_t N, int D, int k, int metric, float* out_d,
+size_t vdb_exact_topk_tc_workspace(int Q, int64_t N, int D, int k, int metric) {
+    TcPlan p;
+    if (!plan_tc(Q, N, D, k, metric, &p)) return 0;
+    return tc_workspace(p, Q).total;
+}
+
+int vdb_exact_topk_tc(const float* q, int Q, const float* db, const void* mirror, float db_max_norm,
+                      const int64_t* ids, int64_t N, int D, int k, int metric, float* out_d,
                       int64_t* out_i, int32_t* out_uncertified, void* ws, size_t ws_bytes, void* stream) {
     VDB_REQUIRE(metric == VDB_METRIC_L2 || metric == VDB_METRIC_COSINE, VDB_ERR_INVALID, "unknown metric %d", metric);
     VDB_REQUIRE(Q > 0 && N > 0 && D > 0 && k > 0, VDB_ERR_INVALID, "vdb_exact_topk_tc: bad shape");
-    VDB_REQUIRE(q && db && db_bf16 && db_sqnorm && out_d && out_i && out_uncertified && ws, VDB_ERR_INVALID,
+    VDB_REQUIRE(q && db && mirror && out_d && out_i && out_uncertified && ws, VDB_ERR_INVALID,
                 "vdb_exact_topk_tc: null pointer");
     VDB_REQUIRE(N < (1ll << 31), VDB_ERR_UNSUPPORTED, "N too large for int32 candidate rows");
     TcPlan p;
-    VDB_REQUIRE(plan_tc(Q, N, D, k, &p), VDB_ERR_UNSUPPORTED, "tensor-core scan does not support D=%d k=%d", D, k);
-    const TcWorkspace w = tc_workspace(p, Q, N, D);
+    VDB_REQUIRE(plan_tc(Q, N, D, k, metric, &p), VDB_ERR_UNSUPPORTED, "tensor-core scan does not support D=%d k=%d", D, k);
+    const TcWorkspace w = tc_workspace(p, Q);
     VDB_REQUIRE(ws_bytes >= w.total, VDB_ERR_WORKSPACE, "workspace %zu < %zu", ws_bytes, w.total);
-    VDB_REQUIRE((reinterpret_cast<uintptr_t>(db_bf16) & 15) == 0 && (reinterpret_cast<uintptr_t>(ws) & 255) == 0,
-                VDB_ERR_INVALID, "bf16 mirror / workspace must be 16 / 256-byte aligned");
+    VDB_REQUIRE((reinterpret_cast<uintptr_t>(mirror) & 15) == 0 && (reinterpret_cast<uintptr_t>(ws) & 255) == 0,
+                VDB_ERR_INVALID, "operand mirror / workspace must be 16 / 256-byte aligned");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     char* base = static_cast<char*>(ws);
     __nv_bfloat16* qb = reinterpret_cast<__nv_bfloat16*>(base + w.qbf16);
-    float* coef = reinterpret_cast<float*>(base + w.coef);
     u64* partial = reinterpret_cast<u64*>(base + w.partial);
     int32_t* cand = reinterpret_cast<int32_t*>(base + w.cand);
     float* tau = reinterpret_cast<float*>(base + w.tau);
 
-    f32_to_bf16_kernel<<<sm_count() * 4, 256, 0, st>>>(q, qb, (int64_t)Q * D);
-    const float* coef_ptr = db_sqnorm;
-    if (metric == VDB_METRIC_COSINE) {
-        cosine_coef_kernel<<<sm_count() * 4, 256, 0, st>>>(db_sqnorm, coef, N);
-        coef_ptr = coef;
-        count_launch(1);
-    }
+    tc_query_operand_kernel<<<sm_count() * 2, 256, 0, st>>>(q, qb, Q, D, p.Dp, metric);
     CUtensorMap map_a, map_b;
-    int rc = make_map(&map_a, qb, Q, D, kTileM);
+    int rc = make_map(&map_a, qb, Q, p.Dp, kTileM);
     if (rc) return rc;
-    rc = make_map(&map_b, db_bf16, N, D, kTileN);
+    rc = make_map(&map_b, mirror, N, p.Dp, kTileN);
     if (rc) return rc;
     {
         ProfScope prof(kProfExactTC, st);
-        if (metric == VDB_METRIC_L2) {
-            VDB_CUDA(cudaFuncSetAttribute(exact_tc_kernel<VDB_METRIC_L2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem));
-            exact_tc_kernel<VDB_METRIC_L2><<<p.grid, kTcThreads, p.smem, st>>>(map_a, map_b, coef_ptr, Q, N, p.num_kb, p.stages, p.NB,
-                                                                              p.m_tiles, p.S, p.tiles_per_slice, p.tiles_total, partial);
-        } else {
-            VDB_CUDA(cudaFuncSetAttribute(exact_tc_kernel<VDB_METRIC_COSINE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem));
-            exact_tc_kernel<VDB_METRIC_COSINE><<<p.grid, kTcThreads, p.smem, st>>>(map_a, map_b, coef_ptr, Q, N, p.num_kb, p.stages, p.NB,
-                                                                                  p.m_tiles, p.S, p.tiles_per_slice, p.tiles_total, partial);
-        }
+        VDB_CUDA(cudaFuncSetAttribute(exact_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem));
+        exact_tc_kernel<<<p.grid, kTcThreads, p.smem, st>>>(map_a, map_b, Q, N, p.Dp, p.num_kb, p.stages, p.m_tiles, p.S,
+                                                           p.tiles_per_slice, p.tiles_total, g_tc_flags, partial);
     }
     VDB_CUDA(cudaGetLastError());
-    const int C = next_pow2(p.S * p.NB < 64 ? 64 : p.S * p.NB);
+    const int L = p.S * kGroups;
+    const int C = next_pow2(L * kNBL < 64 ? 64 : L * kNBL);
     VDB_CUDA(cudaFuncSetAttribute(select_bins_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, C * 8));
-    select_bins_kernel<<<Q, 256, (size_t)C * 8, st>>>(partial, p.S, p.NB, C, N, cand, tau);
+    select_bins_kernel<<<Q, 256, (size_t)C * 8, st>>>(partial, L, kNBL, kNBFinal, C, N, cand, tau);
     count_launch(3);
     VDB_CUDA(cudaGetLastError());
-    rc = vdb_rerank_f32(q, Q, db, ids, N, D, cand, p.NB * kBin, k, metric, out_d, out_i, stream);
+    rc = vdb_rerank_f32(q, Q, db, ids, N, D, cand, kNBFinal * kBin, k, metric, out_d, out_i, stream);
     if (rc) return rc;
     VDB_CUDA(cudaMemsetAsync(out_uncertified, 0, 4, st));
     const int warps_per_block = 8;

@@ -31,6 +31,7 @@ class DeviceVectors:
         self.id_to_row: Dict[int, int] = {}
         self.n_dead = 0
         self._prepared_n = -1
+        self._prepared_metric = -1
         self._sqnorm = None
         self._bf16 = None
         self._max_norm = 0.0
@@ -129,14 +130,16 @@ class DeviceVectors:
         return torch.from_numpy(words.view(np.int32)).to(self.device)
 
     # -- derived arrays for the tensor-core scan ------------------------------------------------
-    def prepared(self):
-        """(sqnorm f32 [n], bf16 mirror [n,D], max row norm) -- rebuilt after every mutation."""
-        if self._prepared_n != self.n:
-            sq, mir = ops.prepare_rows(self.vecs[:self.n])
+    def prepared(self, metric):
+        """(operand mirror bf16 [n, row_elems], max row norm) for the tensor-core scan of `metric`
+        -- rebuilt after every mutation."""
+        m = ops._metric(metric)
+        if self._prepared_n != self.n or self._prepared_metric != m:
+            mir, sq = ops.tc_prepare_rows(self.vecs[:self.n], m)
             self._sqnorm, self._bf16 = sq, mir
             self._max_norm = float(sq.max().sqrt().item()) if self.n else 0.0
-            self._prepared_n = self.n
-        return self._sqnorm, self._bf16, self._max_norm
+            self._prepared_n, self._prepared_metric = self.n, m
+        return self._bf16, self._max_norm
 
     def rows_to_ids(self, rows: np.ndarray) -> np.ndarray:
         host_ids = self.ids[:self.n].cpu().numpy()

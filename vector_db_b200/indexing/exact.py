@@ -42,12 +42,12 @@ class ExactIndex:
         mask = st.bitmap_from_ids(filter_ids) if filter_ids is not None else None
         if mask is None and st.n_dead:
             mask = st.alive
-        use_tc = (self.engine in ("auto", "tc") and mask is None and ops.tc_supported(q.shape[0], st.n, self.dim, k))
+        use_tc = (self.engine in ("auto", "tc") and mask is None and ops.tc_supported(q.shape[0], st.n, self.dim, k, self.metric))
         if self.engine == "tc" and not use_tc:
             raise ValueError("tensor-core engine does not support this shape / filter")
         if use_tc:
-            sq, mir, max_norm = st.prepared()
-            return ops.exact_topk_tc(q, st.vecs, mir, sq, max_norm, k, self.metric, ids=st.ids, n_rows=st.n)
+            mir, max_norm = st.prepared(self.metric)
+            return ops.exact_topk_tc(q, st.vecs, mir, max_norm, k, self.metric, ids=st.ids, n_rows=st.n)
         return ops.exact_topk_f32(q, st.vecs, k, self.metric, ids=st.ids, row_mask=mask, n_rows=st.n)
 
     def search(self, queries: np.ndarray, k: int, filter_ids: Optional[Set[int]] = None

@@ -187,19 +187,33 @@ def hnsw_search(q: torch.Tensor, db: torch.Tensor, n_rows: int, adj0: torch.Tens
     raise _lib.VdbError("hnsw_search: visited table overflow persists")
 
 
-def tc_supported(Q: int, N: int, D: int, k: int) -> bool:
+def tc_supported(Q: int, N: int, D: int, k: int, metric=METRIC_L2) -> bool:
     """True when the tcgen05 tensor-core scan covers this shape (see vdb_exact_topk_tc)."""
     if Q <= 0 or N < 4096:
         return False          # tiny databases: the fp32 scan is already launch-bound
-    return bool(load().vdb_exact_topk_tc_supported(int(Q), int(N), int(D), int(k)))
+    return bool(load().vdb_exact_topk_tc_supported(int(Q), int(N), int(D), int(k), _metric(metric)))
 
 
-def exact_topk_tc(q: torch.Tensor, db: torch.Tensor, db_bf16: torch.Tensor, db_sqnorm: torch.Tensor, max_norm: float,
+def tc_prepare_rows(vecs: torch.Tensor, metric=METRIC_L2):
+    """Per-metric bf16 operand mirror for the tensor-core scan.  Returns (mirror bf16 [N, row_elems],
+    sqnorm f32 [N]); the accumulator of q~ . mirror_row~ is the ranking score itself."""
+    vecs = _f32(vecs, "vecs")
+    n, d = vecs.shape
+    m = _metric(metric)
+    lib = load()
+    dp = lib.vdb_tc_row_elems(d, m)
+    mir = torch.empty((n, dp), dtype=torch.bfloat16, device=vecs.device)
+    sq = torch.empty(n, dtype=torch.float32, device=vecs.device)
+    check(lib.vdb_tc_prepare_rows(ptr(vecs), n, d, m, ptr(sq), ptr(mir), _lib.stream_ptr(vecs.device)))
+    return mir, sq
+
+
+def exact_topk_tc(q: torch.Tensor, db: torch.Tensor, mirror: torch.Tensor, max_norm: float,
                   k: int, metric=METRIC_L2, ids: Optional[torch.Tensor] = None, n_rows: Optional[int] = None,
                   return_uncertified: bool = False):
-    """Exact top-k through the tensor-core coarse scan + fp32 rerank + certificate.  Queries the
-    certificate rejects are re-run through the exact fp32 scan, so the result is always exact.
-    Synchronises once (reads the uncertified count)."""
+    """Exact top-k through the tensor-core coarse scan + fp32 rerank + certificate.  `mirror` comes
+    from tc_prepare_rows(db, metric).  Queries the certificate rejects are re-run through the exact
+    fp32 scan, so the result is always exact.  Synchronises once (reads the uncertified count)."""
     q = _f32(q, "q")
     Q, D = q.shape
     N = db.shape[0] if n_rows is None else int(n_rows)
@@ -209,11 +223,13 @@ def exact_topk_tc(q: torch.Tensor, db: torch.Tensor, db_bf16: torch.Tensor, db_s
     out_i = torch.empty((Q, k), dtype=torch.int64, device=dev)
     uncert = torch.empty((Q + 1,), dtype=torch.int32, device=dev)
     lib = load()
-    nbytes = lib.vdb_exact_topk_tc_workspace(Q, N, D, k)
+    if mirror.shape[1] != lib.vdb_tc_row_elems(D, m):
+        raise ValueError("operand mirror was built for another metric / dimension")
+    nbytes = lib.vdb_exact_topk_tc_workspace(Q, N, D, k, m)
     if nbytes == 0:
         raise ValueError(f"tensor-core scan does not support Q={Q} N={N} D={D} k={k}")
     ws = _ws("exact_tc", nbytes, dev)
-    check(lib.vdb_exact_topk_tc(ptr(q), Q, ptr(db), ptr(db_bf16), ptr(db_sqnorm), float(max_norm), ptr(ids), N, D, k, m,
+    check(lib.vdb_exact_topk_tc(ptr(q), Q, ptr(db), ptr(mirror), float(max_norm), ptr(ids), N, D, k, m,
                                 ptr(out_d), ptr(out_i), ptr(uncert), ptr(ws), ws.numel(), _lib.stream_ptr(dev)))
     n_bad = int(uncert[0].item())
     if n_bad:
