@@ -113,7 +113,8 @@ int vdb_exact_topk_tc(const float* q /*[dev] Q*D fp32*/, int Q,
                       float* out_d, int64_t* out_i,
                       int32_t* out_uncertified /*[dev] Q+1: count, then the query indices that could not be certified*/,
                       void* ws, size_t ws_bytes, void* stream);
-/* bench/debug only: bit 0 = skip the epilogue arithmetic of the coarse pass (results are then invalid) */
+/* bench/debug only: bit 0 = skip the whole epilogue of the coarse pass, bit 1 = skip only its threshold
+ * test and bin-list inserts (results are then invalid) */
 void vdb_debug_set_tc_flags(int flags);
 
 /* ---- a11 PQ encode -------------------------------------------------------------------------

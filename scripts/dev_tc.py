@@ -53,7 +53,10 @@ def timed(metric, mir, mx, flags, iters=10):
 for metric in ("cosine", "l2"):
     mir, sq = ops.tc_prepare_rows(X, metric)
     mx = float(sq.max().sqrt().item())
-    timed(metric, mir, mx, 1)
+    timed(metric, mir, mx, 1)      # TMA + MMA only
+    timed(metric, mir, mx, 1 | (3 << 8))      # same with a 3-deep TMA ring
+    timed(metric, mir, mx, 2)      # + TMEM loads and bin minima, no threshold test / inserts
+    timed(metric, mir, mx, 4)      # full epilogue, 16-entry bin lists
     D_tc, I_tc, nbad = timed(metric, mir, mx, 0)
     ns = min(Q, 128)
     Dr, Ir = ops.exact_topk_f32(Qd[:ns], X, K, metric)

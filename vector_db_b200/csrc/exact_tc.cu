@@ -17,6 +17,7 @@
 // tau - eps > t_k (the k-th exact score) no outside row can enter the top-k: certified.
 // Cosine: c(x) = q~ . bf16(-x/|x|), t(x) = -q.x/|x|, eps = (2^-8 * 1.01 + 2^-13) * |q|.
 #include <cuda.h>
+#include <math.h>
 
 #include "common.cuh"
 #include "sm100.cuh"
@@ -34,7 +35,7 @@ constexpr int kABytes = kTileM * kBlockK * 2;    // 16 KB per A k-block
 constexpr int kBBytes = kTileN * kBlockK * 2;    // 32 KB per B stage
 constexpr int kBin = VDB_TC_BIN;
 constexpr int kMaxStages = 8;
-constexpr int kNBL = 16;                 // bins kept per (query, slice, epilogue group)
+constexpr int kNBLMax = 16;              // bins kept per (query, slice, epilogue group): template NBL <= this
 constexpr int kNBFinal = 32;             // bins reranked per query
 constexpr int kGroups = 2;               // epilogue groups == accumulator stages
 
@@ -51,19 +52,20 @@ __host__ __device__ inline TcSmemLayout tc_layout(int num_kb, int stages) {
     return L;
 }
 
-// Sorted (ascending) register list of the kNBL best (score, bin) pairs of one query row.
+// Sorted (ascending) register list of the NBL best (score, bin) pairs of one query row.
+template <int NBL>
 struct BinList {
-    float s[kNBL];
-    uint32_t b[kNBL];
+    float s[NBL];
+    uint32_t b[NBL];
     __device__ __forceinline__ void reset() {
 #pragma unroll
-        for (int i = 0; i < kNBL; ++i) { s[i] = INFINITY; b[i] = 0xFFFFFFFFu; }
+        for (int i = 0; i < NBL; ++i) { s[i] = INFINITY; b[i] = 0xFFFFFFFFu; }
     }
-    __device__ __forceinline__ float tau() const { return s[kNBL - 1]; }
+    __device__ __forceinline__ float tau() const { return s[NBL - 1]; }
     // requires score < tau(): bubble the new pair to its place, the old worst falls off the end
     __device__ __forceinline__ void insert(float score, uint32_t bin) {
 #pragma unroll
-        for (int i = 0; i < kNBL; ++i) {
+        for (int i = 0; i < NBL; ++i) {
             const bool lt = score < s[i];
             const float ts = s[i];
             const uint32_t tb = b[i];
@@ -80,24 +82,20 @@ __device__ __forceinline__ float min8(const float* v) {
 }
 
 // One 32-column chunk of one accumulator row: the columns ARE the scores (the operand mirror is
-// built so that q~ . b~ = |x|^2 - 2 q.x  or  -q.x/|x|).  Fast path: one min over the chunk against
-// the row's current threshold; only chunks that beat it look at their four bins.
-__device__ __forceinline__ void consume_chunk(float (&v)[32], int n_valid, uint32_t bin0, BinList& list) {
+// built so that q~ . b~ = |x|^2 - 2 q.x  or  -q.x/|x|).  chunk_minima() reduces the chunk to its four
+// bin minima; the caller then compares their minimum with the row's threshold (fast path) and only
+// chunks that beat it walk their bins.  The insert code exists ONCE in the kernel (non-unrolled
+// loops): the previous fully unrolled form was ~180 KB of SASS and ran out of the instruction cache.
+__device__ __forceinline__ void chunk_minima(float (&v)[32], int n_valid, float (&m)[4]) {
     if (n_valid < 32) {
 #pragma unroll
         for (int i = 0; i < 32; ++i) v[i] = (i < n_valid) ? v[i] : INFINITY;
     }
-    const float m0 = min8(v), m1 = min8(v + 8), m2 = min8(v + 16), m3 = min8(v + 24);
-    const float cm = fminf(fminf(m0, m1), fminf(m2, m3));
-    if (cm < list.tau()) {
-        if (m0 < list.tau()) list.insert(m0, bin0);
-        if (m1 < list.tau()) list.insert(m1, bin0 + 1);
-        if (m2 < list.tau()) list.insert(m2, bin0 + 2);
-        if (m3 < list.tau()) list.insert(m3, bin0 + 3);
-    }
+    m[0] = min8(v); m[1] = min8(v + 8); m[2] = min8(v + 16); m[3] = min8(v + 24);
 }
 
 // flags: bit 0 = debug, skip the epilogue arithmetic (measures the TMA + MMA pipeline alone)
+template <int NBL>
 __global__ void __launch_bounds__(kTcThreads, 1)
 exact_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                 int Q, int64_t N, int Dp, int num_kb, int stages, int m_tiles, int S,
@@ -127,7 +125,7 @@ exact_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     }
     if (warp == 1 && lane == 0) {
         for (int i = 0; i < stages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
-        for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 128); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 256); }
         mbar_init(a_full, 1);
         mbar_init(a_empty, 1);
         fence_barrier_init();
@@ -194,47 +192,59 @@ exact_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
             }
         }
     } else if (warp >= 4) {
-        // ====== epilogue: group eg owns accumulator stage eg, i.e. every other tile this CTA computes ======
+        // ====== epilogue: both groups work on EVERY tile, group eg on columns [eg*128, eg*128+128) ======
+        // (The MMA for tile t+2 waits for the epilogue of tile t, so one tile's epilogue must fit in
+        // one tile's MMA time; splitting the columns halves it without a third accumulator stage.)
         const int eg = (warp - 4) >> 2;
         const int ew = warp & 3;                       // TMEM lane quarter this warp may touch
         const int row = ew * 32 + lane;                // accumulator row == query within the tile
-        const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(eg * kTileN);
-        BinList list;
-        int tile_counter = 0, phase = 0;
+        constexpr int kCols = kTileN / kGroups;        // columns per group
+        const uint32_t tbase = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(eg * kCols);
+        BinList<NBL> list;
+        int as = 0, aph = 0;
         for (int u = blockIdx.x; u < units; u += gridDim.x) {
             const int mt = u % m_tiles, s = u / m_tiles;
             const int t0 = s * tiles_per_slice;
             const int t1 = min(tiles_total, t0 + tiles_per_slice);
             list.reset();
-            for (int t = t0; t < t1; ++t, ++tile_counter) {
-                if ((tile_counter & 1) != eg) continue;
-                mbar_wait(&tmem_full[eg], phase);
-                phase ^= 1;
+            for (int t = t0; t < t1; ++t) {
+                mbar_wait(&tmem_full[as], aph);
                 tc_fence_after();
                 if (!(flags & 1)) {
-                    const int64_t left = N - (int64_t)t * kTileN;
-                    const int n_valid = left < kTileN ? (int)left : kTileN;
-                    const uint32_t bin_base = (uint32_t)t * (kTileN / kBin);
-                    float va[32], vb[32];
-                    tmem_ld_x32(taddr, va);
-#pragma unroll
-                    for (int ch = 0; ch < kTileN / 32; ch += 2) {
-                        tmem_ld_wait(va);
-                        tmem_ld_x32(taddr + (uint32_t)((ch + 1) * 32), vb);
-                        consume_chunk(va, n_valid - ch * 32, bin_base + (uint32_t)(ch * 4), list);
-                        tmem_ld_wait(vb);
-                        if (ch + 2 < kTileN / 32) tmem_ld_x32(taddr + (uint32_t)((ch + 2) * 32), va);
-                        consume_chunk(vb, n_valid - (ch + 1) * 32, bin_base + (uint32_t)((ch + 1) * 4), list);
+                    const uint32_t taddr = tbase + (uint32_t)(as * kTileN);
+                    const int64_t left = N - ((int64_t)t * kTileN + eg * kCols);
+                    const int n_valid = left < kCols ? (int)left : kCols;      // may be <= 0: every column masked
+                    const uint32_t bin_base = (uint32_t)t * (kTileN / kBin) + (uint32_t)(eg * (kCols / kBin));
+                    float v[32];
+                    tmem_ld_x32(taddr, v);
+#pragma unroll 1
+                    for (int ch = 0; ch < kCols / 32; ++ch) {
+                        float m[4];
+                        tmem_ld_wait(v);
+                        chunk_minima(v, n_valid - ch * 32, m);
+                        // v is dead from here on: fetch the next chunk under the threshold test / inserts
+                        if (ch + 1 < kCols / 32) tmem_ld_x32(taddr + (uint32_t)((ch + 1) * 32), v);
+                        if (flags & 2) continue;
+                        const float cm = fminf(fminf(m[0], m[1]), fminf(m[2], m[3]));
+                        if (cm < list.tau()) {
+#pragma unroll 1
+                            for (int b = 0; b < 4; ++b) {
+                                const float mb = b == 0 ? m[0] : (b == 1 ? m[1] : (b == 2 ? m[2] : m[3]));
+                                if (mb < list.tau()) list.insert(mb, bin_base + (uint32_t)(ch * 4 + b));
+                            }
+                        }
                     }
                 }
                 tc_fence_before();
-                mbar_arrive(&tmem_empty[eg]);
+                mbar_arrive(&tmem_empty[as]);
+                as ^= 1;
+                if (as == 0) aph ^= 1;
             }
             const int q = mt * kTileM + row;
             if (q < Q) {
-                u64* dst = partial + (((size_t)q * S + s) * kGroups + eg) * kNBL;
+                u64* dst = partial + (((size_t)q * S + s) * kGroups + eg) * NBL;
 #pragma unroll
-                for (int e = 0; e < kNBL; ++e) dst[e] = pack_key(list.s[e], list.b[e]);
+                for (int e = 0; e < NBL; ++e) dst[e] = pack_key(list.s[e], list.b[e]);
             }
         }
     }
@@ -416,6 +426,8 @@ struct TcPlan {
 
 static int tc_row_elems(int D, int metric) { return metric == VDB_METRIC_L2 ? D + 16 : D; }
 
+static int g_tc_flags = 0;
+
 static bool plan_tc(int Q, int64_t N, int D, int k, int metric, TcPlan* p) {
     if (D % 8 != 0 || D <= 0 || Q <= 0 || N <= 0) return false;
     if (k > 16) return false;                       // kNBFinal bins of kBin rows must hold k results with margin
@@ -423,6 +435,7 @@ static bool plan_tc(int Q, int64_t N, int D, int k, int metric, TcPlan* p) {
     p->num_kb = (p->Dp + kBlockK - 1) / kBlockK;
     const int smem_max = max_smem_optin();
     int stages = kMaxStages;
+    if ((g_tc_flags >> 8) & 0xF) stages = (g_tc_flags >> 8) & 0xF;       // debug: cap the TMA ring depth
     // + 1024: the 1024-byte aligned extern array makes the compiler reserve 1 KB of static shared memory
     while (stages >= 2 && tc_layout(p->num_kb, stages).total + 1024 > smem_max) --stages;
     if (stages < 2) return false;
@@ -433,8 +446,11 @@ static bool plan_tc(int Q, int64_t N, int D, int k, int metric, TcPlan* p) {
     if (tiles_total > (1 << 24)) return false;
     p->tiles_total = (int)tiles_total;
     const int sms = sm_count();
-    // number of slices: minimise (waves x tiles per slice), i.e. the length of the critical path
-    long long best_cost = -1;
+    // Number of slices: minimise waves x time per unit.  A unit's time (in tile-MMA units) is the
+    // larger of its MMA time (tps) and its epilogue time: a per-tile fast path plus the bin-list
+    // inserts, whose count per row grows only with log(tps) -- short units are insert-bound
+    // (calibrated on B200: 1M x 384, S = 37 ran 254 tile-times per 106-tile unit).
+    double best_cost = -1.0;
     int best_S = 1;
     for (int S = 1; S <= 64; ++S) {
         int tps = (p->tiles_total + S - 1) / S;
@@ -443,7 +459,9 @@ static bool plan_tc(int Q, int64_t N, int D, int k, int metric, TcPlan* p) {
         long long units = (long long)p->m_tiles * S_eff;
         long long grid = units < sms ? units : sms;
         long long waves = (units + grid - 1) / grid;
-        long long cost = waves * (tps + 2);           // +2: per-unit A load / output overhead in tile units
+        double epi = 0.3 * tps + 39.0 * (log((double)tps) + 1.0);
+        double unit = (tps > epi ? (double)tps : epi) + 2.0;     // +2: per-unit A load / output overhead
+        double cost = (double)waves * unit;
         if (best_cost < 0 || cost < best_cost) { best_cost = cost; best_S = S; }
     }
     p->tiles_per_slice = (p->tiles_total + best_S - 1) / best_S;
@@ -462,14 +480,12 @@ static TcWorkspace tc_workspace(const TcPlan& p, int Q) {
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
     w.qbf16 = take((size_t)Q * p.Dp * 2);
-    w.partial = take((size_t)Q * p.S * kGroups * kNBL * 8);
+    w.partial = take((size_t)Q * p.S * kGroups * kNBLMax * 8);
     w.cand = take((size_t)Q * kNBFinal * kBin * 4);
     w.tau = take((size_t)Q * 4);
     w.total = off;
     return w;
 }
-
-static int g_tc_flags = 0;
 
 }  // namespace vdb
 
@@ -528,6 +544,8 @@ int vdb_exact_topk_tc(const float* q, int Q, const float* db, const void* mirror
     int32_t* cand = reinterpret_cast<int32_t*>(base + w.cand);
     float* tau = reinterpret_cast<float*>(base + w.tau);
 
+    // per-list depth: lists of 8 are enough when there are many of them (L * 8 >= 4 * kNBFinal), debug bit 2 forces 16
+    const int nbl = ((g_tc_flags & 4) || p.S * kGroups * 8 < 4 * kNBFinal) ? 16 : 8;
     tc_query_operand_kernel<<<sm_count() * 2, 256, 0, st>>>(q, qb, Q, D, p.Dp, metric);
     CUtensorMap map_a, map_b;
     int rc = make_map(&map_a, qb, Q, p.Dp, kTileM);
@@ -536,15 +554,21 @@ int vdb_exact_topk_tc(const float* q, int Q, const float* db, const void* mirror
     if (rc) return rc;
     {
         ProfScope prof(kProfExactTC, st);
-        VDB_CUDA(cudaFuncSetAttribute(exact_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem));
-        exact_tc_kernel<<<p.grid, kTcThreads, p.smem, st>>>(map_a, map_b, Q, N, p.Dp, p.num_kb, p.stages, p.m_tiles, p.S,
-                                                           p.tiles_per_slice, p.tiles_total, g_tc_flags, partial);
+        if (nbl == 16) {
+            VDB_CUDA(cudaFuncSetAttribute(exact_tc_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem));
+            exact_tc_kernel<16><<<p.grid, kTcThreads, p.smem, st>>>(map_a, map_b, Q, N, p.Dp, p.num_kb, p.stages, p.m_tiles, p.S,
+                                                                   p.tiles_per_slice, p.tiles_total, g_tc_flags, partial);
+        } else {
+            VDB_CUDA(cudaFuncSetAttribute(exact_tc_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem));
+            exact_tc_kernel<8><<<p.grid, kTcThreads, p.smem, st>>>(map_a, map_b, Q, N, p.Dp, p.num_kb, p.stages, p.m_tiles, p.S,
+                                                                  p.tiles_per_slice, p.tiles_total, g_tc_flags, partial);
+        }
     }
     VDB_CUDA(cudaGetLastError());
     const int L = p.S * kGroups;
-    const int C = next_pow2(L * kNBL < 64 ? 64 : L * kNBL);
+    const int C = next_pow2(L * nbl < 64 ? 64 : L * nbl);
     VDB_CUDA(cudaFuncSetAttribute(select_bins_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, C * 8));
-    select_bins_kernel<<<Q, 256, (size_t)C * 8, st>>>(partial, L, kNBL, kNBFinal, C, N, cand, tau);
+    select_bins_kernel<<<Q, 256, (size_t)C * 8, st>>>(partial, L, nbl, kNBFinal, C, N, cand, tau);
     count_launch(3);
     VDB_CUDA(cudaGetLastError());
     rc = vdb_rerank_f32(q, Q, db, ids, N, D, cand, kNBFinal * kBin, k, metric, out_d, out_i, stream);
