@@ -34,6 +34,16 @@ N_ROWS, DIM, N_QUERIES, K = 1_000_000, 384, 4096, 10
 SEED_DB, SEED_Q = 1234, 4321
 
 
+def _ncu_traffic(kernel: str):
+    """DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` summary
+    (profiles/r01_ncu_summary.json: dram__bytes_read.sum + dram__bytes_write.sum), or None."""
+    p = os.path.join(ROOT, "profiles", "r01_ncu_summary.json")
+    try:
+        return json.load(open(p))[kernel]["dram_bytes_per_launch"]
+    except Exception:
+        return None
+
+
 def _peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -263,6 +273,7 @@ def run_ours(args):
             "workload": f"exact brute-force cosine top-{K}, {N_ROWS} x {DIM} fp32 rows per GPU, {N_QUERIES}-query "
                         f"batch (BASELINE.json configs[1])",
             "engine": engine, "rows_total": N_ROWS * world, "recall_at_10_vs_oracle": recall,
+            "uncertified_queries_last_step": int(index.last_uncertified),
             "value_definition": "queries/s x shards: every query is answered over all shards; each GPU scans its "
                                 "own 1M rows, per-shard top-10 merged after an NCCL all-gather",
             "l2_policy": "inputs (1.5 GB of rows per GPU) are larger than the 126 MB L2",
@@ -274,8 +285,9 @@ def run_ours(args):
                 "h2d_bytes_per_step": int(Q_pin.numel() * 4),
                 "d2h_bytes_per_step": int(N_QUERIES * K * (4 + 8))},
         "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                     "frac": (achieved / peak) if achieved else None, "traffic": None,
-                     "kernel": engine, "kernel_ms": kernel_ms, "peak_source": peaks["source"],
+                     "frac": (achieved / peak) if achieved else None, "traffic": _ncu_traffic(engine),
+                     "kernel": engine, "kernel_ms": kernel_ms,
+                     "peak_source": peaks["source"] + (" burst (kernel timed in a <50 ms step)" if ms_step < 50 else " sustained"),
                      "algorithmic_flops_per_launch": flops},
     }
     if cpu_baseline is not None:
@@ -288,7 +300,7 @@ def run_ours(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--engine", default="auto", choices=["auto", "f32", "tc"])

@@ -1,0 +1,116 @@
+#!/usr/bin/env python
+"""Per-path measurements at the BASELINE.json config sizes that are NOT the headline bench line
+(bench.py covers configs[1]): PQ encode + ADC scan (configs[2]), batched HNSW search (configs[3]).
+Each prints one JSON line with the kernel's CUDA-event time and its roofline fraction against
+MEASURED_PEAKS.json (algorithmic bytes as defined in DESIGN.md).
+
+    python scripts/bench_paths.py adc  [N] [Q] [m] [R]     # default 10_000_000 1024 48 10
+    python scripts/bench_paths.py encode [N] [m]           # default 10_000_000 48   (D = 8 m)
+    python scripts/bench_paths.py hnsw [N] [D] [M] [ef] [Q] # default 200_000 768 32 128 10_000
+"""
+import json
+import os
+import random
+import sys
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from vector_db_b200 import _lib, ops  # noqa: E402
+
+dev = torch.device("cuda", 0)
+PEAKS = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(
+    os.path.join(ROOT, "MEASURED_PEAKS.json")) else {"hbm_gbs": 6650.0}
+HBM = PEAKS["hbm_gbs"]
+
+
+def _time_slot(slot, fn, iters, warm=3):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    _lib.profile_enable(True)
+    _lib.profile_read(slot)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        out = fn()
+    e1.record()
+    torch.cuda.synchronize()
+    n, ms = _lib.profile_read(slot)
+    _lib.profile_enable(False)
+    return out, ms / max(n, 1), e0.elapsed_time(e1) / iters
+
+
+def bench_adc(N=10_000_000, Q=1024, m=48, R=10):
+    g = torch.Generator(device=dev).manual_seed(7)
+    codes = torch.randint(0, 256, (N, m), device=dev, dtype=torch.uint8, generator=g)
+    lut = torch.rand((Q, m, 256), device=dev, generator=g)
+    (d, i), k_ms, step_ms = _time_slot("adc_scan", lambda: ops.pq_adc_topk(codes, lut, R), iters=3, warm=1)
+    alg_bytes = float(Q) * N * m
+    line = {"path": "adc_scan", "N": N, "Q": Q, "m": m, "R": R, "kernel_ms": k_ms, "step_ms": step_ms,
+            "qps": Q / (step_ms * 1e-3),
+            "roofline": {"bound": "hbm", "achieved": alg_bytes / (k_ms * 1e-3) / 1e9, "peak": HBM, "unit": "GB/s",
+                         "frac": alg_bytes / (k_ms * 1e-3) / 1e9 / HBM,
+                         "algorithmic_bytes": alg_bytes, "model": "Q*N*m code bytes (per-query code stream)"},
+            "lookups_per_s": alg_bytes / (k_ms * 1e-3)}
+    # spot parity on 2 queries against a torch gather restatement (fp32, j ascending)
+    acc = torch.zeros((2, N), device=dev)
+    for j in range(m):
+        acc += lut[:2, j, :].gather(1, codes[:, j].long().unsqueeze(0).expand(2, N))
+    ref = torch.topk(acc, R, dim=1, largest=False)
+    line["spot_check_ids_equal"] = bool(torch.equal(torch.sort(ref.indices, 1).values, torch.sort(i[:2], 1).values))
+    print(json.dumps(line), flush=True)
+
+
+def bench_encode(N=10_000_000, m=48):
+    D = 8 * m
+    g = torch.Generator(device=dev).manual_seed(11)
+    cb = torch.randn((m, 256, 8), device=dev, generator=g)
+    chunk = min(N, 2_000_000)                     # 2M x 384 fp32 = 3 GB per call; loop to cover N
+    X = torch.randn((chunk, D), device=dev, generator=g)
+    _, k_ms, step_ms = _time_slot("pq_encode", lambda: ops.pq_encode(X, cb), iters=2, warm=1)
+    alg_bytes = float(chunk) * D * 4 + float(chunk) * m
+    line = {"path": "pq_encode", "rows_per_call": chunk, "D": D, "m": m, "kernel_ms": k_ms,
+            "vectors_per_s": chunk / (k_ms * 1e-3), "ms_for_N": k_ms * N / chunk, "N": N,
+            "roofline": {"bound": "hbm", "achieved": alg_bytes / (k_ms * 1e-3) / 1e9, "peak": HBM, "unit": "GB/s",
+                         "frac": alg_bytes / (k_ms * 1e-3) / 1e9 / HBM, "algorithmic_bytes": alg_bytes}}
+    print(json.dumps(line), flush=True)
+
+
+def bench_hnsw(N=200_000, D=768, M=32, ef=128, Q=10_000):
+    from vector_db_b200.indexing import HNSW
+    from vector_db_b200.types import Node
+    rng = np.random.default_rng(1234)
+    X = rng.standard_normal((N, D), dtype=np.float32)
+    Qh = np.random.default_rng(4321).standard_normal((Q, D), dtype=np.float32)
+    idx = HNSW(M=M, ef_construction=200, rng=random.Random(42))
+    t0 = time.perf_counter()
+    idx.build_index([Node(id=i, embedding=X[i]) for i in range(N)])
+    torch.cuda.synchronize()
+    build_s = time.perf_counter() - t0
+    (d, i, st), k_ms, step_ms = _time_slot(
+        "hnsw_search", lambda: idx.search_batch(Qh, 10, ef=ef, return_stats=True), iters=3, warm=1)
+    evals, expans = float(st[:, 0].mean()), float(st[:, 1].mean())
+    alg_bytes = Q * (evals * D * 4 + expans * 2 * M * 4)
+    # recall against the exact scan on a sample
+    from vector_db_b200.indexing import ExactIndex
+    ex = ExactIndex(D, "l2")
+    ex.add_device(torch.arange(N, device=dev), torch.from_numpy(X).to(dev))
+    _, Iex = ex.search(Qh[:512], 10)
+    recall = float(np.mean([len(set(i[j]) & set(Iex[j])) / 10 for j in range(512)]))
+    line = {"path": "hnsw_search", "N": N, "D": D, "M": M, "ef": ef, "Q": Q, "build_s": build_s,
+            "inserts_per_s": N / build_s, "kernel_ms": k_ms, "step_ms": step_ms, "qps": Q / (step_ms * 1e-3),
+            "evals_per_query": evals, "expansions_per_query": expans, "recall_at_10_vs_exact": recall,
+            "roofline": {"bound": "hbm", "achieved": alg_bytes / (k_ms * 1e-3) / 1e9, "peak": HBM, "unit": "GB/s",
+                         "frac": alg_bytes / (k_ms * 1e-3) / 1e9 / HBM, "algorithmic_bytes": alg_bytes,
+                         "model": "evals*D*4 + expansions*2M*4 per query, counted by the kernel"}}
+    print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    what = sys.argv[1] if len(sys.argv) > 1 else "adc"
+    args = [int(a) for a in sys.argv[2:]]
+    {"adc": bench_adc, "encode": bench_encode, "hnsw": bench_hnsw}[what](*args)
