@@ -126,8 +126,9 @@ class PQIndex:
             raise ValueError("PQIndex supports at most 256 centroids per sub-space (nbits=8)")
         self.dim = self.m * self.dsub
         self.codebooks = torch.from_numpy(np.ascontiguousarray(cb)).to(self.device)
-        if self.K < 256:      # pad to 256 entries so LUT rows have the scan kernel's stride
-            pad = torch.full((self.m, 256 - self.K, self.dsub), 1e18, dtype=torch.float32, device=self.device)
+        if self.K < 256:      # pad to 256 entries so LUT rows have the scan kernel's stride; codes never
+            # reference the padding, which repeats centroid 0 so it cannot disturb the LUT's fixed-point scale
+            pad = self.codebooks[:, :1, :].expand(self.m, 256 - self.K, self.dsub)
             self._cb_lut = torch.cat([self.codebooks, pad], dim=1).contiguous()
         else:
             self._cb_lut = self.codebooks
