@@ -158,7 +158,7 @@ def run_ours(args):
     import torch
     import torch.distributed as dist
 
-    from vector_db_b200 import _lib, ops
+    from vector_db_b200 import _lib, ops, sharded
     from vector_db_b200.indexing import ExactIndex
 
     rank, local_rank, world = _dist_env()
@@ -185,11 +185,8 @@ def run_ours(args):
     def merge(d, i):
         if world == 1:
             return d, i
-        gd = [torch.empty_like(d) for _ in range(world)]
-        gi = [torch.empty_like(i) for _ in range(world)]
-        dist.all_gather(gd, d)
-        dist.all_gather(gi, i)
-        return ops.merge_topk(torch.stack(gd), torch.stack(gi), descending=True)
+        gd, gi = sharded.gather_topk(d, i)                      # one packed NCCL all-gather
+        return sharded.merge_shards(gd, gi, descending=True)
 
     def step_device():
         return merge(*index.search_device(Qd, K))
