@@ -124,6 +124,15 @@ void vdb_debug_set_tc_flags(int flags);
 int vdb_pq_encode(const float* x /*[dev] N*D*/, int64_t N, int D, int m, int K,
                   const float* codebooks /*[dev] m*K*dsub*/, uint8_t* codes /*[dev] N*m*/, void* stream);
 
+/* Same result (bit-exact codes) through the tensor cores, for dsub == 8 and K <= 256: two
+ * tcgen05.mma.kind::tf32 per (128-row tile, sub-space) give every |c|^2 - 2 x.c score, the epilogue
+ * keeps the centroids within a rigorous rounding margin of the minimum and resolves them with the
+ * reference's exact arithmetic.  ws: vdb_pq_encode_tc_workspace(m) bytes, 256-byte aligned. */
+int vdb_pq_encode_tc_supported(int64_t N, int D, int m, int K);
+size_t vdb_pq_encode_tc_workspace(int m);
+int vdb_pq_encode_tc(const float* x, int64_t N, int D, int m, int K, const float* codebooks, uint8_t* codes,
+                     void* ws, size_t ws_bytes, void* stream);
+
 /* ---- a12 PQ training (Lloyd iterations of scipy kmeans2 as called at pq.py:11) ------------------
  * One assignment + mean-update round for all m sub-spaces at once; an empty cluster keeps its
  * centroid.  `labels` int32 [m][N] receives the assignment made BEFORE the update (kmeans2's

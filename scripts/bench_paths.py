@@ -71,12 +71,15 @@ def bench_encode(N=10_000_000, m=48):
     cb = torch.randn((m, 256, 8), device=dev, generator=g)
     chunk = min(N, 2_000_000)                     # 2M x 384 fp32 = 3 GB per call; loop to cover N
     X = torch.randn((chunk, D), device=dev, generator=g)
-    _, k_ms, step_ms = _time_slot("pq_encode", lambda: ops.pq_encode(X, cb), iters=2, warm=1)
+    engine = os.environ.get("VDB_ENCODE_ENGINE", "auto")
+    codes, k_ms, step_ms = _time_slot("pq_encode", lambda: ops.pq_encode(X, cb, engine=engine), iters=3, warm=1)
     alg_bytes = float(chunk) * D * 4 + float(chunk) * m
-    line = {"path": "pq_encode", "rows_per_call": chunk, "D": D, "m": m, "kernel_ms": k_ms,
+    line = {"path": "pq_encode", "engine": engine, "rows_per_call": chunk, "D": D, "m": m, "kernel_ms": k_ms,
             "vectors_per_s": chunk / (k_ms * 1e-3), "ms_for_N": k_ms * N / chunk, "N": N,
             "roofline": {"bound": "hbm", "achieved": alg_bytes / (k_ms * 1e-3) / 1e9, "peak": HBM, "unit": "GB/s",
                          "frac": alg_bytes / (k_ms * 1e-3) / 1e9 / HBM, "algorithmic_bytes": alg_bytes}}
+    ns = 20000
+    line["codes_equal_fp32_kernel_on_sample"] = bool(torch.equal(codes[:ns], ops.pq_encode(X[:ns], cb, engine="f32")))
     print(json.dumps(line), flush=True)
 
 

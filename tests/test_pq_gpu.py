@@ -95,3 +95,34 @@ def test_pq_index_end_to_end_recall_with_rerank(golden_dir):
     Dx, Ix = O.exact_l2_topk(X, np.arange(1200) + 5000, Q, 10)
     np.testing.assert_array_equal(Ie, Ix)
     np.testing.assert_allclose(De, Dx, rtol=1e-5)
+
+
+@pytest.mark.parametrize("n,m,K,scale", [(20_000, 16, 256, 1.0), (9_001, 48, 256, 1.0), (5_000, 4, 64, 30.0),
+                                          (4_100, 6, 200, 1e-3)])
+def test_tensor_core_encode_bit_exact_vs_fp32_kernel_and_oracle(n, m, K, scale):
+    """tcgen05 tf32 candidate pass + exact tie resolution == the fp32 kernel (pinned to the reference's
+    codes above) on random data, with duplicated centroids (exact ties -> first index wins), rows that
+    sit on a centroid and rows between two centroids."""
+    from vector_db_b200 import ops
+    rng = np.random.default_rng(n + m)
+    cb = (rng.standard_normal((m, K, 8)) * scale).astype(np.float32)
+    cb[:, K // 2] = cb[:, 3]                                   # duplicate centroid: index 3 must win
+    X = (rng.standard_normal((n, 8 * m)) * scale).astype(np.float32)
+    X[:50] = cb[:, 7].reshape(-1)                              # rows exactly on centroid 7 of every sub-space
+    X[50:100] = (0.5 * (cb[:, 10].astype(np.float64) + cb[:, 11])).astype(np.float32).reshape(-1)   # midpoints
+    X[100:150] = cb[:, 3].reshape(-1)                          # on the duplicated centroid
+    cbd, Xd = _t(cb), _t(X)
+    tc = ops.pq_encode(Xd, cbd, engine="tc").cpu().numpy()
+    f32 = ops.pq_encode(Xd, cbd, engine="f32").cpu().numpy()
+    np.testing.assert_array_equal(tc, f32)
+    assert (tc[:50] == 7).all() and (tc[100:150] == 3).all()
+    ref = O.pq_encode(X[:600], list(cb))
+    np.testing.assert_array_equal(tc[:600], ref)
+
+
+def test_tensor_core_encode_golden_reference_codes(golden_dir):
+    from vector_db_b200 import ops
+    g8 = np.load(os.path.join(golden_dir, "pq8.npz"))          # dsub = 8, K = 64: codes from the reference itself
+    cb8 = _t(g8["centroids"])
+    np.testing.assert_array_equal(ops.pq_encode(_t(g8["X"]), cb8, engine="tc").cpu().numpy(), g8["codes"])
+    np.testing.assert_array_equal(ops.pq_encode(_t(g8["Y"]), cb8, engine="tc").cpu().numpy(), g8["codes_y"])

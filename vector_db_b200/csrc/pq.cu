@@ -9,35 +9,9 @@
 //           (SURVEY.md 8c), the step kernel restates one Lloyd round.
 //   ADC     no reference symbol; sub-space layout pq.py:48-62, squared form of pq.py:77-80.
 #include "common.cuh"
+#include "pq_common.cuh"
 
 namespace vdb {
-
-// ------------------------------------------------------------------------------------------
-// numpy pairwise_sum order over n rounded squares v[t] = rn(d[t]*d[t])   (n <= 128)
-template <int DS>
-__device__ __forceinline__ float np_sumsq(const float (&d)[DS]) {
-    if (DS < 8) {
-        float r = 0.f;
-#pragma unroll
-        for (int t = 0; t < DS; ++t) r = __fadd_rn(r, __fmul_rn(d[t], d[t]));
-        return r;
-    } else {
-        float r[8];
-#pragma unroll
-        for (int t = 0; t < 8; ++t) r[t] = __fmul_rn(d[t], d[t]);
-        constexpr int main_end = DS - (DS % 8);
-#pragma unroll
-        for (int i = 8; i < main_end; i += 8) {
-#pragma unroll
-            for (int t = 0; t < 8; ++t) r[t] = __fadd_rn(r[t], __fmul_rn(d[i + t], d[i + t]));
-        }
-        float res = __fadd_rn(__fadd_rn(__fadd_rn(r[0], r[1]), __fadd_rn(r[2], r[3])),
-                              __fadd_rn(__fadd_rn(r[4], r[5]), __fadd_rn(r[6], r[7])));
-#pragma unroll
-        for (int i = main_end; i < DS; ++i) res = __fadd_rn(res, __fmul_rn(d[i], d[i]));
-        return res;
-    }
-}
 
 // generic-dsub variant working from memory (x in global/L1, centroid row in shared)
 __device__ __forceinline__ float np_sumsq_mem(const float* __restrict__ c, const float* __restrict__ x, int n) {

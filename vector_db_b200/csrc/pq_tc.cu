@@ -1,0 +1,355 @@
+// PQ encode on the tensor cores (a11): codes[i][j] = argmin_c sqrt(sum((C_j[c]-x_ij)^2)), first min wins
+// (src/vector_db/inference/pq.py:77-89), for dsub = 8 and K <= 256.
+//
+// dsub = 8 is exactly one tf32 UMMA K step, so per (128-row tile, sub-space j) the whole 128 x 256
+// score matrix  s(c) = |c|^2 - 2 x.c  is TWO tcgen05.mma.kind::tf32 instructions: the fp32 rows x_ij
+// straight from the (N, D) matrix (TMA box 8 floats x 128 rows, 32-byte swizzle) against the
+// operand -2 C_j, plus a constant "ones" tile against the exact three-way tf32 split of |c|^2.
+// The accumulator is the score; the epilogue (one thread per row) takes its minimum, then collects
+// every centroid whose score is within a RIGOROUS margin of it (tf32 input rounding, Cauchy-Schwarz,
+// plus the reference's own fp32 rounding); a single candidate is the answer, several candidates are
+// resolved with the reference's exact arithmetic (numpy's pairwise-sum order, sqrt, first index wins)
+// -- so codes stay bit-exact although the heavy lifting is tf32.
+//
+// Roofline: HBM, algorithmic bytes per vector = 4 D + m (rows read once, codes written once).
+#include <cuda.h>
+#include <math.h>
+
+#include "common.cuh"
+#include "pq_common.cuh"
+#include "sm100.cuh"
+#include "tma_host.cuh"
+
+namespace vdb {
+
+using namespace sm100;
+
+constexpr int kEtThreads = 384;            // warp 0 TMA, 1 MMA, 2 TMEM alloc, 3 spare, 4-7 / 8-11 epilogue groups
+constexpr int kEtRows = 128;               // rows per tile (UMMA M)
+constexpr int kEtK = 256;                  // centroids per sub-space (UMMA N)
+constexpr int kEtABytes = kEtRows * 32;    // 4 KB: 128 rows x 8 fp32
+constexpr int kEtBBytes = kEtK * 32;       // 8 KB: 256 centroids x 8 fp32
+constexpr int kEtStageBytes = kEtABytes + 2 * kEtBBytes;   // A + (-2C) + norm split
+constexpr int kEtMaxStages = 8;
+
+struct EtSmem {
+    int stage_off, ones_off, mask_off, codes_off, bar_off, total;
+};
+__host__ __device__ inline EtSmem et_layout(int stages, int m) {
+    EtSmem L;
+    L.stage_off = 0;
+    L.ones_off = stages * kEtStageBytes;                       // 20 KB stages keep 1024-byte alignment
+    L.mask_off = L.ones_off + kEtABytes;
+    L.codes_off = L.mask_off + 8 * 256 * 4;                    // candidate masks [8 chunks][256 epilogue threads]
+    L.bar_off = (L.codes_off + kEtRows * m + 15) & ~15;        // code staging [128 rows][m]
+    L.total = L.bar_off + (2 * kEtMaxStages + 4) * 8 + 16;
+    return L;
+}
+
+// -2 C and the tf32 split of |c|^2, padded to 256 centroids per sub-space (padding can never win)
+__global__ void pq_tc_operands_kernel(const float* __restrict__ cb, int m, int K, float* __restrict__ bc,
+                                      float* __restrict__ bn, float* __restrict__ cmax) {
+    const int j = blockIdx.x;
+    __shared__ float red[256];
+    float mx = 0.f;
+    for (int c = threadIdx.x; c < 256; c += blockDim.x) {
+        float* oc = bc + ((size_t)j * 256 + c) * 8;
+        float* on = bn + ((size_t)j * 256 + c) * 8;
+        float s = 0.f;
+        if (c < K) {
+            const float* src = cb + ((size_t)j * K + c) * 8;
+#pragma unroll
+            for (int t = 0; t < 8; ++t) { const float v = src[t]; oc[t] = -2.f * v; s = fmaf(v, v, s); }
+            mx = fmaxf(mx, s);
+        } else {
+#pragma unroll
+            for (int t = 0; t < 8; ++t) oc[t] = 0.f;
+            s = 3.0e38f;
+        }
+        const float h = __uint_as_float(__float_as_uint(s) & 0xFFFFE000u);
+        const float r1 = s - h;
+        const float mid = __uint_as_float(__float_as_uint(r1) & 0xFFFFE000u);
+        const float lo = r1 - mid;
+        on[0] = h; on[1] = mid; on[2] = lo;
+#pragma unroll
+        for (int t = 3; t < 8; ++t) on[t] = 0.f;
+    }
+    red[threadIdx.x] = mx;
+    __syncthreads();
+    for (int o = blockDim.x / 2; o > 0; o >>= 1) {
+        if (threadIdx.x < o) red[threadIdx.x] = fmaxf(red[threadIdx.x], red[threadIdx.x + o]);
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) cmax[j] = sqrtf(red[0]) * 1.0000005f;     // |c| from the fma-order |c|^2, rounded up
+}
+
+__device__ __forceinline__ float min32(const float (&v)[32]) {
+    float a = fminf(fminf(v[0], v[1]), v[2]), b = fminf(fminf(v[3], v[4]), v[5]);
+    float c = fminf(fminf(v[6], v[7]), v[8]), d = fminf(fminf(v[9], v[10]), v[11]);
+    float e = fminf(fminf(v[12], v[13]), v[14]), f = fminf(fminf(v[15], v[16]), v[17]);
+    float g = fminf(fminf(v[18], v[19]), v[20]), h = fminf(fminf(v[21], v[22]), v[23]);
+    float i = fminf(fminf(v[24], v[25]), v[26]), j = fminf(fminf(v[27], v[28]), v[29]);
+    float k = fminf(v[30], v[31]);
+    a = fminf(fminf(a, b), c); d = fminf(fminf(d, e), f); g = fminf(fminf(g, h), i); j = fminf(j, k);
+    return fminf(fminf(a, d), fminf(g, j));
+}
+
+// bit i of the result: v[i] <= thr
+__device__ __forceinline__ uint32_t le_mask32(const float (&v)[32], float thr) {
+    uint32_t mask = 0;
+#pragma unroll
+    for (int i = 0; i < 32; ++i) mask |= (v[i] <= thr) ? (1u << i) : 0u;
+    return mask;
+}
+
+__global__ void __launch_bounds__(kEtThreads, 1)
+pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_bc,
+                    const __grid_constant__ CUtensorMap map_bn, const float* __restrict__ x, int64_t N, int D, int m,
+                    int K, const float* __restrict__ cb, const float* __restrict__ cmax, int stages, int64_t tiles,
+                    uint8_t* __restrict__ codes) {
+    extern __shared__ __align__(1024) unsigned char smem[];
+    if ((smem_u32(smem) & 1023u) != 0) __trap();
+    const EtSmem L = et_layout(stages, m);
+    unsigned char* sStage = smem + L.stage_off;
+    float* sOnes = reinterpret_cast<float*>(smem + L.ones_off);
+    uint32_t* sMask = reinterpret_cast<uint32_t*>(smem + L.mask_off);
+    uint8_t* sCodes = smem + L.codes_off;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L.bar_off);
+    uint64_t* full = bars;                          // [stages]
+    uint64_t* empty = bars + kEtMaxStages;          // [stages]
+    uint64_t* tmem_full = bars + 2 * kEtMaxStages;  // [2]
+    uint64_t* tmem_empty = tmem_full + 2;           // [2]
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    // constant A tile of the norm MMA: every row is (1,1,1,0,0,0,0,0); with the 32-byte swizzle the two
+    // 16-byte halves of row r trade places when bit 2 of r is set
+    if (threadIdx.x < kEtRows) {
+        const int r = threadIdx.x;
+        const int first = ((r >> 2) & 1) ? 4 : 0;
+#pragma unroll
+        for (int t = 0; t < 8; ++t) sOnes[r * 8 + t] = (t >= first && t < first + 3) ? 1.f : 0.f;
+    }
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&map_x);
+        tma_prefetch_desc(&map_bc);
+        tma_prefetch_desc(&map_bn);
+    }
+    if (warp == 1 && lane == 0) {
+        for (int i = 0; i < stages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1 + 4); }   // MMA commit + 4 epilogue warps
+        for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 128); }
+        fence_barrier_init();
+    }
+    if (warp == 2) tmem_alloc(tmem_ptr, 512);
+    fence_proxy_async();                 // the generic-proxy writes of sOnes must be visible to the MMA (async proxy)
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr;
+
+    if (warp == 0) {
+        // ================= TMA producer =================
+        if (lane == 0) {
+            int st = 0, ph = 0;
+            for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+                for (int j = 0; j < m; ++j) {
+                    mbar_wait(&empty[st], ph ^ 1);
+                    unsigned char* base = sStage + (size_t)st * kEtStageBytes;
+                    mbar_expect_tx(&full[st], (uint32_t)kEtStageBytes);
+                    tma_load_2d(base, &map_x, &full[st], j * 8, (int)(tile * kEtRows), kEvictFirst);
+                    tma_load_2d(base + kEtABytes, &map_bc, &full[st], 0, j * 256, kEvictLast);
+                    tma_load_2d(base + kEtABytes + kEtBBytes, &map_bn, &full[st], 0, j * 256, kEvictLast);
+                    if (++st == stages) { st = 0; ph ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ================= MMA issuer =================
+        if (lane == 0) {
+            const uint32_t idesc = make_idesc_tf32(kEtRows, kEtK);
+            const uint64_t d_ones = make_desc_k_sw32(smem_u32(sOnes));
+            int st = 0, ph = 0, as = 0, aph = 0;
+            for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+                for (int j = 0; j < m; ++j) {
+                    mbar_wait(&tmem_empty[as], aph ^ 1);
+                    mbar_wait(&full[st], ph);
+                    tc_fence_after();
+                    const uint32_t base = smem_u32(sStage + (size_t)st * kEtStageBytes);
+                    const uint32_t d_tmem = tmem_base + (uint32_t)(as * kEtK);
+                    umma_tf32(d_tmem, make_desc_k_sw32(base), make_desc_k_sw32(base + kEtABytes), idesc, 0u);
+                    umma_tf32(d_tmem, d_ones, make_desc_k_sw32(base + kEtABytes + kEtBBytes), idesc, 1u);
+                    umma_commit(&empty[st]);
+                    umma_commit(&tmem_full[as]);
+                    if (++st == stages) { st = 0; ph ^= 1; }
+                    as ^= 1;
+                    if (as == 0) aph ^= 1;
+                }
+            }
+        }
+    } else if (warp >= 4) {
+        // ================= epilogue: one thread per row; group eg owns accumulator stage eg (every other step) =================
+        // The step's operand stage stays resident until the epilogue releases it, so the exact fp32 row
+        // slice and the centroids (-2c, exact) are read back from shared memory, never from global.
+        const int eg = (warp - 4) >> 2;
+        const int ew = warp & 3;
+        const int rt = ew * 32 + lane;                 // row within the tile == TMEM lane
+        const int et = threadIdx.x - 128;              // 0..255
+        const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(eg * kEtK);
+        const int swz = ((rt >> 2) & 1) << 4;          // 32-byte swizzle: 16-byte halves of row r swap when bit 2 of r is set
+        int64_t step = 0;
+        int st = 0, phase = 0;
+        for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+            for (int j = 0; j < m; ++j, ++step, st = (st + 1 == stages ? 0 : st + 1)) {
+                if ((int)(step & 1) != eg) continue;
+                mbar_wait(&tmem_full[eg], phase);      // MMA done => its operands were in shared memory too
+                phase ^= 1;
+                tc_fence_after();
+                const unsigned char* sA = sStage + (size_t)st * kEtStageBytes;
+                const unsigned char* sBc = sA + kEtABytes;
+                float xs[8];
+                {
+                    const float4 a = *reinterpret_cast<const float4*>(sA + rt * 32 + (0 ^ swz));
+                    const float4 b = *reinterpret_cast<const float4*>(sA + rt * 32 + (16 ^ swz));
+                    xs[0] = a.x; xs[1] = a.y; xs[2] = a.z; xs[3] = a.w; xs[4] = b.x; xs[5] = b.y; xs[6] = b.z; xs[7] = b.w;
+                }
+                // pass 1: minimum score of the row
+                float gmin = INFINITY;
+                {
+                    float v[32];
+                    tmem_ld_x32(taddr, v);
+#pragma unroll 1
+                    for (int ch = 0; ch < 8; ++ch) {
+                        tmem_ld_wait(v);
+                        const float cm = min32(v);
+                        if (ch + 1 < 8) tmem_ld_x32(taddr + (uint32_t)((ch + 1) * 32), v);
+                        gmin = fminf(gmin, cm);
+                    }
+                }
+                // rigorous candidate margin (see file header): tf32 rounding of both operands + fp32 noise
+                float xx = 0.f;
+#pragma unroll
+                for (int t = 0; t < 8; ++t) xx = fmaf(xs[t], xs[t], xx);
+                const float xn = sqrtf(xx) * 1.0000005f, cm_j = __ldg(cmax + j);
+                const float thr = gmin + 0.0081f * xn * cm_j + 1e-5f * (xn + cm_j) * (xn + cm_j);
+                // pass 2: every centroid within the margin
+                int cnt = 0, first = -1;
+                {
+                    float v[32];
+                    tmem_ld_x32(taddr, v);
+#pragma unroll 1
+                    for (int ch = 0; ch < 8; ++ch) {
+                        tmem_ld_wait(v);
+                        const uint32_t mask = le_mask32(v, thr);
+                        if (ch + 1 < 8) tmem_ld_x32(taddr + (uint32_t)((ch + 1) * 32), v);
+                        sMask[ch * 256 + et] = mask;
+                        if (mask && first < 0) first = ch * 32 + __ffs(mask) - 1;
+                        cnt += __popc(mask);
+                    }
+                }
+                tc_fence_before();
+                mbar_arrive(&tmem_empty[eg]);          // accumulator drained: the MMA two steps ahead may overwrite it
+                int code = first < 0 ? 0 : first;
+                if (cnt > 1) {
+                    // several candidates: the reference's own arithmetic decides (pq.py:79-80), first minimum wins
+                    float best = INFINITY;
+                    for (int ch = 0; ch < 8; ++ch) {
+                        uint32_t mask = sMask[ch * 256 + et];
+                        while (mask) {
+                            const int c = ch * 32 + __ffs(mask) - 1;
+                            mask &= mask - 1;
+                            if (c < K) {
+                                const int cs = ((c >> 2) & 1) << 4;
+                                const float4 a = *reinterpret_cast<const float4*>(sBc + c * 32 + (0 ^ cs));
+                                const float4 b = *reinterpret_cast<const float4*>(sBc + c * 32 + (16 ^ cs));
+                                // the operand holds -2c (exact), so c = -0.5 * operand (exact)
+                                float d[8] = {-0.5f * a.x - xs[0], -0.5f * a.y - xs[1], -0.5f * a.z - xs[2], -0.5f * a.w - xs[3],
+                                              -0.5f * b.x - xs[4], -0.5f * b.y - xs[5], -0.5f * b.z - xs[6], -0.5f * b.w - xs[7]};
+                                const float dist = sqrtf(np_sumsq<8>(d));
+                                if (dist < best) { best = dist; code = c; }
+                            }
+                        }
+                    }
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&empty[st]);    // this warp no longer reads the operand stage
+                sCodes[rt * m + j] = (uint8_t)code;
+            }
+            // the tile's codes are one contiguous run of 128*m bytes in global memory
+            named_bar_sync(1, 256);
+            const int64_t row0 = tile * kEtRows;
+            const int64_t nbytes = (N - row0 < kEtRows ? N - row0 : kEtRows) * m;
+            uint8_t* dst = codes + row0 * m;
+            if ((reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
+                const int64_t n16 = nbytes >> 4;
+                for (int64_t i = et; i < n16; i += 256)
+                    reinterpret_cast<uint4*>(dst)[i] = reinterpret_cast<const uint4*>(sCodes)[i];
+                for (int64_t i = (n16 << 4) + et; i < nbytes; i += 256) dst[i] = sCodes[i];
+            } else {
+                for (int64_t i = et; i < nbytes; i += 256) dst[i] = sCodes[i];
+            }
+            named_bar_sync(1, 256);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) tmem_dealloc(tmem_base, 512);
+}
+
+}  // namespace vdb
+
+using namespace vdb;
+
+static size_t et_ws_operand(int m) { return (size_t)m * 256 * 8 * 4; }
+
+extern "C" {
+
+int vdb_pq_encode_tc_supported(int64_t N, int D, int m, int K) {
+    return (N > 0 && N < (1ll << 31) && m > 0 && D == 8 * m && K > 0 && K <= 256 && m <= 512) ? 1 : 0;
+}
+
+size_t vdb_pq_encode_tc_workspace(int m) { return 2 * et_ws_operand(m) + (((size_t)m * 4 + 255) & ~(size_t)255) + 256; }
+
+int vdb_pq_encode_tc(const float* x, int64_t N, int D, int m, int K, const float* codebooks, uint8_t* codes, void* ws,
+                     size_t ws_bytes, void* stream) {
+    VDB_REQUIRE(vdb_pq_encode_tc_supported(N, D, m, K), VDB_ERR_UNSUPPORTED,
+                "tensor-core encode needs dsub == 8, K <= 256, N < 2^31 (N=%lld D=%d m=%d K=%d)", (long long)N, D, m, K);
+    VDB_REQUIRE(x && codebooks && codes && ws, VDB_ERR_INVALID, "vdb_pq_encode_tc: null pointer");
+    VDB_REQUIRE(ws_bytes >= vdb_pq_encode_tc_workspace(m), VDB_ERR_WORKSPACE, "workspace %zu < %zu", ws_bytes,
+                vdb_pq_encode_tc_workspace(m));
+    VDB_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0 && (reinterpret_cast<uintptr_t>(ws) & 255) == 0 &&
+                    (reinterpret_cast<uintptr_t>(codebooks) & 15) == 0,
+                VDB_ERR_INVALID, "rows / codebooks / workspace must be 16 / 16 / 256-byte aligned");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    char* base = static_cast<char*>(ws);
+    float* bc = reinterpret_cast<float*>(base);
+    float* bn = reinterpret_cast<float*>(base + et_ws_operand(m));
+    float* cmax = reinterpret_cast<float*>(base + 2 * et_ws_operand(m));
+    pq_tc_operands_kernel<<<m, 256, 0, st>>>(codebooks, m, K, bc, bn, cmax);
+    count_launch(1);
+    CUtensorMap map_x, map_bc, map_bn;
+    int rc = tma_map_2d(&map_x, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, x, (uint64_t)D, (uint64_t)N, (uint64_t)D * 4, 8, kEtRows,
+                        CU_TENSOR_MAP_SWIZZLE_32B);
+    if (rc) return rc;
+    rc = tma_map_2d(&map_bc, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, bc, 8, (uint64_t)m * 256, 32, 8, kEtK, CU_TENSOR_MAP_SWIZZLE_32B);
+    if (rc) return rc;
+    rc = tma_map_2d(&map_bn, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, bn, 8, (uint64_t)m * 256, 32, 8, kEtK, CU_TENSOR_MAP_SWIZZLE_32B);
+    if (rc) return rc;
+    int stages = kEtMaxStages;
+    const int smem_max = max_smem_optin();
+    while (stages >= 2 && et_layout(stages, m).total + 1024 > smem_max) --stages;
+    VDB_REQUIRE(stages >= 2, VDB_ERR_UNSUPPORTED, "m=%d does not fit shared memory", m);
+    const size_t smem = (size_t)et_layout(stages, m).total;
+    const int64_t tiles = (N + kEtRows - 1) / kEtRows;
+    const int grid = (int)(tiles < sm_count() ? tiles : sm_count());
+    VDB_CUDA(cudaFuncSetAttribute(pq_encode_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    {
+        ProfScope prof(kProfPqEncode, st);
+        pq_encode_tc_kernel<<<grid, kEtThreads, smem, st>>>(map_x, map_bc, map_bn, x, N, D, m, K, codebooks, cmax, stages, tiles,
+                                                           codes);
+    }
+    count_launch(1);
+    VDB_CUDA(cudaGetLastError());
+    return VDB_OK;
+}
+
+}  // extern "C"

@@ -87,6 +87,15 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint
         "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+// D[tmem] (+)= A[smem] * B[smem]^T, tf32 x tf32 -> fp32 (fp32 operands in shared memory, K = 8 per instruction)
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(tmem_d),
+        "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
 // mbarrier arrive once every MMA issued so far by this thread has completed (implies fence::before).
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
@@ -125,6 +134,14 @@ __device__ __forceinline__ void tmem_ld_wait(float (&v)[32]) {
 // stepping K by 16 elements inside the swizzled row = +32 B on the start address.
 __device__ __forceinline__ uint64_t make_desc_k_sw128(uint32_t saddr) {
     return (uint64_t)((saddr >> 4) & 0x3FFF) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+}
+// Same for rows of 32 bytes (8 fp32 / 16 bf16), SWIZZLE_32B, 8-row groups 256 B apart; tile 256-byte aligned.
+__device__ __forceinline__ uint64_t make_desc_k_sw32(uint32_t saddr) {
+    return (uint64_t)((saddr >> 4) & 0x3FFF) | (1ull << 16) | (16ull << 32) | (1ull << 46) | (6ull << 61);
+}
+// kind::tf32 instruction descriptor: D fp32, A/B tf32, both K-major, M x N tile.
+__host__ __device__ constexpr uint32_t make_idesc_tf32(int M, int N) {
+    return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 // kind::f16 instruction descriptor: D fp32, A/B bf16, both K-major, M x N tile.
 __host__ __device__ constexpr uint32_t make_idesc_bf16(int M, int N) {

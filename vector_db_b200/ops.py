@@ -87,8 +87,10 @@ def rerank_f32(q: torch.Tensor, db: torch.Tensor, cand: torch.Tensor, k: int, me
     return out_d, out_i
 
 
-def pq_encode(x: torch.Tensor, codebooks: torch.Tensor) -> torch.Tensor:
-    """x [N,D] fp32, codebooks [m,K,dsub] fp32 -> codes uint8 [N,m]."""
+def pq_encode(x: torch.Tensor, codebooks: torch.Tensor, engine: str = "auto") -> torch.Tensor:
+    """x [N,D] fp32, codebooks [m,K,dsub] fp32 -> codes uint8 [N,m] (bit-exact with the reference).
+    engine: "auto" = tensor-core kernel when the shape allows it (dsub == 8, K <= 256) and the batch
+    is large enough to fill the machine, "tc" / "f32" force one of the two kernels."""
     x = _f32(x, "x")
     codebooks = _f32(codebooks, "codebooks")
     n, d = x.shape
@@ -96,7 +98,16 @@ def pq_encode(x: torch.Tensor, codebooks: torch.Tensor) -> torch.Tensor:
     if m * dsub != d:
         raise ValueError(f"codebooks {tuple(codebooks.shape)} do not tile dim {d}")
     codes = torch.empty((n, m), dtype=torch.uint8, device=x.device)
-    check(load().vdb_pq_encode(ptr(x), n, d, m, K, ptr(codebooks), ptr(codes), _lib.stream_ptr(x.device)))
+    lib = load()
+    tc_ok = n > 0 and bool(lib.vdb_pq_encode_tc_supported(n, d, m, K))
+    if engine == "tc" and not tc_ok:
+        raise ValueError("tensor-core encode needs dsub == 8 and K <= 256")
+    if tc_ok and (engine == "tc" or (engine == "auto" and n >= 4096)):
+        ws = _ws("pq_encode_tc", lib.vdb_pq_encode_tc_workspace(m), x.device)
+        check(lib.vdb_pq_encode_tc(ptr(x), n, d, m, K, ptr(codebooks), ptr(codes), ptr(ws), ws.numel(),
+                                   _lib.stream_ptr(x.device)))
+    else:
+        check(lib.vdb_pq_encode(ptr(x), n, d, m, K, ptr(codebooks), ptr(codes), _lib.stream_ptr(x.device)))
     return codes
 
 
