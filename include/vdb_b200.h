@@ -186,6 +186,26 @@ int vdb_hnsw_insert(const float* db, int64_t N, int D, int32_t* adj0, int deg0, 
                     int32_t first, int32_t count, int M, int efc, int32_t* state /*[dev] 4*/,
                     const uint32_t* alive, void* ws, size_t ws_bytes, void* stream);
 
+/* ---- a7, wave-parallel construction -----------------------------------------
+ * The reference builds node by node (hnsw.py:143-225, ~50 inserts/s); these two entry points build
+ * level by level, top-down, in waves: vdb_hnsw_build_search runs the reference's insert-time search
+ * (greedy descent hnsw.py:174-176, ef_construction beam hnsw.py:182) for every node of a wave against
+ * the graph built so far and returns its M closest (hnsw.py:188); vdb_hnsw_reverse_merge links the
+ * wave into its neighbours' lists and cuts them to the closest `deg` (hnsw.py:199-213).  Lists are
+ * kept sorted by distance, with the distances in a parallel float array.  The result is an
+ * approximation of the sequential build (wave members do not see each other), not the reference's
+ * graph; vdb_hnsw_insert remains the parity builder. */
+size_t vdb_hnsw_build_search_workspace(int count, int efc, int deg0);
+int vdb_hnsw_build_search(const float* db, int64_t N, int D, const int32_t* adj0, int deg0,
+                          const int32_t* adj_up, int deg_up, const int32_t* up_ptr,
+                          const int32_t* nodes /*[dev] count rows of this wave*/, int count, int level,
+                          int32_t entry_row, int max_level, int32_t seed_entry, int efc, int M,
+                          int32_t* out_rows /*[dev] count*M*/, float* out_d /*[dev] count*M*/,
+                          void* ws, size_t ws_bytes, void* stream);
+int vdb_hnsw_reverse_merge(int32_t* adj /*[dev] lists*deg*/, float* adjd /*[dev] lists*deg*/, int deg,
+                           const int32_t* list_idx /*[dev] segments*/, const int32_t* seg_start /*[dev] segments+1*/,
+                           int segments, const int32_t* in_rows /*[dev]*/, const float* in_d /*[dev]*/, void* stream);
+
 /* ---- e: multi-GPU merge -----------------------------------------------------------------------
  * lists: L sorted lists per query, d [L][Q][k] / i [L][Q][k] (the all-gathered per-shard results);
  * selects the k best by (d, list, position) -- equal to (d,id) order when shard l owns smaller ids

@@ -90,8 +90,13 @@ def bench_hnsw(N=200_000, D=768, M=32, ef=128, Q=10_000):
     X = rng.standard_normal((N, D), dtype=np.float32)
     Qh = np.random.default_rng(4321).standard_normal((Q, D), dtype=np.float32)
     idx = HNSW(M=M, ef_construction=200, rng=random.Random(42))
+    builder = os.environ.get("VDB_HNSW_BUILDER", "wave" if N > 20000 else "sequential")
     t0 = time.perf_counter()
-    idx.build_index([Node(id=i, embedding=X[i]) for i in range(N)])
+    if builder == "wave":
+        stats = idx.build_from_arrays(range(N), X)
+    else:
+        idx.build_index([Node(id=i, embedding=X[i]) for i in range(N)])
+        stats = {}
     torch.cuda.synchronize()
     build_s = time.perf_counter() - t0
     (d, i, st), k_ms, step_ms = _time_slot(
@@ -104,7 +109,8 @@ def bench_hnsw(N=200_000, D=768, M=32, ef=128, Q=10_000):
     ex.add_device(torch.arange(N, device=dev), torch.from_numpy(X).to(dev))
     _, Iex = ex.search(Qh[:512], 10)
     recall = float(np.mean([len(set(i[j]) & set(Iex[j])) / 10 for j in range(512)]))
-    line = {"path": "hnsw_search", "N": N, "D": D, "M": M, "ef": ef, "Q": Q, "build_s": build_s,
+    line = {"path": "hnsw_search", "N": N, "D": D, "M": M, "ef": ef, "Q": Q, "builder": builder, "build_stats": stats,
+            "build_s": build_s,
             "inserts_per_s": N / build_s, "kernel_ms": k_ms, "step_ms": step_ms, "qps": Q / (step_ms * 1e-3),
             "evals_per_query": evals, "expansions_per_query": expans, "recall_at_10_vs_exact": recall,
             "roofline": {"bound": "hbm", "achieved": alg_bytes / (k_ms * 1e-3) / 1e9, "peak": HBM, "unit": "GB/s",

@@ -158,3 +158,43 @@ def test_oracle_and_gpu_agree_on_larger_graph():
         res = o.search(Q[qi], 10, 100)
         assert [r[1] for r in res] == I[qi].tolist()
         assert o.n_evals == st[qi, 0]
+
+
+def test_wave_parallel_builder_graph_invariants_and_recall():
+    """The wave-parallel builder (vdb_hnsw_build_search + vdb_hnsw_reverse_merge) is NOT the reference's
+    graph; it must be a well-formed HNSW graph whose search quality matches the sequential-semantics build."""
+    import random
+    from vector_db_b200.indexing import HNSW, ExactIndex
+    from vector_db_b200.types import Node
+    rng = np.random.default_rng(11)
+    n, d, M, efc = 6000, 32, 8, 60
+    X = rng.standard_normal((n, d)).astype(np.float32)
+    Q = rng.standard_normal((200, d)).astype(np.float32)
+    fast = HNSW(M=M, ef_construction=efc, rng=random.Random(42))
+    stats = fast.build_from_arrays(range(100, 100 + n), X, wave_max=1024, seed=256)
+    assert stats["nodes"] == n and len(fast.node_store) == n and fast.max_level == stats["top_level"]
+    adj0, adj_up, up_ptr, levels, ids = fast._host_graph()
+    assert adj0.shape == (n, 2 * M) and adj0.max() < n and adj0.min() >= -1
+    assert not (adj0 == np.arange(n)[:, None]).any()                     # no self links
+    deg = (adj0 >= 0).sum(1)
+    assert deg.min() >= 1 and deg.mean() > M
+    for r in (0, 17, n - 1):                                            # lists are sorted by distance, no duplicates
+        row = adj0[r][adj0[r] >= 0]
+        dist = np.linalg.norm(X[row] - X[r], axis=1)
+        assert np.all(np.diff(dist) >= -1e-5) and len(set(row.tolist())) == len(row)
+    seq = HNSW(M=M, ef_construction=efc, rng=random.Random(42))
+    seq.build_index([Node(id=100 + i, embedding=X[i]) for i in range(n)])
+    ex = ExactIndex(d, "l2")
+    ex.add(range(100, 100 + n), X)
+    _, Iex = ex.search(Q, 10)
+
+    def recall(index):
+        _, I = index.search_batch(Q, 10, ef=64)
+        return float(np.mean([len(set(I[j]) & set(Iex[j])) / 10 for j in range(Q.shape[0])]))
+
+    r_fast, r_seq = recall(fast), recall(seq)
+    assert r_fast >= r_seq - 0.03, (r_fast, r_seq)
+    # the reference-API single-query search works on the wave-built graph too (ids are external ids)
+    fast.storage.save(Node(id=100, embedding=X[0]))
+    got = fast.search(X[0], k=1, ef=32)
+    assert got and got[0][0].id == 100 and got[0][1] < 1e-6

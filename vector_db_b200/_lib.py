@@ -51,6 +51,10 @@ SIGNATURES = {
     "vdb_hnsw_insert_workspace": (_sz, [_i, _i]),
     "vdb_hnsw_insert": (_i, [_p, _i64, _i, _p, _i, _p, _i, _p, _p, C.c_int32, C.c_int32, _i, _i, _p, _p,
                              _p, _sz, _p]),
+    "vdb_hnsw_build_search_workspace": (_sz, [_i, _i, _i]),
+    "vdb_hnsw_build_search": (_i, [_p, _i64, _i, _p, _i, _p, _i, _p, _p, _i, _i, C.c_int32, _i, C.c_int32, _i, _i,
+                                   _p, _p, _p, _sz, _p]),
+    "vdb_hnsw_reverse_merge": (_i, [_p, _p, _i, _p, _p, _i, _p, _p, _p]),
     "vdb_merge_topk": (_i, [_p, _p, _i, _i, _i, _i, _p, _p, _p]),
 }
 

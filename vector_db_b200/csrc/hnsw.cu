@@ -458,6 +458,118 @@ hnsw_insert_kernel(Graph g, const int32_t* __restrict__ levels, int32_t first, i
     if (tid == 0) { state[2] = (int32_t)(uint32_t)(total_evals & 0xFFFFFFFFull); state[3] = (int32_t)(uint32_t)(total_evals >> 32); }
 }
 
+// ------------------------------------------------------------------------------------------
+// Batched construction (SURVEY.md 8f rank 1 -- the reference builds node by node at ~50 inserts/s,
+// hnsw.py:143-225, which cannot produce the 1M x 768 graph of BASELINE configs[3]).  Levels are
+// built top-down; within a level, nodes are inserted in waves: every node of a wave runs the
+// reference's search on the graph built so far (greedy descent on the finished upper levels, then
+// the ef_construction beam on this level, hnsw.py:174-182), keeps its M closest as links
+// (hnsw.py:188) and is then reverse-linked into its neighbours' lists, which are cut to the closest
+// `cap` entries (hnsw.py:199-213).  Nodes of one wave do not see each other, so the graph is a
+// wave-parallel approximation of the sequential build, NOT the reference's graph.
+//
+// One CTA per wave node.  out_rows/out_d [count][M]: the M closest found, ascending, -1/inf padded.
+__global__ void __launch_bounds__(kHnswThreads)
+hnsw_build_search_kernel(Graph g, const int32_t* __restrict__ nodes, int count, int level, int32_t entry_row,
+                         int max_level, int32_t seed_entry, int efc, int M, int CC, int NM, int H, uint32_t* global_hash,
+                         int32_t* __restrict__ out_rows, float* __restrict__ out_d, int* __restrict__ overflow_flag) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    BeamMem m;
+    carve(m, smem_raw, g.D, CC, efc, NM, H, global_hash ? global_hash + (size_t)blockIdx.x * H : nullptr);
+    const int tid = threadIdx.x;
+    for (int it = blockIdx.x; it < count; it += gridDim.x) {
+        const int node = nodes[it];
+        __syncthreads();
+        for (int t = tid; t < g.D; t += kHnswThreads) m.qs[t] = g.db[(size_t)node * g.D + t];
+        __syncthreads();
+        unsigned evals = 0, expansions = 0;
+        int cur = entry_row;
+        for (int l = max_level; l > level; --l) cur = greedy_level(g, m, cur, l, &evals);
+        // `cur` may not be linked on this level yet (it is the node itself when the node also lives
+        // on the level above): enter through its closest upper-level neighbour that is, else the seed
+        int deg;
+        const int32_t* mine = nbr_list(g, cur, level, &deg);
+        if (cur == node || __ldcg(mine) < 0) {
+            int pick = seed_entry;
+            if (level < max_level) {
+                int dup;
+                const int32_t* up = nbr_list(g, cur, level + 1, &dup);
+                for (int p = 0; p < dup; ++p) {
+                    const int r = __ldcg(up + p);
+                    if (r < 0) break;
+                    int d2;
+                    if (r != node && __ldcg(nbr_list(g, r, level, &d2)) >= 0) { pick = r; break; }
+                }
+            }
+            cur = pick;
+        }
+        int wf = 0;
+        const int nf = beam_search(g, m, cur, level, efc, nullptr, &wf, &evals, &expansions);
+        if (m.scal[1] && tid == 0) atomicExch(overflow_flag, 1);
+        const u64* found = m.found[wf];
+        // the node itself can be reached (it is linked on the upper levels): skip it
+        if (tid == 0) {
+            int w = 0;
+            for (int i = 0; i < nf && w < M; ++i) {
+                const int r = (int)key_index(found[i]);
+                if (r == node) continue;
+                out_rows[(size_t)it * M + w] = r;
+                out_d[(size_t)it * M + w] = key_score(found[i]);
+                ++w;
+            }
+            for (; w < M; ++w) { out_rows[(size_t)it * M + w] = -1; out_d[(size_t)it * M + w] = INFINITY; }
+        }
+    }
+}
+
+// Reverse links of one wave.  Segment t = all new (source, dist) pairs whose target list is
+// list_idx[t], sorted by distance; one warp merges them with the list's current entries (kept with
+// their distances in adjd) and writes back the closest `deg`.
+constexpr int kMergeMax = 256;      // keys a warp sorts: deg (<= 128) existing + at most 128 incoming
+__global__ void __launch_bounds__(128)
+hnsw_reverse_merge_kernel(int32_t* __restrict__ adj, float* __restrict__ adjd, int deg, const int32_t* __restrict__ list_idx,
+                          const int32_t* __restrict__ seg_start, int segments, const int32_t* __restrict__ in_rows,
+                          const float* __restrict__ in_d) {
+    __shared__ u64 keys_s[4][kMergeMax];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int t = blockIdx.x * 4 + warp;
+    if (t >= segments) return;
+    u64* keys = keys_s[warp];
+    const size_t base = (size_t)list_idx[t] * deg;
+    const int s0 = seg_start[t], s1 = seg_start[t + 1];
+    const int n_in = min(s1 - s0, kMergeMax - deg);
+    for (int i = lane; i < kMergeMax; i += 32) {
+        u64 key = VDB_KEY_MAX;
+        if (i < deg) {
+            const int r = adj[base + i];
+            if (r >= 0) key = pack_key(adjd[base + i], (uint32_t)r);
+        } else if (i - deg < n_in) {
+            key = pack_key(in_d[s0 + i - deg], (uint32_t)in_rows[s0 + i - deg]);
+        }
+        keys[i] = key;
+    }
+    __syncwarp();
+    for (int k = 2; k <= kMergeMax; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int i = lane; i < kMergeMax; i += 32) {
+                const int p = i ^ j;
+                if (p > i) {
+                    const u64 a = keys[i], b = keys[p];
+                    const bool up = ((i & k) == 0);
+                    if ((a > b) == up) { keys[i] = b; keys[p] = a; }
+                }
+            }
+            __syncwarp();
+        }
+    }
+    for (int i = lane; i < deg; i += 32) {
+        const u64 key = keys[i];
+        // duplicates (same row twice) cannot occur: a wave node is new to every list it is merged into
+        adj[base + i] = key == VDB_KEY_MAX ? -1 : (int32_t)key_index(key);
+        adjd[base + i] = key == VDB_KEY_MAX ? INFINITY : key_score(key);
+    }
+}
+
 static int pick_hash_slots(int ef, int deg) {
     long long want = ((long long)(ef + 32) * deg * 5) / 4;
     int h = 1024;
@@ -518,6 +630,66 @@ int vdb_hnsw_search(const float* q, int Q, const float* db, int64_t N, int D, co
     ProfScope prof(kProfHnswSearch, st);
     hnsw_search_kernel<<<grid, kHnswThreads, smem, st>>>(g, q, Q, entry_row, max_level, ef, k, filter, CC, NM, H, ghash,
                                                          out_d, out_rows, out_stats, flag);
+    count_launch(1);
+    VDB_CUDA(cudaGetLastError());
+    return VDB_OK;
+}
+
+size_t vdb_hnsw_build_search_workspace(int count, int efc, int deg0) {
+    (void)count;
+    return 256 + (size_t)sm_count() * 8 * (size_t)pick_hash_slots(efc, deg0) * 4;
+}
+
+int vdb_hnsw_build_search(const float* db, int64_t N, int D, const int32_t* adj0, int deg0, const int32_t* adj_up,
+                          int deg_up, const int32_t* up_ptr, const int32_t* nodes, int count, int level,
+                          int32_t entry_row, int max_level, int32_t seed_entry, int efc, int M, int32_t* out_rows,
+                          float* out_d, void* ws, size_t ws_bytes, void* stream) {
+    VDB_REQUIRE(D > 0 && M > 0 && efc >= M && count >= 0 && level >= 0 && level <= max_level, VDB_ERR_INVALID,
+                "vdb_hnsw_build_search: bad arguments");
+    VDB_REQUIRE(efc <= 1024 && deg0 <= 128 && deg_up <= 128, VDB_ERR_UNSUPPORTED, "efc > 1024 or degree > 128");
+    VDB_REQUIRE(N < (1ll << 31), VDB_ERR_UNSUPPORTED, "N too large for int32 rows");
+    if (count == 0) return VDB_OK;
+    VDB_REQUIRE(db && adj0 && adj_up && up_ptr && nodes && out_rows && out_d && ws && ws_bytes >= 256, VDB_ERR_INVALID,
+                "vdb_hnsw_build_search: null pointer");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    Graph g{db, N, D, adj0, deg0, adj_up, deg_up, up_ptr, nullptr};
+    const int NM = (deg0 > deg_up ? deg0 : deg_up) + 1;
+    const int CC = efc;
+    const int H = pick_hash_slots(efc, level == 0 ? deg0 : deg_up);
+    size_t smem_with = beam_smem_bytes(D, CC, efc, NM, H);
+    size_t smem_without = beam_smem_bytes(D, CC, efc, NM, 0);
+    const bool use_global = smem_with > (size_t)110 * 1024;
+    size_t smem = use_global ? smem_without : smem_with;
+    VDB_REQUIRE(smem <= (size_t)max_smem_optin() - 1024, VDB_ERR_UNSUPPORTED, "D=%d efc=%d exceed shared memory", D, efc);
+    VDB_CUDA(cudaFuncSetAttribute(hnsw_build_search_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 1;
+    VDB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, hnsw_build_search_kernel, kHnswThreads, smem));
+    if (per_sm < 1) per_sm = 1;
+    if (per_sm > 8) per_sm = 8;
+    int grid = sm_count() * per_sm;
+    if (grid > count) grid = count;
+    int* flag = static_cast<int*>(ws);
+    uint32_t* ghash = nullptr;
+    if (use_global) {
+        VDB_REQUIRE(ws_bytes >= 256 + (size_t)grid * H * 4, VDB_ERR_WORKSPACE, "workspace too small");
+        ghash = reinterpret_cast<uint32_t*>(static_cast<char*>(ws) + 256);
+    }
+    VDB_CUDA(cudaMemsetAsync(flag, 0, 4, st));
+    ProfScope prof(kProfHnswInsert, st);
+    hnsw_build_search_kernel<<<grid, kHnswThreads, smem, st>>>(g, nodes, count, level, entry_row, max_level, seed_entry, efc,
+                                                              M, CC, NM, H, ghash, out_rows, out_d, flag);
+    count_launch(1);
+    VDB_CUDA(cudaGetLastError());
+    return VDB_OK;
+}
+
+int vdb_hnsw_reverse_merge(int32_t* adj, float* adjd, int deg, const int32_t* list_idx, const int32_t* seg_start,
+                           int segments, const int32_t* in_rows, const float* in_d, void* stream) {
+    VDB_REQUIRE(deg > 0 && deg <= 128 && segments >= 0, VDB_ERR_INVALID, "vdb_hnsw_reverse_merge: bad arguments");
+    if (segments == 0) return VDB_OK;
+    VDB_REQUIRE(adj && adjd && list_idx && seg_start && in_rows && in_d, VDB_ERR_INVALID, "vdb_hnsw_reverse_merge: null pointer");
+    hnsw_reverse_merge_kernel<<<(segments + 3) / 4, 128, 0, static_cast<cudaStream_t>(stream)>>>(
+        adj, adjd, deg, list_idx, seg_start, segments, in_rows, in_d);
     count_launch(1);
     VDB_CUDA(cudaGetLastError());
     return VDB_OK;

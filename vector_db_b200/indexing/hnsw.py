@@ -228,6 +228,118 @@ class HNSW:
             if self.index_file:
                 self.save_index()                               # hnsw.py:224-225
 
+    # ------------------------------------------------------------------ wave-parallel build
+    def build_from_arrays(self, ids: Sequence[int], vectors: np.ndarray, wave_max: int = 16384, seed: int = 1024,
+                          save_to_storage: bool = False) -> dict:
+        """Build the whole index from scratch with the wave-parallel GPU builder (``vdb_hnsw_build_search`` +
+        ``vdb_hnsw_reverse_merge``): levels are drawn with the reference's ``sample_level`` (hnsw.py:66-68) and
+        built top-down; on each level a brute-force kNN seed of ``seed`` nodes is grown in waves whose members
+        all search the graph built so far with ``ef_construction`` and link to their M closest.  This is what
+        makes the 1M-row configurations buildable (the sequential-semantics ``build_index`` stays the parity
+        builder); the graph is NOT the reference's graph.  Returns build statistics."""
+        with self._lock:
+            if self._graph_ids:
+                raise ValueError("build_from_arrays builds from scratch: the index already holds nodes")
+            X = np.ascontiguousarray(vectors, dtype=np.float32)
+            ids = [int(i) for i in ids]
+            n, dim = X.shape
+            if len(set(ids)) != n:
+                raise ValueError("ids must be unique and match the rows of `vectors`")
+            if save_to_storage:
+                for i, nid in enumerate(ids):
+                    self.storage.save(Node(id=nid, embedding=X[i]))
+            dev = self._device
+            self._reset_graph(dim=None)
+            self._vectors = DeviceVectors(dim, dev, capacity=n)
+            self._vectors.append(ids, X)
+            levels = np.fromiter((self.sample_level() for _ in range(n)), dtype=np.int64, count=n)
+            top = int(levels.max())
+            up_ptr = np.zeros(n + 1, dtype=np.int64)
+            up_ptr[1:] = np.cumsum(levels)
+            self._levels = levels.tolist()
+            self._up_ptr = up_ptr.tolist()
+            self._link_top = self._levels[:]
+            self._graph_ids = {nid: r for r, nid in enumerate(ids)}
+            self._ensure_capacity(n, int(up_ptr[-1]))
+            self._levels_dev[:n].copy_(torch.from_numpy(levels.astype(np.int32)))
+            self._up_ptr_dev[:n + 1].copy_(torch.from_numpy(up_ptr.astype(np.int32)))
+            adjd0 = torch.full(self._adj0.shape, float("inf"), dtype=torch.float32, device=dev)
+            adjd_up = torch.full(self._adj_up.shape, float("inf"), dtype=torch.float32, device=dev)
+            entry_row = int(np.flatnonzero(levels == top)[0])        # first node that reached the top level
+            lib = _lib.load()
+            vec = self._vectors
+            M = self.M
+            up_ptr_dev = self._up_ptr_dev
+            waves = 0
+            for level in range(top, -1, -1):
+                rows = np.flatnonzero(levels >= level)
+                rows = rows[np.lexsort((rows, -levels[rows]))]       # upper-level nodes first, then by row
+                rows_t = torch.from_numpy(rows.astype(np.int32)).to(dev)
+                adj, adjd = (self._adj0, adjd0) if level == 0 else (self._adj_up, adjd_up)
+                deg = adj.shape[1]
+
+                def lists_of(r: torch.Tensor) -> torch.Tensor:
+                    r = r.long()
+                    return r if level == 0 else (up_ptr_dev[r].long() + (level - 1))
+
+                n0 = min(len(rows), max(seed, 2))
+                if n0 >= 2:                                          # brute-force kNN seed
+                    s_rows = rows_t[:n0].long()
+                    Xs = vec.vecs[s_rows].contiguous()
+                    kk = min(M + 1, n0)
+                    d, i = ops.exact_topk_f32(Xs, Xs, kk, "l2")
+                    keep = i != torch.arange(n0, device=dev).unsqueeze(1)
+                    order = torch.argsort((~keep).to(torch.int8), dim=1, stable=True)[:, :kk - 1]
+                    nb = s_rows[torch.gather(i, 1, order)].to(torch.int32)
+                    nd = torch.gather(d, 1, order)
+                    li = lists_of(s_rows)
+                    adj[li, :kk - 1] = nb
+                    adjd[li, :kk - 1] = nd
+                pos = n0
+                out_rows = torch.empty((wave_max, M), dtype=torch.int32, device=dev)
+                out_d = torch.empty((wave_max, M), dtype=torch.float32, device=dev)
+                nbytes = lib.vdb_hnsw_build_search_workspace(wave_max, self.ef_construction, self.M_max0)
+                ws = ops._ws("hnsw_build", nbytes, dev)
+                while pos < len(rows):
+                    b = int(min(max(pos // 4, 256), wave_max, len(rows) - pos))
+                    wave = rows_t[pos:pos + b].contiguous()
+                    _lib.check(lib.vdb_hnsw_build_search(
+                        vec.vecs.data_ptr(), vec.n, vec.dim, self._adj0.data_ptr(), self.M_max0, self._adj_up.data_ptr(),
+                        self.M_max, up_ptr_dev.data_ptr(), wave.data_ptr(), b, level, entry_row, top, int(rows[0]),
+                        self.ef_construction, M, out_rows.data_ptr(), out_d.data_ptr(), ws.data_ptr(), ws.numel(),
+                        _lib.stream_ptr(dev)))
+                    fr, fd = out_rows[:b], out_d[:b]
+                    li = lists_of(wave)
+                    adj[li, :M] = fr
+                    adjd[li, :M] = fd
+                    valid = fr >= 0
+                    tgt = fr[valid].long()
+                    src = wave.unsqueeze(1).expand(b, M)[valid]
+                    dd = fd[valid]
+                    key = (tgt << 32) | dd.view(torch.int32).long()   # distances are >= 0: their bits sort like the values
+                    key, perm = torch.sort(key)
+                    tgt_sorted = key >> 32
+                    uniq, counts = torch.unique_consecutive(tgt_sorted, return_counts=True)
+                    seg_start = torch.zeros(uniq.numel() + 1, dtype=torch.int32, device=dev)
+                    seg_start[1:] = torch.cumsum(counts, 0).to(torch.int32)
+                    seg_lists = lists_of(uniq).to(torch.int32)
+                    in_rows = src[perm].contiguous()
+                    in_d = dd[perm].contiguous()
+                    _lib.check(lib.vdb_hnsw_reverse_merge(adj.data_ptr(), adjd.data_ptr(), deg, seg_lists.data_ptr(),
+                                                          seg_start.data_ptr(), int(uniq.numel()), in_rows.data_ptr(),
+                                                          in_d.data_ptr(), _lib.stream_ptr(dev)))
+                    pos += b
+                    waves += 1
+                if int(ws[:4].view(torch.int32).item()) != 0:
+                    raise _lib.VdbError("hnsw build: visited table overflow (ef_construction * degree too large)")
+            st = (entry_row, top)
+            self._state[:2].copy_(torch.tensor(st, dtype=torch.int32))
+            self._state_host = st
+            self._snapshot = None
+            if self.index_file:
+                self.save_index()
+            return {"nodes": n, "top_level": top, "waves": waves, "entry_row": entry_row}
+
     # ------------------------------------------------------------------ delete
     def delete_node(self, node_id: int) -> None:
         """hnsw.py:227-277: unlink the node from the lists of ITS OWN neighbours, drop it, fix the
