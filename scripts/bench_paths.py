@@ -109,7 +109,27 @@ def bench_hnsw(N=200_000, D=768, M=32, ef=128, Q=10_000):
     ex.add_device(torch.arange(N, device=dev), torch.from_numpy(X).to(dev))
     _, Iex = ex.search(Qh[:512], 10)
     recall = float(np.mean([len(set(i[j]) & set(Iex[j])) / 10 for j in range(512)]))
+    # the reference's own search (oracle restatement of hnsw.py:330-374, pinned to the reference by the golden
+    # fixtures) on the SAME graph, for a sample: recall parity gate (within 0.5 pt) and the CPU baseline
+    from oracle.hnsw_oracle import search_arrays
+    adj0, adj_up, up_ptr, _, _ = idx._host_graph()
+    entry_row, top = idx._read_state()
+    n_or = int(os.environ.get("VDB_HNSW_ORACLE_QUERIES", 64))
+    t0 = time.perf_counter()
+    same, rec_or, rec_gpu, ev_same = 0, 0.0, 0.0, 0
+    for j in range(n_or):
+        res, ev = search_arrays(X, adj0, up_ptr, adj_up, entry_row, top, Qh[j], 10, ef)
+        ids_or = [r for _, r in res]
+        same += int(ids_or == i[j].tolist())
+        ev_same += int(ev == int(st[j, 0]))
+        rec_or += len(set(ids_or) & set(Iex[j])) / 10
+        rec_gpu += len(set(i[j]) & set(Iex[j])) / 10
+    or_s = time.perf_counter() - t0
+    oracle = {"queries": n_or, "identical_result_lists": same, "identical_eval_counts": ev_same,
+              "recall_reference_search": rec_or / max(n_or, 1), "recall_gpu_search": rec_gpu / max(n_or, 1),
+              "reference_search_qps_1core": n_or / or_s if n_or else None}
     line = {"path": "hnsw_search", "N": N, "D": D, "M": M, "ef": ef, "Q": Q, "builder": builder, "build_stats": stats,
+            "vs_reference_search_same_graph": oracle,
             "build_s": build_s,
             "inserts_per_s": N / build_s, "kernel_ms": k_ms, "step_ms": step_ms, "qps": Q / (step_ms * 1e-3),
             "evals_per_query": evals, "expansions_per_query": expans, "recall_at_10_vs_exact": recall,
