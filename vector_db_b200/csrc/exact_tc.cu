@@ -39,16 +39,23 @@ constexpr int kNBLMax = 16;              // bins kept per (query, slice, epilogu
 constexpr int kNBFinal = 32;             // bins reranked per query
 constexpr int kGroups = 2;               // epilogue groups == accumulator stages
 
+constexpr int kA2Bytes = kTileM * 32;            // 4 KB: the L2 norm block of the query tile (16 bf16 per row)
+constexpr int kB2Bytes = kTileN * 32;            // 8 KB: the L2 norm block of one row tile
+
 struct TcSmemLayout {
-    int a_off, b_off, bar_off, total;
+    int a_off, a2_off, b2_off, b_off, bar_off, total;
 };
 
-__host__ __device__ inline TcSmemLayout tc_layout(int num_kb, int stages) {
+// has_norm: the L2 operands carry a 16-column norm block (|x|^2 split / ones) after the D data columns;
+// it travels in its own narrow 32-byte-swizzled tiles (4 KB + 2 x 8 KB) instead of a seventh 32 KB stage.
+__host__ __device__ inline TcSmemLayout tc_layout(int num_kb, int stages, int has_norm) {
     TcSmemLayout L;
     L.a_off = 0;
-    L.b_off = L.a_off + num_kb * kABytes;
+    L.a2_off = L.a_off + num_kb * kABytes;
+    L.b2_off = L.a2_off + (has_norm ? kA2Bytes : 0);
+    L.b_off = L.b2_off + (has_norm ? 2 * kB2Bytes : 0);
     L.bar_off = L.b_off + stages * kBBytes;
-    L.total = L.bar_off + (2 * kMaxStages + 8) * 8 + 16;
+    L.total = L.bar_off + (2 * kMaxStages + 12) * 8 + 16;
     return L;
 }
 
@@ -98,12 +105,15 @@ __device__ __forceinline__ void chunk_minima(float (&v)[32], int n_valid, float 
 template <int NBL>
 __global__ void __launch_bounds__(kTcThreads, 1)
 exact_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-                int Q, int64_t N, int Dp, int num_kb, int stages, int m_tiles, int S,
+                const __grid_constant__ CUtensorMap map_a2, const __grid_constant__ CUtensorMap map_b2,
+                int Q, int64_t N, int D, int has_norm, int num_kb, int stages, int m_tiles, int S,
                 int tiles_per_slice, int tiles_total, int flags, u64* __restrict__ partial) {
     extern __shared__ __align__(1024) unsigned char smem[];   // 128B-swizzled operand tiles need 1024 B alignment
     if ((smem_u32(smem) & 1023u) != 0) __trap();
-    const TcSmemLayout L = tc_layout(num_kb, stages);
+    const TcSmemLayout L = tc_layout(num_kb, stages, has_norm);
     unsigned char* sA = smem + L.a_off;
+    unsigned char* sA2 = smem + L.a2_off;
+    unsigned char* sB2 = smem + L.b2_off;
     unsigned char* sB = smem + L.b_off;
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L.bar_off);
     uint64_t* full = bars;                         // [stages]
@@ -112,22 +122,26 @@ exact_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     uint64_t* tmem_empty = tmem_full + 2;          // [2]
     uint64_t* a_full = tmem_empty + 2;
     uint64_t* a_empty = a_full + 1;
-    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(a_empty + 1);
+    uint64_t* n_full = a_empty + 1;                // [2] norm-block ring
+    uint64_t* n_empty = n_full + 2;                // [2]
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(n_empty + 2);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int units = m_tiles * S;
-    // UMMAs in the last k-block: columns past Dp are zero-filled by TMA, skip the all-zero K steps
-    const int last_steps = (Dp - (num_kb - 1) * kBlockK + kUmmaK - 1) / kUmmaK;
+    // UMMAs in the last k-block: columns past D are zero-filled by TMA, skip the all-zero K steps
+    const int last_steps = (D - (num_kb - 1) * kBlockK + kUmmaK - 1) / kUmmaK;
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&map_a);
         tma_prefetch_desc(&map_b);
+        if (has_norm) { tma_prefetch_desc(&map_a2); tma_prefetch_desc(&map_b2); }
     }
     if (warp == 1 && lane == 0) {
         for (int i = 0; i < stages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
         for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 256); }
         mbar_init(a_full, 1);
         mbar_init(a_empty, 1);
+        for (int i = 0; i < 2; ++i) { mbar_init(&n_full[i], 1); mbar_init(&n_empty[i], 1); }
         fence_barrier_init();
     }
     if (warp == 2) tmem_alloc(tmem_ptr, 512);
@@ -139,16 +153,24 @@ exact_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     if (warp == 0) {
         // ================= TMA producer (one lane) =================
         if (lane == 0) {
-            int st = 0, ph = 0, ui = 0;
+            int st = 0, ph = 0, ui = 0, ns = 0, nph = 0;
             for (int u = blockIdx.x; u < units; u += gridDim.x, ++ui) {
                 const int mt = u % m_tiles, s = u / m_tiles;
                 const int t0 = s * tiles_per_slice;
                 const int t1 = min(tiles_total, t0 + tiles_per_slice);
                 mbar_wait(a_empty, (ui & 1) ^ 1);                 // previous unit's MMAs are done with A
-                mbar_expect_tx(a_full, (uint32_t)(num_kb * kABytes));
+                mbar_expect_tx(a_full, (uint32_t)(num_kb * kABytes + (has_norm ? kA2Bytes : 0)));
                 for (int kb = 0; kb < num_kb; ++kb)
                     tma_load_2d(sA + kb * kABytes, &map_a, a_full, kb * kBlockK, mt * kTileM, kEvictLast);
+                if (has_norm) tma_load_2d(sA2, &map_a2, a_full, D, mt * kTileM, kEvictLast);
                 for (int t = t0; t < t1; ++t) {
+                    if (has_norm) {
+                        mbar_wait(&n_empty[ns], nph ^ 1);
+                        mbar_expect_tx(&n_full[ns], (uint32_t)kB2Bytes);
+                        tma_load_2d(sB2 + ns * kB2Bytes, &map_b2, &n_full[ns], D, t * kTileN, kEvictNormal);
+                        ns ^= 1;
+                        if (ns == 0) nph ^= 1;
+                    }
                     for (int kb = 0; kb < num_kb; ++kb) {
                         mbar_wait(&empty[st], ph ^ 1);
                         mbar_expect_tx(&full[st], (uint32_t)kBBytes);
@@ -162,7 +184,7 @@ exact_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
         // ================= MMA issuer (one lane) =================
         if (lane == 0) {
             const uint32_t idesc = make_idesc_bf16(kTileM, kTileN);
-            int st = 0, ph = 0, as = 0, aph = 0, ui = 0;
+            int st = 0, ph = 0, as = 0, aph = 0, ui = 0, ns = 0, nph = 0;
             for (int u = blockIdx.x; u < units; u += gridDim.x, ++ui) {
                 const int s = u / m_tiles;
                 const int t0 = s * tiles_per_slice;
@@ -173,6 +195,14 @@ exact_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                     mbar_wait(&tmem_empty[as], aph ^ 1);          // epilogue group `as` drained this accumulator
                     tc_fence_after();
                     const uint32_t d_tmem = tmem_base + (uint32_t)(as * kTileN);
+                    if (has_norm) {                               // |x|^2 first: D = ones . split(|x|^2)
+                        mbar_wait(&n_full[ns], nph);
+                        tc_fence_after();
+                        umma_bf16(d_tmem, make_desc_k_sw32(smem_u32(sA2)), make_desc_k_sw32(smem_u32(sB2 + ns * kB2Bytes)), idesc, 0u);
+                        umma_commit(&n_empty[ns]);
+                        ns ^= 1;
+                        if (ns == 0) nph ^= 1;
+                    }
                     for (int kb = 0; kb < num_kb; ++kb) {
                         mbar_wait(&full[st], ph);
                         tc_fence_after();
@@ -180,7 +210,7 @@ exact_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                         const uint64_t db = make_desc_k_sw128(smem_u32(sB + st * kBBytes));
                         const int steps = (kb == num_kb - 1) ? last_steps : kBlockK / kUmmaK;
                         for (int k = 0; k < steps; ++k)
-                            umma_bf16(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((kb | k) != 0));
+                            umma_bf16(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((has_norm | kb | k) != 0));
                         umma_commit(&empty[st]);                   // smem stage reusable once these MMAs retire
                         if (++st == stages) { st = 0; ph ^= 1; }
                     }
@@ -404,23 +434,24 @@ static EncodeTiledFn encode_tiled_fn() {
     return fn;
 }
 
-// bf16 row-major [rows][D] matrix, box = 64 (K) x box_rows, 128-byte swizzle, zero fill out of bounds
-static int make_map(CUtensorMap* map, const void* base, int64_t rows, int D, int box_rows) {
+// bf16 row-major matrix with `cols` visible columns out of rows of `row_elems` elements; box = box_cols x
+// box_rows with the matching swizzle (64 columns -> 128 B, 16 columns -> 32 B); zero fill out of bounds
+static int make_map(CUtensorMap* map, const void* base, int64_t rows, int cols, int row_elems, int box_cols, int box_rows) {
     EncodeTiledFn fn = encode_tiled_fn();
     VDB_REQUIRE(fn != nullptr, VDB_ERR_CUDA, "cuTensorMapEncodeTiled is not available from the driver");
-    cuuint64_t dims[2] = {(cuuint64_t)D, (cuuint64_t)rows};
-    cuuint64_t strides[1] = {(cuuint64_t)D * 2};
-    cuuint32_t box[2] = {(cuuint32_t)kBlockK, (cuuint32_t)box_rows};
+    cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)row_elems * 2};
+    cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
     cuuint32_t estr[2] = {1, 1};
     CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
-                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, box_cols == 16 ? CU_TENSOR_MAP_SWIZZLE_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     VDB_REQUIRE(r == CUDA_SUCCESS, VDB_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
     return VDB_OK;
 }
 
 struct TcPlan {
-    int Dp, num_kb, stages, m_tiles, S, tiles_per_slice, tiles_total, grid;
+    int Dp, has_norm, num_kb, stages, m_tiles, S, tiles_per_slice, tiles_total, grid;
     size_t smem;
 };
 
@@ -432,15 +463,16 @@ static bool plan_tc(int Q, int64_t N, int D, int k, int metric, TcPlan* p) {
     if (D % 8 != 0 || D <= 0 || Q <= 0 || N <= 0) return false;
     if (k > 16) return false;                       // kNBFinal bins of kBin rows must hold k results with margin
     p->Dp = tc_row_elems(D, metric);
-    p->num_kb = (p->Dp + kBlockK - 1) / kBlockK;
+    p->has_norm = metric == VDB_METRIC_L2 ? 1 : 0;
+    p->num_kb = (D + kBlockK - 1) / kBlockK;
     const int smem_max = max_smem_optin();
     int stages = kMaxStages;
     if ((g_tc_flags >> 8) & 0xF) stages = (g_tc_flags >> 8) & 0xF;       // debug: cap the TMA ring depth
     // + 1024: the 1024-byte aligned extern array makes the compiler reserve 1 KB of static shared memory
-    while (stages >= 2 && tc_layout(p->num_kb, stages).total + 1024 > smem_max) --stages;
+    while (stages >= 2 && tc_layout(p->num_kb, stages, p->has_norm).total + 1024 > smem_max) --stages;
     if (stages < 2) return false;
     p->stages = stages;
-    p->smem = (size_t)tc_layout(p->num_kb, stages).total;
+    p->smem = (size_t)tc_layout(p->num_kb, stages, p->has_norm).total;
     p->m_tiles = (Q + kTileM - 1) / kTileM;
     int64_t tiles_total = (N + kTileN - 1) / kTileN;
     if (tiles_total > (1 << 24)) return false;
@@ -548,19 +580,25 @@ int vdb_exact_topk_tc(const float* q, int Q, const float* db, const void* mirror
     const int nbl = ((g_tc_flags & 4) || p.S * kGroups * 8 < 4 * kNBFinal) ? 16 : 8;
     tc_query_operand_kernel<<<sm_count() * 2, 256, 0, st>>>(q, qb, Q, D, p.Dp, metric);
     CUtensorMap map_a, map_b;
-    int rc = make_map(&map_a, qb, Q, p.Dp, kTileM);
+    CUtensorMap map_a2, map_b2;
+    int rc = make_map(&map_a, qb, Q, D, p.Dp, kBlockK, kTileM);
     if (rc) return rc;
-    rc = make_map(&map_b, mirror, N, p.Dp, kTileN);
+    rc = make_map(&map_b, mirror, N, D, p.Dp, kBlockK, kTileN);
+    if (rc) return rc;
+    // norm block (L2 only; cosine passes valid but unused maps): columns D..D+15 of the same operands
+    rc = make_map(&map_a2, qb, Q, p.Dp, p.Dp, 16, kTileM);
+    if (rc) return rc;
+    rc = make_map(&map_b2, mirror, N, p.Dp, p.Dp, 16, kTileN);
     if (rc) return rc;
     {
         ProfScope prof(kProfExactTC, st);
         if (nbl == 16) {
             VDB_CUDA(cudaFuncSetAttribute(exact_tc_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem));
-            exact_tc_kernel<16><<<p.grid, kTcThreads, p.smem, st>>>(map_a, map_b, Q, N, p.Dp, p.num_kb, p.stages, p.m_tiles, p.S,
+            exact_tc_kernel<16><<<p.grid, kTcThreads, p.smem, st>>>(map_a, map_b, map_a2, map_b2, Q, N, D, p.has_norm, p.num_kb, p.stages, p.m_tiles, p.S,
                                                                    p.tiles_per_slice, p.tiles_total, g_tc_flags, partial);
         } else {
             VDB_CUDA(cudaFuncSetAttribute(exact_tc_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem));
-            exact_tc_kernel<8><<<p.grid, kTcThreads, p.smem, st>>>(map_a, map_b, Q, N, p.Dp, p.num_kb, p.stages, p.m_tiles, p.S,
+            exact_tc_kernel<8><<<p.grid, kTcThreads, p.smem, st>>>(map_a, map_b, map_a2, map_b2, Q, N, D, p.has_norm, p.num_kb, p.stages, p.m_tiles, p.S,
                                                                   p.tiles_per_slice, p.tiles_total, g_tc_flags, partial);
         }
     }
