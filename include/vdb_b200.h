@@ -173,6 +173,9 @@ int vdb_hnsw_search(const float* q, int Q, const float* db, int64_t N, int D,
                     float* out_d /*[dev] Q*k*/, int32_t* out_rows /*[dev] Q*k*/, uint32_t* out_stats,
                     void* ws, size_t ws_bytes, void* stream);
 
+/* bench/debug only: CTA shared-memory footprint above which the visited hash moves to global memory */
+void vdb_debug_set_hnsw_smem_hash_limit(int bytes);
+
 /* ---- a7 HNSW construction ----------------------------------------------------------------------
  * Sequential-semantics insert of rows first..first+count-1 (their vectors already in `db`, their
  * levels drawn by the host from random.Random, hnsw.py:66-68,160) by ONE CTA, reproducing

@@ -99,6 +99,12 @@ def bench_hnsw(N=200_000, D=768, M=32, ef=128, Q=10_000):
         stats = {}
     torch.cuda.synchronize()
     build_s = time.perf_counter() - t0
+    variants = {}
+    for lim in [int(v) for v in os.environ.get("VDB_HNSW_HASH_LIMITS", "").split(",") if v]:
+        _lib.load().vdb_debug_set_hnsw_smem_hash_limit(lim)
+        _, vk, _ = _time_slot("hnsw_search", lambda: idx.search_batch(Qh, 10, ef=ef, return_stats=True), iters=3, warm=1)
+        variants[f"smem_hash_limit_{lim}"] = vk
+    _lib.load().vdb_debug_set_hnsw_smem_hash_limit(48 * 1024)
     (d, i, st), k_ms, step_ms = _time_slot(
         "hnsw_search", lambda: idx.search_batch(Qh, 10, ef=ef, return_stats=True), iters=3, warm=1)
     evals, expans = float(st[:, 0].mean()), float(st[:, 1].mean())
@@ -130,7 +136,7 @@ def bench_hnsw(N=200_000, D=768, M=32, ef=128, Q=10_000):
               "reference_search_qps_1core": n_or / or_s if n_or else None}
     line = {"path": "hnsw_search", "N": N, "D": D, "M": M, "ef": ef, "Q": Q, "builder": builder, "build_stats": stats,
             "vs_reference_search_same_graph": oracle,
-            "build_s": build_s,
+            "build_s": build_s, "kernel_ms_variants": variants,
             "inserts_per_s": N / build_s, "kernel_ms": k_ms, "step_ms": step_ms, "qps": Q / (step_ms * 1e-3),
             "evals_per_query": evals, "expansions_per_query": expans, "recall_at_10_vs_exact": recall,
             "roofline": {"bound": "hbm", "achieved": alg_bytes / (k_ms * 1e-3) / 1e9, "peak": HBM, "unit": "GB/s",

@@ -72,6 +72,36 @@ __device__ __forceinline__ float warp_l2(const float* __restrict__ qs, const flo
     return sqrtf(warp_sum(acc));
 }
 
+// two rows at once: both rows' loads are issued before either reduction, doubling the bytes in flight
+// per warp (the traversal is latency bound: ncu shows the FADDs of this loop waiting on the gathers)
+__device__ __forceinline__ void warp_l2_x2(const float* __restrict__ qs, const float* __restrict__ row_a,
+                                           const float* __restrict__ row_b, int D, int lane, float* da, float* db) {
+    float acc_a = 0.f, acc_b = 0.f;
+    if ((D & 3) == 0) {
+        const float4* a4 = reinterpret_cast<const float4*>(row_a);
+        const float4* b4 = reinterpret_cast<const float4*>(row_b);
+        const float4* q4 = reinterpret_cast<const float4*>(qs);
+        for (int c = lane; c < (D >> 2); c += 32) {
+            const float4 xa = __ldg(a4 + c);
+            const float4 xb = __ldg(b4 + c);
+            const float4 qv = q4[c];
+            float d0 = qv.x - xa.x, d1 = qv.y - xa.y, d2 = qv.z - xa.z, d3 = qv.w - xa.w;
+            acc_a = fmaf(d0, d0, acc_a); acc_a = fmaf(d1, d1, acc_a); acc_a = fmaf(d2, d2, acc_a); acc_a = fmaf(d3, d3, acc_a);
+            d0 = qv.x - xb.x; d1 = qv.y - xb.y; d2 = qv.z - xb.z; d3 = qv.w - xb.w;
+            acc_b = fmaf(d0, d0, acc_b); acc_b = fmaf(d1, d1, acc_b); acc_b = fmaf(d2, d2, acc_b); acc_b = fmaf(d3, d3, acc_b);
+        }
+    } else {
+        for (int t = lane; t < D; t += 32) {
+            const float q = qs[t];
+            const float ea = q - __ldg(row_a + t), eb = q - __ldg(row_b + t);
+            acc_a = fmaf(ea, ea, acc_a);
+            acc_b = fmaf(eb, eb, acc_b);
+        }
+    }
+    *da = sqrtf(warp_sum(acc_a));
+    *db = sqrtf(warp_sum(acc_b));
+}
+
 __device__ __forceinline__ bool visited_insert(uint32_t* tab, int H, int logH, uint32_t key) {
     uint32_t h = (key * 2654435761u) >> (32 - logH);
     for (int probe = 0; probe < H; ++probe) {
@@ -195,10 +225,17 @@ __device__ int beam_search(const Graph& g, BeamMem& m, int entry, int level, int
         const int ntodo = m.scal[0];
         *evals += (unsigned)ntodo;
         nvisited += (unsigned)ntodo;
-        for (int i = warp; i < ntodo; i += kHnswWarps) {
+        for (int i = 2 * warp; i < ntodo; i += 2 * kHnswWarps) {
             const int r = m.todo[i];
-            float d = warp_l2(m.qs, g.db + (size_t)r * g.D, g.D, lane);
-            if (lane == 0) m.newk[i] = pack_key(d, (uint32_t)r);
+            if (i + 1 < ntodo) {
+                const int r2 = m.todo[i + 1];
+                float d, d2;
+                warp_l2_x2(m.qs, g.db + (size_t)r * g.D, g.db + (size_t)r2 * g.D, g.D, lane, &d, &d2);
+                if (lane == 0) { m.newk[i] = pack_key(d, (uint32_t)r); m.newk[i + 1] = pack_key(d2, (uint32_t)r2); }
+            } else {
+                float d = warp_l2(m.qs, g.db + (size_t)r * g.D, g.D, lane);
+                if (lane == 0) m.newk[i] = pack_key(d, (uint32_t)r);
+            }
         }
         __syncthreads();
         // rank sort of the new keys; ppass[i] = number of filter-passing keys before sorted slot i
@@ -570,6 +607,7 @@ hnsw_reverse_merge_kernel(int32_t* __restrict__ adj, float* __restrict__ adjd, i
     }
 }
 
+static int g_hnsw_smem_hash_limit = 48 * 1024;   // visited hash stays in shared memory only below this CTA footprint
 static int pick_hash_slots(int ef, int deg) {
     long long want = ((long long)(ef + 32) * deg * 5) / 4;
     int h = 1024;
@@ -582,6 +620,8 @@ static int pick_hash_slots(int ef, int deg) {
 using namespace vdb;
 
 extern "C" {
+
+void vdb_debug_set_hnsw_smem_hash_limit(int bytes) { g_hnsw_smem_hash_limit = bytes; }
 
 size_t vdb_hnsw_search_workspace(int Q, int ef, int deg0) {
     (void)Q;
@@ -609,7 +649,8 @@ int vdb_hnsw_search(const float* q, int Q, const float* db, int64_t N, int D, co
     int H = hash_slots ? hash_slots : pick_hash_slots(ef, deg0);
     size_t smem_with = beam_smem_bytes(D, CC, ef, NM, H);
     size_t smem_without = beam_smem_bytes(D, CC, ef, NM, 0);
-    const bool use_global = hash_slots != 0 || smem_with > (size_t)110 * 1024;
+    // a big shared-memory hash caps the CTAs per SM, and the traversal needs occupancy to hide gather latency
+    const bool use_global = hash_slots != 0 || smem_with > (size_t)g_hnsw_smem_hash_limit;
     size_t smem = use_global ? smem_without : smem_with;
     VDB_REQUIRE(smem <= (size_t)max_smem_optin() - 1024, VDB_ERR_UNSUPPORTED, "D=%d ef=%d exceed shared memory", D, ef);
     VDB_CUDA(cudaFuncSetAttribute(hnsw_search_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
