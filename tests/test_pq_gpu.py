@@ -79,6 +79,26 @@ def test_lut_and_adc_vs_oracle(n, m, dsub, q, R):
     np.testing.assert_array_equal(I.cpu().numpy(), Iref)
 
 
+@pytest.mark.parametrize("n,m,q,R,dup", [(60_000, 16, 5, 1500, False), (40_000, 48, 3, 600, False),
+                                          (40_000, 8, 6, 600, True), (70_000, 24, 2, 4000, False),
+                                          (70_000, 16, 4, 300, False), (40_000, 8, 6, 50, True), (40_000, 7, 3, 120, False)])
+def test_adc_large_shortlist_threshold_collect_vs_oracle(n, m, q, R, dup):
+    """N >= 16 x the collect target takes the threshold-collect path (sampled threshold -> collect -> exact merge, flagged
+    queries rescanned by the running-selection kernel).  dup=True makes half the rows identical, so for
+    some queries the collected set overflows its buffer and the device-side rescan list is exercised."""
+    from vector_db_b200 import ops
+    rng = np.random.default_rng(n + m + R)
+    codes = rng.integers(0, 256, (n, m)).astype(np.uint8)
+    if dup:
+        codes[rng.permutation(n)[: n // 2]] = codes[0]
+    lut = rng.random((q, m, 256), dtype=np.float32) * np.float32(3.0)
+    ids = np.sort(rng.choice(10 * n, n, replace=False)).astype(np.int64)      # increasing: ties break by row == by id
+    Dref, Iref = O.adc_scan_topk(codes, lut, R, ids=ids)
+    D, I = ops.pq_adc_topk(_t(codes), _t(lut), R, ids=_t(ids))
+    np.testing.assert_array_equal(I.cpu().numpy(), Iref)
+    np.testing.assert_array_equal(D.cpu().numpy(), Dref)
+
+
 def test_pq_index_end_to_end_recall_with_rerank(golden_dir):
     from vector_db_b200.inference.pq import PQIndex
     g = np.load(os.path.join(golden_dir, "pq8.npz"))

@@ -102,21 +102,26 @@ __device__ __forceinline__ float4 ld_stream_f4(const float4* p) {
 }
 
 // ------------------------------------------------------------------ CTA-wide bitonic sort (ascending), n = power of two
-__device__ __forceinline__ void block_bitonic_sort(u64* buf, int n) {
+// `lists` independent arrays of n keys each, stored back to back, are sorted by the same network in one
+// pass (one barrier per stage for all of them); every thread handles compare-exchange PAIRS, none idle.
+__device__ __forceinline__ void block_bitonic_sort_lists(u64* buf, int n, int lists) {
+    const int half = n >> 1;
+    const int pairs = half * lists;
     for (int k = 2; k <= n; k <<= 1) {
         for (int j = k >> 1; j > 0; j >>= 1) {
-            for (int i = threadIdx.x; i < n; i += blockDim.x) {
-                int p = i ^ j;
-                if (p > i) {
-                    u64 a = buf[i], b = buf[p];
-                    bool up = ((i & k) == 0);
-                    if ((a > b) == up) { buf[i] = b; buf[p] = a; }
-                }
+            for (int t = threadIdx.x; t < pairs; t += blockDim.x) {
+                const int l = t / half, tl = t - l * half;
+                const int i = ((tl & ~(j - 1)) << 1) | (tl & (j - 1));
+                u64* b = buf + (size_t)l * n;
+                const u64 x = b[i], y = b[i | j];
+                const bool up = ((i & k) == 0);
+                if ((x > y) == up) { b[i] = y; b[i | j] = x; }
             }
             __syncthreads();
         }
     }
 }
+__device__ __forceinline__ void block_bitonic_sort(u64* buf, int n) { block_bitonic_sort_lists(buf, n, 1); }
 
 // ------------------------------------------------------------------ BlockSelect
 // Streaming "keep the R smallest keys" over a shared-memory array of C = 2^c entries.

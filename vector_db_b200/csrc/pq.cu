@@ -216,26 +216,92 @@ adc_quantize_lut_kernel(const float* __restrict__ lut, int per_query, uint32_t* 
     }
 }
 
+struct AdcArgs {
+    const uint8_t* codes;
+    int64_t N;                  // logical rows scanned
+    int64_t row_stride;         // physical row = logical row * row_stride (> 1: strided sample for the threshold estimate)
+    int m;
+    const uint32_t* lutq;
+    int Q, R, C;
+    int64_t slice_rows;
+    int S, groups;
+    u64* partial;               // select mode: [query slot][S][R]
+    const int32_t* qsel;        // optional indirection: only queries qsel[0 .. *qcount) are processed,
+    const int32_t* qcount;      //   query slot b = position in qsel (device-side count: no host round trip)
+    const uint32_t* tau;        // collect mode: per-query fixed-point threshold
+    u64* cbuf;                  //   [Q][ccap] keys with d_int <= tau, unordered
+    int32_t* ccnt;              //   [Q] number of keys found (may exceed ccap: overflow, handled by the caller)
+    int ccap;
+};
+
+// d_int of one row for the G queries of the group: 128-bit code loads, rotated conflict-free lookups.
 // MB = m/8 when m is a multiple of 8 and small enough to unroll, 0 = generic (any m, byte loads).
 template <int G, int MB>
+__device__ __forceinline__ void adc_row(const uint8_t* __restrict__ prow, int m, int mb, const uint32_t* lutS, int rot,
+                                        uint32_t (&acc)[G]) {
+#pragma unroll
+    for (int g = 0; g < G; ++g) acc[g] = 0u;
+    if (MB > 0) {
+        uint32_t w[MB > 0 ? 2 * MB : 2];
+        if ((MB & 1) == 0) {
+            const uint4* p = reinterpret_cast<const uint4*>(prow);
+#pragma unroll
+            for (int i = 0; i < MB / 2; ++i) {
+                const uint4 v = ld_stream_u4(p + i);
+                w[4 * i] = v.x; w[4 * i + 1] = v.y; w[4 * i + 2] = v.z; w[4 * i + 3] = v.w;
+            }
+        } else {
+            const uint2* p = reinterpret_cast<const uint2*>(prow);
+#pragma unroll
+            for (int i = 0; i < MB; ++i) { const uint2 v = __ldg(p + i); w[2 * i] = v.x; w[2 * i + 1] = v.y; }
+        }
+#pragma unroll
+        for (int b = 0; b < MB; ++b) {
+            uint32_t lo = w[2 * b], hi = w[2 * b + 1];
+            rotr_bytes(lo, hi, rot);                         // byte t of (lo,hi) is now sub-space (t + rot) & 7
+#pragma unroll
+            for (int t = 0; t < 8; ++t) {
+                const uint32_t c = ((t < 4 ? lo : hi) >> (8 * (t & 3))) & 0xFFu;
+                lut_add<G>(acc, lutS, (uint32_t)(b * 2048) + c * 8u + (uint32_t)((t + rot) & 7));
+            }
+        }
+    } else {
+        for (int b = 0; b < mb; ++b) {
+            for (int t = 0; t < 8; ++t) {
+                const int jj = (t + rot) & 7, j = b * 8 + jj;
+                const uint32_t c = j < m ? (uint32_t)__ldg(prow + j) : 0u;   // padded sub-spaces hold zeros
+                lut_add<G>(acc, lutS, (uint32_t)(b * 2048) + c * 8u + (uint32_t)jj);
+            }
+        }
+    }
+}
+
+// MODE 0: running top-R per (query, slice) in shared-memory BlockSelects -> partial.
+// MODE 1: collect every row with d_int <= tau[q] into the query's global buffer (large R: the running
+//         selection would dominate; with the threshold known the scan runs at its small-R speed).
+template <int G, int MB, int MODE>
 __global__ void __launch_bounds__(kAdcThreads)
-adc_scan_kernel(const uint8_t* __restrict__ codes, int64_t N, int m, const uint32_t* __restrict__ lutq, int Q, int R,
-                int C, int64_t slice_rows, int S, int groups, u64* __restrict__ partial) {
+adc_scan_kernel(const AdcArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int m = a.m, R = a.R, C = MODE == 0 ? a.C : 0, S = a.S;
     const int mb = (m + 7) >> 3;                                     // blocks of 8 sub-spaces (last one zero padded)
     u64* sel_buf = reinterpret_cast<u64*>(smem_raw);                 // G * C
     u64* sel_thr = sel_buf + (size_t)G * C;                          // G (padded to 2)
     uint32_t* lutS = reinterpret_cast<uint32_t*>(sel_thr + ((G + 1) & ~1));   // mb*256*8 slots of G
     int* sel_cnt = reinterpret_cast<int*>(lutS + (size_t)mb * 2048 * G);
-    __shared__ unsigned compact_mask;
     const int tid = threadIdx.x;
     const int rot = tid & 7;
+    const int Qe = a.qsel ? min(a.Q, __ldg(a.qcount)) : a.Q;
+    const int groups = a.qsel ? (Qe + G - 1) / G : a.groups;
     const int units = S * groups;
 
     for (int u = blockIdx.x; u < units; u += gridDim.x) {
         const int s = u / groups, grp = u - s * groups;
         const int q0 = grp * G;
-        const int nq = min(G, Q - q0);
+        const int nq = min(G, Qe - q0);
+        int qid[G];
+#pragma unroll
+        for (int g = 0; g < G; ++g) qid[g] = g < nq ? (a.qsel ? __ldg(a.qsel + q0 + g) : q0 + g) : 0;
         __syncthreads();   // previous unit fully drained
         // stage the group's LUTs into the rotated-slot layout
         for (int i = tid; i < mb * 2048; i += kAdcThreads) {
@@ -243,111 +309,104 @@ adc_scan_kernel(const uint8_t* __restrict__ codes, int64_t N, int m, const uint3
             const uint32_t slot = (uint32_t)(((j >> 3) * 256 + c) * 8 + (j & 7));
 #pragma unroll
             for (int g = 0; g < G; ++g)
-                lutS[(size_t)slot * G + g] = (g < nq && j < m) ? lutq[((size_t)(q0 + g) * m + j) * 256 + c] : 0u;
+                lutS[(size_t)slot * G + g] = (g < nq && j < m) ? a.lutq[((size_t)qid[g] * m + j) * 256 + c] : 0u;
         }
-        for (int i = tid; i < G * C; i += kAdcThreads) sel_buf[i] = VDB_KEY_MAX;
-        if (tid < G) { sel_cnt[tid] = 0; sel_thr[tid] = VDB_KEY_MAX; }
+        if (MODE == 0) {
+            for (int i = tid; i < G * C; i += kAdcThreads) sel_buf[i] = VDB_KEY_MAX;
+            if (tid < G) { sel_cnt[tid] = 0; sel_thr[tid] = VDB_KEY_MAX; }
+        }
+        uint32_t tau[G];
+#pragma unroll
+        for (int g = 0; g < G; ++g) tau[g] = (MODE == 1 && g < nq) ? __ldg(a.tau + qid[g]) : 0u;
         __syncthreads();
 
-        const int64_t r_begin = (int64_t)s * slice_rows;
-        const int64_t r_end = min(N, r_begin + slice_rows);
+        const int64_t r_begin = (int64_t)s * a.slice_rows;
+        const int64_t r_end = min(a.N, r_begin + a.slice_rows);
         for (int64_t rb = r_begin; rb < r_end; rb += kAdcThreads) {
             const int64_t r = rb + tid;
+            int nearly_full = 0;
             if (r < r_end) {
                 uint32_t acc[G];
-#pragma unroll
-                for (int g = 0; g < G; ++g) acc[g] = 0u;
-                if (MB > 0) {
-                    uint32_t w[MB > 0 ? 2 * MB : 2];
-                    if ((MB & 1) == 0) {
-                        const uint4* p = reinterpret_cast<const uint4*>(codes + r * m);
-#pragma unroll
-                        for (int i = 0; i < MB / 2; ++i) {
-                            const uint4 v = ld_stream_u4(p + i);
-                            w[4 * i] = v.x; w[4 * i + 1] = v.y; w[4 * i + 2] = v.z; w[4 * i + 3] = v.w;
-                        }
-                    } else {
-                        const uint2* p = reinterpret_cast<const uint2*>(codes + r * m);
-#pragma unroll
-                        for (int i = 0; i < MB; ++i) { const uint2 v = __ldg(p + i); w[2 * i] = v.x; w[2 * i + 1] = v.y; }
-                    }
-#pragma unroll
-                    for (int b = 0; b < MB; ++b) {
-                        uint32_t lo = w[2 * b], hi = w[2 * b + 1];
-                        rotr_bytes(lo, hi, rot);                         // byte t of (lo,hi) is now sub-space (t + rot) & 7
-#pragma unroll
-                        for (int t = 0; t < 8; ++t) {
-                            const uint32_t c = ((t < 4 ? lo : hi) >> (8 * (t & 3))) & 0xFFu;
-                            lut_add<G>(acc, lutS, (uint32_t)(b * 2048) + c * 8u + (uint32_t)((t + rot) & 7));
-                        }
-                    }
-                } else {
-                    const uint8_t* p = codes + r * m;
-                    for (int b = 0; b < mb; ++b) {
-                        for (int t = 0; t < 8; ++t) {
-                            const int jj = (t + rot) & 7, j = b * 8 + jj;
-                            const uint32_t c = j < m ? (uint32_t)__ldg(p + j) : 0u;   // padded sub-spaces hold zeros
-                            lut_add<G>(acc, lutS, (uint32_t)(b * 2048) + c * 8u + (uint32_t)jj);
-                        }
-                    }
-                }
+                adc_row<G, MB>(a.codes + r * a.row_stride * m, m, mb, lutS, rot, acc);
 #pragma unroll
                 for (int g = 0; g < G; ++g) {
                     if (g < nq) {
                         const u64 key = ((u64)acc[g] << 32) | (u64)(uint32_t)r;
-                        if (key < *(volatile u64*)(sel_thr + g)) {
-                            int p = atomicAdd(sel_cnt + g, 1);
-                            sel_buf[(size_t)g * C + R + p] = key;
+                        if (MODE == 0) {
+                            if (key < *(volatile u64*)(sel_thr + g)) {
+                                const int p = atomicAdd(sel_cnt + g, 1);
+                                sel_buf[(size_t)g * C + R + p] = key;
+                                nearly_full |= (p + 1 + kAdcThreads > C - R);
+                            }
+                        } else if (acc[g] <= tau[g]) {
+                            const int p = atomicAdd(a.ccnt + qid[g], 1);
+                            if (p < a.ccap) a.cbuf[(size_t)qid[g] * a.ccap + p] = key;
                         }
                     }
                 }
             }
-            // compaction check (CTA-uniform): at most kAdcThreads pushes per query since the last one
-            __syncthreads();
-            if (tid == 0) {
-                unsigned mk = 0;
-                for (int g = 0; g < G; ++g)
-                    if (sel_cnt[g] + kAdcThreads > C - R) mk |= 1u << g;
-                compact_mask = mk;
-            }
-            __syncthreads();
-            const unsigned mk = compact_mask;
-            if (mk) {
-#pragma unroll
-                for (int g = 0; g < G; ++g) {
-                    if (mk & (1u << g)) {
-                        block_bitonic_sort(sel_buf + (size_t)g * C, C);
-                        if (tid == 0) { sel_cnt[g] = 0; sel_thr[g] = sel_buf[(size_t)g * C + R - 1]; }
-                        __syncthreads();
-                    }
+            if (MODE == 0) {
+                // compaction check, one barrier: a pusher that saw its list come within one batch of full
+                // raises the flag (every push of this batch is done at the barrier, so the vote is CTA-uniform)
+                if (__syncthreads_or(nearly_full)) {      // pushes of the G queries are correlated: sort all lists in one pass
+                    block_bitonic_sort_lists(sel_buf, C, G);
+                    if (tid < G) { sel_cnt[tid] = 0; sel_thr[tid] = sel_buf[(size_t)tid * C + R - 1]; }
+                    __syncthreads();
                 }
             }
         }
-        __syncthreads();
-#pragma unroll
-        for (int g = 0; g < G; ++g) {
-            if (g < nq) {
-                block_bitonic_sort(sel_buf + (size_t)g * C, C);
-                u64* dst = partial + ((size_t)(q0 + g) * S + s) * R;
-                for (int i = tid; i < R; i += kAdcThreads) dst[i] = sel_buf[(size_t)g * C + i];
-                __syncthreads();
+        if (MODE == 0) {
+            __syncthreads();
+            block_bitonic_sort_lists(sel_buf, C, G);
+            for (int i = tid; i < nq * R; i += kAdcThreads) {
+                const int g = i / R, j = i - g * R;
+                a.partial[((size_t)(q0 + g) * S + s) * R + j] = sel_buf[(size_t)g * C + j];   // query SLOT (position in qsel)
             }
         }
     }
 }
 
-// R best of L fixed-point keys per query -> (float(d_int) * 2^-e, id).  One CTA per query.
+struct AdcFinArgs {
+    const u64* keys;            // [slot][L]
+    int L, R, C;
+    const int32_t* lens;        // optional per-query key count (collect buffers): count < R or > L flags the query
+    const int32_t* expo;
+    const int64_t* ids;
+    float* out_d;
+    int64_t* out_i;
+    uint32_t* tau_out;          // threshold mode: write d_int of the R-th key instead of the result rows
+    const int32_t* qsel;        // optional indirection (slot b -> query qsel[b], b < *qcount)
+    const int32_t* qcount;
+    int32_t* bad;               // flagged queries are appended here
+    int32_t* bad_count;
+};
+
+// R best of L fixed-point keys per query -> (float(d_int) * 2^-e, id).  One CTA per query slot.
 __global__ void __launch_bounds__(256)
-adc_finalize_kernel(const u64* __restrict__ keys, int L, int R, int C, const int32_t* __restrict__ expo,
-                    const int64_t* __restrict__ ids, float* __restrict__ out_d, int64_t* __restrict__ out_i) {
+adc_finalize_kernel(const AdcFinArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     u64* buf = reinterpret_cast<u64*>(smem_raw);
     __shared__ int cnt;
     __shared__ u64 thr;
+    int q = blockIdx.x;
+    if (a.qsel) {
+        if ((int)blockIdx.x >= __ldg(a.qcount)) return;
+        q = __ldg(a.qsel + blockIdx.x);
+    }
+    const int R = a.R;
+    int L = a.L;
+    if (a.lens) {
+        const int n = a.lens[q];
+        if (n < R || n > L) {       // too few rows under the threshold, or the buffer overflowed: exact rescan
+            if (threadIdx.x == 0) a.bad[atomicAdd(a.bad_count, 1)] = q;
+            return;
+        }
+        L = n;
+    }
     BlockSelect sel;
-    sel.init(buf, &cnt, &thr, C, R, blockDim.x);
+    sel.init(buf, &cnt, &thr, a.C, R, blockDim.x);
     __syncthreads();
-    const u64* src = keys + (size_t)blockIdx.x * L;
+    const u64* src = a.keys + (size_t)(a.qsel ? (int)blockIdx.x : q) * a.L;
     for (int base = 0; base < L; base += blockDim.x) {
         int i = base + threadIdx.x;
         if (i < L) {
@@ -357,17 +416,24 @@ adc_finalize_kernel(const u64* __restrict__ keys, int L, int R, int C, const int
         sel.maybe_compact();
     }
     sel.finalize();
-    const int e = expo[blockIdx.x];
+    if (a.tau_out) {
+        if (threadIdx.x == 0) {
+            const u64 key = buf[R - 1];
+            a.tau_out[q] = key == VDB_KEY_MAX ? 0xFFFFFFFFu : (uint32_t)(key >> 32);
+        }
+        return;
+    }
+    const int e = a.expo[q];
     for (int i = threadIdx.x; i < R; i += blockDim.x) {
         const u64 key = buf[i];
-        const size_t o = (size_t)blockIdx.x * R + i;
+        const size_t o = (size_t)q * R + i;
         if (key == VDB_KEY_MAX) {
-            out_d[o] = INFINITY;
-            out_i[o] = -1;
+            a.out_d[o] = INFINITY;
+            a.out_i[o] = -1;
         } else {
-            out_d[o] = ldexpf((float)(uint32_t)(key >> 32), -e);
+            a.out_d[o] = ldexpf((float)(uint32_t)(key >> 32), -e);
             const int64_t idx = (int64_t)(uint32_t)(key & 0xFFFFFFFFull);
-            out_i[o] = ids ? ids[idx] : idx;
+            a.out_i[o] = a.ids ? a.ids[idx] : idx;
         }
     }
 }
@@ -378,11 +444,44 @@ struct AdcPlan {
     size_t smem;
 };
 
+// Slices and grid for a (slice, query group) unit loop.  ~16 MB of codes per slice (L2-resident while the
+// CTAs of one slice stream it), enough units to fill the machine, not more than max_S; among the admissible
+// slice counts near that, the one whose unit count fills the last wave of CTAs best (768 units on 148 CTAs
+// idle 14% of the machine in the sixth wave; 1036 do not).
+static void plan_adc_slices(AdcPlan* p, int64_t N, int m, int64_t max_S, size_t smem_max) {
+    int per_sm = (int)(smem_max / p->smem);
+    if (per_sm > 4) per_sm = 4;
+    if (per_sm < 1) per_sm = 1;
+    const int64_t cap = (int64_t)sm_count() * per_sm;
+    int64_t S = (N * (int64_t)m + (16ll << 20) - 1) / (16ll << 20);
+    const int64_t fill = (2ll * sm_count() + p->groups - 1) / p->groups;
+    if (S < fill) S = fill;
+    int64_t max_by_rows = (N + 4095) / 4096;
+    if (max_S > max_by_rows) max_S = max_by_rows;
+    if (max_S < 1) max_S = 1;
+    if (S > max_S) S = max_S;
+    if (S < 1) S = 1;
+    int64_t best = S;
+    double best_eff = 0.0;
+    for (int64_t c = S; c <= max_S && c <= 2 * S + 4; ++c) {
+        const int64_t units = c * p->groups, grid = units < cap ? units : cap;
+        const double eff = (double)units / (double)(((units + grid - 1) / grid) * grid);
+        if (eff > best_eff + 0.01) { best_eff = eff; best = c; }
+    }
+    S = best;
+    p->slice_rows = (N + S - 1) / S;
+    if (p->slice_rows < 1) p->slice_rows = 1;
+    p->S = (int)((N + p->slice_rows - 1) / p->slice_rows);
+    if (p->S < 1) p->S = 1;
+    const int64_t units = (int64_t)p->S * p->groups;
+    p->grid = (int)(units < cap ? units : cap);
+}
+
 static bool plan_adc(int Q, int64_t N, int m, int R, AdcPlan* p) {
     const size_t smem_max = (size_t)max_smem_optin() - 64;
-    // pending area of at least one batch of pushes; twice that when it is cheap (fewer compactions)
-    int C = next_pow2(R + kAdcThreads);
-    if (C < 512) C = 512;
+    // pending area: one batch of pushes (kAdcThreads) that must always fit, plus room for ~R more so that a
+    // block sort is amortised over many pushes; 1024 up to R = 512 keeps 4 queries per CTA next to an m = 48 LUT
+    int C = R <= 64 ? 512 : (R <= 512 ? 1024 : next_pow2(R + 2 * kAdcThreads));
     const int mb = (m + 7) / 8;
     const int gs[3] = {4, 2, 1};
     for (int t = 0; t < 3; ++t) {
@@ -392,59 +491,117 @@ static bool plan_adc(int Q, int64_t N, int m, int R, AdcPlan* p) {
         if (smem > smem_max) continue;
         p->G = G; p->C = C; p->smem = smem;
         p->groups = (Q + G - 1) / G;
-        // slices: ~16 MB of codes each (L2-resident while every CTA streams it), at least enough
-        // units to fill the machine, at most what keeps S*R partial keys per query reasonable.
-        int64_t S = (N * (int64_t)m + (16ll << 20) - 1) / (16ll << 20);
-        int64_t fill = (2ll * sm_count() + p->groups - 1) / p->groups;
-        if (S < fill) S = fill;
-        int64_t max_by_rows = (N + 4095) / 4096;
-        if (max_by_rows < 1) max_by_rows = 1;
-        if (S > max_by_rows) S = max_by_rows;
-        int64_t max_by_keys = (1ll << 18) / R;
-        if (max_by_keys < 1) max_by_keys = 1;
-        if (S > max_by_keys) S = max_by_keys;
-        if (S < 1) S = 1;
-        p->slice_rows = (N + S - 1) / S;
-        if (p->slice_rows < 1) p->slice_rows = 1;
-        p->S = (int)((N + p->slice_rows - 1) / p->slice_rows);
-        if (p->S < 1) p->S = 1;
-        int64_t units = (int64_t)p->S * p->groups;
-        p->grid = (int)(units < sm_count() ? units : sm_count());
-        // more than one CTA per SM when shared memory allows it
-        int per_sm = (int)(smem_max / smem);
-        if (per_sm > 4) per_sm = 4;
-        if (per_sm > 1) {
-            int64_t g2 = (int64_t)sm_count() * per_sm;
-            p->grid = (int)(units < g2 ? units : g2);
-        }
+        int64_t max_by_keys = (1ll << 18) / R;          // S*R partial keys per query stay reasonable
+        plan_adc_slices(p, N, m, max_by_keys < 1 ? 1 : max_by_keys, smem_max);
         return true;
     }
     return false;
 }
 
-template <int G>
-static int launch_adc(const AdcPlan& p, const uint8_t* codes, int64_t N, int m, const uint32_t* lutq, int Q, int R,
-                      u64* partial, cudaStream_t st) {
+template <int G, int MODE>
+static int launch_adc(const AdcPlan& p, const AdcArgs& a, cudaStream_t st) {
 #define VDB_ADC_CASE(MBV)                                                                                       \
     {                                                                                                           \
-        auto kern = adc_scan_kernel<G, MBV>;                                                                    \
+        auto kern = adc_scan_kernel<G, MBV, MODE>;                                                              \
         VDB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem));         \
-        kern<<<p.grid, kAdcThreads, p.smem, st>>>(codes, N, m, lutq, Q, R, p.C, p.slice_rows, p.S, p.groups, partial); \
+        kern<<<p.grid, kAdcThreads, p.smem, st>>>(a);                                                           \
     }
-    ProfScope prof(kProfAdcScan, st);
-    const bool aligned16 = (reinterpret_cast<uintptr_t>(codes) & 15) == 0;
+    // vector code loads need every visited row 16 (8) byte aligned: row pitch row_stride*m keeps the alignment of m
+    const int m = a.m;
+    const bool aligned16 = (reinterpret_cast<uintptr_t>(a.codes) & 15) == 0;
+    const bool aligned8 = (reinterpret_cast<uintptr_t>(a.codes) & 7) == 0;
     if (aligned16 && m == 16) VDB_ADC_CASE(2)
     else if (aligned16 && m == 32) VDB_ADC_CASE(4)
     else if (aligned16 && m == 48) VDB_ADC_CASE(6)
     else if (aligned16 && m == 64) VDB_ADC_CASE(8)
     else if (aligned16 && m == 96) VDB_ADC_CASE(12)
-    else if ((reinterpret_cast<uintptr_t>(codes) & 7) == 0 && m == 8) VDB_ADC_CASE(1)
-    else if ((reinterpret_cast<uintptr_t>(codes) & 7) == 0 && m == 24) VDB_ADC_CASE(3)
+    else if (aligned8 && m == 8) VDB_ADC_CASE(1)
+    else if (aligned8 && m == 24) VDB_ADC_CASE(3)
     else VDB_ADC_CASE(0)
 #undef VDB_ADC_CASE
     count_launch(1);
     VDB_CUDA(cudaGetLastError());
     return VDB_OK;
+}
+
+template <int MODE>
+static int launch_adc_g(const AdcPlan& p, const AdcArgs& a, cudaStream_t st) {
+    if (p.G == 4) return launch_adc<4, MODE>(p, a, st);
+    if (p.G == 2) return launch_adc<2, MODE>(p, a, st);
+    return launch_adc<1, MODE>(p, a, st);
+}
+
+static int launch_adc_finalize(const AdcFinArgs& f, int slots, cudaStream_t st) {
+    const size_t smem = (size_t)f.C * 8;
+    VDB_REQUIRE(smem <= (size_t)max_smem_optin() - 1024, VDB_ERR_UNSUPPORTED, "R=%d too large for the final merge", f.R);
+    VDB_CUDA(cudaFuncSetAttribute(adc_finalize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    adc_finalize_kernel<<<slots, 256, smem, st>>>(f);
+    count_launch(1);
+    VDB_CUDA(cudaGetLastError());
+    return VDB_OK;
+}
+
+// Threshold-collect.  The running selection costs a barrier per batch of rows plus block sorts, and for
+// large R its C >= R + 384 keys of shared memory per query push queries out of the CTA (the LUTs need the
+// space), so it, not the code stream, sets the speed.  Instead: (A) the Rs best of a strided row sample give
+// a per-query threshold tau with E[#rows <= tau] = T = Rs * stride; (B) one barrier-free scan collects every
+// row with d_int <= tau; (C) the R best of the collected keys are the exact answer whenever
+// R <= count <= capacity; (D, E) any other query (probability < 1e-5 on exchangeable rows -- count has
+// relative spread 1/sqrt(Rs) and T is chosen >= 4.5 sigma above R; always on adversarial row orders) is
+// rescanned by the running-selection kernel through a device-side list, so the result is exact in every
+// case and the call never synchronises.
+struct AdcCollectPlan {
+    bool use;
+    int64_t stride, n_sample;
+    int cap, Rs;
+    AdcPlan sample, collect, rescan;
+    size_t off_tau, off_cnt, off_bad, off_badn, off_cbuf, off_partial, total;   // after lutq + expo
+};
+
+static bool plan_adc_collect_scan(int Q, int64_t N, int m, AdcPlan* p) {
+    const int mb = (m + 7) / 8;
+    const size_t smem_max = (size_t)max_smem_optin() - 64;
+    const int gs[3] = {4, 2, 1};
+    for (int t = 0; t < 3; ++t) {
+        const int G = gs[t];
+        const size_t smem = (size_t)((G + 1) & ~1) * 8 + (size_t)mb * 2048 * G * 4 + (size_t)G * 4 + 16;
+        if (smem > smem_max) continue;
+        p->G = G; p->C = 0; p->smem = smem;
+        p->groups = (Q + G - 1) / G;
+        plan_adc_slices(p, N, m, 1ll << 30, smem_max);
+        return true;
+    }
+    return false;
+}
+
+static size_t al256(size_t v) { return (v + 255) & ~(size_t)255; }
+
+static bool plan_adc_collect(int Q, int64_t N, int m, int R, AdcCollectPlan* c) {
+    c->use = false;
+    double T;
+    // relative spread of the collected count: sigma = 1/sqrt(Rs); T (1 - 4.5 sigma) >= R and cap >= T (1 + 6 sigma)
+    if (R <= 100) { c->Rs = 32; T = 512.0; c->cap = 2048; }              // sigma 18%
+    else if (R <= 512) { c->Rs = 64; T = 4.0 * R; c->cap = 8 * R; }      // sigma 12.5%
+    else { c->Rs = 128; T = 1.8 * R; c->cap = 4 * R; }                   // sigma 8.8%
+    c->stride = (int64_t)(T / c->Rs);
+    if (c->stride < 1) c->stride = 1;
+    c->n_sample = N / c->stride;
+    if (c->n_sample < 8 * c->Rs || (int64_t)(16.0 * T) > N) return true;   // too few rows for a useful threshold
+    if (!plan_adc(Q, c->n_sample, m, c->Rs, &c->sample)) return true;
+    if (!plan_adc_collect_scan(Q, N, m, &c->collect)) return true;
+    if (!plan_adc(Q, N, m, R, &c->rescan)) return false;
+    size_t o = 0;
+    c->off_tau = o; o += al256((size_t)Q * 4);
+    c->off_cnt = o; o += al256((size_t)Q * 4);
+    c->off_bad = o; o += al256((size_t)Q * 4);
+    c->off_badn = o; o += 256;
+    c->off_cbuf = o; o += al256((size_t)Q * c->cap * 8);
+    c->off_partial = o;
+    const size_t ps = (size_t)Q * c->sample.S * c->Rs * 8, pr = (size_t)Q * c->rescan.S * R * 8;
+    o += al256(ps > pr ? ps : pr);
+    c->total = o;
+    c->use = true;
+    return true;
 }
 
 static size_t adc_lutq_bytes(int Q, int m) { return (((size_t)Q * m * 256 * 4) + 255) & ~(size_t)255; }
@@ -528,6 +685,9 @@ int vdb_pq_lut(const float* q, int Q, int D, int m, int K, const float* codebook
 
 size_t vdb_pq_adc_topk_workspace(int Q, int64_t N, int m, int R) {
     if (Q <= 0 || R <= 0 || m <= 0) return 0;
+    AdcCollectPlan c;
+    if (!plan_adc_collect(Q, N, m, R, &c)) return 0;
+    if (c.use) return adc_lutq_bytes(Q, m) + adc_expo_bytes(Q) + c.total + 256;
     AdcPlan p;
     if (!plan_adc(Q, N, m, R, &p)) return 0;
     return adc_lutq_bytes(Q, m) + adc_expo_bytes(Q) + (size_t)Q * p.S * R * 8 + 256;
@@ -540,35 +700,75 @@ int vdb_pq_adc_topk(const uint8_t* codes, int64_t N, int m, const float* lut, in
     VDB_REQUIRE(m <= 255, VDB_ERR_UNSUPPORTED, "m=%d > 255 overflows the 32-bit fixed-point sum", m);
     if (Q == 0) return VDB_OK;
     VDB_REQUIRE(lut && out_d && out_i && (codes || N == 0), VDB_ERR_INVALID, "vdb_pq_adc_topk: null pointer");
+    AdcCollectPlan c;
     AdcPlan p;
-    VDB_REQUIRE(plan_adc(Q, N, m, R, &p), VDB_ERR_UNSUPPORTED, "m=%d R=%d do not fit shared memory", m, R);
-    const size_t need = adc_lutq_bytes(Q, m) + adc_expo_bytes(Q) + (size_t)Q * p.S * R * 8;
+    VDB_REQUIRE(plan_adc_collect(Q, N, m, R, &c) && (c.use || plan_adc(Q, N, m, R, &p)), VDB_ERR_UNSUPPORTED,
+                "m=%d R=%d do not fit shared memory", m, R);
+    const size_t head = adc_lutq_bytes(Q, m) + adc_expo_bytes(Q);
+    const size_t need = head + (c.use ? c.total : (size_t)Q * p.S * R * 8);
     VDB_REQUIRE(ws && ws_bytes >= need, VDB_ERR_WORKSPACE, "workspace %zu < %zu", ws_bytes, need);
     VDB_REQUIRE((reinterpret_cast<uintptr_t>(ws) & 15) == 0, VDB_ERR_INVALID, "workspace must be 16-byte aligned");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     char* base = static_cast<char*>(ws);
     uint32_t* lutq = reinterpret_cast<uint32_t*>(base);
     int32_t* expo = reinterpret_cast<int32_t*>(base + adc_lutq_bytes(Q, m));
-    u64* partial = reinterpret_cast<u64*>(base + adc_lutq_bytes(Q, m) + adc_expo_bytes(Q));
     adc_quantize_lut_kernel<<<Q, 256, 0, st>>>(lut, m * 256, lutq, expo);
     count_launch(1);
+
+    AdcArgs a{};
+    a.codes = codes; a.N = N; a.row_stride = 1; a.m = m; a.lutq = lutq; a.Q = Q; a.R = R;
+    AdcFinArgs f{};
+    f.R = R; f.expo = expo; f.ids = ids; f.out_d = out_d; f.out_i = out_i;
     int rc;
-    if (p.G == 4) rc = launch_adc<4>(p, codes, N, m, lutq, Q, R, partial, st);
-    else if (p.G == 2) rc = launch_adc<2>(p, codes, N, m, lutq, Q, R, partial, st);
-    else rc = launch_adc<1>(p, codes, N, m, lutq, Q, R, partial, st);
-    if (rc) return rc;
-    const int L = p.S * R;
-    const int C = select_capacity(R, 256);
-    const size_t smem = (size_t)C * 8;
-    VDB_REQUIRE(smem <= (size_t)max_smem_optin() - 1024, VDB_ERR_UNSUPPORTED, "R=%d too large for the final merge", R);
-    VDB_CUDA(cudaFuncSetAttribute(adc_finalize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    {
+    if (!c.use) {
+        u64* partial = reinterpret_cast<u64*>(base + head);
+        a.C = p.C; a.slice_rows = p.slice_rows; a.S = p.S; a.groups = p.groups; a.partial = partial;
+        {
+            ProfScope prof(kProfAdcScan, st);
+            rc = launch_adc_g<0>(p, a, st);
+        }
+        if (rc) return rc;
+        f.keys = partial; f.L = p.S * R; f.C = select_capacity(R, 256);
         ProfScope prof(kProfFinalize, st);
-        adc_finalize_kernel<<<Q, 256, smem, st>>>(partial, L, R, C, expo, ids, out_d, out_i);
+        return launch_adc_finalize(f, Q, st);
     }
-    count_launch(1);
-    VDB_CUDA(cudaGetLastError());
-    return VDB_OK;
+
+    char* w = base + head;
+    uint32_t* tau = reinterpret_cast<uint32_t*>(w + c.off_tau);
+    int32_t* ccnt = reinterpret_cast<int32_t*>(w + c.off_cnt);
+    int32_t* bad = reinterpret_cast<int32_t*>(w + c.off_bad);
+    int32_t* badn = reinterpret_cast<int32_t*>(w + c.off_badn);
+    u64* cbuf = reinterpret_cast<u64*>(w + c.off_cbuf);
+    u64* partial = reinterpret_cast<u64*>(w + c.off_partial);
+    VDB_CUDA(cudaMemsetAsync(ccnt, 0, c.off_cbuf - c.off_cnt, st));       // counters, flagged list and its length
+    {
+        ProfScope prof(kProfAdcScan, st);
+        // (A) threshold from a strided sample
+        AdcArgs s = a;
+        s.N = c.n_sample; s.row_stride = c.stride; s.R = c.Rs; s.C = c.sample.C;
+        s.slice_rows = c.sample.slice_rows; s.S = c.sample.S; s.groups = c.sample.groups; s.partial = partial;
+        if ((rc = launch_adc_g<0>(c.sample, s, st))) return rc;
+        AdcFinArgs fs{};
+        fs.keys = partial; fs.L = c.sample.S * c.Rs; fs.R = c.Rs; fs.C = select_capacity(c.Rs, 256);
+        fs.tau_out = tau;
+        if ((rc = launch_adc_finalize(fs, Q, st))) return rc;
+        // (B) collect
+        AdcArgs b = a;
+        b.C = 0; b.slice_rows = c.collect.slice_rows; b.S = c.collect.S; b.groups = c.collect.groups;
+        b.tau = tau; b.cbuf = cbuf; b.ccnt = ccnt; b.ccap = c.cap;
+        if ((rc = launch_adc_g<1>(c.collect, b, st))) return rc;
+    }
+    ProfScope prof(kProfFinalize, st);
+    // (C) exact top-R of the collected keys; queries outside [R, cap] go to the flagged list
+    f.keys = cbuf; f.L = c.cap; f.lens = ccnt; f.C = select_capacity(R, 256); f.bad = bad; f.bad_count = badn;
+    if ((rc = launch_adc_finalize(f, Q, st))) return rc;
+    // (D, E) flagged queries: running-selection scan + merge, driven by the device-side list
+    a.C = c.rescan.C; a.slice_rows = c.rescan.slice_rows; a.S = c.rescan.S; a.groups = c.rescan.groups;
+    a.partial = partial; a.qsel = bad; a.qcount = badn;
+    if ((rc = launch_adc_g<0>(c.rescan, a, st))) return rc;
+    f.keys = partial; f.L = c.rescan.S * R; f.lens = nullptr; f.bad = nullptr; f.bad_count = nullptr;
+    f.qsel = bad; f.qcount = badn;
+    return launch_adc_finalize(f, Q, st);
 }
 
 }  // extern "C"
