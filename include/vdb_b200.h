@@ -50,7 +50,7 @@ uint64_t vdb_launch_count(void);
  * CUDA events on its own stream.  vdb_profile_read() waits for the slot's events, returns the
  * number of launches and their summed duration, and clears the slot.
  * Slots: 0 exact fp32 scan, 1 exact tensor-core scan, 2 ADC scan, 3 PQ encode, 4 HNSW search,
- * 5 rerank, 6 top-k finalise/merge, 7 HNSW insert. */
+ * 5 rerank, 6 top-k finalise/merge, 7 HNSW insert, 8 IVF list scan. */
 void vdb_profile_enable(int on);
 int vdb_profile_read(int slot, int* launches, float* total_ms);
 
@@ -208,6 +208,36 @@ int vdb_hnsw_build_search(const float* db, int64_t N, int D, const int32_t* adj0
 int vdb_hnsw_reverse_merge(int32_t* adj /*[dev] lists*deg*/, float* adjd /*[dev] lists*deg*/, int deg,
                            const int32_t* list_idx /*[dev] segments*/, const int32_t* seg_start /*[dev] segments+1*/,
                            int segments, const int32_t* in_rows /*[dev]*/, const float* in_d /*[dev]*/, void* stream);
+
+/* ---- f3: IVF (src/vector_db/indexing/ivf.py) -------------------------------------------------
+ * The index is K centroids [K,D] and K inverted lists in CSR form: list_ptr[K+1], list_rows[] = row
+ * indices into the fp32 matrix `db`, each list in the reference's append order (ivf.py:78-81,113).
+ *
+ * vdb_ivf_centroid_dist: out[q][c] = np.linalg.norm(centroids[c] - query[q]) (ivf.py:109,170) in numpy's
+ *   operation order (fp32 subtract and square, pairwise_sum along the row, sqrt) -- bit-identical values,
+ *   so the probe set and the nearest-centroid assignment of add() are the reference's.
+ * vdb_ivf_probe: probes[q][:] = np.argsort(out[q])[:n_probe] (ivf.py:171; ties by centroid index) and,
+ *   when `prefix` is given, prefix[q][p] = number of candidates enumerated before probe p
+ *   (prefix[q][n_probe] = total).  n_probe = 1 is the argmin of ivf.py:110.
+ * vdb_ivf_scan: euclidean_vector_distance (util/distance.py:3-4) to every member of the probed lists,
+ *   candidates ordered by distance with enumeration order (probe rank, list position) as tie-break --
+ *   the stable sort of ivf.py:177-193 -- first k returned.  Rows whose bit in `alive` is cleared are
+ *   skipped (ivf.py:188-190).  out_scanned[q] (nullable) = candidates enumerated.  The distance
+ *   arithmetic is vdb_exact_topk_f32's, so n_probe == K returns that scan's values.
+ * vdb_ivf_centroid_mean: Lloyd mean update over the lists (scipy kmeans2 as called at ivf.py:75: an
+ *   empty cluster keeps its centroid). */
+int vdb_ivf_centroid_dist(const float* q /*[dev] Q*D*/, int Q, int D, const float* centroids /*[dev] K*D*/, int K,
+                          float* out /*[dev] Q*K*/, void* stream);
+int vdb_ivf_probe(const float* cdist /*[dev] Q*K*/, int Q, int K, int n_probe, const int32_t* list_ptr /*[dev] K+1, nullable*/,
+                  int32_t* probes /*[dev] Q*n_probe*/, int32_t* prefix /*[dev] Q*(n_probe+1), nullable*/, void* stream);
+size_t vdb_ivf_scan_workspace(int Q, int k);
+int vdb_ivf_scan(const float* q /*[dev]*/, int Q, const float* db /*[dev] rows*D*/, int D,
+                 const int32_t* list_ptr /*[dev]*/, const int32_t* list_rows /*[dev]*/, const int32_t* probes /*[dev]*/,
+                 const int32_t* prefix /*[dev]*/, int n_probe, const uint32_t* alive /*[dev] nullable*/,
+                 const int64_t* ids /*[dev] nullable*/, int k, float* out_d /*[dev] Q*k*/, int64_t* out_i /*[dev] Q*k*/,
+                 int64_t* out_scanned /*[dev] Q, nullable*/, void* ws, size_t ws_bytes, void* stream);
+int vdb_ivf_centroid_mean(const float* x /*[dev] rows*D*/, int D, const int32_t* list_ptr /*[dev] K+1*/,
+                          const int32_t* list_rows /*[dev]*/, int K, float* centroids /*[dev] K*D, in place*/, void* stream);
 
 /* ---- e: multi-GPU merge -----------------------------------------------------------------------
  * lists: L sorted lists per query, d [L][Q][k] / i [L][Q][k] (the all-gathered per-shard results);

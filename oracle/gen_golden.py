@@ -147,6 +147,60 @@ def gen_hnsw(ref_hnsw, Storage, Node, tag, n, dim, M, efc, nq, ef, k, seed):
                         build_evals=np.int64(build_evals))
 
 
+def gen_ivf(Storage, Node):
+    """Reference IvfIndex (src/vector_db/indexing/ivf.py): build (kmeans2 on the seeded global numpy RNG),
+    add, search at several n_probe, delete + search.  Blobs keep every cluster well populated."""
+    import vector_db.indexing.ivf as ref_ivf
+    rng = np.random.default_rng(2024)
+    n, dim, k, nq, top_k = 1500, 24, 12, 20, 10
+    centres = rng.standard_normal((k, dim)).astype(np.float32) * 2.0
+    X = (centres[rng.integers(0, k, n)] + 0.7 * rng.standard_normal((n, dim))).astype(np.float32)
+    X[40] = X[7]                                # duplicate embedding: stable-sort tie (ivf.py:193)
+    ids = (np.arange(n, dtype=np.int64) * 2 + 11)
+    Q = (centres[rng.integers(0, k, nq)] + 0.9 * rng.standard_normal((nq, dim))).astype(np.float32)
+    Q[0] = X[7]
+    idx = ref_ivf.IvfIndex(k=k, storage=Storage())
+    np.random.seed(5)
+    state = np.random.get_state()
+    idx.build_index([Node(id=int(ids[i]), embedding=X[i]) for i in range(n)])
+    np.random.set_state(state)
+    init_rows = np.random.mtrand._rand.choice(n, size=k, replace=False)     # what scipy's _kpoints drew
+    centroids = np.asarray(idx.centroids)
+    lists0 = [list(l) for l in idx.inverted_lists]
+    # add (ivf.py:87-117)
+    A = (centres[rng.integers(0, k, 30)] + 0.7 * rng.standard_normal((30, dim))).astype(np.float32)
+    add_ids = np.arange(30, dtype=np.int64) + 100000
+    add_cluster = np.empty(30, np.int64)
+    for j in range(30):
+        idx.add(Node(id=int(add_ids[j]), embedding=A[j]))
+        add_cluster[j] = next(c for c, l in enumerate(idx.inverted_lists) if l and l[-1] == int(add_ids[j]))
+    res = {}
+    for n_probe in (1, 3, k):
+        D = np.full((nq, top_k), np.inf, np.float32)
+        I = np.full((nq, top_k), -1, np.int64)
+        for qi in range(nq):
+            out = idx.search(Q[qi], n_probe=n_probe, top_k=top_k)
+            D[qi, :len(out)] = [d for _, d in out]
+            I[qi, :len(out)] = [nd.id for nd, _ in out]
+        res[f"D{n_probe}"], res[f"I{n_probe}"] = D, I
+    cdist = np.stack([np.linalg.norm(centroids - Q[qi], axis=1) for qi in range(nq)])
+    # delete (ivf.py:119-137) then search again
+    dead = np.concatenate([res[f"I{k}"][:, 0][:8], ids[100:110]])
+    for i in dead:
+        idx.delete(int(i))
+    Dd = np.full((nq, top_k), np.inf, np.float32)
+    Id = np.full((nq, top_k), -1, np.int64)
+    for qi in range(nq):
+        out = idx.search(Q[qi], n_probe=3, top_k=top_k)
+        Dd[qi, :len(out)] = [d for _, d in out]
+        Id[qi, :len(out)] = [nd.id for nd, _ in out]
+    flat = np.array([i for l in lists0 for i in l], dtype=np.int64)
+    ptr = np.cumsum([0] + [len(l) for l in lists0]).astype(np.int64)
+    np.savez_compressed(os.path.join(OUT, "ivf.npz"), X=X, ids=ids, Q=Q, k=np.int64(k), init_rows=init_rows,
+                        centroids=centroids, list_ptr=ptr, list_ids=flat, A=A, add_ids=add_ids,
+                        add_cluster=add_cluster, cdist=cdist, dead=dead, Dd=Dd, Id=Id, **res)
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     ref_hnsw, ref_pq, Storage, Node, ref_dist, topk_sorted = _import_reference()
@@ -155,6 +209,7 @@ def main():
     gen_pq8(ref_pq)
     gen_hnsw(ref_hnsw, Storage, Node, "small", n=400, dim=16, M=8, efc=50, nq=24, ef=50, k=10, seed=11)
     gen_hnsw(ref_hnsw, Storage, Node, "medium", n=2000, dim=48, M=16, efc=100, nq=32, ef=64, k=10, seed=12)
+    gen_ivf(Storage, Node)
     print("golden fixtures written to", os.path.abspath(OUT))
 
 

@@ -1,0 +1,174 @@
+"""GPU parity: IVF probe selection, list scan, training, and the reference's IvfIndex contract
+(src/vector_db/indexing/ivf.py, tests/indexing/test_ivf.py)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import ivf_oracle as IO
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _t(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).to(DEV)
+
+
+def _golden_index(golden_dir, with_adds=True):
+    from vector_db_b200.indexing import IvfIndex
+    from vector_db_b200.types import Node
+    g = np.load(os.path.join(golden_dir, "ivf.npz"))
+    k, ptr = int(g["k"]), g["list_ptr"]
+    lists = [[int(i) for i in g["list_ids"][ptr[c]:ptr[c + 1]]] for c in range(k)]
+    vec = {int(i): g["X"][j] for j, i in enumerate(g["ids"])}
+    idx = IvfIndex(k=k)
+    for i, v in vec.items():
+        idx.storage.save(Node(id=i, embedding=v))
+    idx.load_state({"k": k, "centroids": g["centroids"], "inverted_lists": lists}, vectors=vec)
+    if with_adds:
+        for j in range(g["A"].shape[0]):
+            idx.add(Node(id=int(g["add_ids"][j]), embedding=g["A"][j]))
+    return g, idx
+
+
+@pytest.mark.parametrize("K,D", [(12, 24), (50, 7), (33, 130), (64, 384), (10, 777), (5, 1024)])
+def test_centroid_distances_bit_equal_numpy(K, D):
+    """np.linalg.norm(centroids - q, axis=1) (ivf.py:109,170): numpy's pairwise summation order reproduced."""
+    from vector_db_b200 import ops
+    rng = np.random.default_rng(K * 1000 + D)
+    cent = rng.standard_normal((K, D)).astype(np.float32)
+    Q = rng.standard_normal((9, D)).astype(np.float32)
+    got = ops.ivf_centroid_dist(_t(Q), _t(cent)).cpu().numpy()
+    ref = np.stack([IO.centroid_distances(cent, q) for q in Q])
+    np.testing.assert_array_equal(got, ref)
+    probes, _ = ops.ivf_probe(_t(ref), min(K, 4))
+    np.testing.assert_array_equal(probes.cpu().numpy(), np.stack([np.argsort(r, kind="stable")[:min(K, 4)] for r in ref]))
+
+
+def test_search_add_delete_match_reference_run(golden_dir):
+    g, idx = _golden_index(golden_dir)
+    k = int(g["k"])
+    for j in range(g["A"].shape[0]):                                   # add(): nearest cluster, appended last
+        assert int(g["add_ids"][j]) in idx.inverted_lists[int(g["add_cluster"][j])]
+    for n_probe in (1, 3, k):
+        D, I = idx.search_batch(g["Q"], n_probe, 10)
+        np.testing.assert_array_equal(I, g[f"I{n_probe}"])
+        np.testing.assert_allclose(D, g[f"D{n_probe}"], rtol=1e-6, atol=1e-7)
+    res = idx.search(g["Q"][0], n_probe=3, top_k=5)                    # duplicate embeddings: list order breaks the tie
+    assert [n.id for n, _ in res[:2]] == [int(g["ids"][7]), int(g["ids"][40])] and res[0][1] < 1e-6
+    assert isinstance(res[0][1], np.float32) and np.array_equal(res[0][0].embedding, g["X"][7])
+    for i in g["dead"]:
+        idx.delete(int(i))
+    D, I = idx.search_batch(g["Q"], 3, 10)
+    np.testing.assert_array_equal(I, g["Id"])
+    np.testing.assert_allclose(D, g["Dd"], rtol=1e-6, atol=1e-7)
+    assert idx.get_cluster_stats()["total_vectors"] == 1500 + 30 - len(set(int(i) for i in g["dead"]))
+
+
+def test_training_matches_reference_kmeans_given_its_initial_rows(golden_dir):
+    """kmeans2(iter=100, minit='points') (ivf.py:75) from the rows scipy drew: same lists, same centroids."""
+    from vector_db_b200.indexing import IvfIndex
+    g = np.load(os.path.join(golden_dir, "ivf.npz"))
+    k, ptr = int(g["k"]), g["list_ptr"]
+    idx = IvfIndex(k=k)
+    idx.build_from_arrays([int(i) for i in g["ids"]], g["X"], init_rows=g["init_rows"])
+    np.testing.assert_allclose(idx.centroids, g["centroids"], rtol=1e-4, atol=1e-5)
+    assert idx.inverted_lists == [[int(i) for i in g["list_ids"][ptr[c]:ptr[c + 1]]] for c in range(k)]
+    # the same draw through the global numpy RNG, as scipy makes it
+    np.random.seed(5)
+    idx2 = IvfIndex(k=k)
+    idx2.build_from_arrays([int(i) for i in g["ids"]], g["X"])
+    assert idx2.inverted_lists == idx.inverted_lists
+
+
+@pytest.mark.parametrize("n,dim,K,n_probe,nq,top_k", [(6000, 48, 32, 5, 64, 10), (3000, 30, 16, 16, 17, 25),
+                                                     (20000, 128, 100, 8, 300, 10), (500, 8, 7, 2, 5, 600)])
+def test_batched_search_vs_oracle(n, dim, K, n_probe, nq, top_k):
+    from vector_db_b200.indexing import IvfIndex
+    rng = np.random.default_rng(n + K)
+    X = rng.standard_normal((n, dim)).astype(np.float32)
+    ids = np.arange(n, dtype=np.int64) * 3 + 1
+    Q = rng.standard_normal((nq, dim)).astype(np.float32)
+    idx = IvfIndex(k=K)
+    idx.build_from_arrays([int(i) for i in ids], X, iters=5, init_rows=rng.choice(n, K, replace=False))
+    D, I = idx.search_batch(Q, n_probe, top_k)
+    vec = {int(i): X[j] for j, i in enumerate(ids)}
+    lists = idx.inverted_lists
+    assert sum(len(l) for l in lists) == n
+    for qi in range(0, nq, max(1, nq // 16)):
+        res, n_cand, _ = IO.search(idx.centroids, lists, vec, Q[qi], n_probe, top_k)
+        assert int(idx.last_scanned[qi]) == n_cand
+        assert [r[1] for r in res] == [int(i) for i in I[qi] if i >= 0]
+        np.testing.assert_allclose(D[qi][:len(res)], np.array([r[0] for r in res], np.float32), rtol=1e-5)
+        assert np.all(I[qi][len(res):] == -1) and np.all(np.isinf(D[qi][len(res):]))
+
+
+def test_full_probe_equals_exact_scan():
+    """n_probe == k visits every list: the values are the exact fp32 scan's, bit for bit (property at a size the
+    oracle does not reach)."""
+    from vector_db_b200 import ops
+    from vector_db_b200.indexing import IvfIndex
+    rng = np.random.default_rng(99)
+    n, dim, K = 100_000, 64, 64
+    X = rng.standard_normal((n, dim)).astype(np.float32)
+    Q = rng.standard_normal((128, dim)).astype(np.float32)
+    idx = IvfIndex(k=K)
+    idx.build_from_arrays(range(n), X, iters=3, init_rows=np.arange(K))
+    D, I = idx.search_batch(Q, K, 10)
+    De, Ie = ops.exact_topk_f32(_t(Q), _t(X), 10, "l2")
+    np.testing.assert_array_equal(D, De.cpu().numpy())
+    np.testing.assert_array_equal(I, Ie.cpu().numpy())
+    assert np.all(idx.last_scanned == n)
+
+
+def test_reference_contract_errors_stats_persistence(tmp_path):
+    """tests/indexing/test_ivf.py:17-23,47-64,96-102,169-195,231-313 restated against the GPU class."""
+    from vector_db_b200.indexing import IvfIndex
+    from vector_db_b200.types import Node
+    with pytest.raises(ValueError, match="k-means parameter should be positive"):
+        IvfIndex(k=0)
+    ivf = IvfIndex(k=4)
+    assert ivf.k == 4 and ivf.centroids is None and ivf.inverted_lists == []
+    with pytest.raises(ValueError, match="Cannot build index with empty node list"):
+        ivf.build_index([])
+    with pytest.raises(ValueError, match="Need at least 4 vectors for 4 clusters"):
+        ivf.build_index([Node(id=i, embedding=np.random.rand(8).astype(np.float32)) for i in range(2)])
+    with pytest.raises(ValueError, match="Index must be built before adding nodes"):
+        IvfIndex(k=4).add(Node(id=1, embedding=np.zeros(8, np.float32)))
+    with pytest.raises(ValueError, match="Index must be built before searching"):
+        IvfIndex(k=4).search(np.zeros(8, np.float32), n_probe=2, top_k=5)
+    index_file = tmp_path / "ivf.pkl"
+    np.random.seed(3)
+    ivf = IvfIndex(k=4, index_file=index_file)
+    nodes = [Node(id=i, embedding=np.random.rand(8).astype(np.float32), metadata={"i": i}) for i in range(40)]
+    ivf.build_index(nodes)
+    assert ivf.centroids.shape == (4, 8) and len(ivf.inverted_lists) == 4
+    assert sum(len(l) for l in ivf.inverted_lists) == 40
+    for bad in (0, -1, 5):
+        with pytest.raises(ValueError, match="n_probe must be between 1 and 4"):
+            ivf.search(nodes[0].embedding, n_probe=bad, top_k=5)
+    with pytest.raises(ValueError, match="query must be 1D array"):
+        ivf.search(np.zeros((2, 8), np.float32), n_probe=2, top_k=5)
+    with pytest.raises(ValueError, match="doesn't match"):
+        ivf.search(np.zeros(9, np.float32), n_probe=2, top_k=5)
+    first, dist = ivf.search(nodes[0].embedding, n_probe=4, top_k=5)[0]
+    assert first.id == 0 and dist < 1e-6 and first.metadata == {"i": 0}
+    stats = ivf.get_cluster_stats()
+    assert stats["total_vectors"] == 40 and stats["min_size"] <= stats["avg_size"] <= stats["max_size"]
+    assert ivf.get_cluster_size(0) == len(ivf.inverted_lists[0])
+    with pytest.raises(ValueError, match="cluster_id must be between 0 and 3"):
+        ivf.get_cluster_size(4)
+    # persistence: a second instance on the same file + storage answers the same (test_ivf.py:277-313)
+    assert index_file.exists()
+    ivf2 = IvfIndex(k=4, storage=ivf.storage, index_file=index_file)
+    np.testing.assert_array_equal(ivf2.centroids, ivf.centroids)
+    assert ivf2.inverted_lists == ivf.inverted_lists
+    a = [(n.id, d) for n, d in ivf.search(nodes[3].embedding, n_probe=2, top_k=5)]
+    b = [(n.id, d) for n, d in ivf2.search(nodes[3].embedding, n_probe=2, top_k=5)]
+    assert a == b
+    ivf.delete(0)
+    assert all(0 not in l for l in ivf.inverted_lists)
+    assert all(n.id != 0 for n, _ in ivf.search(nodes[0].embedding, n_probe=4, top_k=5))

@@ -123,3 +123,36 @@ def test_pq_dsub8_and_dsub12_codes_match_reference(golden_dir):
     np.testing.assert_array_equal(O.pq_encode(g["Y"], list(g["centroids"])), g["codes_y"])
     np.testing.assert_array_equal(O.pq_encode(g["X"], list(g["centroids"])), g["codes"])
     np.testing.assert_array_equal(O.pq_encode(g["X12"], list(g["centroids12"])), g["codes12"])
+
+
+def test_ivf_oracle_matches_reference(golden_dir):
+    """oracle/ivf_oracle.py against the reference IvfIndex run (oracle/gen_golden.py:gen_ivf): k-means given
+    scipy's initial rows, list construction, add(), search at n_probe 1/3/k, delete() + search."""
+    from oracle import ivf_oracle as IO
+    g = _load(golden_dir, "ivf.npz")
+    X, ids, Q, k = g["X"], g["ids"], g["Q"], int(g["k"])
+    cent, ptr = g["centroids"], g["list_ptr"]
+    lists = [[int(i) for i in g["list_ids"][ptr[c]:ptr[c + 1]]] for c in range(k)]
+    C, labels = O.kmeans_lloyd(X, X[g["init_rows"]], 100)                 # ivf.py:75
+    np.testing.assert_allclose(C, cent, rtol=1e-5, atol=1e-6)
+    assert IO.lists_from_labels(labels, [int(i) for i in ids], k) == lists   # ivf.py:78-81
+    vec = {int(i): X[j] for j, i in enumerate(ids)}
+    for j in range(g["A"].shape[0]):                                       # ivf.py:87-117
+        c = IO.nearest_cluster(cent, g["A"][j])
+        assert c == int(g["add_cluster"][j])
+        lists[c].append(int(g["add_ids"][j]))
+        vec[int(g["add_ids"][j])] = g["A"][j]
+    np.testing.assert_array_equal(np.stack([IO.centroid_distances(cent, q) for q in Q]), g["cdist"])
+    for n_probe in (1, 3, k):
+        for qi in range(Q.shape[0]):
+            res, _, _ = IO.search(cent, lists, vec, Q[qi], n_probe, 10)
+            assert [r[1] for r in res] == [int(i) for i in g[f"I{n_probe}"][qi] if i >= 0]
+            np.testing.assert_array_equal(np.array([r[0] for r in res], np.float32), g[f"D{n_probe}"][qi][:len(res)])
+    for i in g["dead"]:                                                    # ivf.py:119-137
+        for lst in lists:
+            if int(i) in lst:
+                lst.remove(int(i))
+        vec.pop(int(i), None)
+    for qi in range(Q.shape[0]):
+        res, _, _ = IO.search(cent, lists, vec, Q[qi], 3, 10)
+        assert [r[1] for r in res] == [int(i) for i in g["Id"][qi] if i >= 0]

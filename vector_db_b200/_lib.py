@@ -56,6 +56,11 @@ SIGNATURES = {
     "vdb_hnsw_build_search": (_i, [_p, _i64, _i, _p, _i, _p, _i, _p, _p, _i, _i, C.c_int32, _i, C.c_int32, _i, _i,
                                    _p, _p, _p, _sz, _p]),
     "vdb_hnsw_reverse_merge": (_i, [_p, _p, _i, _p, _p, _i, _p, _p, _p]),
+    "vdb_ivf_centroid_dist": (_i, [_p, _i, _i, _p, _i, _p, _p]),
+    "vdb_ivf_probe": (_i, [_p, _i, _i, _i, _p, _p, _p, _p]),
+    "vdb_ivf_scan_workspace": (_sz, [_i, _i]),
+    "vdb_ivf_scan": (_i, [_p, _i, _p, _i, _p, _p, _p, _p, _i, _p, _p, _i, _p, _p, _p, _p, _sz, _p]),
+    "vdb_ivf_centroid_mean": (_i, [_p, _i, _p, _p, _i, _p, _p]),
     "vdb_merge_topk": (_i, [_p, _p, _i, _i, _i, _i, _p, _p, _p]),
 }
 
@@ -117,7 +122,7 @@ def require_cuda() -> torch.device:
 
 
 PROF_SLOTS = {"exact_f32": 0, "exact_tc": 1, "adc_scan": 2, "pq_encode": 3, "hnsw_search": 4, "rerank": 5,
-              "finalize": 6, "hnsw_insert": 7}
+              "finalize": 6, "hnsw_insert": 7, "ivf_scan": 8}
 
 
 def profile_enable(on: bool) -> None:

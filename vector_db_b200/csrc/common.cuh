@@ -39,7 +39,7 @@ void count_launch(int n);
 // Optional per-kernel timing (bench.py): when enabled, a ProfScope brackets ONE kernel launch with a
 // pair of CUDA events on the launching stream; vdb_profile_read() sums and clears a slot.
 enum ProfSlot { kProfExactF32 = 0, kProfExactTC = 1, kProfAdcScan = 2, kProfPqEncode = 3, kProfHnswSearch = 4,
-                kProfRerank = 5, kProfFinalize = 6, kProfHnswInsert = 7, kProfSlots = 8 };
+                kProfRerank = 5, kProfFinalize = 6, kProfHnswInsert = 7, kProfIvfScan = 8, kProfSlots = 9 };
 struct ProfScope {
     int slot; cudaStream_t st; bool on;
     ProfScope(int slot_, cudaStream_t st_);

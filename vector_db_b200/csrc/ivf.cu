@@ -1,0 +1,375 @@
+// IVF (inverted file) search on B200 -- SURVEY.md 8(f) rank 3.
+//
+// Reference: src/vector_db/indexing/ivf.py.  The index is K centroids + K inverted lists of node ids;
+// search (ivf.py:143-199) ranks the centroids by np.linalg.norm(centroids - query, axis=1), takes the
+// n_probe nearest (np.argsort), computes euclidean_vector_distance to every member of those lists,
+// sorts the candidates by distance with a STABLE sort (candidate enumeration order = probe rank, then
+// list position, breaks ties) and returns the first top_k.
+//
+// Here: lists are CSR (list_ptr[K+1], list_rows[] = row indices into the HBM-resident fp32 matrix, in
+// the reference's list order) and queries are processed in batches.
+//   ivf_centroid_dist_kernel  distances to the centroids in numpy's exact operation order (fp32
+//                             subtract, fp32 square, pairwise_sum over the row, sqrt) so that the probe
+//                             set -- index work -- is bit-identical to the reference's
+//   ivf_probe_kernel          n_probe smallest (distance, centroid) per query + candidate prefix sums
+//   ivf_scan_kernel           one CTA per (query, split of the query's flattened candidate sequence):
+//                             warp per row, 128-bit loads, the exact scan's L2 arithmetic (so that
+//                             n_probe == K reproduces vdb_exact_topk_f32 bit for bit), BlockSelect on
+//                             (distance, sequence number) keys = the reference's stable order
+//   ivf_merge_kernel          k best of the splits, sequence number -> row -> external id
+// HBM bound: algorithmic bytes per query = (sum of probed list lengths) * 4 D  (+ 4 per row index).
+#include "common.cuh"
+
+namespace vdb {
+
+constexpr int kIvfThreads = 256;
+constexpr int kIvfWarps = kIvfThreads / 32;
+constexpr int kIvfRowsPerWarp = 4;                         // rows in flight per warp iteration
+constexpr int kIvfBurst = kIvfWarps * kIvfRowsPerWarp;     // pushes between two compaction checks
+constexpr int kIvfMaxProbe = 8192;                         // probe prefix table lives in shared memory
+
+// numpy pairwise_sum (numpy/_core/src/umath/loops_utils.h.src) over v[t] = rn(d[t]^2), d[t] = rn(c[t] - q[t]):
+// n < 8 plain loop; n <= 128 eight strided accumulators combined as ((r0+r1)+(r2+r3))+((r4+r5)+(r6+r7)) then
+// the tail; larger n split at n/2 rounded down to a multiple of 8, recursively.
+__device__ __forceinline__ float np_sq_term(const float* __restrict__ c, const float* __restrict__ q, int t) {
+    const float d = __fsub_rn(__ldg(c + t), q[t]);
+    return __fmul_rn(d, d);
+}
+__device__ float np_block_sumsq(const float* __restrict__ c, const float* __restrict__ q, int n) {
+    if (n < 8) {
+        float r = 0.f;
+        for (int t = 0; t < n; ++t) r = __fadd_rn(r, np_sq_term(c, q, t));
+        return r;
+    }
+    float r[8];
+#pragma unroll
+    for (int t = 0; t < 8; ++t) r[t] = np_sq_term(c, q, t);
+    int i = 8;
+    for (; i < n - (n % 8); i += 8) {
+#pragma unroll
+        for (int t = 0; t < 8; ++t) r[t] = __fadd_rn(r[t], np_sq_term(c, q, i + t));
+    }
+    float res = __fadd_rn(__fadd_rn(__fadd_rn(r[0], r[1]), __fadd_rn(r[2], r[3])),
+                          __fadd_rn(__fadd_rn(r[4], r[5]), __fadd_rn(r[6], r[7])));
+    for (; i < n; ++i) res = __fadd_rn(res, np_sq_term(c, q, i));
+    return res;
+}
+// explicit-stack post-order walk of the recursion (depth <= 24 covers any D < 2^31)
+__device__ float np_pairwise_sumsq(const float* __restrict__ c, const float* __restrict__ q, int n) {
+    if (n <= 128) return np_block_sumsq(c, q, n);
+    int off[24], len[24], state[24];
+    float val[24];
+    int sp = 0, nv = 0;
+    off[0] = 0; len[0] = n; state[0] = 0; sp = 1;
+    while (sp > 0) {
+        const int t = sp - 1;
+        if (len[t] <= 128) {
+            val[nv++] = np_block_sumsq(c + off[t], q + off[t], len[t]);
+            --sp;
+        } else {
+            int n2 = len[t] / 2;
+            n2 -= n2 % 8;
+            if (state[t] == 0) { state[t] = 1; off[sp] = off[t]; len[sp] = n2; state[sp] = 0; ++sp; }
+            else if (state[t] == 1) { state[t] = 2; off[sp] = off[t] + n2; len[sp] = len[t] - n2; state[sp] = 0; ++sp; }
+            else { val[nv - 2] = __fadd_rn(val[nv - 2], val[nv - 1]); --nv; --sp; }
+        }
+    }
+    return val[0];
+}
+
+// out[q][c] = np.linalg.norm(centroids[c] - query[q])  (ivf.py:109, :170).  One thread per (query, centroid).
+__global__ void __launch_bounds__(128)
+ivf_centroid_dist_kernel(const float* __restrict__ q, int Q, int D, const float* __restrict__ cent, int K,
+                         float* __restrict__ out) {
+    extern __shared__ __align__(16) float ivf_qs[];
+    const int qi = blockIdx.y;
+    for (int t = threadIdx.x; t < D; t += blockDim.x) ivf_qs[t] = q[(size_t)qi * D + t];
+    __syncthreads();
+    for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < K; c += gridDim.x * blockDim.x)
+        out[(size_t)qi * K + c] = __fsqrt_rn(np_pairwise_sumsq(cent + (size_t)c * D, ivf_qs, D));
+}
+
+// np.argsort(centroid_distances)[:n_probe] (ivf.py:171), ties by centroid index; plus the prefix sums of the
+// probed lists' lengths: prefix[q][p] = candidates enumerated before probe p, prefix[q][n_probe] = total.
+__global__ void __launch_bounds__(256)
+ivf_probe_kernel(const float* __restrict__ cdist, int K, int n_probe, int C, const int32_t* __restrict__ list_ptr,
+                 int32_t* __restrict__ probes, int32_t* __restrict__ prefix) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    u64* buf = reinterpret_cast<u64*>(smem_raw);
+    __shared__ int cnt;
+    __shared__ u64 thr;
+    BlockSelect sel;
+    sel.init(buf, &cnt, &thr, C, n_probe, blockDim.x);
+    __syncthreads();
+    const float* src = cdist + (size_t)blockIdx.x * K;
+    for (int base = 0; base < K; base += blockDim.x) {
+        const int c = base + threadIdx.x;
+        if (c < K) sel.push(pack_key(src[c], (uint32_t)c));
+        sel.maybe_compact();
+    }
+    sel.finalize();
+    int32_t* pr = probes + (size_t)blockIdx.x * n_probe;
+    for (int p = threadIdx.x; p < n_probe; p += blockDim.x) pr[p] = (int32_t)key_index(buf[p]);
+    if (prefix && threadIdx.x == 0) {
+        int32_t* px = prefix + (size_t)blockIdx.x * (n_probe + 1);
+        int run = 0;
+        for (int p = 0; p < n_probe; ++p) {
+            px[p] = run;
+            const int c = (int)key_index(buf[p]);
+            run += list_ptr[c + 1] - list_ptr[c];
+        }
+        px[n_probe] = run;
+    }
+}
+
+__device__ __forceinline__ bool ivf_bit(const uint32_t* bm, int r) { return (bm[r >> 5] >> (r & 31)) & 1u; }
+
+// largest p with prefix[p] <= seq  (prefix is non-decreasing, prefix[0] = 0, seq < prefix[n])
+__device__ __forceinline__ int ivf_find_probe(const int32_t* prefix, int n, int seq) {
+    int lo = 0, hi = n;                 // invariant: prefix[lo] <= seq < prefix[hi]
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (prefix[mid] <= seq) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+
+// grid (S, Q).  CTA (s, q) evaluates candidates [s*chunk, (s+1)*chunk) of query q's flattened sequence
+// (probe rank major, list position minor -- the enumeration order of ivf.py:177-191).
+__global__ void __launch_bounds__(kIvfThreads)
+ivf_scan_kernel(const float* __restrict__ q, const float* __restrict__ db, int D, const int32_t* __restrict__ list_ptr,
+                const int32_t* __restrict__ list_rows, const int32_t* __restrict__ probes,
+                const int32_t* __restrict__ prefix_g, int n_probe, const uint32_t* __restrict__ alive, int k, int C,
+                int S, u64* __restrict__ partial) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    u64* buf = reinterpret_cast<u64*>(smem_raw);                       // C
+    float* qs = reinterpret_cast<float*>(buf + C);                     // D (padded to 4)
+    int32_t* prefix = reinterpret_cast<int32_t*>(qs + ((D + 3) & ~3)); // n_probe + 1
+    int32_t* pbase = prefix + n_probe + 1;                             // n_probe: list_ptr[probe]
+    __shared__ int cnt;
+    __shared__ u64 thr;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int qi = blockIdx.y, s = blockIdx.x;
+    for (int t = tid; t < D; t += kIvfThreads) qs[t] = q[(size_t)qi * D + t];
+    for (int p = tid; p <= n_probe; p += kIvfThreads) prefix[p] = prefix_g[(size_t)qi * (n_probe + 1) + p];
+    for (int p = tid; p < n_probe; p += kIvfThreads) pbase[p] = list_ptr[probes[(size_t)qi * n_probe + p]];
+    BlockSelect sel;
+    sel.init(buf, &cnt, &thr, C, k, kIvfBurst);
+    __syncthreads();
+    const int total = prefix[n_probe];
+    const int chunk = (total + S - 1) / S;
+    const int begin = min(total, s * chunk), end = min(total, begin + chunk);
+    const bool vec4 = (D & 3) == 0;
+    const int nchunk = D >> 2;
+
+    for (int base = begin; base < end; base += kIvfBurst) {
+        // lane j < kIvfRowsPerWarp decodes the warp's j-th candidate
+        int my_seq = base + warp * kIvfRowsPerWarp + lane, my_row = -1;
+        if (lane < kIvfRowsPerWarp && my_seq < end) {
+            const int p = ivf_find_probe(prefix, n_probe, my_seq);
+            const int r = __ldg(list_rows + pbase[p] + (my_seq - prefix[p]));
+            if (r >= 0 && (alive == nullptr || ivf_bit(alive, r))) my_row = r;      // deleted from storage: skipped (ivf.py:188-190)
+        }
+        int rows[kIvfRowsPerWarp];
+#pragma unroll
+        for (int j = 0; j < kIvfRowsPerWarp; ++j) rows[j] = __shfl_sync(0xffffffffu, my_row, j);
+        float acc[kIvfRowsPerWarp];
+#pragma unroll
+        for (int j = 0; j < kIvfRowsPerWarp; ++j) acc[j] = 0.f;
+        if (vec4) {
+            for (int c = lane; c < nchunk; c += 32) {
+                float4 x[kIvfRowsPerWarp];
+#pragma unroll
+                for (int j = 0; j < kIvfRowsPerWarp; ++j)
+                    x[j] = rows[j] >= 0 ? __ldg(reinterpret_cast<const float4*>(db + (size_t)rows[j] * D) + c)
+                                        : make_float4(0.f, 0.f, 0.f, 0.f);
+                const float4 qv = *reinterpret_cast<const float4*>(qs + 4 * c);
+#pragma unroll
+                for (int j = 0; j < kIvfRowsPerWarp; ++j) {
+                    const float d0 = qv.x - x[j].x, d1 = qv.y - x[j].y, d2 = qv.z - x[j].z, d3 = qv.w - x[j].w;
+                    acc[j] = fmaf(d0, d0, acc[j]); acc[j] = fmaf(d1, d1, acc[j]);
+                    acc[j] = fmaf(d2, d2, acc[j]); acc[j] = fmaf(d3, d3, acc[j]);
+                }
+            }
+        } else {
+            for (int t = lane; t < D; t += 32) {
+                const float qv = qs[t];
+#pragma unroll
+                for (int j = 0; j < kIvfRowsPerWarp; ++j) {
+                    const float d = qv - (rows[j] >= 0 ? __ldg(db + (size_t)rows[j] * D + t) : 0.f);
+                    acc[j] = fmaf(d, d, acc[j]);
+                }
+            }
+        }
+        float mine = 0.f;
+#pragma unroll
+        for (int j = 0; j < kIvfRowsPerWarp; ++j) {
+            const float v = warp_sum(acc[j]);
+            if (lane == j) mine = v;
+        }
+        if (my_row >= 0) sel.push(pack_key(sqrtf(mine), (uint32_t)my_seq));
+        sel.maybe_compact();
+    }
+    sel.finalize();
+    u64* dst = partial + ((size_t)qi * S + s) * k;
+    for (int i = tid; i < k; i += kIvfThreads) dst[i] = buf[i];
+}
+
+// k best (distance, sequence) keys of the S splits; sequence -> row -> external id.  One CTA per query.
+__global__ void __launch_bounds__(256)
+ivf_merge_kernel(const u64* __restrict__ partial, int L, int k, int C, const int32_t* __restrict__ list_ptr,
+                 const int32_t* __restrict__ list_rows, const int32_t* __restrict__ probes,
+                 const int32_t* __restrict__ prefix_g, int n_probe, const int64_t* __restrict__ ids,
+                 float* __restrict__ out_d, int64_t* __restrict__ out_i, int64_t* __restrict__ out_scanned) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    u64* buf = reinterpret_cast<u64*>(smem_raw);
+    __shared__ int cnt;
+    __shared__ u64 thr;
+    const int qi = blockIdx.x;
+    BlockSelect sel;
+    sel.init(buf, &cnt, &thr, C, k, blockDim.x);
+    __syncthreads();
+    const u64* src = partial + (size_t)qi * L;
+    for (int base = 0; base < L; base += blockDim.x) {
+        const int i = base + threadIdx.x;
+        if (i < L) {
+            const u64 key = src[i];
+            if (key != VDB_KEY_MAX) sel.push(key);
+        }
+        sel.maybe_compact();
+    }
+    sel.finalize();
+    const int32_t* prefix = prefix_g + (size_t)qi * (n_probe + 1);
+    for (int i = threadIdx.x; i < k; i += blockDim.x) {
+        const u64 key = buf[i];
+        const size_t o = (size_t)qi * k + i;
+        if (key == VDB_KEY_MAX) {
+            out_d[o] = INFINITY;
+            out_i[o] = -1;
+        } else {
+            const int seq = (int)key_index(key);
+            const int p = ivf_find_probe(prefix, n_probe, seq);
+            const int r = list_rows[list_ptr[probes[(size_t)qi * n_probe + p]] + (seq - prefix[p])];
+            out_d[o] = key_score(key);
+            out_i[o] = ids ? ids[r] : (int64_t)r;
+        }
+    }
+    if (out_scanned && threadIdx.x == 0) out_scanned[qi] = prefix[n_probe];
+}
+
+// K-means mean update over CSR member lists (rows sorted by label, ascending row inside a label -- a
+// deterministic summation order).  Empty cluster keeps its centroid (scipy kmeans2 missing='warn').
+__global__ void __launch_bounds__(128)
+ivf_centroid_mean_kernel(const float* __restrict__ x, int D, const int32_t* __restrict__ list_ptr,
+                         const int32_t* __restrict__ list_rows, float* __restrict__ cent) {
+    const int c = blockIdx.x;
+    const int b = list_ptr[c], e = list_ptr[c + 1];
+    if (e == b) return;
+    const float inv = 1.0f / (float)(e - b);
+    for (int t = threadIdx.x; t < D; t += blockDim.x) {
+        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+        int i = b;
+        for (; i + 4 <= e; i += 4) {
+            s0 += __ldg(x + (size_t)list_rows[i] * D + t);
+            s1 += __ldg(x + (size_t)list_rows[i + 1] * D + t);
+            s2 += __ldg(x + (size_t)list_rows[i + 2] * D + t);
+            s3 += __ldg(x + (size_t)list_rows[i + 3] * D + t);
+        }
+        for (; i < e; ++i) s0 += __ldg(x + (size_t)list_rows[i] * D + t);
+        cent[(size_t)c * D + t] = ((s0 + s1) + (s2 + s3)) * inv;
+    }
+}
+
+static size_t ivf_al(size_t v) { return (v + 255) & ~(size_t)255; }
+static int ivf_splits(int Q) {
+    int S = (8 * sm_count() + Q - 1) / (Q > 0 ? Q : 1);
+    if (S < 1) S = 1;
+    if (S > 32) S = 32;
+    return S;
+}
+
+}  // namespace vdb
+
+using namespace vdb;
+
+extern "C" {
+
+int vdb_ivf_centroid_dist(const float* q, int Q, int D, const float* centroids, int K, float* out, void* stream) {
+    VDB_REQUIRE(Q >= 0 && D > 0 && K > 0, VDB_ERR_INVALID, "vdb_ivf_centroid_dist: bad shape");
+    if (Q == 0) return VDB_OK;
+    VDB_REQUIRE(q && centroids && out, VDB_ERR_INVALID, "vdb_ivf_centroid_dist: null pointer");
+    VDB_REQUIRE(Q <= 65535, VDB_ERR_UNSUPPORTED, "Q=%d > 65535 per call", Q);
+    VDB_REQUIRE((size_t)D * 4 <= 48 * 1024, VDB_ERR_UNSUPPORTED, "D=%d too large", D);
+    int gx = (K + 127) / 128;
+    ivf_centroid_dist_kernel<<<dim3(gx, Q), 128, (size_t)D * 4, static_cast<cudaStream_t>(stream)>>>(q, Q, D, centroids, K, out);
+    count_launch(1);
+    VDB_CUDA(cudaGetLastError());
+    return VDB_OK;
+}
+
+int vdb_ivf_probe(const float* cdist, int Q, int K, int n_probe, const int32_t* list_ptr, int32_t* probes,
+                  int32_t* prefix, void* stream) {
+    VDB_REQUIRE(Q >= 0 && K > 0, VDB_ERR_INVALID, "vdb_ivf_probe: bad shape");
+    VDB_REQUIRE(n_probe >= 1 && n_probe <= K, VDB_ERR_INVALID, "n_probe must be between 1 and %d", K);
+    VDB_REQUIRE(n_probe <= kIvfMaxProbe, VDB_ERR_UNSUPPORTED, "n_probe=%d > %d", n_probe, kIvfMaxProbe);
+    if (Q == 0) return VDB_OK;
+    VDB_REQUIRE(cdist && probes && (!prefix || list_ptr), VDB_ERR_INVALID, "vdb_ivf_probe: null pointer");
+    const int C = select_capacity(n_probe, 256);
+    const size_t smem = (size_t)C * 8;
+    VDB_CUDA(cudaFuncSetAttribute(ivf_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    ivf_probe_kernel<<<Q, 256, smem, static_cast<cudaStream_t>(stream)>>>(cdist, K, n_probe, C, list_ptr, probes, prefix);
+    count_launch(1);
+    VDB_CUDA(cudaGetLastError());
+    return VDB_OK;
+}
+
+size_t vdb_ivf_scan_workspace(int Q, int k) {
+    if (Q <= 0 || k <= 0) return 0;
+    return ivf_al((size_t)Q * ivf_splits(Q) * k * 8) + 256;
+}
+
+int vdb_ivf_scan(const float* q, int Q, const float* db, int D, const int32_t* list_ptr, const int32_t* list_rows,
+                 const int32_t* probes, const int32_t* prefix, int n_probe, const uint32_t* alive, const int64_t* ids,
+                 int k, float* out_d, int64_t* out_i, int64_t* out_scanned, void* ws, size_t ws_bytes, void* stream) {
+    VDB_REQUIRE(Q >= 0 && D > 0 && k > 0 && n_probe >= 1, VDB_ERR_INVALID, "vdb_ivf_scan: bad shape");
+    VDB_REQUIRE(n_probe <= kIvfMaxProbe, VDB_ERR_UNSUPPORTED, "n_probe=%d > %d", n_probe, kIvfMaxProbe);
+    VDB_REQUIRE(k <= 2048, VDB_ERR_UNSUPPORTED, "k=%d > 2048", k);
+    VDB_REQUIRE(Q <= 65535, VDB_ERR_UNSUPPORTED, "Q=%d > 65535 per call", Q);
+    if (Q == 0) return VDB_OK;
+    VDB_REQUIRE(q && db && list_ptr && list_rows && probes && prefix && out_d && out_i, VDB_ERR_INVALID,
+                "vdb_ivf_scan: null pointer");
+    const int S = ivf_splits(Q);
+    const size_t need = (size_t)Q * S * k * 8;
+    VDB_REQUIRE(ws && ws_bytes >= need, VDB_ERR_WORKSPACE, "workspace %zu < %zu", ws_bytes, need);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    u64* partial = static_cast<u64*>(ws);
+    const int C = select_capacity(k, kIvfBurst);
+    const size_t smem = (size_t)C * 8 + (size_t)((D + 3) & ~3) * 4 + (size_t)(2 * n_probe + 1) * 4;
+    VDB_REQUIRE(smem <= (size_t)max_smem_optin() - 1024, VDB_ERR_UNSUPPORTED, "D=%d k=%d n_probe=%d do not fit shared memory",
+                D, k, n_probe);
+    VDB_CUDA(cudaFuncSetAttribute(ivf_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    {
+        ProfScope prof(kProfIvfScan, st);
+        ivf_scan_kernel<<<dim3(S, Q), kIvfThreads, smem, st>>>(q, db, D, list_ptr, list_rows, probes, prefix, n_probe,
+                                                              alive, k, C, S, partial);
+    }
+    const int C2 = select_capacity(k, 256);
+    VDB_CUDA(cudaFuncSetAttribute(ivf_merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(C2 * 8)));
+    ivf_merge_kernel<<<Q, 256, (size_t)C2 * 8, st>>>(partial, S * k, k, C2, list_ptr, list_rows, probes, prefix, n_probe,
+                                                     ids, out_d, out_i, out_scanned);
+    count_launch(2);
+    VDB_CUDA(cudaGetLastError());
+    return VDB_OK;
+}
+
+int vdb_ivf_centroid_mean(const float* x, int D, const int32_t* list_ptr, const int32_t* list_rows, int K,
+                          float* centroids, void* stream) {
+    VDB_REQUIRE(D > 0 && K > 0, VDB_ERR_INVALID, "vdb_ivf_centroid_mean: bad shape");
+    VDB_REQUIRE(x && list_ptr && list_rows && centroids, VDB_ERR_INVALID, "vdb_ivf_centroid_mean: null pointer");
+    ivf_centroid_mean_kernel<<<K, 128, 0, static_cast<cudaStream_t>(stream)>>>(x, D, list_ptr, list_rows, centroids);
+    count_launch(1);
+    VDB_CUDA(cudaGetLastError());
+    return VDB_OK;
+}
+
+}  // extern "C"

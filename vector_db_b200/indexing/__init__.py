@@ -1,4 +1,5 @@
 from .exact import ExactIndex
 from .hnsw import HNSW
+from .ivf import IvfIndex
 
-__all__ = ["HNSW", "ExactIndex"]
+__all__ = ["HNSW", "ExactIndex", "IvfIndex"]

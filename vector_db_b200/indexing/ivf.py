@@ -1,0 +1,313 @@
+"""IVF index with the reference's API (src/vector_db/indexing/ivf.py), lists and vectors in HBM.
+
+Same constructor, methods, attributes, error messages and pickle schema as the reference class
+(ivf.py:13-251): ``build_index / add / delete / search / get_cluster_size / get_cluster_stats /
+save_index / load_index`` and ``k, storage, index_file, centroids, inverted_lists``.  What changes is
+where the work happens:
+
+  * embeddings live in HBM (device_store.DeviceVectors, row = insertion order) and the inverted lists
+    are a CSR pair ``list_ptr`` int32 [k+1] / ``list_rows`` int32 [n] of ROW indices, each list in the
+    reference's append order; ``inverted_lists`` (lists of node ids) is materialised on demand;
+  * ``search`` ranks the centroids with numpy's exact arithmetic (``vdb_ivf_centroid_dist``), takes the
+    ``n_probe`` nearest and scans their lists on the GPU (``vdb_ivf_scan``) in the reference's stable
+    candidate order; ``search_batch`` is the many-query form;
+  * ``build_index`` trains with exactly 100 Lloyd rounds like ``kmeans2(iter=100, minit='points')``
+    (ivf.py:75): initial centroids drawn with the same global-numpy-RNG call scipy makes, assignment by
+    the exact GPU scan, mean update by ``vdb_ivf_centroid_mean``; the lists come from the assignment
+    made BEFORE the last update, as scipy returns it.  Values are parity-unpinned.
+"""
+from __future__ import annotations
+
+import pickle
+import threading
+from pathlib import Path
+from typing import Dict, List, Optional, Sequence, Tuple, Union
+
+import numpy as np
+import torch
+
+from .. import _lib, ops
+from ..device_store import DeviceVectors
+from ..storage import InMemoryNodeStorage, NodeStorage
+from ..types import Node
+
+_ASSIGN_CHUNK = 65536      # rows per assignment call during training
+
+
+class IvfIndex:
+    def __init__(self, k: int, storage: Optional[NodeStorage] = None, index_file: Optional[Union[str, Path]] = None,
+                 device=None):
+        if k <= 0:
+            raise ValueError("k-means parameter should be positive")
+        self.k = k
+        self.storage = storage or InMemoryNodeStorage()
+        self.index_file = Path(index_file) if index_file else None
+        self.centroids: Optional[np.ndarray] = None
+        self._device = _lib.require_cuda() if device is None else torch.device(device)
+        self._lock = threading.RLock()
+        self._vectors: Optional[DeviceVectors] = None
+        self._centroids_dev: Optional[torch.Tensor] = None
+        self._lists: Optional[List[List[int]]] = []      # host lists of ids; None = not materialised from the CSR
+        self._list_ptr: Optional[torch.Tensor] = None    # device CSR, valid when not _csr_dirty
+        self._list_rows: Optional[torch.Tensor] = None
+        self._csr_dirty = True
+        self.last_scanned: Optional[np.ndarray] = None   # candidates enumerated per query by the last search
+        if self.index_file and self.index_file.exists():
+            self.load_index()
+
+    # ------------------------------------------------------------------ lists <-> CSR
+    @property
+    def inverted_lists(self) -> List[List[int]]:
+        """cluster_id -> list of node ids (ivf.py:42), materialised from the device CSR when needed."""
+        if self._lists is None:
+            ptr = self._list_ptr.cpu().numpy()
+            ids = self._vectors.ids[self._list_rows.long()].cpu().numpy()
+            self._lists = [ids[ptr[c]:ptr[c + 1]].tolist() for c in range(len(ptr) - 1)]
+        return self._lists
+
+    @inverted_lists.setter
+    def inverted_lists(self, value: List[List[int]]) -> None:
+        self._lists = value
+        self._csr_dirty = True
+
+    def _csr(self) -> Tuple[torch.Tensor, torch.Tensor]:
+        if self._csr_dirty:
+            lists = self._lists
+            row_of = self._vectors.id_to_row if self._vectors is not None else {}
+            ptr = np.zeros(len(lists) + 1, dtype=np.int64)
+            rows: List[int] = []
+            for c, lst in enumerate(lists):
+                rows.extend(r for r in (row_of.get(int(i)) for i in lst) if r is not None)   # ivf.py:188-190
+                ptr[c + 1] = len(rows)
+            self._list_ptr = torch.from_numpy(ptr.astype(np.int32)).to(self._device)
+            self._list_rows = torch.tensor(rows if rows else [0], dtype=torch.int32, device=self._device)
+            self._csr_dirty = False
+        return self._list_ptr, self._list_rows
+
+    def _set_centroids(self, cent: torch.Tensor) -> None:
+        self._centroids_dev = cent.contiguous()
+        self.centroids = cent.cpu().numpy()
+
+    # ------------------------------------------------------------------ build
+    def build_index(self, nodes: List[Node]) -> None:
+        """ivf.py:49-85: store the nodes, cluster their embeddings, fill the inverted lists."""
+        if not nodes:
+            raise ValueError("Cannot build index with empty node list")
+        for node in nodes:
+            self.storage.save(node)
+        embeddings = np.array([node.embedding for node in nodes])
+        ids = [node.id for node in nodes]
+        if embeddings.ndim != 2:
+            raise ValueError(f"embeddings must be 2D array, got {embeddings.ndim}D")
+        if embeddings.shape[0] < self.k:
+            raise ValueError(f"Need at least {self.k} vectors for {self.k} clusters")
+        self.build_from_arrays(ids, embeddings)
+        if self.index_file:
+            self.save_index()
+
+    def build_from_arrays(self, ids: Sequence[int], vectors: np.ndarray, iters: int = 100,
+                          init_rows: Optional[np.ndarray] = None) -> None:
+        """Bulk form of build_index: no per-node storage writes.  ``init_rows`` replaces the random
+        'points' initialisation (rows of ``vectors`` used as the initial centroids)."""
+        with self._lock:
+            X = np.ascontiguousarray(vectors, dtype=np.float32)
+            n, dim = X.shape
+            if n < self.k:
+                raise ValueError(f"Need at least {self.k} vectors for {self.k} clusters")
+            self._vectors = DeviceVectors(dim, self._device, capacity=n)
+            rows = self._vectors.append(ids, X)
+            row_t = torch.from_numpy(np.asarray(rows, dtype=np.int64)).to(self._device)
+            identity = np.array_equal(rows, np.arange(n))          # no id appeared twice
+            Xd = self._vectors.vecs[:n] if identity else self._vectors.vecs.index_select(0, row_t)
+            if init_rows is None:
+                # scipy.cluster.vq._kpoints: rng.choice(n, size=k, replace=False) on the global numpy RandomState
+                init_rows = np.random.mtrand._rand.choice(n, size=int(self.k), replace=False)
+            cent = Xd.index_select(0, torch.from_numpy(np.asarray(init_rows, dtype=np.int64)).to(self._device)).clone()
+            labels = None
+            for _ in range(iters):
+                labels = self._assign(Xd, cent)
+                ptr, order = self._labels_to_csr(labels)
+                ops.ivf_centroid_mean(Xd, ptr, order, cent)
+            if labels is None:
+                labels = self._assign(Xd, cent)
+            ptr, order = self._labels_to_csr(labels)          # the assignment made before the last update
+            self._list_ptr = ptr
+            self._list_rows = order if identity else row_t.index_select(0, order.long()).to(torch.int32)
+            self._lists = None
+            self._csr_dirty = False
+            self._set_centroids(cent)
+
+    def _assign(self, X: torch.Tensor, cent: torch.Tensor) -> torch.Tensor:
+        """Nearest centroid of every row -> int32 labels (exact fp32 distances, first minimum wins)."""
+        n, dim = X.shape
+        K = cent.shape[0]
+        out = torch.empty((n,), dtype=torch.int32, device=X.device)
+        use_tc = ops.tc_supported(min(n, _ASSIGN_CHUNK), K, dim, 1, "l2")
+        if use_tc:
+            mirror, sq = ops.tc_prepare_rows(cent, "l2")
+            max_norm = float(sq.max().sqrt().item())
+        for s in range(0, n, _ASSIGN_CHUNK):
+            e = min(n, s + _ASSIGN_CHUNK)
+            if use_tc and ops.tc_supported(e - s, K, dim, 1, "l2"):
+                _, i = ops.exact_topk_tc(X[s:e], cent, mirror, max_norm, 1, "l2")
+            else:
+                _, i = ops.exact_topk_f32(X[s:e], cent, 1, "l2")
+            out[s:e] = i[:, 0].to(torch.int32)
+        return out
+
+    def _labels_to_csr(self, labels: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+        order = torch.sort(labels.long(), stable=True).indices.to(torch.int32)      # ascending row inside a label
+        counts = torch.bincount(labels.long(), minlength=self.k)
+        ptr = torch.zeros((self.k + 1,), dtype=torch.int32, device=labels.device)
+        ptr[1:] = torch.cumsum(counts, 0).to(torch.int32)
+        return ptr, order
+
+    # ------------------------------------------------------------------ mutation
+    def add(self, node: Node) -> None:
+        """ivf.py:87-117."""
+        if self.centroids is None:
+            raise ValueError("Index must be built before adding nodes")
+        embedding = node.embedding
+        if embedding.ndim != 1:
+            raise ValueError("embedding must be 1D array")
+        if embedding.shape[0] != self.centroids.shape[1]:
+            raise ValueError(
+                f"embedding dimension {embedding.shape[0]} doesn't match "
+                f"centroid dimension {self.centroids.shape[1]}"
+            )
+        self.storage.save(node)
+        with self._lock:
+            if self._vectors is None:
+                self._vectors = DeviceVectors(self.centroids.shape[1], self._device)
+            self._vectors.append([node.id], np.asarray(embedding, dtype=np.float32)[None, :])
+            q = torch.from_numpy(np.ascontiguousarray(embedding, dtype=np.float32)[None, :]).to(self._device)
+            probes, _ = ops.ivf_probe(ops.ivf_centroid_dist(q, self._centroids_dev), 1)
+            self.inverted_lists[int(probes[0, 0].item())].append(node.id)
+            self._csr_dirty = True
+        if self.index_file:
+            self.save_index()
+
+    def delete(self, node_id: int) -> None:
+        """ivf.py:119-137."""
+        with self._lock:
+            for cluster_list in self.inverted_lists:
+                if node_id in cluster_list:
+                    cluster_list.remove(node_id)
+            self._csr_dirty = True
+            if self._vectors is not None:
+                self._vectors.mark_dead(node_id)
+        if hasattr(self.storage, "delete"):
+            self.storage.delete(node_id)
+        if self.index_file:
+            self.save_index()
+
+    # ------------------------------------------------------------------ search
+    def search_batch(self, queries: np.ndarray, n_probe: int, top_k: int) -> Tuple[np.ndarray, np.ndarray]:
+        """Many queries at once: (dist f32 [Q,top_k], ids i64 [Q,top_k]), padded with (+inf, -1)."""
+        if self.centroids is None:
+            raise ValueError("Index must be built before searching")
+        queries = np.ascontiguousarray(queries, dtype=np.float32)
+        if queries.ndim != 2:
+            raise ValueError("queries must be 2D array")
+        if queries.shape[1] != self.centroids.shape[1]:
+            raise ValueError(
+                f"query dimension {queries.shape[1]} doesn't match "
+                f"centroid dimension {self.centroids.shape[1]}"
+            )
+        if n_probe <= 0 or n_probe > self.k:
+            raise ValueError(f"n_probe must be between 1 and {self.k}")
+        with self._lock:
+            q = torch.from_numpy(queries).to(self._device)
+            d, i, scanned = self.search_device(q, n_probe, top_k)
+            self.last_scanned = scanned.cpu().numpy()
+            return d.cpu().numpy(), i.cpu().numpy()
+
+    def search_device(self, q: torch.Tensor, n_probe: int, top_k: int):
+        """Device in / device out: (dist, ids, candidates enumerated per query)."""
+        ptr, rows = self._csr()
+        vec = self._vectors
+        cdist = ops.ivf_centroid_dist(q, self._centroids_dev)
+        probes, prefix = ops.ivf_probe(cdist, n_probe, ptr)
+        alive = vec.alive if vec.n_dead else None
+        return ops.ivf_scan(q, vec.vecs, ptr, rows, probes, prefix, top_k, alive=alive, ids=vec.ids, return_scanned=True)
+
+    def search(self, query: np.ndarray, n_probe: int, top_k: int) -> List[Tuple[Node, float]]:
+        """ivf.py:139-199: ``[(Node, np.float32 distance)]`` sorted by distance."""
+        if self.centroids is None:
+            raise ValueError("Index must be built before searching")
+        if query.ndim != 1:
+            raise ValueError("query must be 1D array")
+        if query.shape[0] != self.centroids.shape[1]:
+            raise ValueError(
+                f"query dimension {query.shape[0]} doesn't match "
+                f"centroid dimension {self.centroids.shape[1]}"
+            )
+        if n_probe <= 0 or n_probe > self.k:
+            raise ValueError(f"n_probe must be between 1 and {self.k}")
+        if top_k <= 0:
+            return []
+        d, i = self.search_batch(np.asarray(query)[None, :], n_probe, top_k)
+        results = []
+        for dist, node_id in zip(d[0], i[0]):
+            if node_id < 0:
+                break
+            node = self.storage.get(int(node_id))
+            if node:
+                results.append((node, np.float32(dist)))
+        return results
+
+    # ------------------------------------------------------------------ stats (ivf.py:201-216)
+    def get_cluster_size(self, cluster_id: int) -> int:
+        if cluster_id < 0 or cluster_id >= self.k:
+            raise ValueError(f"cluster_id must be between 0 and {self.k - 1}")
+        return len(self.inverted_lists[cluster_id])
+
+    def get_cluster_stats(self) -> dict:
+        sizes = [len(lst) for lst in self.inverted_lists]
+        return {
+            "min_size": min(sizes),
+            "max_size": max(sizes),
+            "avg_size": sum(sizes) / len(sizes) if sizes else 0,
+            "total_vectors": sum(sizes),
+        }
+
+    # ------------------------------------------------------------------ persistence (ivf.py:218-251)
+    def save_index(self) -> None:
+        if self.index_file is None:
+            return
+        index_data = {"k": self.k, "centroids": self.centroids, "inverted_lists": self.inverted_lists}
+        with open(self.index_file, "wb") as f:
+            pickle.dump(index_data, f)
+
+    def load_index(self) -> None:
+        if self.index_file is None or not self.index_file.exists():
+            return
+        with open(self.index_file, "rb") as f:
+            index_data = pickle.load(f)
+        self.load_state(index_data)
+
+    def load_state(self, index_data: dict, vectors: Optional[Dict[int, np.ndarray]] = None) -> None:
+        """Import an index in the reference's pickle schema; embeddings come from ``vectors`` or storage."""
+        with self._lock:
+            self.k = index_data["k"]
+            cent = index_data["centroids"]
+            self._lists = [list(lst) for lst in index_data["inverted_lists"]]
+            self._csr_dirty = True
+            if cent is None:
+                self.centroids, self._centroids_dev, self._vectors = None, None, None
+                return
+            cent = np.ascontiguousarray(cent, dtype=np.float32)
+            self._centroids_dev = torch.from_numpy(cent).to(self._device)
+            self.centroids = index_data["centroids"]
+            ids = [i for lst in self._lists for i in lst]
+            get = (lambda i: vectors[i]) if vectors is not None else self.storage.get_embedding
+            self._vectors = DeviceVectors(cent.shape[1], self._device, capacity=max(len(ids), 1))
+            keep, rows = [], []
+            for i in ids:
+                try:
+                    rows.append(np.asarray(get(i), dtype=np.float32))
+                    keep.append(i)
+                except KeyError:
+                    continue
+            if keep:
+                self._vectors.append(keep, np.stack(rows))

@@ -153,6 +153,61 @@ def pq_adc_topk(codes: torch.Tensor, lut: torch.Tensor, R: int, ids: Optional[to
     return out_d, out_i
 
 
+def ivf_centroid_dist(q: torch.Tensor, centroids: torch.Tensor) -> torch.Tensor:
+    """np.linalg.norm(centroids - q_i, axis=1) for every query, numpy operation order -> f32 [Q,K]."""
+    q = _f32(q, "q")
+    centroids = _f32(centroids, "centroids")
+    Q, D = q.shape
+    K = centroids.shape[0]
+    out = torch.empty((Q, K), dtype=torch.float32, device=q.device)
+    lib = load()
+    for s in range(0, Q, 32768):
+        e = min(Q, s + 32768)
+        check(lib.vdb_ivf_centroid_dist(ptr(q[s:e]), e - s, D, ptr(centroids), K, ptr(out[s:e]), _lib.stream_ptr(q.device)))
+    return out
+
+
+def ivf_probe(cdist: torch.Tensor, n_probe: int, list_ptr: Optional[torch.Tensor] = None):
+    """n_probe nearest centroids per query by (distance, centroid index) -> probes i32 [Q,n_probe] and, when
+    list_ptr is given, the candidate prefix sums i32 [Q,n_probe+1]."""
+    Q, K = cdist.shape
+    probes = torch.empty((Q, n_probe), dtype=torch.int32, device=cdist.device)
+    prefix = torch.empty((Q, n_probe + 1), dtype=torch.int32, device=cdist.device) if list_ptr is not None else None
+    check(load().vdb_ivf_probe(ptr(cdist), Q, K, n_probe, ptr(list_ptr), ptr(probes), ptr(prefix),
+                               _lib.stream_ptr(cdist.device)))
+    return probes, prefix
+
+
+def ivf_scan(q: torch.Tensor, db: torch.Tensor, list_ptr: torch.Tensor, list_rows: torch.Tensor, probes: torch.Tensor,
+             prefix: torch.Tensor, k: int, alive: Optional[torch.Tensor] = None, ids: Optional[torch.Tensor] = None,
+             return_scanned: bool = False):
+    """Distances to every member of the probed lists -> (d f32 [Q,k], id i64 [Q,k]) in the reference's stable
+    candidate order (ivf.py:177-193)."""
+    q = _f32(q, "q")
+    Q, D = q.shape
+    n_probe = probes.shape[1]
+    dev = q.device
+    out_d = torch.empty((Q, k), dtype=torch.float32, device=dev)
+    out_i = torch.empty((Q, k), dtype=torch.int64, device=dev)
+    scanned = torch.empty((Q,), dtype=torch.int64, device=dev) if return_scanned else None
+    lib = load()
+    for s in range(0, Q, 32768):
+        e = min(Q, s + 32768)
+        ws = _ws("ivf", lib.vdb_ivf_scan_workspace(e - s, k), dev)
+        check(lib.vdb_ivf_scan(ptr(q[s:e]), e - s, ptr(db), D, ptr(list_ptr), ptr(list_rows), ptr(probes[s:e]),
+                               ptr(prefix[s:e]), n_probe, ptr(alive), ptr(ids), k, ptr(out_d[s:e]), ptr(out_i[s:e]),
+                               ptr(scanned[s:e]) if scanned is not None else None, ptr(ws), ws.numel(),
+                               _lib.stream_ptr(dev)))
+    return (out_d, out_i, scanned) if return_scanned else (out_d, out_i)
+
+
+def ivf_centroid_mean(x: torch.Tensor, list_ptr: torch.Tensor, list_rows: torch.Tensor, centroids: torch.Tensor) -> None:
+    """Lloyd mean update in place: centroid c = mean of rows list_rows[list_ptr[c]:list_ptr[c+1]] (empty: unchanged)."""
+    K, D = centroids.shape
+    check(load().vdb_ivf_centroid_mean(ptr(x), D, ptr(list_ptr), ptr(list_rows), K, ptr(centroids),
+                                       _lib.stream_ptr(x.device)))
+
+
 def merge_topk(d: torch.Tensor, i: torch.Tensor, descending: bool = False):
     """d,i [L,Q,k] (per-shard sorted lists) -> merged (d [Q,k], i [Q,k])."""
     L, Q, k = d.shape
