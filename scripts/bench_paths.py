@@ -7,6 +7,7 @@ MEASURED_PEAKS.json (algorithmic bytes as defined in DESIGN.md).
     python scripts/bench_paths.py adc  [N] [Q] [m] [R]     # default 10_000_000 1024 48 10
     python scripts/bench_paths.py encode [N] [m]           # default 10_000_000 48   (D = 8 m)
     python scripts/bench_paths.py hnsw [N] [D] [M] [ef] [Q] # default 200_000 768 32 128 10_000
+    python scripts/bench_paths.py ivf [N] [D] [K] [Q] [iters] # default 1_000_000 384 1024 4096 10 (clustered rows)
 """
 import json
 import os
@@ -145,7 +146,59 @@ def bench_hnsw(N=200_000, D=768, M=32, ef=128, Q=10_000):
     print(json.dumps(line), flush=True)
 
 
+def bench_ivf(N=1_000_000, D=384, K=1024, Q=4096, iters=10):
+    """IVF on clustered rows: train, then batched search at several n_probe with recall@10
+    against the exact scan; roofline = bytes of the probed lists' rows / list-scan kernel time."""
+    from vector_db_b200.indexing import ExactIndex, IvfIndex
+    g = torch.Generator(device=dev).manual_seed(1234)
+    centres = torch.randn((1024, D), device=dev, generator=g)
+    sigma = 0.15 * centres.norm(dim=1).mean() / (D ** 0.5)
+    X = centres[torch.randint(0, 1024, (N,), device=dev, generator=g)] + sigma * torch.randn((N, D), device=dev, generator=g)
+    Qd = centres[torch.randint(0, 1024, (Q,), device=dev, generator=g)] + sigma * torch.randn((Q, D), device=dev, generator=g)
+    idx = IvfIndex(k=K)
+    Xh = X.cpu().numpy()
+    t0 = time.perf_counter()
+    idx.build_from_arrays(range(N), Xh, iters=iters, init_rows=np.random.default_rng(777).choice(N, K, replace=False))
+    torch.cuda.synchronize()
+    build_s = time.perf_counter() - t0
+    ex = ExactIndex(D, "l2")
+    ex.add_device(torch.arange(N, device=dev), X)
+    _, Iex = ex.search_device(Qd, 10)
+    truth = [set(r) for r in Iex.cpu().tolist()]
+    sizes = [len(l) for l in idx.inverted_lists]
+    rows = []
+
+    def ev_time(fn, iters=5):
+        fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            out = fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return out, e0.elapsed_time(e1) / iters
+
+    cd, cdist_ms = ev_time(lambda: ops.ivf_centroid_dist(Qd, idx._centroids_dev))
+    _, probe_ms = ev_time(lambda: ops.ivf_probe(cd, 16, idx._csr()[0]))
+    for n_probe in (1, 4, 16, 64):
+        if n_probe > K:
+            break
+        (d, i, scanned), k_ms, step_ms = _time_slot("ivf_scan", lambda: idx.search_device(Qd, n_probe, 10), iters=5, warm=2)
+        got = i.cpu().tolist()
+        recall = sum(len(truth[j] & set(got[j])) for j in range(Q)) / (Q * 10)
+        alg = float(scanned.sum().item()) * (D * 4 + 4)
+        rows.append({"n_probe": n_probe, "recall_at_10": round(recall, 4), "scan_kernel_ms": round(k_ms, 3),
+                     "step_ms": round(step_ms, 3), "qps": round(Q / (step_ms * 1e-3), 1),
+                     "rows_scanned_per_query": float(scanned.float().mean().item()),
+                     "roofline": {"bound": "hbm", "achieved": alg / (k_ms * 1e-3) / 1e9, "peak": HBM, "unit": "GB/s",
+                                  "frac": alg / (k_ms * 1e-3) / 1e9 / HBM, "algorithmic_bytes": alg}})
+    print(json.dumps({"path": "ivf_search", "N": N, "D": D, "K": K, "Q": Q, "train_iters": iters, "build_s": build_s,
+                      "centroid_dist_ms": cdist_ms, "probe16_ms": probe_ms,
+                      "list_size_min_mean_max": [min(sizes), sum(sizes) / len(sizes), max(sizes)], "rows": rows}), flush=True)
+
+
 if __name__ == "__main__":
     what = sys.argv[1] if len(sys.argv) > 1 else "adc"
     args = [int(a) for a in sys.argv[2:]]
-    {"adc": bench_adc, "encode": bench_encode, "hnsw": bench_hnsw}[what](*args)
+    {"adc": bench_adc, "encode": bench_encode, "hnsw": bench_hnsw, "ivf": bench_ivf}[what](*args)

@@ -30,63 +30,138 @@ constexpr int kIvfMaxProbe = 8192;                         // probe prefix table
 
 // numpy pairwise_sum (numpy/_core/src/umath/loops_utils.h.src) over v[t] = rn(d[t]^2), d[t] = rn(c[t] - q[t]):
 // n < 8 plain loop; n <= 128 eight strided accumulators combined as ((r0+r1)+(r2+r3))+((r4+r5)+(r6+r7)) then
-// the tail; larger n split at n/2 rounded down to a multiple of 8, recursively.
-__device__ __forceinline__ float np_sq_term(const float* __restrict__ c, const float* __restrict__ q, int t) {
-    const float d = __fsub_rn(__ldg(c + t), q[t]);
-    return __fmul_rn(d, d);
-}
-__device__ float np_block_sumsq(const float* __restrict__ c, const float* __restrict__ q, int n) {
-    if (n < 8) {
-        float r = 0.f;
-        for (int t = 0; t < n; ++t) r = __fadd_rn(r, np_sq_term(c, q, t));
-        return r;
-    }
-    float r[8];
-#pragma unroll
-    for (int t = 0; t < 8; ++t) r[t] = np_sq_term(c, q, t);
-    int i = 8;
-    for (; i < n - (n % 8); i += 8) {
-#pragma unroll
-        for (int t = 0; t < 8; ++t) r[t] = __fadd_rn(r[t], np_sq_term(c, q, i + t));
-    }
-    float res = __fadd_rn(__fadd_rn(__fadd_rn(r[0], r[1]), __fadd_rn(r[2], r[3])),
-                          __fadd_rn(__fadd_rn(r[4], r[5]), __fadd_rn(r[6], r[7])));
-    for (; i < n; ++i) res = __fadd_rn(res, np_sq_term(c, q, i));
-    return res;
-}
-// explicit-stack post-order walk of the recursion (depth <= 24 covers any D < 2^31)
-__device__ float np_pairwise_sumsq(const float* __restrict__ c, const float* __restrict__ q, int n) {
-    if (n <= 128) return np_block_sumsq(c, q, n);
-    int off[24], len[24], state[24];
-    float val[24];
-    int sp = 0, nv = 0;
-    off[0] = 0; len[0] = n; state[0] = 0; sp = 1;
+// the tail; larger n split at n/2 rounded down to a multiple of 8, recursively.  The recursion depends on n
+// only, so it is flattened once per CTA into its leaf blocks (start, length <= 128, all starts multiples of
+// 8) in visiting order plus, per leaf, the number of pairwise additions that follow it in post-order.
+constexpr int kIvfCdThreads = 128;      // centroids per CTA
+constexpr int kIvfCdQ = 4;              // queries per thread: one centroid element feeds four distances
+constexpr int kIvfCdChunk = 32;         // columns per shared-memory tile
+constexpr int kIvfCdMaxLeaves = 512;
+
+struct IvfLeaves {
+    int n;
+    short start[kIvfCdMaxLeaves];       // in units of 8 columns
+    short len[kIvfCdMaxLeaves];
+    unsigned char comb[kIvfCdMaxLeaves];
+};
+
+__device__ void ivf_flatten_leaves(IvfLeaves* L, int n) {
+    int off[32], len[32], state[32];
+    int sp = 1;
+    off[0] = 0; len[0] = n; state[0] = 0;
+    L->n = 0;
     while (sp > 0) {
         const int t = sp - 1;
         if (len[t] <= 128) {
-            val[nv++] = np_block_sumsq(c + off[t], q + off[t], len[t]);
+            L->start[L->n] = (short)(off[t] >> 3);
+            L->len[L->n] = (short)len[t];
+            L->comb[L->n] = 0;
+            ++L->n;
             --sp;
         } else {
             int n2 = len[t] / 2;
             n2 -= n2 % 8;
             if (state[t] == 0) { state[t] = 1; off[sp] = off[t]; len[sp] = n2; state[sp] = 0; ++sp; }
             else if (state[t] == 1) { state[t] = 2; off[sp] = off[t] + n2; len[sp] = len[t] - n2; state[sp] = 0; ++sp; }
-            else { val[nv - 2] = __fadd_rn(val[nv - 2], val[nv - 1]); --nv; --sp; }
+            else { ++L->comb[L->n - 1]; --sp; }
         }
     }
-    return val[0];
 }
 
-// out[q][c] = np.linalg.norm(centroids[c] - query[q])  (ivf.py:109, :170).  One thread per (query, centroid).
-__global__ void __launch_bounds__(128)
+// out[q][c] = np.linalg.norm(centroids[c] - query[q])  (ivf.py:109, :170).  CTA = 128 centroids x kIvfCdQ queries;
+// centroid columns go through a [128][33] shared tile (coalesced loads, conflict-free per-thread row reads).
+__global__ void __launch_bounds__(kIvfCdThreads)
 ivf_centroid_dist_kernel(const float* __restrict__ q, int Q, int D, const float* __restrict__ cent, int K,
                          float* __restrict__ out) {
-    extern __shared__ __align__(16) float ivf_qs[];
-    const int qi = blockIdx.y;
-    for (int t = threadIdx.x; t < D; t += blockDim.x) ivf_qs[t] = q[(size_t)qi * D + t];
+    extern __shared__ __align__(16) float ivf_smem[];
+    float* qs = ivf_smem;                                              // kIvfCdQ * D
+    float* tile = qs + (size_t)kIvfCdQ * D;                            // 128 * 33
+    __shared__ IvfLeaves leaves;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int c0 = blockIdx.x * kIvfCdThreads, q0 = blockIdx.y * kIvfCdQ;
+    const int nq = min(kIvfCdQ, Q - q0);
+    for (int i = tid; i < kIvfCdQ * D; i += kIvfCdThreads) {
+        const int g = i / D;
+        qs[i] = g < nq ? q[(size_t)(q0 + g) * D + (i - g * D)] : 0.f;
+    }
+    if (tid == 0) ivf_flatten_leaves(&leaves, D);
+    int chunk_base = -kIvfCdChunk;                                     // no tile loaded yet
+    auto need = [&](int t) {                                          // CTA-uniform: make column t resident
+        if (t >= chunk_base + kIvfCdChunk) {
+            __syncthreads();
+            chunk_base = t & ~(kIvfCdChunk - 1);
+            for (int r = warp; r < kIvfCdThreads; r += kIvfCdThreads / 32) {
+                const int c = c0 + r, col = chunk_base + lane;
+                tile[r * (kIvfCdChunk + 1) + lane] = (c < K && col < D) ? __ldg(cent + (size_t)c * D + col) : 0.f;
+            }
+            __syncthreads();
+        }
+    };
     __syncthreads();
-    for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < K; c += gridDim.x * blockDim.x)
-        out[(size_t)qi * K + c] = __fsqrt_rn(np_pairwise_sumsq(cent + (size_t)c * D, ivf_qs, D));
+    const float* mine = tile + tid * (kIvfCdChunk + 1);
+    float val[kIvfCdQ][12];                                            // post-order value stack (depth <= log2(D/64)+1)
+    int nv = 0;
+    for (int l = 0; l < leaves.n; ++l) {
+        const int s = (int)leaves.start[l] << 3, n = leaves.len[l];
+        float res[kIvfCdQ];
+        if (n < 8) {
+#pragma unroll
+            for (int g = 0; g < kIvfCdQ; ++g) res[g] = 0.f;
+            for (int t = 0; t < n; ++t) {
+                need(s + t);
+                const float cv = mine[s + t - chunk_base];
+#pragma unroll
+                for (int g = 0; g < kIvfCdQ; ++g) {
+                    const float d = __fsub_rn(cv, qs[g * D + s + t]);
+                    res[g] = __fadd_rn(res[g], __fmul_rn(d, d));
+                }
+            }
+        } else {
+            float r[kIvfCdQ][8];
+            const int main_end = n - (n % 8);
+            for (int i = 0; i < main_end; i += 8) {
+                need(s + i);
+                const float* cp = mine + (s + i - chunk_base);
+#pragma unroll
+                for (int t = 0; t < 8; ++t) {
+                    const float cv = cp[t];
+#pragma unroll
+                    for (int g = 0; g < kIvfCdQ; ++g) {
+                        const float d = __fsub_rn(cv, qs[g * D + s + i + t]);
+                        const float v = __fmul_rn(d, d);
+                        r[g][t] = i == 0 ? v : __fadd_rn(r[g][t], v);
+                    }
+                }
+            }
+#pragma unroll
+            for (int g = 0; g < kIvfCdQ; ++g)
+                res[g] = __fadd_rn(__fadd_rn(__fadd_rn(r[g][0], r[g][1]), __fadd_rn(r[g][2], r[g][3])),
+                                   __fadd_rn(__fadd_rn(r[g][4], r[g][5]), __fadd_rn(r[g][6], r[g][7])));
+            for (int i = main_end; i < n; ++i) {
+                need(s + i);
+                const float cv = mine[s + i - chunk_base];
+#pragma unroll
+                for (int g = 0; g < kIvfCdQ; ++g) {
+                    const float d = __fsub_rn(cv, qs[g * D + s + i]);
+                    res[g] = __fadd_rn(res[g], __fmul_rn(d, d));
+                }
+            }
+        }
+#pragma unroll
+        for (int g = 0; g < kIvfCdQ; ++g) val[g][nv] = res[g];
+        ++nv;
+        for (int k = 0; k < (int)leaves.comb[l]; ++k) {
+#pragma unroll
+            for (int g = 0; g < kIvfCdQ; ++g) val[g][nv - 2] = __fadd_rn(val[g][nv - 2], val[g][nv - 1]);
+            --nv;
+        }
+    }
+    const int c = c0 + tid;
+    if (c < K) {
+#pragma unroll
+        for (int g = 0; g < kIvfCdQ; ++g)
+            if (g < nq) out[(size_t)(q0 + g) * K + c] = __fsqrt_rn(val[g][0]);
+    }
 }
 
 // np.argsort(centroid_distances)[:n_probe] (ivf.py:171), ties by centroid index; plus the prefix sums of the
@@ -298,10 +373,12 @@ int vdb_ivf_centroid_dist(const float* q, int Q, int D, const float* centroids, 
     VDB_REQUIRE(Q >= 0 && D > 0 && K > 0, VDB_ERR_INVALID, "vdb_ivf_centroid_dist: bad shape");
     if (Q == 0) return VDB_OK;
     VDB_REQUIRE(q && centroids && out, VDB_ERR_INVALID, "vdb_ivf_centroid_dist: null pointer");
-    VDB_REQUIRE(Q <= 65535, VDB_ERR_UNSUPPORTED, "Q=%d > 65535 per call", Q);
-    VDB_REQUIRE((size_t)D * 4 <= 48 * 1024, VDB_ERR_UNSUPPORTED, "D=%d too large", D);
-    int gx = (K + 127) / 128;
-    ivf_centroid_dist_kernel<<<dim3(gx, Q), 128, (size_t)D * 4, static_cast<cudaStream_t>(stream)>>>(q, Q, D, centroids, K, out);
+    VDB_REQUIRE(Q <= 65535 * kIvfCdQ, VDB_ERR_UNSUPPORTED, "Q=%d too large per call", Q);
+    VDB_REQUIRE(D <= 8192, VDB_ERR_UNSUPPORTED, "D=%d > 8192", D);
+    const size_t smem = ((size_t)kIvfCdQ * D + (size_t)kIvfCdThreads * (kIvfCdChunk + 1)) * 4;
+    VDB_CUDA(cudaFuncSetAttribute(ivf_centroid_dist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    dim3 grid((K + kIvfCdThreads - 1) / kIvfCdThreads, (Q + kIvfCdQ - 1) / kIvfCdQ);
+    ivf_centroid_dist_kernel<<<grid, kIvfCdThreads, smem, static_cast<cudaStream_t>(stream)>>>(q, Q, D, centroids, K, out);
     count_launch(1);
     VDB_CUDA(cudaGetLastError());
     return VDB_OK;
