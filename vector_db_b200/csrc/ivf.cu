@@ -25,7 +25,10 @@ namespace vdb {
 constexpr int kIvfThreads = 256;
 constexpr int kIvfWarps = kIvfThreads / 32;
 constexpr int kIvfRowsPerWarp = 4;                         // rows in flight per warp iteration
-constexpr int kIvfBurst = kIvfWarps * kIvfRowsPerWarp;     // pushes between two compaction checks
+constexpr int kIvfCheckEvery = 4;                          // warp iterations between two compaction checks (one barrier)
+constexpr int kIvfBatch = kIvfWarps * kIvfRowsPerWarp;     // candidates per CTA iteration
+constexpr int kIvfBurst = kIvfBatch * kIvfCheckEvery;      // pushes between two compaction checks
+constexpr int kIvfSplits = 32;                             // CTAs per query (those past the query's candidates exit)
 constexpr int kIvfMaxProbe = 8192;                         // probe prefix table lives in shared memory
 
 // numpy pairwise_sum (numpy/_core/src/umath/loops_utils.h.src) over v[t] = rn(d[t]^2), d[t] = rn(c[t] - q[t]):
@@ -209,14 +212,21 @@ __device__ __forceinline__ int ivf_find_probe(const int32_t* prefix, int n, int 
     return lo;
 }
 
-// grid (S, Q).  CTA (s, q) evaluates candidates [s*chunk, (s+1)*chunk) of query q's flattened sequence
-// (probe rank major, list position minor -- the enumeration order of ivf.py:177-191).
+// grid (kIvfSplits, Q).  CTA (s, q) evaluates candidates [s*chunk, (s+1)*chunk) of query q's flattened sequence
+// (probe rank major, list position minor -- the enumeration order of ivf.py:177-191); chunk =
+// max(chunk_min, ceil(total_q / kIvfSplits)), so a query with few candidates uses few CTAs and one with a huge
+// list is still spread over 32 (list sizes after k-means are very uneven).  partial is pre-filled with VDB_KEY_MAX.
 __global__ void __launch_bounds__(kIvfThreads)
 ivf_scan_kernel(const float* __restrict__ q, const float* __restrict__ db, int D, const int32_t* __restrict__ list_ptr,
                 const int32_t* __restrict__ list_rows, const int32_t* __restrict__ probes,
                 const int32_t* __restrict__ prefix_g, int n_probe, const uint32_t* __restrict__ alive, int k, int C,
-                int S, u64* __restrict__ partial) {
+                int chunk_min, u64* __restrict__ partial) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
+    {
+        const int total_q = __ldg(prefix_g + (size_t)blockIdx.y * (n_probe + 1) + n_probe);
+        const int chunk_q = max(chunk_min, (total_q + kIvfSplits - 1) / kIvfSplits);
+        if ((int)blockIdx.x * chunk_q >= total_q) return;               // nothing for this split
+    }
     u64* buf = reinterpret_cast<u64*>(smem_raw);                       // C
     float* qs = reinterpret_cast<float*>(buf + C);                     // D (padded to 4)
     int32_t* prefix = reinterpret_cast<int32_t*>(qs + ((D + 3) & ~3)); // n_probe + 1
@@ -232,12 +242,13 @@ ivf_scan_kernel(const float* __restrict__ q, const float* __restrict__ db, int D
     sel.init(buf, &cnt, &thr, C, k, kIvfBurst);
     __syncthreads();
     const int total = prefix[n_probe];
-    const int chunk = (total + S - 1) / S;
+    const int chunk = max(chunk_min, (total + kIvfSplits - 1) / kIvfSplits);
     const int begin = min(total, s * chunk), end = min(total, begin + chunk);
     const bool vec4 = (D & 3) == 0;
     const int nchunk = D >> 2;
 
-    for (int base = begin; base < end; base += kIvfBurst) {
+    int batch = 0;
+    for (int base = begin; base < end; base += kIvfBatch) {
         // lane j < kIvfRowsPerWarp decodes the warp's j-th candidate
         int my_seq = base + warp * kIvfRowsPerWarp + lane, my_row = -1;
         if (lane < kIvfRowsPerWarp && my_seq < end) {
@@ -283,10 +294,10 @@ ivf_scan_kernel(const float* __restrict__ q, const float* __restrict__ db, int D
             if (lane == j) mine = v;
         }
         if (my_row >= 0) sel.push(pack_key(sqrtf(mine), (uint32_t)my_seq));
-        sel.maybe_compact();
+        if (++batch == kIvfCheckEvery) { batch = 0; sel.maybe_compact(); }
     }
     sel.finalize();
-    u64* dst = partial + ((size_t)qi * S + s) * k;
+    u64* dst = partial + ((size_t)qi * kIvfSplits + s) * k;
     for (int i = tid; i < k; i += kIvfThreads) dst[i] = buf[i];
 }
 
@@ -356,12 +367,7 @@ ivf_centroid_mean_kernel(const float* __restrict__ x, int D, const int32_t* __re
 }
 
 static size_t ivf_al(size_t v) { return (v + 255) & ~(size_t)255; }
-static int ivf_splits(int Q) {
-    int S = (8 * sm_count() + Q - 1) / (Q > 0 ? Q : 1);
-    if (S < 1) S = 1;
-    if (S > 32) S = 32;
-    return S;
-}
+static int ivf_chunk_min(int Q) { return Q >= 1024 ? 16384 : (Q >= 128 ? 2048 : 256); }
 
 }  // namespace vdb
 
@@ -402,7 +408,7 @@ int vdb_ivf_probe(const float* cdist, int Q, int K, int n_probe, const int32_t* 
 
 size_t vdb_ivf_scan_workspace(int Q, int k) {
     if (Q <= 0 || k <= 0) return 0;
-    return ivf_al((size_t)Q * ivf_splits(Q) * k * 8) + 256;
+    return ivf_al((size_t)Q * kIvfSplits * k * 8) + 256;
 }
 
 int vdb_ivf_scan(const float* q, int Q, const float* db, int D, const int32_t* list_ptr, const int32_t* list_rows,
@@ -415,7 +421,7 @@ int vdb_ivf_scan(const float* q, int Q, const float* db, int D, const int32_t* l
     if (Q == 0) return VDB_OK;
     VDB_REQUIRE(q && db && list_ptr && list_rows && probes && prefix && out_d && out_i, VDB_ERR_INVALID,
                 "vdb_ivf_scan: null pointer");
-    const int S = ivf_splits(Q);
+    const int S = kIvfSplits;
     const size_t need = (size_t)Q * S * k * 8;
     VDB_REQUIRE(ws && ws_bytes >= need, VDB_ERR_WORKSPACE, "workspace %zu < %zu", ws_bytes, need);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -425,10 +431,11 @@ int vdb_ivf_scan(const float* q, int Q, const float* db, int D, const int32_t* l
     VDB_REQUIRE(smem <= (size_t)max_smem_optin() - 1024, VDB_ERR_UNSUPPORTED, "D=%d k=%d n_probe=%d do not fit shared memory",
                 D, k, n_probe);
     VDB_CUDA(cudaFuncSetAttribute(ivf_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    VDB_CUDA(cudaMemsetAsync(partial, 0xFF, need, st));          // VDB_KEY_MAX for the splits that exit early
     {
         ProfScope prof(kProfIvfScan, st);
         ivf_scan_kernel<<<dim3(S, Q), kIvfThreads, smem, st>>>(q, db, D, list_ptr, list_rows, probes, prefix, n_probe,
-                                                              alive, k, C, S, partial);
+                                                              alive, k, C, ivf_chunk_min(Q), partial);
     }
     const int C2 = select_capacity(k, 256);
     VDB_CUDA(cudaFuncSetAttribute(ivf_merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(C2 * 8)));
