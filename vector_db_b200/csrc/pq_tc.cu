@@ -29,7 +29,7 @@ constexpr int kEtRows = 128;               // rows per tile (UMMA M)
 constexpr int kEtK = 256;                  // centroids per sub-space (UMMA N)
 constexpr int kEtABytes = kEtRows * 32;    // 4 KB: 128 rows x 8 fp32
 constexpr int kEtBBytes = kEtK * 32;       // 8 KB: 256 centroids x 8 fp32
-constexpr int kEtStageBytes = kEtABytes + 2 * kEtBBytes;   // A + (-2C) + norm split
+constexpr int kEtStageBytes = 2 * kEtABytes + 3 * kEtBBytes;   // x | x_lo | hi(-2C) | lo(-2C) | norm split  (32 KB)
 constexpr int kEtMaxStages = 8;
 
 struct EtSmem {
@@ -38,37 +38,46 @@ struct EtSmem {
 __host__ __device__ inline EtSmem et_layout(int stages, int m) {
     EtSmem L;
     L.stage_off = 0;
-    L.ones_off = stages * kEtStageBytes;                       // 20 KB stages keep 1024-byte alignment
+    L.ones_off = stages * kEtStageBytes;                       // 32 KB stages keep 1024-byte alignment
     L.mask_off = L.ones_off + kEtABytes;
     L.codes_off = L.mask_off + 8 * 256 * 4;                    // candidate masks [8 chunks][256 epilogue threads]
     L.bar_off = (L.codes_off + kEtRows * m + 15) & ~15;        // code staging [128 rows][m]
-    L.total = L.bar_off + (2 * kEtMaxStages + 4) * 8 + 16;
+    L.total = L.bar_off + (3 * kEtMaxStages + 4) * 8 + 16;
     return L;
 }
 
-// -2 C and the tf32 split of |c|^2, padded to 256 centroids per sub-space (padding can never win)
-__global__ void pq_tc_operands_kernel(const float* __restrict__ cb, int m, int K, float* __restrict__ bc,
-                                      float* __restrict__ bn, float* __restrict__ cmax) {
+// tf32 keeps 10 explicit mantissa bits: the tensor core ignores the low 13 bits of an fp32 operand
+__device__ __forceinline__ float tf32_hi(float v) { return __uint_as_float(__float_as_uint(v) & 0xFFFFE000u); }
+
+// Operand tensor [m][3][256][8]: part 0 = hi(-2C), part 1 = lo(-2C) = -2C - hi (exact), part 2 = three-way
+// tf32 split of |c|^2 in columns 0..2.  Padded to 256 centroids per sub-space (padding can never win).
+__global__ void pq_tc_operands_kernel(const float* __restrict__ cb, int m, int K, float* __restrict__ ops,
+                                      float* __restrict__ cmax) {
     const int j = blockIdx.x;
     __shared__ float red[256];
     float mx = 0.f;
     for (int c = threadIdx.x; c < 256; c += blockDim.x) {
-        float* oc = bc + ((size_t)j * 256 + c) * 8;
-        float* on = bn + ((size_t)j * 256 + c) * 8;
+        float* oh = ops + (((size_t)j * 3 + 0) * 256 + c) * 8;
+        float* ol = ops + (((size_t)j * 3 + 1) * 256 + c) * 8;
+        float* on = ops + (((size_t)j * 3 + 2) * 256 + c) * 8;
         float s = 0.f;
         if (c < K) {
             const float* src = cb + ((size_t)j * K + c) * 8;
 #pragma unroll
-            for (int t = 0; t < 8; ++t) { const float v = src[t]; oc[t] = -2.f * v; s = fmaf(v, v, s); }
+            for (int t = 0; t < 8; ++t) {
+                const float v = src[t], w = -2.f * v, h = tf32_hi(w);
+                oh[t] = h; ol[t] = w - h;
+                s = fmaf(v, v, s);
+            }
             mx = fmaxf(mx, s);
         } else {
 #pragma unroll
-            for (int t = 0; t < 8; ++t) oc[t] = 0.f;
+            for (int t = 0; t < 8; ++t) { oh[t] = 0.f; ol[t] = 0.f; }
             s = 3.0e38f;
         }
-        const float h = __uint_as_float(__float_as_uint(s) & 0xFFFFE000u);
+        const float h = tf32_hi(s);
         const float r1 = s - h;
-        const float mid = __uint_as_float(__float_as_uint(r1) & 0xFFFFE000u);
+        const float mid = tf32_hi(r1);
         const float lo = r1 - mid;
         on[0] = h; on[1] = mid; on[2] = lo;
 #pragma unroll
@@ -97,17 +106,17 @@ __device__ __forceinline__ float min32(const float (&v)[32]) {
 // bit i of the result: v[i] <= thr.  Written as setp + predicated or (2 SASS instructions per element);
 // the plain C++ form compiles to FSETP + SEL + LOP3.
 __device__ __forceinline__ uint32_t le_mask32(const float (&v)[32], float thr) {
-    uint32_t mask = 0;
+    uint32_t mk[4] = {0u, 0u, 0u, 0u};          // four independent chains: the predicated ORs of one chain serialise
 #pragma unroll
     for (int i = 0; i < 32; ++i)
         asm("{\n\t.reg .pred p;\n\tsetp.le.f32 p, %1, %2;\n\t@p or.b32 %0, %0, %3;\n\t}"
-            : "+r"(mask) : "f"(v[i]), "f"(thr), "r"(1u << i));
-    return mask;
+            : "+r"(mk[i & 3]) : "f"(v[i]), "f"(thr), "r"(1u << i));
+    return (mk[0] | mk[1]) | (mk[2] | mk[3]);
 }
 
 __global__ void __launch_bounds__(kEtThreads, 1)
-pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_bc,
-                    const __grid_constant__ CUtensorMap map_bn, const float* __restrict__ x, int64_t N, int D, int m,
+pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_b,
+                    const float* __restrict__ x, int64_t N, int D, int m,
                     int K, const float* __restrict__ cb, const float* __restrict__ cmax, int stages, int64_t tiles,
                     uint8_t* __restrict__ codes) {
     extern __shared__ __align__(1024) unsigned char smem[];
@@ -120,7 +129,8 @@ pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L.bar_off);
     uint64_t* full = bars;                          // [stages]
     uint64_t* empty = bars + kEtMaxStages;          // [stages]
-    uint64_t* tmem_full = bars + 2 * kEtMaxStages;  // [2]
+    uint64_t* xlo_full = bars + 2 * kEtMaxStages;   // [stages]: x_lo written by the split warp
+    uint64_t* tmem_full = bars + 3 * kEtMaxStages;  // [2]
     uint64_t* tmem_empty = tmem_full + 2;           // [2]
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 2);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -135,11 +145,12 @@ pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     }
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&map_x);
-        tma_prefetch_desc(&map_bc);
-        tma_prefetch_desc(&map_bn);
+        tma_prefetch_desc(&map_b);
     }
     if (warp == 1 && lane == 0) {
-        for (int i = 0; i < stages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1 + 4); }   // MMA commit + 4 epilogue warps
+        for (int i = 0; i < stages; ++i) {
+            mbar_init(&full[i], 1); mbar_init(&empty[i], 1 + 4); mbar_init(&xlo_full[i], 1);   // empty: MMA commit + 4 epilogue warps
+        }
         for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 128); }
         fence_barrier_init();
     }
@@ -158,10 +169,12 @@ pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                 for (int j = 0; j < m; ++j) {
                     mbar_wait(&empty[st], ph ^ 1);
                     unsigned char* base = sStage + (size_t)st * kEtStageBytes;
-                    mbar_expect_tx(&full[st], (uint32_t)kEtStageBytes);
+                    mbar_expect_tx(&full[st], (uint32_t)(kEtABytes + 3 * kEtBBytes));
                     tma_load_2d(base, &map_x, &full[st], j * 8, (int)(tile * kEtRows), kEvictFirst);
-                    tma_load_2d(base + kEtABytes, &map_bc, &full[st], 0, j * 256, kEvictLast);
-                    tma_load_2d(base + kEtABytes + kEtBBytes, &map_bn, &full[st], 0, j * 256, kEvictLast);
+#pragma unroll
+                    for (int part = 0; part < 3; ++part)
+                        tma_load_2d(base + 2 * kEtABytes + part * kEtBBytes, &map_b, &full[st], 0, (j * 3 + part) * 256,
+                                    kEvictLast);
                     if (++st == stages) { st = 0; ph ^= 1; }
                 }
             }
@@ -176,17 +189,47 @@ pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                 for (int j = 0; j < m; ++j) {
                     mbar_wait(&tmem_empty[as], aph ^ 1);
                     mbar_wait(&full[st], ph);
+                    mbar_wait(&xlo_full[st], ph);
                     tc_fence_after();
                     const uint32_t base = smem_u32(sStage + (size_t)st * kEtStageBytes);
                     const uint32_t d_tmem = tmem_base + (uint32_t)(as * kEtK);
-                    umma_tf32(d_tmem, make_desc_k_sw32(base), make_desc_k_sw32(base + kEtABytes), idesc, 0u);
-                    umma_tf32(d_tmem, d_ones, make_desc_k_sw32(base + kEtABytes + kEtBBytes), idesc, 1u);
+                    const uint64_t d_x = make_desc_k_sw32(base), d_xlo = make_desc_k_sw32(base + kEtABytes);
+                    const uint64_t d_hi = make_desc_k_sw32(base + 2 * kEtABytes);
+                    const uint64_t d_lo = make_desc_k_sw32(base + 2 * kEtABytes + kEtBBytes);
+                    // x.(-2c) to ~2^-20: hi(x).hi + hi(x).lo + lo(x).hi  (the tensor core drops the low 13 bits of every operand)
+                    umma_tf32(d_tmem, d_x, d_hi, idesc, 0u);
+                    umma_tf32(d_tmem, d_x, d_lo, idesc, 1u);
+                    umma_tf32(d_tmem, d_xlo, d_hi, idesc, 1u);
+                    umma_tf32(d_tmem, d_ones, make_desc_k_sw32(base + 2 * kEtABytes + 2 * kEtBBytes), idesc, 1u);
                     umma_commit(&empty[st]);
                     umma_commit(&tmem_full[as]);
                     if (++st == stages) { st = 0; ph ^= 1; }
                     as ^= 1;
                     if (as == 0) aph ^= 1;
                 }
+            }
+        }
+    } else if (warp == 3) {
+        // ================= operand split: x -> hi(x) in place, x_lo = x - hi(x) beside it; elementwise on the landed
+        // tile, so the swizzled layout does not matter =================
+        int st = 0, ph = 0;
+        for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+            for (int j = 0; j < m; ++j) {
+                mbar_wait(&full[st], ph);
+                float4* src_w = reinterpret_cast<float4*>(sStage + (size_t)st * kEtStageBytes);
+                const float4* src = src_w;
+                float4* dst = reinterpret_cast<float4*>(sStage + (size_t)st * kEtStageBytes + kEtABytes);
+#pragma unroll
+                for (int i = 0; i < kEtABytes / 16 / 32; ++i) {
+                    const float4 v = src[i * 32 + lane];
+                    const float4 h = make_float4(tf32_hi(v.x), tf32_hi(v.y), tf32_hi(v.z), tf32_hi(v.w));
+                    src_w[i * 32 + lane] = h;           // operands are tf32-exact: no dependence on the MMA's input rounding mode
+                    dst[i * 32 + lane] = make_float4(v.x - h.x, v.y - h.y, v.z - h.z, v.w - h.w);
+                }
+                fence_proxy_async();                   // generic-proxy writes -> visible to the MMA's async-proxy reads
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&xlo_full[st]);
+                if (++st == stages) { st = 0; ph ^= 1; }
             }
         }
     } else if (warp >= 4) {
@@ -208,44 +251,58 @@ pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                 phase ^= 1;
                 tc_fence_after();
                 const unsigned char* sA = sStage + (size_t)st * kEtStageBytes;
-                const unsigned char* sBc = sA + kEtABytes;
+                const unsigned char* sBh = sA + 2 * kEtABytes;      // hi(-2c)
+                const unsigned char* sBl = sBh + kEtBBytes;         // lo(-2c)
                 float xs[8];
                 {
-                    const float4 a = *reinterpret_cast<const float4*>(sA + rt * 32 + (0 ^ swz));
-                    const float4 b = *reinterpret_cast<const float4*>(sA + rt * 32 + (16 ^ swz));
+                    float4 a = *reinterpret_cast<const float4*>(sA + rt * 32 + (0 ^ swz));
+                    float4 b = *reinterpret_cast<const float4*>(sA + rt * 32 + (16 ^ swz));
+                    const float4 al = *reinterpret_cast<const float4*>(sA + kEtABytes + rt * 32 + (0 ^ swz));
+                    const float4 bl = *reinterpret_cast<const float4*>(sA + kEtABytes + rt * 32 + (16 ^ swz));
+                    a.x += al.x; a.y += al.y; a.z += al.z; a.w += al.w;      // hi + lo = x exactly
+                    b.x += bl.x; b.y += bl.y; b.z += bl.z; b.w += bl.w;
                     xs[0] = a.x; xs[1] = a.y; xs[2] = a.z; xs[3] = a.w; xs[4] = b.x; xs[5] = b.y; xs[6] = b.z; xs[7] = b.w;
                 }
+                // Two 32-column register buffers: while one chunk is reduced the next one's TMEM load is in
+                // flight (tcgen05.wait::ld waits for ALL outstanding loads, so exactly one is outstanding at
+                // every wait).  With a single buffer each of the 16 chunk visits exposed the full TMEM latency.
+                float va[32], vb[32];
                 // pass 1: minimum score of the row
                 float gmin = INFINITY;
-                {
-                    float v[32];
-                    tmem_ld_x32(taddr, v);
+                tmem_ld_x32(taddr, va);
 #pragma unroll 1
-                    for (int ch = 0; ch < 8; ++ch) {
-                        tmem_ld_wait(v);
-                        const float cm = min32(v);
-                        if (ch + 1 < 8) tmem_ld_x32(taddr + (uint32_t)((ch + 1) * 32), v);
-                        gmin = fminf(gmin, cm);
-                    }
+                for (int ch = 0; ch < 8; ch += 2) {
+                    tmem_ld_wait(va);
+                    tmem_ld_x32(taddr + (uint32_t)((ch + 1) * 32), vb);
+                    gmin = fminf(gmin, min32(va));
+                    tmem_ld_wait(vb);
+                    tmem_ld_x32(taddr + (uint32_t)(((ch + 2) & 7) * 32), va);     // last round: chunk 0 again, for pass 2
+                    gmin = fminf(gmin, min32(vb));
                 }
                 // rigorous candidate margin (see file header): tf32 rounding of both operands + fp32 noise
                 float xx = 0.f;
 #pragma unroll
                 for (int t = 0; t < 8; ++t) xx = fmaf(xs[t], xs[t], xx);
                 const float xn = sqrtf(xx) * 1.0000005f, cm_j = __ldg(cmax + j);
-                const float thr = gmin + 0.0081f * xn * cm_j + 1e-5f * (xn + cm_j) * (xn + cm_j);
+                const float thr = gmin + 1.2e-5f * xn * cm_j + 1e-5f * (xn + cm_j) * (xn + cm_j);
                 // pass 2: every centroid within the margin
                 int cnt = 0, first = -1;
-                {
-                    float v[32];
-                    tmem_ld_x32(taddr, v);
 #pragma unroll 1
-                    for (int ch = 0; ch < 8; ++ch) {
-                        tmem_ld_wait(v);
-                        const uint32_t mask = le_mask32(v, thr);
-                        if (ch + 1 < 8) tmem_ld_x32(taddr + (uint32_t)((ch + 1) * 32), v);
+                for (int ch = 0; ch < 8; ch += 2) {
+                    tmem_ld_wait(va);
+                    tmem_ld_x32(taddr + (uint32_t)((ch + 1) * 32), vb);
+                    {
+                        const uint32_t mask = le_mask32(va, thr);
                         sMask[ch * 256 + et] = mask;
                         if (mask && first < 0) first = ch * 32 + __ffs(mask) - 1;
+                        cnt += __popc(mask);
+                    }
+                    tmem_ld_wait(vb);
+                    if (ch + 2 < 8) tmem_ld_x32(taddr + (uint32_t)((ch + 2) * 32), va);
+                    {
+                        const uint32_t mask = le_mask32(vb, thr);
+                        sMask[(ch + 1) * 256 + et] = mask;
+                        if (mask && first < 0) first = (ch + 1) * 32 + __ffs(mask) - 1;
                         cnt += __popc(mask);
                     }
                 }
@@ -262,9 +319,13 @@ pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                             mask &= mask - 1;
                             if (c < K) {
                                 const int cs = ((c >> 2) & 1) << 4;
-                                const float4 a = *reinterpret_cast<const float4*>(sBc + c * 32 + (0 ^ cs));
-                                const float4 b = *reinterpret_cast<const float4*>(sBc + c * 32 + (16 ^ cs));
-                                // the operand holds -2c (exact), so c = -0.5 * operand (exact)
+                                float4 a = *reinterpret_cast<const float4*>(sBh + c * 32 + (0 ^ cs));
+                                float4 b = *reinterpret_cast<const float4*>(sBh + c * 32 + (16 ^ cs));
+                                const float4 al = *reinterpret_cast<const float4*>(sBl + c * 32 + (0 ^ cs));
+                                const float4 bl = *reinterpret_cast<const float4*>(sBl + c * 32 + (16 ^ cs));
+                                // hi + lo = -2c exactly, so c = -0.5 * (hi + lo) exactly
+                                a.x += al.x; a.y += al.y; a.z += al.z; a.w += al.w;
+                                b.x += bl.x; b.y += bl.y; b.z += bl.z; b.w += bl.w;
                                 float d[8] = {-0.5f * a.x - xs[0], -0.5f * a.y - xs[1], -0.5f * a.z - xs[2], -0.5f * a.w - xs[3],
                                               -0.5f * b.x - xs[4], -0.5f * b.y - xs[5], -0.5f * b.z - xs[6], -0.5f * b.w - xs[7]};
                                 const float dist = sqrtf(np_sumsq<8>(d));
@@ -310,7 +371,7 @@ int vdb_pq_encode_tc_supported(int64_t N, int D, int m, int K) {
     return (N > 0 && N < (1ll << 31) && m > 0 && D == 8 * m && K > 0 && K <= 256 && m <= 512) ? 1 : 0;
 }
 
-size_t vdb_pq_encode_tc_workspace(int m) { return 2 * et_ws_operand(m) + (((size_t)m * 4 + 255) & ~(size_t)255) + 256; }
+size_t vdb_pq_encode_tc_workspace(int m) { return 3 * et_ws_operand(m) + (((size_t)m * 4 + 255) & ~(size_t)255) + 256; }
 
 int vdb_pq_encode_tc(const float* x, int64_t N, int D, int m, int K, const float* codebooks, uint8_t* codes, void* ws,
                      size_t ws_bytes, void* stream) {
@@ -324,18 +385,15 @@ int vdb_pq_encode_tc(const float* x, int64_t N, int D, int m, int K, const float
                 VDB_ERR_INVALID, "rows / codebooks / workspace must be 16 / 16 / 256-byte aligned");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     char* base = static_cast<char*>(ws);
-    float* bc = reinterpret_cast<float*>(base);
-    float* bn = reinterpret_cast<float*>(base + et_ws_operand(m));
-    float* cmax = reinterpret_cast<float*>(base + 2 * et_ws_operand(m));
-    pq_tc_operands_kernel<<<m, 256, 0, st>>>(codebooks, m, K, bc, bn, cmax);
+    float* opnd = reinterpret_cast<float*>(base);
+    float* cmax = reinterpret_cast<float*>(base + 3 * et_ws_operand(m));
+    pq_tc_operands_kernel<<<m, 256, 0, st>>>(codebooks, m, K, opnd, cmax);
     count_launch(1);
-    CUtensorMap map_x, map_bc, map_bn;
+    CUtensorMap map_x, map_b;
     int rc = tma_map_2d(&map_x, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, x, (uint64_t)D, (uint64_t)N, (uint64_t)D * 4, 8, kEtRows,
                         CU_TENSOR_MAP_SWIZZLE_32B);
     if (rc) return rc;
-    rc = tma_map_2d(&map_bc, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, bc, 8, (uint64_t)m * 256, 32, 8, kEtK, CU_TENSOR_MAP_SWIZZLE_32B);
-    if (rc) return rc;
-    rc = tma_map_2d(&map_bn, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, bn, 8, (uint64_t)m * 256, 32, 8, kEtK, CU_TENSOR_MAP_SWIZZLE_32B);
+    rc = tma_map_2d(&map_b, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, opnd, 8, (uint64_t)m * 3 * 256, 32, 8, kEtK, CU_TENSOR_MAP_SWIZZLE_32B);
     if (rc) return rc;
     int stages = kEtMaxStages;
     const int smem_max = max_smem_optin();
@@ -347,7 +405,7 @@ int vdb_pq_encode_tc(const float* x, int64_t N, int D, int m, int K, const float
     VDB_CUDA(cudaFuncSetAttribute(pq_encode_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     {
         ProfScope prof(kProfPqEncode, st);
-        pq_encode_tc_kernel<<<grid, kEtThreads, smem, st>>>(map_x, map_bc, map_bn, x, N, D, m, K, codebooks, cmax, stages, tiles,
+        pq_encode_tc_kernel<<<grid, kEtThreads, smem, st>>>(map_x, map_b, x, N, D, m, K, codebooks, cmax, stages, tiles,
                                                            codes);
     }
     count_launch(1);
