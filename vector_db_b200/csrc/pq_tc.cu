@@ -2,14 +2,22 @@
 // (src/vector_db/inference/pq.py:77-89), for dsub = 8 and K <= 256.
 //
 // dsub = 8 is exactly one tf32 UMMA K step, so per (128-row tile, sub-space j) the whole 128 x 256
-// score matrix  s(c) = |c|^2 - 2 x.c  is TWO tcgen05.mma.kind::tf32 instructions: the fp32 rows x_ij
-// straight from the (N, D) matrix (TMA box 8 floats x 128 rows, 32-byte swizzle) against the
-// operand -2 C_j, plus a constant "ones" tile against the exact three-way tf32 split of |c|^2.
+// score matrix  s(c) = |c|^2 - 2 x.c  is FOUR tcgen05.mma.kind::tf32 instructions.  The tensor core keeps
+// 10 mantissa bits of each operand, so both operands are split into tf32-exact parts (3xTF32 style):
+//   x = hi(x) + lo(x)        -- a helper warp rewrites the landed TMA tile in place and writes lo(x) beside it
+//   -2c = hi(-2c) + lo(-2c)  -- prepared once per call
+// and the score is hi(x).hi(-2c) + hi(x).lo(-2c) + lo(x).hi(-2c) + ones.split3(|c|^2): every operand the MMA
+// sees is exactly representable, the dropped term and the re-rounding of the lo parts are ~2^-20 |x||c|.
 // The accumulator is the score; the epilogue (one thread per row) takes its minimum, then collects
-// every centroid whose score is within a RIGOROUS margin of it (tf32 input rounding, Cauchy-Schwarz,
-// plus the reference's own fp32 rounding); a single candidate is the answer, several candidates are
-// resolved with the reference's exact arithmetic (numpy's pairwise-sum order, sqrt, first index wins)
-// -- so codes stay bit-exact although the heavy lifting is tf32.
+// every centroid whose score is within a RIGOROUS margin of it (1.2e-5 |x| max|c| for the split, plus
+// 1e-5 (|x|+max|c|)^2 for the fp32 accumulation and the reference's own fp32 rounding); a single candidate
+// is the answer, several candidates are resolved with the reference's exact arithmetic (numpy's pairwise-sum
+// order, sqrt, first index wins) -- so codes stay bit-exact although the heavy lifting is tf32.  With a
+// single-pass tf32 product the margin had to be 0.0081 |x| max|c| and a fifth of all rows took the slow path.
+//
+// Tried and measured slower (kept out): parking each lane's arg-min chunk in shared memory to skip the second
+// TMEM pass (the predicated 128-bit stores cost the shared-memory bandwidth of the whole score tile), and a
+// 16-warp epilogue with the columns of a row split over two warps (two pair barriers per step ate the gain).
 //
 // Roofline: HBM, algorithmic bytes per vector = 4 D + m (rows read once, codes written once).
 #include <cuda.h>
@@ -40,7 +48,7 @@ __host__ __device__ inline EtSmem et_layout(int stages, int m) {
     L.stage_off = 0;
     L.ones_off = stages * kEtStageBytes;                       // 32 KB stages keep 1024-byte alignment
     L.mask_off = L.ones_off + kEtABytes;
-    L.codes_off = L.mask_off + 8 * 2 * 8 * 32 * 16;            // parked chunks [8 warps][2 slots][8 quads][32 lanes] float4 = 64 KB
+    L.codes_off = L.mask_off + 8 * 256 * 4;                    // candidate masks [8 chunks][256 epilogue threads]
     L.bar_off = (L.codes_off + kEtRows * m + 15) & ~15;        // code staging [128 rows][m]
     L.total = L.bar_off + (3 * kEtMaxStages + 4) * 8 + 16;
     return L;
@@ -124,7 +132,7 @@ pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     const EtSmem L = et_layout(stages, m);
     unsigned char* sStage = smem + L.stage_off;
     float* sOnes = reinterpret_cast<float*>(smem + L.ones_off);
-    float4* sSlots = reinterpret_cast<float4*>(smem + L.mask_off);
+    uint32_t* sMask = reinterpret_cast<uint32_t*>(smem + L.mask_off);
     uint8_t* sCodes = smem + L.codes_off;
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L.bar_off);
     uint64_t* full = bars;                          // [stages]
@@ -263,115 +271,74 @@ pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                     b.x += bl.x; b.y += bl.y; b.z += bl.z; b.w += bl.w;
                     xs[0] = a.x; xs[1] = a.y; xs[2] = a.z; xs[3] = a.w; xs[4] = b.x; xs[5] = b.y; xs[6] = b.z; xs[7] = b.w;
                 }
-                // Per row only the 32-column chunk(s) that can hold the answer need a second look, but a TMEM load
-                // is warp-wide (lane = row), so "each lane re-reads its own chunk" does not exist.  Instead pass 1
-                // parks the chunk in shared memory whenever it sets a new running minimum for the lane (slot 0
-                // therefore ends up holding the arg-min chunk); a second TMEM pass runs only for warps where some
-                // lane has ANOTHER chunk within the margin (slot 1).  Two register buffers keep one TMEM load in
-                // flight while the previous chunk is reduced (tcgen05.wait::ld waits for all outstanding loads).
+                // Two 32-column register buffers: while one chunk is reduced the next one's TMEM load is in
+                // flight (tcgen05.wait::ld waits for ALL outstanding loads, so exactly one is outstanding at
+                // every wait).  With a single buffer each of the 16 chunk visits exposed the full TMEM latency.
                 float va[32], vb[32];
-                float cm[8];
+                // pass 1: minimum score of the row
                 float gmin = INFINITY;
-                int ch0 = 0;
-                float4* slot0 = sSlots + ((size_t)((warp - 4) * 2 + 0) * 8) * 32 + lane;      // [quad][lane], 16 B each
-                float4* slot1 = sSlots + ((size_t)((warp - 4) * 2 + 1) * 8) * 32 + lane;
-#define VDB_ET_PARK(slot, v)                                                                         \
-    {                                                                                                 \
-        _Pragma("unroll") for (int qd = 0; qd < 8; ++qd)                                              \
-            (slot)[qd * 32] = make_float4((v)[4 * qd], (v)[4 * qd + 1], (v)[4 * qd + 2], (v)[4 * qd + 3]); \
-    }
                 tmem_ld_x32(taddr, va);
-#pragma unroll
+#pragma unroll 1
                 for (int ch = 0; ch < 8; ch += 2) {
                     tmem_ld_wait(va);
                     tmem_ld_x32(taddr + (uint32_t)((ch + 1) * 32), vb);
-                    cm[ch] = min32(va);
-                    if (cm[ch] < gmin) { gmin = cm[ch]; ch0 = ch; VDB_ET_PARK(slot0, va) }
+                    gmin = fminf(gmin, min32(va));
                     tmem_ld_wait(vb);
-                    if (ch + 2 < 8) tmem_ld_x32(taddr + (uint32_t)((ch + 2) * 32), va);
-                    cm[ch + 1] = min32(vb);
-                    if (cm[ch + 1] < gmin) { gmin = cm[ch + 1]; ch0 = ch + 1; VDB_ET_PARK(slot0, vb) }
+                    tmem_ld_x32(taddr + (uint32_t)(((ch + 2) & 7) * 32), va);     // last round: chunk 0 again, for pass 2
+                    gmin = fminf(gmin, min32(vb));
                 }
-                // rigorous candidate margin (see file header): operand split error + fp32 accumulation / reference rounding
+                // rigorous candidate margin (see file header): tf32 rounding of both operands + fp32 noise
                 float xx = 0.f;
 #pragma unroll
                 for (int t = 0; t < 8; ++t) xx = fmaf(xs[t], xs[t], xx);
                 const float xn = sqrtf(xx) * 1.0000005f, cm_j = __ldg(cmax + j);
                 const float thr = gmin + 1.2e-5f * xn * cm_j + 1e-5f * (xn + cm_j) * (xn + cm_j);
-                unsigned others = 0;                    // chunks besides ch0 that hold a score within the margin
-#pragma unroll
-                for (int ch = 0; ch < 8; ++ch) others |= (cm[ch] <= thr && ch != ch0) ? (1u << ch) : 0u;
-                const int ch1 = others ? __ffs(others) - 1 : -1;
-                if (__any_sync(0xffffffffu, others != 0)) {
+                // pass 2: every centroid within the margin
+                int cnt = 0, first = -1;
 #pragma unroll 1
-                    for (int ch = 0; ch < 8; ++ch) {
-                        if (!__any_sync(0xffffffffu, ch == ch1)) continue;
-                        tmem_ld_x32(taddr + (uint32_t)(ch * 32), va);
-                        tmem_ld_wait(va);
-                        if (ch == ch1) VDB_ET_PARK(slot1, va)
+                for (int ch = 0; ch < 8; ch += 2) {
+                    tmem_ld_wait(va);
+                    tmem_ld_x32(taddr + (uint32_t)((ch + 1) * 32), vb);
+                    {
+                        const uint32_t mask = le_mask32(va, thr);
+                        sMask[ch * 256 + et] = mask;
+                        if (mask && first < 0) first = ch * 32 + __ffs(mask) - 1;
+                        cnt += __popc(mask);
+                    }
+                    tmem_ld_wait(vb);
+                    if (ch + 2 < 8) tmem_ld_x32(taddr + (uint32_t)((ch + 2) * 32), va);
+                    {
+                        const uint32_t mask = le_mask32(vb, thr);
+                        sMask[(ch + 1) * 256 + et] = mask;
+                        if (mask && first < 0) first = (ch + 1) * 32 + __ffs(mask) - 1;
+                        cnt += __popc(mask);
                     }
                 }
-#undef VDB_ET_PARK
                 tc_fence_before();
                 mbar_arrive(&tmem_empty[eg]);          // accumulator drained: the MMA two steps ahead may overwrite it
-                __syncwarp();
-                // candidates = scores <= thr in the parked chunks; one candidate is the answer, several are decided by
-                // the reference's own arithmetic (pq.py:79-80), first minimum wins
-                auto exact_dist = [&](int c) {
-                    const int cs = ((c >> 2) & 1) << 4;
-                    float4 a = *reinterpret_cast<const float4*>(sBh + c * 32 + (0 ^ cs));
-                    float4 b = *reinterpret_cast<const float4*>(sBh + c * 32 + (16 ^ cs));
-                    const float4 al = *reinterpret_cast<const float4*>(sBl + c * 32 + (0 ^ cs));
-                    const float4 bl = *reinterpret_cast<const float4*>(sBl + c * 32 + (16 ^ cs));
-                    // hi + lo = -2c exactly, so c = -0.5 * (hi + lo) exactly
-                    a.x += al.x; a.y += al.y; a.z += al.z; a.w += al.w;
-                    b.x += bl.x; b.y += bl.y; b.z += bl.z; b.w += bl.w;
-                    float d[8] = {-0.5f * a.x - xs[0], -0.5f * a.y - xs[1], -0.5f * a.z - xs[2], -0.5f * a.w - xs[3],
-                                  -0.5f * b.x - xs[4], -0.5f * b.y - xs[5], -0.5f * b.z - xs[6], -0.5f * b.w - xs[7]};
-                    return sqrtf(np_sumsq<8>(d));
-                };
-                uint32_t mk0, mk1 = 0;
-                {
-#pragma unroll
-                    for (int qd = 0; qd < 8; ++qd) {
-                        const float4 t = slot0[qd * 32];
-                        va[4 * qd] = t.x; va[4 * qd + 1] = t.y; va[4 * qd + 2] = t.z; va[4 * qd + 3] = t.w;
-                    }
-                    mk0 = le_mask32(va, thr);
-                }
-                int code;
-                if (__popc(others) > 1) {
-                    // three or more chunks within the margin (never seen on real data): every centroid, exactly
+                int code = first < 0 ? 0 : first;
+                if (cnt > 1) {
+                    // several candidates: the reference's own arithmetic decides (pq.py:79-80), first minimum wins
                     float best = INFINITY;
-                    code = 0;
-                    for (int c = 0; c < K; ++c) {
-                        const float dist = exact_dist(c);
-                        if (dist < best) { best = dist; code = c; }
-                    }
-                } else {
-                    if (ch1 >= 0) {
-#pragma unroll
-                        for (int qd = 0; qd < 8; ++qd) {
-                            const float4 t = slot1[qd * 32];
-                            vb[4 * qd] = t.x; vb[4 * qd + 1] = t.y; vb[4 * qd + 2] = t.z; vb[4 * qd + 3] = t.w;
-                        }
-                        mk1 = le_mask32(vb, thr);
-                    }
-                    code = ch0 * 32 + __ffs(mk0) - 1;
-                    if (__popc(mk0) + __popc(mk1) > 1) {
-                        // visit candidates in ascending centroid order so that the first minimum wins
-                        const int lo_ch = (ch1 >= 0 && ch1 < ch0) ? ch1 : ch0, hi_ch = (ch1 >= 0 && ch1 < ch0) ? ch0 : ch1;
-                        uint32_t mlo = (ch1 >= 0 && ch1 < ch0) ? mk1 : mk0, mhi = (ch1 >= 0 && ch1 < ch0) ? mk0 : mk1;
-                        float best = INFINITY;
-                        while (mlo) {
-                            const int c = lo_ch * 32 + __ffs(mlo) - 1;
-                            mlo &= mlo - 1;
-                            if (c < K) { const float dist = exact_dist(c); if (dist < best) { best = dist; code = c; } }
-                        }
-                        while (mhi) {
-                            const int c = hi_ch * 32 + __ffs(mhi) - 1;
-                            mhi &= mhi - 1;
-                            if (c < K) { const float dist = exact_dist(c); if (dist < best) { best = dist; code = c; } }
+                    for (int ch = 0; ch < 8; ++ch) {
+                        uint32_t mask = sMask[ch * 256 + et];
+                        while (mask) {
+                            const int c = ch * 32 + __ffs(mask) - 1;
+                            mask &= mask - 1;
+                            if (c < K) {
+                                const int cs = ((c >> 2) & 1) << 4;
+                                float4 a = *reinterpret_cast<const float4*>(sBh + c * 32 + (0 ^ cs));
+                                float4 b = *reinterpret_cast<const float4*>(sBh + c * 32 + (16 ^ cs));
+                                const float4 al = *reinterpret_cast<const float4*>(sBl + c * 32 + (0 ^ cs));
+                                const float4 bl = *reinterpret_cast<const float4*>(sBl + c * 32 + (16 ^ cs));
+                                // hi + lo = -2c exactly, so c = -0.5 * (hi + lo) exactly
+                                a.x += al.x; a.y += al.y; a.z += al.z; a.w += al.w;
+                                b.x += bl.x; b.y += bl.y; b.z += bl.z; b.w += bl.w;
+                                float d[8] = {-0.5f * a.x - xs[0], -0.5f * a.y - xs[1], -0.5f * a.z - xs[2], -0.5f * a.w - xs[3],
+                                              -0.5f * b.x - xs[4], -0.5f * b.y - xs[5], -0.5f * b.z - xs[6], -0.5f * b.w - xs[7]};
+                                const float dist = sqrtf(np_sumsq<8>(d));
+                                if (dist < best) { best = dist; code = c; }
+                            }
                         }
                     }
                 }
