@@ -239,6 +239,16 @@ int vdb_ivf_scan(const float* q /*[dev]*/, int Q, const float* db /*[dev] rows*D
 int vdb_ivf_centroid_mean(const float* x /*[dev] rows*D*/, int D, const int32_t* list_ptr /*[dev] K+1*/,
                           const int32_t* list_rows /*[dev]*/, int K, float* centroids /*[dev] K*D, in place*/, void* stream);
 
+/* IVF-PQ: ADC (vdb_pq_adc_topk's fixed-point arithmetic) over the members of the probed lists only.
+ * codes are LIST-MAJOR: the code of CSR position p (row list_rows[p]) is codes[p*m .. p*m+m).  Returns the
+ * R best by (d_int, candidate enumeration order) as squared-distance estimates and ROW indices (-1 padded),
+ * ready for vdb_rerank_f32.  No reference symbol (the reference has IVF, ivf.py, and PQ, pq.py, separately). */
+size_t vdb_ivf_adc_workspace(int Q, int m, int R);
+int vdb_ivf_adc_scan(const uint8_t* codes /*[dev] total*m*/, int m, const float* lut /*[dev] Q*m*256*/, int Q,
+                     const int32_t* list_ptr /*[dev]*/, const int32_t* list_rows /*[dev]*/, const int32_t* probes /*[dev]*/,
+                     const int32_t* prefix /*[dev]*/, int n_probe, int R, float* out_d /*[dev] Q*R*/,
+                     int32_t* out_rows /*[dev] Q*R*/, void* ws, size_t ws_bytes, void* stream);
+
 /* ---- e: multi-GPU merge -----------------------------------------------------------------------
  * lists: L sorted lists per query, d [L][Q][k] / i [L][Q][k] (the all-gathered per-shard results);
  * selects the k best by (d, list, position) -- equal to (d,id) order when shard l owns smaller ids

@@ -61,3 +61,25 @@ def lists_from_labels(labels: np.ndarray, ids: Sequence[int], k: int) -> List[Li
     for i, lab in enumerate(labels):
         lists[int(lab)].append(ids[i])
     return lists
+
+
+def ivf_adc_search(centroids: np.ndarray, lists: Sequence[Sequence[int]], codes: Dict[int, np.ndarray], lut: np.ndarray,
+                   query: np.ndarray, n_probe: int, R: int):
+    """PARITY UNPINNED (no reference implementation: the reference has IVF and PQ but not IVF-PQ).  ADC in the
+    fixed-point arithmetic of :func:`oracle.adc_scan_topk` over the members of the probed lists (ivf.py:170-191
+    enumeration order); the R best by (d_int, enumeration order).  ``lut`` is the query's [m,256] table.
+    Returns ([(float32 d, id)], candidates enumerated)."""
+    from oracle.oracle import adc_quantize_lut
+    lutq, e = adc_quantize_lut(lut[None])
+    lutq, e = lutq[0], int(e[0])
+    m = lut.shape[0]
+    cand = []
+    for c in probe_order(centroids, query, n_probe):
+        for node_id in lists[int(c)]:
+            if node_id not in codes:
+                continue
+            code = codes[node_id]
+            cand.append((int(sum(int(lutq[j, code[j]]) for j in range(m))), len(cand), node_id))
+    n_cand = len(cand)
+    cand.sort(key=lambda t: (t[0], t[1]))
+    return [(np.float32(np.ldexp(np.float32(t[0]), -e)), t[2]) for t in cand[:R]], n_cand

@@ -172,3 +172,42 @@ def test_reference_contract_errors_stats_persistence(tmp_path):
     ivf.delete(0)
     assert all(0 not in l for l in ivf.inverted_lists)
     assert all(n.id != 0 for n, _ in ivf.search(nodes[0].embedding, n_probe=4, top_k=5))
+
+
+@pytest.mark.parametrize("n,dim,K,m,n_probe,nq,R", [(6000, 64, 24, 8, 4, 40, 50), (4000, 48, 10, 16, 10, 9, 300),
+                                                   (3000, 40, 8, 5, 3, 7, 20)])
+def test_ivf_pq_scan_vs_oracle(n, dim, K, m, n_probe, nq, R):
+    """IVF-PQ shortlist = fixed-point ADC over the probed lists in enumeration order; rerank = exact L2."""
+    from vector_db_b200 import ops
+    from vector_db_b200.indexing import IvfPqIndex
+    rng = np.random.default_rng(n + m)
+    X = rng.standard_normal((n, dim)).astype(np.float32)
+    ids = np.arange(n, dtype=np.int64) * 2 + 5
+    Q = rng.standard_normal((nq, dim)).astype(np.float32)
+    idx = IvfPqIndex(k=K, chunks=m, pq_k=64 if m == 5 else 256)
+    idx.build_from_arrays([int(i) for i in ids], X, iters=4, init_rows=rng.choice(n, K, replace=False))
+    idx.train_pq(iters=3, train_rows=2000)
+    cb = idx.codebooks.cpu().numpy()
+    codes_all = O.pq_encode(X, list(cb))
+    codes = {int(i): codes_all[j] for j, i in enumerate(ids)}
+    lut = O.adc_lut(Q, list(idx._cb_lut.cpu().numpy()))
+    D, I = idx.search_batch(Q, n_probe, R, rerank=False)
+    lists = idx.inverted_lists
+    for qi in range(nq):
+        ref, n_cand = IO.ivf_adc_search(idx.centroids, lists, codes, lut[qi], Q[qi], n_probe, R)
+        assert int(idx.last_scanned[qi]) == n_cand
+        assert [r[1] for r in ref] == [int(i) for i in I[qi] if i >= 0]
+        np.testing.assert_array_equal(D[qi][:len(ref)], np.array([r[0] for r in ref], np.float32))
+    # rerank over the full candidate set == plain IVF search
+    Dr, Ir = idx.search_batch(Q, n_probe, 10, shortlist=min(4096, n), rerank=True)
+    De, Ie = IvfIndex_search(idx, Q, n_probe, 10)
+    full = idx.last_scanned <= min(4096, n)
+    np.testing.assert_array_equal(Ir[full], Ie[full])
+    np.testing.assert_array_equal(Dr[full], De[full])
+
+
+def IvfIndex_search(idx, Q, n_probe, k):
+    """Plain IVF search (exact distances over all probed members) on an IvfPqIndex."""
+    from vector_db_b200.indexing import IvfIndex
+    d, i, _ = IvfIndex.search_device(idx, _t(Q), n_probe, k)
+    return d.cpu().numpy(), i.cpu().numpy()

@@ -61,6 +61,8 @@ SIGNATURES = {
     "vdb_ivf_scan_workspace": (_sz, [_i, _i]),
     "vdb_ivf_scan": (_i, [_p, _i, _p, _i, _p, _p, _p, _p, _i, _p, _p, _i, _p, _p, _p, _p, _sz, _p]),
     "vdb_ivf_centroid_mean": (_i, [_p, _i, _p, _p, _i, _p, _p]),
+    "vdb_ivf_adc_workspace": (_sz, [_i, _i, _i]),
+    "vdb_ivf_adc_scan": (_i, [_p, _i, _p, _i, _p, _p, _p, _p, _i, _i, _p, _p, _p, _sz, _p]),
     "vdb_merge_topk": (_i, [_p, _p, _i, _i, _i, _i, _p, _p, _p]),
 }
 

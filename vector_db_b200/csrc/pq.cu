@@ -438,6 +438,110 @@ adc_finalize_kernel(const AdcFinArgs a) {
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// IVF-PQ: ADC restricted to the probed inverted lists.  Codes are stored LIST-MAJOR
+// (code of CSR position p at codes[p*m]), so a list is one contiguous byte run.  grid (kIvfAdcSplits, Q):
+// CTA (s, q) evaluates candidates [s*chunk, (s+1)*chunk) of query q's flattened candidate sequence (probe
+// rank major, list position minor, as ivf.cu), with the query's fixed-point LUT in shared memory in the
+// rotated conflict-free slot order of the full scan.  Keys are (d_int, sequence number).
+constexpr int kIvfAdcThreads = 256;
+constexpr int kIvfAdcSplits = 32;
+
+__device__ __forceinline__ int adc_find_probe(const int32_t* prefix, int n, int seq) {
+    int lo = 0, hi = n;                 // invariant: prefix[lo] <= seq < prefix[hi]
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (prefix[mid] <= seq) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+
+template <int MB>
+__global__ void __launch_bounds__(kIvfAdcThreads)
+ivf_adc_scan_kernel(const uint8_t* __restrict__ codes, int m, const uint32_t* __restrict__ lutq,
+                    const int32_t* __restrict__ list_ptr, const int32_t* __restrict__ probes,
+                    const int32_t* __restrict__ prefix_g, int n_probe, int R, int C, int chunk_min,
+                    u64* __restrict__ partial) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int qi = blockIdx.y, s = blockIdx.x;
+    const int total = __ldg(prefix_g + (size_t)qi * (n_probe + 1) + n_probe);
+    const int chunk = max(chunk_min, (total + kIvfAdcSplits - 1) / kIvfAdcSplits);
+    if (s * chunk >= total) return;
+    const int mb = (m + 7) >> 3;
+    u64* buf = reinterpret_cast<u64*>(smem_raw);                                // C
+    uint32_t* lutS = reinterpret_cast<uint32_t*>(buf + C);                      // mb * 2048
+    int32_t* prefix = reinterpret_cast<int32_t*>(lutS + (size_t)mb * 2048);     // n_probe + 1
+    int32_t* pbase = prefix + n_probe + 1;                                      // n_probe
+    __shared__ int cnt;
+    __shared__ u64 thr;
+    const int tid = threadIdx.x, rot = tid & 7;
+    for (int i = tid; i < mb * 2048; i += kIvfAdcThreads) {
+        const int j = i >> 8, c = i & 255;
+        lutS[((j >> 3) * 256 + c) * 8 + (j & 7)] = j < m ? lutq[((size_t)qi * m + j) * 256 + c] : 0u;
+    }
+    for (int p = tid; p <= n_probe; p += kIvfAdcThreads) prefix[p] = prefix_g[(size_t)qi * (n_probe + 1) + p];
+    for (int p = tid; p < n_probe; p += kIvfAdcThreads) pbase[p] = list_ptr[probes[(size_t)qi * n_probe + p]];
+    BlockSelect sel;
+    sel.init(buf, &cnt, &thr, C, R, kIvfAdcThreads);
+    __syncthreads();
+    const int begin = s * chunk, end = min(total, begin + chunk);
+    for (int base = begin; base < end; base += kIvfAdcThreads) {
+        const int seq = base + tid;
+        if (seq < end) {
+            const int p = adc_find_probe(prefix, n_probe, seq);
+            const int64_t pos = (int64_t)pbase[p] + (seq - prefix[p]);
+            uint32_t acc[1];
+            adc_row<1, MB>(codes + pos * m, m, mb, lutS, rot, acc);
+            sel.push(((u64)acc[0] << 32) | (u64)(uint32_t)seq);
+        }
+        sel.maybe_compact();
+    }
+    sel.finalize();
+    u64* dst = partial + ((size_t)qi * kIvfAdcSplits + s) * R;
+    for (int i = tid; i < R; i += kIvfAdcThreads) dst[i] = buf[i];
+}
+
+// R best (d_int, sequence) keys of the splits -> (float(d_int) * 2^-e, row).  One CTA per query.
+__global__ void __launch_bounds__(256)
+ivf_adc_merge_kernel(const u64* __restrict__ partial, int L, int R, int C, const int32_t* __restrict__ expo,
+                     const int32_t* __restrict__ list_ptr, const int32_t* __restrict__ list_rows,
+                     const int32_t* __restrict__ probes, const int32_t* __restrict__ prefix_g, int n_probe,
+                     float* __restrict__ out_d, int32_t* __restrict__ out_rows) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    u64* buf = reinterpret_cast<u64*>(smem_raw);
+    __shared__ int cnt;
+    __shared__ u64 thr;
+    const int qi = blockIdx.x;
+    BlockSelect sel;
+    sel.init(buf, &cnt, &thr, C, R, blockDim.x);
+    __syncthreads();
+    const u64* src = partial + (size_t)qi * L;
+    for (int base = 0; base < L; base += blockDim.x) {
+        const int i = base + threadIdx.x;
+        if (i < L) {
+            const u64 key = src[i];
+            if (key != VDB_KEY_MAX) sel.push(key);
+        }
+        sel.maybe_compact();
+    }
+    sel.finalize();
+    const int32_t* prefix = prefix_g + (size_t)qi * (n_probe + 1);
+    const int e = expo[qi];
+    for (int i = threadIdx.x; i < R; i += blockDim.x) {
+        const u64 key = buf[i];
+        const size_t o = (size_t)qi * R + i;
+        if (key == VDB_KEY_MAX) {
+            out_d[o] = INFINITY;
+            out_rows[o] = -1;
+        } else {
+            const int seq = (int)(uint32_t)(key & 0xFFFFFFFFull);
+            const int p = adc_find_probe(prefix, n_probe, seq);
+            out_d[o] = ldexpf((float)(uint32_t)(key >> 32), -e);
+            out_rows[o] = list_rows[list_ptr[probes[(size_t)qi * n_probe + p]] + (seq - prefix[p])];
+        }
+    }
+}
+
 struct AdcPlan {
     int G, C, S, groups, grid;
     int64_t slice_rows;
@@ -769,6 +873,65 @@ int vdb_pq_adc_topk(const uint8_t* codes, int64_t N, int m, const float* lut, in
     f.keys = partial; f.L = c.rescan.S * R; f.lens = nullptr; f.bad = nullptr; f.bad_count = nullptr;
     f.qsel = bad; f.qcount = badn;
     return launch_adc_finalize(f, Q, st);
+}
+
+size_t vdb_ivf_adc_workspace(int Q, int m, int R) {
+    if (Q <= 0 || m <= 0 || R <= 0) return 0;
+    return adc_lutq_bytes(Q, m) + adc_expo_bytes(Q) + (size_t)Q * kIvfAdcSplits * R * 8 + 256;
+}
+
+int vdb_ivf_adc_scan(const uint8_t* codes, int m, const float* lut, int Q, const int32_t* list_ptr,
+                     const int32_t* list_rows, const int32_t* probes, const int32_t* prefix, int n_probe, int R,
+                     float* out_d, int32_t* out_rows, void* ws, size_t ws_bytes, void* stream) {
+    VDB_REQUIRE(Q >= 0 && m > 0 && R > 0 && n_probe >= 1, VDB_ERR_INVALID, "vdb_ivf_adc_scan: bad shape");
+    VDB_REQUIRE(m <= 255, VDB_ERR_UNSUPPORTED, "m=%d > 255 overflows the 32-bit fixed-point sum", m);
+    VDB_REQUIRE(Q <= 65535 && n_probe <= 8192 && R <= 4096, VDB_ERR_UNSUPPORTED, "Q=%d n_probe=%d R=%d outside the envelope",
+                Q, n_probe, R);
+    if (Q == 0) return VDB_OK;
+    VDB_REQUIRE(codes && lut && list_ptr && list_rows && probes && prefix && out_d && out_rows, VDB_ERR_INVALID,
+                "vdb_ivf_adc_scan: null pointer");
+    const size_t head = adc_lutq_bytes(Q, m) + adc_expo_bytes(Q);
+    const size_t need = head + (size_t)Q * kIvfAdcSplits * R * 8;
+    VDB_REQUIRE(ws && ws_bytes >= need, VDB_ERR_WORKSPACE, "workspace %zu < %zu", ws_bytes, need);
+    VDB_REQUIRE((reinterpret_cast<uintptr_t>(ws) & 15) == 0, VDB_ERR_INVALID, "workspace must be 16-byte aligned");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    char* base = static_cast<char*>(ws);
+    uint32_t* lutq = reinterpret_cast<uint32_t*>(base);
+    int32_t* expo = reinterpret_cast<int32_t*>(base + adc_lutq_bytes(Q, m));
+    u64* partial = reinterpret_cast<u64*>(base + head);
+    adc_quantize_lut_kernel<<<Q, 256, 0, st>>>(lut, m * 256, lutq, expo);
+    VDB_CUDA(cudaMemsetAsync(partial, 0xFF, (size_t)Q * kIvfAdcSplits * R * 8, st));
+    const int mb = (m + 7) / 8;
+    const int C = select_capacity(R, kIvfAdcThreads);
+    const size_t smem = (size_t)C * 8 + (size_t)mb * 2048 * 4 + (size_t)(2 * n_probe + 1) * 4;
+    VDB_REQUIRE(smem <= (size_t)max_smem_optin() - 1024, VDB_ERR_UNSUPPORTED, "m=%d R=%d n_probe=%d do not fit shared memory",
+                m, R, n_probe);
+    const int chunk_min = Q >= 1024 ? 16384 : (Q >= 128 ? 4096 : 1024);
+    const bool a16 = (reinterpret_cast<uintptr_t>(codes) & 15) == 0, a8 = (reinterpret_cast<uintptr_t>(codes) & 7) == 0;
+#define VDB_IVFADC_CASE(MBV)                                                                                    \
+    {                                                                                                           \
+        auto kern = ivf_adc_scan_kernel<MBV>;                                                                   \
+        VDB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));           \
+        kern<<<dim3(kIvfAdcSplits, Q), kIvfAdcThreads, smem, st>>>(codes, m, lutq, list_ptr, probes, prefix, n_probe, R, C, \
+                                                                   chunk_min, partial);                         \
+    }
+    {
+        ProfScope prof(kProfAdcScan, st);
+        if (a16 && m == 16) VDB_IVFADC_CASE(2)
+        else if (a16 && m == 32) VDB_IVFADC_CASE(4)
+        else if (a16 && m == 48) VDB_IVFADC_CASE(6)
+        else if (a16 && m == 64) VDB_IVFADC_CASE(8)
+        else if (a8 && m == 8) VDB_IVFADC_CASE(1)
+        else VDB_IVFADC_CASE(0)
+    }
+#undef VDB_IVFADC_CASE
+    const int C2 = select_capacity(R, 256);
+    VDB_CUDA(cudaFuncSetAttribute(ivf_adc_merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, C2 * 8));
+    ivf_adc_merge_kernel<<<Q, 256, (size_t)C2 * 8, st>>>(partial, kIvfAdcSplits * R, R, C2, expo, list_ptr, list_rows, probes,
+                                                         prefix, n_probe, out_d, out_rows);
+    count_launch(3);
+    VDB_CUDA(cudaGetLastError());
+    return VDB_OK;
 }
 
 }  // extern "C"

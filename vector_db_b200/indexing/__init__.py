@@ -1,5 +1,5 @@
 from .exact import ExactIndex
 from .hnsw import HNSW
-from .ivf import IvfIndex
+from .ivf import IvfIndex, IvfPqIndex
 
-__all__ = ["HNSW", "ExactIndex", "IvfIndex"]
+__all__ = ["HNSW", "ExactIndex", "IvfIndex", "IvfPqIndex"]

@@ -311,3 +311,105 @@ class IvfIndex:
                     continue
             if keep:
                 self._vectors.append(keep, np.stack(rows))
+
+
+class IvfPqIndex(IvfIndex):
+    """IVF-PQ: the IVF coarse quantiser of :class:`IvfIndex` + product-quantised codes of
+    the raw vectors (``ProductQuantizationService`` sub-space layout, src/vector_db/inference/pq.py:48-62),
+    stored list-major next to the lists.  ``search_batch`` probes ``n_probe`` lists, takes the ``shortlist``
+    best by asymmetric distance (fixed-point ADC, the arithmetic of ``vdb_pq_adc_topk``) and re-scores them with
+    the exact fp32 L2 distance.  The reference has the two halves (ivf.py, pq.py) but not their combination."""
+
+    def __init__(self, k: int, chunks: int, pq_k: int = 256, storage: Optional[NodeStorage] = None,
+                 index_file: Optional[Union[str, Path]] = None, device=None):
+        super().__init__(k, storage=storage, index_file=index_file, device=device)
+        if chunks <= 0:
+            raise ValueError("k-means parameter and number of chunks should be positive")     # pq.py:24-25
+        if pq_k <= 0 or pq_k > 256:
+            raise ValueError("pq_k must be between 1 and 256 (uint8 codes)")
+        self.chunks = chunks
+        self.pq_k = pq_k
+        self.codebooks: Optional[torch.Tensor] = None      # [chunks, pq_k, dsub]
+        self._cb_lut: Optional[torch.Tensor] = None        # padded to 256 entries per sub-space
+        self._codes_lm: Optional[torch.Tensor] = None      # uint8 [n listed rows, chunks], CSR order
+        self._codes_for: Optional[torch.Tensor] = None     # the list_rows tensor _codes_lm was built for
+
+    def train_pq(self, iters: int = 25, train_rows: int = 100_000, init_rows: Optional[np.ndarray] = None,
+                 seed: int = 777) -> None:
+        """Lloyd rounds on a row sample, all sub-spaces per launch (``vdb_pq_kmeans_step``)."""
+        vec = self._vectors
+        if vec is None or vec.n == 0:
+            raise ValueError("Index must be built before training the product quantiser")
+        if vec.dim % self.chunks != 0:
+            raise ValueError("embedding dimension must be divisible by number of chunks")             # pq.py:28-29
+        n = vec.n
+        rng = np.random.default_rng(seed)
+        sample_rows = rng.choice(n, min(n, train_rows), replace=False)
+        sample = vec.vecs.index_select(0, torch.from_numpy(np.sort(sample_rows)).to(self._device)).contiguous()
+        if sample.shape[0] < self.pq_k:
+            raise ValueError(f"Need at least {self.pq_k} vectors to train {self.pq_k} centroids")
+        if init_rows is None:
+            init_rows = rng.choice(sample.shape[0], self.pq_k, replace=False)
+        dsub = vec.dim // self.chunks
+        init = sample.index_select(0, torch.from_numpy(np.asarray(init_rows, dtype=np.int64)).to(self._device))
+        cb = init.view(self.pq_k, self.chunks, dsub).permute(1, 0, 2).contiguous()
+        for _ in range(iters):
+            ops.pq_kmeans_step(sample, cb)
+        self.set_codebooks(cb)
+
+    def set_codebooks(self, codebooks) -> None:
+        cb = torch.as_tensor(np.asarray(codebooks, dtype=np.float32) if not torch.is_tensor(codebooks) else codebooks)
+        cb = cb.to(self._device, torch.float32).contiguous()
+        if cb.ndim != 3 or cb.shape[0] != self.chunks or cb.shape[1] != self.pq_k:
+            raise ValueError(f"codebooks must have shape ({self.chunks}, {self.pq_k}, dsub)")
+        self.codebooks = cb
+        if self.pq_k < 256:      # LUT rows have 256 entries; the padding repeats centroid 0 and is never referenced
+            pad = cb[:, :1, :].expand(self.chunks, 256 - self.pq_k, cb.shape[2])
+            self._cb_lut = torch.cat([cb, pad], dim=1).contiguous()
+        else:
+            self._cb_lut = cb
+        self._codes_lm = None
+
+    def _list_codes(self) -> torch.Tensor:
+        ptr, rows = self._csr()
+        if self._codes_lm is None or self._codes_for is not rows:
+            listed = self._vectors.vecs.index_select(0, rows.long())
+            self._codes_lm = ops.pq_encode(listed, self.codebooks)
+            self._codes_for = rows
+        return self._codes_lm
+
+    def search_device(self, q: torch.Tensor, n_probe: int, top_k: int, shortlist: Optional[int] = None,
+                      rerank: bool = True):
+        """(dist, ids, candidates enumerated).  With ``rerank`` the distances are exact non-squared L2 over the
+        ADC shortlist; without it they are the squared ADC estimates and ``top_k`` of them are returned."""
+        if self.codebooks is None:
+            raise ValueError("Product quantiser must be trained before searching (train_pq / set_codebooks)")
+        ptr, rows = self._csr()
+        vec = self._vectors
+        codes = self._list_codes()
+        cdist = ops.ivf_centroid_dist(q, self._centroids_dev)
+        probes, prefix = ops.ivf_probe(cdist, n_probe, ptr)
+        R = max(top_k, shortlist or top_k)
+        lut = ops.pq_lut(q.to(torch.float32).contiguous(), self._cb_lut)
+        d, cand = ops.ivf_adc_scan(codes, lut, ptr, rows, probes, prefix, R)
+        scanned = prefix[:, -1].to(torch.int64)
+        if rerank:
+            dd, ii = ops.rerank_f32(q, vec.vecs, cand, min(top_k, R), "l2", ids=vec.ids, n_rows=vec.n)
+            return dd, ii, scanned
+        ids = torch.where(cand >= 0, vec.ids[cand.clamp(min=0).long()], cand.long())
+        return d[:, :top_k], ids[:, :top_k], scanned
+
+    def search_batch(self, queries: np.ndarray, n_probe: int, top_k: int, shortlist: Optional[int] = None,
+                     rerank: bool = True) -> Tuple[np.ndarray, np.ndarray]:
+        if self.centroids is None:
+            raise ValueError("Index must be built before searching")
+        queries = np.ascontiguousarray(queries, dtype=np.float32)
+        if queries.ndim != 2 or queries.shape[1] != self.centroids.shape[1]:
+            raise ValueError(f"queries must have shape (Q, {self.centroids.shape[1]})")
+        if n_probe <= 0 or n_probe > self.k:
+            raise ValueError(f"n_probe must be between 1 and {self.k}")
+        with self._lock:
+            q = torch.from_numpy(queries).to(self._device)
+            d, i, scanned = self.search_device(q, n_probe, top_k, shortlist, rerank)
+            self.last_scanned = scanned.cpu().numpy()
+            return d.cpu().numpy(), i.cpu().numpy()

@@ -208,6 +208,26 @@ def ivf_centroid_mean(x: torch.Tensor, list_ptr: torch.Tensor, list_rows: torch.
                                        _lib.stream_ptr(x.device)))
 
 
+def ivf_adc_scan(codes_lm: torch.Tensor, lut: torch.Tensor, list_ptr: torch.Tensor, list_rows: torch.Tensor,
+                 probes: torch.Tensor, prefix: torch.Tensor, R: int):
+    """IVF-PQ: ADC over the probed lists (codes list-major) -> (d f32 [Q,R] squared estimates, rows i32 [Q,R])."""
+    if lut.shape[2] != 256:
+        raise ValueError("ADC scan needs 256-entry LUT rows (nbits=8); pad the codebooks")
+    Q, m = lut.shape[0], lut.shape[1]
+    n_probe = probes.shape[1]
+    dev = lut.device
+    out_d = torch.empty((Q, R), dtype=torch.float32, device=dev)
+    out_r = torch.empty((Q, R), dtype=torch.int32, device=dev)
+    lib = load()
+    for s in range(0, Q, 32768):
+        e = min(Q, s + 32768)
+        ws = _ws("ivf_adc", lib.vdb_ivf_adc_workspace(e - s, m, R), dev)
+        check(lib.vdb_ivf_adc_scan(ptr(codes_lm), m, ptr(lut[s:e]), e - s, ptr(list_ptr), ptr(list_rows), ptr(probes[s:e]),
+                                   ptr(prefix[s:e]), n_probe, R, ptr(out_d[s:e]), ptr(out_r[s:e]), ptr(ws), ws.numel(),
+                                   _lib.stream_ptr(dev)))
+    return out_d, out_r
+
+
 def merge_topk(d: torch.Tensor, i: torch.Tensor, descending: bool = False):
     """d,i [L,Q,k] (per-shard sorted lists) -> merged (d [Q,k], i [Q,k])."""
     L, Q, k = d.shape
