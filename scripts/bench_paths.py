@@ -149,13 +149,13 @@ def bench_hnsw(N=200_000, D=768, M=32, ef=128, Q=10_000):
 def bench_ivf(N=1_000_000, D=384, K=1024, Q=4096, iters=10):
     """IVF on clustered rows: train, then batched search at several n_probe with recall@10
     against the exact scan; roofline = bytes of the probed lists' rows / list-scan kernel time."""
-    from vector_db_b200.indexing import ExactIndex, IvfIndex
+    from vector_db_b200.indexing import ExactIndex, IvfIndex, IvfPqIndex
     g = torch.Generator(device=dev).manual_seed(1234)
     centres = torch.randn((1024, D), device=dev, generator=g)
     sigma = 0.15 * centres.norm(dim=1).mean() / (D ** 0.5)
     X = centres[torch.randint(0, 1024, (N,), device=dev, generator=g)] + sigma * torch.randn((N, D), device=dev, generator=g)
     Qd = centres[torch.randint(0, 1024, (Q,), device=dev, generator=g)] + sigma * torch.randn((Q, D), device=dev, generator=g)
-    idx = IvfIndex(k=K)
+    idx = IvfPqIndex(k=K, chunks=D // 8)
     Xh = X.cpu().numpy()
     t0 = time.perf_counter()
     idx.build_from_arrays(range(N), Xh, iters=iters, init_rows=np.random.default_rng(777).choice(N, K, replace=False))
@@ -184,7 +184,7 @@ def bench_ivf(N=1_000_000, D=384, K=1024, Q=4096, iters=10):
     for n_probe in (1, 4, 16, 64):
         if n_probe > K:
             break
-        (d, i, scanned), k_ms, step_ms = _time_slot("ivf_scan", lambda: idx.search_device(Qd, n_probe, 10), iters=5, warm=2)
+        (d, i, scanned), k_ms, step_ms = _time_slot("ivf_scan", lambda: IvfIndex.search_device(idx, Qd, n_probe, 10), iters=5, warm=2)
         got = i.cpu().tolist()
         recall = sum(len(truth[j] & set(got[j])) for j in range(Q)) / (Q * 10)
         alg = float(scanned.sum().item()) * (D * 4 + 4)
@@ -193,7 +193,27 @@ def bench_ivf(N=1_000_000, D=384, K=1024, Q=4096, iters=10):
                      "rows_scanned_per_query": float(scanned.float().mean().item()),
                      "roofline": {"bound": "hbm", "achieved": alg / (k_ms * 1e-3) / 1e9, "peak": HBM, "unit": "GB/s",
                                   "frac": alg / (k_ms * 1e-3) / 1e9 / HBM, "algorithmic_bytes": alg}})
+    # IVF-PQ on the same lists: m = D/8 sub-spaces, ADC shortlist + exact rerank
+    t0 = time.perf_counter()
+    idx.train_pq(iters=25)
+    idx._list_codes()
+    torch.cuda.synchronize()
+    pq_train_s = time.perf_counter() - t0
+    pq_rows = []
+    for n_probe, R in ((4, 100), (4, 1000), (16, 1000), (64, 1000)):
+        if n_probe > K:
+            continue
+        (d, i, scanned), k_ms, step_ms = _time_slot("adc_scan", lambda: idx.search_device(Qd, n_probe, 10, shortlist=R), iters=5, warm=2)
+        got = i.cpu().tolist()
+        recall = sum(len(truth[j] & set(got[j])) for j in range(Q)) / (Q * 10)
+        alg = float(scanned.sum().item()) * (D // 8)
+        pq_rows.append({"n_probe": n_probe, "shortlist": R, "recall_at_10": round(recall, 4), "adc_kernel_ms": round(k_ms, 3),
+                        "step_ms": round(step_ms, 3), "qps": round(Q / (step_ms * 1e-3), 1),
+                        "rows_scanned_per_query": float(scanned.float().mean().item()),
+                        "roofline": {"bound": "hbm", "achieved": alg / (k_ms * 1e-3) / 1e9, "peak": HBM, "unit": "GB/s",
+                                     "frac": alg / (k_ms * 1e-3) / 1e9 / HBM, "algorithmic_bytes": alg}})
     print(json.dumps({"path": "ivf_search", "N": N, "D": D, "K": K, "Q": Q, "train_iters": iters, "build_s": build_s,
+                      "pq_train_encode_s": pq_train_s, "ivf_pq_rows": pq_rows,
                       "centroid_dist_ms": cdist_ms, "probe16_ms": probe_ms,
                       "list_size_min_mean_max": [min(sizes), sum(sizes) / len(sizes), max(sizes)], "rows": rows}), flush=True)
 
