@@ -111,7 +111,9 @@ int vdb_exact_topk_tc(const float* q /*[dev] Q*D fp32*/, int Q,
                       float db_max_norm /* max |x| over the rows, used by the L2 certificate */,
                       const int64_t* ids /*[dev] or NULL*/, int64_t N, int D, int k, int metric,
                       float* out_d, int64_t* out_i,
-                      int32_t* out_uncertified /*[dev] Q+1: count, then the query indices that could not be certified*/,
+                      int32_t* out_uncertified /*[dev] Q+1: count, then the indices of the queries the certificate rejected;
+                         those queries were re-scanned by the exact fp32 kernel inside this call (device-side list, no host
+                         round trip), so out_d / out_i are exact for every query on return*/,
                       void* ws, size_t ws_bytes, void* stream);
 /* bench/debug only: bit 0 = skip the whole epilogue of the coarse pass, bit 1 = skip only its threshold
  * test and bin-list inserts (results are then invalid) */

@@ -21,7 +21,12 @@ template <int TQ, int METRIC>
 __global__ void __launch_bounds__(kScanThreads)
 exact_scan_f32_kernel(const float* __restrict__ q, int Q, const float* __restrict__ db,
                       const uint32_t* __restrict__ row_mask, int64_t N, int D, int k, int C,
-                      int64_t slice_rows, u64* __restrict__ partial, int S) {
+                      int64_t slice_rows, u64* __restrict__ partial, int S, const int32_t* __restrict__ qsel,
+                      const int32_t* __restrict__ qcount) {
+    // subset mode: only the queries qsel[0 .. *qcount) are scanned (count read on the device, so the caller
+    // never synchronises); query SLOT b = position in qsel indexes `partial`
+    if (qsel) Q = min(Q, __ldg(qcount));
+    if ((int)blockIdx.x * TQ >= Q) return;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     u64* sel_buf = reinterpret_cast<u64*>(smem_raw);                      // TQ * C
     u64* sel_thr = sel_buf + (size_t)TQ * C;                              // TQ (padded to even)
@@ -39,7 +44,7 @@ exact_scan_f32_kernel(const float* __restrict__ q, int Q, const float* __restric
 
     for (int i = tid; i < TQ * D; i += kScanThreads) {
         int g = i / D;
-        qs[i] = (g < nq) ? q[(size_t)(q0 + g) * D + (i - g * D)] : 0.f;
+        qs[i] = (g < nq) ? q[(size_t)(qsel ? __ldg(qsel + q0 + g) : q0 + g) * D + (i - g * D)] : 0.f;
     }
     BlockSelect sel[TQ];
 #pragma unroll
@@ -154,8 +159,14 @@ exact_scan_f32_kernel(const float* __restrict__ q, int Q, const float* __restric
 // transform: 0 = score as is, 1 = negate (cosine similarities were keyed on -sim).
 __global__ void __launch_bounds__(256)
 finalize_keys_kernel(const u64* __restrict__ keys, int L, int k, int C, const int64_t* __restrict__ ids,
-                     int64_t idx_offset, int negate, float* __restrict__ out_d, int64_t* __restrict__ out_i) {
+                     int64_t idx_offset, int negate, float* __restrict__ out_d, int64_t* __restrict__ out_i,
+                     const int32_t* __restrict__ qsel, const int32_t* __restrict__ qcount) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
+    int qo = blockIdx.x;                              // output row; subset mode: slot b -> query qsel[b]
+    if (qsel) {
+        if ((int)blockIdx.x >= __ldg(qcount)) return;
+        qo = __ldg(qsel + blockIdx.x);
+    }
     u64* buf = reinterpret_cast<u64*>(smem_raw);
     __shared__ int cnt;
     __shared__ u64 thr;
@@ -174,7 +185,7 @@ finalize_keys_kernel(const u64* __restrict__ keys, int L, int k, int C, const in
     sel.finalize();
     for (int i = threadIdx.x; i < k; i += blockDim.x) {
         u64 key = buf[i];
-        size_t o = (size_t)blockIdx.x * k + i;
+        size_t o = (size_t)qo * k + i;
         if (key == VDB_KEY_MAX) {
             out_d[o] = negate ? -INFINITY : INFINITY;
             out_i[o] = -1;
@@ -342,13 +353,13 @@ static bool plan_scan(int Q, int64_t N, int D, int k, ScanPlan* p) {
 }
 
 int finalize_keys(const u64* keys, int Q, int L, int k, const int64_t* ids, int64_t idx_offset, int negate,
-                  float* out_d, int64_t* out_i, cudaStream_t st) {
+                  float* out_d, int64_t* out_i, cudaStream_t st, const int32_t* qsel, const int32_t* qcount) {
     const int C = select_capacity(k, 256);
     size_t smem = (size_t)C * 8;
     VDB_REQUIRE(smem <= (size_t)max_smem_optin() - 1024, VDB_ERR_UNSUPPORTED, "top-k too large for finalize (k=%d)", k);
     VDB_CUDA(cudaFuncSetAttribute(finalize_keys_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     ProfScope prof(kProfFinalize, st);
-    finalize_keys_kernel<<<Q, 256, smem, st>>>(keys, L, k, C, ids, idx_offset, negate, out_d, out_i);
+    finalize_keys_kernel<<<Q, 256, smem, st>>>(keys, L, k, C, ids, idx_offset, negate, out_d, out_i, qsel, qcount);
     count_launch(1);
     VDB_CUDA(cudaGetLastError());
     return VDB_OK;
@@ -356,15 +367,44 @@ int finalize_keys(const u64* keys, int Q, int L, int k, const int64_t* ids, int6
 
 template <int TQ, int METRIC>
 static int launch_scan(const ScanPlan& p, const float* q, int Q, const float* db, const uint32_t* mask, int64_t N,
-                       int D, int k, u64* partial, cudaStream_t st) {
+                       int D, int k, u64* partial, cudaStream_t st, const int32_t* qsel = nullptr,
+                       const int32_t* qcount = nullptr) {
     auto kern = exact_scan_f32_kernel<TQ, METRIC>;
     VDB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem));
     dim3 grid(p.groups, p.slices);
     ProfScope prof(kProfExactF32, st);
-    kern<<<grid, kScanThreads, p.smem, st>>>(q, Q, db, mask, N, D, k, p.C, p.slice_rows, partial, p.slices);
+    kern<<<grid, kScanThreads, p.smem, st>>>(q, Q, db, mask, N, D, k, p.C, p.slice_rows, partial, p.slices, qsel, qcount);
     count_launch(1);
     VDB_CUDA(cudaGetLastError());
     return VDB_OK;
+}
+
+size_t exact_f32_subset_workspace(int Q, int64_t N, int D, int k) {
+    ScanPlan p;
+    if (Q <= 0 || !plan_scan(Q, N, D, k, &p)) return 0;
+    return (size_t)Q * p.slices * k * 8;
+}
+
+// Exact fp32 scan of the queries qsel[0 .. *qcount) only (device-side list), results written to their rows of
+// out_d / out_i; the grid covers the worst case (all Q) and CTAs past the count exit at once.
+int exact_f32_subset(const float* q, int Q, const float* db, const int64_t* ids, int64_t N, int D, int k, int metric,
+                     const int32_t* qsel, const int32_t* qcount, float* out_d, int64_t* out_i, void* ws, size_t ws_bytes,
+                     cudaStream_t st) {
+    ScanPlan p;
+    VDB_REQUIRE(plan_scan(Q, N, D, k, &p), VDB_ERR_UNSUPPORTED, "D=%d k=%d does not fit shared memory", D, k);
+    const size_t need = (size_t)Q * p.slices * k * 8;
+    VDB_REQUIRE(ws && ws_bytes >= need, VDB_ERR_WORKSPACE, "workspace %zu < %zu", ws_bytes, need);
+    u64* partial = static_cast<u64*>(ws);
+    int rc;
+#define VDB_LAUNCH(TQ)                                                                                                    \
+    rc = (metric == VDB_METRIC_L2) ? launch_scan<TQ, VDB_METRIC_L2>(p, q, Q, db, nullptr, N, D, k, partial, st, qsel, qcount) \
+                                   : launch_scan<TQ, VDB_METRIC_COSINE>(p, q, Q, db, nullptr, N, D, k, partial, st, qsel, qcount)
+    if (p.tq == 16) { VDB_LAUNCH(16); }
+    else if (p.tq == 4) { VDB_LAUNCH(4); }
+    else { VDB_LAUNCH(1); }
+#undef VDB_LAUNCH
+    if (rc) return rc;
+    return finalize_keys(partial, Q, p.slices * k, k, ids, 0, metric == VDB_METRIC_COSINE, out_d, out_i, st, qsel, qcount);
 }
 
 }  // namespace vdb

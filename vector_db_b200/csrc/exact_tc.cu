@@ -504,10 +504,10 @@ static bool plan_tc(int Q, int64_t N, int D, int k, int metric, TcPlan* p) {
 }
 
 struct TcWorkspace {
-    size_t qbf16, partial, cand, tau, total;
+    size_t qbf16, partial, cand, tau, rescan, rescan_bytes, total;
 };
 
-static TcWorkspace tc_workspace(const TcPlan& p, int Q) {
+static TcWorkspace tc_workspace(const TcPlan& p, int Q, int64_t N, int D, int k) {
     TcWorkspace w;
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
@@ -515,6 +515,8 @@ static TcWorkspace tc_workspace(const TcPlan& p, int Q) {
     w.partial = take((size_t)Q * p.S * kGroups * kNBLMax * 8);
     w.cand = take((size_t)Q * kNBFinal * kBin * 4);
     w.tau = take((size_t)Q * 4);
+    w.rescan_bytes = exact_f32_subset_workspace(Q, N, D, k);      // fp32 rescan of uncertified queries
+    w.rescan = take(w.rescan_bytes);
     w.total = off;
     return w;
 }
@@ -552,7 +554,7 @@ int vdb_tc_prepare_rows(const float* vecs, int64_t N, int D, int metric, float* 
 size_t vdb_exact_topk_tc_workspace(int Q, int64_t N, int D, int k, int metric) {
     TcPlan p;
     if (!plan_tc(Q, N, D, k, metric, &p)) return 0;
-    return tc_workspace(p, Q).total;
+    return tc_workspace(p, Q, N, D, k).total;
 }
 
 int vdb_exact_topk_tc(const float* q, int Q, const float* db, const void* mirror, float db_max_norm,
@@ -565,7 +567,7 @@ int vdb_exact_topk_tc(const float* q, int Q, const float* db, const void* mirror
     VDB_REQUIRE(N < (1ll << 31), VDB_ERR_UNSUPPORTED, "N too large for int32 candidate rows");
     TcPlan p;
     VDB_REQUIRE(plan_tc(Q, N, D, k, metric, &p), VDB_ERR_UNSUPPORTED, "tensor-core scan does not support D=%d k=%d", D, k);
-    const TcWorkspace w = tc_workspace(p, Q);
+    const TcWorkspace w = tc_workspace(p, Q, N, D, k);
     VDB_REQUIRE(ws_bytes >= w.total, VDB_ERR_WORKSPACE, "workspace %zu < %zu", ws_bytes, w.total);
     VDB_REQUIRE((reinterpret_cast<uintptr_t>(mirror) & 15) == 0 && (reinterpret_cast<uintptr_t>(ws) & 255) == 0,
                 VDB_ERR_INVALID, "operand mirror / workspace must be 16 / 256-byte aligned");
@@ -620,7 +622,9 @@ int vdb_exact_topk_tc(const float* q, int Q, const float* db, const void* mirror
         certify_kernel<VDB_METRIC_COSINE><<<blocks, warps_per_block * 32, 0, st>>>(q, Q, D, k, out_d, out_i, tau, db_max_norm, out_uncertified);
     count_launch(1);
     VDB_CUDA(cudaGetLastError());
-    return VDB_OK;
+    // queries the certificate rejected: exact fp32 scan, driven by the device-side list (no host round trip)
+    return exact_f32_subset(q, Q, db, ids, N, D, k, metric, out_uncertified + 1, out_uncertified, out_d, out_i,
+                            base + w.rescan, w.rescan_bytes, st);
 }
 
 }  // extern "C"

@@ -24,7 +24,12 @@ class ExactIndex:
         self.engine = engine          # "auto" | "f32" | "tc"
         self.store = DeviceVectors(dim, device)
         self._pin = None
-        self.last_uncertified = 0     # queries of the last tensor-core search that fell back to the fp32 scan
+        self._last_uncertified = 0    # int or 0-dim device tensor (read lazily: reading synchronises)
+
+    @property
+    def last_uncertified(self) -> int:
+        """Queries of the last tensor-core search that the certificate rejected (re-scanned in fp32)."""
+        return int(self._last_uncertified)
 
     # -- population -----------------------------------------------------------------------------
     def add(self, ids: Sequence[int], vectors: np.ndarray) -> None:
@@ -48,7 +53,7 @@ class ExactIndex:
             raise ValueError("tensor-core engine does not support this shape / filter")
         if use_tc:
             mir, max_norm = st.prepared(self.metric)
-            d, i, self.last_uncertified = ops.exact_topk_tc(q, st.vecs, mir, max_norm, k, self.metric, ids=st.ids,
+            d, i, self._last_uncertified = ops.exact_topk_tc(q, st.vecs, mir, max_norm, k, self.metric, ids=st.ids,
                                                             n_rows=st.n, return_uncertified=True)
             return d, i
         return ops.exact_topk_f32(q, st.vecs, k, self.metric, ids=st.ids, row_mask=mask, n_rows=st.n)

@@ -299,7 +299,9 @@ def exact_topk_tc(q: torch.Tensor, db: torch.Tensor, mirror: torch.Tensor, max_n
                   return_uncertified: bool = False):
     """Exact top-k through the tensor-core coarse scan + fp32 rerank + certificate.  `mirror` comes
     from tc_prepare_rows(db, metric).  Queries the certificate rejects are re-run through the exact
-    fp32 scan, so the result is always exact.  Synchronises once (reads the uncertified count)."""
+    fp32 scan inside the same library call (device-side list), so the result is always exact and the
+    call never synchronises.  With ``return_uncertified`` the third value is a 0-dim int32 DEVICE
+    tensor holding the number of such queries (reading it synchronises)."""
     q = _f32(q, "q")
     Q, D = q.shape
     N = db.shape[0] if n_rows is None else int(n_rows)
@@ -317,12 +319,6 @@ def exact_topk_tc(q: torch.Tensor, db: torch.Tensor, mirror: torch.Tensor, max_n
     ws = _ws("exact_tc", nbytes, dev)
     check(lib.vdb_exact_topk_tc(ptr(q), Q, ptr(db), ptr(mirror), float(max_norm), ptr(ids), N, D, k, m,
                                 ptr(out_d), ptr(out_i), ptr(uncert), ptr(ws), ws.numel(), _lib.stream_ptr(dev)))
-    n_bad = int(uncert[0].item())
-    if n_bad:
-        bad = uncert[1:1 + n_bad].long()
-        fd, fi = exact_topk_f32(q.index_select(0, bad), db, k, m, ids=ids, n_rows=N)
-        out_d.index_copy_(0, bad, fd)
-        out_i.index_copy_(0, bad, fi)
     if return_uncertified:
-        return out_d, out_i, n_bad
+        return out_d, out_i, uncert[0]
     return out_d, out_i
