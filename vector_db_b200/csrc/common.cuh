@@ -175,7 +175,7 @@ __host__ __device__ __forceinline__ int select_capacity(int R, int burst) {
 // (exact_f32.cu) select the k best of L keys per query and translate them to (value, id)
 int finalize_keys(const u64* keys, int Q, int L, int k, const int64_t* ids, int64_t idx_offset, int negate,
                   float* out_d, int64_t* out_i, cudaStream_t st, const int32_t* qsel = nullptr,
-                  const int32_t* qcount = nullptr);
+                  const int32_t* qcount = nullptr, int sub_tq = 0, int sub_grid = 0, int64_t sub_N = 0);
 // (exact_f32.cu) exact fp32 scan of a device-side list of queries (the tensor-core scan's uncertified ones)
 size_t exact_f32_subset_workspace(int Q, int64_t N, int D, int k);
 int exact_f32_subset(const float* q, int Q, const float* db, const int64_t* ids, int64_t N, int D, int k, int metric,

@@ -13,6 +13,32 @@ constexpr int kScanWarps = kScanThreads / 32;
 constexpr int kCheckEvery = 16;                       // row batches between compaction checks
 constexpr int kScanBurst = kScanWarps * kCheckEvery;  // max pushes per query between checks
 
+// Subset mode (device-side list of queries, e.g. the tensor-core scan's uncertified ones): the number of
+// queries is only known on the device, so the slicing is derived there -- few queries get many row slices
+// (all CTAs busy), many queries get few.  Units = groups * slices <= grid + groups, which bounds `partial`.
+struct SubsetPlan { int groups, slices; int64_t slice_rows; };
+__host__ __device__ inline SubsetPlan subset_plan(int count, int tq, int grid, int64_t N) {
+    SubsetPlan p;
+    p.groups = (count + tq - 1) / tq;
+    if (p.groups < 1) p.groups = 1;
+    int64_t slices = (grid + p.groups - 1) / p.groups;
+    int64_t max_slices = (N + 2047) / 2048;
+    if (max_slices < 1) max_slices = 1;
+    if (slices > max_slices) slices = max_slices;
+    if (slices < 1) slices = 1;
+    p.slice_rows = (N + slices - 1) / slices;
+    p.slice_rows = (p.slice_rows + 7) / 8 * 8;          // multiple of the warps per CTA
+    if (p.slice_rows < 8) p.slice_rows = 8;
+    p.slices = (int)((N + p.slice_rows - 1) / p.slice_rows);
+    if (p.slices < 1) p.slices = 1;
+    return p;
+}
+
+static int subset_grid() { return 4 * sm_count(); }
+// queries-per-CTA tile of the subset scan as a function of the (device-side) count: a 16-query tile spends 16x the
+// shared-memory reads on a single uncertified query, so small counts get narrow tiles and more row slices
+__host__ __device__ inline int subset_tq(int count) { return count <= 2 ? 1 : (count <= 16 ? 4 : 16); }
+
 // One CTA = TQ queries (resident in shared memory) x one slice of database rows.  Each warp owns a
 // row at a time: lanes stride the row with 128-bit loads, accumulate TQ partial sums against the
 // shared-memory queries, shuffle-reduce, and lane g pushes query g's (score,row) key into that
@@ -24,9 +50,17 @@ exact_scan_f32_kernel(const float* __restrict__ q, int Q, const float* __restric
                       int64_t slice_rows, u64* __restrict__ partial, int S, const int32_t* __restrict__ qsel,
                       const int32_t* __restrict__ qcount) {
     // subset mode: only the queries qsel[0 .. *qcount) are scanned (count read on the device, so the caller
-    // never synchronises); query SLOT b = position in qsel indexes `partial`
-    if (qsel) Q = min(Q, __ldg(qcount));
-    if ((int)blockIdx.x * TQ >= Q) return;
+    // never synchronises); the grid is 1-D and walks (group, slice) units of the device-side plan; query SLOT
+    // b = position in qsel indexes `partial`
+    int n_units = 1;
+    if (qsel) {
+        Q = min(Q, __ldg(qcount));
+        if (Q <= 0 || subset_tq(Q) != TQ) return;           // one launch per tile width; the count picks which one runs
+        const SubsetPlan sp = subset_plan(Q, TQ, (int)gridDim.x, N);
+        S = sp.slices;
+        slice_rows = sp.slice_rows;
+        n_units = sp.groups * sp.slices;
+    }
     extern __shared__ __align__(16) unsigned char smem_raw[];
     u64* sel_buf = reinterpret_cast<u64*>(smem_raw);                      // TQ * C
     u64* sel_thr = sel_buf + (size_t)TQ * C;                              // TQ (padded to even)
@@ -36,11 +70,13 @@ exact_scan_f32_kernel(const float* __restrict__ q, int Q, const float* __restric
     __shared__ unsigned compact_mask;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int q0 = blockIdx.x * TQ;
+    for (int unit = qsel ? (int)blockIdx.x : 0; unit < n_units; unit += qsel ? (int)gridDim.x : 1) {
+    const int q0 = (qsel ? unit / S : (int)blockIdx.x) * TQ;
     const int nq = min(TQ, Q - q0);
-    const int s = blockIdx.y;
+    const int s = qsel ? unit % S : (int)blockIdx.y;
     const int64_t r_begin = (int64_t)s * slice_rows;
     const int64_t r_end = min(N, r_begin + slice_rows);
+    __syncthreads();                                  // previous unit drained before its shared state is reset
 
     for (int i = tid; i < TQ * D; i += kScanThreads) {
         int g = i / D;
@@ -153,6 +189,7 @@ exact_scan_f32_kernel(const float* __restrict__ q, int Q, const float* __restric
             for (int i = tid; i < k; i += kScanThreads) dst[i] = sel_buf[(size_t)g * C + i];
         }
     }
+    }   // unit loop
 }
 
 // Select the k best of L keys per query and translate to (value, id).  One CTA per query.
@@ -160,12 +197,15 @@ exact_scan_f32_kernel(const float* __restrict__ q, int Q, const float* __restric
 __global__ void __launch_bounds__(256)
 finalize_keys_kernel(const u64* __restrict__ keys, int L, int k, int C, const int64_t* __restrict__ ids,
                      int64_t idx_offset, int negate, float* __restrict__ out_d, int64_t* __restrict__ out_i,
-                     const int32_t* __restrict__ qsel, const int32_t* __restrict__ qcount) {
+                     const int32_t* __restrict__ qsel, const int32_t* __restrict__ qcount, int sub_tq, int sub_grid,
+                     int64_t sub_N) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     int qo = blockIdx.x;                              // output row; subset mode: slot b -> query qsel[b]
     if (qsel) {
-        if ((int)blockIdx.x >= __ldg(qcount)) return;
+        const int count = __ldg(qcount);
+        if ((int)blockIdx.x >= count) return;
         qo = __ldg(qsel + blockIdx.x);
+        L = subset_plan(count, subset_tq(count), sub_grid, sub_N).slices * k;      // the scan's device-side slicing
     }
     u64* buf = reinterpret_cast<u64*>(smem_raw);
     __shared__ int cnt;
@@ -353,13 +393,15 @@ static bool plan_scan(int Q, int64_t N, int D, int k, ScanPlan* p) {
 }
 
 int finalize_keys(const u64* keys, int Q, int L, int k, const int64_t* ids, int64_t idx_offset, int negate,
-                  float* out_d, int64_t* out_i, cudaStream_t st, const int32_t* qsel, const int32_t* qcount) {
+                  float* out_d, int64_t* out_i, cudaStream_t st, const int32_t* qsel, const int32_t* qcount, int sub_tq,
+                  int sub_grid, int64_t sub_N) {
     const int C = select_capacity(k, 256);
     size_t smem = (size_t)C * 8;
     VDB_REQUIRE(smem <= (size_t)max_smem_optin() - 1024, VDB_ERR_UNSUPPORTED, "top-k too large for finalize (k=%d)", k);
     VDB_CUDA(cudaFuncSetAttribute(finalize_keys_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     ProfScope prof(kProfFinalize, st);
-    finalize_keys_kernel<<<Q, 256, smem, st>>>(keys, L, k, C, ids, idx_offset, negate, out_d, out_i, qsel, qcount);
+    finalize_keys_kernel<<<Q, 256, smem, st>>>(keys, L, k, C, ids, idx_offset, negate, out_d, out_i, qsel, qcount, sub_tq,
+                                               sub_grid, sub_N);
     count_launch(1);
     VDB_CUDA(cudaGetLastError());
     return VDB_OK;
@@ -372,6 +414,7 @@ static int launch_scan(const ScanPlan& p, const float* q, int Q, const float* db
     auto kern = exact_scan_f32_kernel<TQ, METRIC>;
     VDB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem));
     dim3 grid(p.groups, p.slices);
+    if (qsel) grid = dim3(subset_grid(), 1);
     ProfScope prof(kProfExactF32, st);
     kern<<<grid, kScanThreads, p.smem, st>>>(q, Q, db, mask, N, D, k, p.C, p.slice_rows, partial, p.slices, qsel, qcount);
     count_launch(1);
@@ -382,7 +425,8 @@ static int launch_scan(const ScanPlan& p, const float* q, int Q, const float* db
 size_t exact_f32_subset_workspace(int Q, int64_t N, int D, int k) {
     ScanPlan p;
     if (Q <= 0 || !plan_scan(Q, N, D, k, &p)) return 0;
-    return (size_t)Q * p.slices * k * 8;
+    // units = groups * slices <= grid + groups for every possible count (subset_plan), TQ <= 16 slots per group
+    return ((size_t)16 * subset_grid() + (size_t)Q + 16) * k * 8;
 }
 
 // Exact fp32 scan of the queries qsel[0 .. *qcount) only (device-side list), results written to their rows of
@@ -392,19 +436,28 @@ int exact_f32_subset(const float* q, int Q, const float* db, const int64_t* ids,
                      cudaStream_t st) {
     ScanPlan p;
     VDB_REQUIRE(plan_scan(Q, N, D, k, &p), VDB_ERR_UNSUPPORTED, "D=%d k=%d does not fit shared memory", D, k);
-    const size_t need = (size_t)Q * p.slices * k * 8;
+    const size_t need = exact_f32_subset_workspace(Q, N, D, k);
     VDB_REQUIRE(ws && ws_bytes >= need, VDB_ERR_WORKSPACE, "workspace %zu < %zu", ws_bytes, need);
     u64* partial = static_cast<u64*>(ws);
-    int rc;
-#define VDB_LAUNCH(TQ)                                                                                                    \
-    rc = (metric == VDB_METRIC_L2) ? launch_scan<TQ, VDB_METRIC_L2>(p, q, Q, db, nullptr, N, D, k, partial, st, qsel, qcount) \
-                                   : launch_scan<TQ, VDB_METRIC_COSINE>(p, q, Q, db, nullptr, N, D, k, partial, st, qsel, qcount)
-    if (p.tq == 16) { VDB_LAUNCH(16); }
-    else if (p.tq == 4) { VDB_LAUNCH(4); }
-    else { VDB_LAUNCH(1); }
+    const int tqs[3] = {1, 4, 16};
+    for (int t = 0; t < 3; ++t) {
+        ScanPlan pt = p;
+        pt.tq = tqs[t];
+        pt.smem = (size_t)pt.tq * p.C * 8 + (size_t)((pt.tq + 1) & ~1) * 8 + (size_t)pt.tq * D * 4 + (size_t)pt.tq * 8 + 16;
+        VDB_REQUIRE(pt.smem <= (size_t)max_smem_optin() - 1024, VDB_ERR_UNSUPPORTED,
+                    "subset scan: the %d-query tile does not fit shared memory (D=%d k=%d)", pt.tq, D, k);
+        int rc;
+#define VDB_LAUNCH(TQ)                                                                                                     \
+    rc = (metric == VDB_METRIC_L2) ? launch_scan<TQ, VDB_METRIC_L2>(pt, q, Q, db, nullptr, N, D, k, partial, st, qsel, qcount) \
+                                   : launch_scan<TQ, VDB_METRIC_COSINE>(pt, q, Q, db, nullptr, N, D, k, partial, st, qsel, qcount)
+        if (pt.tq == 16) { VDB_LAUNCH(16); }
+        else if (pt.tq == 4) { VDB_LAUNCH(4); }
+        else { VDB_LAUNCH(1); }
 #undef VDB_LAUNCH
-    if (rc) return rc;
-    return finalize_keys(partial, Q, p.slices * k, k, ids, 0, metric == VDB_METRIC_COSINE, out_d, out_i, st, qsel, qcount);
+        if (rc) return rc;
+    }
+    return finalize_keys(partial, Q, p.slices * k, k, ids, 0, metric == VDB_METRIC_COSINE, out_d, out_i, st, qsel, qcount,
+                         0, subset_grid(), N);
 }
 
 }  // namespace vdb
