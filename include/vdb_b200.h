@@ -147,12 +147,17 @@ int vdb_pq_kmeans_step(const float* x, int64_t N, int D, int m, int K, float* co
  * lut[q][j][c] = sum_t (q_jt - C_j[c][t])^2, fp32 [Q][m][K]. */
 int vdb_pq_lut(const float* q /*[dev] Q*D*/, int Q, int D, int m, int K, const float* codebooks,
                float* lut /*[dev] Q*m*K*/, void* stream);
-/* d(q,i) = sum_j lut[q][j][codes[i][j]] (fp32, j ascending); the R smallest by (d, row).
- * K must be 256 (nbits=8).  out_i are row indices (int64), or ids[row] when ids != NULL. */
+/* d(q,i) = sum_j lut[q][j][codes[i][j]] on a per-query fixed-point table (lutq = rint(lut * 2^e),
+ * e = 23 - exponent(max entry of the query's table); exact integer sums, so the result does not depend on
+ * the summation order and is bit-reproducible); the R smallest by (d_int, row), reported as
+ * float(d_int) * 2^-e.  K must be 256 (nbits=8), m <= 255.  out_i are row indices (int64), or ids[row]
+ * when ids != NULL.  row_mask (nullable): bitmap over rows, a cleared bit skips the row -- tombstones and
+ * the metadata pre-filter (filter_ids of src/vector_db/indexing/hnsw.py:96,127) -- the result is exact over
+ * the remaining rows. */
 size_t vdb_pq_adc_topk_workspace(int Q, int64_t N, int m, int R);
 int vdb_pq_adc_topk(const uint8_t* codes /*[dev] N*m*/, int64_t N, int m, const float* lut, int Q, int R,
-                    const int64_t* ids, float* out_d /*[dev] Q*R*/, int64_t* out_i /*[dev] Q*R*/,
-                    void* ws, size_t ws_bytes, void* stream);
+                    const int64_t* ids, const uint32_t* row_mask /*[dev] nullable*/, float* out_d /*[dev] Q*R*/,
+                    int64_t* out_i /*[dev] Q*R*/, void* ws, size_t ws_bytes, void* stream);
 
 /* ---- a4/a5/a6 batched HNSW search -------------------------------------------------------------
  * One CTA per query: greedy descent on levels max_level..1 (hnsw.py:289-328, strict '<'), then the

@@ -211,3 +211,17 @@ def IvfIndex_search(idx, Q, n_probe, k):
     from vector_db_b200.indexing import IvfIndex
     d, i, _ = IvfIndex.search_device(idx, _t(Q), n_probe, k)
     return d.cpu().numpy(), i.cpu().numpy()
+
+
+def test_ivf_filter_ids_restricts_results(golden_dir):
+    """filter_ids (the metadata pre-filter of services/storage_service.py:106-128 -> hnsw.py:96,127, offered for
+    IVF as an extension): results equal the oracle run on the allowed nodes only."""
+    g, idx = _golden_index(golden_dir, with_adds=False)
+    k, ptr = int(g["k"]), g["list_ptr"]
+    lists = [[int(i) for i in g["list_ids"][ptr[c]:ptr[c + 1]]] for c in range(k)]
+    allowed = set(int(i) for i in g["ids"][::4])
+    vec = {int(i): g["X"][j] for j, i in enumerate(g["ids"]) if int(i) in allowed}
+    D, I = idx.search_batch(g["Q"], 3, 10, filter_ids=allowed)
+    for qi in range(g["Q"].shape[0]):
+        res, _, _ = IO.search(g["centroids"], lists, vec, g["Q"][qi], 3, 10)
+        assert [r[1] for r in res] == [int(i) for i in I[qi] if i >= 0]

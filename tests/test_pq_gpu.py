@@ -146,3 +146,38 @@ def test_tensor_core_encode_golden_reference_codes(golden_dir):
     cb8 = _t(g8["centroids"])
     np.testing.assert_array_equal(ops.pq_encode(_t(g8["X"]), cb8, engine="tc").cpu().numpy(), g8["codes"])
     np.testing.assert_array_equal(ops.pq_encode(_t(g8["Y"]), cb8, engine="tc").cpu().numpy(), g8["codes_y"])
+
+
+@pytest.mark.parametrize("n,m,q,R,keep", [(60_000, 16, 4, 10, 0.5), (60_000, 16, 4, 10, 0.01), (3_000, 8, 3, 20, 0.3),
+                                           (50_000, 48, 2, 800, 0.7)])
+def test_adc_row_mask_is_exact_over_the_remaining_rows(n, m, q, R, keep):
+    """Metadata pre-filter / tombstones: rows whose bit is cleared are skipped; the answer equals the oracle on
+    the kept rows.  A selective filter makes the sampled threshold collect fewer than R rows, so the
+    device-side rescan path is what answers (keep = 0.01)."""
+    from vector_db_b200 import ops
+    rng = np.random.default_rng(n + m + int(keep * 100))
+    codes = rng.integers(0, 256, (n, m)).astype(np.uint8)
+    lut = rng.random((q, m, 256), dtype=np.float32)
+    kept = np.flatnonzero(rng.random(n) < keep)
+    words = np.zeros((n + 31) // 32, dtype=np.uint32)
+    np.bitwise_or.at(words, kept >> 5, np.uint32(1) << (kept & 31).astype(np.uint32))
+    R_eff = min(R, kept.size)
+    Dref, Iref = O.adc_scan_topk(codes[kept], lut, R_eff, ids=kept)
+    D, I = ops.pq_adc_topk(_t(codes), _t(lut), R_eff, row_mask=_t(words.view(np.int32)))
+    np.testing.assert_array_equal(I.cpu().numpy(), Iref)
+    np.testing.assert_array_equal(D.cpu().numpy(), Dref)
+
+
+def test_pq_index_filter_ids(golden_dir):
+    from vector_db_b200.inference.pq import PQIndex
+    g = np.load(os.path.join(golden_dir, "pq8.npz"))
+    cents, X = list(g["centroids"]), g["X"]
+    ids = np.arange(1200) + 5000
+    idx = PQIndex(cents, keep_vectors=True)
+    idx.add(X, ids=ids)
+    allowed = set(int(i) for i in ids[::3])
+    D, I = idx.search(g["Y"][:8], 10, filter_ids=allowed)
+    keep = np.array(sorted(allowed)) - 5000
+    Dref, Iref = O.adc_scan_topk(g["codes"][keep], O.adc_lut(g["Y"][:8], cents), 10, ids=ids[keep])
+    np.testing.assert_array_equal(I, Iref)
+    np.testing.assert_array_equal(D, Dref)

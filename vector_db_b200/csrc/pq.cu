@@ -218,6 +218,7 @@ adc_quantize_lut_kernel(const float* __restrict__ lut, int per_query, uint32_t* 
 
 struct AdcArgs {
     const uint8_t* codes;
+    const uint32_t* mask;       // optional row bitmap (bit cleared = row skipped): tombstones / metadata pre-filter
     int64_t N;                  // logical rows scanned
     int64_t row_stride;         // physical row = logical row * row_stride (> 1: strided sample for the threshold estimate)
     int m;
@@ -325,7 +326,9 @@ adc_scan_kernel(const AdcArgs a) {
         for (int64_t rb = r_begin; rb < r_end; rb += kAdcThreads) {
             const int64_t r = rb + tid;
             int nearly_full = 0;
-            if (r < r_end) {
+            bool live = r < r_end;
+            if (live && a.mask) { const int64_t pr = r * a.row_stride; live = (a.mask[pr >> 5] >> (pr & 31)) & 1u; }
+            if (live) {
                 uint32_t acc[G];
                 adc_row<G, MB>(a.codes + r * a.row_stride * m, m, mb, lutS, rot, acc);
 #pragma unroll
@@ -798,7 +801,7 @@ size_t vdb_pq_adc_topk_workspace(int Q, int64_t N, int m, int R) {
 }
 
 int vdb_pq_adc_topk(const uint8_t* codes, int64_t N, int m, const float* lut, int Q, int R, const int64_t* ids,
-                    float* out_d, int64_t* out_i, void* ws, size_t ws_bytes, void* stream) {
+                    const uint32_t* row_mask, float* out_d, int64_t* out_i, void* ws, size_t ws_bytes, void* stream) {
     VDB_REQUIRE(Q >= 0 && N >= 0 && m > 0 && R > 0, VDB_ERR_INVALID, "vdb_pq_adc_topk: bad shape");
     VDB_REQUIRE(N < (1ll << 32), VDB_ERR_UNSUPPORTED, "N=%lld exceeds 2^32 rows per call", (long long)N);
     VDB_REQUIRE(m <= 255, VDB_ERR_UNSUPPORTED, "m=%d > 255 overflows the 32-bit fixed-point sum", m);
@@ -820,7 +823,7 @@ int vdb_pq_adc_topk(const uint8_t* codes, int64_t N, int m, const float* lut, in
     count_launch(1);
 
     AdcArgs a{};
-    a.codes = codes; a.N = N; a.row_stride = 1; a.m = m; a.lutq = lutq; a.Q = Q; a.R = R;
+    a.codes = codes; a.mask = row_mask; a.N = N; a.row_stride = 1; a.m = m; a.lutq = lutq; a.Q = Q; a.R = R;
     AdcFinArgs f{};
     f.R = R; f.expo = expo; f.ids = ids; f.out_d = out_d; f.out_i = out_i;
     int rc;

@@ -202,8 +202,9 @@ class IvfIndex:
             self.save_index()
 
     # ------------------------------------------------------------------ search
-    def search_batch(self, queries: np.ndarray, n_probe: int, top_k: int) -> Tuple[np.ndarray, np.ndarray]:
-        """Many queries at once: (dist f32 [Q,top_k], ids i64 [Q,top_k]), padded with (+inf, -1)."""
+    def search_batch(self, queries: np.ndarray, n_probe: int, top_k: int, filter_ids=None) -> Tuple[np.ndarray, np.ndarray]:
+        """Many queries at once: (dist f32 [Q,top_k], ids i64 [Q,top_k]), padded with (+inf, -1).
+        ``filter_ids``: optional set of node ids the results are restricted to (metadata pre-filter)."""
         if self.centroids is None:
             raise ValueError("Index must be built before searching")
         queries = np.ascontiguousarray(queries, dtype=np.float32)
@@ -218,17 +219,20 @@ class IvfIndex:
             raise ValueError(f"n_probe must be between 1 and {self.k}")
         with self._lock:
             q = torch.from_numpy(queries).to(self._device)
-            d, i, scanned = self.search_device(q, n_probe, top_k)
+            d, i, scanned = self.search_device(q, n_probe, top_k, filter_ids=filter_ids)
             self.last_scanned = scanned.cpu().numpy()
             return d.cpu().numpy(), i.cpu().numpy()
 
-    def search_device(self, q: torch.Tensor, n_probe: int, top_k: int):
+    def search_device(self, q: torch.Tensor, n_probe: int, top_k: int, filter_ids=None):
         """Device in / device out: (dist, ids, candidates enumerated per query)."""
         ptr, rows = self._csr()
         vec = self._vectors
         cdist = ops.ivf_centroid_dist(q, self._centroids_dev)
         probes, prefix = ops.ivf_probe(cdist, n_probe, ptr)
         alive = vec.alive if vec.n_dead else None
+        if filter_ids is not None:
+            flt = vec.bitmap_from_ids(filter_ids)
+            alive = flt if alive is None else torch.bitwise_and(alive[:flt.numel()], flt)
         return ops.ivf_scan(q, vec.vecs, ptr, rows, probes, prefix, top_k, alive=alive, ids=vec.ids, return_scanned=True)
 
     def search(self, query: np.ndarray, n_probe: int, top_k: int) -> List[Tuple[Node, float]]:
@@ -379,9 +383,12 @@ class IvfPqIndex(IvfIndex):
         return self._codes_lm
 
     def search_device(self, q: torch.Tensor, n_probe: int, top_k: int, shortlist: Optional[int] = None,
-                      rerank: bool = True):
+                      rerank: bool = True, filter_ids=None):
         """(dist, ids, candidates enumerated).  With ``rerank`` the distances are exact non-squared L2 over the
-        ADC shortlist; without it they are the squared ADC estimates and ``top_k`` of them are returned."""
+        ADC shortlist; without it they are the squared ADC estimates and ``top_k`` of them are returned.
+        A filtered search (``filter_ids``) takes the exact list scan of :class:`IvfIndex`."""
+        if filter_ids is not None:
+            return IvfIndex.search_device(self, q, n_probe, top_k, filter_ids=filter_ids)
         if self.codebooks is None:
             raise ValueError("Product quantiser must be trained before searching (train_pq / set_codebooks)")
         ptr, rows = self._csr()
@@ -400,7 +407,7 @@ class IvfPqIndex(IvfIndex):
         return d[:, :top_k], ids[:, :top_k], scanned
 
     def search_batch(self, queries: np.ndarray, n_probe: int, top_k: int, shortlist: Optional[int] = None,
-                     rerank: bool = True) -> Tuple[np.ndarray, np.ndarray]:
+                     rerank: bool = True, filter_ids=None) -> Tuple[np.ndarray, np.ndarray]:
         if self.centroids is None:
             raise ValueError("Index must be built before searching")
         queries = np.ascontiguousarray(queries, dtype=np.float32)
@@ -410,6 +417,6 @@ class IvfPqIndex(IvfIndex):
             raise ValueError(f"n_probe must be between 1 and {self.k}")
         with self._lock:
             q = torch.from_numpy(queries).to(self._device)
-            d, i, scanned = self.search_device(q, n_probe, top_k, shortlist, rerank)
+            d, i, scanned = self.search_device(q, n_probe, top_k, shortlist, rerank, filter_ids)
             self.last_scanned = scanned.cpu().numpy()
             return d.cpu().numpy(), i.cpu().numpy()

@@ -154,7 +154,18 @@ class PQIndex:
         i = None if ids is None else torch.as_tensor(np.asarray(ids, dtype=np.int64), device=self.device)
         self.add_device(v, i)
 
-    def search_device(self, q: torch.Tensor, k: int, shortlist: Optional[int] = None, rerank: bool = False):
+    def bitmap_from_ids(self, ids) -> torch.Tensor:
+        """Row bitmap (int32 words) with the bits of the given external ids set -- the metadata pre-filter
+        (filter_ids of src/vector_db/indexing/hnsw.py:96,127) for the ADC scan."""
+        want = torch.as_tensor(sorted(int(i) for i in ids), dtype=torch.int64, device=self.device)
+        hit = torch.isin(self.ids[:self.n], want)
+        bits = torch.zeros(((self.n + 31) // 32) * 32, dtype=torch.int64, device=self.device)
+        bits[:self.n] = hit.to(torch.int64)
+        words = (bits.view(-1, 32) << torch.arange(32, device=self.device, dtype=torch.int64)).sum(dim=1)
+        return torch.where(words >= 2 ** 31, words - 2 ** 32, words).to(torch.int32)
+
+    def search_device(self, q: torch.Tensor, k: int, shortlist: Optional[int] = None, rerank: bool = False,
+                      filter_ids=None):
         """ADC top-``shortlist`` (default k); with ``rerank`` the shortlist is re-scored with the exact
         fp32 L2 distance and the k best returned.  Returns (dist, ids) device tensors; ADC
         distances are SQUARED sub-space sums, reranked distances are non-squared L2."""
@@ -162,7 +173,8 @@ class PQIndex:
         R = max(k, shortlist or k)
         R = min(R, max(self.n, 1))
         lut = ops.pq_lut(q, self._cb_lut)
-        d, rows = ops.pq_adc_topk(self.codes, lut, R, ids=None, n_rows=self.n)
+        mask = self.bitmap_from_ids(filter_ids) if filter_ids is not None else None
+        d, rows = ops.pq_adc_topk(self.codes, lut, R, ids=None, n_rows=self.n, row_mask=mask)
         if rerank:
             if not self.keep_vectors:
                 raise ValueError("rerank needs keep_vectors=True")
@@ -170,8 +182,8 @@ class PQIndex:
         ids = torch.where(rows >= 0, self.ids[rows.clamp(min=0)], rows)
         return d[:, :k], ids[:, :k]
 
-    def search(self, queries: np.ndarray, k: int, shortlist: Optional[int] = None, rerank: bool = False
-               ) -> Tuple[np.ndarray, np.ndarray]:
+    def search(self, queries: np.ndarray, k: int, shortlist: Optional[int] = None, rerank: bool = False,
+               filter_ids=None) -> Tuple[np.ndarray, np.ndarray]:
         q = torch.from_numpy(np.ascontiguousarray(queries, dtype=np.float32).reshape(-1, self.dim)).to(self.device)
-        d, i = self.search_device(q, k, shortlist, rerank)
+        d, i = self.search_device(q, k, shortlist, rerank, filter_ids)
         return d.cpu().numpy(), i.cpu().numpy()

@@ -134,8 +134,9 @@ def pq_lut(q: torch.Tensor, codebooks: torch.Tensor) -> torch.Tensor:
 
 
 def pq_adc_topk(codes: torch.Tensor, lut: torch.Tensor, R: int, ids: Optional[torch.Tensor] = None,
-                n_rows: Optional[int] = None):
-    """codes uint8 [N,m], lut fp32 [Q,m,256] -> (d f32 [Q,R], idx i64 [Q,R]) by (d,row) ascending."""
+                n_rows: Optional[int] = None, row_mask: Optional[torch.Tensor] = None):
+    """codes uint8 [N,m], lut fp32 [Q,m,256] -> (d f32 [Q,R], idx i64 [Q,R]) by (d,row) ascending.
+    row_mask: optional int32 bitmap over rows (bit cleared = row skipped)."""
     if lut.shape[2] != 256:
         raise ValueError("ADC scan needs 256-entry LUT rows (nbits=8); pad the codebooks")
     Q, m = lut.shape[0], lut.shape[1]
@@ -148,7 +149,7 @@ def pq_adc_topk(codes: torch.Tensor, lut: torch.Tensor, R: int, ids: Optional[to
     if nbytes == 0 and Q > 0:
         raise ValueError(f"ADC scan: m={m} R={R} do not fit shared memory")
     ws = _ws("adc", nbytes, dev)
-    check(lib.vdb_pq_adc_topk(ptr(codes), N, m, ptr(lut), Q, R, ptr(ids), ptr(out_d), ptr(out_i), ptr(ws),
+    check(lib.vdb_pq_adc_topk(ptr(codes), N, m, ptr(lut), Q, R, ptr(ids), ptr(row_mask), ptr(out_d), ptr(out_i), ptr(ws),
                               ws.numel(), _lib.stream_ptr(dev)))
     return out_d, out_i
 
