@@ -114,14 +114,15 @@ def bench_hnsw(N=200_000, D=768, M=32, ef=128, Q=10_000):
     from vector_db_b200.indexing import ExactIndex
     ex = ExactIndex(D, "l2")
     ex.add_device(torch.arange(N, device=dev), torch.from_numpy(X).to(dev))
-    _, Iex = ex.search(Qh[:512], 10)
-    recall = float(np.mean([len(set(i[j]) & set(Iex[j])) / 10 for j in range(512)]))
+    n_rec = min(512, Q)
+    _, Iex = ex.search(Qh[:n_rec], 10)
+    recall = float(np.mean([len(set(i[j]) & set(Iex[j])) / 10 for j in range(n_rec)]))
     # the reference's own search (oracle restatement of hnsw.py:330-374, pinned to the reference by the golden
     # fixtures) on the SAME graph, for a sample: recall parity gate (within 0.5 pt) and the CPU baseline
     from oracle.hnsw_oracle import search_arrays
     adj0, adj_up, up_ptr, _, _ = idx._host_graph()
     entry_row, top = idx._read_state()
-    n_or = int(os.environ.get("VDB_HNSW_ORACLE_QUERIES", 64))
+    n_or = min(int(os.environ.get("VDB_HNSW_ORACLE_QUERIES", 64)), n_rec)
     t0 = time.perf_counter()
     same, rec_or, rec_gpu, ev_same = 0, 0.0, 0.0, 0
     for j in range(n_or):
