@@ -50,7 +50,7 @@ __host__ __device__ inline EtSmem et_layout(int stages, int m) {
     L.mask_off = L.ones_off + kEtABytes;
     L.codes_off = L.mask_off + 8 * 256 * 4;                    // candidate masks [8 chunks][256 epilogue threads]
     L.bar_off = (L.codes_off + kEtRows * m + 15) & ~15;        // code staging [128 rows][m]
-    L.total = L.bar_off + (3 * kEtMaxStages + 4) * 8 + 16;
+    L.total = L.bar_off + (3 * kEtMaxStages + 8) * 8 + 16;
     return L;
 }
 
@@ -138,9 +138,9 @@ pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     uint64_t* full = bars;                          // [stages]
     uint64_t* empty = bars + kEtMaxStages;          // [stages]
     uint64_t* xlo_full = bars + 2 * kEtMaxStages;   // [stages]: x_lo written by the split warp
-    uint64_t* tmem_full = bars + 3 * kEtMaxStages;  // [2]
-    uint64_t* tmem_empty = tmem_full + 2;           // [2]
-    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+    uint64_t* tmem_full = bars + 3 * kEtMaxStages;  // [2 accumulator stages][2 column halves]
+    uint64_t* tmem_empty = tmem_full + 4;           // [2][2]
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 4);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     // constant A tile of the norm MMA: every row is (1,1,1,0,0,0,0,0); with the 32-byte swizzle the two
@@ -159,7 +159,7 @@ pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         for (int i = 0; i < stages; ++i) {
             mbar_init(&full[i], 1); mbar_init(&empty[i], 1 + 4); mbar_init(&xlo_full[i], 1);   // empty: MMA commit + 4 epilogue warps
         }
-        for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 128); }
+        for (int i = 0; i < 4; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 128); }
         fence_barrier_init();
     }
     if (warp == 2) tmem_alloc(tmem_ptr, 512);
@@ -190,27 +190,34 @@ pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     } else if (warp == 1) {
         // ================= MMA issuer =================
         if (lane == 0) {
-            const uint32_t idesc = make_idesc_tf32(kEtRows, kEtK);
+            // Each 256-column accumulator is produced and released in two 128-column halves: the epilogue frees half 0
+            // while it is still masking half 1, so the next-but-one step's MMAs start (and finish) under epilogue work
+            // instead of after it -- with whole-stage hand-over the epilogue warps waited ~20 % of the time for tmem_full.
+            const uint32_t idesc = make_idesc_tf32(kEtRows, kEtK / 2);
             const uint64_t d_ones = make_desc_k_sw32(smem_u32(sOnes));
             int st = 0, ph = 0, as = 0, aph = 0;
             for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
                 for (int j = 0; j < m; ++j) {
-                    mbar_wait(&tmem_empty[as], aph ^ 1);
                     mbar_wait(&full[st], ph);
                     mbar_wait(&xlo_full[st], ph);
-                    tc_fence_after();
                     const uint32_t base = smem_u32(sStage + (size_t)st * kEtStageBytes);
-                    const uint32_t d_tmem = tmem_base + (uint32_t)(as * kEtK);
                     const uint64_t d_x = make_desc_k_sw32(base), d_xlo = make_desc_k_sw32(base + kEtABytes);
-                    const uint64_t d_hi = make_desc_k_sw32(base + 2 * kEtABytes);
-                    const uint64_t d_lo = make_desc_k_sw32(base + 2 * kEtABytes + kEtBBytes);
-                    // x.(-2c) to ~2^-20: hi(x).hi + hi(x).lo + lo(x).hi  (the tensor core drops the low 13 bits of every operand)
-                    umma_tf32(d_tmem, d_x, d_hi, idesc, 0u);
-                    umma_tf32(d_tmem, d_x, d_lo, idesc, 1u);
-                    umma_tf32(d_tmem, d_xlo, d_hi, idesc, 1u);
-                    umma_tf32(d_tmem, d_ones, make_desc_k_sw32(base + 2 * kEtABytes + 2 * kEtBBytes), idesc, 1u);
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        mbar_wait(&tmem_empty[as * 2 + h], aph ^ 1);
+                        tc_fence_after();
+                        const uint32_t d_tmem = tmem_base + (uint32_t)(as * kEtK + h * (kEtK / 2));
+                        const uint32_t boff = (uint32_t)(h * (kEtBBytes / 2));       // centroids 128 h .. 128 h + 127
+                        const uint64_t d_hi = make_desc_k_sw32(base + 2 * kEtABytes + boff);
+                        const uint64_t d_lo = make_desc_k_sw32(base + 2 * kEtABytes + kEtBBytes + boff);
+                        // x.(-2c) to ~2^-20: hi(x).hi + hi(x).lo + lo(x).hi  (every operand is tf32-exact)
+                        umma_tf32(d_tmem, d_x, d_hi, idesc, 0u);
+                        umma_tf32(d_tmem, d_x, d_lo, idesc, 1u);
+                        umma_tf32(d_tmem, d_xlo, d_hi, idesc, 1u);
+                        umma_tf32(d_tmem, d_ones, make_desc_k_sw32(base + 2 * kEtABytes + 2 * kEtBBytes + boff), idesc, 1u);
+                        umma_commit(&tmem_full[as * 2 + h]);
+                    }
                     umma_commit(&empty[st]);
-                    umma_commit(&tmem_full[as]);
                     if (++st == stages) { st = 0; ph ^= 1; }
                     as ^= 1;
                     if (as == 0) aph ^= 1;
@@ -255,8 +262,7 @@ pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
             for (int j = 0; j < m; ++j, ++step, st = (st + 1 == stages ? 0 : st + 1)) {
                 if ((int)(step & 1) != eg) continue;
-                mbar_wait(&tmem_full[eg], phase);      // MMA done => its operands were in shared memory too
-                phase ^= 1;
+                mbar_wait(&tmem_full[eg * 2], phase);  // columns 0..127 done => the step's operands were in shared memory too
                 tc_fence_after();
                 const unsigned char* sA = sStage + (size_t)st * kEtStageBytes;
                 const unsigned char* sBh = sA + 2 * kEtABytes;      // hi(-2c)
@@ -275,11 +281,24 @@ pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                 // flight (tcgen05.wait::ld waits for ALL outstanding loads, so exactly one is outstanding at
                 // every wait).  With a single buffer each of the 16 chunk visits exposed the full TMEM latency.
                 float va[32], vb[32];
-                // pass 1: minimum score of the row
+                // pass 1: minimum score of the row, half by half (the MMAs of columns 128..255 may still be running)
                 float gmin = INFINITY;
                 tmem_ld_x32(taddr, va);
 #pragma unroll 1
-                for (int ch = 0; ch < 8; ch += 2) {
+                for (int ch = 0; ch < 4; ch += 2) {
+                    tmem_ld_wait(va);
+                    tmem_ld_x32(taddr + (uint32_t)((ch + 1) * 32), vb);
+                    gmin = fminf(gmin, min32(va));
+                    tmem_ld_wait(vb);
+                    if (ch + 2 < 4) tmem_ld_x32(taddr + (uint32_t)((ch + 2) * 32), va);
+                    gmin = fminf(gmin, min32(vb));
+                }
+                mbar_wait(&tmem_full[eg * 2 + 1], phase);
+                phase ^= 1;
+                tc_fence_after();
+                tmem_ld_x32(taddr + 128u, va);
+#pragma unroll 1
+                for (int ch = 4; ch < 8; ch += 2) {
                     tmem_ld_wait(va);
                     tmem_ld_x32(taddr + (uint32_t)((ch + 1) * 32), vb);
                     gmin = fminf(gmin, min32(va));
@@ -287,13 +306,13 @@ pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                     tmem_ld_x32(taddr + (uint32_t)(((ch + 2) & 7) * 32), va);     // last round: chunk 0 again, for pass 2
                     gmin = fminf(gmin, min32(vb));
                 }
-                // rigorous candidate margin (see file header): tf32 rounding of both operands + fp32 noise
+                // rigorous candidate margin (see file header): operand split error + fp32 accumulation / reference rounding
                 float xx = 0.f;
 #pragma unroll
                 for (int t = 0; t < 8; ++t) xx = fmaf(xs[t], xs[t], xx);
                 const float xn = sqrtf(xx) * 1.0000005f, cm_j = __ldg(cmax + j);
                 const float thr = gmin + 1.2e-5f * xn * cm_j + 1e-5f * (xn + cm_j) * (xn + cm_j);
-                // pass 2: every centroid within the margin
+                // pass 2: every centroid within the margin; each half is handed back to the MMA as soon as it is read
                 int cnt = 0, first = -1;
 #pragma unroll 1
                 for (int ch = 0; ch < 8; ch += 2) {
@@ -305,7 +324,11 @@ pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                         if (mask && first < 0) first = ch * 32 + __ffs(mask) - 1;
                         cnt += __popc(mask);
                     }
-                    tmem_ld_wait(vb);
+                    tmem_ld_wait(vb);                   // every load of chunks <= ch + 1 has landed
+                    if (ch == 2 || ch == 6) {
+                        tc_fence_before();
+                        mbar_arrive(&tmem_empty[eg * 2 + (ch >> 2)]);     // half drained: the MMA two steps ahead may overwrite it
+                    }
                     if (ch + 2 < 8) tmem_ld_x32(taddr + (uint32_t)((ch + 2) * 32), va);
                     {
                         const uint32_t mask = le_mask32(vb, thr);
@@ -314,8 +337,6 @@ pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                         cnt += __popc(mask);
                     }
                 }
-                tc_fence_before();
-                mbar_arrive(&tmem_empty[eg]);          // accumulator drained: the MMA two steps ahead may overwrite it
                 int code = first < 0 ? 0 : first;
                 if (cnt > 1) {
                     // several candidates: the reference's own arithmetic decides (pq.py:79-80), first minimum wins
