@@ -343,7 +343,7 @@ adc_scan_kernel(const AdcArgs a) {
                             }
                         } else if (acc[g] <= tau[g]) {
                             const int p = atomicAdd(a.ccnt + qid[g], 1);
-                            if (p < a.ccap) a.cbuf[(size_t)qid[g] * a.ccap + p] = key;
+                            if ((unsigned)p < (unsigned)a.ccap) a.cbuf[(size_t)qid[g] * a.ccap + p] = key;   // a wrapped counter (> 2^31 hits) must not index
                         }
                     }
                 }
