@@ -99,12 +99,13 @@ int vdb_rerank_f32(const float* q, int Q, const float* db, const int64_t* ids, i
  * are returned so the caller re-runs them through vdb_exact_topk_f32.
  * Requirements: D % 8 == 0, one query tile's operand fits shared memory (D <= 512), k <= 16;
  * vdb_exact_topk_tc_supported() answers for a shape.
- * Mirror layout: bf16 [N][vdb_tc_row_elems(D, metric)], 16-byte aligned. */
+ * Mirror: one bf16 buffer of vdb_tc_mirror_elems(N, D, metric) elements, 128-byte aligned: the N x D operand
+ * rows, then (L2) a packed [ceil4(N)][16] block holding the bf16 split of |x|^2 of every row. */
 #define VDB_TC_BIN 8
 int vdb_exact_topk_tc_supported(int Q, int64_t N, int D, int k, int metric);
-int vdb_tc_row_elems(int D, int metric);
+size_t vdb_tc_mirror_elems(int64_t N, int D, int metric);
 int vdb_tc_prepare_rows(const float* vecs /*[dev] N*D*/, int64_t N, int D, int metric,
-                        float* sqnorm /*[dev] N or NULL*/, void* mirror /*[dev] N*row_elems bf16*/, void* stream);
+                        float* sqnorm /*[dev] N or NULL*/, void* mirror /*[dev] vdb_tc_mirror_elems bf16*/, void* stream);
 size_t vdb_exact_topk_tc_workspace(int Q, int64_t N, int D, int k, int metric);
 int vdb_exact_topk_tc(const float* q /*[dev] Q*D fp32*/, int Q,
                       const float* db /*[dev] N*D fp32*/, const void* mirror /*[dev] see above*/,

@@ -167,7 +167,7 @@ exact_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                     if (has_norm) {
                         mbar_wait(&n_empty[ns], nph ^ 1);
                         mbar_expect_tx(&n_full[ns], (uint32_t)kB2Bytes);
-                        tma_load_2d(sB2 + ns * kB2Bytes, &map_b2, &n_full[ns], D, t * kTileN, kEvictNormal);
+                        tma_load_2d(sB2 + ns * kB2Bytes, &map_b2, &n_full[ns], 0, t * (kTileN / 4), kEvictNormal);
                         ns ^= 1;
                         if (ns == 0) nph ^= 1;
                     }
@@ -303,34 +303,43 @@ __global__ void tc_query_operand_kernel(const float* __restrict__ q, __nv_bfloat
 }
 
 // Row operand ("mirror"), one warp per row, built once per index mutation:
-//   L2     : bf16(-2 x) = -2 bf16(x) in columns [0,D), bf16 split (hi, mid, lo) of |x|^2 in D..D+2, zeros up to Dp
+//   L2     : bf16(-2 x) = -2 bf16(x), row stride D; the bf16 split (hi, mid, lo) of |x|^2 goes to a separate packed
+//            norm area [ceil4(N)][16] behind the rows (tc_norm_offset) -- as 16 extra columns of every row it cost 256
+//            32-byte TMA row fetches per tile and the TMA unit, not the tensor pipe, set the pace of the L2 scan
 //   cosine : bf16(-x/|x|) (zero rows stay zero)
 // so that the fp32 accumulator of q~ . row~ is the ranking score itself.  Also emits sqnorm.
-__global__ void tc_row_operand_kernel(const float* __restrict__ x, int64_t N, int D, int Dp, int metric,
-                                      float* __restrict__ sqnorm, __nv_bfloat16* __restrict__ mirror) {
+__global__ void tc_row_operand_kernel(const float* __restrict__ x, int64_t N, int D, int metric,
+                                      float* __restrict__ sqnorm, __nv_bfloat16* __restrict__ mirror,
+                                      __nv_bfloat16* __restrict__ norms) {
     const int lane = threadIdx.x & 31;
     const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
-    for (int64_t r = (((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5); r < N; r += warps) {
+    const int64_t n4 = (N + 3) & ~(int64_t)3;
+    for (int64_t r = (((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5); r < n4; r += warps) {
+        if (r >= N) {                                   // padding rows of the norm area (it is read in 4-row lines)
+            if (norms && lane < 16) norms[r * 16 + lane] = __float2bfloat16_rn(0.f);
+            continue;
+        }
         const float* row = x + r * D;
         float acc = 0.f;
         for (int t = lane; t < D; t += 32) { const float v = row[t]; acc = fmaf(v, v, acc); }
         acc = warp_sum(acc);
         if (sqnorm && lane == 0) sqnorm[r] = acc;
-        __nv_bfloat16* out = mirror + r * Dp;
+        __nv_bfloat16* out = mirror + r * D;
         if (metric == VDB_METRIC_L2) {
             for (int t = lane; t < D; t += 32) out[t] = __float2bfloat16_rn(-2.f * row[t]);
-            if (lane == 0) {
+            if (lane < 16) {
+                // 16-element norm row in the byte order the UMMA reads (32-byte swizzle: the two 16-byte halves
+                // of row r trade places when bit 2 of r is set), so a 256-row tile is a linear 8 KB copy
                 const __nv_bfloat16 h = __float2bfloat16_rn(acc);
                 const float r1 = acc - __bfloat162float(h);
                 const __nv_bfloat16 m = __float2bfloat16_rn(r1);
                 const __nv_bfloat16 l = __float2bfloat16_rn(r1 - __bfloat162float(m));
-                out[D] = h; out[D + 1] = m; out[D + 2] = l;
+                const __nv_bfloat16 v = lane == 0 ? h : (lane == 1 ? m : (lane == 2 ? l : __float2bfloat16_rn(0.f)));
+                norms[r * 16 + (lane ^ ((int)((r >> 2) & 1) << 3))] = v;
             }
-            for (int t = D + 3 + lane; t < Dp; t += 32) out[t] = __float2bfloat16_rn(0.f);
         } else {
             const float rinv = acc > 0.f ? -1.f / sqrtf(acc) : 0.f;
             for (int t = lane; t < D; t += 32) out[t] = __float2bfloat16_rn(row[t] * rinv);
-            for (int t = D + lane; t < Dp; t += 32) out[t] = __float2bfloat16_rn(0.f);
         }
     }
 }
@@ -436,7 +445,8 @@ static EncodeTiledFn encode_tiled_fn() {
 
 // bf16 row-major matrix with `cols` visible columns out of rows of `row_elems` elements; box = box_cols x
 // box_rows with the matching swizzle (64 columns -> 128 B, 16 columns -> 32 B); zero fill out of bounds
-static int make_map(CUtensorMap* map, const void* base, int64_t rows, int cols, int row_elems, int box_cols, int box_rows) {
+static int make_map(CUtensorMap* map, const void* base, int64_t rows, int cols, int row_elems, int box_cols, int box_rows,
+                    int swizzle = -1) {
     EncodeTiledFn fn = encode_tiled_fn();
     VDB_REQUIRE(fn != nullptr, VDB_ERR_CUDA, "cuTensorMapEncodeTiled is not available from the driver");
     cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
@@ -444,7 +454,8 @@ static int make_map(CUtensorMap* map, const void* base, int64_t rows, int cols, 
     cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
     cuuint32_t estr[2] = {1, 1};
     CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
-                    CU_TENSOR_MAP_INTERLEAVE_NONE, box_cols == 16 ? CU_TENSOR_MAP_SWIZZLE_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    swizzle == 0 ? CU_TENSOR_MAP_SWIZZLE_NONE : (box_cols == 16 ? CU_TENSOR_MAP_SWIZZLE_32B : CU_TENSOR_MAP_SWIZZLE_128B),
                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     VDB_REQUIRE(r == CUDA_SUCCESS, VDB_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
     return VDB_OK;
@@ -455,7 +466,12 @@ struct TcPlan {
     size_t smem;
 };
 
-static int tc_row_elems(int D, int metric) { return metric == VDB_METRIC_L2 ? D + 16 : D; }
+static int tc_row_elems(int D, int metric) { return metric == VDB_METRIC_L2 ? D + 16 : D; }   // QUERY operand row
+// element offset of the packed norm area behind the N x D operand rows (128-byte aligned), and the buffer size
+static size_t tc_norm_offset(int64_t N, int D) { return ((size_t)N * D + 63) & ~(size_t)63; }
+static size_t tc_mirror_elems(int64_t N, int D, int metric) {
+    return tc_norm_offset(N, D) + (metric == VDB_METRIC_L2 ? (size_t)((N + 3) & ~(int64_t)3) * 16 : 0);
+}
 
 static int g_tc_flags = 0;
 
@@ -534,7 +550,7 @@ int vdb_exact_topk_tc_supported(int Q, int64_t N, int D, int k, int metric) {
     return plan_tc(Q, N, D, k, metric, &p) && N < (1ll << 31) ? 1 : 0;
 }
 
-int vdb_tc_row_elems(int D, int metric) { return tc_row_elems(D, metric); }
+size_t vdb_tc_mirror_elems(int64_t N, int D, int metric) { return tc_mirror_elems(N, D, metric); }
 
 int vdb_tc_prepare_rows(const float* vecs, int64_t N, int D, int metric, float* sqnorm, void* mirror, void* stream) {
     VDB_REQUIRE(N >= 0 && D > 0 && D % 8 == 0, VDB_ERR_INVALID, "vdb_tc_prepare_rows: bad N=%lld D=%d", (long long)N, D);
@@ -545,7 +561,8 @@ int vdb_tc_prepare_rows(const float* vecs, int64_t N, int D, int metric, float* 
     int64_t need = (N + 7) / 8;
     if (need < blocks) blocks = (int)need;
     tc_row_operand_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-        vecs, N, D, tc_row_elems(D, metric), metric, sqnorm, static_cast<__nv_bfloat16*>(mirror));
+        vecs, N, D, metric, sqnorm, static_cast<__nv_bfloat16*>(mirror),
+        metric == VDB_METRIC_L2 ? static_cast<__nv_bfloat16*>(mirror) + tc_norm_offset(N, D) : nullptr);
     count_launch(1);
     VDB_CUDA(cudaGetLastError());
     return VDB_OK;
@@ -585,12 +602,14 @@ int vdb_exact_topk_tc(const float* q, int Q, const float* db, const void* mirror
     CUtensorMap map_a2, map_b2;
     int rc = make_map(&map_a, qb, Q, D, p.Dp, kBlockK, kTileM);
     if (rc) return rc;
-    rc = make_map(&map_b, mirror, N, D, p.Dp, kBlockK, kTileN);
+    rc = make_map(&map_b, mirror, N, D, D, kBlockK, kTileN);
     if (rc) return rc;
     // norm block (L2 only; cosine passes valid but unused maps): columns D..D+15 of the same operands
     rc = make_map(&map_a2, qb, Q, p.Dp, p.Dp, 16, kTileM);
     if (rc) return rc;
-    rc = make_map(&map_b2, mirror, N, p.Dp, p.Dp, 16, kTileN);
+    // norm area viewed as lines of 4 rows (64 bf16 = 128 B): a 256-row tile is 64 line fetches, no swizzle (pre-applied)
+    rc = make_map(&map_b2, p.has_norm ? static_cast<const void*>(static_cast<const __nv_bfloat16*>(mirror) + tc_norm_offset(N, D)) : mirror,
+                  p.has_norm ? (N + 3) / 4 : N, p.has_norm ? 64 : D, p.has_norm ? 64 : D, 64, 64, p.has_norm ? 0 : -1);
     if (rc) return rc;
     {
         ProfScope prof(kProfExactTC, st);

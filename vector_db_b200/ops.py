@@ -282,14 +282,14 @@ def tc_supported(Q: int, N: int, D: int, k: int, metric=METRIC_L2) -> bool:
 
 
 def tc_prepare_rows(vecs: torch.Tensor, metric=METRIC_L2):
-    """Per-metric bf16 operand mirror for the tensor-core scan.  Returns (mirror bf16 [N, row_elems],
-    sqnorm f32 [N]); the accumulator of q~ . mirror_row~ is the ranking score itself."""
+    """Per-metric bf16 operand mirror for the tensor-core scan.  Returns (mirror: flat bf16 buffer of
+    vdb_tc_mirror_elems(N, D, metric) elements -- the N x D operand rows, then for L2 the packed norm block --
+    and sqnorm f32 [N]); the accumulator of q~ . mirror_row~ is the ranking score itself."""
     vecs = _f32(vecs, "vecs")
     n, d = vecs.shape
     m = _metric(metric)
     lib = load()
-    dp = lib.vdb_tc_row_elems(d, m)
-    mir = torch.empty((n, dp), dtype=torch.bfloat16, device=vecs.device)
+    mir = torch.empty((lib.vdb_tc_mirror_elems(n, d, m),), dtype=torch.bfloat16, device=vecs.device)
     sq = torch.empty(n, dtype=torch.float32, device=vecs.device)
     check(lib.vdb_tc_prepare_rows(ptr(vecs), n, d, m, ptr(sq), ptr(mir), _lib.stream_ptr(vecs.device)))
     return mir, sq
@@ -312,8 +312,8 @@ def exact_topk_tc(q: torch.Tensor, db: torch.Tensor, mirror: torch.Tensor, max_n
     out_i = torch.empty((Q, k), dtype=torch.int64, device=dev)
     uncert = torch.empty((Q + 1,), dtype=torch.int32, device=dev)
     lib = load()
-    if mirror.shape[1] != lib.vdb_tc_row_elems(D, m):
-        raise ValueError("operand mirror was built for another metric / dimension")
+    if mirror.numel() != lib.vdb_tc_mirror_elems(N, D, m):
+        raise ValueError("operand mirror was built for another metric / shape")
     nbytes = lib.vdb_exact_topk_tc_workspace(Q, N, D, k, m)
     if nbytes == 0:
         raise ValueError(f"tensor-core scan does not support Q={Q} N={N} D={D} k={k}")
