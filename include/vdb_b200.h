@@ -143,6 +143,10 @@ int vdb_pq_encode_tc(const float* x, int64_t N, int D, int m, int K, const float
 size_t vdb_pq_kmeans_workspace(int m, int K, int dsub);
 int vdb_pq_kmeans_step(const float* x, int64_t N, int D, int m, int K, float* codebooks /*in/out*/,
                        int32_t* labels /*[dev] m*N or NULL*/, void* ws, size_t ws_bytes, void* stream);
+/* The same round with the assignment supplied as uint8 codes [N][m] (vdb_pq_encode / vdb_pq_encode_tc of the
+ * CURRENT codebooks: the nearest-centroid rule of pq.py:77-80) -- mean update only.  Same workspace. */
+int vdb_pq_kmeans_step_coded(const float* x, int64_t N, int D, int m, int K, const uint8_t* codes /*[dev] N*m*/,
+                             float* codebooks /*in/out*/, void* ws, size_t ws_bytes, void* stream);
 
 /* ---- a13 ADC scan (no reference symbol; sub-space layout pq.py:48-62, distance pq.py:77-80) ----
  * lut[q][j][c] = sum_t (q_jt - C_j[c][t])^2, fp32 [Q][m][K]. */

@@ -60,6 +60,21 @@ def test_kmeans_matches_lloyd_restatement():
         np.testing.assert_allclose(cents[j], ref, rtol=1e-3, atol=1e-3)
 
 
+def test_kmeans_round_through_tensor_core_encode_matches_lloyd_restatement():
+    """dsub == 8 and >= 4096 rows: the assignment of a Lloyd round is one tensor-core encode call and the round is
+    the mean update over its codes (vdb_pq_kmeans_step_coded)."""
+    from vector_db_b200.inference.pq import ProductQuantizationService as PQ
+    rng = np.random.default_rng(5)
+    centers = rng.standard_normal((16, 16)).astype(np.float32) * 4
+    X = (centers[rng.integers(0, 16, 6000)] + 0.3 * rng.standard_normal((6000, 16))).astype(np.float32)
+    init = rng.choice(6000, 16, replace=False)
+    svc = PQ(k=16, chunks=2, dim=16)
+    cents = svc.fit(X, init_rows=init, iters=20)
+    for j in range(2):
+        ref, _ = O.kmeans_lloyd(X[:, 8 * j:8 * j + 8], X[init, 8 * j:8 * j + 8], 20)
+        np.testing.assert_allclose(cents[j], ref, rtol=1e-3, atol=1e-3)
+
+
 @pytest.mark.parametrize("n,m,dsub,q,R", [(30000, 16, 4, 9, 10), (20000, 48, 2, 5, 10), (20000, 48, 2, 3, 700),
                                          (5000, 5, 3, 2, 17), (100, 8, 4, 6, 10), (9000, 32, 2, 1, 64)])
 def test_lut_and_adc_vs_oracle(n, m, dsub, q, R):

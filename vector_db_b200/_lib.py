@@ -42,6 +42,7 @@ SIGNATURES = {
     "vdb_pq_encode_tc": (_i, [_p, _i64, _i, _i, _i, _p, _p, _p, _sz, _p]),
     "vdb_pq_kmeans_workspace": (_sz, [_i, _i, _i]),
     "vdb_pq_kmeans_step": (_i, [_p, _i64, _i, _i, _i, _p, _p, _p, _sz, _p]),
+    "vdb_pq_kmeans_step_coded": (_i, [_p, _i64, _i, _i, _i, _p, _p, _p, _sz, _p]),
     "vdb_pq_lut": (_i, [_p, _i, _i, _i, _i, _p, _p, _p]),
     "vdb_pq_adc_topk_workspace": (_sz, [_i, _i64, _i, _i]),
     "vdb_pq_adc_topk": (_i, [_p, _i64, _i, _p, _i, _i, _p, _p, _p, _p, _p, _sz, _p]),

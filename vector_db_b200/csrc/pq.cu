@@ -116,6 +116,31 @@ kmeans_assign_kernel(const float* __restrict__ x, int64_t N, int D, int m, int K
         if (scnt[i] != 0.f) atomicAdd(counts + (size_t)j * K + i, scnt[i]);
 }
 
+// Same accumulation with the assignment given (uint8 codes from the encode kernels: argmin with the reference's
+// arithmetic, first minimum wins) -- the Lloyd round then costs one tensor-core encode plus this pass.
+__global__ void __launch_bounds__(256)
+kmeans_accumulate_kernel(const float* __restrict__ x, int64_t N, int D, int m, int K, int dsub,
+                         const uint8_t* __restrict__ codes, float* __restrict__ sums, float* __restrict__ counts) {
+    extern __shared__ __align__(16) float sm[];
+    float* ssum = sm;                       // K*dsub
+    float* scnt = ssum + (size_t)K * dsub;  // K
+    const int j = blockIdx.y;
+    for (int i = threadIdx.x; i < K * dsub; i += blockDim.x) ssum[i] = 0.f;
+    for (int i = threadIdx.x; i < K; i += blockDim.x) scnt[i] = 0.f;
+    __syncthreads();
+    for (int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; row < N; row += (int64_t)gridDim.x * blockDim.x) {
+        const float* xr = x + row * D + (size_t)j * dsub;
+        const int bi = codes[row * m + j];
+        for (int t = 0; t < dsub; ++t) atomicAdd(ssum + bi * dsub + t, xr[t]);
+        atomicAdd(scnt + bi, 1.f);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < K * dsub; i += blockDim.x)
+        if (ssum[i] != 0.f) atomicAdd(sums + (size_t)j * K * dsub + i, ssum[i]);
+    for (int i = threadIdx.x; i < K; i += blockDim.x)
+        if (scnt[i] != 0.f) atomicAdd(counts + (size_t)j * K + i, scnt[i]);
+}
+
 __global__ void kmeans_update_kernel(float* __restrict__ cb, const float* __restrict__ sums,
                                      const float* __restrict__ counts, int total, int dsub) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -773,6 +798,33 @@ int vdb_pq_kmeans_step(const float* x, int64_t N, int D, int m, int K, float* co
     if (gx * m < sm_count() && rb > gx) gx = (int)(rb < sm_count() ? rb : sm_count());
     kmeans_assign_kernel<<<dim3(gx, m), 256, smem, st>>>(x, N, D, m, K, dsub, codebooks, labels, sums, counts);
     int total = m * K * dsub;
+    kmeans_update_kernel<<<(total + 255) / 256, 256, 0, st>>>(codebooks, sums, counts, total, dsub);
+    count_launch(2);
+    VDB_CUDA(cudaGetLastError());
+    return VDB_OK;
+}
+
+int vdb_pq_kmeans_step_coded(const float* x, int64_t N, int D, int m, int K, const uint8_t* codes, float* codebooks,
+                             void* ws, size_t ws_bytes, void* stream) {
+    VDB_REQUIRE(N > 0 && D > 0 && m > 0 && K > 0 && K <= 256 && D % m == 0, VDB_ERR_INVALID,
+                "vdb_pq_kmeans_step_coded: bad shape");
+    const int dsub = D / m;
+    VDB_REQUIRE(x && codes && codebooks, VDB_ERR_INVALID, "vdb_pq_kmeans_step_coded: null pointer");
+    const size_t need = vdb_pq_kmeans_workspace(m, K, dsub);
+    VDB_REQUIRE(ws && ws_bytes >= need, VDB_ERR_WORKSPACE, "workspace %zu < %zu", ws_bytes, need);
+    const size_t smem = ((size_t)K * dsub + K) * 4;
+    VDB_REQUIRE(smem <= (size_t)max_smem_optin() - 1024, VDB_ERR_UNSUPPORTED, "K*dsub too large for shared memory");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    float* sums = static_cast<float*>(ws);
+    float* counts = sums + (size_t)m * K * dsub;
+    VDB_CUDA(cudaMemsetAsync(ws, 0, need, st));
+    VDB_CUDA(cudaFuncSetAttribute(kmeans_accumulate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int64_t rb = (N + 255) / 256;
+    int gx = (int)((4ll * sm_count() + m - 1) / m);
+    if (gx < 1) gx = 1;
+    if (gx > rb) gx = (int)rb;
+    kmeans_accumulate_kernel<<<dim3(gx, m), 256, smem, st>>>(x, N, D, m, K, dsub, codes, sums, counts);
+    const int total = m * K * dsub;
     kmeans_update_kernel<<<(total + 255) / 256, 256, 0, st>>>(codebooks, sums, counts, total, dsub);
     count_launch(2);
     VDB_CUDA(cudaGetLastError());

@@ -112,12 +112,19 @@ def pq_encode(x: torch.Tensor, codebooks: torch.Tensor, engine: str = "auto") ->
 
 
 def pq_kmeans_step(x: torch.Tensor, codebooks: torch.Tensor, labels: Optional[torch.Tensor] = None) -> None:
-    """One Lloyd round for all sub-spaces, in place on `codebooks` [m,K,dsub]."""
+    """One Lloyd round for all sub-spaces, in place on `codebooks` [m,K,dsub].  When the tensor-core encoder
+    applies (dsub == 8, large batch) and no labels are requested, the assignment is one encode call and the
+    round is the mean update over its codes."""
     n, d = x.shape
     m, K, dsub = codebooks.shape
     lib = load()
     nbytes = lib.vdb_pq_kmeans_workspace(m, K, dsub)
     ws = _ws("kmeans", nbytes, x.device)
+    if labels is None and n >= 4096 and lib.vdb_pq_encode_tc_supported(n, d, m, K):
+        codes = pq_encode(x, codebooks, engine="tc")
+        check(lib.vdb_pq_kmeans_step_coded(ptr(x), n, d, m, K, ptr(codes), ptr(codebooks), ptr(ws), ws.numel(),
+                                           _lib.stream_ptr(x.device)))
+        return
     check(lib.vdb_pq_kmeans_step(ptr(x), n, d, m, K, ptr(codebooks), ptr(labels), ptr(ws), ws.numel(),
                                  _lib.stream_ptr(x.device)))
 
