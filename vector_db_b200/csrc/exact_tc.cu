@@ -350,13 +350,21 @@ __global__ void tc_row_operand_kernel(const float* __restrict__ x, int64_t N, in
 // because it was dropped from a full list, whose worst entry bounds it.  One CTA per query.
 __global__ void __launch_bounds__(256)
 select_bins_kernel(const u64* __restrict__ partial, int L, int NBL, int NB, int C, int64_t N, int32_t* __restrict__ cand,
-                   float* __restrict__ tau_out) {
+                   float* __restrict__ tau_out, const float* __restrict__ qv, int D, int k, int metric, float max_norm) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     u64* buf = reinterpret_cast<u64*>(smem_raw);
     __shared__ unsigned tau_bits;          // ordered-float minimum over the full lists' worst entries
+    __shared__ float qsq_s;
+    __shared__ int keep_s;
     const int q = blockIdx.x, total = L * NBL;
-    if (threadIdx.x == 0) tau_bits = f32_to_ordered(INFINITY);
+    if (threadIdx.x == 0) { tau_bits = f32_to_ordered(INFINITY); qsq_s = 0.f; }
     __syncthreads();
+    {
+        float a = 0.f;
+        for (int t = threadIdx.x; t < D; t += blockDim.x) { const float v = qv[(size_t)q * D + t]; a = fmaf(v, v, a); }
+        a = warp_sum(a);
+        if ((threadIdx.x & 31) == 0 && a != 0.f) atomicAdd(&qsq_s, a);
+    }
     for (int i = threadIdx.x; i < C; i += blockDim.x) {
         u64 key = VDB_KEY_MAX;
         if (i < total) {
@@ -371,12 +379,33 @@ select_bins_kernel(const u64* __restrict__ partial, int L, int NBL, int NB, int 
     if (threadIdx.x == 0) {
         float tau = ordered_to_f32(tau_bits);
         if (NB - 1 < C && buf[NB - 1] != VDB_KEY_MAX) tau = fminf(tau, key_score(buf[NB - 1]));
+        // Trim: the k-th smallest bin minimum c_k bounds the k-th smallest coarse row score from above, so k rows
+        // have exact scores <= c_k + eps and no row of a bin whose minimum exceeds c_k + 2 eps can enter the
+        // top-k.  Those bins are not reranked; the first of them becomes the bound the certificate tests
+        // (a little extra slack keeps the certificate's own rounding allowance from rejecting the query).
+        int keep = NB;
+        if (k - 1 < C && buf[k - 1] != VDB_KEY_MAX) {
+            const float qn = sqrtf(qsq_s);
+            const float c = 0.00406742f;                             // 2^-8 * 1.01 + 2^-13, as in certify_kernel
+            float eps, slack;
+            if (metric == VDB_METRIC_L2) { eps = 2.f * c * qn * max_norm; slack = 4e-6f * (qn + max_norm) * (qn + max_norm); }
+            else { eps = c * qn; slack = 4e-6f * qn; }
+            const float cutoff = key_score(buf[k - 1]) + 2.f * eps + 4.f * slack;
+            // first bin (sorted ascending) above the cutoff; NB <= 32, a linear scan by one thread is fine
+            for (int j = k; j < NB && j < C; ++j) {
+                if (buf[j] == VDB_KEY_MAX) break;
+                if (key_score(buf[j]) > cutoff) { keep = j; tau = fminf(tau, key_score(buf[j])); break; }
+            }
+        }
+        keep_s = keep;
         tau_out[q] = tau;
     }
+    __syncthreads();
+    const int keep = keep_s;
     for (int i = threadIdx.x; i < NB * kBin; i += blockDim.x) {
         const int j = i / kBin, e = i - j * kBin;
         int32_t r = -1;
-        if (j < C && buf[j] != VDB_KEY_MAX) {
+        if (j < keep && j < C && buf[j] != VDB_KEY_MAX) {
             int64_t row = (int64_t)key_index(buf[j]) * kBin + e;
             if (row < N) r = (int32_t)row;
         }
@@ -627,10 +656,16 @@ int vdb_exact_topk_tc(const float* q, int Q, const float* db, const void* mirror
     const int L = p.S * kGroups;
     const int C = next_pow2(L * nbl < 64 ? 64 : L * nbl);
     VDB_CUDA(cudaFuncSetAttribute(select_bins_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, C * 8));
-    select_bins_kernel<<<Q, 256, (size_t)C * 8, st>>>(partial, L, nbl, kNBFinal, C, N, cand, tau);
+    // bins handed to the rerank per query (select_bins_kernel drops those that provably cannot matter);
+    // debug bits 12..19 override the count, bit 4 disables the trimming
+    int nbf = kNBFinal;
+    if ((g_tc_flags >> 12) & 0xFF) nbf = (g_tc_flags >> 12) & 0xFF;
+    if (nbf > kNBFinal) nbf = kNBFinal;
+    select_bins_kernel<<<Q, 256, (size_t)C * 8, st>>>(partial, L, nbl, nbf, C, N, cand, tau, q, D, k, metric,
+                                                      (g_tc_flags & 16) ? INFINITY : db_max_norm);
     count_launch(3);
     VDB_CUDA(cudaGetLastError());
-    rc = vdb_rerank_f32(q, Q, db, ids, N, D, cand, kNBFinal * kBin, k, metric, out_d, out_i, stream);
+    rc = vdb_rerank_f32(q, Q, db, ids, N, D, cand, nbf * kBin, k, metric, out_d, out_i, stream);
     if (rc) return rc;
     VDB_CUDA(cudaMemsetAsync(out_uncertified, 0, 4, st));
     const int warps_per_block = 8;
