@@ -214,9 +214,27 @@ def run_ours(args):
     X = index.store.vecs[:N_ROWS]
     Q_pin = Qd.cpu().pin_memory()
 
+    # shard exchange: one fused kernel over NVLink peer memory (csrc/exchange.cu); --exchange nccl selects the
+    # packed all-gather + merge kernel instead, which is also what a box without peer mapping ends up with
+    exchange, peer = "none", None
+    if world > 1:
+        exchange = args.exchange
+        if exchange == "peer":
+            try:
+                peer = sharded.PeerExchange(N_QUERIES * K, dev)
+            except Exception as e:                                  # noqa: BLE001 -- no symmetric memory here
+                print(f"bench.py: peer exchange unavailable ({type(e).__name__}: {e}); using NCCL", file=sys.stderr)
+                exchange = "nccl"
+        flag = torch.tensor([1 if exchange == "peer" else 0], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)                 # all ranks must take the same path
+        if int(flag.item()) == 0:
+            exchange, peer = "nccl", None
+
     def merge(d, i):
         if world == 1:
             return d, i
+        if peer is not None:
+            return peer.exchange_merge(d, i, descending=True)
         gd, gi = sharded.gather_topk(d, i)                      # one packed NCCL all-gather
         return sharded.merge_shards(gd, gi, descending=True)
 
@@ -272,6 +290,8 @@ def run_ours(args):
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
     e2e_step = float(e2e_s.item()) / args.steps
 
+    if peer is not None:
+        peer.check()                                                # raises if any exchange gave up waiting for a peer
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -304,7 +324,10 @@ def run_ours(args):
             "engine": engine, "rows_total": N_ROWS * world, "recall_at_10_vs_oracle": recall,
             "uncertified_queries_last_step": int(index.last_uncertified),
             "value_definition": "queries/s x shards: every query is answered over all shards; each GPU scans its "
-                                "own 1M rows, per-shard top-10 merged after an NCCL all-gather",
+                                "own 1M rows, per-shard top-10 exchanged and merged on the GPU",
+            "shard_exchange": {"none": "single GPU", "peer": "one fused kernel: NVLink peer-memory stores + arrival "
+                               "counters + merge (csrc/exchange.cu)",
+                               "nccl": "packed NCCL all-gather + merge kernel"}[exchange],
             "l2_policy": "inputs (1.5 GB of rows per GPU) are larger than the 126 MB L2",
             "kernel_ms": {s: (round(v[1] / max(v[0], 1), 4), v[0]) for s, v in prof.items() if v[0]},
         },
@@ -333,6 +356,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--engine", default="auto", choices=["auto", "f32", "tc"])
+    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
+                    help="N>1: fused peer-memory exchange+merge kernel, or NCCL all-gather + merge kernel")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

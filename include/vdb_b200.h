@@ -268,6 +268,23 @@ int vdb_ivf_adc_scan(const uint8_t* codes /*[dev] total*m*/, int m, const float*
 int vdb_merge_topk(const float* d, const int64_t* i, int L, int Q, int k, int descending,
                    float* out_d, int64_t* out_i, void* stream);
 
+/* Exchange + merge in one kernel over NVLink peer memory (csrc/exchange.cu).  Every rank owns an exchange
+ * buffer of vdb_exchange_bytes(world, cap) bytes, zero-filled once, mapped into every peer (torch symmetric
+ * memory; cap >= Q*k elements per list plane); peer_bufs is the device array of the `world` base addresses in
+ * rank order.  Call number c (0, 1, ... in step on all ranks, one stream per rank) passes parity = c & 1 and
+ * target = the running sum of vdb_exchange_grid(Q) over the calls made so far with that parity, this one
+ * included.  Each rank stores its lists d/i [Q][k] into every rank's buffer, waits for all ranks' stores and
+ * merges: out = k best by (value, shard, position), exactly vdb_merge_topk of the all-gathered lists.
+ * status (device int32) becomes 1 if a wait ran into its clock limit (a peer never arrived).
+ * Replaces, for this path, torch.distributed.all_gather + vdb_merge_topk (no reference symbol: the reference
+ * scales by replicas only, README.md:116-126). */
+size_t vdb_exchange_bytes(int world, int64_t cap);
+int vdb_exchange_grid(int Q);
+int vdb_exchange_merge_topk(const float* d /*[dev] Q*k*/, const int64_t* i /*[dev] Q*k*/, int Q, int k, int descending,
+                            const uint64_t* peer_bufs /*[dev] world*/, int rank, int world, int64_t cap, int parity,
+                            uint32_t target, float* out_d /*[dev] Q*k*/, int64_t* out_i /*[dev] Q*k*/,
+                            int32_t* status /*[dev]*/, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

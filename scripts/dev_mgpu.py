@@ -51,4 +51,29 @@ gd, gi = timed("gather", lambda: sharded.gather_topk(d, i))
 timed("merge", lambda: sharded.merge_shards(gd, gi, descending=True))
 timed("search+gather", lambda: sharded.gather_topk(*index.search_device(Qd, K)))
 timed("full step", lambda: sharded.merge_shards(*sharded.gather_topk(*index.search_device(Qd, K)), descending=True))
+ex = sharded.PeerExchange(Q * K, dev)
+timed("full step, fused peer exchange", lambda: ex.exchange_merge(*index.search_device(Qd, K), descending=True))
+timed("search_device again", lambda: index.search_device(Qd, K))
+
+
+def ev_timed(name, fn, iters=20):
+    for _ in range(3):
+        fn()
+    torch.cuda.synchronize()
+    dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record()
+    host_ms = (time.perf_counter() - t0) / iters * 1e3
+    torch.cuda.synchronize()
+    print(f"[rank {rank}] {name}: device {e0.elapsed_time(e1) / iters:.3f} ms/iter, host enqueue {host_ms:.3f} ms/iter", flush=True)
+
+
+ev_timed("search_device (events)", lambda: index.search_device(Qd, K))
+ev_timed("full step fused (events)", lambda: ex.exchange_merge(*index.search_device(Qd, K), descending=True))
+ex.check()
 dist.destroy_process_group()

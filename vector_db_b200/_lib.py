@@ -65,6 +65,9 @@ SIGNATURES = {
     "vdb_ivf_adc_workspace": (_sz, [_i, _i, _i]),
     "vdb_ivf_adc_scan": (_i, [_p, _i, _p, _i, _p, _p, _p, _p, _i, _i, _p, _p, _p, _sz, _p]),
     "vdb_merge_topk": (_i, [_p, _p, _i, _i, _i, _i, _p, _p, _p]),
+    "vdb_exchange_bytes": (_sz, [_i, _i64]),
+    "vdb_exchange_grid": (_i, [_i]),
+    "vdb_exchange_merge_topk": (_i, [_p, _p, _i, _i, _i, _p, _i, _i, _i64, _i, C.c_uint32, _p, _p, _p, _p]),
 }
 
 _lib = None

@@ -181,6 +181,9 @@ size_t exact_f32_subset_workspace(int Q, int64_t N, int D, int k);
 int exact_f32_subset(const float* q, int Q, const float* db, const int64_t* ids, int64_t N, int D, int k, int metric,
                      const int32_t* qsel, const int32_t* qcount, float* out_d, int64_t* out_i, void* ws, size_t ws_bytes,
                      cudaStream_t st);
+// (exact_f32.cu) vdb_rerank_f32 with an optional per-query count of meaningful candidates (front-packed)
+int rerank_f32_counted(const float* q, int Q, const float* db, const int64_t* ids, int64_t N, int D, const int32_t* cand,
+                       const int32_t* cand_cnt, int R, int k, int metric, float* out_d, int64_t* out_i, void* stream);
 #endif  // __CUDACC__
 
 }  // namespace vdb

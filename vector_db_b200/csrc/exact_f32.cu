@@ -242,14 +242,22 @@ finalize_keys_kernel(const u64* __restrict__ keys, int L, int k, int C, const in
 template <int METRIC>
 __global__ void __launch_bounds__(256)
 rerank_f32_kernel(const float* __restrict__ q, const float* __restrict__ db, const int64_t* __restrict__ ids,
-                  int64_t N, int D, const int32_t* __restrict__ cand, int R, int k, int C,
-                  float* __restrict__ out_d, int64_t* __restrict__ out_i) {
+                  int64_t N, int D, const int32_t* __restrict__ cand, const int32_t* __restrict__ cand_cnt, int R_max,
+                  int k, int C_max, float* __restrict__ out_d, int64_t* __restrict__ out_i) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    u64* buf = reinterpret_cast<u64*>(smem_raw);          // C
-    float* qs = reinterpret_cast<float*>(buf + C);        // D
+    u64* buf = reinterpret_cast<u64*>(smem_raw);          // C_max
+    float* qs = reinterpret_cast<float*>(buf + C_max);    // D
     __shared__ float qn_s;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
     const int qi = blockIdx.x;
+    // cand_cnt: only the first cand_cnt[qi] entries of the query's candidate row are meaningful -- the sort
+    // then runs over the next power of two of that count instead of R_max
+    int R = R_max, C = C_max;
+    if (cand_cnt) {
+        R = min(R_max, max(0, cand_cnt[qi]));
+        C = 32;
+        while (C < R) C <<= 1;
+    }
     for (int t = tid; t < D; t += blockDim.x) qs[t] = q[(size_t)qi * D + t];
     for (int i = tid; i < C; i += blockDim.x) buf[i] = VDB_KEY_MAX;
     __syncthreads();
@@ -264,7 +272,7 @@ rerank_f32_kernel(const float* __restrict__ q, const float* __restrict__ db, con
     }
     const bool vec4 = (D & 3) == 0;
     for (int c = warp; c < R; c += nwarp) {
-        const int32_t r = cand[(size_t)qi * R + c];
+        const int32_t r = cand[(size_t)qi * R_max + c];
         if (r < 0 || (int64_t)r >= N) continue;
         const float* row = db + (size_t)r * D;
         float acc = 0.f, xx = 0.f;
@@ -506,6 +514,14 @@ int vdb_exact_topk_f32(const float* q, int Q, const float* db, const int64_t* id
 
 int vdb_rerank_f32(const float* q, int Q, const float* db, const int64_t* ids, int64_t N, int D, const int32_t* cand,
                    int R, int k, int metric, float* out_d, int64_t* out_i, void* stream) {
+    return vdb::rerank_f32_counted(q, Q, db, ids, N, D, cand, nullptr, R, k, metric, out_d, out_i, stream);
+}
+
+}  // extern "C"
+
+namespace vdb {
+int rerank_f32_counted(const float* q, int Q, const float* db, const int64_t* ids, int64_t N, int D, const int32_t* cand,
+                       const int32_t* cand_cnt, int R, int k, int metric, float* out_d, int64_t* out_i, void* stream) {
     VDB_REQUIRE(Q >= 0 && D > 0 && R > 0 && k > 0, VDB_ERR_INVALID, "vdb_rerank_f32: bad shape");
     VDB_REQUIRE(metric == VDB_METRIC_L2 || metric == VDB_METRIC_COSINE, VDB_ERR_INVALID, "unknown metric %d", metric);
     VDB_REQUIRE(R <= 16384, VDB_ERR_UNSUPPORTED, "R=%d > 16384", R);
@@ -518,15 +534,18 @@ int vdb_rerank_f32(const float* q, int Q, const float* db, const int64_t* ids, i
     ProfScope prof(kProfRerank, st);
     if (metric == VDB_METRIC_L2) {
         VDB_CUDA(cudaFuncSetAttribute(rerank_f32_kernel<VDB_METRIC_L2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        rerank_f32_kernel<VDB_METRIC_L2><<<Q, 256, smem, st>>>(q, db, ids, N, D, cand, R, k, C, out_d, out_i);
+        rerank_f32_kernel<VDB_METRIC_L2><<<Q, 256, smem, st>>>(q, db, ids, N, D, cand, cand_cnt, R, k, C, out_d, out_i);
     } else {
         VDB_CUDA(cudaFuncSetAttribute(rerank_f32_kernel<VDB_METRIC_COSINE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        rerank_f32_kernel<VDB_METRIC_COSINE><<<Q, 256, smem, st>>>(q, db, ids, N, D, cand, R, k, C, out_d, out_i);
+        rerank_f32_kernel<VDB_METRIC_COSINE><<<Q, 256, smem, st>>>(q, db, ids, N, D, cand, cand_cnt, R, k, C, out_d, out_i);
     }
     count_launch(1);
     VDB_CUDA(cudaGetLastError());
     return VDB_OK;
 }
+}  // namespace vdb
+
+extern "C" {
 
 int vdb_merge_topk(const float* d, const int64_t* i, int L, int Q, int k, int descending, float* out_d, int64_t* out_i,
                    void* stream) {

@@ -36,7 +36,7 @@ constexpr int kBBytes = kTileN * kBlockK * 2;    // 32 KB per B stage
 constexpr int kBin = VDB_TC_BIN;
 constexpr int kMaxStages = 8;
 constexpr int kNBLMax = 16;              // bins kept per (query, slice, epilogue group): template NBL <= this
-constexpr int kNBFinal = 32;             // bins reranked per query
+constexpr int kNBFinal = 64;             // bins handed to the rerank per query, before trimming
 constexpr int kGroups = 2;               // epilogue groups == accumulator stages
 
 constexpr int kA2Bytes = kTileM * 32;            // 4 KB: the L2 norm block of the query tile (16 bf16 per row)
@@ -350,7 +350,7 @@ __global__ void tc_row_operand_kernel(const float* __restrict__ x, int64_t N, in
 // because it was dropped from a full list, whose worst entry bounds it.  One CTA per query.
 __global__ void __launch_bounds__(256)
 select_bins_kernel(const u64* __restrict__ partial, int L, int NBL, int NB, int C, int64_t N, int32_t* __restrict__ cand,
-                   float* __restrict__ tau_out, const float* __restrict__ qv, int D, int k, int metric, float max_norm) {
+                   int32_t* __restrict__ cand_cnt, float* __restrict__ tau_out, const float* __restrict__ qv, int D, int k, int metric, float max_norm) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     u64* buf = reinterpret_cast<u64*>(smem_raw);
     __shared__ unsigned tau_bits;          // ordered-float minimum over the full lists' worst entries
@@ -383,29 +383,32 @@ select_bins_kernel(const u64* __restrict__ partial, int L, int NBL, int NB, int 
         // have exact scores <= c_k + eps and no row of a bin whose minimum exceeds c_k + 2 eps can enter the
         // top-k.  Those bins are not reranked; the first of them becomes the bound the certificate tests
         // (a little extra slack keeps the certificate's own rounding allowance from rejecting the query).
-        int keep = NB;
+        const int nb = NB < C ? NB : C;
+        int keep = nb;
+        float cutoff = INFINITY;
         if (k - 1 < C && buf[k - 1] != VDB_KEY_MAX) {
             const float qn = sqrtf(qsq_s);
             const float c = 0.00406742f;                             // 2^-8 * 1.01 + 2^-13, as in certify_kernel
             float eps, slack;
             if (metric == VDB_METRIC_L2) { eps = 2.f * c * qn * max_norm; slack = 4e-6f * (qn + max_norm) * (qn + max_norm); }
             else { eps = c * qn; slack = 4e-6f * qn; }
-            const float cutoff = key_score(buf[k - 1]) + 2.f * eps + 4.f * slack;
-            // first bin (sorted ascending) above the cutoff; NB <= 32, a linear scan by one thread is fine
-            for (int j = k; j < NB && j < C; ++j) {
-                if (buf[j] == VDB_KEY_MAX) break;
-                if (key_score(buf[j]) > cutoff) { keep = j; tau = fminf(tau, key_score(buf[j])); break; }
-            }
+            cutoff = key_score(buf[k - 1]) + 2.f * eps + 4.f * slack;
+        }
+        // first empty slot, or first bin (sorted ascending) above the cutoff; nb <= 64, one thread scans it
+        for (int j = 0; j < nb; ++j) {
+            if (buf[j] == VDB_KEY_MAX) { keep = j; break; }
+            if (j >= k && key_score(buf[j]) > cutoff) { keep = j; tau = fminf(tau, key_score(buf[j])); break; }
         }
         keep_s = keep;
+        cand_cnt[q] = keep * kBin;
         tau_out[q] = tau;
     }
     __syncthreads();
     const int keep = keep_s;
-    for (int i = threadIdx.x; i < NB * kBin; i += blockDim.x) {
+    for (int i = threadIdx.x; i < keep * kBin; i += blockDim.x) {          // the rerank reads cand_cnt entries only
         const int j = i / kBin, e = i - j * kBin;
         int32_t r = -1;
-        if (j < keep && j < C && buf[j] != VDB_KEY_MAX) {
+        if (j < C && buf[j] != VDB_KEY_MAX) {
             int64_t row = (int64_t)key_index(buf[j]) * kBin + e;
             if (row < N) r = (int32_t)row;
         }
@@ -549,7 +552,7 @@ static bool plan_tc(int Q, int64_t N, int D, int k, int metric, TcPlan* p) {
 }
 
 struct TcWorkspace {
-    size_t qbf16, partial, cand, tau, rescan, rescan_bytes, total;
+    size_t qbf16, partial, cand, tau, cand_cnt, rescan, rescan_bytes, total;
 };
 
 static TcWorkspace tc_workspace(const TcPlan& p, int Q, int64_t N, int D, int k) {
@@ -560,6 +563,7 @@ static TcWorkspace tc_workspace(const TcPlan& p, int Q, int64_t N, int D, int k)
     w.partial = take((size_t)Q * p.S * kGroups * kNBLMax * 8);
     w.cand = take((size_t)Q * kNBFinal * kBin * 4);
     w.tau = take((size_t)Q * 4);
+    w.cand_cnt = take((size_t)Q * 4);
     w.rescan_bytes = exact_f32_subset_workspace(Q, N, D, k);      // fp32 rescan of uncertified queries
     w.rescan = take(w.rescan_bytes);
     w.total = off;
@@ -623,6 +627,7 @@ int vdb_exact_topk_tc(const float* q, int Q, const float* db, const void* mirror
     u64* partial = reinterpret_cast<u64*>(base + w.partial);
     int32_t* cand = reinterpret_cast<int32_t*>(base + w.cand);
     float* tau = reinterpret_cast<float*>(base + w.tau);
+    int32_t* cand_cnt = reinterpret_cast<int32_t*>(base + w.cand_cnt);
 
     // per-list depth: lists of 8 are enough when there are many of them (L * 8 >= 4 * kNBFinal), debug bit 2 forces 16
     const int nbl = ((g_tc_flags & 4) || p.S * kGroups * 8 < 4 * kNBFinal) ? 16 : 8;
@@ -661,11 +666,11 @@ int vdb_exact_topk_tc(const float* q, int Q, const float* db, const void* mirror
     int nbf = kNBFinal;
     if ((g_tc_flags >> 12) & 0xFF) nbf = (g_tc_flags >> 12) & 0xFF;
     if (nbf > kNBFinal) nbf = kNBFinal;
-    select_bins_kernel<<<Q, 256, (size_t)C * 8, st>>>(partial, L, nbl, nbf, C, N, cand, tau, q, D, k, metric,
+    select_bins_kernel<<<Q, 256, (size_t)C * 8, st>>>(partial, L, nbl, nbf, C, N, cand, cand_cnt, tau, q, D, k, metric,
                                                       (g_tc_flags & 16) ? INFINITY : db_max_norm);
     count_launch(3);
     VDB_CUDA(cudaGetLastError());
-    rc = vdb_rerank_f32(q, Q, db, ids, N, D, cand, nbf * kBin, k, metric, out_d, out_i, stream);
+    rc = rerank_f32_counted(q, Q, db, ids, N, D, cand, cand_cnt, nbf * kBin, k, metric, out_d, out_i, stream);
     if (rc) return rc;
     VDB_CUDA(cudaMemsetAsync(out_uncertified, 0, 4, st));
     const int warps_per_block = 8;

@@ -248,6 +248,30 @@ def merge_topk(d: torch.Tensor, i: torch.Tensor, descending: bool = False):
     return out_d, out_i
 
 
+def exchange_bytes(world: int, cap: int) -> int:
+    return int(load().vdb_exchange_bytes(int(world), int(cap)))
+
+
+def exchange_grid(Q: int) -> int:
+    return int(load().vdb_exchange_grid(int(Q)))
+
+
+def exchange_merge_topk(d: torch.Tensor, i: torch.Tensor, peer_bufs: torch.Tensor, rank: int, world: int, cap: int,
+                        parity: int, target: int, status: torch.Tensor, descending: bool = False):
+    """Fused shard exchange + merge over peer memory (csrc/exchange.cu); d f32 [Q,k], i i64 [Q,k] local lists;
+    peer_bufs i64 [world] device array of exchange-buffer addresses.  Returns merged (d [Q,k], i [Q,k])."""
+    d = _f32(d, "d")
+    if i.dtype != torch.int64 or not i.is_contiguous():
+        i = i.to(torch.int64).contiguous()
+    Q, k = d.shape
+    out_d = torch.empty((Q, k), dtype=torch.float32, device=d.device)
+    out_i = torch.empty((Q, k), dtype=torch.int64, device=d.device)
+    check(load().vdb_exchange_merge_topk(ptr(d), ptr(i), Q, k, int(descending), ptr(peer_bufs), int(rank), int(world),
+                                         int(cap), int(parity), int(target) & 0xFFFFFFFF, ptr(out_d), ptr(out_i),
+                                         ptr(status), _lib.stream_ptr(d.device)))
+    return out_d, out_i
+
+
 def hnsw_search(q: torch.Tensor, db: torch.Tensor, n_rows: int, adj0: torch.Tensor, adj_up: torch.Tensor,
                 up_ptr: torch.Tensor, entry_row: int, max_level: int, ef: int, k: int,
                 alive: Optional[torch.Tensor] = None, flt: Optional[torch.Tensor] = None, want_stats: bool = False):
