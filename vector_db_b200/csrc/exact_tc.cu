@@ -36,7 +36,7 @@ constexpr int kBBytes = kTileN * kBlockK * 2;    // 32 KB per B stage
 constexpr int kBin = VDB_TC_BIN;
 constexpr int kMaxStages = 8;
 constexpr int kNBLMax = 16;              // bins kept per (query, slice, epilogue group): template NBL <= this
-constexpr int kNBFinal = 64;             // bins handed to the rerank per query, before trimming
+constexpr int kNBFinal = 64;  // bins handed to the rerank per query, before trimming
 constexpr int kGroups = 2;               // epilogue groups == accumulator stages
 
 constexpr int kA2Bytes = kTileM * 32;            // 4 KB: the L2 norm block of the query tile (16 bf16 per row)
