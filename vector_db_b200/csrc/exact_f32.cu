@@ -271,36 +271,74 @@ rerank_f32_kernel(const float* __restrict__ q, const float* __restrict__ db, con
         __syncthreads();
     }
     const bool vec4 = (D & 3) == 0;
-    for (int c = warp; c < R; c += nwarp) {
-        const int32_t r = cand[(size_t)qi * R_max + c];
-        if (r < 0 || (int64_t)r >= N) continue;
-        const float* row = db + (size_t)r * D;
-        float acc = 0.f, xx = 0.f;
-        if (vec4) {
-            const float4* row4 = reinterpret_cast<const float4*>(row);
-            for (int t = lane; t < (D >> 2); t += 32) {
-                const float4 x = __ldg(row4 + t);
+    if (vec4) {
+        // four candidate rows in flight per warp: their loads are independent, the per-row arithmetic (lane-strided
+        // fma chain, then the shuffle tree) is the single-row order -- one row at a time the kernel sat on HBM latency
+        constexpr int RW = 4;
+        const int nchunk = D >> 2;
+        for (int base = warp * RW; base < R; base += nwarp * RW) {
+            int my_r = -1;
+            if (lane < RW && base + lane < R) {
+                my_r = cand[(size_t)qi * R_max + base + lane];
+                if ((int64_t)my_r >= N) my_r = -1;
+            }
+            int rows[RW];
+#pragma unroll
+            for (int j = 0; j < RW; ++j) rows[j] = __shfl_sync(0xffffffffu, my_r, j);
+            if (rows[0] < 0 && rows[1] < 0 && rows[2] < 0 && rows[3] < 0) continue;
+            float acc[RW], xx[RW];
+#pragma unroll
+            for (int j = 0; j < RW; ++j) { acc[j] = 0.f; xx[j] = 0.f; }
+            for (int t = lane; t < nchunk; t += 32) {
+                float4 x[RW];
+#pragma unroll
+                for (int j = 0; j < RW; ++j)
+                    x[j] = rows[j] >= 0 ? __ldg(reinterpret_cast<const float4*>(db + (size_t)rows[j] * D) + t)
+                                        : make_float4(0.f, 0.f, 0.f, 0.f);
                 const float4 qv = *reinterpret_cast<const float4*>(qs + 4 * t);
-                if (METRIC == VDB_METRIC_L2) {
-                    float d0 = qv.x - x.x, d1 = qv.y - x.y, d2 = qv.z - x.z, d3 = qv.w - x.w;
-                    acc = fmaf(d0, d0, acc); acc = fmaf(d1, d1, acc); acc = fmaf(d2, d2, acc); acc = fmaf(d3, d3, acc);
-                } else {
-                    acc = fmaf(qv.x, x.x, acc); acc = fmaf(qv.y, x.y, acc); acc = fmaf(qv.z, x.z, acc); acc = fmaf(qv.w, x.w, acc);
-                    xx = fmaf(x.x, x.x, xx); xx = fmaf(x.y, x.y, xx); xx = fmaf(x.z, x.z, xx); xx = fmaf(x.w, x.w, xx);
+#pragma unroll
+                for (int j = 0; j < RW; ++j) {
+                    if (METRIC == VDB_METRIC_L2) {
+                        const float d0 = qv.x - x[j].x, d1 = qv.y - x[j].y, d2 = qv.z - x[j].z, d3 = qv.w - x[j].w;
+                        acc[j] = fmaf(d0, d0, acc[j]); acc[j] = fmaf(d1, d1, acc[j]);
+                        acc[j] = fmaf(d2, d2, acc[j]); acc[j] = fmaf(d3, d3, acc[j]);
+                    } else {
+                        acc[j] = fmaf(qv.x, x[j].x, acc[j]); acc[j] = fmaf(qv.y, x[j].y, acc[j]);
+                        acc[j] = fmaf(qv.z, x[j].z, acc[j]); acc[j] = fmaf(qv.w, x[j].w, acc[j]);
+                        xx[j] = fmaf(x[j].x, x[j].x, xx[j]); xx[j] = fmaf(x[j].y, x[j].y, xx[j]);
+                        xx[j] = fmaf(x[j].z, x[j].z, xx[j]); xx[j] = fmaf(x[j].w, x[j].w, xx[j]);
+                    }
                 }
             }
-        } else {
+            float a_mine = 0.f, x_mine = 0.f;
+#pragma unroll
+            for (int j = 0; j < RW; ++j) {
+                const float a = warp_sum(acc[j]);
+                const float b = (METRIC == VDB_METRIC_COSINE) ? warp_sum(xx[j]) : 0.f;
+                if (lane == j) { a_mine = a; x_mine = b; }
+            }
+            if (my_r >= 0) {
+                const float score = (METRIC == VDB_METRIC_L2) ? sqrtf(a_mine) : -(a_mine / (sqrtf(x_mine) * qn_s));
+                buf[base + lane] = pack_key(score, (uint32_t)my_r);
+            }
+        }
+    } else {
+        for (int c = warp; c < R; c += nwarp) {
+            const int32_t r = cand[(size_t)qi * R_max + c];
+            if (r < 0 || (int64_t)r >= N) continue;
+            const float* row = db + (size_t)r * D;
+            float acc = 0.f, xx = 0.f;
             for (int t = lane; t < D; t += 32) {
                 const float x = __ldg(row + t);
                 if (METRIC == VDB_METRIC_L2) { float d = qs[t] - x; acc = fmaf(d, d, acc); }
                 else { acc = fmaf(qs[t], x, acc); xx = fmaf(x, x, xx); }
             }
-        }
-        acc = warp_sum(acc);
-        if (METRIC == VDB_METRIC_COSINE) xx = warp_sum(xx);
-        if (lane == 0) {
-            float score = (METRIC == VDB_METRIC_L2) ? sqrtf(acc) : -(acc / (sqrtf(xx) * qn_s));
-            buf[c] = pack_key(score, (uint32_t)r);
+            acc = warp_sum(acc);
+            if (METRIC == VDB_METRIC_COSINE) xx = warp_sum(xx);
+            if (lane == 0) {
+                float score = (METRIC == VDB_METRIC_L2) ? sqrtf(acc) : -(acc / (sqrtf(xx) * qn_s));
+                buf[c] = pack_key(score, (uint32_t)r);
+            }
         }
     }
     __syncthreads();
