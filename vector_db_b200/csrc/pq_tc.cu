@@ -41,14 +41,13 @@ constexpr int kEtStageBytes = 2 * kEtABytes + 3 * kEtBBytes;   // x | x_lo | hi(
 constexpr int kEtMaxStages = 8;
 
 struct EtSmem {
-    int stage_off, ones_off, mask_off, codes_off, bar_off, total;
+    int stage_off, ones_off, codes_off, bar_off, total;
 };
 __host__ __device__ inline EtSmem et_layout(int stages, int m) {
     EtSmem L;
     L.stage_off = 0;
     L.ones_off = stages * kEtStageBytes;                       // 32 KB stages keep 1024-byte alignment
-    L.mask_off = L.ones_off + kEtABytes;
-    L.codes_off = L.mask_off + 8 * 256 * 4;                    // candidate masks [8 chunks][256 epilogue threads]
+    L.codes_off = L.ones_off + kEtABytes;
     L.bar_off = (L.codes_off + kEtRows * m + 15) & ~15;        // code staging [128 rows][m]
     L.total = L.bar_off + (3 * kEtMaxStages + 8) * 8 + 16;
     return L;
@@ -100,23 +99,43 @@ __global__ void pq_tc_operands_kernel(const float* __restrict__ cb, int m, int K
     if (threadIdx.x == 0) cmax[j] = sqrtf(red[0]) * 1.0000005f;     // |c| from the fma-order |c|^2, rounded up
 }
 
-__device__ __forceinline__ float min32(const float (&v)[32]) {
-    float a = fminf(fminf(v[0], v[1]), v[2]), b = fminf(fminf(v[3], v[4]), v[5]);
-    float c = fminf(fminf(v[6], v[7]), v[8]), d = fminf(fminf(v[9], v[10]), v[11]);
-    float e = fminf(fminf(v[12], v[13]), v[14]), f = fminf(fminf(v[15], v[16]), v[17]);
-    float g = fminf(fminf(v[18], v[19]), v[20]), h = fminf(fminf(v[21], v[22]), v[23]);
-    float i = fminf(fminf(v[24], v[25]), v[26]), j = fminf(fminf(v[27], v[28]), v[29]);
-    float k = fminf(v[30], v[31]);
-    a = fminf(fminf(a, b), c); d = fminf(fminf(d, e), f); g = fminf(fminf(g, h), i); j = fminf(j, k);
-    return fminf(fminf(a, d), fminf(g, j));
+__device__ __forceinline__ float min3f(float a, float b, float c) { return fminf(fminf(a, b), c); }   // one FMNMX3
+
+// minimum of v[O .. O+15]: 8 instructions
+template <int O>
+__device__ __forceinline__ float min16(const float (&v)[32]) {
+    const float a = min3f(v[O + 0], v[O + 1], v[O + 2]), b = min3f(v[O + 3], v[O + 4], v[O + 5]);
+    const float c = min3f(v[O + 6], v[O + 7], v[O + 8]), d = min3f(v[O + 9], v[O + 10], v[O + 11]);
+    const float e = min3f(v[O + 12], v[O + 13], v[O + 14]);
+    return fminf(min3f(a, b, c), min3f(d, e, v[O + 15]));
+}
+__device__ __forceinline__ float min16(const float (&v)[16]) {
+    const float a = min3f(v[0], v[1], v[2]), b = min3f(v[3], v[4], v[5]);
+    const float c = min3f(v[6], v[7], v[8]), d = min3f(v[9], v[10], v[11]);
+    const float e = min3f(v[12], v[13], v[14]);
+    return fminf(min3f(a, b, c), min3f(d, e, v[15]));
+}
+
+// One 32-column chunk CH of a row's 256 scores folded into two families of minima (1 instruction per score):
+//   A[a] = min over the 16 consecutive centroids 16a .. 16a+15          (a = 2 CH, 2 CH + 1)
+//   B[b] = min over the 16 centroids with index = b (mod 16)            (running over all chunks)
+// Two different centroids differ in a or in b, so "exactly one A and exactly one B within the margin" proves
+// that exactly one centroid is within the margin -- and names it (16 a + b) -- without a second pass over the
+// scores and without a per-score compare: the margin test runs over 32 minima instead of 256 scores.
+template <int CH>
+__device__ __forceinline__ void fold_chunk(const float (&v)[32], float (&A)[16], float (&B)[16]) {
+    A[2 * CH] = min16<0>(v);
+    A[2 * CH + 1] = min16<16>(v);
+#pragma unroll
+    for (int i = 0; i < 16; ++i) B[i] = min3f(B[i], v[i], v[i + 16]);
 }
 
 // bit i of the result: v[i] <= thr.  Written as setp + predicated or (2 SASS instructions per element);
 // the plain C++ form compiles to FSETP + SEL + LOP3.
-__device__ __forceinline__ uint32_t le_mask32(const float (&v)[32], float thr) {
+__device__ __forceinline__ uint32_t le_mask16(const float (&v)[16], float thr) {
     uint32_t mk[4] = {0u, 0u, 0u, 0u};          // four independent chains: the predicated ORs of one chain serialise
 #pragma unroll
-    for (int i = 0; i < 32; ++i)
+    for (int i = 0; i < 16; ++i)
         asm("{\n\t.reg .pred p;\n\tsetp.le.f32 p, %1, %2;\n\t@p or.b32 %0, %0, %3;\n\t}"
             : "+r"(mk[i & 3]) : "f"(v[i]), "f"(thr), "r"(1u << i));
     return (mk[0] | mk[1]) | (mk[2] | mk[3]);
@@ -132,7 +151,6 @@ pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     const EtSmem L = et_layout(stages, m);
     unsigned char* sStage = smem + L.stage_off;
     float* sOnes = reinterpret_cast<float*>(smem + L.ones_off);
-    uint32_t* sMask = reinterpret_cast<uint32_t*>(smem + L.mask_off);
     uint8_t* sCodes = smem + L.codes_off;
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L.bar_off);
     uint64_t* full = bars;                          // [stages]
@@ -277,75 +295,50 @@ pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                     b.x += bl.x; b.y += bl.y; b.z += bl.z; b.w += bl.w;
                     xs[0] = a.x; xs[1] = a.y; xs[2] = a.z; xs[3] = a.w; xs[4] = b.x; xs[5] = b.y; xs[6] = b.z; xs[7] = b.w;
                 }
-                // Two 32-column register buffers: while one chunk is reduced the next one's TMEM load is in
-                // flight (tcgen05.wait::ld waits for ALL outstanding loads, so exactly one is outstanding at
-                // every wait).  With a single buffer each of the 16 chunk visits exposed the full TMEM latency.
-                float va[32], vb[32];
-                // pass 1: minimum score of the row, half by half (the MMAs of columns 128..255 may still be running)
-                float gmin = INFINITY;
-                tmem_ld_x32(taddr, va);
-#pragma unroll 1
-                for (int ch = 0; ch < 4; ch += 2) {
-                    tmem_ld_wait(va);
-                    tmem_ld_x32(taddr + (uint32_t)((ch + 1) * 32), vb);
-                    gmin = fminf(gmin, min32(va));
-                    tmem_ld_wait(vb);
-                    if (ch + 2 < 4) tmem_ld_x32(taddr + (uint32_t)((ch + 2) * 32), va);
-                    gmin = fminf(gmin, min32(vb));
-                }
-                mbar_wait(&tmem_full[eg * 2 + 1], phase);
-                phase ^= 1;
-                tc_fence_after();
-                tmem_ld_x32(taddr + 128u, va);
-#pragma unroll 1
-                for (int ch = 4; ch < 8; ch += 2) {
-                    tmem_ld_wait(va);
-                    tmem_ld_x32(taddr + (uint32_t)((ch + 1) * 32), vb);
-                    gmin = fminf(gmin, min32(va));
-                    tmem_ld_wait(vb);
-                    tmem_ld_x32(taddr + (uint32_t)(((ch + 2) & 7) * 32), va);     // last round: chunk 0 again, for pass 2
-                    gmin = fminf(gmin, min32(vb));
-                }
-                // rigorous candidate margin (see file header): operand split error + fp32 accumulation / reference rounding
                 float xx = 0.f;
 #pragma unroll
                 for (int t = 0; t < 8; ++t) xx = fmaf(xs[t], xs[t], xx);
                 const float xn = sqrtf(xx) * 1.0000005f, cm_j = __ldg(cmax + j);
-                const float thr = gmin + 1.2e-5f * xn * cm_j + 1e-5f * (xn + cm_j) * (xn + cm_j);
-                // pass 2: every centroid within the margin; each half is handed back to the MMA as soon as it is read
-                int cnt = 0, first = -1;
-#pragma unroll 1
-                for (int ch = 0; ch < 8; ch += 2) {
-                    tmem_ld_wait(va);
-                    tmem_ld_x32(taddr + (uint32_t)((ch + 1) * 32), vb);
-                    {
-                        const uint32_t mask = le_mask32(va, thr);
-                        sMask[ch * 256 + et] = mask;
-                        if (mask && first < 0) first = ch * 32 + __ffs(mask) - 1;
-                        cnt += __popc(mask);
-                    }
-                    tmem_ld_wait(vb);                   // every load of chunks <= ch + 1 has landed
-                    if (ch == 2 || ch == 6) {
-                        tc_fence_before();
-                        mbar_arrive(&tmem_empty[eg * 2 + (ch >> 2)]);     // half drained: the MMA two steps ahead may overwrite it
-                    }
-                    if (ch + 2 < 8) tmem_ld_x32(taddr + (uint32_t)((ch + 2) * 32), va);
-                    {
-                        const uint32_t mask = le_mask32(vb, thr);
-                        sMask[(ch + 1) * 256 + et] = mask;
-                        if (mask && first < 0) first = (ch + 1) * 32 + __ffs(mask) - 1;
-                        cnt += __popc(mask);
-                    }
-                }
-                int code = first < 0 ? 0 : first;
-                if (cnt > 1) {
-                    // several candidates: the reference's own arithmetic decides (pq.py:79-80), first minimum wins
+                // rigorous candidate margin (see file header): operand split error + fp32 accumulation / reference rounding
+                const float margin = 1.2e-5f * xn * cm_j + 1e-5f * (xn + cm_j) * (xn + cm_j);
+                // ONE pass over the scores.  Two 32-column register buffers: while one chunk is folded the next one's
+                // TMEM load is in flight (tcgen05.wait::ld waits for ALL outstanding loads, so exactly one is
+                // outstanding at every wait).  Each accumulator half goes back to the MMA as soon as its last chunk
+                // is in registers.
+                float va[32], vb[32], A[16], B[16];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) B[i] = INFINITY;
+                tmem_ld_x32(taddr, va);
+                tmem_ld_wait(va); tmem_ld_x32(taddr + 32u, vb); fold_chunk<0>(va, A, B);
+                tmem_ld_wait(vb); tmem_ld_x32(taddr + 64u, va); fold_chunk<1>(vb, A, B);
+                tmem_ld_wait(va); tmem_ld_x32(taddr + 96u, vb); fold_chunk<2>(va, A, B);
+                tmem_ld_wait(vb);
+                tc_fence_before();
+                mbar_arrive(&tmem_empty[eg * 2]);              // columns 0..127 are in registers
+                mbar_wait(&tmem_full[eg * 2 + 1], phase);
+                phase ^= 1;
+                tc_fence_after();
+                tmem_ld_x32(taddr + 128u, va); fold_chunk<3>(vb, A, B);
+                tmem_ld_wait(va); tmem_ld_x32(taddr + 160u, vb); fold_chunk<4>(va, A, B);
+                tmem_ld_wait(vb); tmem_ld_x32(taddr + 192u, va); fold_chunk<5>(vb, A, B);
+                tmem_ld_wait(va); tmem_ld_x32(taddr + 224u, vb); fold_chunk<6>(va, A, B);
+                tmem_ld_wait(vb);
+                tc_fence_before();
+                mbar_arrive(&tmem_empty[eg * 2 + 1]);          // columns 128..255 are in registers
+                fold_chunk<7>(vb, A, B);
+                const float thr = min16(B) + margin;
+                const uint32_t mA = le_mask16(A, thr), mB = le_mask16(B, thr);
+                int code = 0;
+                if (__popc(mA) == 1 && __popc(mB) == 1) {
+                    code = (__ffs(mA) - 1) * 16 + __ffs(mB) - 1;
+                } else if (mA && mB) {
+                    // several candidates (a superset: the cross product of the two families): the reference's own
+                    // arithmetic decides (pq.py:79-80), first minimum wins
                     float best = INFINITY;
-                    for (int ch = 0; ch < 8; ++ch) {
-                        uint32_t mask = sMask[ch * 256 + et];
-                        while (mask) {
-                            const int c = ch * 32 + __ffs(mask) - 1;
-                            mask &= mask - 1;
+                    for (uint32_t ra = mA; ra; ra &= ra - 1) {
+                        const int c0 = (__ffs(ra) - 1) * 16;
+                        for (uint32_t rb = mB; rb; rb &= rb - 1) {
+                            const int c = c0 + __ffs(rb) - 1;
                             if (c < K) {
                                 const int cs = ((c >> 2) & 1) << 4;
                                 float4 a = *reinterpret_cast<const float4*>(sBh + c * 32 + (0 ^ cs));
