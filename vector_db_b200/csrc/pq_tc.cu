@@ -1,23 +1,33 @@
 // PQ encode on the tensor cores (a11): codes[i][j] = argmin_c sqrt(sum((C_j[c]-x_ij)^2)), first min wins
 // (src/vector_db/inference/pq.py:77-89), for dsub = 8 and K <= 256.
 //
-// dsub = 8 is exactly one tf32 UMMA K step, so per (128-row tile, sub-space j) the whole 128 x 256
-// score matrix  s(c) = |c|^2 - 2 x.c  is FOUR tcgen05.mma.kind::tf32 instructions.  The tensor core keeps
-// 10 mantissa bits of each operand, so both operands are split into tf32-exact parts (3xTF32 style):
-//   x = hi(x) + lo(x)        -- a helper warp rewrites the landed TMA tile in place and writes lo(x) beside it
-//   -2c = hi(-2c) + lo(-2c)  -- prepared once per call
-// and the score is hi(x).hi(-2c) + hi(x).lo(-2c) + lo(x).hi(-2c) + ones.split3(|c|^2): every operand the MMA
-// sees is exactly representable, the dropped term and the re-rounding of the lo parts are ~2^-20 |x||c|.
-// The accumulator is the score; the epilogue (one thread per row) takes its minimum, then collects
-// every centroid whose score is within a RIGOROUS margin of it (1.2e-5 |x| max|c| for the split, plus
-// 1e-5 (|x|+max|c|)^2 for the fp32 accumulation and the reference's own fp32 rounding); a single candidate
-// is the answer, several candidates are resolved with the reference's exact arithmetic (numpy's pairwise-sum
-// order, sqrt, first index wins) -- so codes stay bit-exact although the heavy lifting is tf32.  With a
-// single-pass tf32 product the margin had to be 0.0081 |x| max|c| and a fifth of all rows took the slow path.
+// Per (128-row tile, sub-space j) the whole 128 x 256 score matrix  s(c) = |c|^2 - 2 x.c  is TWO
+// tcgen05.mma.kind::f16 instructions (bf16 operands, K = 16 each, fp32 accumulation in TMEM).  bf16 keeps 8
+// significant bits, so both operands are split into bf16-exact pieces:
+//   x  = x1 + x2 + (rest <= 2^-18 |x|)        -- two helper warps convert the landed fp32 TMA tile
+//   -2c = c1 + c2 + (rest <= 2^-18 |2c|)      -- prepared once per call
+//   A0 = [x1 | x1]   B0 = [c1 | c2]           -> x1.c1 + x1.c2
+//   A1 = [x2 | 1 1 1 0 0 0 0 0]   B1 = [c1 | n1 n2 n3 0 0 0 0 0]   -> x2.c1 + |c|^2   (n = 3-way bf16 split of |c|^2)
+// Every product the MMA forms is exact in fp32; the dropped terms x1.c3 + x2.c2 + x2.c3 + x3.c are bounded by
+// 3.01 * 2^-18 |x| |2c| = 2.3e-5 |x| |c| (Cauchy-Schwarz on the piece norms).  (An earlier version used four
+// kind::tf32 instructions on a hi/lo split: twice the tensor time and twice the shared-memory operand traffic --
+// K = 8 tf32 MMAs read 128 B of operands per clock, which starved the epilogue's own shared-memory reads.)
 //
-// Tried and measured slower (kept out): parking each lane's arg-min chunk in shared memory to skip the second
-// TMEM pass (the predicated 128-bit stores cost the shared-memory bandwidth of the whole score tile), and a
-// 16-warp epilogue with the columns of a row split over two warps (two pair barriers per step ate the gain).
+// The accumulator is the score.  The epilogue (one thread per row) makes ONE pass over the 256 scores and folds
+// them into 16 block minima A[a] (centroids 16a..16a+15) and 16 residue minima B[b] (centroids = b mod 16), one
+// FMNMX3 per score.  Two different centroids differ in a or in b, so "exactly one A and exactly one B within the
+// margin of the row minimum" proves that exactly one centroid is within the margin and names it (16a + b); the
+// margin test therefore runs over 32 minima, not 256 scores, and there is no second pass over TMEM.  The margin is
+// RIGOROUS (5.2e-5 |x| max|c| for the split of both compared scores, plus 1e-5 (|x|+max|c|)^2 for the fp32
+// accumulation and the reference's own fp32 rounding); rows with several candidates (the cross product of the
+// two families, a superset) are resolved with the reference's exact arithmetic (numpy's pairwise-sum order,
+// sqrt, first index wins) from the fp32 row still in shared memory and the fp32 codebook -- so codes stay
+// bit-exact although the heavy lifting is bf16.
+//
+// Tried and measured slower (kept out): a two-pass epilogue (row minimum, then a 256-bit candidate mask:
+// 2.5 instructions per score on the half-rate ALU pipe, 5.2 ms per 2M x 384 against 3.3 ms for the fold);
+// parking each lane's arg-min chunk in shared memory; a 16-warp epilogue with the columns of a row split over
+// two warps (two pair barriers per step ate the gain).
 //
 // Roofline: HBM, algorithmic bytes per vector = 4 D + m (rows read once, codes written once).
 #include <cuda.h>
@@ -32,63 +42,71 @@ namespace vdb {
 
 using namespace sm100;
 
-constexpr int kEtThreads = 384;            // warp 0 TMA, 1 MMA, 2 TMEM alloc, 3 spare, 4-7 / 8-11 epilogue groups
+constexpr int kEtThreads = 384;            // warp 0 TMA, 1 MMA (+ TMEM alloc), 2-3 operand split, 4-7 / 8-11 epilogue groups
 constexpr int kEtRows = 128;               // rows per tile (UMMA M)
 constexpr int kEtK = 256;                  // centroids per sub-space (UMMA N)
-constexpr int kEtABytes = kEtRows * 32;    // 4 KB: 128 rows x 8 fp32
-constexpr int kEtBBytes = kEtK * 32;       // 8 KB: 256 centroids x 8 fp32
-constexpr int kEtStageBytes = 2 * kEtABytes + 3 * kEtBBytes;   // x | x_lo | hi(-2C) | lo(-2C) | norm split  (32 KB)
+constexpr int kEtXBytes = kEtRows * 32;    // 4 KB: 128 rows x 8 fp32 (TMA landing tile, not swizzled)
+constexpr int kEtABytes = kEtRows * 32;    // 4 KB: 128 rows x 16 bf16 (32-byte swizzle)
+constexpr int kEtBBytes = kEtK * 32;       // 8 KB: 256 centroids x 16 bf16 (32-byte swizzle)
+constexpr int kEtStageBytes = kEtXBytes + 2 * kEtABytes + 2 * kEtBBytes;   // x | A0 | A1 | B0 | B1  (28 KB)
 constexpr int kEtMaxStages = 8;
 
 struct EtSmem {
-    int stage_off, ones_off, codes_off, bar_off, total;
+    int stage_off, cmax_off, codes_off, bar_off, total;
 };
 __host__ __device__ inline EtSmem et_layout(int stages, int m) {
     EtSmem L;
     L.stage_off = 0;
-    L.ones_off = stages * kEtStageBytes;                       // 32 KB stages keep 1024-byte alignment
-    L.codes_off = L.ones_off + kEtABytes;
+    L.cmax_off = stages * kEtStageBytes;                       // 28 KB stages keep 1024-byte alignment
+    L.codes_off = L.cmax_off + ((m * 4 + 15) & ~15);
     L.bar_off = (L.codes_off + kEtRows * m + 15) & ~15;        // code staging [128 rows][m]
-    L.total = L.bar_off + (3 * kEtMaxStages + 8) * 8 + 16;
+    L.total = L.bar_off + (3 * kEtMaxStages + 4) * 8 + 16;
     return L;
 }
 
-// tf32 keeps 10 explicit mantissa bits: the tensor core ignores the low 13 bits of an fp32 operand
-__device__ __forceinline__ float tf32_hi(float v) { return __uint_as_float(__float_as_uint(v) & 0xFFFFE000u); }
+// two fp32 -> packed bf16x2 (round to nearest even); `lo` lands in the low half = the lower address
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+    uint32_t r;
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+    return r;
+}
+__device__ __forceinline__ float bf16_lo(uint32_t p) { return __uint_as_float(p << 16); }
+__device__ __forceinline__ float bf16_hi(uint32_t p) { return __uint_as_float(p & 0xFFFF0000u); }
+__device__ __forceinline__ float bf16_round(float v) { return bf16_lo(pack_bf16x2(v, 0.f)); }
 
-// Operand tensor [m][3][256][8]: part 0 = hi(-2C), part 1 = lo(-2C) = -2C - hi (exact), part 2 = three-way
-// tf32 split of |c|^2 in columns 0..2.  Padded to 256 centroids per sub-space (padding can never win).
-__global__ void pq_tc_operands_kernel(const float* __restrict__ cb, int m, int K, float* __restrict__ ops,
+// Operand tensor [m][2][256] rows of 16 bf16: part 0 = [c1 | c2], part 1 = [c1 | n1 n2 n3 0 0 0 0 0] with
+// -2c = c1 + c2 + rest and |c|^2 = n1 + n2 + n3 + rest.  Padded to 256 centroids per sub-space (padding can never win).
+__global__ void pq_tc_operands_kernel(const float* __restrict__ cb, int m, int K, uint32_t* __restrict__ ops,
                                       float* __restrict__ cmax) {
     const int j = blockIdx.x;
     __shared__ float red[256];
     float mx = 0.f;
     for (int c = threadIdx.x; c < 256; c += blockDim.x) {
-        float* oh = ops + (((size_t)j * 3 + 0) * 256 + c) * 8;
-        float* ol = ops + (((size_t)j * 3 + 1) * 256 + c) * 8;
-        float* on = ops + (((size_t)j * 3 + 2) * 256 + c) * 8;
+        uint32_t* o0 = ops + (((size_t)j * 2 + 0) * 256 + c) * 8;      // 8 words = 16 bf16
+        uint32_t* o1 = ops + (((size_t)j * 2 + 1) * 256 + c) * 8;
         float s = 0.f;
+        uint32_t p1[4] = {0u, 0u, 0u, 0u}, p2[4] = {0u, 0u, 0u, 0u};
         if (c < K) {
             const float* src = cb + ((size_t)j * K + c) * 8;
 #pragma unroll
-            for (int t = 0; t < 8; ++t) {
-                const float v = src[t], w = -2.f * v, h = tf32_hi(w);
-                oh[t] = h; ol[t] = w - h;
-                s = fmaf(v, v, s);
+            for (int t = 0; t < 4; ++t) {
+                const float v0 = src[2 * t], v1 = src[2 * t + 1], w0 = -2.f * v0, w1 = -2.f * v1;
+                p1[t] = pack_bf16x2(w0, w1);
+                p2[t] = pack_bf16x2(w0 - bf16_lo(p1[t]), w1 - bf16_hi(p1[t]));
+                s = fmaf(v0, v0, s);
+                s = fmaf(v1, v1, s);
             }
             mx = fmaxf(mx, s);
         } else {
-#pragma unroll
-            for (int t = 0; t < 8; ++t) { oh[t] = 0.f; ol[t] = 0.f; }
             s = 3.0e38f;
         }
-        const float h = tf32_hi(s);
-        const float r1 = s - h;
-        const float mid = tf32_hi(r1);
-        const float lo = r1 - mid;
-        on[0] = h; on[1] = mid; on[2] = lo;
+        const float n1 = bf16_round(s), r1 = s - n1, n2 = bf16_round(r1), n3 = bf16_round(r1 - n2);
 #pragma unroll
-        for (int t = 3; t < 8; ++t) on[t] = 0.f;
+        for (int t = 0; t < 4; ++t) { o0[t] = p1[t]; o0[4 + t] = p2[t]; o1[t] = p1[t]; }
+        o1[4] = pack_bf16x2(n1, n2);
+        o1[5] = pack_bf16x2(n3, 0.f);
+        o1[6] = 0u;
+        o1[7] = 0u;
     }
     red[threadIdx.x] = mx;
     __syncthreads();
@@ -141,47 +159,52 @@ __device__ __forceinline__ uint32_t le_mask16(const float (&v)[16], float thr) {
     return (mk[0] | mk[1]) | (mk[2] | mk[3]);
 }
 
+__device__ __forceinline__ float4 lds128(uint32_t saddr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(saddr));
+    return v;
+}
+
 __global__ void __launch_bounds__(kEtThreads, 1)
 pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_b,
-                    const float* __restrict__ x, int64_t N, int D, int m,
-                    int K, const float* __restrict__ cb, const float* __restrict__ cmax, int stages, int64_t tiles,
-                    uint8_t* __restrict__ codes) {
+                    int64_t N, int m, int K, const float* __restrict__ cb, const float* __restrict__ cmax, int stages,
+                    int64_t tiles, uint8_t* __restrict__ codes) {
     extern __shared__ __align__(1024) unsigned char smem[];
     if ((smem_u32(smem) & 1023u) != 0) __trap();
     const EtSmem L = et_layout(stages, m);
     unsigned char* sStage = smem + L.stage_off;
-    float* sOnes = reinterpret_cast<float*>(smem + L.ones_off);
+    float* sCmax = reinterpret_cast<float*>(smem + L.cmax_off);
     uint8_t* sCodes = smem + L.codes_off;
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L.bar_off);
-    uint64_t* full = bars;                          // [stages]
-    uint64_t* empty = bars + kEtMaxStages;          // [stages]
-    uint64_t* xlo_full = bars + 2 * kEtMaxStages;   // [stages]: x_lo written by the split warp
-    uint64_t* tmem_full = bars + 3 * kEtMaxStages;  // [2 accumulator stages][2 column halves]
-    uint64_t* tmem_empty = tmem_full + 4;           // [2][2]
-    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 4);
+    uint64_t* full = bars;                          // [stages]: TMA landed (x fp32, B0, B1)
+    uint64_t* empty = bars + kEtMaxStages;          // [stages]: MMA done with the operands + epilogue done with x
+    uint64_t* a_full = bars + 2 * kEtMaxStages;     // [stages]: A0 / A1 written by the split warps
+    uint64_t* tmem_full = bars + 3 * kEtMaxStages;  // [2 accumulator stages]
+    uint64_t* tmem_empty = tmem_full + 2;           // [2]
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 2);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
-    // constant A tile of the norm MMA: every row is (1,1,1,0,0,0,0,0); with the 32-byte swizzle the two
-    // 16-byte halves of row r trade places when bit 2 of r is set
-    if (threadIdx.x < kEtRows) {
-        const int r = threadIdx.x;
-        const int first = ((r >> 2) & 1) ? 4 : 0;
-#pragma unroll
-        for (int t = 0; t < 8; ++t) sOnes[r * 8 + t] = (t >= first && t < first + 3) ? 1.f : 0.f;
+    // constant half of every A1 row: (1,1,1,0,0,0,0,0) bf16 against the norm pieces; with the 32-byte swizzle the
+    // two 16-byte halves of row r trade places when bit 2 of r is set
+    for (int i = threadIdx.x; i < stages * kEtRows; i += kEtThreads) {
+        const int sidx = i / kEtRows, r = i % kEtRows;
+        unsigned char* a1 = sStage + (size_t)sidx * kEtStageBytes + kEtXBytes + kEtABytes;
+        *reinterpret_cast<uint4*>(a1 + r * 32 + (16 ^ (((r >> 2) & 1) << 4))) = make_uint4(0x3F803F80u, 0x00003F80u, 0u, 0u);
     }
+    for (int i = threadIdx.x; i < m; i += kEtThreads) sCmax[i] = cmax[i];
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&map_x);
         tma_prefetch_desc(&map_b);
     }
     if (warp == 1 && lane == 0) {
         for (int i = 0; i < stages; ++i) {
-            mbar_init(&full[i], 1); mbar_init(&empty[i], 1 + 4); mbar_init(&xlo_full[i], 1);   // empty: MMA commit + 4 epilogue warps
+            mbar_init(&full[i], 1); mbar_init(&empty[i], 1 + 4); mbar_init(&a_full[i], 2);   // empty: MMA commit + 4 epilogue warps
         }
-        for (int i = 0; i < 4; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 128); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 128); }
         fence_barrier_init();
     }
     if (warp == 2) tmem_alloc(tmem_ptr, 512);
-    fence_proxy_async();                 // the generic-proxy writes of sOnes must be visible to the MMA (async proxy)
+    fence_proxy_async();                 // the generic-proxy writes of the A1 constants must be visible to the MMA (async proxy)
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -195,12 +218,10 @@ pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                 for (int j = 0; j < m; ++j) {
                     mbar_wait(&empty[st], ph ^ 1);
                     unsigned char* base = sStage + (size_t)st * kEtStageBytes;
-                    mbar_expect_tx(&full[st], (uint32_t)(kEtABytes + 3 * kEtBBytes));
+                    mbar_expect_tx(&full[st], (uint32_t)(kEtXBytes + 2 * kEtBBytes));
                     tma_load_2d(base, &map_x, &full[st], j * 8, (int)(tile * kEtRows), kEvictFirst);
-#pragma unroll
-                    for (int part = 0; part < 3; ++part)
-                        tma_load_2d(base + 2 * kEtABytes + part * kEtBBytes, &map_b, &full[st], 0, (j * 3 + part) * 256,
-                                    kEvictLast);
+                    tma_load_2d(base + kEtXBytes + 2 * kEtABytes, &map_b, &full[st], 0, (j * 2) * 256, kEvictLast);
+                    tma_load_2d(base + kEtXBytes + 2 * kEtABytes + kEtBBytes, &map_b, &full[st], 0, (j * 2 + 1) * 256, kEvictLast);
                     if (++st == stages) { st = 0; ph ^= 1; }
                 }
             }
@@ -208,33 +229,20 @@ pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     } else if (warp == 1) {
         // ================= MMA issuer =================
         if (lane == 0) {
-            // Each 256-column accumulator is produced and released in two 128-column halves: the epilogue frees half 0
-            // while it is still masking half 1, so the next-but-one step's MMAs start (and finish) under epilogue work
-            // instead of after it -- with whole-stage hand-over the epilogue warps waited ~20 % of the time for tmem_full.
-            const uint32_t idesc = make_idesc_tf32(kEtRows, kEtK / 2);
-            const uint64_t d_ones = make_desc_k_sw32(smem_u32(sOnes));
+            const uint32_t idesc = make_idesc_bf16(kEtRows, kEtK);
             int st = 0, ph = 0, as = 0, aph = 0;
             for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
                 for (int j = 0; j < m; ++j) {
                     mbar_wait(&full[st], ph);
-                    mbar_wait(&xlo_full[st], ph);
+                    mbar_wait(&a_full[st], ph);
+                    mbar_wait(&tmem_empty[as], aph ^ 1);
+                    tc_fence_after();
                     const uint32_t base = smem_u32(sStage + (size_t)st * kEtStageBytes);
-                    const uint64_t d_x = make_desc_k_sw32(base), d_xlo = make_desc_k_sw32(base + kEtABytes);
-#pragma unroll
-                    for (int h = 0; h < 2; ++h) {
-                        mbar_wait(&tmem_empty[as * 2 + h], aph ^ 1);
-                        tc_fence_after();
-                        const uint32_t d_tmem = tmem_base + (uint32_t)(as * kEtK + h * (kEtK / 2));
-                        const uint32_t boff = (uint32_t)(h * (kEtBBytes / 2));       // centroids 128 h .. 128 h + 127
-                        const uint64_t d_hi = make_desc_k_sw32(base + 2 * kEtABytes + boff);
-                        const uint64_t d_lo = make_desc_k_sw32(base + 2 * kEtABytes + kEtBBytes + boff);
-                        // x.(-2c) to ~2^-20: hi(x).hi + hi(x).lo + lo(x).hi  (every operand is tf32-exact)
-                        umma_tf32(d_tmem, d_x, d_hi, idesc, 0u);
-                        umma_tf32(d_tmem, d_x, d_lo, idesc, 1u);
-                        umma_tf32(d_tmem, d_xlo, d_hi, idesc, 1u);
-                        umma_tf32(d_tmem, d_ones, make_desc_k_sw32(base + 2 * kEtABytes + 2 * kEtBBytes + boff), idesc, 1u);
-                        umma_commit(&tmem_full[as * 2 + h]);
-                    }
+                    const uint32_t a0 = base + kEtXBytes, b0 = a0 + 2 * kEtABytes;
+                    const uint32_t d_tmem = tmem_base + (uint32_t)(as * kEtK);
+                    umma_bf16(d_tmem, make_desc_k_sw32(a0), make_desc_k_sw32(b0), idesc, 0u);                          // x1.c1 + x1.c2
+                    umma_bf16(d_tmem, make_desc_k_sw32(a0 + kEtABytes), make_desc_k_sw32(b0 + kEtBBytes), idesc, 1u);  // x2.c1 + |c|^2
+                    umma_commit(&tmem_full[as]);
                     umma_commit(&empty[st]);
                     if (++st == stages) { st = 0; ph ^= 1; }
                     as ^= 1;
@@ -242,91 +250,80 @@ pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                 }
             }
         }
-    } else if (warp == 3) {
-        // ================= operand split: x -> hi(x) in place, x_lo = x - hi(x) beside it; elementwise on the landed
-        // tile, so the swizzled layout does not matter =================
+    } else if (warp < 4) {
+        // ================= operand split (warps 2, 3; one row per lane, 64 rows per pass): the landed fp32 row ->
+        // x1 = bf16(x), x2 = bf16(x - x1); A0 row = [x1 | x1], A1 row = [x2 | ones] =================
         int st = 0, ph = 0;
         for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
             for (int j = 0; j < m; ++j) {
                 mbar_wait(&full[st], ph);
-                float4* src_w = reinterpret_cast<float4*>(sStage + (size_t)st * kEtStageBytes);
-                const float4* src = src_w;
-                float4* dst = reinterpret_cast<float4*>(sStage + (size_t)st * kEtStageBytes + kEtABytes);
+                unsigned char* base = sStage + (size_t)st * kEtStageBytes;
 #pragma unroll
-                for (int i = 0; i < kEtABytes / 16 / 32; ++i) {
-                    const float4 v = src[i * 32 + lane];
-                    const float4 h = make_float4(tf32_hi(v.x), tf32_hi(v.y), tf32_hi(v.z), tf32_hi(v.w));
-                    src_w[i * 32 + lane] = h;           // operands are tf32-exact: no dependence on the MMA's input rounding mode
-                    dst[i * 32 + lane] = make_float4(v.x - h.x, v.y - h.y, v.z - h.z, v.w - h.w);
+                for (int it = 0; it < 2; ++it) {
+                    const int r = it * 64 + (warp - 2) * 32 + lane;
+                    const float4 a = *reinterpret_cast<const float4*>(base + r * 32);
+                    const float4 b = *reinterpret_cast<const float4*>(base + r * 32 + 16);
+                    uint4 p, q;
+                    p.x = pack_bf16x2(a.x, a.y); p.y = pack_bf16x2(a.z, a.w); p.z = pack_bf16x2(b.x, b.y); p.w = pack_bf16x2(b.z, b.w);
+                    q.x = pack_bf16x2(a.x - bf16_lo(p.x), a.y - bf16_hi(p.x));
+                    q.y = pack_bf16x2(a.z - bf16_lo(p.y), a.w - bf16_hi(p.y));
+                    q.z = pack_bf16x2(b.x - bf16_lo(p.z), b.y - bf16_hi(p.z));
+                    q.w = pack_bf16x2(b.z - bf16_lo(p.w), b.w - bf16_hi(p.w));
+                    unsigned char* a0 = base + kEtXBytes + r * 32;
+                    *reinterpret_cast<uint4*>(a0) = p;
+                    *reinterpret_cast<uint4*>(a0 + 16) = p;
+                    *reinterpret_cast<uint4*>(a0 + kEtABytes + (((r >> 2) & 1) << 4)) = q;
                 }
                 fence_proxy_async();                   // generic-proxy writes -> visible to the MMA's async-proxy reads
                 __syncwarp();
-                if (lane == 0) mbar_arrive(&xlo_full[st]);
+                if (lane == 0) mbar_arrive(&a_full[st]);
                 if (++st == stages) { st = 0; ph ^= 1; }
             }
         }
-    } else if (warp >= 4) {
-        // ================= epilogue: one thread per row; group eg owns accumulator stage eg (every other step) =================
-        // The step's operand stage stays resident until the epilogue releases it, so the exact fp32 row
-        // slice and the centroids (-2c, exact) are read back from shared memory, never from global.
+    } else {
+        // ================= epilogue: one thread per row; group eg owns accumulator stage eg = every other step =================
+        // The step's operand stage stays resident until the epilogue releases it, so the exact fp32 row slice is
+        // read back from shared memory, never from global.
         const int eg = (warp - 4) >> 2;
         const int ew = warp & 3;
         const int rt = ew * 32 + lane;                 // row within the tile == TMEM lane
         const int et = threadIdx.x - 128;              // 0..255
         const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(eg * kEtK);
-        const int swz = ((rt >> 2) & 1) << 4;          // 32-byte swizzle: 16-byte halves of row r swap when bit 2 of r is set
-        int64_t step = 0;
-        int st = 0, phase = 0;
-        for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
-            for (int j = 0; j < m; ++j, ++step, st = (st + 1 == stages ? 0 : st + 1)) {
-                if ((int)(step & 1) != eg) continue;
-                mbar_wait(&tmem_full[eg * 2], phase);  // columns 0..127 done => the step's operands were in shared memory too
+        int64_t step0 = 0;                             // global step index of (tile, j = 0)
+        int phase = 0;
+        for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x, step0 += m) {
+            int st = (int)((step0 + ((eg - step0) & 1)) % stages);
+            for (int j = (int)((eg - step0) & 1); j < m; j += 2) {
+                const uint32_t sx = smem_u32(sStage + (size_t)st * kEtStageBytes) + (uint32_t)(rt * 32);
+                mbar_wait(&tmem_full[eg], phase);      // MMAs done => the step's operands were in shared memory too
+                phase ^= 1;
                 tc_fence_after();
-                const unsigned char* sA = sStage + (size_t)st * kEtStageBytes;
-                const unsigned char* sBh = sA + 2 * kEtABytes;      // hi(-2c)
-                const unsigned char* sBl = sBh + kEtBBytes;         // lo(-2c)
-                float xs[8];
-                {
-                    float4 a = *reinterpret_cast<const float4*>(sA + rt * 32 + (0 ^ swz));
-                    float4 b = *reinterpret_cast<const float4*>(sA + rt * 32 + (16 ^ swz));
-                    const float4 al = *reinterpret_cast<const float4*>(sA + kEtABytes + rt * 32 + (0 ^ swz));
-                    const float4 bl = *reinterpret_cast<const float4*>(sA + kEtABytes + rt * 32 + (16 ^ swz));
-                    a.x += al.x; a.y += al.y; a.z += al.z; a.w += al.w;      // hi + lo = x exactly
-                    b.x += bl.x; b.y += bl.y; b.z += bl.z; b.w += bl.w;
-                    xs[0] = a.x; xs[1] = a.y; xs[2] = a.z; xs[3] = a.w; xs[4] = b.x; xs[5] = b.y; xs[6] = b.z; xs[7] = b.w;
-                }
-                float xx = 0.f;
-#pragma unroll
-                for (int t = 0; t < 8; ++t) xx = fmaf(xs[t], xs[t], xx);
-                const float xn = sqrtf(xx) * 1.0000005f, cm_j = __ldg(cmax + j);
-                // rigorous candidate margin (see file header): operand split error + fp32 accumulation / reference rounding
-                const float margin = 1.2e-5f * xn * cm_j + 1e-5f * (xn + cm_j) * (xn + cm_j);
                 // ONE pass over the scores.  Two 32-column register buffers: while one chunk is folded the next one's
                 // TMEM load is in flight (tcgen05.wait::ld waits for ALL outstanding loads, so exactly one is
-                // outstanding at every wait).  Each accumulator half goes back to the MMA as soon as its last chunk
-                // is in registers.
+                // outstanding at every wait).
                 float va[32], vb[32], A[16], B[16];
 #pragma unroll
                 for (int i = 0; i < 16; ++i) B[i] = INFINITY;
                 tmem_ld_x32(taddr, va);
+                const float4 xa = lds128(sx), xb = lds128(sx + 16);     // issued here, consumed after the fold
                 tmem_ld_wait(va); tmem_ld_x32(taddr + 32u, vb); fold_chunk<0>(va, A, B);
                 tmem_ld_wait(vb); tmem_ld_x32(taddr + 64u, va); fold_chunk<1>(vb, A, B);
                 tmem_ld_wait(va); tmem_ld_x32(taddr + 96u, vb); fold_chunk<2>(va, A, B);
-                tmem_ld_wait(vb);
-                tc_fence_before();
-                mbar_arrive(&tmem_empty[eg * 2]);              // columns 0..127 are in registers
-                mbar_wait(&tmem_full[eg * 2 + 1], phase);
-                phase ^= 1;
-                tc_fence_after();
-                tmem_ld_x32(taddr + 128u, va); fold_chunk<3>(vb, A, B);
+                tmem_ld_wait(vb); tmem_ld_x32(taddr + 128u, va); fold_chunk<3>(vb, A, B);
                 tmem_ld_wait(va); tmem_ld_x32(taddr + 160u, vb); fold_chunk<4>(va, A, B);
                 tmem_ld_wait(vb); tmem_ld_x32(taddr + 192u, va); fold_chunk<5>(vb, A, B);
                 tmem_ld_wait(va); tmem_ld_x32(taddr + 224u, vb); fold_chunk<6>(va, A, B);
                 tmem_ld_wait(vb);
                 tc_fence_before();
-                mbar_arrive(&tmem_empty[eg * 2 + 1]);          // columns 128..255 are in registers
+                mbar_arrive(&tmem_empty[eg]);          // all 256 columns are in registers: the MMA two steps ahead may start
                 fold_chunk<7>(vb, A, B);
-                const float thr = min16(B) + margin;
+                const float xs[8] = {xa.x, xa.y, xa.z, xa.w, xb.x, xb.y, xb.z, xb.w};
+                float xx = 0.f;
+#pragma unroll
+                for (int t = 0; t < 8; ++t) xx = fmaf(xs[t], xs[t], xx);
+                const float xn = sqrtf(xx) * 1.0000005f, cm_j = sCmax[j];
+                // rigorous candidate margin (see file header): operand split error + fp32 accumulation / reference rounding
+                const float thr = min16(B) + 5.2e-5f * xn * cm_j + 1e-5f * (xn + cm_j) * (xn + cm_j);
                 const uint32_t mA = le_mask16(A, thr), mB = le_mask16(B, thr);
                 int code = 0;
                 if (__popc(mA) == 1 && __popc(mB) == 1) {
@@ -340,16 +337,10 @@ pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                         for (uint32_t rb = mB; rb; rb &= rb - 1) {
                             const int c = c0 + __ffs(rb) - 1;
                             if (c < K) {
-                                const int cs = ((c >> 2) & 1) << 4;
-                                float4 a = *reinterpret_cast<const float4*>(sBh + c * 32 + (0 ^ cs));
-                                float4 b = *reinterpret_cast<const float4*>(sBh + c * 32 + (16 ^ cs));
-                                const float4 al = *reinterpret_cast<const float4*>(sBl + c * 32 + (0 ^ cs));
-                                const float4 bl = *reinterpret_cast<const float4*>(sBl + c * 32 + (16 ^ cs));
-                                // hi + lo = -2c exactly, so c = -0.5 * (hi + lo) exactly
-                                a.x += al.x; a.y += al.y; a.z += al.z; a.w += al.w;
-                                b.x += bl.x; b.y += bl.y; b.z += bl.z; b.w += bl.w;
-                                float d[8] = {-0.5f * a.x - xs[0], -0.5f * a.y - xs[1], -0.5f * a.z - xs[2], -0.5f * a.w - xs[3],
-                                              -0.5f * b.x - xs[4], -0.5f * b.y - xs[5], -0.5f * b.z - xs[6], -0.5f * b.w - xs[7]};
+                                const float4* cp = reinterpret_cast<const float4*>(cb + ((size_t)j * K + c) * 8);
+                                const float4 ca = __ldg(cp), cc = __ldg(cp + 1);
+                                float d[8] = {ca.x - xs[0], ca.y - xs[1], ca.z - xs[2], ca.w - xs[3],
+                                              cc.x - xs[4], cc.y - xs[5], cc.z - xs[6], cc.w - xs[7]};
                                 const float dist = sqrtf(np_sumsq<8>(d));
                                 if (dist < best) { best = dist; code = c; }
                             }
@@ -359,6 +350,8 @@ pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&empty[st]);    // this warp no longer reads the operand stage
                 sCodes[rt * m + j] = (uint8_t)code;
+                st += 2;
+                if (st >= stages) st -= stages;
             }
             // the tile's codes are one contiguous run of 128*m bytes in global memory
             named_bar_sync(1, 256);
@@ -407,15 +400,15 @@ int vdb_pq_encode_tc(const float* x, int64_t N, int D, int m, int K, const float
                 VDB_ERR_INVALID, "rows / codebooks / workspace must be 16 / 16 / 256-byte aligned");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     char* base = static_cast<char*>(ws);
-    float* opnd = reinterpret_cast<float*>(base);
+    uint32_t* opnd = reinterpret_cast<uint32_t*>(base);
     float* cmax = reinterpret_cast<float*>(base + 3 * et_ws_operand(m));
     pq_tc_operands_kernel<<<m, 256, 0, st>>>(codebooks, m, K, opnd, cmax);
     count_launch(1);
     CUtensorMap map_x, map_b;
     int rc = tma_map_2d(&map_x, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, x, (uint64_t)D, (uint64_t)N, (uint64_t)D * 4, 8, kEtRows,
-                        CU_TENSOR_MAP_SWIZZLE_32B);
+                        CU_TENSOR_MAP_SWIZZLE_NONE);
     if (rc) return rc;
-    rc = tma_map_2d(&map_b, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, opnd, 8, (uint64_t)m * 3 * 256, 32, 8, kEtK, CU_TENSOR_MAP_SWIZZLE_32B);
+    rc = tma_map_2d(&map_b, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, opnd, 16, (uint64_t)m * 2 * 256, 32, 16, kEtK, CU_TENSOR_MAP_SWIZZLE_32B);
     if (rc) return rc;
     int stages = kEtMaxStages;
     const int smem_max = max_smem_optin();
@@ -427,8 +420,7 @@ int vdb_pq_encode_tc(const float* x, int64_t N, int D, int m, int K, const float
     VDB_CUDA(cudaFuncSetAttribute(pq_encode_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     {
         ProfScope prof(kProfPqEncode, st);
-        pq_encode_tc_kernel<<<grid, kEtThreads, smem, st>>>(map_x, map_b, x, N, D, m, K, codebooks, cmax, stages, tiles,
-                                                           codes);
+        pq_encode_tc_kernel<<<grid, kEtThreads, smem, st>>>(map_x, map_b, N, m, K, codebooks, cmax, stages, tiles, codes);
     }
     count_launch(1);
     VDB_CUDA(cudaGetLastError());
