@@ -24,10 +24,19 @@
 // sqrt, first index wins) from the fp32 row still in shared memory and the fp32 codebook -- so codes stay
 // bit-exact although the heavy lifting is bf16.
 //
-// Tried and measured slower (kept out): a two-pass epilogue (row minimum, then a 256-bit candidate mask:
-// 2.5 instructions per score on the half-rate ALU pipe, 5.2 ms per 2M x 384 against 3.3 ms for the fold);
-// parking each lane's arg-min chunk in shared memory; a 16-warp epilogue with the columns of a row split over
-// two warps (two pair barriers per step ate the gain).
+// Measured (2M x 384 rows, m = 48, B200): 2.90 ms = 690 M vectors/s; ncu: ALU pipe 66 %, tensor pipe 25 %, issue slots
+// 55 % -- the fold is one FMNMX3 per score on the half-rate ALU pipe (2 clocks per warp instruction), ~580 clocks of
+// the ~1020 a step takes; the rest is the dependent tail of a step (norm, margin, the FMA-pipe margin test) with two
+// epilogue warps per scheduler to hide it.  The kernel is sensitive to the operand ring: time = 1.6 ms + 7.7 ms /
+// stages for 2..6 stages (a stage is held from its TMA issue to the END of the step's epilogue).
+//
+// Tried and measured slower or equal (kept out): a two-pass epilogue (row minimum, then a 256-bit candidate mask:
+// 2.5 instructions per score, 5.2 ms); parking each lane's arg-min chunk in shared memory; a 16-warp epilogue with
+// the columns of a row split over two warps; four kind::tf32 MMAs on a hi/lo split (3.3 ms: twice the tensor time,
+// and K = 8 tf32 MMAs read 128 B of operands per clock, starving the epilogue's shared-memory reads); separate
+// row / operand rings with 128-byte row boxes and operand slots released at MMA completion (3.4 ms); the epilogue
+// groups preparing their own next-step operands instead of a split warp (3.6 ms: fence.proxy.async per thread and
+// step); ambiguous rows parked in shared memory and resolved once per tile (2.96 ms with 7 stages of 28 KB).
 //
 // Roofline: HBM, algorithmic bytes per vector = 4 D + m (rows read once, codes written once).
 #include <cuda.h>
@@ -42,13 +51,14 @@ namespace vdb {
 
 using namespace sm100;
 
-constexpr int kEtThreads = 384;            // warp 0 TMA, 1 MMA (+ TMEM alloc), 2-3 operand split, 4-7 / 8-11 epilogue groups
+constexpr int kEtThreads = 384;            // warp 0 TMA, 1-2 MMA issuers (2: TMEM alloc), 3 operand split, 4-7 / 8-11 epilogue groups
 constexpr int kEtRows = 128;               // rows per tile (UMMA M)
 constexpr int kEtK = 256;                  // centroids per sub-space (UMMA N)
 constexpr int kEtXBytes = kEtRows * 32;    // 4 KB: 128 rows x 8 fp32 (TMA landing tile, not swizzled)
 constexpr int kEtABytes = kEtRows * 32;    // 4 KB: 128 rows x 16 bf16 (32-byte swizzle)
 constexpr int kEtBBytes = kEtK * 32;       // 8 KB: 256 centroids x 16 bf16 (32-byte swizzle)
-constexpr int kEtStageBytes = kEtXBytes + 2 * kEtABytes + 2 * kEtBBytes;   // x | A0 | A1 | B0 | B1  (28 KB)
+constexpr int kEtCBytes = kEtK * 32;       // 8 KB: the sub-space's fp32 codebook (exact tie resolution reads it)
+constexpr int kEtStageBytes = kEtXBytes + 2 * kEtABytes + 2 * kEtBBytes + kEtCBytes;   // x | A0 | A1 | B0 | B1 | C  (36 KB)
 constexpr int kEtMaxStages = 8;
 
 struct EtSmem {
@@ -57,10 +67,10 @@ struct EtSmem {
 __host__ __device__ inline EtSmem et_layout(int stages, int m) {
     EtSmem L;
     L.stage_off = 0;
-    L.cmax_off = stages * kEtStageBytes;                       // 28 KB stages keep 1024-byte alignment
+    L.cmax_off = stages * kEtStageBytes;                       // 36 KB stages keep 1024-byte alignment
     L.codes_off = L.cmax_off + ((m * 4 + 15) & ~15);
     L.bar_off = (L.codes_off + kEtRows * m + 15) & ~15;        // code staging [128 rows][m]
-    L.total = L.bar_off + (3 * kEtMaxStages + 4) * 8 + 16;
+    L.total = L.bar_off + (3 * kEtMaxStages + 8) * 8 + 16;
     return L;
 }
 
@@ -159,6 +169,18 @@ __device__ __forceinline__ uint32_t le_mask16(const float (&v)[16], float thr) {
     return (mk[0] | mk[1]) | (mk[2] | mk[3]);
 }
 
+// sum over i of sat((v[i] - thr) * S) * (1 + 32 i), all on the FMA pipe (FFMA.SAT + FFMA per element, four chains)
+__device__ __forceinline__ float gt_accumulate16(const float (&v)[16], float S, float nts) {
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        float u;
+        asm("fma.rn.sat.f32 %0, %1, %2, %3;" : "=f"(u) : "f"(v[i]), "f"(S), "f"(nts));
+        acc[i & 3] = fmaf(u, (float)(1 + 32 * i), acc[i & 3]);
+    }
+    return (acc[0] + acc[1]) + (acc[2] + acc[3]);
+}
+
 __device__ __forceinline__ float4 lds128(uint32_t saddr) {
     float4 v;
     asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(saddr));
@@ -167,7 +189,7 @@ __device__ __forceinline__ float4 lds128(uint32_t saddr) {
 
 __global__ void __launch_bounds__(kEtThreads, 1)
 pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_b,
-                    int64_t N, int m, int K, const float* __restrict__ cb, const float* __restrict__ cmax, int stages,
+                    const __grid_constant__ CUtensorMap map_c, int64_t N, int m, int K, const float* __restrict__ cmax, int stages,
                     int64_t tiles, uint8_t* __restrict__ codes) {
     extern __shared__ __align__(1024) unsigned char smem[];
     if ((smem_u32(smem) & 1023u) != 0) __trap();
@@ -179,9 +201,9 @@ pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     uint64_t* full = bars;                          // [stages]: TMA landed (x fp32, B0, B1)
     uint64_t* empty = bars + kEtMaxStages;          // [stages]: MMA done with the operands + epilogue done with x
     uint64_t* a_full = bars + 2 * kEtMaxStages;     // [stages]: A0 / A1 written by the split warps
-    uint64_t* tmem_full = bars + 3 * kEtMaxStages;  // [2 accumulator stages]
-    uint64_t* tmem_empty = tmem_full + 2;           // [2]
-    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+    uint64_t* tmem_full = bars + 3 * kEtMaxStages;  // [2 accumulator stages][2 column halves]
+    uint64_t* tmem_empty = tmem_full + 4;           // [2][2]
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 4);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     // constant half of every A1 row: (1,1,1,0,0,0,0,0) bf16 against the norm pieces; with the 32-byte swizzle the
@@ -195,12 +217,13 @@ pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&map_x);
         tma_prefetch_desc(&map_b);
+        tma_prefetch_desc(&map_c);
     }
     if (warp == 1 && lane == 0) {
         for (int i = 0; i < stages; ++i) {
-            mbar_init(&full[i], 1); mbar_init(&empty[i], 1 + 4); mbar_init(&a_full[i], 2);   // empty: MMA commit + 4 epilogue warps
+            mbar_init(&full[i], 1); mbar_init(&empty[i], 1 + 4); mbar_init(&a_full[i], 1);   // empty: MMA commit + 4 epilogue warps
         }
-        for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 128); }
+        for (int i = 0; i < 4; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 128); }
         fence_barrier_init();
     }
     if (warp == 2) tmem_alloc(tmem_ptr, 512);
@@ -218,40 +241,56 @@ pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                 for (int j = 0; j < m; ++j) {
                     mbar_wait(&empty[st], ph ^ 1);
                     unsigned char* base = sStage + (size_t)st * kEtStageBytes;
-                    mbar_expect_tx(&full[st], (uint32_t)(kEtXBytes + 2 * kEtBBytes));
+                    mbar_expect_tx(&full[st], (uint32_t)(kEtXBytes + 2 * kEtBBytes + kEtCBytes));
                     tma_load_2d(base, &map_x, &full[st], j * 8, (int)(tile * kEtRows), kEvictFirst);
                     tma_load_2d(base + kEtXBytes + 2 * kEtABytes, &map_b, &full[st], 0, (j * 2) * 256, kEvictLast);
                     tma_load_2d(base + kEtXBytes + 2 * kEtABytes + kEtBBytes, &map_b, &full[st], 0, (j * 2 + 1) * 256, kEvictLast);
+                    tma_load_2d(base + kEtXBytes + 2 * kEtABytes + 2 * kEtBBytes, &map_c, &full[st], 0, j * K, kEvictLast);
                     if (++st == stages) { st = 0; ph ^= 1; }
                 }
             }
         }
-    } else if (warp == 1) {
-        // ================= MMA issuer =================
+    } else if (warp < 3) {
+        // ================= MMA issuers: warp 1 owns accumulator stage 0 (even steps), warp 2 stage 1 (odd steps).
+        // With ONE in-order issuer the MMAs of a step whose accumulator half was already free queued behind the
+        // other stage's wait for its epilogue group, and the two groups fell into lock step. =================
         if (lane == 0) {
-            const uint32_t idesc = make_idesc_bf16(kEtRows, kEtK);
-            int st = 0, ph = 0, as = 0, aph = 0;
-            for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
-                for (int j = 0; j < m; ++j) {
+            // Each 256-column accumulator is produced and released in two 128-column halves: the epilogue hands half 0
+            // back while it is still folding half 1, so the MMAs of the group's next step run under epilogue work and
+            // only the short second half sits in the release -> MMA -> fold dependency chain.
+            const int as = warp - 1;
+            const uint32_t idesc = make_idesc_bf16(kEtRows, kEtK / 2);
+            int64_t step0 = 0;
+            int aph = 0;
+            for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x, step0 += m) {
+                int64_t sidx = step0 + ((as - step0) & 1);
+                int st = (int)(sidx % stages);
+                int ph = (int)((sidx / stages) & 1);
+                for (int j = (int)((as - step0) & 1); j < m; j += 2) {
                     mbar_wait(&full[st], ph);
                     mbar_wait(&a_full[st], ph);
-                    mbar_wait(&tmem_empty[as], aph ^ 1);
-                    tc_fence_after();
                     const uint32_t base = smem_u32(sStage + (size_t)st * kEtStageBytes);
                     const uint32_t a0 = base + kEtXBytes, b0 = a0 + 2 * kEtABytes;
-                    const uint32_t d_tmem = tmem_base + (uint32_t)(as * kEtK);
-                    umma_bf16(d_tmem, make_desc_k_sw32(a0), make_desc_k_sw32(b0), idesc, 0u);                          // x1.c1 + x1.c2
-                    umma_bf16(d_tmem, make_desc_k_sw32(a0 + kEtABytes), make_desc_k_sw32(b0 + kEtBBytes), idesc, 1u);  // x2.c1 + |c|^2
-                    umma_commit(&tmem_full[as]);
+                    const uint64_t d_a0 = make_desc_k_sw32(a0), d_a1 = make_desc_k_sw32(a0 + kEtABytes);
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        mbar_wait(&tmem_empty[as * 2 + h], aph ^ 1);
+                        tc_fence_after();
+                        const uint32_t d_tmem = tmem_base + (uint32_t)(as * kEtK + h * (kEtK / 2));
+                        const uint32_t boff = (uint32_t)(h * (kEtBBytes / 2));       // centroids 128 h .. 128 h + 127
+                        umma_bf16(d_tmem, d_a0, make_desc_k_sw32(b0 + boff), idesc, 0u);                   // x1.c1 + x1.c2
+                        umma_bf16(d_tmem, d_a1, make_desc_k_sw32(b0 + kEtBBytes + boff), idesc, 1u);       // x2.c1 + |c|^2
+                        umma_commit(&tmem_full[as * 2 + h]);
+                    }
                     umma_commit(&empty[st]);
-                    if (++st == stages) { st = 0; ph ^= 1; }
-                    as ^= 1;
-                    if (as == 0) aph ^= 1;
+                    aph ^= 1;
+                    st += 2;
+                    if (st >= stages) { st -= stages; ph ^= 1; }
                 }
             }
         }
-    } else if (warp < 4) {
-        // ================= operand split (warps 2, 3; one row per lane, 64 rows per pass): the landed fp32 row ->
+    } else if (warp == 3) {
+        // ================= operand split (one row per lane, 32 rows per pass): the landed fp32 row ->
         // x1 = bf16(x), x2 = bf16(x - x1); A0 row = [x1 | x1], A1 row = [x2 | ones] =================
         int st = 0, ph = 0;
         for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
@@ -259,8 +298,8 @@ pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                 mbar_wait(&full[st], ph);
                 unsigned char* base = sStage + (size_t)st * kEtStageBytes;
 #pragma unroll
-                for (int it = 0; it < 2; ++it) {
-                    const int r = it * 64 + (warp - 2) * 32 + lane;
+                for (int it = 0; it < 4; ++it) {
+                    const int r = it * 32 + lane;
                     const float4 a = *reinterpret_cast<const float4*>(base + r * 32);
                     const float4 b = *reinterpret_cast<const float4*>(base + r * 32 + 16);
                     uint4 p, q;
@@ -294,9 +333,9 @@ pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x, step0 += m) {
             int st = (int)((step0 + ((eg - step0) & 1)) % stages);
             for (int j = (int)((eg - step0) & 1); j < m; j += 2) {
+                const unsigned char* sC = sStage + (size_t)st * kEtStageBytes + kEtXBytes + 2 * kEtABytes + 2 * kEtBBytes;
                 const uint32_t sx = smem_u32(sStage + (size_t)st * kEtStageBytes) + (uint32_t)(rt * 32);
-                mbar_wait(&tmem_full[eg], phase);      // MMAs done => the step's operands were in shared memory too
-                phase ^= 1;
+                mbar_wait(&tmem_full[eg * 2], phase);  // columns 0..127 done => the step's operands were in shared memory too
                 tc_fence_after();
                 // ONE pass over the scores.  Two 32-column register buffers: while one chunk is folded the next one's
                 // TMEM load is in flight (tcgen05.wait::ld waits for ALL outstanding loads, so exactly one is
@@ -309,13 +348,19 @@ pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                 tmem_ld_wait(va); tmem_ld_x32(taddr + 32u, vb); fold_chunk<0>(va, A, B);
                 tmem_ld_wait(vb); tmem_ld_x32(taddr + 64u, va); fold_chunk<1>(vb, A, B);
                 tmem_ld_wait(va); tmem_ld_x32(taddr + 96u, vb); fold_chunk<2>(va, A, B);
-                tmem_ld_wait(vb); tmem_ld_x32(taddr + 128u, va); fold_chunk<3>(vb, A, B);
+                tmem_ld_wait(vb);
+                tc_fence_before();
+                mbar_arrive(&tmem_empty[eg * 2]);              // columns 0..127 are in registers
+                mbar_wait(&tmem_full[eg * 2 + 1], phase);
+                phase ^= 1;
+                tc_fence_after();
+                tmem_ld_x32(taddr + 128u, va); fold_chunk<3>(vb, A, B);
                 tmem_ld_wait(va); tmem_ld_x32(taddr + 160u, vb); fold_chunk<4>(va, A, B);
                 tmem_ld_wait(vb); tmem_ld_x32(taddr + 192u, va); fold_chunk<5>(vb, A, B);
                 tmem_ld_wait(va); tmem_ld_x32(taddr + 224u, vb); fold_chunk<6>(va, A, B);
                 tmem_ld_wait(vb);
                 tc_fence_before();
-                mbar_arrive(&tmem_empty[eg]);          // all 256 columns are in registers: the MMA two steps ahead may start
+                mbar_arrive(&tmem_empty[eg * 2 + 1]);          // columns 128..255 are in registers
                 fold_chunk<7>(vb, A, B);
                 const float xs[8] = {xa.x, xa.y, xa.z, xa.w, xb.x, xb.y, xb.z, xb.w};
                 float xx = 0.f;
@@ -324,11 +369,17 @@ pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                 const float xn = sqrtf(xx) * 1.0000005f, cm_j = sCmax[j];
                 // rigorous candidate margin (see file header): operand split error + fp32 accumulation / reference rounding
                 const float thr = min16(B) + 5.2e-5f * xn * cm_j + 1e-5f * (xn + cm_j) * (xn + cm_j);
-                const uint32_t mA = le_mask16(A, thr), mB = le_mask16(B, thr);
+                // Margin test on the FMA pipe (the fold above owns the half-rate ALU pipe): u = sat((V - thr) * S) is
+                // exactly 1 for V > thr and 0 for V <= thr once S >= 2 / ulp(thr); acc = sum u * (1 + 32 i) then holds
+                // the count of minima outside the margin (low 5 bits) and the sum of their indices.
+                const uint32_t tb = __float_as_uint(thr), te = (tb >> 23) & 0xFFu;
+                const float S = __uint_as_float((279u - te) << 23), nts = -thr * S;
+                const float accA = gt_accumulate16(A, S, nts), accB = gt_accumulate16(B, S, nts);
+                const int ia = __float2int_rn(accA), ib = __float2int_rn(accB);
                 int code = 0;
-                if (__popc(mA) == 1 && __popc(mB) == 1) {
-                    code = (__ffs(mA) - 1) * 16 + __ffs(mB) - 1;
-                } else if (mA && mB) {
+                if (te >= 27u && (ia & 31) == 15 && (ib & 31) == 15) {
+                    code = (120 - (ia >> 5)) * 16 + 120 - (ib >> 5);      // the one index that is missing from each sum
+                } else if (const uint32_t mA = le_mask16(A, thr), mB = le_mask16(B, thr); mA && mB) {
                     // several candidates (a superset: the cross product of the two families): the reference's own
                     // arithmetic decides (pq.py:79-80), first minimum wins
                     float best = INFINITY;
@@ -337,8 +388,8 @@ pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                         for (uint32_t rb = mB; rb; rb &= rb - 1) {
                             const int c = c0 + __ffs(rb) - 1;
                             if (c < K) {
-                                const float4* cp = reinterpret_cast<const float4*>(cb + ((size_t)j * K + c) * 8);
-                                const float4 ca = __ldg(cp), cc = __ldg(cp + 1);
+                                const float4* cp = reinterpret_cast<const float4*>(sC + c * 32);
+                                const float4 ca = cp[0], cc = cp[1];
                                 float d[8] = {ca.x - xs[0], ca.y - xs[1], ca.z - xs[2], ca.w - xs[3],
                                               cc.x - xs[4], cc.y - xs[5], cc.z - xs[6], cc.w - xs[7]};
                                 const float dist = sqrtf(np_sumsq<8>(d));
@@ -410,6 +461,9 @@ int vdb_pq_encode_tc(const float* x, int64_t N, int D, int m, int K, const float
     if (rc) return rc;
     rc = tma_map_2d(&map_b, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, opnd, 16, (uint64_t)m * 2 * 256, 32, 16, kEtK, CU_TENSOR_MAP_SWIZZLE_32B);
     if (rc) return rc;
+    CUtensorMap map_c;
+    rc = tma_map_2d(&map_c, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, codebooks, 8, (uint64_t)m * K, 32, 8, kEtK, CU_TENSOR_MAP_SWIZZLE_NONE);
+    if (rc) return rc;
     int stages = kEtMaxStages;
     const int smem_max = max_smem_optin();
     while (stages >= 2 && et_layout(stages, m).total + 1024 > smem_max) --stages;
@@ -420,7 +474,7 @@ int vdb_pq_encode_tc(const float* x, int64_t N, int D, int m, int K, const float
     VDB_CUDA(cudaFuncSetAttribute(pq_encode_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     {
         ProfScope prof(kProfPqEncode, st);
-        pq_encode_tc_kernel<<<grid, kEtThreads, smem, st>>>(map_x, map_b, N, m, K, codebooks, cmax, stages, tiles, codes);
+        pq_encode_tc_kernel<<<grid, kEtThreads, smem, st>>>(map_x, map_b, map_c, N, m, K, cmax, stages, tiles, codes);
     }
     count_launch(1);
     VDB_CUDA(cudaGetLastError());
