@@ -135,7 +135,7 @@ def test_pq_index_end_to_end_recall_with_rerank(golden_dir):
 @pytest.mark.parametrize("n,m,K,scale", [(20_000, 16, 256, 1.0), (9_001, 48, 256, 1.0), (5_000, 4, 64, 30.0),
                                           (4_100, 6, 200, 1e-3)])
 def test_tensor_core_encode_bit_exact_vs_fp32_kernel_and_oracle(n, m, K, scale):
-    """tcgen05 tf32 candidate pass + exact tie resolution == the fp32 kernel (pinned to the reference's
+    """tcgen05 bf16-split candidate pass + exact tie resolution == the fp32 kernel (pinned to the reference's
     codes above) on random data, with duplicated centroids (exact ties -> first index wins), rows that
     sit on a centroid and rows between two centroids."""
     from vector_db_b200 import ops
@@ -153,6 +153,22 @@ def test_tensor_core_encode_bit_exact_vs_fp32_kernel_and_oracle(n, m, K, scale):
     assert (tc[:50] == 7).all() and (tc[100:150] == 3).all()
     ref = O.pq_encode(X[:600], list(cb))
     np.testing.assert_array_equal(tc[:600], ref)
+
+
+@pytest.mark.parametrize("offset,spread", [(100.0, 1.0), (-3000.0, 0.05), (0.0, 1e-18)])
+def test_tensor_core_encode_cancellation_and_tiny_inputs(offset, spread):
+    """Scores |c|^2 - 2 x.c that cancel catastrophically (rows and centroids far from the origin, close to each
+    other) and inputs whose scores underflow the margin test's exponent range: the candidate margin grows / the
+    test falls back to the exact path, codes stay equal to the fp32 kernel's and the oracle's."""
+    from vector_db_b200 import ops
+    rng = np.random.default_rng(99)
+    n, m, K = 6_000, 8, 256
+    cb = (offset + spread * rng.standard_normal((m, K, 8))).astype(np.float32)
+    X = (offset + spread * rng.standard_normal((n, 8 * m))).astype(np.float32)
+    tc = ops.pq_encode(_t(X), _t(cb), engine="tc").cpu().numpy()
+    f32 = ops.pq_encode(_t(X), _t(cb), engine="f32").cpu().numpy()
+    np.testing.assert_array_equal(tc, f32)
+    np.testing.assert_array_equal(tc[:300], O.pq_encode(X[:300], list(cb)))
 
 
 def test_tensor_core_encode_golden_reference_codes(golden_dir):
