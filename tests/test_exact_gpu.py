@@ -140,3 +140,27 @@ def test_large_scan_properties():
     d2, i2 = ops.exact_topk_f32(Q, X[100_000:], 10, "l2")
     md, mi = ops.merge_topk(torch.stack([d1, d2]), torch.stack([i1, i2 + 100_000]))
     assert torch.equal(mi, I) and torch.equal(md, D)
+
+
+@pytest.mark.gpu
+def test_search_batches_streams_results_in_order_and_equal_to_search():
+    """The pipelined host-in / host-out API (copies on their own streams, depth 2 and 3) returns, batch by
+    batch and in submission order, exactly what the blocking search() returns -- including ragged batch sizes
+    and a batch handed over as a pinned tensor."""
+    import torch
+    from vector_db_b200.indexing import ExactIndex
+    rng = np.random.default_rng(5)
+    X = rng.standard_normal((30_000, 64)).astype(np.float32)
+    idx = ExactIndex(64, "l2")
+    idx.add(range(30_000), X)
+    sizes = [200, 1, 333, 200, 64, 128, 7]
+    batches = [rng.standard_normal((n, 64)).astype(np.float32) for n in sizes]
+    want = [idx.search(b, 10) for b in batches]
+    for depth in (1, 2, 3):
+        feed = [torch.from_numpy(b).pin_memory() if j == 3 else b for j, b in enumerate(batches)]
+        got = list(idx.search_batches(iter(feed), 10, depth=depth))
+        assert len(got) == len(want)
+        for (d, i), (dw, iw) in zip(got, want):
+            np.testing.assert_array_equal(i, iw)
+            np.testing.assert_array_equal(d, dw)
+    assert list(idx.search_batches(iter([]), 10)) == []

@@ -8,7 +8,7 @@ results are ordered by (distance, id) ascending for L2 (non-squared distances) a
 """
 from __future__ import annotations
 
-from typing import Optional, Sequence, Set, Tuple
+from typing import Callable, Iterable, Iterator, Optional, Sequence, Set, Tuple
 
 import numpy as np
 import torch
@@ -70,3 +70,69 @@ class ExactIndex:
         q = self._pin[:nq].to(dev, non_blocking=True)
         d, i = self.search_device(q, k, filter_ids)
         return d.cpu().numpy(), i.cpu().numpy()
+
+    def search_batches(self, batches: Iterable, k: int, post: Optional[Callable] = None, depth: int = 2
+                       ) -> Iterator[Tuple[np.ndarray, np.ndarray]]:
+        """Host in / host out over a STREAM of query batches, software-pipelined: the H2D copy of batch n+1 and the
+        D2H copy of batch n-1 run on their own CUDA streams under the kernels of batch n, so a serving loop pays
+        max(copy, compute) per batch instead of their sum.  `batches` yields (nq, dim) float32 arrays (numpy, or
+        pinned torch tensors, which are copied from directly); results come back in order, `depth - 1` batches
+        behind the submissions.  `post(d, i) -> (d, i)`, if given, runs on the compute stream after each search
+        (the multi-GPU shard merge).  Every batch's input and output still cross PCIe -- nothing is cached."""
+        dev = self.store.device
+        cur = torch.cuda.current_stream(dev)
+        if getattr(self, "_copy_streams", None) is None:
+            self._copy_streams = (torch.cuda.Stream(dev), torch.cuda.Stream(dev))
+        s_in, s_out = self._copy_streams
+        slots = [dict(q=None, pin=None, d=None, i=None, dh=None, ih=None, nq=0, busy=False,
+                      h2d=torch.cuda.Event(), done=torch.cuda.Event(), d2h=torch.cuda.Event()) for _ in range(max(1, depth))]
+
+        def collect(slot):
+            slot["d2h"].synchronize()
+            slot["busy"] = False
+            nq = slot["nq"]
+            out = (slot["dh"][:nq].numpy().copy(), slot["ih"][:nq].numpy().copy())
+            slot["d"] = slot["i"] = None
+            return out
+
+        count = 0
+        for b in batches:
+            slot = slots[count % len(slots)]
+            if slot["busy"]:
+                yield collect(slot)
+            if isinstance(b, torch.Tensor) and b.is_pinned() and b.dtype == torch.float32 and b.is_contiguous():
+                src = b.reshape(-1, self.dim)
+            else:
+                host = np.ascontiguousarray(b, dtype=np.float32).reshape(-1, self.dim)
+                if slot["pin"] is None or slot["pin"].shape[0] < host.shape[0]:
+                    slot["pin"] = torch.empty((max(host.shape[0], 64), self.dim), dtype=torch.float32).pin_memory()
+                src = slot["pin"][:host.shape[0]]
+                src.copy_(torch.from_numpy(host))
+            nq = src.shape[0]
+            if slot["q"] is None or slot["q"].shape[0] < nq:
+                slot["q"] = torch.empty((nq, self.dim), dtype=torch.float32, device=dev)
+            with torch.cuda.stream(s_in):
+                s_in.wait_event(slot["done"])              # the slot's previous search has consumed its query buffer
+                slot["q"][:nq].copy_(src, non_blocking=True)
+                slot["h2d"].record(s_in)
+            cur.wait_event(slot["h2d"])
+            d, i = self.search_device(slot["q"][:nq], k)
+            if post is not None:
+                d, i = post(d, i)
+            slot["done"].record(cur)
+            if slot["dh"] is None or slot["dh"].shape[0] < nq or slot["dh"].shape[1] != d.shape[1]:
+                slot["dh"] = torch.empty((nq, d.shape[1]), dtype=d.dtype).pin_memory()
+                slot["ih"] = torch.empty((nq, i.shape[1]), dtype=i.dtype).pin_memory()
+            with torch.cuda.stream(s_out):
+                s_out.wait_event(slot["done"])
+                d.record_stream(s_out)
+                i.record_stream(s_out)
+                slot["dh"][:nq].copy_(d, non_blocking=True)
+                slot["ih"][:nq].copy_(i, non_blocking=True)
+                slot["d2h"].record(s_out)
+            slot.update(d=d, i=i, nq=nq, busy=True)
+            count += 1
+        for m in range(len(slots)):                        # drain in submission order
+            slot = slots[(count + m) % len(slots)]
+            if slot["busy"]:
+                yield collect(slot)
