@@ -70,3 +70,51 @@ def test_stage_memmap_to_hbm(tmp_path):
     idx.add_device(ids, vecs)
     D, I = idx.search(X[10:12], 1)
     assert I[:, 0].tolist() == [70, 77] and np.all(D[:, 0] == 0)
+
+
+def test_concurrent_search_and_insert_from_threads():
+    """The reference's callers are Starlette threadpool threads with no locks (api/app.py:120,166).  Here:
+    one thread inserts 300 nodes in order while four threads search; nothing raises, every hit is a node that
+    exists, and the graph ends up equal to the one a single-threaded build of the same insertion order gives."""
+    import random
+    import threading
+    from vector_db_b200.indexing import HNSW
+    from vector_db_b200.types import Node
+    rng = np.random.default_rng(3)
+    X = rng.standard_normal((300, 32)).astype(np.float32)
+    g = HNSW(M=8, ef_construction=40, rng=random.Random(42))
+    for i in range(20):
+        g.insert_node(Node(id=i, embedding=X[i]))
+    errors, hits = [], []
+    stop = threading.Event()
+
+    def searcher(seed):
+        r = np.random.default_rng(seed)
+        try:
+            while not stop.is_set():
+                q = X[int(r.integers(0, 20))]
+                res = g.search(q, k=5, ef=30)
+                assert 1 <= len(res) <= 5 and res[0][1] < 1e-6          # a stored row finds itself first
+                assert all(0 <= n.id < 300 for n, _ in res)
+                hits.append(len(res))
+        except Exception as e:                                            # noqa: BLE001
+            errors.append(e)
+
+    threads = [threading.Thread(target=searcher, args=(s,)) for s in range(4)]
+    for t in threads:
+        t.start()
+    try:
+        for i in range(20, 300):
+            g.insert_node(Node(id=i, embedding=X[i]))
+    finally:
+        stop.set()
+        for t in threads:
+            t.join(timeout=60)
+    assert not errors, errors[:1]
+    assert len(hits) > 0
+    ref = HNSW(M=8, ef_construction=40, rng=random.Random(42))
+    for i in range(300):
+        ref.insert_node(Node(id=i, embedding=X[i]))
+    assert g.entry_node_id == ref.entry_node_id and g.max_level == ref.max_level
+    for i in range(300):
+        assert g.node_store[i].neighbors == ref.node_store[i].neighbors
