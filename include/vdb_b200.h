@@ -209,7 +209,8 @@ int vdb_hnsw_insert(const float* db, int64_t N, int D, int32_t* adj0, int deg0, 
  * wave into its neighbours' lists and cuts them to the closest `deg` (hnsw.py:199-213).  Lists are
  * kept sorted by distance, with the distances in a parallel float array.  The result is an
  * approximation of the sequential build (wave members do not see each other), not the reference's
- * graph; vdb_hnsw_insert remains the parity builder. */
+ * graph; vdb_hnsw_insert remains the parity builder.  First int32 of ws = visited-table overflow flag,
+ * STICKY over the calls of a build: the caller zeroes it before the first wave and reads it after the last. */
 size_t vdb_hnsw_build_search_workspace(int count, int efc, int deg0);
 int vdb_hnsw_build_search(const float* db, int64_t N, int D, const int32_t* adj0, int deg0,
                           const int32_t* adj_up, int deg_up, const int32_t* up_ptr,
@@ -260,6 +261,15 @@ int vdb_ivf_adc_scan(const uint8_t* codes /*[dev] total*m*/, int m, const float*
                      const int32_t* list_ptr /*[dev]*/, const int32_t* list_rows /*[dev]*/, const int32_t* probes /*[dev]*/,
                      const int32_t* prefix /*[dev]*/, int n_probe, int R, float* out_d /*[dev] Q*R*/,
                      int32_t* out_rows /*[dev] Q*R*/, void* ws, size_t ws_bytes, void* stream);
+
+/* ---- f4: metadata pre-filter --------------------------------------------------------------------
+ * Replaces StorageService.filter_by_metadata (src/vector_db/services/storage_service.py:106-128: a Python
+ * scan that JSON-decodes every node) for the search path.  column = dictionary codes of ONE metadata key,
+ * int32 [n] in row order (0 = key missing / value None); ANDs `column[r] == want` (and the alive bitmap,
+ * if given) into bitmap [ceil(n/32)] -- first != 0 overwrites instead.  The bitmap is the row_mask /
+ * filter_bitmap argument of the search entry points (what hnsw.py:96,127 does with filter_ids). */
+int vdb_filter_eq(const int32_t* column /*[dev] n*/, int64_t n, int32_t want, const uint32_t* alive /*[dev] nullable*/,
+                  uint32_t* bitmap /*[dev] ceil(n/32)*/, int first, void* stream);
 
 /* ---- e: multi-GPU merge -----------------------------------------------------------------------
  * lists: L sorted lists per query, d [L][Q][k] / i [L][Q][k] (the all-gathered per-shard results);

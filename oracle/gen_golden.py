@@ -201,6 +201,41 @@ def gen_ivf(Storage, Node):
                         add_cluster=add_cluster, cdist=cdist, dead=dead, Dd=Dd, Id=Id, **res)
 
 
+def gen_metadata_filter():
+    """Reference StorageService.filter_by_metadata (storage_service.py:106-128) over an MMapNodeStorage in a
+    temporary directory: metadata with ints / floats / bools / strings / None / lists / missing keys, and the id
+    sets the reference returns for a list of filters."""
+    import json
+    import tempfile
+
+    from vector_db.services.storage_service import StorageService
+    from vector_db.types import Node
+    rng = np.random.default_rng(77)
+    colors = ["red", "green", "blue", None]
+    mds = []
+    for i in range(120):
+        md = {"parity": i % 2, "color": colors[i % 4], "score": float(i % 5) / 2, "flag": bool(i % 3 == 0),
+              "tags": ["a", "b"] if i % 6 == 0 else ["a"]}
+        if i % 7 == 0:
+            md.pop("color")
+        if i % 11 == 0:
+            md = {}
+        mds.append(md)
+    filters = [{"parity": 1}, {"parity": 1.0}, {"parity": True}, {"color": "red"}, {"color": None}, {"color": "purple"},
+               {"score": 1}, {"score": 0.5, "flag": True}, {"flag": 1}, {"tags": ["a", "b"]}, {"tags": ["a"]},
+               {"nokey": None}, {"nokey": 3}, {}, {"parity": 0, "color": "green", "flag": False}]
+    with tempfile.TemporaryDirectory() as tmp:
+        svc = StorageService(os.path.join(tmp, "db.npy"), dim=8, capacity=256)
+        for i, md in enumerate(mds):
+            svc.save(Node(id=i, embedding=rng.standard_normal(8).astype(np.float32) + 1.0, metadata=md, content=f"d{i}"))
+        deleted = [5, 18, 40]
+        for i in deleted:
+            svc.delete(i)
+        expect = [sorted(svc.filter_by_metadata(f)) for f in filters]
+    with open(os.path.join(OUT, "metadata_filter.json"), "w") as fh:
+        json.dump({"metadatas": mds, "deleted": deleted, "filters": filters, "expect": expect}, fh)
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     ref_hnsw, ref_pq, Storage, Node, ref_dist, topk_sorted = _import_reference()
@@ -210,8 +245,12 @@ def main():
     gen_hnsw(ref_hnsw, Storage, Node, "small", n=400, dim=16, M=8, efc=50, nq=24, ef=50, k=10, seed=11)
     gen_hnsw(ref_hnsw, Storage, Node, "medium", n=2000, dim=48, M=16, efc=100, nq=32, ef=64, k=10, seed=12)
     gen_ivf(Storage, Node)
+    gen_metadata_filter()
     print("golden fixtures written to", os.path.abspath(OUT))
 
 
-if __name__ == "__main__":
+if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "metadata":
+    _import_reference()
+    gen_metadata_filter()
+elif __name__ == "__main__":
     main()

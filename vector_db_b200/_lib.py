@@ -64,6 +64,7 @@ SIGNATURES = {
     "vdb_ivf_centroid_mean": (_i, [_p, _i, _p, _p, _i, _p, _p]),
     "vdb_ivf_adc_workspace": (_sz, [_i, _i, _i]),
     "vdb_ivf_adc_scan": (_i, [_p, _i, _p, _i, _p, _p, _p, _p, _i, _i, _p, _p, _p, _sz, _p]),
+    "vdb_filter_eq": (_i, [_p, _i64, C.c_int32, _p, _p, _i, _p]),
     "vdb_merge_topk": (_i, [_p, _p, _i, _i, _i, _i, _p, _p, _p]),
     "vdb_exchange_bytes": (_sz, [_i, _i64]),
     "vdb_exchange_grid": (_i, [_i]),

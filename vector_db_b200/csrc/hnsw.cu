@@ -715,7 +715,7 @@ int vdb_hnsw_build_search(const float* db, int64_t N, int D, const int32_t* adj0
         VDB_REQUIRE(ws_bytes >= 256 + (size_t)grid * H * 4, VDB_ERR_WORKSPACE, "workspace too small");
         ghash = reinterpret_cast<uint32_t*>(static_cast<char*>(ws) + 256);
     }
-    VDB_CUDA(cudaMemsetAsync(flag, 0, 4, st));
+    // the overflow flag is STICKY over the waves of a build: the caller zeroes it once and reads it once
     ProfScope prof(kProfHnswInsert, st);
     hnsw_build_search_kernel<<<grid, kHnswThreads, smem, st>>>(g, nodes, count, level, entry_row, max_level, seed_entry, efc,
                                                               M, CC, NM, H, ghash, out_rows, out_d, flag);

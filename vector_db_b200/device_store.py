@@ -120,14 +120,45 @@ class DeviceVectors:
         self.n_dead += 1
         return r
 
-    def bitmap_from_ids(self, ids: Iterable[int]) -> torch.Tensor:
-        """Row bitmap (uint32 words as int32 tensor) with the bits of the given external ids set."""
+    def bitmap_from_ids(self, ids) -> torch.Tensor:
+        """Row bitmap (uint32 words as int32 tensor) with the bits of the given external ids set.  A device
+        tensor is taken to BE such a bitmap already (metadata_bitmap's result) and is passed through."""
+        if isinstance(ids, torch.Tensor):
+            if ids.dtype != torch.int32 or ids.numel() < (max(self.n, 1) + 31) // 32:
+                raise ValueError("a row bitmap must be int32 words covering every row")
+            return ids.to(self.device)
         words = np.zeros((max(self.n, 1) + 31) // 32, dtype=np.uint32)
         for i in ids:
             r = self.id_to_row.get(int(i))
             if r is not None:
                 words[r // 32] |= np.uint32(1 << (r % 32))
         return torch.from_numpy(words.view(np.int32)).to(self.device)
+
+    # -- metadata columns (SURVEY.md 8f rank 4) ----------------------------------------------------
+    @property
+    def meta(self):
+        if getattr(self, "_meta", None) is None:
+            from .metadata import DeviceMetadata
+            self._meta = DeviceMetadata(self.device)
+        return self._meta
+
+    def set_metadata(self, ids: Iterable[int], metadatas) -> None:
+        """Attach metadata dicts to stored ids (ids that are not stored are skipped)."""
+        for i, md in zip(ids, metadatas):
+            r = self.id_to_row.get(int(i))
+            if r is not None:
+                self.meta.set_row(r, md)
+
+    def metadata_bitmap(self, filter_dict) -> torch.Tensor:
+        """Row bitmap of the live rows whose metadata matches every key of the filter, evaluated on the GPU
+        (storage_service.py:106-128 semantics); usable wherever ``filter_ids`` is accepted."""
+        words = (max(self.n, 1) + 31) // 32
+        return self.meta.filter_bitmap(filter_dict, self.n, alive=self.alive[:words])
+
+    def bitmap_to_ids(self, bitmap: torch.Tensor) -> set:
+        w = bitmap[:(max(self.n, 1) + 31) // 32].cpu().numpy().view(np.uint32)
+        rows = np.nonzero(np.unpackbits(w.view(np.uint8), bitorder="little")[:self.n])[0]
+        return set(self.ids[:self.n].cpu().numpy()[rows].tolist())
 
     # -- derived arrays for the tensor-core scan ------------------------------------------------
     def prepared(self, metric):

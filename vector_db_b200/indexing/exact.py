@@ -32,8 +32,16 @@ class ExactIndex:
         return int(self._last_uncertified)
 
     # -- population -----------------------------------------------------------------------------
-    def add(self, ids: Sequence[int], vectors: np.ndarray) -> None:
+    def add(self, ids: Sequence[int], vectors: np.ndarray, metadata: Optional[Sequence[dict]] = None) -> None:
+        ids = list(ids)
         self.store.append(ids, vectors)
+        if metadata is not None:
+            self.store.set_metadata(ids, metadata)
+
+    def metadata_bitmap(self, metadata_filter: dict) -> torch.Tensor:
+        """GPU-evaluated equality filter (storage_service.py:106-128 semantics) as a row bitmap; pass it as
+        ``filter_ids`` to the searches."""
+        return self.store.metadata_bitmap(metadata_filter)
 
     def add_device(self, ids: torch.Tensor, vecs: torch.Tensor) -> None:
         self.store.append_device(ids, vecs)
@@ -42,10 +50,14 @@ class ExactIndex:
         return self.store.n
 
     # -- search -----------------------------------------------------------------------------------
-    def search_device(self, q: torch.Tensor, k: int, filter_ids: Optional[Set[int]] = None
-                      ) -> Tuple[torch.Tensor, torch.Tensor]:
+    def search_device(self, q: torch.Tensor, k: int, filter_ids=None) -> Tuple[torch.Tensor, torch.Tensor]:
+        """``filter_ids``: a set of node ids, a metadata filter dict (evaluated on the GPU), or a row bitmap."""
         st = self.store
+        if isinstance(filter_ids, dict):
+            filter_ids = st.metadata_bitmap(filter_ids)
         mask = st.bitmap_from_ids(filter_ids) if filter_ids is not None else None
+        if mask is not None and st.n_dead and not isinstance(filter_ids, torch.Tensor):
+            mask = torch.bitwise_and(mask, st.alive[:mask.numel()])
         if mask is None and st.n_dead:
             mask = st.alive
         use_tc = (self.engine in ("auto", "tc") and mask is None and ops.tc_supported(q.shape[0], st.n, self.dim, k, self.metric))
@@ -58,8 +70,7 @@ class ExactIndex:
             return d, i
         return ops.exact_topk_f32(q, st.vecs, k, self.metric, ids=st.ids, row_mask=mask, n_rows=st.n)
 
-    def search(self, queries: np.ndarray, k: int, filter_ids: Optional[Set[int]] = None
-               ) -> Tuple[np.ndarray, np.ndarray]:
+    def search(self, queries: np.ndarray, k: int, filter_ids=None) -> Tuple[np.ndarray, np.ndarray]:
         """Host in / host out: pinned staging, one H2D copy, kernels, one D2H copy."""
         q_host = np.ascontiguousarray(queries, dtype=np.float32).reshape(-1, self.dim)
         nq = q_host.shape[0]

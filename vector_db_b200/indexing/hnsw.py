@@ -104,6 +104,7 @@ class HNSW:
         self._state = torch.tensor([-1, -1, 0, 0], dtype=torch.int32, device=self._device)
         self._state_host: Optional[Tuple[int, int]] = (-1, -1)
         self._snapshot = None
+        self._meta_stale = set()                      # rows whose metadata changed since the columns were built
 
     def _ensure_capacity(self, rows: int, up_rows: int) -> None:
         dev = self._device
@@ -182,6 +183,7 @@ class HNSW:
                 if node.id in self._graph_ids or node.id in fresh_set:
                     if node.id in self._graph_ids:              # idempotent insert (hnsw.py:153-155);
                         self._vectors.append([node.id], emb[None, :])   # storage was overwritten, mirror it
+                        self._meta_stale.add(self._graph_ids[node.id])
                     continue
                 fresh_ids.append(node.id)
                 fresh_set.add(node.id)
@@ -271,6 +273,8 @@ class HNSW:
             M = self.M
             up_ptr_dev = self._up_ptr_dev
             waves = 0
+            ws = ops._ws("hnsw_build", lib.vdb_hnsw_build_search_workspace(wave_max, self.ef_construction, self.M_max0), dev)
+            ws[:4].zero_()                                           # sticky overflow flag of vdb_hnsw_build_search
             for level in range(top, -1, -1):
                 rows = np.flatnonzero(levels >= level)
                 rows = rows[np.lexsort((rows, -levels[rows]))]       # upper-level nodes first, then by row
@@ -298,8 +302,6 @@ class HNSW:
                 pos = n0
                 out_rows = torch.empty((wave_max, M), dtype=torch.int32, device=dev)
                 out_d = torch.empty((wave_max, M), dtype=torch.float32, device=dev)
-                nbytes = lib.vdb_hnsw_build_search_workspace(wave_max, self.ef_construction, self.M_max0)
-                ws = ops._ws("hnsw_build", nbytes, dev)
                 while pos < len(rows):
                     b = int(min(max(pos // 4, 256), wave_max, len(rows) - pos))
                     wave = rows_t[pos:pos + b].contiguous()
@@ -330,8 +332,8 @@ class HNSW:
                                                           in_d.data_ptr(), _lib.stream_ptr(dev)))
                     pos += b
                     waves += 1
-                if int(ws[:4].view(torch.int32).item()) != 0:
-                    raise _lib.VdbError("hnsw build: visited table overflow (ef_construction * degree too large)")
+            if int(ws[:4].view(torch.int32).item()) != 0:
+                raise _lib.VdbError("hnsw build: visited table overflow (ef_construction * degree too large)")
             st = (entry_row, top)
             self._state[:2].copy_(torch.tensor(st, dtype=torch.int32))
             self._state_host = st
@@ -385,9 +387,30 @@ class HNSW:
                 self.save_index()
 
     # ------------------------------------------------------------------ search
-    def search_batch(self, queries: np.ndarray, k: int, ef: int = 50, filter_ids: Optional[Set[int]] = None,
-                     return_stats: bool = False):
-        """Many queries at once: (dist f32 [Q,k], ids i64 [Q,k]) ordered by (dist,id), padded (+inf,-1)."""
+    def _metadata_bitmap(self, metadata_filter: dict) -> torch.Tensor:
+        """Row bitmap of a metadata equality filter, evaluated on the GPU (storage_service.py:106-128 semantics).
+        Rows that came in without going through insert_node / build_index (load_index, build_from_arrays) get
+        their metadata from the storage on first use."""
+        vec = self._vectors
+        meta = vec.meta
+        todo = sorted(self._meta_stale) + list(range(meta.rows, vec.n))   # re-inserted ids, then rows not seen yet
+        if todo:
+            host_ids = vec.ids[:vec.n].cpu().numpy()
+            for r in todo:
+                try:
+                    node = self.storage.get(int(host_ids[r]))
+                except Exception:                               # noqa: BLE001 -- missing nodes are skipped (hnsw.py:120-121)
+                    node = None
+                meta.set_row(r, node.metadata if node else None)
+            meta.rows = max(meta.rows, vec.n)
+            self._meta_stale.clear()
+        return vec.metadata_bitmap(metadata_filter)
+
+    def search_batch(self, queries: np.ndarray, k: int, ef: int = 50, filter_ids=None,
+                     return_stats: bool = False, metadata_filter: Optional[dict] = None):
+        """Many queries at once: (dist f32 [Q,k], ids i64 [Q,k]) ordered by (dist,id), padded (+inf,-1).
+        ``filter_ids``: id set or row bitmap; ``metadata_filter``: {key: value} evaluated on the GPU (additive
+        kwarg: the reference builds the id set on the host, api/app.py:184-198)."""
         with self._lock:
             queries = np.ascontiguousarray(queries, dtype=np.float32)
             if queries.ndim == 1:
@@ -403,6 +426,9 @@ class HNSW:
                 raise ValueError(f"query dimension {queries.shape[1]} != index dimension {vec.dim}")
             q = torch.from_numpy(queries).to(self._device)
             flt = vec.bitmap_from_ids(filter_ids) if filter_ids is not None else None
+            if metadata_filter is not None:
+                mb = self._metadata_bitmap(metadata_filter)
+                flt = mb if flt is None else torch.bitwise_and(flt[:mb.numel()], mb)
             alive = vec.alive if vec.n_dead else None
             kk = min(k, ef)
             d, r, st = ops.hnsw_search(q, vec.vecs, vec.n, self._adj0, self._adj_up, self._up_ptr_dev, entry_row, top,
@@ -426,7 +452,7 @@ class HNSW:
         query = np.asarray(query)
         if query.ndim != 1:
             raise ValueError("query must be 1D array")
-        d, i = self.search_batch(query[None, :], k, ef=ef, filter_ids=filter_ids)
+        d, i = self.search_batch(query[None, :], k, ef=ef, filter_ids=filter_ids, metadata_filter=kwargs.get("metadata_filter"))
         results = []
         for dist, node_id in zip(d[0], i[0]):
             if node_id < 0:
