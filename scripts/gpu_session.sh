@@ -15,6 +15,7 @@ run() { # name timeout cmd...
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw,memory.used --format=csv > gpurun_out/smi.log 2>&1
 if [[ "$what" == *tests* || "$what" == *all* ]]; then
   run smoke 600 python __graft_entry__.py smoke
+  run suite_one_process 1200 python -m pytest tests -q -m gpu -x --timeout 600     # the way the driver runs it
   for f in ${TESTS:-test_exact_tc_gpu test_exact_gpu test_pq_gpu test_hnsw_gpu test_ivf_gpu test_service_gpu test_exchange_gpu}; do
     [ -f tests/$f.py ] && run $f 900 python -m pytest tests/$f.py -q -m gpu -x --timeout 600
   done
