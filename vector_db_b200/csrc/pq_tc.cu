@@ -4,7 +4,7 @@
 // Per (128-row tile, sub-space j) the whole 128 x 256 score matrix  s(c) = |c|^2 - 2 x.c  is TWO
 // tcgen05.mma.kind::f16 instructions (bf16 operands, K = 16 each, fp32 accumulation in TMEM).  bf16 keeps 8
 // significant bits, so both operands are split into bf16-exact pieces:
-//   x  = x1 + x2 + (rest <= 2^-18 |x|)        -- two helper warps convert the landed fp32 TMA tile
+//   x  = x1 + x2 + (rest <= 2^-18 |x|)        -- a helper warp converts the landed fp32 TMA tile
 //   -2c = c1 + c2 + (rest <= 2^-18 |2c|)      -- prepared once per call
 //   A0 = [x1 | x1]   B0 = [c1 | c2]           -> x1.c1 + x1.c2
 //   A1 = [x2 | 1 1 1 0 0 0 0 0]   B1 = [c1 | n1 n2 n3 0 0 0 0 0]   -> x2.c1 + |c|^2   (n = 3-way bf16 split of |c|^2)
@@ -21,22 +21,25 @@
 // RIGOROUS (5.2e-5 |x| max|c| for the split of both compared scores, plus 1e-5 (|x|+max|c|)^2 for the fp32
 // accumulation and the reference's own fp32 rounding); rows with several candidates (the cross product of the
 // two families, a superset) are resolved with the reference's exact arithmetic (numpy's pairwise-sum order,
-// sqrt, first index wins) from the fp32 row still in shared memory and the fp32 codebook -- so codes stay
+// sqrt, first index wins) from the fp32 row still in shared memory and the fp32 codebook (global memory, L2 resident) -- so codes stay
 // bit-exact although the heavy lifting is bf16.
 //
-// Measured (2M x 384 rows, m = 48, B200): 2.90 ms = 690 M vectors/s; ncu: ALU pipe 66 %, tensor pipe 25 %, issue slots
-// 55 % -- the fold is one FMNMX3 per score on the half-rate ALU pipe (2 clocks per warp instruction), ~580 clocks of
-// the ~1020 a step takes; the rest is the dependent tail of a step (norm, margin, the FMA-pipe margin test) with two
-// epilogue warps per scheduler to hide it.  The kernel is sensitive to the operand ring: time = 1.6 ms + 7.7 ms /
-// stages for 2..6 stages (a stage is held from its TMA issue to the END of the step's epilogue).
+// Measured (2M x 384 rows, m = 48, B200): 2.90 ms = 690 M vectors/s (m = 16, D = 128: 0.99 ms = 2.0 G vectors/s); ncu:
+// ALU pipe 66 %, tensor pipe 25 %, issue slots 55 % -- the fold is one FMNMX3 per score on the half-rate ALU pipe
+// (2 clocks per warp instruction), ~580 clocks of the ~1020 a step takes; the rest is the dependent tail of a step
+// (norm, margin, the FMA-pipe margin test) and the MMA hand-over, with two epilogue warps per scheduler to hide them.
 //
 // Tried and measured slower or equal (kept out): a two-pass epilogue (row minimum, then a 256-bit candidate mask:
 // 2.5 instructions per score, 5.2 ms); parking each lane's arg-min chunk in shared memory; a 16-warp epilogue with
 // the columns of a row split over two warps; four kind::tf32 MMAs on a hi/lo split (3.3 ms: twice the tensor time,
-// and K = 8 tf32 MMAs read 128 B of operands per clock, starving the epilogue's shared-memory reads); separate
-// row / operand rings with 128-byte row boxes and operand slots released at MMA completion (3.4 ms); the epilogue
-// groups preparing their own next-step operands instead of a split warp (3.6 ms: fence.proxy.async per thread and
-// step); ambiguous rows parked in shared memory and resolved once per tile (2.96 ms with 7 stages of 28 KB).
+// and K = 8 tf32 MMAs read 128 B of operands per clock, starving the epilogue's shared-memory reads); one 36 KB
+// stage per step with the fp32 codebook slice in it (2.90 ms at 6 stages, 1.6 ms + 7.7 ms / stages below that --
+// the pair-major order here reaches 10 steps of look-ahead and the same 2.90 ms: past 6 stages the ring is not the
+// bound); operand slots released at MMA completion with 128-byte row boxes (3.4 ms); the epilogue groups preparing
+// their own next-step operands instead of a split warp (3.6 ms: fence.proxy.async per thread and step); two split
+// warps with the highest warp ids (2.96 ms); THREE epilogue groups rotating over the two accumulator stages (3.5 ms
+// at 128 registers; needs a full-barrier per (step mod 6), a barrier per stage aliases use u with u + 2); ambiguous
+// rows parked in shared memory and resolved once per tile (2.96 ms).
 //
 // Roofline: HBM, algorithmic bytes per vector = 4 D + m (rows read once, codes written once).
 #include <cuda.h>
@@ -57,20 +60,28 @@ constexpr int kEtK = 256;                  // centroids per sub-space (UMMA N)
 constexpr int kEtXBytes = kEtRows * 32;    // 4 KB: 128 rows x 8 fp32 (TMA landing tile, not swizzled)
 constexpr int kEtABytes = kEtRows * 32;    // 4 KB: 128 rows x 16 bf16 (32-byte swizzle)
 constexpr int kEtBBytes = kEtK * 32;       // 8 KB: 256 centroids x 16 bf16 (32-byte swizzle)
-constexpr int kEtCBytes = kEtK * 32;       // 8 KB: the sub-space's fp32 codebook (exact tie resolution reads it)
-constexpr int kEtStageBytes = kEtXBytes + 2 * kEtABytes + 2 * kEtBBytes + kEtCBytes;   // x | A0 | A1 | B0 | B1 | C  (36 KB)
-constexpr int kEtMaxStages = 8;
+constexpr int kEtXaBytes = kEtXBytes + 2 * kEtABytes;       // x | A0 | A1  (12 KB per step)
+constexpr int kEtBsBytes = 2 * kEtBBytes;                   // B0 | B1  (16 KB per sub-space, shared by the two tiles of a pair)
+constexpr int kEtMaxXa = 16, kEtMaxBs = 8;
 
+// Work order: a CTA takes PAIRS of row tiles and walks the sub-spaces j-major over the pair -- (tile 0, j), (tile 1, j),
+// (tile 0, j+1), ... -- so the codebook operands of sub-space j are fetched once for two steps.  Two rings: the ROW
+// ring (fp32 row slice as TMA lands it + its two bf16 operand tiles, 12 KB per step) and the CODEBOOK ring (16 KB per
+// sub-space, two steps each).  At the same shared memory the look-ahead is 10 steps instead of 6 -- the kernel's
+// time follows the ring depth (1.6 ms + 7.7 ms / stages per 2M x 384 rows with one 36 KB stage per step) -- and the
+// codebook traffic from L2 halves.  Step s uses accumulator stage s & 1 = its tile within the pair, so each
+// epilogue group owns one tile of the pair and stages that tile's codes on its own.
 struct EtSmem {
-    int stage_off, cmax_off, codes_off, bar_off, total;
+    int xa_off, bs_off, cmax_off, codes_off, bar_off, total;
 };
-__host__ __device__ inline EtSmem et_layout(int stages, int m) {
+__host__ __device__ inline EtSmem et_layout(int nxa, int nbs, int m) {
     EtSmem L;
-    L.stage_off = 0;
-    L.cmax_off = stages * kEtStageBytes;                       // 36 KB stages keep 1024-byte alignment
+    L.bs_off = 0;                                              // 16 KB slots first: 1024-byte aligned
+    L.xa_off = nbs * kEtBsBytes;                               // 12 KB slots: 1024-byte aligned as well
+    L.cmax_off = L.xa_off + nxa * kEtXaBytes;
     L.codes_off = L.cmax_off + ((m * 4 + 15) & ~15);
-    L.bar_off = (L.codes_off + kEtRows * m + 15) & ~15;        // code staging [128 rows][m]
-    L.total = L.bar_off + (3 * kEtMaxStages + 8) * 8 + 16;
+    L.bar_off = (L.codes_off + 2 * kEtRows * m + 15) & ~15;    // code staging [2 tiles][128 rows][m]
+    L.total = L.bar_off + (3 * kEtMaxXa + 2 * kEtMaxBs + 8) * 8 + 16;
     return L;
 }
 
@@ -189,40 +200,43 @@ __device__ __forceinline__ float4 lds128(uint32_t saddr) {
 
 __global__ void __launch_bounds__(kEtThreads, 1)
 pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_b,
-                    const __grid_constant__ CUtensorMap map_c, int64_t N, int m, int K, const float* __restrict__ cmax, int stages,
-                    int64_t tiles, uint8_t* __restrict__ codes) {
+                    const float* __restrict__ x, int64_t N, int D, int m, int K, const float* __restrict__ cb,
+                    const float* __restrict__ cmax, int nxa, int nbs, int64_t pairs, uint8_t* __restrict__ codes) {
     extern __shared__ __align__(1024) unsigned char smem[];
     if ((smem_u32(smem) & 1023u) != 0) __trap();
-    const EtSmem L = et_layout(stages, m);
-    unsigned char* sStage = smem + L.stage_off;
+    const EtSmem L = et_layout(nxa, nbs, m);
+    unsigned char* sXa = smem + L.xa_off;
+    unsigned char* sBs = smem + L.bs_off;
     float* sCmax = reinterpret_cast<float*>(smem + L.cmax_off);
     uint8_t* sCodes = smem + L.codes_off;
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L.bar_off);
-    uint64_t* full = bars;                          // [stages]: TMA landed (x fp32, B0, B1)
-    uint64_t* empty = bars + kEtMaxStages;          // [stages]: MMA done with the operands + epilogue done with x
-    uint64_t* a_full = bars + 2 * kEtMaxStages;     // [stages]: A0 / A1 written by the split warps
-    uint64_t* tmem_full = bars + 3 * kEtMaxStages;  // [2 accumulator stages][2 column halves]
+    uint64_t* x_full = bars;                        // [nxa]: TMA landed the fp32 row slice
+    uint64_t* a_full = bars + kEtMaxXa;             // [nxa]: A0 / A1 written by the split warp
+    uint64_t* xa_empty = bars + 2 * kEtMaxXa;       // [nxa]: MMAs done with A0 / A1 + epilogue done with x
+    uint64_t* b_full = bars + 3 * kEtMaxXa;         // [nbs]: TMA landed B0, B1
+    uint64_t* b_empty = b_full + kEtMaxBs;          // [nbs]: the MMAs of BOTH steps of the sub-space are done
+    uint64_t* tmem_full = b_empty + kEtMaxBs;       // [2 accumulator stages][2 column halves]
     uint64_t* tmem_empty = tmem_full + 4;           // [2][2]
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 4);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     // constant half of every A1 row: (1,1,1,0,0,0,0,0) bf16 against the norm pieces; with the 32-byte swizzle the
     // two 16-byte halves of row r trade places when bit 2 of r is set
-    for (int i = threadIdx.x; i < stages * kEtRows; i += kEtThreads) {
+    for (int i = threadIdx.x; i < nxa * kEtRows; i += kEtThreads) {
         const int sidx = i / kEtRows, r = i % kEtRows;
-        unsigned char* a1 = sStage + (size_t)sidx * kEtStageBytes + kEtXBytes + kEtABytes;
+        unsigned char* a1 = sXa + (size_t)sidx * kEtXaBytes + kEtXBytes + kEtABytes;
         *reinterpret_cast<uint4*>(a1 + r * 32 + (16 ^ (((r >> 2) & 1) << 4))) = make_uint4(0x3F803F80u, 0x00003F80u, 0u, 0u);
     }
     for (int i = threadIdx.x; i < m; i += kEtThreads) sCmax[i] = cmax[i];
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&map_x);
         tma_prefetch_desc(&map_b);
-        tma_prefetch_desc(&map_c);
     }
     if (warp == 1 && lane == 0) {
-        for (int i = 0; i < stages; ++i) {
-            mbar_init(&full[i], 1); mbar_init(&empty[i], 1 + 4); mbar_init(&a_full[i], 1);   // empty: MMA commit + 4 epilogue warps
+        for (int i = 0; i < nxa; ++i) {
+            mbar_init(&x_full[i], 1); mbar_init(&a_full[i], 1); mbar_init(&xa_empty[i], 1 + 4);   // MMA commit + 4 epilogue warps
         }
+        for (int i = 0; i < nbs; ++i) { mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], 2); }
         for (int i = 0; i < 4; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 128); }
         fence_barrier_init();
     }
@@ -236,41 +250,45 @@ pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     if (warp == 0) {
         // ================= TMA producer =================
         if (lane == 0) {
-            int st = 0, ph = 0;
-            for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+            int xs = 0, bs = 0;
+            uint32_t xph = 0, bph = 0;
+            for (int64_t pair = blockIdx.x; pair < pairs; pair += gridDim.x) {
                 for (int j = 0; j < m; ++j) {
-                    mbar_wait(&empty[st], ph ^ 1);
-                    unsigned char* base = sStage + (size_t)st * kEtStageBytes;
-                    mbar_expect_tx(&full[st], (uint32_t)(kEtXBytes + 2 * kEtBBytes + kEtCBytes));
-                    tma_load_2d(base, &map_x, &full[st], j * 8, (int)(tile * kEtRows), kEvictFirst);
-                    tma_load_2d(base + kEtXBytes + 2 * kEtABytes, &map_b, &full[st], 0, (j * 2) * 256, kEvictLast);
-                    tma_load_2d(base + kEtXBytes + 2 * kEtABytes + kEtBBytes, &map_b, &full[st], 0, (j * 2 + 1) * 256, kEvictLast);
-                    tma_load_2d(base + kEtXBytes + 2 * kEtABytes + 2 * kEtBBytes, &map_c, &full[st], 0, j * K, kEvictLast);
-                    if (++st == stages) { st = 0; ph ^= 1; }
+                    mbar_wait(&b_empty[bs], bph ^ 1);
+                    unsigned char* bb = sBs + (size_t)bs * kEtBsBytes;
+                    mbar_expect_tx(&b_full[bs], (uint32_t)kEtBsBytes);
+                    tma_load_2d(bb, &map_b, &b_full[bs], 0, (j * 2) * 256, kEvictLast);
+                    tma_load_2d(bb + kEtBBytes, &map_b, &b_full[bs], 0, (j * 2 + 1) * 256, kEvictLast);
+                    if (++bs == nbs) { bs = 0; bph ^= 1; }
+#pragma unroll
+                    for (int t = 0; t < 2; ++t) {
+                        mbar_wait(&xa_empty[xs], xph ^ 1);
+                        mbar_expect_tx(&x_full[xs], (uint32_t)kEtXBytes);
+                        // rows past N (a pair's missing second tile included) land as zeros and are never stored
+                        tma_load_2d(sXa + (size_t)xs * kEtXaBytes, &map_x, &x_full[xs], j * 8, (int)((pair * 2 + t) * kEtRows), kEvictFirst);
+                        if (++xs == nxa) { xs = 0; xph ^= 1; }
+                    }
                 }
             }
         }
     } else if (warp < 3) {
-        // ================= MMA issuers: warp 1 owns accumulator stage 0 (even steps), warp 2 stage 1 (odd steps).
+        // ================= MMA issuers: warp 1 owns accumulator stage 0 (tile 0 of every pair), warp 2 stage 1 (tile 1).
         // With ONE in-order issuer the MMAs of a step whose accumulator half was already free queued behind the
-        // other stage's wait for its epilogue group, and the two groups fell into lock step. =================
+        // other stage's wait for its epilogue group. =================
         if (lane == 0) {
             // Each 256-column accumulator is produced and released in two 128-column halves: the epilogue hands half 0
             // back while it is still folding half 1, so the MMAs of the group's next step run under epilogue work and
             // only the short second half sits in the release -> MMA -> fold dependency chain.
             const int as = warp - 1;
             const uint32_t idesc = make_idesc_bf16(kEtRows, kEtK / 2);
-            int64_t step0 = 0;
-            int aph = 0;
-            for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x, step0 += m) {
-                int64_t sidx = step0 + ((as - step0) & 1);
-                int st = (int)(sidx % stages);
-                int ph = (int)((sidx / stages) & 1);
-                for (int j = (int)((as - step0) & 1); j < m; j += 2) {
-                    mbar_wait(&full[st], ph);
-                    mbar_wait(&a_full[st], ph);
-                    const uint32_t base = smem_u32(sStage + (size_t)st * kEtStageBytes);
-                    const uint32_t a0 = base + kEtXBytes, b0 = a0 + 2 * kEtABytes;
+            int xs = as % nxa, bs = 0, aph = 0;        // own steps s = as, as + 2, ...: row slot s mod nxa, codebook slot (s / 2) mod nbs
+            uint32_t xph = 0, bph = 0;
+            for (int64_t pair = blockIdx.x; pair < pairs; pair += gridDim.x) {
+                for (int j = 0; j < m; ++j) {
+                    mbar_wait(&b_full[bs], bph);
+                    mbar_wait(&a_full[xs], xph);
+                    const uint32_t a0 = smem_u32(sXa + (size_t)xs * kEtXaBytes) + kEtXBytes;
+                    const uint32_t b0 = smem_u32(sBs + (size_t)bs * kEtBsBytes);
                     const uint64_t d_a0 = make_desc_k_sw32(a0), d_a1 = make_desc_k_sw32(a0 + kEtABytes);
 #pragma unroll
                     for (int h = 0; h < 2; ++h) {
@@ -282,21 +300,24 @@ pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                         umma_bf16(d_tmem, d_a1, make_desc_k_sw32(b0 + kEtBBytes + boff), idesc, 1u);       // x2.c1 + |c|^2
                         umma_commit(&tmem_full[as * 2 + h]);
                     }
-                    umma_commit(&empty[st]);
+                    umma_commit(&xa_empty[xs]);
+                    umma_commit(&b_empty[bs]);
                     aph ^= 1;
-                    st += 2;
-                    if (st >= stages) { st -= stages; ph ^= 1; }
+                    xs += 2;
+                    if (xs >= nxa) { xs -= nxa; xph ^= 1; }
+                    if (++bs == nbs) { bs = 0; bph ^= 1; }
                 }
             }
         }
     } else if (warp == 3) {
         // ================= operand split (one row per lane, 32 rows per pass): the landed fp32 row ->
         // x1 = bf16(x), x2 = bf16(x - x1); A0 row = [x1 | x1], A1 row = [x2 | ones] =================
-        int st = 0, ph = 0;
-        for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
-            for (int j = 0; j < m; ++j) {
-                mbar_wait(&full[st], ph);
-                unsigned char* base = sStage + (size_t)st * kEtStageBytes;
+        int xs = 0;
+        uint32_t xph = 0;
+        for (int64_t pair = blockIdx.x; pair < pairs; pair += gridDim.x) {
+            for (int sidx = 0; sidx < 2 * m; ++sidx) {
+                mbar_wait(&x_full[xs], xph);
+                unsigned char* base = sXa + (size_t)xs * kEtXaBytes;
 #pragma unroll
                 for (int it = 0; it < 4; ++it) {
                     const int r = it * 32 + lane;
@@ -315,26 +336,25 @@ pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                 }
                 fence_proxy_async();                   // generic-proxy writes -> visible to the MMA's async-proxy reads
                 __syncwarp();
-                if (lane == 0) mbar_arrive(&a_full[st]);
-                if (++st == stages) { st = 0; ph ^= 1; }
+                if (lane == 0) mbar_arrive(&a_full[xs]);
+                if (++xs == nxa) { xs = 0; xph ^= 1; }
             }
         }
     } else {
-        // ================= epilogue: one thread per row; group eg owns accumulator stage eg = every other step =================
-        // The step's operand stage stays resident until the epilogue releases it, so the exact fp32 row slice is
-        // read back from shared memory, never from global.
+        // ================= epilogue: one thread per row; group eg owns accumulator stage eg = tile eg of every pair =================
+        // The step's row slot stays resident until the epilogue releases it, so the exact fp32 row slice is read back
+        // from shared memory; the fp32 centroids of the rare ambiguous row come from global memory (L2 resident).
         const int eg = (warp - 4) >> 2;
         const int ew = warp & 3;
         const int rt = ew * 32 + lane;                 // row within the tile == TMEM lane
-        const int et = threadIdx.x - 128;              // 0..255
+        const int et = threadIdx.x - 128 - eg * 128;   // 0..127 within the group
         const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(eg * kEtK);
-        int64_t step0 = 0;                             // global step index of (tile, j = 0)
+        uint8_t* sCodesG = sCodes + (size_t)eg * kEtRows * m;
+        int xs = eg % nxa;                             // own steps s = eg, eg + 2, ...: row slot s mod nxa
         int phase = 0;
-        for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x, step0 += m) {
-            int st = (int)((step0 + ((eg - step0) & 1)) % stages);
-            for (int j = (int)((eg - step0) & 1); j < m; j += 2) {
-                const unsigned char* sC = sStage + (size_t)st * kEtStageBytes + kEtXBytes + 2 * kEtABytes + 2 * kEtBBytes;
-                const uint32_t sx = smem_u32(sStage + (size_t)st * kEtStageBytes) + (uint32_t)(rt * 32);
+        for (int64_t pair = blockIdx.x; pair < pairs; pair += gridDim.x) {
+            for (int j = 0; j < m; ++j) {
+                const uint32_t sx = smem_u32(sXa + (size_t)xs * kEtXaBytes) + (uint32_t)(rt * 32);
                 mbar_wait(&tmem_full[eg * 2], phase);  // columns 0..127 done => the step's operands were in shared memory too
                 tc_fence_after();
                 // ONE pass over the scores.  Two 32-column register buffers: while one chunk is folded the next one's
@@ -362,10 +382,12 @@ pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                 tc_fence_before();
                 mbar_arrive(&tmem_empty[eg * 2 + 1]);          // columns 128..255 are in registers
                 fold_chunk<7>(vb, A, B);
-                const float xs[8] = {xa.x, xa.y, xa.z, xa.w, xb.x, xb.y, xb.z, xb.w};
+                const float xs8[8] = {xa.x, xa.y, xa.z, xa.w, xb.x, xb.y, xb.z, xb.w};
                 float xx = 0.f;
 #pragma unroll
-                for (int t = 0; t < 8; ++t) xx = fmaf(xs[t], xs[t], xx);
+                for (int t = 0; t < 8; ++t) xx = fmaf(xs8[t], xs8[t], xx);
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&xa_empty[xs]);     // this warp no longer reads the step's row slice
                 const float xn = sqrtf(xx) * 1.0000005f, cm_j = sCmax[j];
                 // rigorous candidate margin (see file header): operand split error + fp32 accumulation / reference rounding
                 const float thr = min16(B) + 5.2e-5f * xn * cm_j + 1e-5f * (xn + cm_j) * (xn + cm_j);
@@ -383,41 +405,42 @@ pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                     // several candidates (a superset: the cross product of the two families): the reference's own
                     // arithmetic decides (pq.py:79-80), first minimum wins
                     float best = INFINITY;
+                    const float* cbj = cb + (size_t)j * K * 8;
                     for (uint32_t ra = mA; ra; ra &= ra - 1) {
                         const int c0 = (__ffs(ra) - 1) * 16;
                         for (uint32_t rb = mB; rb; rb &= rb - 1) {
                             const int c = c0 + __ffs(rb) - 1;
                             if (c < K) {
-                                const float4* cp = reinterpret_cast<const float4*>(sC + c * 32);
-                                const float4 ca = cp[0], cc = cp[1];
-                                float d[8] = {ca.x - xs[0], ca.y - xs[1], ca.z - xs[2], ca.w - xs[3],
-                                              cc.x - xs[4], cc.y - xs[5], cc.z - xs[6], cc.w - xs[7]};
+                                const float4* cp = reinterpret_cast<const float4*>(cbj + (size_t)c * 8);
+                                const float4 ca = __ldg(cp), cc = __ldg(cp + 1);
+                                float d[8] = {ca.x - xs8[0], ca.y - xs8[1], ca.z - xs8[2], ca.w - xs8[3],
+                                              cc.x - xs8[4], cc.y - xs8[5], cc.z - xs8[6], cc.w - xs8[7]};
                                 const float dist = sqrtf(np_sumsq<8>(d));
                                 if (dist < best) { best = dist; code = c; }
                             }
                         }
                     }
                 }
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&empty[st]);    // this warp no longer reads the operand stage
-                sCodes[rt * m + j] = (uint8_t)code;
-                st += 2;
-                if (st >= stages) st -= stages;
+                sCodesG[rt * m + j] = (uint8_t)code;
+                xs += 2;
+                if (xs >= nxa) xs -= nxa;
             }
             // the tile's codes are one contiguous run of 128*m bytes in global memory
-            named_bar_sync(1, 256);
-            const int64_t row0 = tile * kEtRows;
-            const int64_t nbytes = (N - row0 < kEtRows ? N - row0 : kEtRows) * m;
-            uint8_t* dst = codes + row0 * m;
-            if ((reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
-                const int64_t n16 = nbytes >> 4;
-                for (int64_t i = et; i < n16; i += 256)
-                    reinterpret_cast<uint4*>(dst)[i] = reinterpret_cast<const uint4*>(sCodes)[i];
-                for (int64_t i = (n16 << 4) + et; i < nbytes; i += 256) dst[i] = sCodes[i];
-            } else {
-                for (int64_t i = et; i < nbytes; i += 256) dst[i] = sCodes[i];
+            named_bar_sync(1 + eg, 128);
+            const int64_t row0 = (pair * 2 + eg) * kEtRows;
+            if (row0 < N) {
+                const int64_t nbytes = (N - row0 < kEtRows ? N - row0 : kEtRows) * m;
+                uint8_t* dst = codes + row0 * m;
+                if ((reinterpret_cast<uintptr_t>(dst) & 15) == 0 && (reinterpret_cast<uintptr_t>(sCodesG) & 15) == 0) {
+                    const int64_t n16 = nbytes >> 4;
+                    for (int64_t i = et; i < n16; i += 128)
+                        reinterpret_cast<uint4*>(dst)[i] = reinterpret_cast<const uint4*>(sCodesG)[i];
+                    for (int64_t i = (n16 << 4) + et; i < nbytes; i += 128) dst[i] = sCodesG[i];
+                } else {
+                    for (int64_t i = et; i < nbytes; i += 128) dst[i] = sCodesG[i];
+                }
             }
-            named_bar_sync(1, 256);
+            named_bar_sync(1 + eg, 128);
         }
     }
     tc_fence_before();
@@ -461,20 +484,20 @@ int vdb_pq_encode_tc(const float* x, int64_t N, int D, int m, int K, const float
     if (rc) return rc;
     rc = tma_map_2d(&map_b, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, opnd, 16, (uint64_t)m * 2 * 256, 32, 16, kEtK, CU_TENSOR_MAP_SWIZZLE_32B);
     if (rc) return rc;
-    CUtensorMap map_c;
-    rc = tma_map_2d(&map_c, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, codebooks, 8, (uint64_t)m * K, 32, 8, kEtK, CU_TENSOR_MAP_SWIZZLE_NONE);
-    if (rc) return rc;
-    int stages = kEtMaxStages;
+    // ring depths: 5 codebook slots (10 steps), as many row slots as shared memory allows
     const int smem_max = max_smem_optin();
-    while (stages >= 2 && et_layout(stages, m).total + 1024 > smem_max) --stages;
-    VDB_REQUIRE(stages >= 2, VDB_ERR_UNSUPPORTED, "m=%d does not fit shared memory", m);
-    const size_t smem = (size_t)et_layout(stages, m).total;
+    int nbs = 5, nxa = kEtMaxXa;
+    while (nxa > 4 && et_layout(nxa, nbs, m).total + 1024 > smem_max) --nxa;
+    while (nbs > 2 && et_layout(nxa, nbs, m).total + 1024 > smem_max) --nbs;
+    VDB_REQUIRE(et_layout(nxa, nbs, m).total + 1024 <= smem_max, VDB_ERR_UNSUPPORTED, "m=%d does not fit shared memory", m);
+    const size_t smem = (size_t)et_layout(nxa, nbs, m).total;
     const int64_t tiles = (N + kEtRows - 1) / kEtRows;
-    const int grid = (int)(tiles < sm_count() ? tiles : sm_count());
+    const int64_t pairs = (tiles + 1) / 2;
+    const int grid = (int)(pairs < sm_count() ? pairs : sm_count());
     VDB_CUDA(cudaFuncSetAttribute(pq_encode_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     {
         ProfScope prof(kProfPqEncode, st);
-        pq_encode_tc_kernel<<<grid, kEtThreads, smem, st>>>(map_x, map_b, map_c, N, m, K, cmax, stages, tiles, codes);
+        pq_encode_tc_kernel<<<grid, kEtThreads, smem, st>>>(map_x, map_b, x, N, D, m, K, codebooks, cmax, nxa, nbs, pairs, codes);
     }
     count_launch(1);
     VDB_CUDA(cudaGetLastError());
