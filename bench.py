@@ -159,12 +159,20 @@ def run_reference(args):
     rank, _, world = _dist_env()
     if rank != 0:
         return
-    rng = np.random.default_rng(SEED_DB)
-    X = rng.standard_normal((N_ROWS, DIM), dtype=np.float32)
+    # the ours arm is weak scaling: at N GPUs every query is answered over N x 1M rows, so the CPU arm scans that many
+    rows = N_ROWS * max(1, int(args.gpus))
+    try:                                              # torchrun exports OMP_NUM_THREADS=1: give BLAS the host's cores back
+        from threadpoolctl import threadpool_limits
+        threadpool_limits(limits=os.cpu_count())
+    except Exception:                                 # noqa: BLE001
+        pass
+    X = np.empty((rows, DIM), dtype=np.float32)
+    for r in range(max(1, int(args.gpus))):           # the same per-shard seeds as the GPU arm's shards
+        X[r * N_ROWS:(r + 1) * N_ROWS] = np.random.default_rng(SEED_DB + r).standard_normal((N_ROWS, DIM), dtype=np.float32)
     Q = np.random.default_rng(SEED_Q).standard_normal((N_QUERIES, DIM), dtype=np.float32)
     from oracle import oracle as O
     xn = np.sqrt(np.einsum("ij,ij->i", X, X)).astype(np.float32)
-    ids = np.arange(N_ROWS, dtype=np.int64)
+    ids = np.arange(rows, dtype=np.int64)
     nq = 32                                           # bounded sample per step
     for _ in range(args.warmup):
         O.exact_cosine_topk_gemm(X, ids, Q[:nq], K, xn=xn)
@@ -177,10 +185,10 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": qps, "unit": "queries/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"exact cosine top-{K}, {N_ROWS} x {DIM} fp32, {nq}-query sample of the "
+        "config": {"workload": f"exact cosine top-{K}, {rows} x {DIM} fp32, {nq}-query sample of the "
                                f"{N_QUERIES}-query batch per step (CPU port of the reference path)"},
         "cpu_baseline": {"value": qps, "unit": "queries/s", "cores": os.cpu_count(), "kind": "port",
-                         "sample": f"{nq} queries x {N_ROWS} rows per step, numpy sgemm + argpartition"},
+                         "sample": f"{nq} queries x {rows} rows per step, numpy sgemm + argpartition"},
         "e2e": {"value": qps, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
