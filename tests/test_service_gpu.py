@@ -118,3 +118,53 @@ def test_concurrent_search_and_insert_from_threads():
     assert g.entry_node_id == ref.entry_node_id and g.max_level == ref.max_level
     for i in range(300):
         assert g.node_store[i].neighbors == ref.node_store[i].neighbors
+
+
+def test_memory_mapping_service_dropin(tmp_path):
+    """tests/inference/test_mmap_vector_store.py restated against the GPU-backed facade: constructor validation,
+    write / read / get_embedding / delete / search contracts and messages, persistence across a reopen."""
+    from vector_db_b200.inference import MemoryMappingService
+    cfg = tmp_path / "config.yaml"
+    cfg.write_text("index:\n  M: 4\n  ef_construction: 10\n")
+    base = str(tmp_path / "vectors")
+    with pytest.raises(ValueError, match="Dimension must be greater than 0"):
+        MemoryMappingService(base, dim=0, capacity=10, config_path=str(cfg))
+    with pytest.raises(ValueError, match="Capacity must be greater than 0"):
+        MemoryMappingService(base, dim=4, capacity=0, config_path=str(cfg))
+    with pytest.raises(ValueError, match="config_path is required"):
+        MemoryMappingService(base, dim=4, capacity=10)
+    svc = MemoryMappingService(base, dim=4, capacity=10, config_path=str(cfg), index_file=str(tmp_path / "index.pkl"))
+    assert svc.size == 0 and svc.dim == 4 and svc.capacity == 10 and svc.index.M == 4 and svc.index.ef_construction == 10
+    with pytest.raises(TypeError, match="Embedding must be a numpy array"):
+        svc.write([1.0, 2.0, 3.0, 4.0])
+    with pytest.raises(ValueError, match="Embedding must be a 1D array"):
+        svc.write(np.zeros((2, 2), dtype=np.float32))
+    with pytest.raises(ValueError, match="Embedding must be of dimension 4"):
+        svc.write(np.zeros(3, dtype=np.float32))
+    embs = [np.array([1.0, 0.0, 0.0, 0.0]), np.array([0.0, 1.0, 0.0, 0.0], dtype=np.float32),
+            np.array([0.0, 0.0, 1.0, 0.0], dtype=np.float32)]
+    ids = [svc.write(e, content=f"node_{i}", metadata={"n": i}) for i, e in enumerate(embs)]     # float64 is cast
+    assert ids == [0, 1, 2] and svc.size == 3
+    node = svc.read(1)
+    assert node.id == 1 and node.content == "node_1" and node.metadata == {"n": 1}
+    np.testing.assert_array_equal(node.embedding, embs[1])
+    np.testing.assert_array_equal(svc.get_embedding(0), embs[0].astype(np.float32))
+    with pytest.raises(TypeError, match="Node ID must be an integer"):
+        svc.read("0")
+    with pytest.raises(IndexError, match="Node 999 not found"):
+        svc.read(999)
+    res = svc.search(np.array([1.0, 0.0, 0.0, 0.0], dtype=np.float32), k=2, ef=10)
+    assert 0 < len(res) <= 2 and res[0][0].id == 0 and res[0][1] < 1e-6
+    more = svc.write_many(np.eye(4, dtype=np.float32)[3:4] * 2.0, contents=["batched"])
+    assert more == [3] and svc.read(3).content == "batched" and svc.size == 4
+    svc.delete(1)
+    assert svc.size == 3
+    with pytest.raises(IndexError):
+        svc.read(1)
+    assert all(n.id != 1 for n, _ in svc.search(embs[1].astype(np.float32), k=3, ef=10))
+    before = [(n.id, float(d)) for n, d in svc.search(embs[2], k=3, ef=10)]
+    svc.storage.close()
+    del svc
+    svc2 = MemoryMappingService(base, dim=4, capacity=10, config_path=str(cfg), index_file=str(tmp_path / "index.pkl"))
+    assert svc2.size == 3 and svc2.read(0).content == "node_0"
+    assert [(n.id, float(d)) for n, d in svc2.search(embs[2], k=3, ef=10)] == before
