@@ -374,8 +374,34 @@ select_bins_kernel(const u64* __restrict__ partial, int L, int NBL, int NB, int 
         }
         buf[i] = key;
     }
+    u64* top = buf + C;                    // the NB best keys, ascending
+    for (int i = threadIdx.x; i < NB; i += blockDim.x) top[i] = VDB_KEY_MAX;
     __syncthreads();
-    block_bitonic_sort(buf, C);
+    // The L lists arrive sorted by score, so a key's rank among all keys is its position in its own list plus, for
+    // every other list, the number of entries ahead of it -- a 5-probe binary search per list instead of a bitonic
+    // sort of all C keys (the sort was 45 barrier-separated passes and made this kernel 4 % of a search step).
+    // Ties on the score are ordered by (list, position), which keeps the ranks unique whatever the bins are.
+    for (int i = threadIdx.x; i < total; i += blockDim.x) {
+        const u64 key = buf[i];
+        if (key == VDB_KEY_MAX) continue;
+        const unsigned sc = (unsigned)(key >> 32);
+        const int la = i / NBL;
+        int rank = i - la * NBL;
+        for (int l = 0; l < L; ++l) {
+            if (l == la) continue;
+            const u64* lst = buf + l * NBL;
+            const unsigned t = sc + (l < la ? 1u : 0u);            // entries with score < t are ahead (sc < 0xFFFFFFFF: a real key)
+            int pos = 0;
+            for (int h = NBL >> 1; h > 0; h >>= 1)
+                if ((unsigned)(lst[pos + h - 1] >> 32) < t) pos += h;
+            if ((unsigned)(lst[pos] >> 32) < t) ++pos;
+            rank += pos;
+        }
+        if (rank < NB) top[rank] = key;
+    }
+    __syncthreads();
+    buf = top;
+    C = NB;
     if (threadIdx.x == 0) {
         float tau = ordered_to_f32(tau_bits);
         if (NB - 1 < C && buf[NB - 1] != VDB_KEY_MAX) tau = fminf(tau, key_score(buf[NB - 1]));
@@ -660,13 +686,13 @@ int vdb_exact_topk_tc(const float* q, int Q, const float* db, const void* mirror
     VDB_CUDA(cudaGetLastError());
     const int L = p.S * kGroups;
     const int C = next_pow2(L * nbl < 64 ? 64 : L * nbl);
-    VDB_CUDA(cudaFuncSetAttribute(select_bins_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, C * 8));
+    VDB_CUDA(cudaFuncSetAttribute(select_bins_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (C + kNBFinal) * 8));
     // bins handed to the rerank per query (select_bins_kernel drops those that provably cannot matter);
     // debug bits 12..19 override the count, bit 4 disables the trimming
     int nbf = kNBFinal;
     if ((g_tc_flags >> 12) & 0xFF) nbf = (g_tc_flags >> 12) & 0xFF;
     if (nbf > kNBFinal) nbf = kNBFinal;
-    select_bins_kernel<<<Q, 256, (size_t)C * 8, st>>>(partial, L, nbl, nbf, C, N, cand, cand_cnt, tau, q, D, k, metric,
+    select_bins_kernel<<<Q, 256, (size_t)(C + kNBFinal) * 8, st>>>(partial, L, nbl, nbf, C, N, cand, cand_cnt, tau, q, D, k, metric,
                                                       (g_tc_flags & 16) ? INFINITY : db_max_norm);
     count_launch(3);
     VDB_CUDA(cudaGetLastError());
