@@ -85,7 +85,9 @@ struct BinList {
 };
 
 __device__ __forceinline__ float min8(const float* v) {
-    return fminf(fminf(fminf(v[0], v[1]), fminf(v[2], v[3])), fminf(fminf(v[4], v[5]), fminf(v[6], v[7])));
+    // three FMNMX3 + one FMNMX (the balanced two-input tree is seven instructions on the half-rate ALU pipe)
+    const float a = fminf(fminf(v[0], v[1]), v[2]), b = fminf(fminf(v[3], v[4]), v[5]);
+    return fminf(fminf(a, b), fminf(v[6], v[7]));
 }
 
 // One 32-column chunk of one accumulator row: the columns ARE the scores (the operand mirror is
