@@ -167,6 +167,126 @@ struct BlockSelect {
     }
 };
 
+// ------------------------------------------------------------------ BlockSelectRadix
+// The same streaming "keep the R smallest keys" protocol WITHOUT sorting, for large R next to few candidates
+// (IVF-PQ shortlists: R = 1000 of ~16 k candidates per CTA, where the bitonic sorts of BlockSelect were 3/4 of
+// the kernel's shared-memory traffic).  A compaction finds the R-th smallest key exactly with an 8-pass radix
+// select over the 64-bit keys (one warp-aggregated shared histogram per byte) and then moves the keys <= it to
+// the front with a stable in-place compaction.  buf[0, kept) holds the survivors in NO particular order.
+// Requirements: keys unique and < VDB_KEY_MAX; blockDim.x a multiple of 32, >= 256 and <= 1024; `scratch` =
+// kSelectRadixScratch ints of shared memory.
+constexpr int kSelectRadixScratch = 256 + 64 + 2;
+
+struct BlockSelectRadix {
+    u64* buf;
+    int* cnt;
+    u64* thr;
+    int* hist;    // 256 bins
+    int* wsum;    // 2 x 32 warp totals
+    int* sel;     // chosen bin, rank inside it
+    int C, R, burst;
+    int kept;     // CTA-uniform: keys at the front of buf (0 until the first compaction, then R)
+
+    __device__ __forceinline__ void init(u64* b, int* c, u64* t, int* scratch, int C_, int R_, int burst_) {
+        buf = b; cnt = c; thr = t; hist = scratch; wsum = scratch + 256; sel = scratch + 320;
+        C = C_; R = R_; burst = burst_; kept = 0;
+        if (threadIdx.x == 0) { *cnt = 0; *thr = VDB_KEY_MAX; }
+        // caller must __syncthreads()
+    }
+    __device__ __forceinline__ void push(u64 key) {
+        if (key < *thr) {
+            const int p = atomicAdd(cnt, 1);
+            buf[kept + p] = key;
+        }
+    }
+    __device__ __forceinline__ void maybe_compact() {
+        const int pending = *(volatile int*)cnt;
+        if (__syncthreads_or(kept + pending + burst > C)) compact_after_barrier();
+    }
+    // the key with exactly `rank` keys <= it among buf[0, n); CTA-uniform result
+    __device__ __forceinline__ u64 radix_select(int n, int rank) {
+        const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+        u64 prefix = 0;
+        for (int shift = 56; shift >= 0; shift -= 8) {
+            for (int b = tid; b < 256; b += blockDim.x) hist[b] = 0;
+            __syncthreads();
+            const u64 himask = shift == 56 ? 0ull : (~0ull << (shift + 8));
+            for (int base = 0; base < n; base += blockDim.x) {      // uniform trip count: every lane reaches the match
+                const int i = base + tid;
+                int digit = -1;
+                if (i < n) {
+                    const u64 key = buf[i];
+                    if ((key & himask) == prefix) digit = (int)((key >> shift) & 255u);
+                }
+                const unsigned peers = __match_any_sync(0xFFFFFFFFu, digit);
+                if (digit >= 0 && lane == __ffs(peers) - 1) atomicAdd(&hist[digit], __popc(peers));
+            }
+            __syncthreads();
+            int v = 0, incl = 0;
+            if (tid < 256) {
+                v = hist[tid];
+                incl = v;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const int t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+                    if (lane >= o) incl += t;
+                }
+                if (lane == 31) wsum[warp] = incl;
+            }
+            __syncthreads();
+            if (tid < 256) {
+                int off = 0;
+                for (int w = 0; w < warp; ++w) off += wsum[w];
+                incl += off;
+                if (incl - v < rank && rank <= incl) { sel[0] = tid; sel[1] = rank - (incl - v); }
+            }
+            __syncthreads();
+            prefix |= (u64)(unsigned)sel[0] << shift;
+            rank = sel[1];
+        }
+        return prefix;
+    }
+    // requires: a barrier since the last push
+    __device__ __forceinline__ void compact_after_barrier() {
+        const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = blockDim.x >> 5;
+        const int n = kept + *(volatile int*)cnt;
+        if (n <= R) {                                  // nothing to drop (only finalize() gets here)
+            __syncthreads();
+            kept = n;
+            if (tid == 0) *cnt = 0;
+            __syncthreads();
+            return;
+        }
+        const u64 kth = radix_select(n, R);
+        // stable compaction, one round of blockDim keys per barrier: a round writes only below its own end, and
+        // its own keys are in registers by the barrier
+        int out = 0, round = 0;
+        for (int base = 0; base < n; base += blockDim.x, ++round) {
+            const int i = base + tid;
+            const u64 key = i < n ? buf[i] : VDB_KEY_MAX;
+            const bool keep = key <= kth;
+            const unsigned bal = __ballot_sync(0xFFFFFFFFu, keep);
+            int* ws = wsum + (round & 1) * 32;
+            if (lane == 0) ws[warp] = __popc(bal);
+            __syncthreads();
+            int off = out, total = 0;
+            for (int w = 0; w < nw; ++w) { const int c = ws[w]; total += c; if (w < warp) off += c; }
+            if (keep) buf[off + __popc(bal & ((1u << lane) - 1u))] = key;
+            out += total;
+        }
+        kept = R;                                      // unique keys: exactly R survive
+        if (tid == 0) { *cnt = 0; *thr = kth; }
+        __syncthreads();
+    }
+    // leaves the min(R, seen) best keys in buf[0, kept), unordered, and VDB_KEY_MAX in buf[kept, fill_to)
+    __device__ __forceinline__ void finalize(int fill_to) {
+        __syncthreads();
+        compact_after_barrier();
+        for (int i = kept + threadIdx.x; i < fill_to; i += blockDim.x) buf[i] = VDB_KEY_MAX;
+        __syncthreads();
+    }
+};
+
 __host__ __device__ __forceinline__ int select_capacity(int R, int burst) {
     int c = next_pow2(R + 2 * burst);
     return c < 256 ? 256 : c;

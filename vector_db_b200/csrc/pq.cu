@@ -502,6 +502,7 @@ ivf_adc_scan_kernel(const uint8_t* __restrict__ codes, int m, const uint32_t* __
     int32_t* pbase = prefix + n_probe + 1;                                      // n_probe
     __shared__ int cnt;
     __shared__ u64 thr;
+    __shared__ int scratch[kSelectRadixScratch];
     const int tid = threadIdx.x, rot = tid & 7;
     for (int i = tid; i < mb * 2048; i += kIvfAdcThreads) {
         const int j = i >> 8, c = i & 255;
@@ -509,8 +510,9 @@ ivf_adc_scan_kernel(const uint8_t* __restrict__ codes, int m, const uint32_t* __
     }
     for (int p = tid; p <= n_probe; p += kIvfAdcThreads) prefix[p] = prefix_g[(size_t)qi * (n_probe + 1) + p];
     for (int p = tid; p < n_probe; p += kIvfAdcThreads) pbase[p] = list_ptr[probes[(size_t)qi * n_probe + p]];
-    BlockSelect sel;
-    sel.init(buf, &cnt, &thr, C, R, kIvfAdcThreads);
+    // a shortlist is large next to the CTA's candidates: select by radix, never sort (the keys leave unordered)
+    BlockSelectRadix sel;
+    sel.init(buf, &cnt, &thr, scratch, C, R, kIvfAdcThreads);
     __syncthreads();
     const int begin = s * chunk, end = min(total, begin + chunk);
     for (int base = begin; base < end; base += kIvfAdcThreads) {
@@ -524,7 +526,7 @@ ivf_adc_scan_kernel(const uint8_t* __restrict__ codes, int m, const uint32_t* __
         }
         sel.maybe_compact();
     }
-    sel.finalize();
+    sel.finalize(R);
     u64* dst = partial + ((size_t)qi * kIvfAdcSplits + s) * R;
     for (int i = tid; i < R; i += kIvfAdcThreads) dst[i] = buf[i];
 }
@@ -533,27 +535,34 @@ ivf_adc_scan_kernel(const uint8_t* __restrict__ codes, int m, const uint32_t* __
 __global__ void __launch_bounds__(256)
 ivf_adc_merge_kernel(const u64* __restrict__ partial, int L, int R, int C, const int32_t* __restrict__ expo,
                      const int32_t* __restrict__ list_ptr, const int32_t* __restrict__ list_rows,
-                     const int32_t* __restrict__ probes, const int32_t* __restrict__ prefix_g, int n_probe,
+                     const int32_t* __restrict__ probes, const int32_t* __restrict__ prefix_g, int n_probe, int chunk_min,
                      float* __restrict__ out_d, int32_t* __restrict__ out_rows) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     u64* buf = reinterpret_cast<u64*>(smem_raw);
     __shared__ int cnt;
     __shared__ u64 thr;
+    __shared__ int scratch[kSelectRadixScratch];
     const int qi = blockIdx.x;
-    BlockSelect sel;
-    sel.init(buf, &cnt, &thr, C, R, blockDim.x);
+    const int32_t* prefix = prefix_g + (size_t)qi * (n_probe + 1);
+    // the splits that ran (the same chunk rule as the scan); the others never wrote their slots
+    const int total = __ldg(prefix + n_probe);
+    const int chunk = max(chunk_min, (total + kIvfAdcSplits - 1) / kIvfAdcSplits);
+    const int live = min(L, ((total + chunk - 1) / chunk) * R);
+    BlockSelectRadix sel;
+    sel.init(buf, &cnt, &thr, scratch, C, R, blockDim.x);
     __syncthreads();
     const u64* src = partial + (size_t)qi * L;
-    for (int base = 0; base < L; base += blockDim.x) {
+    for (int base = 0; base < live; base += blockDim.x) {
         const int i = base + threadIdx.x;
-        if (i < L) {
+        if (i < live) {
             const u64 key = src[i];
             if (key != VDB_KEY_MAX) sel.push(key);
         }
         sel.maybe_compact();
     }
-    sel.finalize();
-    const int32_t* prefix = prefix_g + (size_t)qi * (n_probe + 1);
+    const int P = next_pow2(R);                       // <= C
+    sel.finalize(P);
+    block_bitonic_sort(buf, P);                       // the result rows leave in ascending ADC distance
     const int e = expo[qi];
     for (int i = threadIdx.x; i < R; i += blockDim.x) {
         const u64 key = buf[i];
@@ -955,7 +964,6 @@ int vdb_ivf_adc_scan(const uint8_t* codes, int m, const float* lut, int Q, const
     int32_t* expo = reinterpret_cast<int32_t*>(base + adc_lutq_bytes(Q, m));
     u64* partial = reinterpret_cast<u64*>(base + head);
     adc_quantize_lut_kernel<<<Q, 256, 0, st>>>(lut, m * 256, lutq, expo);
-    VDB_CUDA(cudaMemsetAsync(partial, 0xFF, (size_t)Q * kIvfAdcSplits * R * 8, st));
     const int mb = (m + 7) / 8;
     const int C = select_capacity(R, kIvfAdcThreads);
     const size_t smem = (size_t)C * 8 + (size_t)mb * 2048 * 4 + (size_t)(2 * n_probe + 1) * 4;
@@ -983,7 +991,7 @@ int vdb_ivf_adc_scan(const uint8_t* codes, int m, const float* lut, int Q, const
     const int C2 = select_capacity(R, 256);
     VDB_CUDA(cudaFuncSetAttribute(ivf_adc_merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, C2 * 8));
     ivf_adc_merge_kernel<<<Q, 256, (size_t)C2 * 8, st>>>(partial, kIvfAdcSplits * R, R, C2, expo, list_ptr, list_rows, probes,
-                                                         prefix, n_probe, out_d, out_rows);
+                                                         prefix, n_probe, chunk_min, out_d, out_rows);
     count_launch(3);
     VDB_CUDA(cudaGetLastError());
     return VDB_OK;
