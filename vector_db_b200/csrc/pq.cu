@@ -262,36 +262,56 @@ struct AdcArgs {
 
 // d_int of one row for the G queries of the group: 128-bit code loads, rotated conflict-free lookups.
 // MB = m/8 when m is a multiple of 8 and small enough to unroll, 0 = generic (any m, byte loads).
+// the row's code bytes as 2*MB words (MB > 0 only): 128-bit streaming loads when MB is even
+// STREAM: bypass L1 (the full scan reads every code once per CTA).  A lane's 16-byte pieces sit 8*MB bytes apart, so
+// each load instruction touches a 32-byte sector per lane for 16 useful bytes; without L1 the IVF-PQ scan (one
+// query per CTA: four times the code traffic per lookup of the grouped full scan) moved twice its code bytes out
+// of L2 and ran at the L2's pace.
+template <int MB, bool STREAM = true>
+__device__ __forceinline__ void adc_load_codes(const uint8_t* __restrict__ prow, uint32_t (&w)[MB > 0 ? 2 * MB : 2]) {
+    if ((MB & 1) == 0) {
+        const uint4* p = reinterpret_cast<const uint4*>(prow);
+#pragma unroll
+        for (int i = 0; i < MB / 2; ++i) {
+            const uint4 v = STREAM ? ld_stream_u4(p + i) : __ldg(p + i);
+            w[4 * i] = v.x; w[4 * i + 1] = v.y; w[4 * i + 2] = v.z; w[4 * i + 3] = v.w;
+        }
+    } else {
+        const uint2* p = reinterpret_cast<const uint2*>(prow);
+#pragma unroll
+        for (int i = 0; i < MB; ++i) { const uint2 v = __ldg(p + i); w[2 * i] = v.x; w[2 * i + 1] = v.y; }
+    }
+}
+
+// P = copies of every LUT row interleaved in shared memory (slot (b, c, copy) at ((b*256 + c)*P + copy)*8 + j');
+// the caller passes lutS already advanced to its own copy
+template <int G, int MB, int P = 1>
+__device__ __forceinline__ void adc_sum_codes(const uint32_t (&w)[MB > 0 ? 2 * MB : 2], const uint32_t* lutS, int rot,
+                                              uint32_t (&acc)[G]) {
+#pragma unroll
+    for (int g = 0; g < G; ++g) acc[g] = 0u;
+#pragma unroll
+    for (int b = 0; b < MB; ++b) {
+        uint32_t lo = w[2 * b], hi = w[2 * b + 1];
+        rotr_bytes(lo, hi, rot);                         // byte t of (lo,hi) is now sub-space (t + rot) & 7
+#pragma unroll
+        for (int t = 0; t < 8; ++t) {
+            const uint32_t c = ((t < 4 ? lo : hi) >> (8 * (t & 3))) & 0xFFu;
+            lut_add<G>(acc, lutS, (uint32_t)(b * 2048 * P) + c * (uint32_t)(8 * P) + (uint32_t)((t + rot) & 7));
+        }
+    }
+}
+
 template <int G, int MB>
 __device__ __forceinline__ void adc_row(const uint8_t* __restrict__ prow, int m, int mb, const uint32_t* lutS, int rot,
                                         uint32_t (&acc)[G]) {
-#pragma unroll
-    for (int g = 0; g < G; ++g) acc[g] = 0u;
     if (MB > 0) {
         uint32_t w[MB > 0 ? 2 * MB : 2];
-        if ((MB & 1) == 0) {
-            const uint4* p = reinterpret_cast<const uint4*>(prow);
-#pragma unroll
-            for (int i = 0; i < MB / 2; ++i) {
-                const uint4 v = ld_stream_u4(p + i);
-                w[4 * i] = v.x; w[4 * i + 1] = v.y; w[4 * i + 2] = v.z; w[4 * i + 3] = v.w;
-            }
-        } else {
-            const uint2* p = reinterpret_cast<const uint2*>(prow);
-#pragma unroll
-            for (int i = 0; i < MB; ++i) { const uint2 v = __ldg(p + i); w[2 * i] = v.x; w[2 * i + 1] = v.y; }
-        }
-#pragma unroll
-        for (int b = 0; b < MB; ++b) {
-            uint32_t lo = w[2 * b], hi = w[2 * b + 1];
-            rotr_bytes(lo, hi, rot);                         // byte t of (lo,hi) is now sub-space (t + rot) & 7
-#pragma unroll
-            for (int t = 0; t < 8; ++t) {
-                const uint32_t c = ((t < 4 ? lo : hi) >> (8 * (t & 3))) & 0xFFu;
-                lut_add<G>(acc, lutS, (uint32_t)(b * 2048) + c * 8u + (uint32_t)((t + rot) & 7));
-            }
-        }
+        adc_load_codes<MB>(prow, w);
+        adc_sum_codes<G, MB>(w, lutS, rot, acc);
     } else {
+#pragma unroll
+        for (int g = 0; g < G; ++g) acc[g] = 0u;
         for (int b = 0; b < mb; ++b) {
             for (int t = 0; t < 8; ++t) {
                 const int jj = (t + rot) & 7, j = b * 8 + jj;
@@ -470,9 +490,14 @@ adc_finalize_kernel(const AdcFinArgs a) {
 // IVF-PQ: ADC restricted to the probed inverted lists.  Codes are stored LIST-MAJOR
 // (code of CSR position p at codes[p*m]), so a list is one contiguous byte run.  grid (kIvfAdcSplits, Q):
 // CTA (s, q) evaluates candidates [s*chunk, (s+1)*chunk) of query q's flattened candidate sequence (probe
-// rank major, list position minor, as ivf.cu), with the query's fixed-point LUT in shared memory in the
-// rotated conflict-free slot order of the full scan.  Keys are (d_int, sequence number).
-constexpr int kIvfAdcThreads = 256;
+// rank major, list position minor, as ivf.cu), with the query's fixed-point LUT in shared memory.  Keys are
+// (d_int, sequence number).
+// LUT layout: one query per CTA means 32-bit lookups, and with the rotated slot order of the full scan alone
+// (bank = (c mod 4)*8 + j', 8 rotations for 32 lanes) the four lanes of a rotation class collide whenever their
+// codes agree mod 4: ~3 wavefronts per lookup, and the kernel ran at the shared-memory pipe's limit.  P = 4
+// keeps FOUR copies of every row, lane l reads copy (l >> 3) & 3: bank = copy*8 + j', conflict-free whatever
+// the codes.  4 x 48 KB at m = 48 leaves one CTA per SM, so that variant runs 1024 threads; P = 1 / 256 threads
+// is the fallback when the copies do not fit.
 constexpr int kIvfAdcSplits = 32;
 
 __device__ __forceinline__ int adc_find_probe(const int32_t* prefix, int n, int seq) {
@@ -484,51 +509,80 @@ __device__ __forceinline__ int adc_find_probe(const int32_t* prefix, int n, int 
     return lo;
 }
 
-template <int MB>
-__global__ void __launch_bounds__(kIvfAdcThreads)
+template <int MB, int P>
+__global__ void __launch_bounds__(P == 4 ? 1024 : 256)
 ivf_adc_scan_kernel(const uint8_t* __restrict__ codes, int m, const uint32_t* __restrict__ lutq,
                     const int32_t* __restrict__ list_ptr, const int32_t* __restrict__ probes,
                     const int32_t* __restrict__ prefix_g, int n_probe, int R, int C, int chunk_min,
                     u64* __restrict__ partial) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    const int qi = blockIdx.y, s = blockIdx.x;
+    const int qi = blockIdx.y, s = blockIdx.x, nt = blockDim.x;
     const int total = __ldg(prefix_g + (size_t)qi * (n_probe + 1) + n_probe);
     const int chunk = max(chunk_min, (total + kIvfAdcSplits - 1) / kIvfAdcSplits);
     if (s * chunk >= total) return;
     const int mb = (m + 7) >> 3;
     u64* buf = reinterpret_cast<u64*>(smem_raw);                                // C
-    uint32_t* lutS = reinterpret_cast<uint32_t*>(buf + C);                      // mb * 2048
-    int32_t* prefix = reinterpret_cast<int32_t*>(lutS + (size_t)mb * 2048);     // n_probe + 1
+    uint32_t* lutS = reinterpret_cast<uint32_t*>(buf + C);                      // mb * 2048 * P
+    int32_t* prefix = reinterpret_cast<int32_t*>(lutS + (size_t)mb * 2048 * P); // n_probe + 1
     int32_t* pbase = prefix + n_probe + 1;                                      // n_probe
     __shared__ int cnt;
     __shared__ u64 thr;
     __shared__ int scratch[kSelectRadixScratch];
     const int tid = threadIdx.x, rot = tid & 7;
-    for (int i = tid; i < mb * 2048; i += kIvfAdcThreads) {
-        const int j = i >> 8, c = i & 255;
-        lutS[((j >> 3) * 256 + c) * 8 + (j & 7)] = j < m ? lutq[((size_t)qi * m + j) * 256 + c] : 0u;
+    // a warp stages 8 sub-spaces x 4 consecutive codes: 16-byte runs from global, 32 distinct banks per store
+    for (int i = tid; i < mb * 2048; i += nt) {
+        const int jj = i & 7, c = (i >> 3) & 255, b = i >> 11, j = b * 8 + jj;
+        const uint32_t v = j < m ? __ldg(lutq + ((size_t)qi * m + j) * 256 + c) : 0u;
+#pragma unroll
+        for (int k = 0; k < P; ++k) {
+            const int copy = (c + k) & (P - 1);
+            lutS[(((b * 256 + c) * P + copy) << 3) + jj] = v;
+        }
     }
-    for (int p = tid; p <= n_probe; p += kIvfAdcThreads) prefix[p] = prefix_g[(size_t)qi * (n_probe + 1) + p];
-    for (int p = tid; p < n_probe; p += kIvfAdcThreads) pbase[p] = list_ptr[probes[(size_t)qi * n_probe + p]];
+    for (int p = tid; p <= n_probe; p += nt) prefix[p] = prefix_g[(size_t)qi * (n_probe + 1) + p];
+    for (int p = tid; p < n_probe; p += nt) pbase[p] = list_ptr[probes[(size_t)qi * n_probe + p]];
     // a shortlist is large next to the CTA's candidates: select by radix, never sort (the keys leave unordered)
     BlockSelectRadix sel;
-    sel.init(buf, &cnt, &thr, scratch, C, R, kIvfAdcThreads);
+    sel.init(buf, &cnt, &thr, scratch, C, R, nt);
     __syncthreads();
+    const uint32_t* lutL = lutS + ((tid >> 3) & (P - 1)) * 8;                   // this lane's copy
     const int begin = s * chunk, end = min(total, begin + chunk);
-    for (int base = begin; base < end; base += kIvfAdcThreads) {
-        const int seq = base + tid;
-        if (seq < end) {
-            const int p = adc_find_probe(prefix, n_probe, seq);
-            const int64_t pos = (int64_t)pbase[p] + (seq - prefix[p]);
-            uint32_t acc[1];
-            adc_row<1, MB>(codes + pos * m, m, mb, lutS, rot, acc);
-            sel.push(((u64)acc[0] << 32) | (u64)(uint32_t)seq);
+    auto row_of = [&](int seq) -> const uint8_t* {
+        const int p = adc_find_probe(prefix, n_probe, seq);
+        return codes + ((int64_t)pbase[p] + (seq - prefix[p])) * m;
+    };
+    if (MB > 0) {
+        // the codes of the NEXT batch are in flight while this one is summed (one CTA per SM at P = 4: nothing else
+        // would cover the load latency behind the selection's CTA-wide barrier)
+        uint32_t wn[MB > 0 ? 2 * MB : 2];
+        if (begin + tid < end) adc_load_codes<MB, false>(row_of(begin + tid), wn);
+        for (int base = begin; base < end; base += nt) {
+            const int seq = base + tid;
+            uint32_t w[MB > 0 ? 2 * MB : 2];
+#pragma unroll
+            for (int i = 0; i < (MB > 0 ? 2 * MB : 2); ++i) w[i] = wn[i];
+            if (seq + nt < end) adc_load_codes<MB, false>(row_of(seq + nt), wn);
+            if (seq < end) {
+                uint32_t acc[1];
+                adc_sum_codes<1, MB, P>(w, lutL, rot, acc);
+                sel.push(((u64)acc[0] << 32) | (u64)(uint32_t)seq);
+            }
+            sel.maybe_compact();
         }
-        sel.maybe_compact();
+    } else {
+        for (int base = begin; base < end; base += nt) {
+            const int seq = base + tid;
+            if (seq < end) {
+                uint32_t acc[1];
+                adc_row<1, MB>(row_of(seq), m, mb, lutS, rot, acc);
+                sel.push(((u64)acc[0] << 32) | (u64)(uint32_t)seq);
+            }
+            sel.maybe_compact();
+        }
     }
     sel.finalize(R);
     u64* dst = partial + ((size_t)qi * kIvfAdcSplits + s) * R;
-    for (int i = tid; i < R; i += kIvfAdcThreads) dst[i] = buf[i];
+    for (int i = tid; i < R; i += nt) dst[i] = buf[i];
 }
 
 // R best (d_int, sequence) keys of the splits -> (float(d_int) * 2^-e, row).  One CTA per query.
@@ -965,18 +1019,28 @@ int vdb_ivf_adc_scan(const uint8_t* codes, int m, const float* lut, int Q, const
     u64* partial = reinterpret_cast<u64*>(base + head);
     adc_quantize_lut_kernel<<<Q, 256, 0, st>>>(lut, m * 256, lutq, expo);
     const int mb = (m + 7) / 8;
-    const int C = select_capacity(R, kIvfAdcThreads);
-    const size_t smem = (size_t)C * 8 + (size_t)mb * 2048 * 4 + (size_t)(2 * n_probe + 1) * 4;
-    VDB_REQUIRE(smem <= (size_t)max_smem_optin() - 1024, VDB_ERR_UNSUPPORTED, "m=%d R=%d n_probe=%d do not fit shared memory",
-                m, R, n_probe);
-    const int chunk_min = Q >= 1024 ? 16384 : (Q >= 128 ? 4096 : 1024);
     const bool a16 = (reinterpret_cast<uintptr_t>(codes) & 15) == 0, a8 = (reinterpret_cast<uintptr_t>(codes) & 7) == 0;
+    const bool unrolled = (a16 && (m == 16 || m == 32 || m == 48 || m == 64)) || (a8 && m == 8);
+    const size_t tail = (size_t)(2 * n_probe + 1) * 4, smem_cap = (size_t)max_smem_optin() - 3072;   // static shared: 2.3 KB
+    // four LUT copies + 1024 threads when they fit next to the selection buffer (radix select: any C >= R + 2 bursts)
+    const size_t smem4 = (size_t)(R + 2 * 1024) * 8 + (size_t)mb * 2048 * 4 * 4 + tail;
+    const bool four = unrolled && smem4 <= smem_cap;
+    const int threads = four ? 1024 : 256;
+    const int C = four ? R + 2 * 1024 : select_capacity(R, 256);
+    const size_t smem = four ? smem4 : (size_t)C * 8 + (size_t)mb * 2048 * 4 + tail;
+    VDB_REQUIRE(smem <= smem_cap, VDB_ERR_UNSUPPORTED, "m=%d R=%d n_probe=%d do not fit shared memory", m, R, n_probe);
+    // candidates per CTA: the LUT staging (48 KB read, up to 192 KB written) is paid once per CTA
+    const int chunk_min = Q >= 1024 ? 65536 : (Q >= 128 ? 16384 : 2048);
+#define VDB_IVFADC_LAUNCH(MBV, PV)                                                                              \
+    {                                                                                                           \
+        auto kern = ivf_adc_scan_kernel<MBV, PV>;                                                               \
+        VDB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));           \
+        kern<<<dim3(kIvfAdcSplits, Q), threads, smem, st>>>(codes, m, lutq, list_ptr, probes, prefix, n_probe, R, C, \
+                                                            chunk_min, partial);                                \
+    }
 #define VDB_IVFADC_CASE(MBV)                                                                                    \
     {                                                                                                           \
-        auto kern = ivf_adc_scan_kernel<MBV>;                                                                   \
-        VDB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));           \
-        kern<<<dim3(kIvfAdcSplits, Q), kIvfAdcThreads, smem, st>>>(codes, m, lutq, list_ptr, probes, prefix, n_probe, R, C, \
-                                                                   chunk_min, partial);                         \
+        if (four) VDB_IVFADC_LAUNCH(MBV, 4) else VDB_IVFADC_LAUNCH(MBV, 1)                                      \
     }
     {
         ProfScope prof(kProfAdcScan, st);
@@ -985,8 +1049,9 @@ int vdb_ivf_adc_scan(const uint8_t* codes, int m, const float* lut, int Q, const
         else if (a16 && m == 48) VDB_IVFADC_CASE(6)
         else if (a16 && m == 64) VDB_IVFADC_CASE(8)
         else if (a8 && m == 8) VDB_IVFADC_CASE(1)
-        else VDB_IVFADC_CASE(0)
+        else VDB_IVFADC_LAUNCH(0, 1)
     }
+#undef VDB_IVFADC_LAUNCH
 #undef VDB_IVFADC_CASE
     const int C2 = select_capacity(R, 256);
     VDB_CUDA(cudaFuncSetAttribute(ivf_adc_merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, C2 * 8));
