@@ -175,7 +175,7 @@ struct BlockSelect {
 // the front with a stable in-place compaction.  buf[0, kept) holds the survivors in NO particular order.
 // Requirements: keys unique and < VDB_KEY_MAX; blockDim.x a multiple of 32, >= 256 and <= 1024; `scratch` =
 // kSelectRadixScratch ints of shared memory.
-constexpr int kSelectRadixScratch = 256 + 64 + 2;
+constexpr int kSelectRadixScratch = 256 + 64 + 2 + 1;
 
 struct BlockSelectRadix {
     u64* buf;
@@ -184,19 +184,34 @@ struct BlockSelectRadix {
     int* hist;    // 256 bins
     int* wsum;    // 2 x 32 warp totals
     int* sel;     // chosen bin, rank inside it
+    int* flag;    // barrier-free protocol: raised by a pusher when the pending area is within one burst of full
     int C, R, burst;
     int kept;     // CTA-uniform: keys at the front of buf (0 until the first compaction, then R)
 
     __device__ __forceinline__ void init(u64* b, int* c, u64* t, int* scratch, int C_, int R_, int burst_) {
         buf = b; cnt = c; thr = t; hist = scratch; wsum = scratch + 256; sel = scratch + 320;
+        flag = scratch + 322;
         C = C_; R = R_; burst = burst_; kept = 0;
-        if (threadIdx.x == 0) { *cnt = 0; *thr = VDB_KEY_MAX; }
+        if (threadIdx.x == 0) { *cnt = 0; *thr = VDB_KEY_MAX; *flag = 0; }
         // caller must __syncthreads()
     }
     __device__ __forceinline__ void push(u64 key) {
         if (key < *thr) {
             const int p = atomicAdd(cnt, 1);
             buf[kept + p] = key;
+        }
+    }
+    // Barrier-free variant (burst = blockDim.x, C >= R + 2 * burst): every thread polls flag_raised() before EACH
+    // push_flagging() and, once it sees the flag, pushes nothing more until the CTA has met at a barrier and run
+    // compact_after_barrier().  A thread whose slot lies at or past the trigger raises the flag itself, so it
+    // pushes at most once after the trigger slot was taken: at most burst - 1 slots follow the trigger and the
+    // buffer cannot overflow.  The threads need not be at the same batch when they meet.
+    __device__ __forceinline__ bool flag_raised() const { return *(volatile int*)flag != 0; }
+    __device__ __forceinline__ void push_flagging(u64 key) {
+        if (key < *(volatile u64*)thr) {
+            const int p = atomicAdd(cnt, 1);
+            buf[kept + p] = key;
+            if (kept + p + 1 + burst >= C) *(volatile int*)flag = 1;
         }
     }
     __device__ __forceinline__ void maybe_compact() {
@@ -253,7 +268,7 @@ struct BlockSelectRadix {
         if (n <= R) {                                  // nothing to drop (only finalize() gets here)
             __syncthreads();
             kept = n;
-            if (tid == 0) *cnt = 0;
+            if (tid == 0) { *cnt = 0; *flag = 0; }
             __syncthreads();
             return;
         }
@@ -275,7 +290,7 @@ struct BlockSelectRadix {
             out += total;
         }
         kept = R;                                      // unique keys: exactly R survive
-        if (tid == 0) { *cnt = 0; *thr = kth; }
+        if (tid == 0) { *cnt = 0; *thr = kth; *flag = 0; }
         __syncthreads();
     }
     // leaves the min(R, seen) best keys in buf[0, kept), unordered, and VDB_KEY_MAX in buf[kept, fill_to)

@@ -551,36 +551,37 @@ ivf_adc_scan_kernel(const uint8_t* __restrict__ codes, int m, const uint32_t* __
         const int p = adc_find_probe(prefix, n_probe, seq);
         return codes + ((int64_t)pbase[p] + (seq - prefix[p])) * m;
     };
-    if (MB > 0) {
-        // the codes of the NEXT batch are in flight while this one is summed (one CTA per SM at P = 4: nothing else
-        // would cover the load latency behind the selection's CTA-wide barrier)
-        uint32_t wn[MB > 0 ? 2 * MB : 2];
-        if (begin + tid < end) adc_load_codes<MB, false>(row_of(begin + tid), wn);
-        for (int base = begin; base < end; base += nt) {
+    // No barrier per batch: the warps drift apart (their load, lookup and push phases then overlap instead of
+    // hitting the same pipe together) and meet only when a pusher raises the selection's flag or the candidates
+    // run out; a thread that is done keeps attending the meetings until every thread is.
+    // The codes of the NEXT batch are in flight while this one is summed (one CTA per SM at P = 4).
+    uint32_t wn[MB > 0 ? 2 * MB : 2];
+    if (MB > 0 && begin + tid < end) adc_load_codes<MB, false>(row_of(begin + tid), wn);
+    int base = begin;
+    bool done = false;
+    while (true) {
+        while (!done && !sel.flag_raised()) {
             const int seq = base + tid;
-            uint32_t w[MB > 0 ? 2 * MB : 2];
+            uint32_t acc[1];
+            if (MB > 0) {
+                uint32_t w[MB > 0 ? 2 * MB : 2];
 #pragma unroll
-            for (int i = 0; i < (MB > 0 ? 2 * MB : 2); ++i) w[i] = wn[i];
-            if (seq + nt < end) adc_load_codes<MB, false>(row_of(seq + nt), wn);
-            if (seq < end) {
-                uint32_t acc[1];
-                adc_sum_codes<1, MB, P>(w, lutL, rot, acc);
-                sel.push(((u64)acc[0] << 32) | (u64)(uint32_t)seq);
-            }
-            sel.maybe_compact();
-        }
-    } else {
-        for (int base = begin; base < end; base += nt) {
-            const int seq = base + tid;
-            if (seq < end) {
-                uint32_t acc[1];
+                for (int i = 0; i < (MB > 0 ? 2 * MB : 2); ++i) w[i] = wn[i];
+                if (seq + nt < end) adc_load_codes<MB, false>(row_of(seq + nt), wn);
+                if (seq < end) adc_sum_codes<1, MB, P>(w, lutL, rot, acc);
+            } else if (seq < end) {
                 adc_row<1, MB>(row_of(seq), m, mb, lutS, rot, acc);
-                sel.push(((u64)acc[0] << 32) | (u64)(uint32_t)seq);
             }
-            sel.maybe_compact();
+            if (seq < end) sel.push_flagging(((u64)acc[0] << 32) | (u64)(uint32_t)seq);
+            base += nt;
+            done = base >= end;
         }
+        __syncthreads();
+        sel.compact_after_barrier();
+        if (__syncthreads_and(done)) break;
     }
-    sel.finalize(R);
+    for (int i = sel.kept + tid; i < R; i += nt) buf[i] = VDB_KEY_MAX;
+    __syncthreads();
     u64* dst = partial + ((size_t)qi * kIvfAdcSplits + s) * R;
     for (int i = tid; i < R; i += nt) dst[i] = buf[i];
 }
