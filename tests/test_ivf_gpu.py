@@ -177,7 +177,8 @@ def test_reference_contract_errors_stats_persistence(tmp_path):
 @pytest.mark.parametrize("n,dim,K,m,n_probe,nq,R", [(6000, 64, 24, 8, 4, 40, 50), (4000, 48, 10, 16, 10, 9, 300),
                                                    (3000, 40, 8, 5, 3, 7, 20),
                                                    (40000, 32, 6, 4, 6, 5, 1000),   # several radix compactions per CTA
-                                                   (3000, 128, 6, 64, 3, 6, 40)])   # m = 64: one LUT copy, 256 threads
+                                                   (3000, 128, 6, 64, 3, 6, 40),    # m = 64: one LUT copy, 256 threads
+                                                   (300, 32, 8, 4, 2, 5, 200)])     # fewer candidates than the shortlist
 def test_ivf_pq_scan_vs_oracle(n, dim, K, m, n_probe, nq, R):
     """IVF-PQ shortlist = fixed-point ADC over the probed lists in enumeration order; rerank = exact L2."""
     from vector_db_b200 import ops
