@@ -547,9 +547,12 @@ ivf_adc_scan_kernel(const uint8_t* __restrict__ codes, int m, const uint32_t* __
     __syncthreads();
     const uint32_t* lutL = lutS + ((tid >> 3) & (P - 1)) * 8;                   // this lane's copy
     const int begin = s * chunk, end = min(total, begin + chunk);
+    // a thread's sequence numbers only grow, and lists are long next to the batch: the probe of the previous row is
+    // almost always the probe of the next one (one compare instead of a binary search per row)
+    int pcur = adc_find_probe(prefix, n_probe, min(begin + tid, total - 1));
     auto row_of = [&](int seq) -> const uint8_t* {
-        const int p = adc_find_probe(prefix, n_probe, seq);
-        return codes + ((int64_t)pbase[p] + (seq - prefix[p])) * m;
+        while (seq >= prefix[pcur + 1]) ++pcur;          // seq < total = prefix[n_probe]
+        return codes + ((int64_t)pbase[pcur] + (seq - prefix[pcur])) * m;
     };
     // No barrier per batch: the warps drift apart (their load, lookup and push phases then overlap instead of
     // hitting the same pipe together) and meet only when a pusher raises the selection's flag or the candidates
