@@ -57,6 +57,7 @@ for metric in ("cosine", "l2"):
     timed(metric, mir, mx, 1 | (3 << 8))      # same with a 3-deep TMA ring
     timed(metric, mir, mx, 2)      # + TMEM loads and bin minima, no threshold test / inserts
     timed(metric, mir, mx, 4)      # full epilogue, 16-entry bin lists
+    timed(metric, mir, mx, 8)      # full epilogue without the threshold exchange between the two groups
     D_tc, I_tc, nbad = timed(metric, mir, mx, 0)
     ns = min(Q, 128)
     Dr, Ir = ops.exact_topk_f32(Qd[:ns], X, K, metric)

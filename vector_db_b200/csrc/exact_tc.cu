@@ -43,7 +43,7 @@ constexpr int kA2Bytes = kTileM * 32;            // 4 KB: the L2 norm block of t
 constexpr int kB2Bytes = kTileN * 32;            // 8 KB: the L2 norm block of one row tile
 
 struct TcSmemLayout {
-    int a_off, a2_off, b2_off, b_off, bar_off, total;
+    int a_off, a2_off, b2_off, b_off, bar_off, tau_off, total;
 };
 
 // has_norm: the L2 operands carry a 16-column norm block (|x|^2 split / ones) after the D data columns;
@@ -55,7 +55,8 @@ __host__ __device__ inline TcSmemLayout tc_layout(int num_kb, int stages, int ha
     L.b2_off = L.a2_off + (has_norm ? kA2Bytes : 0);
     L.b_off = L.b2_off + (has_norm ? 2 * kB2Bytes : 0);
     L.bar_off = L.b_off + stages * kBBytes;
-    L.total = L.bar_off + (2 * kMaxStages + 12) * 8 + 16;
+    L.tau_off = L.bar_off + (2 * kMaxStages + 12) * 8 + 16;
+    L.total = L.tau_off + kGroups * kTileM * 4;                 // threshold exchange between the two epilogue groups
     return L;
 }
 
@@ -103,6 +104,21 @@ __device__ __forceinline__ void chunk_minima(float (&v)[32], int n_valid, float 
     m[0] = min8(v); m[1] = min8(v + 8); m[2] = min8(v + 16); m[3] = min8(v + 24);
 }
 
+// Threshold exchange between the two epilogue groups of a CTA (same query row, other half of the columns): a bin
+// that cannot enter the PARTNER's full list cannot enter the merged selection either (select_bins_kernel takes
+// tau from the worst entry of every full list), so each group tests against min(own tau, partner's tau) and
+// inserts ~45 % less often -- and an insert by ONE lane sends its whole warp through the insert code.
+// The word carries the unit counter mod 4 in its two low bits (the groups are at most two tiles, hence at most two
+// units, apart) and the ordered threshold rounded UP to a multiple of 4: a stale or foreign word reads as +inf.
+__device__ __forceinline__ uint32_t tau_word(float tau, int ui) {
+    uint32_t u = f32_to_ordered(tau) + 4u;
+    if (u > 0xFF800000u) u = 0xFF800000u;                       // +inf stays +inf
+    return (u & ~3u) | (uint32_t)(ui & 3);
+}
+__device__ __forceinline__ float tau_of_word(uint32_t w, int ui) {
+    return ((w & 3u) == (uint32_t)(ui & 3)) ? ordered_to_f32(w & ~3u) : INFINITY;
+}
+
 // flags: bit 0 = debug, skip the epilogue arithmetic (measures the TMA + MMA pipeline alone)
 template <int NBL>
 __global__ void __launch_bounds__(kTcThreads, 1)
@@ -127,6 +143,7 @@ exact_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     uint64_t* n_full = a_empty + 1;                // [2] norm-block ring
     uint64_t* n_empty = n_full + 2;                // [2]
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(n_empty + 2);
+    uint32_t* sTau = reinterpret_cast<uint32_t*>(smem + L.tau_off);   // [group][row]
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int units = m_tiles * S;
@@ -147,6 +164,7 @@ exact_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
         fence_barrier_init();
     }
     if (warp == 2) tmem_alloc(tmem_ptr, 512);
+    for (int i = threadIdx.x; i < kGroups * kTileM; i += kTcThreads) sTau[i] = 0xFF800000u;   // +inf (any tag)
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -233,16 +251,21 @@ exact_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
         constexpr int kCols = kTileN / kGroups;        // columns per group
         const uint32_t tbase = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(eg * kCols);
         BinList<NBL> list;
-        int as = 0, aph = 0;
-        for (int u = blockIdx.x; u < units; u += gridDim.x) {
+        volatile uint32_t* my_tau = sTau + eg * kTileM + row;
+        const volatile uint32_t* partner_tau = sTau + (eg ^ 1) * kTileM + row;
+        int as = 0, aph = 0, ui = 0;
+        for (int u = blockIdx.x; u < units; u += gridDim.x, ++ui) {
             const int mt = u % m_tiles, s = u / m_tiles;
             const int t0 = s * tiles_per_slice;
             const int t1 = min(tiles_total, t0 + tiles_per_slice);
             list.reset();
+            float told = INFINITY;                 // own threshold as last published
+            *my_tau = tau_word(INFINITY, ui);
             for (int t = t0; t < t1; ++t) {
                 mbar_wait(&tmem_full[as], aph);
                 tc_fence_after();
                 if (!(flags & 1)) {
+                    const float ptau = (flags & 8) ? INFINITY : tau_of_word(*partner_tau, ui);
                     const uint32_t taddr = tbase + (uint32_t)(as * kTileN);
                     const int64_t left = N - ((int64_t)t * kTileN + eg * kCols);
                     const int n_valid = left < kCols ? (int)left : kCols;      // may be <= 0: every column masked
@@ -258,14 +281,15 @@ exact_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                         if (ch + 1 < kCols / 32) tmem_ld_x32(taddr + (uint32_t)((ch + 1) * 32), v);
                         if (flags & 2) continue;
                         const float cm = fminf(fminf(m[0], m[1]), fminf(m[2], m[3]));
-                        if (cm < list.tau()) {
+                        if (cm < fminf(list.tau(), ptau)) {
 #pragma unroll 1
                             for (int b = 0; b < 4; ++b) {
                                 const float mb = b == 0 ? m[0] : (b == 1 ? m[1] : (b == 2 ? m[2] : m[3]));
-                                if (mb < list.tau()) list.insert(mb, bin_base + (uint32_t)(ch * 4 + b));
+                                if (mb < fminf(list.tau(), ptau)) list.insert(mb, bin_base + (uint32_t)(ch * 4 + b));
                             }
                         }
                     }
+                    if (list.tau() < told) { told = list.tau(); *my_tau = tau_word(told, ui); }
                 }
                 tc_fence_before();
                 mbar_arrive(&tmem_empty[as]);
