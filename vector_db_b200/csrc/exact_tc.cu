@@ -125,7 +125,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
 exact_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                 const __grid_constant__ CUtensorMap map_a2, const __grid_constant__ CUtensorMap map_b2,
                 int Q, int64_t N, int D, int has_norm, int num_kb, int stages, int m_tiles, int S,
-                int tiles_per_slice, int tiles_total, int flags, u64* __restrict__ partial) {
+                int tiles_per_slice, int tiles_total, int flags, u64* __restrict__ partial, uint32_t* gtau) {
     extern __shared__ __align__(1024) unsigned char smem[];   // 128B-swizzled operand tiles need 1024 B alignment
     if ((smem_u32(smem) & 1023u) != 0) __trap();
     const TcSmemLayout L = tc_layout(num_kb, stages, has_norm);
@@ -261,11 +261,16 @@ exact_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
             list.reset();
             float told = INFINITY;                 // own threshold as last published
             *my_tau = tau_word(INFINITY, ui);
+            // the same argument holds for EVERY list of the query in this launch (other slices run in other CTAs or
+            // ran in an earlier wave): gtau[q] is the ordered minimum of all published list thresholds
+            const int qrow = mt * kTileM + row;
+            volatile uint32_t* gq = (qrow < Q && !(flags & 8)) ? gtau + qrow : nullptr;
             for (int t = t0; t < t1; ++t) {
+                const uint32_t gw = gq ? *gq : 0xFF800000u;      // issued before the wait: the L2 round trip hides under it
                 mbar_wait(&tmem_full[as], aph);
                 tc_fence_after();
                 if (!(flags & 1)) {
-                    const float ptau = (flags & 8) ? INFINITY : tau_of_word(*partner_tau, ui);
+                    const float ptau = (flags & 8) ? INFINITY : fminf(tau_of_word(*partner_tau, ui), ordered_to_f32(gw));
                     const uint32_t taddr = tbase + (uint32_t)(as * kTileN);
                     const int64_t left = N - ((int64_t)t * kTileN + eg * kCols);
                     const int n_valid = left < kCols ? (int)left : kCols;      // may be <= 0: every column masked
@@ -289,7 +294,11 @@ exact_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                             }
                         }
                     }
-                    if (list.tau() < told) { told = list.tau(); *my_tau = tau_word(told, ui); }
+                    if (list.tau() < told) {
+                        told = list.tau();
+                        *my_tau = tau_word(told, ui);
+                        if (gq) atomicMin(const_cast<uint32_t*>(gq), f32_to_ordered(told));
+                    }
                 }
                 tc_fence_before();
                 mbar_arrive(&tmem_empty[as]);
@@ -316,11 +325,12 @@ exact_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
 // Query operand: bf16(q) padded to Dp columns; for L2 the three columns after D hold 1.0 so that
 // the MMA adds the (hi, mid, lo) bf16 split of |x|^2 stored in the same columns of the row mirror.
 __global__ void tc_query_operand_kernel(const float* __restrict__ q, __nv_bfloat16* __restrict__ y, int Q, int D, int Dp,
-                                        int metric) {
+                                        int metric, uint32_t* __restrict__ gtau) {
     const int64_t total = (int64_t)Q * Dp;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
         const int64_t r = i / Dp;
         const int c = (int)(i - r * Dp);
+        if (c == 0) gtau[r] = 0xFF800000u;                      // the scan's per-query threshold exchange starts at +inf
         float v = 0.f;
         if (c < D) v = q[r * D + c];
         else if (metric == VDB_METRIC_L2 && c < D + 3) v = 1.f;
@@ -683,7 +693,8 @@ int vdb_exact_topk_tc(const float* q, int Q, const float* db, const void* mirror
 
     // per-list depth: lists of 8 are enough when there are many of them (L * 8 >= 4 * kNBFinal), debug bit 2 forces 16
     const int nbl = ((g_tc_flags & 4) || p.S * kGroups * 8 < 4 * kNBFinal) ? 16 : 8;
-    tc_query_operand_kernel<<<sm_count() * 2, 256, 0, st>>>(q, qb, Q, D, p.Dp, metric);
+    uint32_t* gtau = reinterpret_cast<uint32_t*>(tau);            // free until select_bins_kernel writes tau
+    tc_query_operand_kernel<<<sm_count() * 2, 256, 0, st>>>(q, qb, Q, D, p.Dp, metric, gtau);
     CUtensorMap map_a, map_b;
     CUtensorMap map_a2, map_b2;
     int rc = make_map(&map_a, qb, Q, D, p.Dp, kBlockK, kTileM);
@@ -702,11 +713,11 @@ int vdb_exact_topk_tc(const float* q, int Q, const float* db, const void* mirror
         if (nbl == 16) {
             VDB_CUDA(cudaFuncSetAttribute(exact_tc_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem));
             exact_tc_kernel<16><<<p.grid, kTcThreads, p.smem, st>>>(map_a, map_b, map_a2, map_b2, Q, N, D, p.has_norm, p.num_kb, p.stages, p.m_tiles, p.S,
-                                                                   p.tiles_per_slice, p.tiles_total, g_tc_flags, partial);
+                                                                   p.tiles_per_slice, p.tiles_total, g_tc_flags, partial, gtau);
         } else {
             VDB_CUDA(cudaFuncSetAttribute(exact_tc_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem));
             exact_tc_kernel<8><<<p.grid, kTcThreads, p.smem, st>>>(map_a, map_b, map_a2, map_b2, Q, N, D, p.has_norm, p.num_kb, p.stages, p.m_tiles, p.S,
-                                                                  p.tiles_per_slice, p.tiles_total, g_tc_flags, partial);
+                                                                  p.tiles_per_slice, p.tiles_total, g_tc_flags, partial, gtau);
         }
     }
     VDB_CUDA(cudaGetLastError());
