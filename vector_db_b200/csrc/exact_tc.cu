@@ -96,12 +96,24 @@ __device__ __forceinline__ float min8(const float* v) {
 // bin minima; the caller then compares their minimum with the row's threshold (fast path) and only
 // chunks that beat it walk their bins.  The insert code exists ONCE in the kernel (non-unrolled
 // loops): the previous fully unrolled form was ~180 KB of SASS and ran out of the instruction cache.
-__device__ __forceinline__ void chunk_minima(float (&v)[32], int n_valid, float (&m)[4]) {
+constexpr int kBinsPerChunk = 32 / kBin;
+__device__ __forceinline__ float bin_min(const float* v) {
+    if (kBin == 8) return min8(v);
+    return fminf(fminf(fminf(v[0], v[1]), v[2]), v[3]);        // kBin == 4: FMNMX3 + FMNMX
+}
+__device__ __forceinline__ void chunk_minima(float (&v)[32], int n_valid, float (&m)[kBinsPerChunk]) {
     if (n_valid < 32) {
 #pragma unroll
         for (int i = 0; i < 32; ++i) v[i] = (i < n_valid) ? v[i] : INFINITY;
     }
-    m[0] = min8(v); m[1] = min8(v + 8); m[2] = min8(v + 16); m[3] = min8(v + 24);
+#pragma unroll
+    for (int b = 0; b < kBinsPerChunk; ++b) m[b] = bin_min(v + b * kBin);
+}
+__device__ __forceinline__ float pick_bin(const float (&m)[kBinsPerChunk], int b) {
+    float r = m[0];
+#pragma unroll
+    for (int i = 1; i < kBinsPerChunk; ++i) r = (b == i) ? m[i] : r;
+    return r;
 }
 
 // Threshold exchange between the two epilogue groups of a CTA (same query row, other half of the columns): a bin
@@ -279,18 +291,20 @@ exact_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                     tmem_ld_x32(taddr, v);
 #pragma unroll 1
                     for (int ch = 0; ch < kCols / 32; ++ch) {
-                        float m[4];
+                        float m[kBinsPerChunk];
                         tmem_ld_wait(v);
                         chunk_minima(v, n_valid - ch * 32, m);
                         // v is dead from here on: fetch the next chunk under the threshold test / inserts
                         if (ch + 1 < kCols / 32) tmem_ld_x32(taddr + (uint32_t)((ch + 1) * 32), v);
                         if (flags & 2) continue;
-                        const float cm = fminf(fminf(m[0], m[1]), fminf(m[2], m[3]));
+                        float cm = fminf(fminf(m[0], m[1]), fminf(m[2], m[3]));
+                        if (kBinsPerChunk == 8) cm = fminf(fminf(cm, fminf(m[4 % kBinsPerChunk], m[5 % kBinsPerChunk])),
+                                                           fminf(m[6 % kBinsPerChunk], m[7 % kBinsPerChunk]));
                         if (cm < fminf(list.tau(), ptau)) {
 #pragma unroll 1
-                            for (int b = 0; b < 4; ++b) {
-                                const float mb = b == 0 ? m[0] : (b == 1 ? m[1] : (b == 2 ? m[2] : m[3]));
-                                if (mb < fminf(list.tau(), ptau)) list.insert(mb, bin_base + (uint32_t)(ch * 4 + b));
+                            for (int b = 0; b < kBinsPerChunk; ++b) {
+                                const float mb = pick_bin(m, b);
+                                if (mb < fminf(list.tau(), ptau)) list.insert(mb, bin_base + (uint32_t)(ch * kBinsPerChunk + b));
                             }
                         }
                     }
