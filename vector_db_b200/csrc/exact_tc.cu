@@ -271,6 +271,8 @@ exact_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
             const int t0 = s * tiles_per_slice;
             const int t1 = min(tiles_total, t0 + tiles_per_slice);
             list.reset();
+            float pend_s = INFINITY;               // parked hit of this lane, not yet in the list
+            uint32_t pend_b = 0xFFFFFFFFu;
             float told = INFINITY;                 // own threshold as last published
             *my_tau = tau_word(INFINITY, ui);
             // the same argument holds for EVERY list of the query in this launch (other slices run in other CTAs or
@@ -300,11 +302,21 @@ exact_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                         float cm = fminf(fminf(m[0], m[1]), fminf(m[2], m[3]));
                         if (kBinsPerChunk == 8) cm = fminf(fminf(cm, fminf(m[4 % kBinsPerChunk], m[5 % kBinsPerChunk])),
                                                            fminf(m[6 % kBinsPerChunk], m[7 % kBinsPerChunk]));
-                        if (cm < fminf(list.tau(), ptau)) {
+                        // An insert by ONE lane sends the whole warp through the bubble (5 instructions per list slot),
+                        // so a lane parks its hit in a one-entry pending slot and the warp inserts only when some
+                        // lane's slot is already taken: ~7 hits per bubble instead of one.  (+inf, x) inserts nothing.
+                        if (__any_sync(0xFFFFFFFFu, cm < fminf(list.tau(), ptau))) {
 #pragma unroll 1
                             for (int b = 0; b < kBinsPerChunk; ++b) {
                                 const float mb = pick_bin(m, b);
-                                if (mb < fminf(list.tau(), ptau)) list.insert(mb, bin_base + (uint32_t)(ch * kBinsPerChunk + b));
+                                const bool hit = mb < fminf(list.tau(), ptau);
+                                if (__any_sync(0xFFFFFFFFu, hit)) {
+                                    if (__any_sync(0xFFFFFFFFu, hit && pend_s < INFINITY)) {
+                                        list.insert(pend_s, pend_b);
+                                        pend_s = INFINITY;
+                                    }
+                                    if (hit) { pend_s = mb; pend_b = bin_base + (uint32_t)(ch * kBinsPerChunk + b); }
+                                }
                             }
                         }
                     }
@@ -319,6 +331,7 @@ exact_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                 as ^= 1;
                 if (as == 0) aph ^= 1;
             }
+            list.insert(pend_s, pend_b);
             const int q = mt * kTileM + row;
             if (q < Q) {
                 u64* dst = partial + (((size_t)q * S + s) * kGroups + eg) * NBL;
