@@ -16,6 +16,13 @@
 // select_bins_kernel), hence t(x) >= tau - eps.  All rows inside them are re-scored exactly.  If
 // tau - eps > t_k (the k-th exact score) no outside row can enter the top-k: certified.
 // Cosine: c(x) = q~ . bf16(-x/|x|), t(x) = -q.x/|x|, eps = (2^-8 * 1.01 + 2^-13) * |q|.
+//
+// Which bins a list may refuse.  tau is (at most) the worst entry of every FULL per-(slice, column group) list of
+// the query, so a bin may be refused by ANY list as soon as its minimum is >= the worst entry of SOME full list of
+// the same query: the bound above does not change.  The epilogue therefore tests against the minimum of its own
+// threshold, its CTA partner's (shared memory) and every other list's of this launch (one global word per query),
+// which keeps most lanes out of the insert code; the hits that remain are parked per lane and inserted by the
+// warp together (exact_tc_kernel).
 #include <cuda.h>
 #include <math.h>
 
