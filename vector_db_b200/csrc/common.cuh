@@ -5,7 +5,8 @@
 //    the (dist, id) tuple order the reference sorts by (tests/indexing/test_hnsw.py:128-134,
 //    src/vector_db/indexing/hnsw.py:366)
 //  * BlockSelect: CTA-wide streaming top-R in shared memory (threshold filter + pending area +
-//    bitonic compaction) used by every scan kernel and by the merge kernels
+//    bitonic compaction) used by the scan kernels and by the merge kernels; BlockSelectRadix: the same protocol
+//    with a radix select instead of sorts and an optional barrier-free flag, for large shortlists (IVF-PQ)
 #pragma once
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
