@@ -95,8 +95,9 @@ int vdb_rerank_f32(const float* q, int Q, const float* db, const int64_t* ids, i
  * reduces every accumulator row to per-bin minima (bin = VDB_TC_BIN consecutive rows) and keeps
  * the best bins per (query, db slice) in registers.  vdb_exact_topk_tc merges the slices, reranks
  * every row of the selected bins in fp32 (the reference's direct-difference arithmetic) and
- * certifies the result with a rigorous bf16 error bound; the indices of queries it cannot certify
- * are returned so the caller re-runs them through vdb_exact_topk_f32.
+ * certifies the result with a rigorous bf16 error bound, eps = s (|q~-q| A + |q| B + 2^-13 |q| A), s = 2 for L2 and
+ * 1 for cosine (two Cauchy-Schwarz terms, one per rounded operand, on MEASURED residual norms); the queries it cannot
+ * certify are re-scanned by the fp32 kernel inside the same call.
  * Requirements: D % 8 == 0, one query tile's operand fits shared memory (D <= 512), k <= 16;
  * vdb_exact_topk_tc_supported() answers for a shape.
  * Mirror: one bf16 buffer of vdb_tc_mirror_elems(N, D, metric) elements, 128-byte aligned: the N x D operand
@@ -105,11 +106,15 @@ int vdb_rerank_f32(const float* q, int Q, const float* db, const int64_t* ids, i
 int vdb_exact_topk_tc_supported(int Q, int64_t N, int D, int k, int metric);
 size_t vdb_tc_mirror_elems(int64_t N, int D, int metric);
 int vdb_tc_prepare_rows(const float* vecs /*[dev] N*D*/, int64_t N, int D, int metric,
-                        float* sqnorm /*[dev] N or NULL*/, void* mirror /*[dev] vdb_tc_mirror_elems bf16*/, void* stream);
+                        float* sqnorm /*[dev] N or NULL*/, void* mirror /*[dev] vdb_tc_mirror_elems bf16*/,
+                        float* stats /*[dev] 2 floats out: A = max |x~| and B = max |x~ - x| over the rows, x~ the bf16
+                           operand row (x for L2, x/|x| for cosine) -- the measured rounding residual the certificate
+                           of vdb_exact_topk_tc is built on*/,
+                        void* stream);
 size_t vdb_exact_topk_tc_workspace(int Q, int64_t N, int D, int k, int metric);
 int vdb_exact_topk_tc(const float* q /*[dev] Q*D fp32*/, int Q,
                       const float* db /*[dev] N*D fp32*/, const void* mirror /*[dev] see above*/,
-                      float db_max_norm /* max |x| over the rows, used by the L2 certificate */,
+                      const float* db_stats /*[dev] the 2 floats vdb_tc_prepare_rows wrote for this mirror */,
                       const int64_t* ids /*[dev] or NULL*/, int64_t N, int D, int k, int metric,
                       float* out_d, int64_t* out_i,
                       int32_t* out_uncertified /*[dev] Q+1: count, then the indices of the queries the certificate rejected;

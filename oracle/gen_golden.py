@@ -50,6 +50,65 @@ def gen_exact(ref_dist, topk_sorted):
                         scores=scores, top7=topk_sorted(scores, 7))
 
 
+def gen_cosine(ref_dist, topk_sorted):
+    """Pins the cosine order to the reference's OWN arithmetic (the reference has no cosine function, VERDICT r1
+    next #3): rows and queries are L2-normalised in fp32, then ranked (a) by the reference's
+    euclidean_vector_distance + (dist, id) tuple sort (test_hnsw.py:128-134) -- |q^ - x^|^2 = 2 - 2 cos, so this
+    order IS the cosine order up to fp32 ties -- and (b) by top_k_indices_sorted (util/math.py:3-5) applied to
+    the dot products q^ . x^."""
+    rng = np.random.default_rng(2468)
+    n, dim, nq, k = 600, 48, 16, 10
+    X = (rng.standard_normal((n, dim)) * rng.uniform(0.2, 4.0, (n, 1))).astype(np.float32)
+    X[33] = 2.0 * X[9]                # same direction, different length: a cosine tie, distinct L2
+    ids = np.arange(n, dtype=np.int64) * 2 + 5
+    Q = rng.standard_normal((nq, dim)).astype(np.float32)
+    Q[0] = 3.0 * X[9]
+    Xn = (X / np.linalg.norm(X, axis=1, keepdims=True)).astype(np.float32)
+    Qn = (Q / np.linalg.norm(Q, axis=1, keepdims=True)).astype(np.float32)
+    D = np.empty((nq, k), np.float32)
+    I = np.empty((nq, k), np.int64)
+    S = np.empty((nq, k), np.float32)
+    Is = np.empty((nq, k), np.int64)
+    for qi in range(nq):
+        pairs = [(ref_dist(Qn[qi], Xn[i]), int(ids[i])) for i in range(n)]
+        pairs.sort()
+        D[qi] = [p_[0] for p_ in pairs[:k]]
+        I[qi] = [p_[1] for p_ in pairs[:k]]
+        sims = np.array([np.dot(Qn[qi], Xn[i]) for i in range(n)], dtype=np.float32)
+        top = topk_sorted(sims, k)
+        S[qi] = sims[top]
+        Is[qi] = ids[top]
+    np.savez_compressed(os.path.join(OUT, "cosine.npz"), X=X, ids=ids, Q=Q, D_unit_l2=D, I_unit_l2=I, S_dot=S, I_dot=Is)
+
+
+def gen_adc(ref_dist):
+    """Pins the ADC scan to the reference's arithmetic: for the centroids / codes the
+    reference's compress() produced (pq.npz, pq8.npz), the distance of a query to a row's DECODED vector
+    (concatenated centroids, pq.py:48-62 layout) by euclidean_vector_distance, squared, and its (dist, id) top-k.
+    sum_j |q_j - C_j[c_j]|^2 == |q - decode(c)|^2, so the ADC order is this order up to fp32 rounding."""
+    out = {}
+    for tag, seed in (("pq", 31), ("pq8", 32)):
+        g = np.load(os.path.join(OUT, f"{tag}.npz"))
+        cents, codes = g["centroids"], g["codes"]                  # (m,K,dsub), (N,m)
+        m = cents.shape[0]
+        dec = np.concatenate([cents[j][codes[:, j]] for j in range(m)], axis=1).astype(np.float32)
+        rng = np.random.default_rng(seed)
+        nq, k = 12, 10
+        Q = rng.standard_normal((nq, dec.shape[1])).astype(np.float32)
+        Q[0] = dec[4]                                              # a query ON a decoded point: ADC distance 0
+        D = np.empty((nq, k), np.float32)
+        I = np.empty((nq, k), np.int64)
+        full = np.empty((nq, dec.shape[0]), np.float32)
+        for qi in range(nq):
+            pairs = [(ref_dist(Q[qi], dec[i]), i) for i in range(dec.shape[0])]
+            full[qi] = [p_[0] for p_ in pairs]
+            pairs.sort()
+            D[qi] = [p_[0] for p_ in pairs[:k]]
+            I[qi] = [p_[1] for p_ in pairs[:k]]
+        out.update({f"{tag}_Q": Q, f"{tag}_D": D, f"{tag}_I": I, f"{tag}_full": full})
+    np.savez_compressed(os.path.join(OUT, "adc.npz"), **out)
+
+
 def gen_pq(ref_pq):
     # KATs restated from tests/inference/test_pq.py:78-116
     svc = ref_pq.ProductQuantizationService(k=3, chunks=2, dim=4)
@@ -246,11 +305,17 @@ def main():
     gen_hnsw(ref_hnsw, Storage, Node, "medium", n=2000, dim=48, M=16, efc=100, nq=32, ef=64, k=10, seed=12)
     gen_ivf(Storage, Node)
     gen_metadata_filter()
+    gen_cosine(ref_dist, topk_sorted)
+    gen_adc(ref_dist)
     print("golden fixtures written to", os.path.abspath(OUT))
 
 
 if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "metadata":
     _import_reference()
     gen_metadata_filter()
+elif __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "pins":        # r2 additions only
+    _ref = _import_reference()
+    gen_cosine(_ref[4], _ref[5])
+    gen_adc(_ref[4])
 elif __name__ == "__main__":
     main()

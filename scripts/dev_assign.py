@@ -33,8 +33,7 @@ for K in (256, 1024, 4096):
         cnt = torch.bincount(lab, minlength=K).clamp(min=1).unsqueeze(1)
         cent = sums / cnt
     _, ref = ops.exact_topk_f32(X, cent, 1, "l2")
-    mirror, sq = ops.tc_prepare_rows(cent, "l2")
-    max_norm = float(sq.max().sqrt().item())
+    mirror, sq, max_norm = ops.tc_prepare_rows(cent, "l2")       # max_norm: the 2-float stats tensor
     for nbf, flags in (("trim", 0), ("all32", 16), ("trim16", 16 << 12), ("trim8", 8 << 12)):
         lib.vdb_debug_set_tc_flags(flags)
         for rep in range(3):

@@ -31,7 +31,7 @@ def test_library_exports_every_declared_symbol():
         assert hasattr(lib, n), f"{n} declared in vdb_b200.h but not exported"
     assert set(names) == set(_lib.SIGNATURES), "ctypes table out of step with the header"
     lib.vdb_abi_version.restype = ctypes.c_int
-    assert lib.vdb_abi_version() == 3
+    assert lib.vdb_abi_version() == 4
 
 
 def test_no_cpu_fallback_without_device():

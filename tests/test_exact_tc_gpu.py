@@ -5,6 +5,7 @@ import pytest
 import torch
 
 from oracle import oracle as O
+from tests._util import check_topk
 
 pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
@@ -12,8 +13,8 @@ DEV = "cuda:0"
 
 def _prep(X, metric="l2"):
     from vector_db_b200 import ops
-    mir, sq = ops.tc_prepare_rows(X, metric)
-    return mir, float(sq.max().sqrt().item())
+    mir, _, stats = ops.tc_prepare_rows(X, metric)
+    return mir, stats
 
 
 @pytest.mark.parametrize("n,d,q,k,metric", [(50_000, 384, 300, 10, "l2"), (20_011, 128, 129, 10, "l2"),
@@ -65,6 +66,48 @@ def test_tc_adversarial_near_duplicates_fall_back_not_fail():
     Dr, Ir = ops.exact_topk_f32(Q, X, 10, "l2")
     assert torch.equal(I, Ir) and torch.equal(D, Dr)
     assert n_bad > 0          # this data cannot be certified from a bf16 pass
+
+
+@pytest.mark.parametrize("metric", ["l2", "cosine"])
+def test_tc_certificate_covers_both_bf16_roundings(metric):
+    """ADVICE r1 (exact_tc.cu:487): the coarse score carries TWO bf16 roundings (query and row), so its error can
+    reach (4u + 2u^2)|q||x|, u = 2^-8 -- attained by q = x on bf16 half-way points, where both operands round the
+    same way.  Rows are 9-bit integers (257 = 0b100000001 needs nine significand bits: every odd value is a
+    half-way point), queries are rows of the database and near-copies of them.  The answer must be the fp32 scan's,
+    whatever the certificate decides, and the measured residual stats must show the full half-ulp residual."""
+    from vector_db_b200 import ops
+    g = torch.Generator(device=DEV).manual_seed(9)
+    n, d, nq = 30_000, 128, 192
+    X = (2 * torch.randint(128, 256, (n, d), device=DEV, generator=g) + 1).float()          # odd integers in [257, 511]
+    X *= (torch.randint(0, 2, (n, d), device=DEV, generator=g) * 2 - 1).float()
+    Q = X[torch.randint(0, n, (nq,), device=DEV, generator=g)].clone()
+    Q[nq // 2:] += torch.randint(-2, 3, (nq - nq // 2, d), device=DEV, generator=g).float() * 2
+    mir, stats = _prep(X, metric)
+    A, B = stats.tolist()
+    if metric == "l2":
+        rn = X.norm(dim=1).max().item()
+        assert abs(B - d ** 0.5) < 0.01 * d ** 0.5        # |x~ - x| = 1 per element on this grid (ulp = 2 in [256, 512))
+        assert 0.99 * rn * (1 - 2.0 ** -8) <= A <= 1.01 * rn * (1 + 2.0 ** -8)
+    D, I, n_bad = ops.exact_topk_tc(Q, X, mir, stats, 10, metric, return_uncertified=True)
+    Dr, Ir = ops.exact_topk_f32(Q, X, 10, metric)
+    assert torch.equal(I, Ir) and torch.equal(D, Dr), f"{(I != Ir).sum().item()} ids differ"
+    Dref, Iref = (O.exact_l2_topk if metric == "l2" else O.exact_cosine_topk)(
+        X.cpu().numpy(), np.arange(n, dtype=np.int64), Q[:8].cpu().numpy(), 10)
+    np.testing.assert_array_equal(I[:8].cpu().numpy(), Iref)
+
+
+def test_tc_cosine_vs_oracle():
+    """The tensor-core cosine path against the oracle itself (not only against the fp32 kernel)."""
+    from vector_db_b200 import ops
+    rng = np.random.default_rng(15)
+    X = rng.standard_normal((16_000, 384)).astype(np.float32)
+    Q = rng.standard_normal((48, 384)).astype(np.float32)
+    ids = np.arange(16_000, dtype=np.int64) * 3 + 1
+    Xd, Qd = torch.from_numpy(X).to(DEV), torch.from_numpy(Q).to(DEV)
+    mir, stats = _prep(Xd, "cosine")
+    S, I = ops.exact_topk_tc(Qd, Xd, mir, stats, 10, "cosine", ids=torch.from_numpy(ids).to(DEV))
+    Sref, Iref = O.exact_cosine_topk(X, ids, Q, 10)
+    check_topk(S.cpu().numpy(), I.cpu().numpy(), Sref, Iref, rtol=1e-5, atol=2e-6, max_tied_rows=1)
 
 
 def test_exact_index_uses_tensor_cores_when_it_can():

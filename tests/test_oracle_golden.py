@@ -6,6 +6,7 @@ import numpy as np
 
 from oracle import oracle as O
 from oracle.hnsw_oracle import HnswOracle, search_arrays
+from tests._util import check_topk
 
 
 def _load(golden_dir, name):
@@ -46,6 +47,36 @@ def test_cosine_topk_is_largest_first():
     S, I = O.exact_cosine_topk(X, np.arange(200), X[:4] * 3.0, 5)
     assert list(I[:, 0]) == [0, 1, 2, 3]
     assert np.all(np.diff(S, axis=1) <= 0) and np.allclose(S[:, 0], 1.0, atol=1e-6)
+
+
+def test_cosine_order_pinned_to_reference_arithmetic(golden_dir):
+    """cosine.npz (oracle/gen_golden.py:gen_cosine): the reference's euclidean_vector_distance + (dist, id) sort on
+    L2-normalised vectors, and top_k_indices_sorted on their dot products.  The oracle's cosine top-k must give
+    the same ids except inside fp32 value ties, sims equal to the reference's dot products, and
+    |q^ - x^|^2 == 2 - 2 sim."""
+    g = _load(golden_dir, "cosine.npz")
+    S, I = O.exact_cosine_topk(g["X"], g["ids"], g["Q"], 10)
+    check_topk(S, I, g["S_dot"], g["I_dot"], rtol=1e-5, atol=2e-6)
+    # unit-vector L2 order == cosine order: compare through the monotone map sim -> sqrt(2 - 2 sim)
+    d_from_s = np.sqrt(np.maximum(0.0, 2.0 - 2.0 * S.astype(np.float64))).astype(np.float32)
+    check_topk(d_from_s, I, g["D_unit_l2"], g["I_unit_l2"], rtol=2e-4, atol=1e-3)
+    assert I[0, 0] in (g["ids"][9], g["ids"][33]) and I[0, 1] in (g["ids"][9], g["ids"][33])   # same direction twice
+    assert abs(S[0, 0] - 1.0) < 1e-6
+
+
+def test_adc_pinned_to_reference_decode_distance(golden_dir):
+    """adc.npz (oracle/gen_golden.py:gen_adc): euclidean_vector_distance(q, decode(code)) from the reference on
+    the reference's own centroids / codes.  The ADC restatement (fixed-point table) must give that order and the
+    squared distances to fp32 rounding."""
+    a = _load(golden_dir, "adc.npz")
+    for tag in ("pq", "pq8"):
+        g = _load(golden_dir, f"{tag}.npz")
+        cents = list(g["centroids"])
+        lut = O.adc_lut(a[f"{tag}_Q"], cents)
+        D, I = O.adc_scan_topk(g["codes"], lut, 10)
+        ref_sq = (a[f"{tag}_D"].astype(np.float32) ** 2).astype(np.float32)
+        check_topk(D, I, ref_sq, a[f"{tag}_I"], rtol=1e-5, atol=1e-5)
+        assert I[0, 0] == a[f"{tag}_I"][0, 0] and D[0, 0] < 1e-6       # query on a decoded point
 
 
 def test_pq_kats_and_codes_match_reference(golden_dir):

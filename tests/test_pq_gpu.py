@@ -6,6 +6,7 @@ import pytest
 import torch
 
 from oracle import oracle as O
+from tests._util import check_topk
 
 pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
@@ -92,6 +93,30 @@ def test_lut_and_adc_vs_oracle(n, m, dsub, q, R):
     D, I = ops.pq_adc_topk(_t(codes), lut, R_eff)
     np.testing.assert_array_equal(D.cpu().numpy(), Dref)
     np.testing.assert_array_equal(I.cpu().numpy(), Iref)
+
+
+def test_golden_adc_pinned_to_reference_decode_distance(golden_dir):
+    """tests/golden/adc.npz: euclidean_vector_distance(q, decode(code)) computed by the reference on its own
+    centroids and codes (oracle/gen_golden.py:gen_adc).  LUT + ADC scan on the GPU must give that (dist, id)
+    order and the squared distances to fp32 rounding -- through the raw ops and through PQIndex."""
+    from vector_db_b200 import ops
+    from vector_db_b200.inference.pq import PQIndex
+    a = np.load(os.path.join(golden_dir, "adc.npz"))
+    for tag in ("pq", "pq8"):
+        g = np.load(os.path.join(golden_dir, f"{tag}.npz"))
+        cents = g["centroids"]
+        m, K, dsub = cents.shape
+        cb = np.concatenate([cents, np.repeat(cents[:, :1, :], 256 - K, axis=1)], axis=1)     # pad LUT rows to 256
+        lut = ops.pq_lut(_t(a[f"{tag}_Q"]), _t(cb))
+        D, I = ops.pq_adc_topk(_t(g["codes"].astype(np.uint8)), lut, 10)
+        ref_sq = (a[f"{tag}_D"].astype(np.float32) ** 2).astype(np.float32)
+        check_topk(D.cpu().numpy(), I.cpu().numpy(), ref_sq, a[f"{tag}_I"], rtol=1e-5, atol=1e-5)
+        assert D[0, 0].item() < 1e-6 and I[0, 0].item() == a[f"{tag}_I"][0, 0]
+        idx = PQIndex(list(cents), keep_vectors=False)
+        idx.add(g["X"])                                                # GPU encode == the reference's codes (pinned above)
+        D2, I2 = idx.search(a[f"{tag}_Q"], 10)
+        np.testing.assert_array_equal(I2, I.cpu().numpy())
+        np.testing.assert_array_equal(D2, D.cpu().numpy())
 
 
 @pytest.mark.parametrize("n,m,q,R,dup", [(60_000, 16, 5, 1500, False), (40_000, 48, 3, 600, False),

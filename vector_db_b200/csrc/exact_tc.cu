@@ -10,12 +10,19 @@
 // Why the answer is still exact.  The reference computes sqrt(sum((q-x)^2)) in fp32.  The coarse
 // pass ranks by c(x) = |x|^2 - 2 q~.x~ (q~, x~ = bf16 roundings; |x|^2 enters the MMA as an exact
 // three-way bf16 split against ones in the query operand), whose error against the true
-// t(x) = |x|^2 - 2 q.x is bounded by eps = 2 * (2^-8 * 1.01 + 2^-13) * |q| * max|x| (Cauchy-Schwarz
-// on the two roundings + fp32 accumulation).  The kernel keeps, per query, the bins (8 consecutive
+// t(x) = |x|^2 - 2 q.x is bounded through the MEASURED rounding residuals of both operands:
+//   |q~.x~ - q.x| = |(q~-q).x~ + q.(x~-x)| <= |q~-q| |x~| + |q| |x~-x|        (Cauchy-Schwarz, twice)
+//   eps = 2 * (rq * A + |q| * B + 2^-13 |q| A),   rq = |q~-q| (per query, computed from q),
+//   A = max |x~|, B = max |x~-x| over the rows (vdb_tc_prepare_rows measures both while it builds the mirror);
+// the last term covers the fp32 accumulation of the MMA.  (Round 1 used 2 * 2^-8 |q| max|x|, which covers ONE
+// rounding: the worst case of two is (4u + 2u^2)|q||x|, u = 2^-8 -- attained by q = x on bf16 half-way points.
+// The residual form is rigorous for any input and, on ordinary data, tighter than either constant because a
+// rounding residual is ~0.4 u |x|, not u |x|.)  The kernel keeps, per query, the bins (8 consecutive
 // rows) with the smallest bin minimum; every row outside them has c(x) >= tau (see
 // select_bins_kernel), hence t(x) >= tau - eps.  All rows inside them are re-scored exactly.  If
 // tau - eps > t_k (the k-th exact score) no outside row can enter the top-k: certified.
-// Cosine: c(x) = q~ . bf16(-x/|x|), t(x) = -q.x/|x|, eps = (2^-8 * 1.01 + 2^-13) * |q|.
+// Cosine: c(x) = q~ . bf16(-x/|x|), t(x) = -q.x/|x|: the same bound without the factor 2, A and B measured on the
+// normalised rows (A ~ 1).
 //
 // Which bins a list may refuse.  tau is (at most) the worst entry of every FULL per-(slice, column group) list of
 // the query, so a bin may be refused by ANY list as soon as its minimum is >= the worst entry of SOME full list of
@@ -380,10 +387,11 @@ __global__ void tc_query_operand_kernel(const float* __restrict__ q, __nv_bfloat
 // so that the fp32 accumulator of q~ . row~ is the ranking score itself.  Also emits sqnorm.
 __global__ void tc_row_operand_kernel(const float* __restrict__ x, int64_t N, int D, int metric,
                                       float* __restrict__ sqnorm, __nv_bfloat16* __restrict__ mirror,
-                                      __nv_bfloat16* __restrict__ norms) {
+                                      __nv_bfloat16* __restrict__ norms, float* __restrict__ stats) {
     const int lane = threadIdx.x & 31;
     const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
     const int64_t n4 = (N + 3) & ~(int64_t)3;
+    float amax = 0.f, bmax = 0.f;                       // squared operand norm / squared rounding residual, max over my rows
     for (int64_t r = (((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5); r < n4; r += warps) {
         if (r >= N) {                                   // padding rows of the norm area (it is read in 4-row lines)
             if (norms && lane < 16) norms[r * 16 + lane] = __float2bfloat16_rn(0.f);
@@ -395,24 +403,51 @@ __global__ void tc_row_operand_kernel(const float* __restrict__ x, int64_t N, in
         acc = warp_sum(acc);
         if (sqnorm && lane == 0) sqnorm[r] = acc;
         __nv_bfloat16* out = mirror + r * D;
-        if (metric == VDB_METRIC_L2) {
-            for (int t = lane; t < D; t += 32) out[t] = __float2bfloat16_rn(-2.f * row[t]);
-            if (lane < 16) {
-                // 16-element norm row in the byte order the UMMA reads (32-byte swizzle: the two 16-byte halves
-                // of row r trade places when bit 2 of r is set), so a 256-row tile is a linear 8 KB copy
-                const __nv_bfloat16 h = __float2bfloat16_rn(acc);
-                const float r1 = acc - __bfloat162float(h);
-                const __nv_bfloat16 m = __float2bfloat16_rn(r1);
-                const __nv_bfloat16 l = __float2bfloat16_rn(r1 - __bfloat162float(m));
-                const __nv_bfloat16 v = lane == 0 ? h : (lane == 1 ? m : (lane == 2 ? l : __float2bfloat16_rn(0.f)));
-                norms[r * 16 + (lane ^ ((int)((r >> 2) & 1) << 3))] = v;
-            }
-        } else {
-            const float rinv = acc > 0.f ? -1.f / sqrtf(acc) : 0.f;
-            for (int t = lane; t < D; t += 32) out[t] = __float2bfloat16_rn(row[t] * rinv);
+        // operand value o (x for L2 -- the stored -2 bf16(x) is an exact scaling --, x/|x| for cosine), its bf16
+        // rounding o~ and the residual o~ - o, which is exact in fp32
+        const float rinv = metric == VDB_METRIC_L2 ? 1.f : (acc > 0.f ? 1.f / sqrtf(acc) : 0.f);
+        float a2 = 0.f, b2 = 0.f;
+        for (int t = lane; t < D; t += 32) {
+            const float o = metric == VDB_METRIC_L2 ? row[t] : row[t] * rinv;
+            const __nv_bfloat16 ob = __float2bfloat16_rn(o);
+            const float of = __bfloat162float(ob), res = of - o;
+            a2 = fmaf(of, of, a2);
+            b2 = fmaf(res, res, b2);
+            out[t] = metric == VDB_METRIC_L2 ? __float2bfloat16_rn(-2.f * o) : __float2bfloat16_rn(-o);
+        }
+        if (stats) {
+            amax = fmaxf(amax, warp_sum(a2));
+            bmax = fmaxf(bmax, warp_sum(b2));
+        }
+        if (metric == VDB_METRIC_L2 && lane < 16) {
+            // 16-element norm row in the byte order the UMMA reads (32-byte swizzle: the two 16-byte halves
+            // of row r trade places when bit 2 of r is set), so a 256-row tile is a linear 8 KB copy
+            const __nv_bfloat16 h = __float2bfloat16_rn(acc);
+            const float r1 = acc - __bfloat162float(h);
+            const __nv_bfloat16 m = __float2bfloat16_rn(r1);
+            const __nv_bfloat16 l = __float2bfloat16_rn(r1 - __bfloat162float(m));
+            const __nv_bfloat16 v = lane == 0 ? h : (lane == 1 ? m : (lane == 2 ? l : __float2bfloat16_rn(0.f)));
+            norms[r * 16 + (lane ^ ((int)((r >> 2) & 1) << 3))] = v;
+        }
+    }
+    if (stats) {
+        // sqrt with a relative allowance for the fp32 summation, max over all warps as raw bits (values >= 0)
+        if (lane == 0) {
+            atomicMax(reinterpret_cast<unsigned*>(stats), __float_as_uint(sqrtf(amax) * 1.0001f));
+            atomicMax(reinterpret_cast<unsigned*>(stats) + 1, __float_as_uint(sqrtf(bmax) * 1.0001f));
         }
     }
 }
+
+// The certificate's allowance for one query (file header): eps bounds |coarse score - exact score| for every row,
+// slack covers the fp32 rounding of the exact side (rerank arithmetic, |q|^2, the normalisation of cosine rows).
+// qn = |q|, rq = |bf16(q) - q|, A = max |x~|, B = max |x~ - x| (stats of vdb_tc_prepare_rows).
+__device__ __forceinline__ void tc_bound(int metric, float qn, float rq, float A, float B, float* eps, float* slack) {
+    const float e = (rq * A + qn * B) * 1.001f + 1.2207031e-4f * qn * A;          // + 2^-13 |q| A: MMA accumulation
+    if (metric == VDB_METRIC_L2) { *eps = 2.f * e; *slack = 4e-6f * (qn + 1.004f * A) * (qn + 1.004f * A); }
+    else { *eps = e; *slack = 4e-6f * qn; }
+}
+__device__ __forceinline__ float bf16_residual(float v) { return __bfloat162float(__float2bfloat16_rn(v)) - v; }
 
 // Per query: merge the L per-(slice, group) bin lists, keep the NB best bins, expand them to
 // candidate rows and record tau (see the certificate in the file header): every bin that is NOT a
@@ -420,20 +455,26 @@ __global__ void tc_row_operand_kernel(const float* __restrict__ x, int64_t N, in
 // because it was dropped from a full list, whose worst entry bounds it.  One CTA per query.
 __global__ void __launch_bounds__(256)
 select_bins_kernel(const u64* __restrict__ partial, int L, int NBL, int NB, int C, int64_t N, int32_t* __restrict__ cand,
-                   int32_t* __restrict__ cand_cnt, float* __restrict__ tau_out, const float* __restrict__ qv, int D, int k, int metric, float max_norm) {
+                   int32_t* __restrict__ cand_cnt, float* __restrict__ tau_out, const float* __restrict__ qv, int D, int k, int metric,
+                   const float* __restrict__ stats, int no_trim) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     u64* buf = reinterpret_cast<u64*>(smem_raw);
     __shared__ unsigned tau_bits;          // ordered-float minimum over the full lists' worst entries
-    __shared__ float qsq_s;
+    __shared__ float qsq_s, rsq_s;
     __shared__ int keep_s;
     const int q = blockIdx.x, total = L * NBL;
-    if (threadIdx.x == 0) { tau_bits = f32_to_ordered(INFINITY); qsq_s = 0.f; }
+    if (threadIdx.x == 0) { tau_bits = f32_to_ordered(INFINITY); qsq_s = 0.f; rsq_s = 0.f; }
     __syncthreads();
     {
-        float a = 0.f;
-        for (int t = threadIdx.x; t < D; t += blockDim.x) { const float v = qv[(size_t)q * D + t]; a = fmaf(v, v, a); }
+        float a = 0.f, b = 0.f;
+        for (int t = threadIdx.x; t < D; t += blockDim.x) {
+            const float v = qv[(size_t)q * D + t], r = bf16_residual(v);
+            a = fmaf(v, v, a);
+            b = fmaf(r, r, b);
+        }
         a = warp_sum(a);
-        if ((threadIdx.x & 31) == 0 && a != 0.f) atomicAdd(&qsq_s, a);
+        b = warp_sum(b);
+        if ((threadIdx.x & 31) == 0 && a != 0.f) { atomicAdd(&qsq_s, a); atomicAdd(&rsq_s, b); }
     }
     for (int i = threadIdx.x; i < C; i += blockDim.x) {
         u64 key = VDB_KEY_MAX;
@@ -482,12 +523,9 @@ select_bins_kernel(const u64* __restrict__ partial, int L, int NBL, int NB, int 
         const int nb = NB < C ? NB : C;
         int keep = nb;
         float cutoff = INFINITY;
-        if (k - 1 < C && buf[k - 1] != VDB_KEY_MAX) {
-            const float qn = sqrtf(qsq_s);
-            const float c = 0.00406742f;                             // 2^-8 * 1.01 + 2^-13, as in certify_kernel
-            float eps, slack;
-            if (metric == VDB_METRIC_L2) { eps = 2.f * c * qn * max_norm; slack = 4e-6f * (qn + max_norm) * (qn + max_norm); }
-            else { eps = c * qn; slack = 4e-6f * qn; }
+        if (!no_trim && k - 1 < C && buf[k - 1] != VDB_KEY_MAX) {
+            float eps, slack;                                        // the same allowance as certify_kernel
+            tc_bound(metric, sqrtf(qsq_s) * 1.0001f, sqrtf(rsq_s) * 1.0001f, stats[0], stats[1], &eps, &slack);
             cutoff = key_score(buf[k - 1]) + 2.f * eps + 4.f * slack;
         }
         // first empty slot, or first bin (sorted ascending) above the cutoff; nb <= 64, one thread scans it
@@ -515,17 +553,23 @@ select_bins_kernel(const u64* __restrict__ partial, int L, int NBL, int NB, int 
 // One warp per query: decide whether the reranked top-k is provably the exact top-k.
 template <int METRIC>
 __global__ void certify_kernel(const float* __restrict__ q, int Q, int D, int k, const float* __restrict__ out_d,
-                               const int64_t* __restrict__ out_i, const float* __restrict__ tau, float max_norm,
-                               int32_t* __restrict__ uncert) {
+                               const int64_t* __restrict__ out_i, const float* __restrict__ tau,
+                               const float* __restrict__ stats, int32_t* __restrict__ uncert) {
     const int lane = threadIdx.x & 31;
     const int qi = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (qi >= Q) return;
-    float a = 0.f;
-    for (int t = lane; t < D; t += 32) { float v = q[(size_t)qi * D + t]; a = fmaf(v, v, a); }
+    float a = 0.f, b = 0.f;
+    for (int t = lane; t < D; t += 32) {
+        const float v = q[(size_t)qi * D + t], r = bf16_residual(v);
+        a = fmaf(v, v, a);
+        b = fmaf(r, r, b);
+    }
     a = warp_sum(a);
+    b = warp_sum(b);
     if (lane != 0) return;
     const float qn = sqrtf(a);
-    const float c = 0.00406742f;                                   // 2^-8 * 1.01 + 2^-13
+    float eps, slack;
+    tc_bound(METRIC, qn * 1.0001f, sqrtf(b) * 1.0001f, stats[0], stats[1], &eps, &slack);
     const float t_bound = tau[qi];
     bool ok;
     if (out_i[(size_t)qi * k + k - 1] < 0) {
@@ -533,14 +577,10 @@ __global__ void certify_kernel(const float* __restrict__ q, int Q, int D, int k,
     } else if (METRIC == VDB_METRIC_L2) {
         const float dk = out_d[(size_t)qi * k + k - 1];
         const float tk = dk * dk - a;
-        const float eps = 2.f * c * qn * max_norm;
-        const float slack = 4e-6f * (qn + max_norm) * (qn + max_norm);
         ok = (t_bound - eps - slack) > tk;
     } else {
         const float simk = out_d[(size_t)qi * k + k - 1];
         const float tk = -simk * qn;
-        const float eps = c * qn;
-        const float slack = 4e-6f * qn;
         ok = (t_bound - eps - slack) > tk;
     }
     if (!ok) {
@@ -681,9 +721,11 @@ int vdb_exact_topk_tc_supported(int Q, int64_t N, int D, int k, int metric) {
 
 size_t vdb_tc_mirror_elems(int64_t N, int D, int metric) { return tc_mirror_elems(N, D, metric); }
 
-int vdb_tc_prepare_rows(const float* vecs, int64_t N, int D, int metric, float* sqnorm, void* mirror, void* stream) {
+int vdb_tc_prepare_rows(const float* vecs, int64_t N, int D, int metric, float* sqnorm, void* mirror, float* stats,
+                        void* stream) {
     VDB_REQUIRE(N >= 0 && D > 0 && D % 8 == 0, VDB_ERR_INVALID, "vdb_tc_prepare_rows: bad N=%lld D=%d", (long long)N, D);
     VDB_REQUIRE(metric == VDB_METRIC_L2 || metric == VDB_METRIC_COSINE, VDB_ERR_INVALID, "unknown metric %d", metric);
+    if (stats) VDB_CUDA(cudaMemsetAsync(stats, 0, 2 * sizeof(float), static_cast<cudaStream_t>(stream)));
     if (N == 0) return VDB_OK;
     VDB_REQUIRE(vecs && mirror, VDB_ERR_INVALID, "vdb_tc_prepare_rows: null pointer");
     int blocks = sm_count() * 8;
@@ -691,7 +733,7 @@ int vdb_tc_prepare_rows(const float* vecs, int64_t N, int D, int metric, float* 
     if (need < blocks) blocks = (int)need;
     tc_row_operand_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
         vecs, N, D, metric, sqnorm, static_cast<__nv_bfloat16*>(mirror),
-        metric == VDB_METRIC_L2 ? static_cast<__nv_bfloat16*>(mirror) + tc_norm_offset(N, D) : nullptr);
+        metric == VDB_METRIC_L2 ? static_cast<__nv_bfloat16*>(mirror) + tc_norm_offset(N, D) : nullptr, stats);
     count_launch(1);
     VDB_CUDA(cudaGetLastError());
     return VDB_OK;
@@ -703,12 +745,12 @@ size_t vdb_exact_topk_tc_workspace(int Q, int64_t N, int D, int k, int metric) {
     return tc_workspace(p, Q, N, D, k).total;
 }
 
-int vdb_exact_topk_tc(const float* q, int Q, const float* db, const void* mirror, float db_max_norm,
+int vdb_exact_topk_tc(const float* q, int Q, const float* db, const void* mirror, const float* db_stats,
                       const int64_t* ids, int64_t N, int D, int k, int metric, float* out_d,
                       int64_t* out_i, int32_t* out_uncertified, void* ws, size_t ws_bytes, void* stream) {
     VDB_REQUIRE(metric == VDB_METRIC_L2 || metric == VDB_METRIC_COSINE, VDB_ERR_INVALID, "unknown metric %d", metric);
     VDB_REQUIRE(Q > 0 && N > 0 && D > 0 && k > 0, VDB_ERR_INVALID, "vdb_exact_topk_tc: bad shape");
-    VDB_REQUIRE(q && db && mirror && out_d && out_i && out_uncertified && ws, VDB_ERR_INVALID,
+    VDB_REQUIRE(q && db && mirror && db_stats && out_d && out_i && out_uncertified && ws, VDB_ERR_INVALID,
                 "vdb_exact_topk_tc: null pointer");
     VDB_REQUIRE(N < (1ll << 31), VDB_ERR_UNSUPPORTED, "N too large for int32 candidate rows");
     TcPlan p;
@@ -764,7 +806,7 @@ int vdb_exact_topk_tc(const float* q, int Q, const float* db, const void* mirror
     if ((g_tc_flags >> 12) & 0xFF) nbf = (g_tc_flags >> 12) & 0xFF;
     if (nbf > kNBFinal) nbf = kNBFinal;
     select_bins_kernel<<<Q, 256, (size_t)(C + kNBFinal) * 8, st>>>(partial, L, nbl, nbf, C, N, cand, cand_cnt, tau, q, D, k, metric,
-                                                      (g_tc_flags & 16) ? INFINITY : db_max_norm);
+                                                      db_stats, (g_tc_flags & 16) ? 1 : 0);
     count_launch(3);
     VDB_CUDA(cudaGetLastError());
     rc = rerank_f32_counted(q, Q, db, ids, N, D, cand, cand_cnt, nbf * kBin, k, metric, out_d, out_i, stream);
@@ -773,9 +815,9 @@ int vdb_exact_topk_tc(const float* q, int Q, const float* db, const void* mirror
     const int warps_per_block = 8;
     const int blocks = (Q + warps_per_block - 1) / warps_per_block;
     if (metric == VDB_METRIC_L2)
-        certify_kernel<VDB_METRIC_L2><<<blocks, warps_per_block * 32, 0, st>>>(q, Q, D, k, out_d, out_i, tau, db_max_norm, out_uncertified);
+        certify_kernel<VDB_METRIC_L2><<<blocks, warps_per_block * 32, 0, st>>>(q, Q, D, k, out_d, out_i, tau, db_stats, out_uncertified);
     else
-        certify_kernel<VDB_METRIC_COSINE><<<blocks, warps_per_block * 32, 0, st>>>(q, Q, D, k, out_d, out_i, tau, db_max_norm, out_uncertified);
+        certify_kernel<VDB_METRIC_COSINE><<<blocks, warps_per_block * 32, 0, st>>>(q, Q, D, k, out_d, out_i, tau, db_stats, out_uncertified);
     count_launch(1);
     VDB_CUDA(cudaGetLastError());
     // queries the certificate rejected: exact fp32 scan, driven by the device-side list (no host round trip)

@@ -112,7 +112,7 @@ using namespace vdb;
 extern "C" {
 
 const char* vdb_last_error(void) { return vdb::g_err; }
-int vdb_abi_version(void) { return 3; }
+int vdb_abi_version(void) { return 4; }
 uint64_t vdb_launch_count(void) { return vdb::g_launches.load(); }
 
 void vdb_profile_enable(int on) { vdb::g_prof_on.store(on); }

@@ -34,7 +34,7 @@ class DeviceVectors:
         self._prepared_metric = -1
         self._sqnorm = None
         self._bf16 = None
-        self._max_norm = 0.0
+        self._tc_stats = None
         self._reserve(capacity)
 
     # -- capacity ---------------------------------------------------------------------------
@@ -162,15 +162,14 @@ class DeviceVectors:
 
     # -- derived arrays for the tensor-core scan ------------------------------------------------
     def prepared(self, metric):
-        """(operand mirror bf16 [n, row_elems], max row norm) for the tensor-core scan of `metric`
-        -- rebuilt after every mutation."""
+        """(operand mirror bf16, stats f32 [2] on the device) for the tensor-core scan of `metric`
+        -- rebuilt after every mutation; no host synchronisation."""
         m = ops._metric(metric)
         if self._prepared_n != self.n or self._prepared_metric != m:
-            mir, sq = ops.tc_prepare_rows(self.vecs[:self.n], m)
-            self._sqnorm, self._bf16 = sq, mir
-            self._max_norm = float(sq.max().sqrt().item()) if self.n else 0.0
+            mir, sq, stats = ops.tc_prepare_rows(self.vecs[:self.n], m)
+            self._sqnorm, self._bf16, self._tc_stats = sq, mir, stats
             self._prepared_n, self._prepared_metric = self.n, m
-        return self._bf16, self._max_norm
+        return self._bf16, self._tc_stats
 
     def rows_to_ids(self, rows: np.ndarray) -> np.ndarray:
         host_ids = self.ids[:self.n].cpu().numpy()

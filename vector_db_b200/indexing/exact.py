@@ -64,8 +64,8 @@ class ExactIndex:
         if self.engine == "tc" and not use_tc:
             raise ValueError("tensor-core engine does not support this shape / filter")
         if use_tc:
-            mir, max_norm = st.prepared(self.metric)
-            d, i, self._last_uncertified = ops.exact_topk_tc(q, st.vecs, mir, max_norm, k, self.metric, ids=st.ids,
+            mir, stats = st.prepared(self.metric)
+            d, i, self._last_uncertified = ops.exact_topk_tc(q, st.vecs, mir, stats, k, self.metric, ids=st.ids,
                                                             n_rows=st.n, return_uncertified=True)
             return d, i
         return ops.exact_topk_f32(q, st.vecs, k, self.metric, ids=st.ids, row_mask=mask, n_rows=st.n)

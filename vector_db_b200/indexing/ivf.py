@@ -144,12 +144,11 @@ class IvfIndex:
         out = torch.empty((n,), dtype=torch.int32, device=X.device)
         use_tc = ops.tc_supported(min(n, _ASSIGN_CHUNK), K, dim, 1, "l2")
         if use_tc:
-            mirror, sq = ops.tc_prepare_rows(cent, "l2")
-            max_norm = float(sq.max().sqrt().item())
+            mirror, _, stats = ops.tc_prepare_rows(cent, "l2")
         for s in range(0, n, _ASSIGN_CHUNK):
             e = min(n, s + _ASSIGN_CHUNK)
             if use_tc and ops.tc_supported(e - s, K, dim, 1, "l2"):
-                _, i = ops.exact_topk_tc(X[s:e], cent, mirror, max_norm, 1, "l2")
+                _, i = ops.exact_topk_tc(X[s:e], cent, mirror, stats, 1, "l2")
             else:
                 _, i = ops.exact_topk_f32(X[s:e], cent, 1, "l2")
             out[s:e] = i[:, 0].to(torch.int32)

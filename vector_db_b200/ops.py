@@ -315,23 +315,25 @@ def tc_supported(Q: int, N: int, D: int, k: int, metric=METRIC_L2) -> bool:
 
 def tc_prepare_rows(vecs: torch.Tensor, metric=METRIC_L2):
     """Per-metric bf16 operand mirror for the tensor-core scan.  Returns (mirror: flat bf16 buffer of
-    vdb_tc_mirror_elems(N, D, metric) elements -- the N x D operand rows, then for L2 the packed norm block --
-    and sqnorm f32 [N]); the accumulator of q~ . mirror_row~ is the ranking score itself."""
+    vdb_tc_mirror_elems(N, D, metric) elements -- the N x D operand rows, then for L2 the packed norm block --,
+    sqnorm f32 [N], stats f32 [2] = max operand norm / max bf16 rounding residual norm over the rows, which the
+    certificate of exact_topk_tc needs); the accumulator of q~ . mirror_row~ is the ranking score itself."""
     vecs = _f32(vecs, "vecs")
     n, d = vecs.shape
     m = _metric(metric)
     lib = load()
     mir = torch.empty((lib.vdb_tc_mirror_elems(n, d, m),), dtype=torch.bfloat16, device=vecs.device)
     sq = torch.empty(n, dtype=torch.float32, device=vecs.device)
-    check(lib.vdb_tc_prepare_rows(ptr(vecs), n, d, m, ptr(sq), ptr(mir), _lib.stream_ptr(vecs.device)))
-    return mir, sq
+    stats = torch.empty(2, dtype=torch.float32, device=vecs.device)
+    check(lib.vdb_tc_prepare_rows(ptr(vecs), n, d, m, ptr(sq), ptr(mir), ptr(stats), _lib.stream_ptr(vecs.device)))
+    return mir, sq, stats
 
 
-def exact_topk_tc(q: torch.Tensor, db: torch.Tensor, mirror: torch.Tensor, max_norm: float,
+def exact_topk_tc(q: torch.Tensor, db: torch.Tensor, mirror: torch.Tensor, stats: torch.Tensor,
                   k: int, metric=METRIC_L2, ids: Optional[torch.Tensor] = None, n_rows: Optional[int] = None,
                   return_uncertified: bool = False):
-    """Exact top-k through the tensor-core coarse scan + fp32 rerank + certificate.  `mirror` comes
-    from tc_prepare_rows(db, metric).  Queries the certificate rejects are re-run through the exact
+    """Exact top-k through the tensor-core coarse scan + fp32 rerank + certificate.  `mirror` and `stats`
+    come from tc_prepare_rows(db, metric).  Queries the certificate rejects are re-run through the exact
     fp32 scan inside the same library call (device-side list), so the result is always exact and the
     call never synchronises.  With ``return_uncertified`` the third value is a 0-dim int32 DEVICE
     tensor holding the number of such queries (reading it synchronises)."""
@@ -344,13 +346,15 @@ def exact_topk_tc(q: torch.Tensor, db: torch.Tensor, mirror: torch.Tensor, max_n
     out_i = torch.empty((Q, k), dtype=torch.int64, device=dev)
     uncert = torch.empty((Q + 1,), dtype=torch.int32, device=dev)
     lib = load()
+    if stats.dtype != torch.float32 or stats.numel() != 2 or not stats.is_cuda:
+        raise ValueError("stats must be the 2-float device tensor of tc_prepare_rows")
     if mirror.numel() != lib.vdb_tc_mirror_elems(N, D, m):
         raise ValueError("operand mirror was built for another metric / shape")
     nbytes = lib.vdb_exact_topk_tc_workspace(Q, N, D, k, m)
     if nbytes == 0:
         raise ValueError(f"tensor-core scan does not support Q={Q} N={N} D={D} k={k}")
     ws = _ws("exact_tc", nbytes, dev)
-    check(lib.vdb_exact_topk_tc(ptr(q), Q, ptr(db), ptr(mirror), float(max_norm), ptr(ids), N, D, k, m,
+    check(lib.vdb_exact_topk_tc(ptr(q), Q, ptr(db), ptr(mirror), ptr(stats), ptr(ids), N, D, k, m,
                                 ptr(out_d), ptr(out_i), ptr(uncert), ptr(ws), ws.numel(), _lib.stream_ptr(dev)))
     if return_uncertified:
         return out_d, out_i, uncert[0]
