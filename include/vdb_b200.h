@@ -186,8 +186,14 @@ size_t vdb_hnsw_search_workspace(int Q, int ef, int deg0);
 int vdb_hnsw_search(const float* q, int Q, const float* db, int64_t N, int D,
                     const int32_t* adj0, int deg0, const int32_t* adj_up, int deg_up,
                     const int32_t* up_ptr, int32_t entry_row, int max_level, int ef, int k,
-                    const uint32_t* alive, const uint32_t* filter, int hash_slots,
+                    const uint32_t* alive, const uint32_t* filter,
+                    const int32_t* levels /*[dev] N or NULL: top level of every row; a list above it reads as empty
+                       (the reference's entry point can lack its top lists, hnsw.py:179-191)*/,
+                    int hash_slots,
                     float* out_d /*[dev] Q*k*/, int32_t* out_rows /*[dev] Q*k*/, uint32_t* out_stats,
+                    int32_t* out_status /*[dev] Q or NULL: per query, bit 0 = visited table filled up, bit 1 = the
+                       bounded frontier dropped candidates (filtered search only: the reference's heap is unbounded,
+                       hnsw.py:102-131) -- the caller finishes such queries with the exact masked scan*/,
                     void* ws, size_t ws_bytes, void* stream);
 
 /* bench/debug only: CTA shared-memory footprint above which the visited hash moves to global memory */
@@ -199,7 +205,8 @@ void vdb_debug_set_hnsw_smem_hash_limit(int bytes);
  * hnsw.py:143-225: greedy descent, ef_construction beam per level, M closest as links, reverse
  * links with closest-cap truncation.  state int32[4] = {entry_row, max_level, evals_lo, evals_hi} is
  * read and updated (evals = running count of distance evaluations, for parity checks against the
- * reference's call count).  First int32 of ws = visited-table overflow flag as in vdb_hnsw_search. */
+ * reference's call count).  First int32 of ws = visited-table overflow flag, STICKY over the calls of a build: the
+ * caller zeroes it before the first chunk and reads it after the last. */
 size_t vdb_hnsw_insert_workspace(int efc, int deg0);
 int vdb_hnsw_insert(const float* db, int64_t N, int D, int32_t* adj0, int deg0, int32_t* adj_up,
                     int deg_up, const int32_t* up_ptr, const int32_t* levels /*[dev] N*/,

@@ -206,6 +206,50 @@ def gen_hnsw(ref_hnsw, Storage, Node, tag, n, dim, M, efc, nq, ef, k, seed):
                         build_evals=np.int64(build_evals))
 
 
+def gen_hnsw_toplevel(ref_hnsw, Storage, Node):
+    """a graph whose ENTRY POINT lacks its top-level keys.  random.Random(7), M=4, 500 nodes:
+    the entry is inserted at level 6 while the top was 4, so its `neighbors` has keys 0..4 only (hnsw.py:179-191)
+    and max_level = 6 (hnsw.py:215-217).  Records the key sets (empty lists included), searches on that graph, then
+    60 more inserts through the same rng (some of them link into the entry's missing levels) and searches again."""
+    rng = np.random.default_rng(3)
+    n, extra, dim, nq, k, ef = 500, 60, 8, 16, 5, 30
+    X = rng.standard_normal((n + extra, dim)).astype(np.float32)
+    Q = rng.standard_normal((nq, dim)).astype(np.float32)
+    idx = ref_hnsw.HNSW(M=4, ef_construction=20, rng=random.Random(7), storage=Storage())
+    for i in range(n):
+        idx.insert_node(Node(id=i, embedding=X[i]))
+
+    def snap():
+        rows, keys = [], []
+        for nid, node in idx.node_store.items():
+            for lvl, lst in node.neighbors.items():
+                keys.append((nid, lvl))
+                for pos, nb in enumerate(lst):
+                    rows.append((nid, lvl, pos, nb))
+        return np.array(rows, dtype=np.int64), np.array(keys, dtype=np.int64)
+
+    def run():
+        D = np.full((nq, k), np.inf, np.float32)
+        I = np.full((nq, k), -1, np.int64)
+        for qi in range(nq):
+            for j, (node, d) in enumerate(idx.search(Q[qi], k=k, ef=ef)):
+                D[qi, j], I[qi, j] = d, node.id
+        return D, I
+
+    graph0, keys0 = snap()
+    entry0, top0 = idx.entry_node_id, idx.max_level
+    assert top0 > max(idx.node_store[entry0].neighbors.keys()), "fixture lost its point: entry has all its keys"
+    D0, I0 = run()
+    for i in range(n, n + extra):
+        idx.insert_node(Node(id=i, embedding=X[i]))
+    graph1, keys1 = snap()
+    D1, I1 = run()
+    np.savez_compressed(os.path.join(OUT, "hnsw_toplevel.npz"), X=X, Q=Q, n=np.int64(n), M=np.int64(4), efc=np.int64(20),
+                        ef=np.int64(ef), k=np.int64(k), graph0=graph0, keys0=keys0, entry0=np.int64(entry0),
+                        top0=np.int64(top0), D0=D0, I0=I0, graph1=graph1, keys1=keys1, entry1=np.int64(idx.entry_node_id),
+                        top1=np.int64(idx.max_level), D1=D1, I1=I1)
+
+
 def gen_ivf(Storage, Node):
     """Reference IvfIndex (src/vector_db/indexing/ivf.py): build (kmeans2 on the seeded global numpy RNG),
     add, search at several n_probe, delete + search.  Blobs keep every cluster well populated."""
@@ -307,6 +351,7 @@ def main():
     gen_metadata_filter()
     gen_cosine(ref_dist, topk_sorted)
     gen_adc(ref_dist)
+    gen_hnsw_toplevel(ref_hnsw, Storage, Node)
     print("golden fixtures written to", os.path.abspath(OUT))
 
 
@@ -317,5 +362,6 @@ elif __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "pins":    
     _ref = _import_reference()
     gen_cosine(_ref[4], _ref[5])
     gen_adc(_ref[4])
+    gen_hnsw_toplevel(_ref[0], _ref[2], _ref[3])
 elif __name__ == "__main__":
     main()

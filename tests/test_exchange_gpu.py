@@ -66,9 +66,11 @@ def test_exchange_reports_a_missing_peer_instead_of_hanging():
     ex0 = PeerExchange(Q * k, dev, rank=0, world=world, buffers=bufs)
     d = torch.zeros((Q, k), device=dev)
     i = torch.zeros((Q, k), dtype=torch.int64, device=dev)
-    ex0.exchange_merge(d, i)                                # rank 1 never calls
+    out_d, out_i = ex0.exchange_merge(d, i)                 # rank 1 never calls
     with pytest.raises(RuntimeError, match="never arrived"):
         ex0.check()
+    # a timed-out exchange must not return a merge of stale slots: (inf, -1) instead
+    assert torch.isinf(out_d).all() and (out_i == -1).all()
 
 
 def test_exchange_rejects_bad_arguments():
@@ -80,3 +82,10 @@ def test_exchange_rejects_bad_arguments():
     with pytest.raises(ValueError, match="exceeds the exchange capacity"):
         ex.exchange_merge(torch.zeros((8, 4), device=dev), torch.zeros((8, 4), dtype=torch.int64, device=dev))  # 32 > cap
     assert ops.exchange_bytes(17, 16) == 0 and ops.exchange_bytes(0, 16) == 0
+    # the rejected call must not have advanced the arrival counters: the next valid call completes at once
+    assert ex.calls == 0 and ex.sent == [0, 0]
+    d = torch.rand((4, 4), device=dev).sort(dim=1).values
+    i = torch.arange(16, dtype=torch.int64, device=dev).view(4, 4)
+    od, oi = ex.exchange_merge(d, i)
+    ex.check()
+    assert torch.equal(od, d) and torch.equal(oi, i)

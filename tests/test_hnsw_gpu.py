@@ -198,3 +198,110 @@ def test_wave_parallel_builder_graph_invariants_and_recall():
     fast.storage.save(Node(id=100, embedding=X[0]))
     got = fast.search(X[0], k=1, ef=32)
     assert got and got[0][0].id == 100 and got[0][1] < 1e-6
+
+
+class _ScriptedRng:
+    """random.Random stand-in whose next draws are scripted (forces a level above the current top)."""
+
+    def __init__(self, draws):
+        self.draws = list(draws)
+
+    def random(self):
+        return self.draws.pop(0)
+
+
+def test_load_graph_whose_entry_lacks_top_level_keys(golden_dir, tmp_path):
+    """ADVICE r1 (high).  tests/golden/hnsw_toplevel.npz is a reference-built graph (Random(7), M=4) whose entry
+    point was inserted at level 6 above a top of 4: its pickle record has keys 0..4 while max_level = 6
+    (hnsw.py:179-191,215-217).  After load_graph the greedy descent must read the entry's OWN (empty) lists on
+    levels 5-6, results must equal the reference's, later inserts must reproduce the reference's graph, and an
+    insert ABOVE the top must link into fresh rows rather than into another node's lists."""
+    from vector_db_b200.indexing import HNSW
+    g = np.load(os.path.join(golden_dir, "hnsw_toplevel.npz"))
+    n, M, efc, k, ef = int(g["n"]), int(g["M"]), int(g["efc"]), int(g["k"]), int(g["ef"])
+    X, Q = g["X"], g["Q"]
+    store = {}
+    for nid, lvl in g["keys0"]:
+        store.setdefault(int(nid), {"id": int(nid), "neighbors": {}})["neighbors"][int(lvl)] = []
+    for nid, lvl, pos, nb in sorted(map(tuple, g["graph0"])):
+        store[int(nid)]["neighbors"][int(lvl)].append(int(nb))
+    store = {i: store[i] for i in range(n)}                                  # insertion order, as the pickle has it
+    data = {"M": M, "M_max": M, "M_max0": 2 * M, "ef_construction": efc, "max_level": int(g["top0"]),
+            "entry_node_id": int(g["entry0"]), "node_store": store}
+    entry = int(g["entry0"])
+    assert max(store[entry]["neighbors"]) < data["max_level"]               # the point of the fixture
+    rng = random.Random(7)
+    for _ in range(n):
+        rng.random()                                                         # the draws the reference build consumed
+    idx = HNSW(M=M, ef_construction=efc, rng=rng, index_file=tmp_path / "g.pkl")
+    for node in _nodes(X[:n]):
+        idx.storage.save(node)
+    idx.load_graph(data)
+    assert idx.entry_node_id == entry and idx.max_level == int(g["top0"])
+    assert sorted(idx.node_store[entry].neighbors) == sorted(store[entry]["neighbors"])     # keys 0..4 survive the load
+    D, I = idx.search_batch(Q, k, ef=ef)
+    np.testing.assert_array_equal(I, g["I0"])
+    np.testing.assert_allclose(D, g["D0"], rtol=1e-5, atol=1e-6)
+    # save -> load round trip through the pickle keeps the shape of the problem and the answers
+    idx.save_index()
+    idx2 = HNSW(M=M, ef_construction=efc, rng=random.Random(0), storage=idx.storage, index_file=tmp_path / "g.pkl")
+    assert idx2.max_level == int(g["top0"]) and sorted(idx2.node_store[entry].neighbors) == sorted(store[entry]["neighbors"])
+    np.testing.assert_array_equal(idx2.search_batch(Q, k, ef=ef)[1], g["I0"])
+    # the reference's next 60 inserts (same rng stream) on the loaded graph
+    idx.index_file = None
+    idx.build_index(_nodes(X[n:], ids=range(n, X.shape[0])))
+    np.testing.assert_array_equal(_graph_rows(idx), np.array(sorted(map(tuple, g["graph1"])), dtype=np.int64))
+    D1, I1 = idx.search_batch(Q, k, ef=ef)
+    np.testing.assert_array_equal(I1, g["I1"])
+    # an insert above the top: level = int(-ln(u) / ln(M)) = 8 for u = 1e-5; mirror it in the oracle restatement
+    o = HnswOracle(M, efc)
+    for nid in idx.node_store:
+        o.links[nid] = {l: list(v) for l, v in idx.node_store[nid].neighbors.items()}
+        o.vec[nid] = X[nid]
+    o.entry, o.max_level = idx.entry_node_id, idx.max_level
+    rs = np.random.default_rng(8)
+    new = rs.standard_normal((3, X.shape[1])).astype(np.float32)
+    draws = [1e-5, 0.9, 2e-4]                                                # levels 8, 0, 6
+    idx.rng = _ScriptedRng(draws)
+    o.rng = _ScriptedRng(draws)
+    for j in range(3):
+        idx.insert_node(_nodes(new[j:j + 1], ids=[9000 + j])[0])
+        o.insert(9000 + j, new[j])
+    assert idx.entry_node_id == o.entry == 9000 and idx.max_level == o.max_level == 8
+    rows = sorted((nid, lvl, pos, nb) for nid, d in o.links.items() for lvl, lst in d.items() for pos, nb in enumerate(lst))
+    np.testing.assert_array_equal(_graph_rows(idx), np.array(rows, dtype=np.int64))
+    for qi in range(Q.shape[0]):
+        assert [r[1] for r in o.search(Q[qi], k, ef)] == [i for i in idx.search_batch(Q[qi], k, ef=ef)[1][0].tolist() if i >= 0]
+
+
+def test_selective_filter_falls_back_to_exact_masked_scan():
+    """ADVICE r1 (medium).  The reference walks on until `ef` MATCHING nodes are found, keeping every evaluated node
+    as a candidate (hnsw.py:102-131): with fewer than ef matches it visits the whole component and returns every
+    match.  The bounded frontier / visited table cannot, so such searches are answered by the exact masked scan
+    over the allowed rows -- every match, in (distance, id) order -- instead of raising or returning fewer."""
+    from vector_db_b200.indexing import HNSW
+    rng = np.random.default_rng(21)
+    n, dim = 6000, 24
+    X = rng.standard_normal((n, dim)).astype(np.float32)
+    Q = rng.standard_normal((12, dim)).astype(np.float32)
+    idx = HNSW(M=8, ef_construction=40, rng=random.Random(42))
+    idx.build_from_arrays(range(n), X, save_to_storage=False)
+    for allowed in ({5, 77, 1234, 4000, 5999}, set(range(0, n, 150))):       # 5 and 40 matches, both < ef = 50
+        D, I = idx.search_batch(Q, 10, ef=50, filter_ids=allowed)
+        ids = np.array(sorted(allowed))
+        for qi in range(Q.shape[0]):
+            d = np.sqrt(((X[ids] - Q[qi]) ** 2).sum(axis=1))
+            order = np.lexsort((ids, d))[:10]
+            want = ids[order].tolist()
+            assert [i for i in I[qi].tolist() if i >= 0] == want
+            np.testing.assert_allclose(D[qi][:len(want)], d[order], rtol=1e-5)
+    # ef <= matches < frontier capacity: still the reference's traversal (oracle restatement), not the fallback
+    o = HnswOracle(8, 40)
+    for nid in idx.node_store:
+        o.links[nid] = {l: list(v) for l, v in idx.node_store[nid].neighbors.items()}
+        o.vec[nid] = X[nid]
+    o.entry, o.max_level = idx.entry_node_id, idx.max_level
+    allowed = set(range(0, n, 3))
+    D, I = idx.search_batch(Q, 10, ef=50, filter_ids=allowed)
+    for qi in range(Q.shape[0]):
+        assert [r[1] for r in o.search(Q[qi], 10, 50, allowed)] == [i for i in I[qi].tolist() if i >= 0]

@@ -84,15 +84,24 @@ exchange_merge_kernel(const XchgArgs a) {
         red_release_sys_add(reinterpret_cast<uint32_t*>(a.peer[tid]) + a.parity * kXMaxWorld + a.rank, 1u);
 
     // ---- phase 2: wait for every rank's CTAs, then merge my share of the queries
+    int gave_up = 0;
     if (tid < a.world) {
         const uint32_t* f = reinterpret_cast<const uint32_t*>(a.peer[a.rank]) + a.parity * kXMaxWorld + tid;
         const long long t0 = clock64();
         while ((int32_t)(ld_acquire_sys(f) - a.target) < 0) {
-            if (clock64() - t0 > kXSpinLimit) { atomicExch(a.status, 1); break; }
+            if (clock64() - t0 > kXSpinLimit) { atomicExch(a.status, 1); gave_up = 1; break; }
             __nanosleep(100);
         }
     }
-    __syncthreads();
+    if (__syncthreads_or(gave_up)) {
+        // a peer never arrived: its slot holds a previous call's lists (or nothing).  Merging them would return a
+        // plausible, WRONG answer -- return (inf, -1) for this CTA's queries; status tells the host (PeerExchange.check)
+        for (long long e = e0 + tid; e < e1; e += kXThreads) {
+            a.out_d[e] = a.descending ? -INFINITY : INFINITY;
+            a.out_i[e] = -1;
+        }
+        return;
+    }
 
     const int total = a.world * a.k;
     const unsigned char* mine = reinterpret_cast<const unsigned char*>(a.peer[a.rank]) + slot;

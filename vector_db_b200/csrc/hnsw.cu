@@ -31,6 +31,7 @@ struct Graph {
     int deg_up;
     const int32_t* up_ptr;
     const uint32_t* alive;
+    const int32_t* levels;     // per-row top level (nullable): a list above it does not exist
 };
 
 struct BeamMem {
@@ -50,6 +51,10 @@ __device__ __forceinline__ bool bit_set(const uint32_t* bm, int r) { return (bm[
 
 __device__ __forceinline__ const int32_t* nbr_list(const Graph& g, int node, int level, int* deg) {
     if (level == 0) { *deg = g.deg0; return g.adj0 + (size_t)node * g.deg0; }
+    // The reference creates neighbors[l] only for l <= the top level at insert time (hnsw.py:179-191), so the entry
+    // point can lack its top lists; a level above the rows reserved for `node` reads as an empty list
+    // (neighbors.get(level, []), hnsw.py:113) instead of running into the next node's rows.
+    if (g.levels != nullptr && level > g.levels[node]) { *deg = 0; return g.adj_up; }
     *deg = g.deg_up;
     return g.adj_up + ((size_t)g.up_ptr[node] + level - 1) * g.deg_up;
 }
@@ -312,12 +317,18 @@ __device__ int beam_search(const Graph& g, BeamMem& m, int entry, int level, int
             if (pos < m.CC) cdst[pos] = key;
         }
         int ncand_new = keep_old + keep_new;
-        if (ncand_new > m.CC) ncand_new = m.CC;
+        if (ncand_new > m.CC) {
+            // Only possible with a filter (without one the frontier never outgrows ef): the reference's heap is
+            // unbounded, so entries dropped here could have been expanded -- flag the query, the host finishes it
+            // with the exact masked scan over the allowed rows (ops.hnsw_search).
+            ncand_new = m.CC;
+            if (tid == 0) m.scal[1] |= 2;
+        }
         __syncthreads();
         cc ^= 1;
         ncand = ncand_new;
         if (nvisited + (unsigned)m.scal[2] > (unsigned)(m.H - (m.H >> 2))) {   // visited table above 75% load
-            if (tid == 0) m.scal[1] = 1;
+            if (tid == 0) m.scal[1] |= 1;
             break;
         }
     }
@@ -360,7 +371,7 @@ __global__ void __launch_bounds__(kHnswThreads)
 hnsw_search_kernel(Graph g, const float* __restrict__ q, int Q, int32_t entry_row, int max_level, int ef, int k,
                    const uint32_t* __restrict__ filter, int CC, int NM, int H, uint32_t* global_hash,
                    float* __restrict__ out_d, int32_t* __restrict__ out_rows, uint32_t* __restrict__ out_stats,
-                   int* __restrict__ overflow_flag) {
+                   int32_t* __restrict__ out_status, int* __restrict__ overflow_flag) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     BeamMem m;
     carve(m, smem_raw, g.D, CC, ef, NM, H, global_hash ? global_hash + (size_t)blockIdx.x * H : nullptr);
@@ -375,7 +386,10 @@ hnsw_search_kernel(Graph g, const float* __restrict__ q, int Q, int32_t entry_ro
             int cur = entry_row;
             for (int level = max_level; level >= 1; --level) cur = greedy_level(g, m, cur, level, &evals);
             nfound = beam_search(g, m, cur, 0, ef, filter, &wf, &evals, &expansions);
-            if (m.scal[1] && tid == 0) atomicExch(overflow_flag, 1);
+            if (m.scal[1] && tid == 0) atomicOr(overflow_flag, m.scal[1]);
+            if (out_status && tid == 0) out_status[qi] = m.scal[1];      // bit 0 visited table full, bit 1 frontier cut
+        } else if (out_status && tid == 0) {
+            out_status[qi] = 0;
         }
         for (int i = tid; i < k; i += kHnswThreads) {
             size_t o = (size_t)qi * k + i;
@@ -435,7 +449,7 @@ hnsw_insert_kernel(Graph g, const int32_t* __restrict__ levels, int32_t first, i
         for (int level = (lvl < top ? lvl : top); level >= 0; --level) {
             int wf = 0;
             const int nf = beam_search(g, m, cur, level, efc, nullptr, &wf, &evals, &expansions);
-            if (m.scal[1] && tid == 0) atomicExch(overflow_flag, 1);
+            if (m.scal[1] && tid == 0) atomicOr(overflow_flag, 1);
             const u64* found = m.found[wf];
             const int nsel = nf < M ? nf : M;
             int deg;
@@ -526,7 +540,7 @@ hnsw_build_search_kernel(Graph g, const int32_t* __restrict__ nodes, int count, 
         // on the level above): enter through its closest upper-level neighbour that is, else the seed
         int deg;
         const int32_t* mine = nbr_list(g, cur, level, &deg);
-        if (cur == node || __ldcg(mine) < 0) {
+        if (cur == node || deg == 0 || __ldcg(mine) < 0) {
             int pick = seed_entry;
             if (level < max_level) {
                 int dup;
@@ -535,14 +549,15 @@ hnsw_build_search_kernel(Graph g, const int32_t* __restrict__ nodes, int count, 
                     const int r = __ldcg(up + p);
                     if (r < 0) break;
                     int d2;
-                    if (r != node && __ldcg(nbr_list(g, r, level, &d2)) >= 0) { pick = r; break; }
+                    const int32_t* rl = nbr_list(g, r, level, &d2);
+                    if (r != node && d2 > 0 && __ldcg(rl) >= 0) { pick = r; break; }
                 }
             }
             cur = pick;
         }
         int wf = 0;
         const int nf = beam_search(g, m, cur, level, efc, nullptr, &wf, &evals, &expansions);
-        if (m.scal[1] && tid == 0) atomicExch(overflow_flag, 1);
+        if (m.scal[1] && tid == 0) atomicOr(overflow_flag, 1);
         const u64* found = m.found[wf];
         // the node itself can be reached (it is linked on the upper levels): skip it
         if (tid == 0) {
@@ -631,8 +646,9 @@ size_t vdb_hnsw_search_workspace(int Q, int ef, int deg0) {
 
 int vdb_hnsw_search(const float* q, int Q, const float* db, int64_t N, int D, const int32_t* adj0, int deg0,
                     const int32_t* adj_up, int deg_up, const int32_t* up_ptr, int32_t entry_row, int max_level, int ef,
-                    int k, const uint32_t* alive, const uint32_t* filter, int hash_slots, float* out_d,
-                    int32_t* out_rows, uint32_t* out_stats, void* ws, size_t ws_bytes, void* stream) {
+                    int k, const uint32_t* alive, const uint32_t* filter, const int32_t* levels, int hash_slots,
+                    float* out_d, int32_t* out_rows, uint32_t* out_stats, int32_t* out_status, void* ws, size_t ws_bytes,
+                    void* stream) {
     VDB_REQUIRE(Q >= 0 && D > 0 && ef > 0 && k > 0 && deg0 > 0, VDB_ERR_INVALID, "vdb_hnsw_search: bad shape");
     VDB_REQUIRE(ef <= 1024, VDB_ERR_UNSUPPORTED, "ef=%d > 1024", ef);
     VDB_REQUIRE(deg0 <= 128 && deg_up <= 128, VDB_ERR_UNSUPPORTED, "degree > 128");
@@ -643,9 +659,11 @@ int vdb_hnsw_search(const float* q, int Q, const float* db, int64_t N, int D, co
     VDB_REQUIRE(entry_row < 0 || (db && adj0), VDB_ERR_INVALID, "vdb_hnsw_search: null graph");
     VDB_REQUIRE(max_level <= 0 || (adj_up && up_ptr), VDB_ERR_INVALID, "vdb_hnsw_search: upper levels missing");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    Graph g{db, N, D, adj0, deg0, adj_up, deg_up, up_ptr, alive};
+    Graph g{db, N, D, adj0, deg0, adj_up, deg_up, up_ptr, alive, levels};
     const int NM = (deg0 > deg_up ? deg0 : deg_up) + 1;
-    const int CC = filter ? (2 * ef > 256 ? 2 * ef : 256) : ef;
+    // filtered: the reference's heap is unbounded; 4 ef (>= 512) entries cover a filter that passes ~1 row in 8
+    // before the beam fills, anything beyond is flagged (out_status bit 1) and finished by the exact masked scan
+    const int CC = filter ? (4 * ef > 512 ? 4 * ef : 512) : ef;
     int H = hash_slots ? hash_slots : pick_hash_slots(ef, deg0);
     size_t smem_with = beam_smem_bytes(D, CC, ef, NM, H);
     size_t smem_without = beam_smem_bytes(D, CC, ef, NM, 0);
@@ -670,7 +688,7 @@ int vdb_hnsw_search(const float* q, int Q, const float* db, int64_t N, int D, co
     VDB_CUDA(cudaMemsetAsync(flag, 0, 4, st));
     ProfScope prof(kProfHnswSearch, st);
     hnsw_search_kernel<<<grid, kHnswThreads, smem, st>>>(g, q, Q, entry_row, max_level, ef, k, filter, CC, NM, H, ghash,
-                                                         out_d, out_rows, out_stats, flag);
+                                                         out_d, out_rows, out_stats, out_status, flag);
     count_launch(1);
     VDB_CUDA(cudaGetLastError());
     return VDB_OK;
@@ -693,7 +711,7 @@ int vdb_hnsw_build_search(const float* db, int64_t N, int D, const int32_t* adj0
     VDB_REQUIRE(db && adj0 && adj_up && up_ptr && nodes && out_rows && out_d && ws && ws_bytes >= 256, VDB_ERR_INVALID,
                 "vdb_hnsw_build_search: null pointer");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    Graph g{db, N, D, adj0, deg0, adj_up, deg_up, up_ptr, nullptr};
+    Graph g{db, N, D, adj0, deg0, adj_up, deg_up, up_ptr, nullptr, nullptr};
     const int NM = (deg0 > deg_up ? deg0 : deg_up) + 1;
     const int CC = efc;
     const int H = pick_hash_slots(efc, level == 0 ? deg0 : deg_up);
@@ -750,7 +768,7 @@ int vdb_hnsw_insert(const float* db, int64_t N, int D, int32_t* adj0, int deg0, 
     VDB_REQUIRE(db && adj0 && adj_up && up_ptr && levels && state && ws && ws_bytes >= 256, VDB_ERR_INVALID,
                 "vdb_hnsw_insert: null pointer");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    Graph g{db, N, D, adj0, deg0, adj_up, deg_up, up_ptr, alive};
+    Graph g{db, N, D, adj0, deg0, adj_up, deg_up, up_ptr, alive, levels};
     const int NM = (deg0 > deg_up ? deg0 : deg_up) + 1;
     const int CC = efc;
     const int H = pick_hash_slots(efc, deg0);
@@ -767,7 +785,8 @@ int vdb_hnsw_insert(const float* db, int64_t N, int D, int32_t* adj0, int deg0, 
         ghash = reinterpret_cast<uint32_t*>(static_cast<char*>(ws) + 256);
     }
     VDB_CUDA(cudaFuncSetAttribute(hnsw_insert_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    VDB_CUDA(cudaMemsetAsync(flag, 0, 4, st));
+    // the overflow flag (first word of ws) is STICKY over the chunks of a build: the caller zeroes it once before
+    // the first chunk and reads it once after the last (a per-call memset erased an overflow of an earlier chunk)
     ProfScope prof(kProfHnswInsert, st);
     hnsw_insert_kernel<<<1, kHnswThreads, smem, st>>>(g, levels, first, count, M, efc, state, CC, NM, H, ghash, flag);
     count_launch(1);

@@ -216,6 +216,7 @@ class HNSW:
             nbytes = lib.vdb_hnsw_insert_workspace(self.ef_construction, self.M_max0)
             ws = ops._ws("hnsw_insert", nbytes, self._device)
             vec = self._vectors
+            ws[:4].zero_()                                      # sticky overflow flag of vdb_hnsw_insert: zeroed once
             for s in range(first, n, _INSERT_CHUNK):
                 cnt = min(_INSERT_CHUNK, n - s)
                 _lib.check(lib.vdb_hnsw_insert(
@@ -432,7 +433,7 @@ class HNSW:
             alive = vec.alive if vec.n_dead else None
             kk = min(k, ef)
             d, r, st = ops.hnsw_search(q, vec.vecs, vec.n, self._adj0, self._adj_up, self._up_ptr_dev, entry_row, top,
-                                       ef, kk, alive=alive, flt=flt, want_stats=return_stats)
+                                       ef, kk, alive=alive, flt=flt, want_stats=return_stats, levels=self._levels_dev)
             ids = torch.where(r >= 0, vec.ids[r.clamp(min=0).long()], torch.full_like(r, -1, dtype=torch.int64))
             d_h, i_h = d.cpu().numpy(), ids.cpu().numpy()
             if kk < k:
@@ -506,6 +507,13 @@ class HNSW:
             for nid in ids:
                 nb = store[nid]["neighbors"]
                 levels.append(max(nb.keys()) if nb else 0)
+            # The reference gives a node inserted above the old top NO lists for the levels above it
+            # (hnsw.py:179-191) but makes it the entry point at its full level (hnsw.py:215-217): the pickle then
+            # carries max_level > max(entry's keys).  Reserve the entry's rows up to max_level (empty lists) so the
+            # greedy descent reads its own rows, and later inserts at those levels link into them.
+            entry = data["entry_node_id"]
+            if entry is not None and entry in row:
+                levels[row[entry]] = max(levels[row[entry]], int(data["max_level"]))
             up_ptr = np.zeros(n + 1, dtype=np.int64)
             up_ptr[1:] = np.cumsum(levels)
             adj0 = np.full((n, self.M_max0), -1, dtype=np.int32)
@@ -524,7 +532,6 @@ class HNSW:
             self._adj_up[:adj_up.shape[0]].copy_(torch.from_numpy(adj_up))
             self._levels_dev[:n].copy_(torch.tensor(self._levels, dtype=torch.int32))
             self._up_ptr_dev[:n + 1].copy_(torch.from_numpy(up_ptr.astype(np.int32)))
-            entry = data["entry_node_id"]
             st = (row[entry] if entry is not None else -1, int(data["max_level"]))
             self._state[:2].copy_(torch.tensor(st, dtype=torch.int32))
             self._state_host = st

@@ -272,11 +272,29 @@ def exchange_merge_topk(d: torch.Tensor, i: torch.Tensor, peer_bufs: torch.Tenso
     return out_d, out_i
 
 
+def _popcount_words(words: torch.Tensor) -> int:
+    """Set bits of an int32 bitmap (one small reduction + a synchronising read)."""
+    b = words.view(torch.uint8).to(torch.int32)
+    b = (b & 0x55) + ((b >> 1) & 0x55)
+    b = (b & 0x33) + ((b >> 2) & 0x33)
+    b = (b & 0x0F) + (b >> 4)
+    return int(b.sum().item())
+
+
 def hnsw_search(q: torch.Tensor, db: torch.Tensor, n_rows: int, adj0: torch.Tensor, adj_up: torch.Tensor,
                 up_ptr: torch.Tensor, entry_row: int, max_level: int, ef: int, k: int,
-                alive: Optional[torch.Tensor] = None, flt: Optional[torch.Tensor] = None, want_stats: bool = False):
+                alive: Optional[torch.Tensor] = None, flt: Optional[torch.Tensor] = None, want_stats: bool = False,
+                levels: Optional[torch.Tensor] = None):
     """Batched graph search.  Returns (dist f32 [Q,k], rows i32 [Q,k], stats u32 [Q,2] | None).
-    Synchronises once to read the visited-table overflow flag and retries with a larger table."""
+    Synchronises once to read the status word; a full visited table is retried with a larger table.
+
+    Filtered search (``flt``: row bitmap, bit set = allowed).  The reference keeps EVERY evaluated node in its
+    candidate heap and walks on until ``ef`` matches are found (hnsw.py:102-131), i.e. through the whole
+    component when fewer than ``ef`` rows match.  The kernel's frontier is bounded, so:
+      * fewer than ``ef`` allowed rows -> the beam can never fill; the answer is the exact masked scan over the
+        allowed rows (what the exhaustive walk returns on a connected graph, a superset otherwise), run directly;
+      * a query whose frontier had to drop candidates, or whose visited table filled up, is finished the same way.
+    Envelope: every other filtered query is the reference's traversal, step for step."""
     q = _f32(q, "q")
     Q, D = q.shape
     dev = q.device
@@ -286,14 +304,37 @@ def hnsw_search(q: torch.Tensor, db: torch.Tensor, n_rows: int, adj0: torch.Tens
     lib = load()
     deg0 = adj0.shape[1]
     deg_up = adj_up.shape[1] if adj_up is not None and adj_up.dim() == 2 else deg0 // 2
+
+    def masked_scan(sel: Optional[torch.Tensor]):
+        words = (max(n_rows, 1) + 31) // 32
+        mask = flt[:words]
+        if alive is not None:
+            mask = torch.bitwise_and(mask, alive[:words])
+        qq = q if sel is None else q[sel]
+        d, r = exact_topk_f32(qq, db, k, METRIC_L2, row_mask=mask.contiguous(), n_rows=n_rows)
+        if sel is None:
+            out_d.copy_(d)
+            out_r.copy_(r.to(torch.int32))
+        else:
+            out_d[sel] = d
+            out_r[sel] = r.to(torch.int32)
+
+    if flt is not None and Q > 0 and _popcount_words(flt[:(max(n_rows, 1) + 31) // 32]) < ef:
+        masked_scan(None)
+        return out_d, out_r, stats
+    status = torch.zeros((Q,), dtype=torch.int32, device=dev)
     nbytes = lib.vdb_hnsw_search_workspace(Q, ef, deg0)
     hash_slots = 0
-    for _ in range(4):
+    for attempt in range(4):
         ws = _ws("hnsw", nbytes, dev)
         check(lib.vdb_hnsw_search(ptr(q), Q, ptr(db), n_rows, D, ptr(adj0), deg0, ptr(adj_up), deg_up, ptr(up_ptr),
-                                  entry_row, max_level, ef, k, ptr(alive), ptr(flt), hash_slots, ptr(out_d),
-                                  ptr(out_r), ptr(stats), ptr(ws), ws.numel(), _lib.stream_ptr(dev)))
-        if int(ws[:4].view(torch.int32).item()) == 0:
+                                  entry_row, max_level, ef, k, ptr(alive), ptr(flt), ptr(levels), hash_slots, ptr(out_d),
+                                  ptr(out_r), ptr(stats), ptr(status), ptr(ws), ws.numel(), _lib.stream_ptr(dev)))
+        flag = int(ws[:4].view(torch.int32).item()) if Q else 0
+        if flag == 0:
+            return out_d, out_r, stats
+        if flt is not None and (flag & 2 or attempt >= 1):
+            masked_scan(torch.nonzero(status).flatten())
             return out_d, out_r, stats
         # a visited table filled up: force a (4x) larger table in global memory and retry
         base = 1024

@@ -96,13 +96,18 @@ class PeerExchange:
                        ) -> Tuple[torch.Tensor, torch.Tensor]:
         from . import ops
         parity = self.calls & 1
-        self.sent[parity] += ops.exchange_grid(d.shape[0])
+        target = self.sent[parity] + ops.exchange_grid(d.shape[0])
+        # the call validates its arguments before it launches: the counters move only once the kernel is enqueued,
+        # so a ValueError (Q*k over the capacity, ...) does not leave the arrival target ahead of what was pushed
+        out = ops.exchange_merge_topk(d, i, self.peers, self.rank, self.world, self.cap, parity, target,
+                                      self.status, descending)
+        self.sent[parity] = target
         self.calls += 1
-        return ops.exchange_merge_topk(d, i, self.peers, self.rank, self.world, self.cap, parity, self.sent[parity],
-                                       self.status, descending)
+        return out
 
     def check(self) -> None:
-        """Synchronising: raise if any call so far gave up waiting for a peer."""
+        """Synchronising: raise if any call so far gave up waiting for a peer (such a call returned (inf, -1)
+        lists for the affected queries, never a merge of stale slots).  Call it wherever the results are read."""
         if int(self.status.item()) != 0:
             raise RuntimeError("shard exchange: a peer never arrived (wait ran into its clock limit)")
 
