@@ -61,6 +61,15 @@ int vdb_profile_read(int slot, int* launches, float* total_ms);
 int vdb_stage_aos_h2d(const void* host_records /*[host,pinned]*/, int64_t n, int D,
                       int64_t* ids /*[dev] n*/, float* vecs /*[dev] n*D*/, void* stream);
 
+/* The same upload from PAGEABLE memory -- the memmap of the reference's `.embeddings.npy` file itself
+ * (storage.py:135-144): `threads` host threads copy record slices into a caller-owned ring of `depth` pinned buffers
+ * of `buffer_bytes` each while the copy engine drains the previous buffers with the two strided DMA copies above.
+ * Returns after the last copy has left the ring (the device arrays are then complete on `stream`). */
+int vdb_stage_aos_pageable_h2d(const void* records /*[host,pageable] n records*/, int64_t n, int D,
+                               int64_t* ids /*[dev] n or NULL*/, float* vecs /*[dev] n*D*/,
+                               void* pinned_ring /*[host,pinned] depth*buffer_bytes*/, size_t buffer_bytes, int depth,
+                               int threads, void* stream);
+
 /* Per-row squared norms and the bf16 mirror used by the tensor-core scan.
  * Either output may be NULL. */
 int vdb_prepare_rows(const float* vecs /*[dev] N*D*/, int64_t N, int D,

@@ -3,8 +3,11 @@
 // (squared norms + bf16 mirror) that feeds the tensor-core scan.
 #include <stdarg.h>
 
+#include <string.h>
+
 #include <atomic>
 #include <mutex>
+#include <thread>
 #include <utility>
 #include <vector>
 
@@ -148,6 +151,71 @@ int vdb_stage_aos_h2d(const void* host_records, int64_t n, int D, int64_t* ids, 
     VDB_CUDA(cudaMemcpy2DAsync(vecs, 4 * (size_t)D, base + 8, stride, 4 * (size_t)D, (size_t)n,
                                cudaMemcpyHostToDevice, s));
     return VDB_OK;
+}
+
+// Pageable source (the memmap itself): worker threads fill a ring of pinned buffers while the copy engine drains the
+// previous ones.  A single-threaded fill runs at one core's page-cache memcpy rate (a few GB/s), an order of
+// magnitude under the PCIe rate of the strided DMA that follows it -- the fill, not the link, bounded the upload.
+int vdb_stage_aos_pageable_h2d(const void* records, int64_t n, int D, int64_t* ids, float* vecs, void* pinned_ring,
+                               size_t buffer_bytes, int depth, int threads, void* stream) {
+    VDB_REQUIRE(n >= 0 && D > 0, VDB_ERR_INVALID, "vdb_stage_aos_pageable_h2d: bad n=%lld D=%d", (long long)n, D);
+    if (n == 0) return VDB_OK;
+    const size_t stride = 8 + 4 * (size_t)D;
+    VDB_REQUIRE(records && vecs && pinned_ring, VDB_ERR_INVALID, "vdb_stage_aos_pageable_h2d: null pointer");
+    VDB_REQUIRE(depth >= 2 && depth <= 16 && buffer_bytes >= stride, VDB_ERR_INVALID,
+                "vdb_stage_aos_pageable_h2d: ring of %d x %zu bytes cannot hold a record of %zu", depth, buffer_bytes, stride);
+    if (threads < 1) threads = 1;
+    if (threads > 64) threads = 64;
+    const int64_t per_buf = (int64_t)(buffer_bytes / stride);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    std::vector<cudaEvent_t> done((size_t)depth, nullptr);
+    int rc = VDB_OK;
+    const char* src = static_cast<const char*>(records);
+    char* ring = static_cast<char*>(pinned_ring);
+    int64_t chunk_i = 0;
+    for (int64_t s = 0; s < n && rc == VDB_OK; s += per_buf, ++chunk_i) {
+        const int64_t cnt = (n - s < per_buf) ? n - s : per_buf;
+        const int b = (int)(chunk_i % depth);
+        char* buf = ring + (size_t)b * buffer_bytes;
+        if (done[b]) {                                   // the DMA that last read this buffer has finished
+            if (cudaEventSynchronize(done[b]) != cudaSuccess) { rc = cuda_fail(cudaGetLastError(), "event wait", __FILE__, __LINE__); break; }
+        } else if (cudaEventCreateWithFlags(&done[b], cudaEventDisableTiming) != cudaSuccess) {
+            rc = cuda_fail(cudaGetLastError(), "event create", __FILE__, __LINE__);
+            break;
+        }
+        const size_t bytes = (size_t)cnt * stride;
+        const char* from = src + (size_t)s * stride;
+        int nt = threads;
+        if ((size_t)nt * (1u << 20) > bytes) nt = (int)(bytes >> 20) + 1;      // at least 1 MB per thread
+        if (nt <= 1) {
+            memcpy(buf, from, bytes);
+        } else {
+            std::vector<std::thread> pool;
+            pool.reserve((size_t)nt);
+            const size_t per = ((bytes / (size_t)nt) + 4095) & ~(size_t)4095;  // page-aligned slices
+            for (int t = 0; t < nt; ++t) {
+                const size_t o = (size_t)t * per;
+                if (o >= bytes) break;
+                const size_t len = (o + per < bytes) ? per : bytes - o;
+                pool.emplace_back([=] { memcpy(buf + o, from + o, len); });
+            }
+            for (auto& th : pool) th.join();
+        }
+        cudaError_t e = cudaSuccess;
+        if (ids) e = cudaMemcpy2DAsync(ids + s, 8, buf, stride, 8, (size_t)cnt, cudaMemcpyHostToDevice, st);
+        if (e == cudaSuccess)
+            e = cudaMemcpy2DAsync(vecs + (size_t)s * D, 4 * (size_t)D, buf + 8, stride, 4 * (size_t)D, (size_t)cnt,
+                                  cudaMemcpyHostToDevice, st);
+        if (e == cudaSuccess) e = cudaEventRecord(done[b], st);
+        if (e != cudaSuccess) rc = cuda_fail(e, "strided H2D copy", __FILE__, __LINE__);
+    }
+    // the ring belongs to the caller, who may free it on return: drain the copies that still read it
+    for (auto ev : done) {
+        if (!ev) continue;
+        if (rc == VDB_OK && cudaEventSynchronize(ev) != cudaSuccess) rc = cuda_fail(cudaGetLastError(), "event wait", __FILE__, __LINE__);
+        cudaEventDestroy(ev);
+    }
+    return rc;
 }
 
 int vdb_prepare_rows(const float* vecs, int64_t N, int D, float* sqnorm, void* bf16_mirror, void* stream) {

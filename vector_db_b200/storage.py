@@ -218,10 +218,15 @@ class MMapNodeStorage(NodeStorage):
         self.metadata.flush()
 
     # -- HBM staging ----------------------------------------------------------------------------
-    def stage_to_device(self, device=None, chunk_records: int = 65536) -> Tuple["torch.Tensor", "torch.Tensor"]:
+    def stage_to_device(self, device=None, chunk_records: int = 65536, threads: Optional[int] = None, depth: int = 3
+                        ) -> Tuple["torch.Tensor", "torch.Tensor"]:
         """Upload every valid record to HBM as SoA tensors ``(ids i64 [n], vecs f32 [n,dim])`` in slot
-        order.  Records travel memmap -> pinned ring (2 buffers) -> strided DMA that splits the
-        id and embedding columns (vdb_stage_aos_h2d); invalid slots are dropped on the device."""
+        order.  Records travel memmap -> ring of ``depth`` pinned buffers, filled by ``threads`` host threads
+        (vdb_stage_aos_pageable_h2d) -> strided DMA that splits the id and embedding columns; invalid slots are
+        dropped on the device.  ``self.last_stage`` records bytes / seconds of the last upload."""
+        import os
+        import time
+
         import torch
 
         from . import _lib
@@ -235,21 +240,21 @@ class MMapNodeStorage(NodeStorage):
             return ids, vecs
         rec = self.embeddings.dtype.itemsize
         chunk = max(1, min(chunk_records, hw))
-        ring = [torch.empty(chunk * rec, dtype=torch.uint8).pin_memory() for _ in range(2)]
-        events = [None, None]
+        depth = max(2, min(int(depth), 16))
+        if threads is None:
+            threads = max(1, min(16, (os.cpu_count() or 2) // 2))
+        ring = getattr(self, "_stage_ring", None)
+        if ring is None or ring.numel() < depth * chunk * rec:
+            ring = self._stage_ring = torch.empty(depth * chunk * rec, dtype=torch.uint8).pin_memory()
         stream = torch.cuda.current_stream(dev)
         raw = self.embeddings.view(np.uint8).reshape(self.capacity, rec)
-        for n, s in enumerate(range(0, hw, chunk)):
-            cnt = min(chunk, hw - s)
-            buf = ring[n & 1]
-            if events[n & 1] is not None:
-                events[n & 1].synchronize()          # the DMA that last read this buffer is done
-            buf.numpy()[:cnt * rec].reshape(cnt, rec)[:] = raw[s:s + cnt]
-            _lib.check(lib.vdb_stage_aos_h2d(buf.data_ptr(), cnt, self.dim, ids[s:].data_ptr(), vecs[s:].data_ptr(),
-                                             stream.cuda_stream))
-            ev = torch.cuda.Event()
-            ev.record(stream)
-            events[n & 1] = ev
+        t0 = time.perf_counter()
+        _lib.check(lib.vdb_stage_aos_pageable_h2d(raw.ctypes.data, hw, self.dim, ids.data_ptr(), vecs.data_ptr(),
+                                                  ring.data_ptr(), chunk * rec, depth, int(threads), stream.cuda_stream))
+        stream.synchronize()
+        dt = time.perf_counter() - t0
+        self.last_stage = {"bytes": hw * rec, "seconds": dt, "gb_per_s": hw * rec / dt / 1e9, "threads": int(threads),
+                           "depth": depth, "chunk_bytes": chunk * rec}
         valid = (ids >= 0) & (vecs != 0).any(dim=1)
         if bool(valid.all()):
             return ids, vecs
