@@ -243,18 +243,23 @@ class HNSW:
         with self._lock:
             if self._graph_ids:
                 raise ValueError("build_from_arrays builds from scratch: the index already holds nodes")
-            X = np.ascontiguousarray(vectors, dtype=np.float32)
+            on_device = isinstance(vectors, torch.Tensor) and vectors.is_cuda     # rows already in HBM (staged / generated)
+            X = vectors.to(torch.float32).contiguous() if on_device else np.ascontiguousarray(vectors, dtype=np.float32)
             ids = [int(i) for i in ids]
             n, dim = X.shape
             if len(set(ids)) != n:
                 raise ValueError("ids must be unique and match the rows of `vectors`")
             if save_to_storage:
+                Xh = X.cpu().numpy() if on_device else X
                 for i, nid in enumerate(ids):
-                    self.storage.save(Node(id=nid, embedding=X[i]))
+                    self.storage.save(Node(id=nid, embedding=Xh[i]))
             dev = self._device
             self._reset_graph(dim=None)
             self._vectors = DeviceVectors(dim, dev, capacity=n)
-            self._vectors.append(ids, X)
+            if on_device:
+                self._vectors.append_device(torch.as_tensor(ids, dtype=torch.int64, device=dev), X)
+            else:
+                self._vectors.append(ids, X)
             levels = np.fromiter((self.sample_level() for _ in range(n)), dtype=np.int64, count=n)
             top = int(levels.max())
             up_ptr = np.zeros(n + 1, dtype=np.int64)

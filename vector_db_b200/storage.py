@@ -94,10 +94,12 @@ _META_CHARS = 5120
 class MMapNodeStorage(NodeStorage):
     """Two-layer memmap storage, byte-compatible with the reference's files."""
 
-    def __init__(self, embedding_file: Union[str, Path], metadata_file: Union[str, Path], dim: int,
+    def __init__(self, embedding_file: Union[str, Path], metadata_file: Optional[Union[str, Path]], dim: int,
                  capacity: int = 1_000_000):
+        """``metadata_file=None`` opens layer 1 only (embeddings: what ``stage_to_device`` / ``get_embedding`` need);
+        ``save`` / ``get`` / ``delete`` then leave layer 2 alone."""
         self.embedding_file = Path(embedding_file)
-        self.metadata_file = Path(metadata_file)
+        self.metadata_file = Path(metadata_file) if metadata_file is not None else None
         self.dim = dim
         self.capacity = capacity
         self._init_embedding_memmap()
@@ -131,6 +133,9 @@ class MMapNodeStorage(NodeStorage):
 
     # -- layer 2 ------------------------------------------------------------------------------
     def _init_metadata_memmap(self) -> None:
+        if self.metadata_file is None:
+            self.metadata = None
+            return
         mode = "r+" if self.metadata_file.exists() else "w+"
         dtype = np.dtype([("id", np.int64), ("content", f"U{_CONTENT_CHARS}"), ("metadata_json", f"U{_META_CHARS}")])
         self.metadata = np.memmap(self.metadata_file, dtype=dtype, mode=mode, shape=(self.capacity,))
@@ -154,6 +159,9 @@ class MMapNodeStorage(NodeStorage):
             self._size += 1
         self.embeddings[idx]["id"] = node.id
         self.embeddings[idx]["embedding"] = np.asarray(node.embedding).astype(np.float32)
+        if self.metadata is None:
+            self.embeddings.flush()
+            return
         metadata_json = json.dumps(node.metadata) if node.metadata else ""
         content = node.content or ""
         if len(content) > _CONTENT_CHARS:
@@ -171,6 +179,8 @@ class MMapNodeStorage(NodeStorage):
         if idx is None:
             return None
         embedding = self.embeddings[idx]["embedding"].copy()
+        if self.metadata is None:
+            return Node(id=node_id, embedding=embedding, content=None, metadata={})
         content = str(self.metadata[idx]["content"]).strip("\x00") or None
         metadata_json = str(self.metadata[idx]["metadata_json"]).strip("\x00") or None
         metadata = json.loads(metadata_json) if metadata_json else {}
@@ -209,13 +219,15 @@ class MMapNodeStorage(NodeStorage):
         # the reference clears the slot and sets id 0, not -1 (storage.py:295-299)
         self.embeddings[idx]["id"] = 0
         self.embeddings[idx]["embedding"] = 0.0
-        self.metadata[idx]["id"] = 0
-        self.metadata[idx]["content"] = ""
-        self.metadata[idx]["metadata_json"] = ""
+        if self.metadata is not None:
+            self.metadata[idx]["id"] = 0
+            self.metadata[idx]["content"] = ""
+            self.metadata[idx]["metadata_json"] = ""
         self._size -= 1
         heapq.heappush(self._free, idx)
         self.embeddings.flush()
-        self.metadata.flush()
+        if self.metadata is not None:
+            self.metadata.flush()
 
     # -- HBM staging ----------------------------------------------------------------------------
     def stage_to_device(self, device=None, chunk_records: int = 65536, threads: Optional[int] = None, depth: int = 3
