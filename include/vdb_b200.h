@@ -67,8 +67,10 @@ int vdb_stage_aos_h2d(const void* host_records /*[host,pinned]*/, int64_t n, int
  * Returns after the last copy has left the ring (the device arrays are then complete on `stream`). */
 int vdb_stage_aos_pageable_h2d(const void* records /*[host,pageable] n records*/, int64_t n, int D,
                                int64_t* ids /*[dev] n or NULL*/, float* vecs /*[dev] n*D*/,
-                               void* pinned_ring /*[host,pinned] depth*buffer_bytes*/, size_t buffer_bytes, int depth,
-                               int threads, void* stream);
+                               void* pinned_ring /*[host,pinned] depth*buffer_bytes*/,
+                               void* device_ring /*[dev] depth*buffer_bytes: chunks land here by ONE contiguous DMA each
+                                  and a kernel splits the id / embedding columns (strided DMA of 8-byte rows is 5x slower)*/,
+                               size_t buffer_bytes, int depth, int threads, void* stream);
 
 /* Per-row squared norms and the bf16 mirror used by the tensor-core scan.
  * Either output may be NULL. */

@@ -26,7 +26,7 @@ SIGNATURES = {
     "vdb_profile_enable": (None, [_i]),
     "vdb_profile_read": (_i, [_i, C.POINTER(C.c_int), C.POINTER(C.c_float)]),
     "vdb_stage_aos_h2d": (_i, [_p, _i64, _i, _p, _p, _p]),
-    "vdb_stage_aos_pageable_h2d": (_i, [_p, _i64, _i, _p, _p, _p, _sz, _i, _i, _p]),
+    "vdb_stage_aos_pageable_h2d": (_i, [_p, _i64, _i, _p, _p, _p, _p, _sz, _i, _i, _p]),
     "vdb_prepare_rows": (_i, [_p, _i64, _i, _p, _p, _p]),
     "vdb_exact_topk_f32_workspace": (_sz, [_i, _i64, _i]),
     "vdb_exact_topk_f32": (_i, [_p, _i, _p, _p, _p, _i64, _i, _i, _i, _p, _p, _p, _sz, _p]),

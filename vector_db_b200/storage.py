@@ -258,11 +258,13 @@ class MMapNodeStorage(NodeStorage):
         ring = getattr(self, "_stage_ring", None)
         if ring is None or ring.numel() < depth * chunk * rec:
             ring = self._stage_ring = torch.empty(depth * chunk * rec, dtype=torch.uint8).pin_memory()
+        dring = torch.empty(depth * chunk * rec, dtype=torch.uint8, device=dev)
         stream = torch.cuda.current_stream(dev)
         raw = self.embeddings.view(np.uint8).reshape(self.capacity, rec)
         t0 = time.perf_counter()
         _lib.check(lib.vdb_stage_aos_pageable_h2d(raw.ctypes.data, hw, self.dim, ids.data_ptr(), vecs.data_ptr(),
-                                                  ring.data_ptr(), chunk * rec, depth, int(threads), stream.cuda_stream))
+                                                  ring.data_ptr(), dring.data_ptr(), chunk * rec, depth, int(threads),
+                                                  stream.cuda_stream))
         stream.synchronize()
         dt = time.perf_counter() - t0
         self.last_stage = {"bytes": hw * rec, "seconds": dt, "gb_per_s": hw * rec / dt / 1e9, "threads": int(threads),
