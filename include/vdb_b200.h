@@ -91,6 +91,22 @@ int vdb_exact_topk_f32(const float* q /*[dev] Q*D*/, int Q, const float* db /*[d
                        float* out_d /*[dev] Q*k*/, int64_t* out_i /*[dev] Q*k*/,
                        void* ws, size_t ws_bytes, void* stream);
 
+/* Allocation-free variant of vdb_exact_topk_f32.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot allocate device memory (CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  Same inputs, outputs and results as vdb_exact_topk_f32, but the scan's scratch (Q x slices x k
+ * partial keys of 8 bytes) lives in a file-scope `static __device__` array of vdb_exact_topk_f32_static_max_bytes()
+ * = 8 MiB inside the library (held by every GPU that loads it, until exit) instead of a caller workspace; the call
+ * makes no cudaMalloc / cudaFree / allocating library call.  Shapes whose scratch exceeds the limit are rejected
+ * with VDB_ERR_UNSUPPORTED and a message naming the need (Q = 4096, k = 10 needs 1 MB; Q x k up to ~100k fits in the
+ * worst case of 4 x SMs slices per query group).  All calls on a device SHARE the array, which keeps the previous
+ * call's contents (the entry point re-initialises what it reads): calls that overlap on the GPU -- different streams,
+ * different threads -- race; serialise them on one stream. */
+size_t vdb_exact_topk_f32_static_max_bytes(void);
+int vdb_exact_topk_f32_static(const float* q /*[dev] Q*D*/, int Q, const float* db /*[dev] N*D*/,
+                              const int64_t* ids /*[dev] N or NULL*/, const uint32_t* row_mask /*[dev] or NULL*/,
+                              int64_t N, int D, int k, int metric,
+                              float* out_d /*[dev] Q*k*/, int64_t* out_i /*[dev] Q*k*/, void* stream);
+
 /* Exact fp32 rerank of per-query candidate rows (cand[q][r], -1 = empty; duplicates allowed and
  * collapsed): the direct-difference distance of util/distance.py:3-4 and the (dist,id) order.
  * out_kth (optional) receives the k-th returned distance per query (+inf if fewer). */

@@ -30,6 +30,8 @@ SIGNATURES = {
     "vdb_prepare_rows": (_i, [_p, _i64, _i, _p, _p, _p]),
     "vdb_exact_topk_f32_workspace": (_sz, [_i, _i64, _i]),
     "vdb_exact_topk_f32": (_i, [_p, _i, _p, _p, _p, _i64, _i, _i, _i, _p, _p, _p, _sz, _p]),
+    "vdb_exact_topk_f32_static_max_bytes": (_sz, []),
+    "vdb_exact_topk_f32_static": (_i, [_p, _i, _p, _p, _p, _i64, _i, _i, _i, _p, _p, _p]),
     "vdb_rerank_f32": (_i, [_p, _i, _p, _p, _i64, _i, _p, _i, _i, _i, _p, _p, _p]),
     "vdb_exact_topk_tc_supported": (_i, [_i, _i64, _i, _i, _i]),
     "vdb_tc_mirror_elems": (_sz, [_i64, _i, _i]),

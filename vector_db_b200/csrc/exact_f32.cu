@@ -4,6 +4,8 @@
 //
 // Reference arithmetic replaced: src/vector_db/util/distance.py:3-4 (sqrt(sum((q-x)^2)), fp32),
 // the (dist,id) sort of tests/indexing/test_hnsw.py:128-134 / src/vector_db/indexing/ivf.py:176-199.
+#include <mutex>
+
 #include "common.cuh"
 
 namespace vdb {
@@ -598,6 +600,78 @@ int vdb_merge_topk(const float* d, const int64_t* i, int L, int Q, int k, int de
     count_launch(1);
     VDB_CUDA(cudaGetLastError());
     return VDB_OK;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------
+// Allocation-free variant of vdb_exact_topk_f32 (no counterpart in the reference; added
+// for callers that cannot allocate: CUDA graph capture, tight serving loops).  The scan's scratch --
+// the per-(query, slice) partial top-k keys -- lives in this file-scope device array instead of a caller workspace.
+// Every GPU that loads the library holds these 8 MiB until the process exits.
+#define VDB_STATIC_SCRATCH_BYTES (8u << 20)
+static __device__ __align__(256) unsigned char g_static_scratch[VDB_STATIC_SCRATCH_BYTES];
+
+namespace vdb {
+
+// In HOST code `g_static_scratch` is only a stand-in for the symbol, not a device address: the address is asked of
+// the runtime once per device, with that device current, and cached.
+static int static_scratch_ptr(void** out) {
+    constexpr int kMaxDevices = 64;
+    static void* ptrs[kMaxDevices] = {nullptr};
+    static std::mutex mu;
+    int dev = -1;
+    VDB_CUDA(cudaGetDevice(&dev));
+    VDB_REQUIRE(dev >= 0 && dev < kMaxDevices, VDB_ERR_UNSUPPORTED, "device ordinal %d out of range", dev);
+    std::lock_guard<std::mutex> lk(mu);
+    if (ptrs[dev] == nullptr) {
+        void* p = nullptr;
+        VDB_CUDA(cudaGetSymbolAddress(&p, g_static_scratch));
+        VDB_REQUIRE(p != nullptr, VDB_ERR_CUDA, "cudaGetSymbolAddress returned a null scratch address on device %d", dev);
+        ptrs[dev] = p;
+    }
+    *out = ptrs[dev];
+    return VDB_OK;
+}
+
+}  // namespace vdb
+
+extern "C" {
+
+size_t vdb_exact_topk_f32_static_max_bytes(void) { return (size_t)VDB_STATIC_SCRATCH_BYTES; }
+
+int vdb_exact_topk_f32_static(const float* q, int Q, const float* db, const int64_t* ids, const uint32_t* row_mask,
+                              int64_t N, int D, int k, int metric, float* out_d, int64_t* out_i, void* stream) {
+    VDB_REQUIRE(Q >= 0 && N >= 0 && D > 0 && k > 0, VDB_ERR_INVALID, "vdb_exact_topk_f32_static: bad shape Q=%d N=%lld D=%d k=%d",
+                Q, (long long)N, D, k);
+    VDB_REQUIRE(metric == VDB_METRIC_L2 || metric == VDB_METRIC_COSINE, VDB_ERR_INVALID, "unknown metric %d", metric);
+    VDB_REQUIRE(N < (1ll << 32), VDB_ERR_UNSUPPORTED, "N=%lld exceeds 2^32 rows per call", (long long)N);
+    VDB_REQUIRE(k <= 2048, VDB_ERR_UNSUPPORTED, "k=%d > 2048", k);
+    if (Q == 0) return VDB_OK;
+    VDB_REQUIRE(q && out_d && out_i && (db || N == 0), VDB_ERR_INVALID, "vdb_exact_topk_f32_static: null pointer");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    ScanPlan p;
+    VDB_REQUIRE(plan_scan(Q, N, D, k, &p), VDB_ERR_UNSUPPORTED, "D=%d k=%d does not fit shared memory", D, k);
+    const size_t need = (size_t)Q * p.slices * k * 8;
+    VDB_REQUIRE(need <= (size_t)VDB_STATIC_SCRATCH_BYTES, VDB_ERR_UNSUPPORTED,
+                "vdb_exact_topk_f32_static: Q=%d k=%d needs %zu bytes of scratch (Q x %d slices x k x 8), the built-in "
+                "scratch holds %u; use vdb_exact_topk_f32 with a caller workspace", Q, k, need, p.slices,
+                (unsigned)VDB_STATIC_SCRATCH_BYTES);
+    void* scratch = nullptr;
+    int rc = static_scratch_ptr(&scratch);
+    if (rc) return rc;
+    u64* partial = static_cast<u64*>(scratch);
+    // the array keeps the previous call's keys: start every slot this call reads at "empty" (all ones)
+    VDB_CUDA(cudaMemsetAsync(partial, 0xFF, need, st));
+#define VDB_LAUNCH(TQ)                                                                                   \
+    rc = (metric == VDB_METRIC_L2) ? launch_scan<TQ, VDB_METRIC_L2>(p, q, Q, db, row_mask, N, D, k, partial, st) \
+                                   : launch_scan<TQ, VDB_METRIC_COSINE>(p, q, Q, db, row_mask, N, D, k, partial, st)
+    if (p.tq == 16) { VDB_LAUNCH(16); }
+    else if (p.tq == 4) { VDB_LAUNCH(4); }
+    else { VDB_LAUNCH(1); }
+#undef VDB_LAUNCH
+    if (rc) return rc;
+    return finalize_keys(partial, Q, p.slices * k, k, ids, 0, metric == VDB_METRIC_COSINE, out_d, out_i, st);
 }
 
 }  // extern "C"
