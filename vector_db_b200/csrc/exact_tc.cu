@@ -19,7 +19,7 @@
 // The residual form is rigorous for any input and, on ordinary data, tighter than either constant because a
 // rounding residual is ~0.4 u |x|, not u |x|.)  The kernel keeps, per query, the bins (8 consecutive
 // rows) with the smallest bin minimum; every row outside them has c(x) >= tau (see
-// select_bins_kernel), hence t(x) >= tau - eps.  All rows inside them are re-scored exactly.  If
+// tc_post_kernel), hence t(x) >= tau - eps.  All rows inside them are re-scored exactly.  If
 // tau - eps > t_k (the k-th exact score) no outside row can enter the top-k: certified.
 // Cosine: c(x) = q~ . bf16(-x/|x|), t(x) = -q.x/|x|: the same bound without the factor 2, A and B measured on the
 // normalised rows (A ~ 1).
@@ -131,7 +131,7 @@ __device__ __forceinline__ float pick_bin(const float (&m)[kBinsPerChunk], int b
 }
 
 // Threshold exchange between the two epilogue groups of a CTA (same query row, other half of the columns): a bin
-// that cannot enter the PARTNER's full list cannot enter the merged selection either (select_bins_kernel takes
+// that cannot enter the PARTNER's full list cannot enter the merged selection either (tc_post_kernel takes
 // tau from the worst entry of every full list), so each group tests against min(own tau, partner's tau) and
 // inserts ~45 % less often -- and an insert by ONE lane sends its whole warp through the insert code.
 // The word carries the unit counter mod 4 in its two low bits (the groups are at most two tiles, hence at most two
@@ -366,7 +366,8 @@ exact_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
 // Query operand: bf16(q) padded to Dp columns; for L2 the three columns after D hold 1.0 so that
 // the MMA adds the (hi, mid, lo) bf16 split of |x|^2 stored in the same columns of the row mirror.
 __global__ void tc_query_operand_kernel(const float* __restrict__ q, __nv_bfloat16* __restrict__ y, int Q, int D, int Dp,
-                                        int metric, uint32_t* __restrict__ gtau) {
+                                        int metric, uint32_t* __restrict__ gtau, int32_t* __restrict__ uncert) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) uncert[0] = 0;      // the post-scan kernel appends rejected queries
     const int64_t total = (int64_t)Q * Dp;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
         const int64_t r = i / Dp;
@@ -449,34 +450,45 @@ __device__ __forceinline__ void tc_bound(int metric, float qn, float rq, float A
 }
 __device__ __forceinline__ float bf16_residual(float v) { return __bfloat162float(__float2bfloat16_rn(v)) - v; }
 
-// Per query: merge the L per-(slice, group) bin lists, keep the NB best bins, expand them to
-// candidate rows and record tau (see the certificate in the file header): every bin that is NOT a
-// candidate has a coarse minimum >= tau, either because it ranks behind the NB-th merged bin or
-// because it was dropped from a full list, whose worst entry bounds it.  One CTA per query.
+// Post-scan, ONE kernel and one CTA per query (round 1 ran select_bins -> rerank -> memset -> certify as four stream
+// nodes with the candidate rows going through global memory; 0.39 ms of a 2.6 ms step):
+//  (1) merge the L per-(slice, group) bin lists, keep the NB best bins and trim them (below);
+//  (2) re-score every row of the kept bins with the reference's fp32 arithmetic (util/distance.py:3-4; the SAME operation
+//      order as rerank_f32_kernel / the fp32 scan, so the three agree bit for bit) and sort by (score, row);
+//  (3) certify: every bin that is NOT a candidate has a coarse minimum >= tau, either because it ranks behind the NB-th
+//      merged bin or because it was dropped from a full list, whose worst entry bounds it; the query is exact iff
+//      tau - eps - slack > t_k.  Rejected queries go to the device-side list the fp32 rescan reads.
+template <int METRIC>
 __global__ void __launch_bounds__(256)
-select_bins_kernel(const u64* __restrict__ partial, int L, int NBL, int NB, int C, int64_t N, int32_t* __restrict__ cand,
-                   int32_t* __restrict__ cand_cnt, float* __restrict__ tau_out, const float* __restrict__ qv, int D, int k, int metric,
-                   const float* __restrict__ stats, int no_trim) {
+tc_post_kernel(const u64* __restrict__ partial, int L, int NBL, int NB, int C, int64_t N, const float* __restrict__ qv,
+               const float* __restrict__ db, const int64_t* __restrict__ ids, int D, int k, const float* __restrict__ stats,
+               int no_trim, float* __restrict__ out_d, int64_t* __restrict__ out_i, int32_t* __restrict__ uncert) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    u64* buf = reinterpret_cast<u64*>(smem_raw);
+    u64* buf = reinterpret_cast<u64*>(smem_raw);           // [C] merged list slots, then [kNBFinal] the best bins
+    u64* top = buf + C;
+    u64* rk = top + kNBFinal;                              // [kNBFinal * kBin] rerank keys
+    float* qs = reinterpret_cast<float*>(rk + kNBFinal * kBin);   // [D]
     __shared__ unsigned tau_bits;          // ordered-float minimum over the full lists' worst entries
-    __shared__ float qsq_s, rsq_s;
+    __shared__ float qsq_s, rsq_s, tau_s;
     __shared__ int keep_s;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
     const int q = blockIdx.x, total = L * NBL;
-    if (threadIdx.x == 0) { tau_bits = f32_to_ordered(INFINITY); qsq_s = 0.f; rsq_s = 0.f; }
+    if (tid == 0) tau_bits = f32_to_ordered(INFINITY);
+    for (int t = tid; t < D; t += blockDim.x) qs[t] = qv[(size_t)q * D + t];
+    for (int i = tid; i < NB; i += blockDim.x) top[i] = VDB_KEY_MAX;
     __syncthreads();
-    {
+    if (warp == 0) {                                       // |q|^2 in the order rerank_f32_kernel uses, and |bf16(q) - q|^2
         float a = 0.f, b = 0.f;
-        for (int t = threadIdx.x; t < D; t += blockDim.x) {
-            const float v = qv[(size_t)q * D + t], r = bf16_residual(v);
+        for (int t = lane; t < D; t += 32) {
+            const float v = qs[t], r = bf16_residual(v);
             a = fmaf(v, v, a);
             b = fmaf(r, r, b);
         }
         a = warp_sum(a);
         b = warp_sum(b);
-        if ((threadIdx.x & 31) == 0 && a != 0.f) { atomicAdd(&qsq_s, a); atomicAdd(&rsq_s, b); }
+        if (lane == 0) { qsq_s = a; rsq_s = b; }
     }
-    for (int i = threadIdx.x; i < C; i += blockDim.x) {
+    for (int i = tid; i < C; i += blockDim.x) {
         u64 key = VDB_KEY_MAX;
         if (i < total) {
             key = partial[(size_t)q * total + i];
@@ -485,14 +497,11 @@ select_bins_kernel(const u64* __restrict__ partial, int L, int NBL, int NB, int 
         }
         buf[i] = key;
     }
-    u64* top = buf + C;                    // the NB best keys, ascending
-    for (int i = threadIdx.x; i < NB; i += blockDim.x) top[i] = VDB_KEY_MAX;
     __syncthreads();
     // The L lists arrive sorted by score, so a key's rank among all keys is its position in its own list plus, for
     // every other list, the number of entries ahead of it -- a 5-probe binary search per list instead of a bitonic
-    // sort of all C keys (the sort was 45 barrier-separated passes and made this kernel 4 % of a search step).
-    // Ties on the score are ordered by (list, position), which keeps the ranks unique whatever the bins are.
-    for (int i = threadIdx.x; i < total; i += blockDim.x) {
+    // sort of all C keys.  Ties on the score are ordered by (list, position), which keeps the ranks unique.
+    for (int i = tid; i < total; i += blockDim.x) {
         const u64 key = buf[i];
         if (key == VDB_KEY_MAX) continue;
         const unsigned sc = (unsigned)(key >> 32);
@@ -511,81 +520,106 @@ select_bins_kernel(const u64* __restrict__ partial, int L, int NBL, int NB, int 
         if (rank < NB) top[rank] = key;
     }
     __syncthreads();
-    buf = top;
-    C = NB;
-    if (threadIdx.x == 0) {
+    float eps, slack;                                                // the certificate's allowance, also the trim's
+    tc_bound(METRIC, sqrtf(qsq_s) * 1.0001f, sqrtf(rsq_s) * 1.0001f, stats[0], stats[1], &eps, &slack);
+    if (tid == 0) {
         float tau = ordered_to_f32(tau_bits);
-        if (NB - 1 < C && buf[NB - 1] != VDB_KEY_MAX) tau = fminf(tau, key_score(buf[NB - 1]));
+        if (top[NB - 1] != VDB_KEY_MAX) tau = fminf(tau, key_score(top[NB - 1]));
         // Trim: the k-th smallest bin minimum c_k bounds the k-th smallest coarse row score from above, so k rows
         // have exact scores <= c_k + eps and no row of a bin whose minimum exceeds c_k + 2 eps can enter the
         // top-k.  Those bins are not reranked; the first of them becomes the bound the certificate tests
         // (a little extra slack keeps the certificate's own rounding allowance from rejecting the query).
-        const int nb = NB < C ? NB : C;
-        int keep = nb;
+        int keep = NB;
         float cutoff = INFINITY;
-        if (!no_trim && k - 1 < C && buf[k - 1] != VDB_KEY_MAX) {
-            float eps, slack;                                        // the same allowance as certify_kernel
-            tc_bound(metric, sqrtf(qsq_s) * 1.0001f, sqrtf(rsq_s) * 1.0001f, stats[0], stats[1], &eps, &slack);
-            cutoff = key_score(buf[k - 1]) + 2.f * eps + 4.f * slack;
-        }
-        // first empty slot, or first bin (sorted ascending) above the cutoff; nb <= 64, one thread scans it
-        for (int j = 0; j < nb; ++j) {
-            if (buf[j] == VDB_KEY_MAX) { keep = j; break; }
-            if (j >= k && key_score(buf[j]) > cutoff) { keep = j; tau = fminf(tau, key_score(buf[j])); break; }
+        if (!no_trim && k - 1 < NB && top[k - 1] != VDB_KEY_MAX) cutoff = key_score(top[k - 1]) + 2.f * eps + 4.f * slack;
+        for (int j = 0; j < NB; ++j) {                               // NB <= 64, one thread scans it
+            if (top[j] == VDB_KEY_MAX) { keep = j; break; }
+            if (j >= k && key_score(top[j]) > cutoff) { keep = j; tau = fminf(tau, key_score(top[j])); break; }
         }
         keep_s = keep;
-        cand_cnt[q] = keep * kBin;
-        tau_out[q] = tau;
+        tau_s = tau;
     }
     __syncthreads();
-    const int keep = keep_s;
-    for (int i = threadIdx.x; i < keep * kBin; i += blockDim.x) {          // the rerank reads cand_cnt entries only
-        const int j = i / kBin, e = i - j * kBin;
-        int32_t r = -1;
-        if (j < C && buf[j] != VDB_KEY_MAX) {
-            int64_t row = (int64_t)key_index(buf[j]) * kBin + e;
-            if (row < N) r = (int32_t)row;
+    // ---- exact rerank of the rows of the kept bins (kBin consecutive rows each: one contiguous kBin x 4D-byte run)
+    const int R = keep_s * kBin;
+    int C2 = 32;
+    while (C2 < R) C2 <<= 1;
+    for (int i = tid; i < C2; i += blockDim.x) rk[i] = VDB_KEY_MAX;
+    __syncthreads();
+    const float qn = sqrtf(qsq_s);
+    constexpr int RW = 4;                                            // rows in flight per warp (kBin % RW == 0)
+    const int nchunk = D >> 2;
+    for (int base = warp * RW; base < R; base += nwarp * RW) {
+        const int64_t row0 = (int64_t)key_index(top[base / kBin]) * kBin + (base % kBin);
+        float acc[RW], xx[RW];
+#pragma unroll
+        for (int j = 0; j < RW; ++j) { acc[j] = 0.f; xx[j] = 0.f; }
+        for (int t = lane; t < nchunk; t += 32) {
+            float4 x[RW];
+#pragma unroll
+            for (int j = 0; j < RW; ++j)
+                x[j] = row0 + j < N ? __ldg(reinterpret_cast<const float4*>(db + (size_t)(row0 + j) * D) + t)
+                                    : make_float4(0.f, 0.f, 0.f, 0.f);
+            const float4 qv4 = *reinterpret_cast<const float4*>(qs + 4 * t);
+#pragma unroll
+            for (int j = 0; j < RW; ++j) {
+                if (METRIC == VDB_METRIC_L2) {
+                    const float d0 = qv4.x - x[j].x, d1 = qv4.y - x[j].y, d2 = qv4.z - x[j].z, d3 = qv4.w - x[j].w;
+                    acc[j] = fmaf(d0, d0, acc[j]); acc[j] = fmaf(d1, d1, acc[j]);
+                    acc[j] = fmaf(d2, d2, acc[j]); acc[j] = fmaf(d3, d3, acc[j]);
+                } else {
+                    acc[j] = fmaf(qv4.x, x[j].x, acc[j]); acc[j] = fmaf(qv4.y, x[j].y, acc[j]);
+                    acc[j] = fmaf(qv4.z, x[j].z, acc[j]); acc[j] = fmaf(qv4.w, x[j].w, acc[j]);
+                    xx[j] = fmaf(x[j].x, x[j].x, xx[j]); xx[j] = fmaf(x[j].y, x[j].y, xx[j]);
+                    xx[j] = fmaf(x[j].z, x[j].z, xx[j]); xx[j] = fmaf(x[j].w, x[j].w, xx[j]);
+                }
+            }
         }
-        cand[(size_t)q * NB * kBin + i] = r;
+        float a_mine = 0.f, x_mine = 0.f;
+#pragma unroll
+        for (int j = 0; j < RW; ++j) {
+            const float a = warp_sum(acc[j]);
+            const float b = (METRIC == VDB_METRIC_COSINE) ? warp_sum(xx[j]) : 0.f;
+            if (lane == j) { a_mine = a; x_mine = b; }
+        }
+        if (lane < RW && row0 + lane < N) {
+            const float score = (METRIC == VDB_METRIC_L2) ? sqrtf(a_mine) : -(a_mine / (sqrtf(x_mine) * qn));
+            rk[base + lane] = pack_key(score, (uint32_t)(row0 + lane));
+        }
     }
-}
-
-// One warp per query: decide whether the reranked top-k is provably the exact top-k.
-template <int METRIC>
-__global__ void certify_kernel(const float* __restrict__ q, int Q, int D, int k, const float* __restrict__ out_d,
-                               const int64_t* __restrict__ out_i, const float* __restrict__ tau,
-                               const float* __restrict__ stats, int32_t* __restrict__ uncert) {
-    const int lane = threadIdx.x & 31;
-    const int qi = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    if (qi >= Q) return;
-    float a = 0.f, b = 0.f;
-    for (int t = lane; t < D; t += 32) {
-        const float v = q[(size_t)qi * D + t], r = bf16_residual(v);
-        a = fmaf(v, v, a);
-        b = fmaf(r, r, b);
-    }
-    a = warp_sum(a);
-    b = warp_sum(b);
-    if (lane != 0) return;
-    const float qn = sqrtf(a);
-    float eps, slack;
-    tc_bound(METRIC, qn * 1.0001f, sqrtf(b) * 1.0001f, stats[0], stats[1], &eps, &slack);
-    const float t_bound = tau[qi];
-    bool ok;
-    if (out_i[(size_t)qi * k + k - 1] < 0) {
-        ok = (t_bound == INFINITY);                                // fewer than k rows exist: all must have been reranked
-    } else if (METRIC == VDB_METRIC_L2) {
-        const float dk = out_d[(size_t)qi * k + k - 1];
-        const float tk = dk * dk - a;
-        ok = (t_bound - eps - slack) > tk;
-    } else {
-        const float simk = out_d[(size_t)qi * k + k - 1];
-        const float tk = -simk * qn;
-        ok = (t_bound - eps - slack) > tk;
-    }
-    if (!ok) {
-        int slot = atomicAdd(uncert, 1);
-        uncert[1 + slot] = qi;
+    __syncthreads();
+    block_bitonic_sort(rk, C2);
+    if (tid == 0) {
+        int n = 0;
+        for (int i = 0; i < C2 && n < k; ++i, ++n) {
+            const u64 key = rk[i];
+            if (key == VDB_KEY_MAX) break;
+            const float sc = key_score(key);
+            out_d[(size_t)q * k + n] = (METRIC == VDB_METRIC_L2) ? sc : -sc;
+            const int64_t idx = (int64_t)key_index(key);
+            out_i[(size_t)q * k + n] = ids ? ids[idx] : idx;
+        }
+        const int got = n;
+        for (; n < k; ++n) {
+            out_d[(size_t)q * k + n] = (METRIC == VDB_METRIC_L2) ? INFINITY : -INFINITY;
+            out_i[(size_t)q * k + n] = -1;
+        }
+        // ---- certificate
+        const float t_bound = tau_s;
+        bool ok;
+        if (got < k) {
+            ok = (t_bound == INFINITY);                              // fewer than k rows exist: all must have been reranked
+        } else if (METRIC == VDB_METRIC_L2) {
+            const float dk = key_score(rk[k - 1]);
+            ok = (t_bound - eps - slack) > dk * dk - qsq_s;
+        } else {
+            const float simk = -key_score(rk[k - 1]);
+            ok = (t_bound - eps - slack) > -simk * qn;
+        }
+        if (!ok) {
+            const int slot = atomicAdd(uncert, 1);
+            uncert[1 + slot] = q;
+        }
     }
 }
 
@@ -688,7 +722,7 @@ static bool plan_tc(int Q, int64_t N, int D, int k, int metric, TcPlan* p) {
 }
 
 struct TcWorkspace {
-    size_t qbf16, partial, cand, tau, cand_cnt, rescan, rescan_bytes, total;
+    size_t qbf16, partial, tau, rescan, rescan_bytes, total;
 };
 
 static TcWorkspace tc_workspace(const TcPlan& p, int Q, int64_t N, int D, int k) {
@@ -697,9 +731,7 @@ static TcWorkspace tc_workspace(const TcPlan& p, int Q, int64_t N, int D, int k)
     auto take = [&](size_t bytes) { size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
     w.qbf16 = take((size_t)Q * p.Dp * 2);
     w.partial = take((size_t)Q * p.S * kGroups * kNBLMax * 8);
-    w.cand = take((size_t)Q * kNBFinal * kBin * 4);
     w.tau = take((size_t)Q * 4);
-    w.cand_cnt = take((size_t)Q * 4);
     w.rescan_bytes = exact_f32_subset_workspace(Q, N, D, k);      // fp32 rescan of uncertified queries
     w.rescan = take(w.rescan_bytes);
     w.total = off;
@@ -763,14 +795,12 @@ int vdb_exact_topk_tc(const float* q, int Q, const float* db, const void* mirror
     char* base = static_cast<char*>(ws);
     __nv_bfloat16* qb = reinterpret_cast<__nv_bfloat16*>(base + w.qbf16);
     u64* partial = reinterpret_cast<u64*>(base + w.partial);
-    int32_t* cand = reinterpret_cast<int32_t*>(base + w.cand);
     float* tau = reinterpret_cast<float*>(base + w.tau);
-    int32_t* cand_cnt = reinterpret_cast<int32_t*>(base + w.cand_cnt);
 
     // per-list depth: lists of 8 are enough when there are many of them (L * 8 >= 4 * kNBFinal), debug bit 2 forces 16
     const int nbl = ((g_tc_flags & 4) || p.S * kGroups * 8 < 4 * kNBFinal) ? 16 : 8;
-    uint32_t* gtau = reinterpret_cast<uint32_t*>(tau);            // free until select_bins_kernel writes tau
-    tc_query_operand_kernel<<<sm_count() * 2, 256, 0, st>>>(q, qb, Q, D, p.Dp, metric, gtau);
+    uint32_t* gtau = reinterpret_cast<uint32_t*>(tau);            // per-query threshold exchange of the scan
+    tc_query_operand_kernel<<<sm_count() * 2, 256, 0, st>>>(q, qb, Q, D, p.Dp, metric, gtau, out_uncertified);
     CUtensorMap map_a, map_b;
     CUtensorMap map_a2, map_b2;
     int rc = make_map(&map_a, qb, Q, D, p.Dp, kBlockK, kTileM);
@@ -799,26 +829,26 @@ int vdb_exact_topk_tc(const float* q, int Q, const float* db, const void* mirror
     VDB_CUDA(cudaGetLastError());
     const int L = p.S * kGroups;
     const int C = next_pow2(L * nbl < 64 ? 64 : L * nbl);
-    VDB_CUDA(cudaFuncSetAttribute(select_bins_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (C + kNBFinal) * 8));
-    // bins handed to the rerank per query (select_bins_kernel drops those that provably cannot matter);
+    // bins handed to the rerank per query (the post-scan kernel drops those that provably cannot matter);
     // debug bits 12..19 override the count, bit 4 disables the trimming
     int nbf = kNBFinal;
     if ((g_tc_flags >> 12) & 0xFF) nbf = (g_tc_flags >> 12) & 0xFF;
     if (nbf > kNBFinal) nbf = kNBFinal;
-    select_bins_kernel<<<Q, 256, (size_t)(C + kNBFinal) * 8, st>>>(partial, L, nbl, nbf, C, N, cand, cand_cnt, tau, q, D, k, metric,
-                                                      db_stats, (g_tc_flags & 16) ? 1 : 0);
+    if (nbf < k) nbf = k;
+    const size_t post_smem = (size_t)(C + kNBFinal + kNBFinal * kBin) * 8 + (size_t)D * 4;
+    {
+        ProfScope prof(kProfRerank, st);
+        if (metric == VDB_METRIC_L2) {
+            VDB_CUDA(cudaFuncSetAttribute(tc_post_kernel<VDB_METRIC_L2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)post_smem));
+            tc_post_kernel<VDB_METRIC_L2><<<Q, 256, post_smem, st>>>(partial, L, nbl, nbf, C, N, q, db, ids, D, k, db_stats,
+                                                                    (g_tc_flags & 16) ? 1 : 0, out_d, out_i, out_uncertified);
+        } else {
+            VDB_CUDA(cudaFuncSetAttribute(tc_post_kernel<VDB_METRIC_COSINE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)post_smem));
+            tc_post_kernel<VDB_METRIC_COSINE><<<Q, 256, post_smem, st>>>(partial, L, nbl, nbf, C, N, q, db, ids, D, k, db_stats,
+                                                                        (g_tc_flags & 16) ? 1 : 0, out_d, out_i, out_uncertified);
+        }
+    }
     count_launch(3);
-    VDB_CUDA(cudaGetLastError());
-    rc = rerank_f32_counted(q, Q, db, ids, N, D, cand, cand_cnt, nbf * kBin, k, metric, out_d, out_i, stream);
-    if (rc) return rc;
-    VDB_CUDA(cudaMemsetAsync(out_uncertified, 0, 4, st));
-    const int warps_per_block = 8;
-    const int blocks = (Q + warps_per_block - 1) / warps_per_block;
-    if (metric == VDB_METRIC_L2)
-        certify_kernel<VDB_METRIC_L2><<<blocks, warps_per_block * 32, 0, st>>>(q, Q, D, k, out_d, out_i, tau, db_stats, out_uncertified);
-    else
-        certify_kernel<VDB_METRIC_COSINE><<<blocks, warps_per_block * 32, 0, st>>>(q, Q, D, k, out_d, out_i, tau, db_stats, out_uncertified);
-    count_launch(1);
     VDB_CUDA(cudaGetLastError());
     // queries the certificate rejected: exact fp32 scan, driven by the device-side list (no host round trip)
     return exact_f32_subset(q, Q, db, ids, N, D, k, metric, out_uncertified + 1, out_uncertified, out_d, out_i,

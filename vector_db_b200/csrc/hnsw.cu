@@ -66,7 +66,7 @@ __device__ __forceinline__ float warp_l2(const float* __restrict__ qs, const flo
         const float4* r4 = reinterpret_cast<const float4*>(row);
         const float4* q4 = reinterpret_cast<const float4*>(qs);
         for (int c = lane; c < (D >> 2); c += 32) {
-            const float4 x = __ldg(r4 + c);
+            const float4 x = ld_stream_f4(r4 + c);
             const float4 qv = q4[c];
             float d0 = qv.x - x.x, d1 = qv.y - x.y, d2 = qv.z - x.z, d3 = qv.w - x.w;
             acc = fmaf(d0, d0, acc); acc = fmaf(d1, d1, acc); acc = fmaf(d2, d2, acc); acc = fmaf(d3, d3, acc);
@@ -87,8 +87,8 @@ __device__ __forceinline__ void warp_l2_x2(const float* __restrict__ qs, const f
         const float4* b4 = reinterpret_cast<const float4*>(row_b);
         const float4* q4 = reinterpret_cast<const float4*>(qs);
         for (int c = lane; c < (D >> 2); c += 32) {
-            const float4 xa = __ldg(a4 + c);
-            const float4 xb = __ldg(b4 + c);
+            const float4 xa = ld_stream_f4(a4 + c);             // read once: no L1 allocation (keeps adjacency / stack lines)
+            const float4 xb = ld_stream_f4(b4 + c);
             const float4 qv = q4[c];
             float d0 = qv.x - xa.x, d1 = qv.y - xa.y, d2 = qv.z - xa.z, d3 = qv.w - xa.w;
             acc_a = fmaf(d0, d0, acc_a); acc_a = fmaf(d1, d1, acc_a); acc_a = fmaf(d2, d2, acc_a); acc_a = fmaf(d3, d3, acc_a);
@@ -622,6 +622,7 @@ hnsw_reverse_merge_kernel(int32_t* __restrict__ adj, float* __restrict__ adjd, i
     }
 }
 
+static int g_hnsw_ctas_per_sm = 8;               // resident CTAs per SM the search grid is sized for (debug setter below)
 static int g_hnsw_smem_hash_limit = 48 * 1024;   // visited hash stays in shared memory only below this CTA footprint
 static int pick_hash_slots(int ef, int deg) {
     long long want = ((long long)(ef + 32) * deg * 5) / 4;
@@ -637,11 +638,12 @@ using namespace vdb;
 extern "C" {
 
 void vdb_debug_set_hnsw_smem_hash_limit(int bytes) { g_hnsw_smem_hash_limit = bytes; }
+void vdb_debug_set_hnsw_ctas_per_sm(int n) { g_hnsw_ctas_per_sm = n < 1 ? 1 : (n > 16 ? 16 : n); }
 
 size_t vdb_hnsw_search_workspace(int Q, int ef, int deg0) {
     (void)Q;
     size_t h = (size_t)pick_hash_slots(ef, deg0) * 4;   // forced-retry variant may ask for 4x
-    return 256 + (size_t)sm_count() * 8 * h * 4;
+    return 256 + (size_t)sm_count() * 16 * h * 4;
 }
 
 int vdb_hnsw_search(const float* q, int Q, const float* db, int64_t N, int D, const int32_t* adj0, int deg0,
@@ -675,7 +677,7 @@ int vdb_hnsw_search(const float* q, int Q, const float* db, int64_t N, int D, co
     int per_sm = 1;
     VDB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, hnsw_search_kernel, kHnswThreads, smem));
     if (per_sm < 1) per_sm = 1;
-    if (per_sm > 8) per_sm = 8;
+    if (per_sm > g_hnsw_ctas_per_sm) per_sm = g_hnsw_ctas_per_sm;
     int grid = sm_count() * per_sm;
     if (grid > Q) grid = Q;
     int* flag = static_cast<int*>(ws);

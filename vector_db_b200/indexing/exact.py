@@ -71,16 +71,32 @@ class ExactIndex:
         return ops.exact_topk_f32(q, st.vecs, k, self.metric, ids=st.ids, row_mask=mask, n_rows=st.n)
 
     def search(self, queries: np.ndarray, k: int, filter_ids=None) -> Tuple[np.ndarray, np.ndarray]:
-        """Host in / host out: pinned staging, one H2D copy, kernels, one D2H copy."""
+        """Host in / host out, one blocking call.  A large unfiltered batch is cut into 1024-query-aligned pieces that
+        go through the ``search_batches`` pipeline, so the call's own H2D / host staging / D2H copies run under the
+        scan of the neighbouring piece instead of in front of and behind one big scan (a 4096-query piece count of 2
+        keeps every piece a full wave of the tensor-core scan)."""
         q_host = np.ascontiguousarray(queries, dtype=np.float32).reshape(-1, self.dim)
         nq = q_host.shape[0]
         dev = self.store.device
+        if filter_ids is None and nq >= 2048:
+            pieces = 2 if nq < 8192 else 4
+            step = (-(-nq // pieces) + 127) // 128 * 128
+            outs = list(self.search_batches((q_host[s:s + step] for s in range(0, nq, step)), k, depth=2))
+            return np.concatenate([o[0] for o in outs]), np.concatenate([o[1] for o in outs])
         if self._pin is None or self._pin.shape[0] < nq:
             self._pin = torch.empty((max(nq, 64), self.dim), dtype=torch.float32).pin_memory()
+            self._pin_out = None
         self._pin[:nq].copy_(torch.from_numpy(q_host))
         q = self._pin[:nq].to(dev, non_blocking=True)
         d, i = self.search_device(q, k, filter_ids)
-        return d.cpu().numpy(), i.cpu().numpy()
+        po = getattr(self, "_pin_out", None)
+        if po is None or po[0].shape[0] < nq or po[0].shape[1] != k:
+            po = self._pin_out = (torch.empty((max(nq, 64), k), dtype=torch.float32).pin_memory(),
+                                  torch.empty((max(nq, 64), k), dtype=torch.int64).pin_memory())
+        po[0][:nq].copy_(d, non_blocking=True)
+        po[1][:nq].copy_(i, non_blocking=True)
+        torch.cuda.current_stream(dev).synchronize()
+        return po[0][:nq].numpy().copy(), po[1][:nq].numpy().copy()
 
     def search_batches(self, batches: Iterable, k: int, post: Optional[Callable] = None, depth: int = 2
                        ) -> Iterator[Tuple[np.ndarray, np.ndarray]]:
