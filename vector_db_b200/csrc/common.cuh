@@ -102,6 +102,16 @@ __device__ __forceinline__ float4 ld_stream_f4(const float4* p) {
     return r;
 }
 
+// The same load for READ-ONLY data as a plain (non-volatile) asm: the compiler may hoist a group of them ahead of the
+// arithmetic that consumes them (gather loops want every load of a row group in flight before the first use; the
+// volatile form pins each load between the arithmetic statements around it).
+__device__ __forceinline__ float4 ld_gather_f4(const float4* p) {
+    float4 r;
+    asm("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+        : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+    return r;
+}
+
 // ------------------------------------------------------------------ CTA-wide bitonic sort (ascending), n = power of two
 // `lists` independent arrays of n keys each, stored back to back, are sorted by the same network in one
 // pass (one barrier per stage for all of them); every thread handles compare-exchange PAIRS, none idle.

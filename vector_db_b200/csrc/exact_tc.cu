@@ -19,7 +19,7 @@
 // The residual form is rigorous for any input and, on ordinary data, tighter than either constant because a
 // rounding residual is ~0.4 u |x|, not u |x|.)  The kernel keeps, per query, the bins (8 consecutive
 // rows) with the smallest bin minimum; every row outside them has c(x) >= tau (see
-// tc_post_kernel), hence t(x) >= tau - eps.  All rows inside them are re-scored exactly.  If
+// tc_select_kernel), hence t(x) >= tau - eps.  All rows inside them are re-scored exactly.  If
 // tau - eps > t_k (the k-th exact score) no outside row can enter the top-k: certified.
 // Cosine: c(x) = q~ . bf16(-x/|x|), t(x) = -q.x/|x|: the same bound without the factor 2, A and B measured on the
 // normalised rows (A ~ 1).
@@ -131,7 +131,7 @@ __device__ __forceinline__ float pick_bin(const float (&m)[kBinsPerChunk], int b
 }
 
 // Threshold exchange between the two epilogue groups of a CTA (same query row, other half of the columns): a bin
-// that cannot enter the PARTNER's full list cannot enter the merged selection either (tc_post_kernel takes
+// that cannot enter the PARTNER's full list cannot enter the merged selection either (tc_select_kernel takes
 // tau from the worst entry of every full list), so each group tests against min(own tau, partner's tau) and
 // inserts ~45 % less often -- and an insert by ONE lane sends its whole warp through the insert code.
 // The word carries the unit counter mod 4 in its two low bits (the groups are at most two tiles, hence at most two
@@ -366,8 +366,9 @@ exact_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
 // Query operand: bf16(q) padded to Dp columns; for L2 the three columns after D hold 1.0 so that
 // the MMA adds the (hi, mid, lo) bf16 split of |x|^2 stored in the same columns of the row mirror.
 __global__ void tc_query_operand_kernel(const float* __restrict__ q, __nv_bfloat16* __restrict__ y, int Q, int D, int Dp,
-                                        int metric, uint32_t* __restrict__ gtau, int32_t* __restrict__ uncert) {
-    if (blockIdx.x == 0 && threadIdx.x == 0) uncert[0] = 0;      // the post-scan kernel appends rejected queries
+                                        int metric, uint32_t* __restrict__ gtau, int32_t* __restrict__ uncert,
+                                        int32_t* __restrict__ item_count) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) { uncert[0] = 0; item_count[0] = 0; }   // filled by the post-scan kernels
     const int64_t total = (int64_t)Q * Dp;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
         const int64_t r = i / Dp;
@@ -450,37 +451,45 @@ __device__ __forceinline__ void tc_bound(int metric, float qn, float rq, float A
 }
 __device__ __forceinline__ float bf16_residual(float v) { return __bfloat162float(__float2bfloat16_rn(v)) - v; }
 
-// Post-scan, ONE kernel and one CTA per query (round 1 ran select_bins -> rerank -> memset -> certify as four stream
-// nodes with the candidate rows going through global memory; 0.39 ms of a 2.6 ms step):
-//  (1) merge the L per-(slice, group) bin lists, keep the NB best bins and trim them (below);
-//  (2) re-score every row of the kept bins with the reference's fp32 arithmetic (util/distance.py:3-4; the SAME operation
-//      order as rerank_f32_kernel / the fp32 scan, so the three agree bit for bit) and sort by (score, row);
-//  (3) certify: every bin that is NOT a candidate has a coarse minimum >= tau, either because it ranks behind the NB-th
-//      merged bin or because it was dropped from a full list, whose worst entry bounds it; the query is exact iff
-//      tau - eps - slack > t_k.  Rejected queries go to the device-side list the fp32 rescan reads.
-template <int METRIC>
-__global__ void __launch_bounds__(256)
-tc_post_kernel(const u64* __restrict__ partial, int L, int NBL, int NB, int C, int64_t N, const float* __restrict__ qv,
-               const float* __restrict__ db, const int64_t* __restrict__ ids, int D, int k, const float* __restrict__ stats,
-               int no_trim, float* __restrict__ out_d, int64_t* __restrict__ out_i, int32_t* __restrict__ uncert) {
+// Post-scan = three small kernels (round 1: select_bins -> per-query rerank -> certify, 0.39 ms of a 2.6 ms step, the
+// per-query rerank CTA alternating serial phases with a few loads in flight; a single fused per-query kernel measured
+// the same 0.32-0.38 ms for the same reason):
+//   tc_select_kernel   one CTA per query: merge the L per-(slice, group) bin lists, keep the NB best bins, trim them,
+//                      append the kept bins to ONE flat work list, record tau and the certificate's allowance;
+//   tc_rerank_bins_kernel  persistent CTAs stream the flat bin list: every bin is kBin consecutive rows = one contiguous
+//                      kBin x 4D-byte run, fetched with a 1-D bulk copy into a shared-memory ring (nothing but loads in
+//                      flight, no query-sized imbalance), re-scored with the reference's fp32 arithmetic (the operation
+//                      order of rerank_f32_kernel / the fp32 scan, so the three agree bit for bit);
+//   tc_final_kernel    one warp per query: k best of the query's keys by (score, row), then the certificate:
+//                      every bin that is NOT a candidate has a coarse minimum >= tau (it ranks behind the NB-th merged
+//                      bin, or it was dropped from a full list whose worst entry bounds it, or it was trimmed); the query
+//                      is exact iff tau - eps - slack > t_k.  Rejected queries go to the list the fp32 rescan reads.
+struct TcPostQuery {          // per query, written by tc_select_kernel
+    float tau_minus;          // tau - eps - slack
+    float qsq;                // |q|^2 in rerank_f32_kernel's summation order
+    int keep;                 // bins kept
+    int pad;
+};
+
+__global__ void __launch_bounds__(128)
+tc_select_kernel(const u64* __restrict__ partial, int L, int NBL, int NB, int C, const float* __restrict__ qv, int D, int k,
+                 int metric, const float* __restrict__ stats, int no_trim, TcPostQuery* __restrict__ pq,
+                 uint2* __restrict__ items, int32_t* __restrict__ item_count) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     u64* buf = reinterpret_cast<u64*>(smem_raw);           // [C] merged list slots, then [kNBFinal] the best bins
     u64* top = buf + C;
-    u64* rk = top + kNBFinal;                              // [kNBFinal * kBin] rerank keys
-    float* qs = reinterpret_cast<float*>(rk + kNBFinal * kBin);   // [D]
     __shared__ unsigned tau_bits;          // ordered-float minimum over the full lists' worst entries
-    __shared__ float qsq_s, rsq_s, tau_s;
-    __shared__ int keep_s;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
+    __shared__ float qsq_s, rsq_s;
+    __shared__ int keep_s, base_s;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int q = blockIdx.x, total = L * NBL;
     if (tid == 0) tau_bits = f32_to_ordered(INFINITY);
-    for (int t = tid; t < D; t += blockDim.x) qs[t] = qv[(size_t)q * D + t];
     for (int i = tid; i < NB; i += blockDim.x) top[i] = VDB_KEY_MAX;
     __syncthreads();
-    if (warp == 0) {                                       // |q|^2 in the order rerank_f32_kernel uses, and |bf16(q) - q|^2
+    if (warp == 3) {                                       // |q|^2 in the order rerank_f32_kernel uses, and |bf16(q) - q|^2
         float a = 0.f, b = 0.f;
         for (int t = lane; t < D; t += 32) {
-            const float v = qs[t], r = bf16_residual(v);
+            const float v = qv[(size_t)q * D + t], r = bf16_residual(v);
             a = fmaf(v, v, a);
             b = fmaf(r, r, b);
         }
@@ -520,101 +529,224 @@ tc_post_kernel(const u64* __restrict__ partial, int L, int NBL, int NB, int C, i
         if (rank < NB) top[rank] = key;
     }
     __syncthreads();
+    // Trim: the k-th smallest bin minimum c_k bounds the k-th smallest coarse row score from above, so k rows have
+    // exact scores <= c_k + eps and no row of a bin whose minimum exceeds c_k + 2 eps can enter the top-k.  Those bins
+    // are not reranked; the first of them becomes the bound the certificate tests (a little extra slack keeps the
+    // certificate's own rounding allowance from rejecting the query).  keep = first j that is empty or (j >= k and
+    // above the cutoff): every thread tests one slot, the minimum wins.
     float eps, slack;                                                // the certificate's allowance, also the trim's
-    tc_bound(METRIC, sqrtf(qsq_s) * 1.0001f, sqrtf(rsq_s) * 1.0001f, stats[0], stats[1], &eps, &slack);
-    if (tid == 0) {
-        float tau = ordered_to_f32(tau_bits);
-        if (top[NB - 1] != VDB_KEY_MAX) tau = fminf(tau, key_score(top[NB - 1]));
-        // Trim: the k-th smallest bin minimum c_k bounds the k-th smallest coarse row score from above, so k rows
-        // have exact scores <= c_k + eps and no row of a bin whose minimum exceeds c_k + 2 eps can enter the
-        // top-k.  Those bins are not reranked; the first of them becomes the bound the certificate tests
-        // (a little extra slack keeps the certificate's own rounding allowance from rejecting the query).
-        int keep = NB;
+    tc_bound(metric, sqrtf(qsq_s) * 1.0001f, sqrtf(rsq_s) * 1.0001f, stats[0], stats[1], &eps, &slack);
+    if (tid == 0) keep_s = NB;
+    __syncthreads();
+    {
         float cutoff = INFINITY;
         if (!no_trim && k - 1 < NB && top[k - 1] != VDB_KEY_MAX) cutoff = key_score(top[k - 1]) + 2.f * eps + 4.f * slack;
-        for (int j = 0; j < NB; ++j) {                               // NB <= 64, one thread scans it
-            if (top[j] == VDB_KEY_MAX) { keep = j; break; }
-            if (j >= k && key_score(top[j]) > cutoff) { keep = j; tau = fminf(tau, key_score(top[j])); break; }
+        if (tid < NB) {
+            const u64 key = top[tid];
+            if (key == VDB_KEY_MAX || (tid >= k && key_score(key) > cutoff)) atomicMin(&keep_s, tid);
         }
-        keep_s = keep;
-        tau_s = tau;
     }
     __syncthreads();
-    // ---- exact rerank of the rows of the kept bins (kBin consecutive rows each: one contiguous kBin x 4D-byte run)
-    const int R = keep_s * kBin;
-    int C2 = 32;
-    while (C2 < R) C2 <<= 1;
-    for (int i = tid; i < C2; i += blockDim.x) rk[i] = VDB_KEY_MAX;
+    if (tid == 0) {
+        const int keep = keep_s;
+        float tau = ordered_to_f32(tau_bits);
+        if (top[NB - 1] != VDB_KEY_MAX) tau = fminf(tau, key_score(top[NB - 1]));
+        if (keep < NB && top[keep] != VDB_KEY_MAX) tau = fminf(tau, key_score(top[keep]));   // the first trimmed bin
+        base_s = keep > 0 ? atomicAdd(item_count, keep) : 0;
+        TcPostQuery o;
+        o.tau_minus = tau - eps - slack;
+        o.qsq = qsq_s;
+        o.keep = keep;
+        o.pad = 0;
+        pq[q] = o;
+    }
     __syncthreads();
-    const float qn = sqrtf(qsq_s);
-    constexpr int RW = 4;                                            // rows in flight per warp (kBin % RW == 0)
+    for (int j = tid; j < keep_s; j += blockDim.x)
+        items[base_s + j] = make_uint2((uint32_t)q * (uint32_t)kNBFinal + (uint32_t)j, key_index(top[j]));
+}
+
+constexpr int kRrMaxWarps = 8;             // warps per CTA, each with its own two-slot ring and its own work items
+constexpr int kRrSlots = 2;
+
+__host__ __device__ inline size_t rr_slot_bytes(int D) { return (size_t)(kBin + 1) * D * 4; }   // kBin rows + the query
+
+// Every WARP streams its own work items (bin = kBin consecutive rows = one contiguous run, plus the bin's query) through
+// a private two-slot ring filled by 1-D bulk copies; no CTA barrier anywhere.  (A CTA-wide ring with one warp per row of
+// a bin ran at 3.7 TB/s: eight warps in lockstep paid the shuffle / global-load latency of every bin in sequence.)
+template <int METRIC>
+__global__ void __launch_bounds__(32 * kRrMaxWarps)
+tc_rerank_bins_kernel(const uint2* __restrict__ items, const int32_t* __restrict__ item_count, const float* __restrict__ qv,
+                      const float* __restrict__ db, int64_t N, int D, const TcPostQuery* __restrict__ pq,
+                      u64* __restrict__ keys) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    __shared__ __align__(8) uint64_t full_s[kRrMaxWarps * kRrSlots];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+    const size_t slot_floats = (size_t)(kBin + 1) * D;
+    float* ring = reinterpret_cast<float*>(smem_raw) + (size_t)warp * kRrSlots * slot_floats;
+    uint64_t* full = full_s + warp * kRrSlots;
+    const int total = *item_count;
+    if (lane == 0) {
+        for (int i = 0; i < kRrSlots; ++i) mbar_init(&full[i], 1);
+        fence_barrier_init();
+    }
+    __syncwarp();
     const int nchunk = D >> 2;
-    for (int base = warp * RW; base < R; base += nwarp * RW) {
-        const int64_t row0 = (int64_t)key_index(top[base / kBin]) * kBin + (base % kBin);
-        float acc[RW], xx[RW];
+    const int gw = (int)blockIdx.x * nwarp + warp, gstride = (int)gridDim.x * nwarp;   // item n of this warp = gw + n * gstride
+    const int mine = total > gw ? (total - gw + gstride - 1) / gstride : 0;
+    uint2 it_l = make_uint2(0u, 0u);                                  // lane l: item (blk + l) of the current 32-item block
+    float qsq_l = 0.f;
+    auto load_block = [&](int blk) {                                  // descriptors of items blk .. blk + 31, one per lane
+        if (blk + lane < mine) {
+            it_l = items[(size_t)gw + (size_t)(blk + lane) * gstride];
+            qsq_l = pq[it_l.x / kNBFinal].qsq;
+        }
+    };
+    auto issue = [&](uint2 it, int n) {                               // lane 0 only
+        const int sl = n % kRrSlots;
+        const int64_t r0 = (int64_t)it.y * kBin;
+        const int64_t rows = N - r0 < kBin ? N - r0 : kBin;
+        const uint32_t bytes = (uint32_t)rows * (uint32_t)D * 4u;
+        float* dst = ring + (size_t)sl * slot_floats;
+        mbar_expect_tx(&full[sl], bytes + (uint32_t)D * 4u);
+        bulk_load_1d(dst, db + (size_t)r0 * D, bytes, &full[sl]);
+        bulk_load_1d(dst + (size_t)kBin * D, qv + (size_t)(it.x / kNBFinal) * D, (uint32_t)D * 4u, &full[sl]);
+    };
+    load_block(0);
+    for (int n = 0; n < kRrSlots && n < mine; ++n) {
+        const uint2 it = make_uint2(__shfl_sync(0xffffffffu, it_l.x, n), __shfl_sync(0xffffffffu, it_l.y, n));
+        if (lane == 0) issue(it, n);
+    }
+    uint2 nx_l = it_l;                                                // descriptors of the NEXT block (prefetched)
+    float nqsq_l = qsq_l;
+    for (int n = 0; n < mine; ++n) {
+        const int j = n & 31;
+        if (j == 0 && n > 0) { it_l = nx_l; qsq_l = nqsq_l; }
+        if (j == 0 && n + 32 < mine) {                                // prefetch the block after this one
+            const uint2 keep_it = it_l;
+            const float keep_q = qsq_l;
+            load_block(n + 32);
+            nx_l = it_l; nqsq_l = qsq_l;
+            it_l = keep_it; qsq_l = keep_q;
+        }
+        const uint2 it = make_uint2(__shfl_sync(0xffffffffu, it_l.x, j), __shfl_sync(0xffffffffu, it_l.y, j));
+        const float qsq = __shfl_sync(0xffffffffu, qsq_l, j);
+        const int sl = n % kRrSlots;
+        mbar_wait(&full[sl], (uint32_t)((n / kRrSlots) & 1));
+        const float* base = ring + (size_t)sl * slot_floats;
+        const float4* q4 = reinterpret_cast<const float4*>(base + (size_t)kBin * D);
+        float acc[kBin], xx[kBin];
 #pragma unroll
-        for (int j = 0; j < RW; ++j) { acc[j] = 0.f; xx[j] = 0.f; }
+        for (int r = 0; r < kBin; ++r) { acc[r] = 0.f; xx[r] = 0.f; }
+        // rerank_f32_kernel's operation order per row: chunk t = lane, lane + 32, ...; four fmas per chunk; butterfly
         for (int t = lane; t < nchunk; t += 32) {
-            float4 x[RW];
+            const float4 qv4 = q4[t];
 #pragma unroll
-            for (int j = 0; j < RW; ++j)
-                x[j] = row0 + j < N ? __ldg(reinterpret_cast<const float4*>(db + (size_t)(row0 + j) * D) + t)
-                                    : make_float4(0.f, 0.f, 0.f, 0.f);
-            const float4 qv4 = *reinterpret_cast<const float4*>(qs + 4 * t);
-#pragma unroll
-            for (int j = 0; j < RW; ++j) {
+            for (int r = 0; r < kBin; ++r) {
+                const float4 v = reinterpret_cast<const float4*>(base + (size_t)r * D)[t];
                 if (METRIC == VDB_METRIC_L2) {
-                    const float d0 = qv4.x - x[j].x, d1 = qv4.y - x[j].y, d2 = qv4.z - x[j].z, d3 = qv4.w - x[j].w;
-                    acc[j] = fmaf(d0, d0, acc[j]); acc[j] = fmaf(d1, d1, acc[j]);
-                    acc[j] = fmaf(d2, d2, acc[j]); acc[j] = fmaf(d3, d3, acc[j]);
+                    const float d0 = qv4.x - v.x, d1 = qv4.y - v.y, d2 = qv4.z - v.z, d3 = qv4.w - v.w;
+                    acc[r] = fmaf(d0, d0, acc[r]); acc[r] = fmaf(d1, d1, acc[r]);
+                    acc[r] = fmaf(d2, d2, acc[r]); acc[r] = fmaf(d3, d3, acc[r]);
                 } else {
-                    acc[j] = fmaf(qv4.x, x[j].x, acc[j]); acc[j] = fmaf(qv4.y, x[j].y, acc[j]);
-                    acc[j] = fmaf(qv4.z, x[j].z, acc[j]); acc[j] = fmaf(qv4.w, x[j].w, acc[j]);
-                    xx[j] = fmaf(x[j].x, x[j].x, xx[j]); xx[j] = fmaf(x[j].y, x[j].y, xx[j]);
-                    xx[j] = fmaf(x[j].z, x[j].z, xx[j]); xx[j] = fmaf(x[j].w, x[j].w, xx[j]);
+                    acc[r] = fmaf(qv4.x, v.x, acc[r]); acc[r] = fmaf(qv4.y, v.y, acc[r]);
+                    acc[r] = fmaf(qv4.z, v.z, acc[r]); acc[r] = fmaf(qv4.w, v.w, acc[r]);
+                    xx[r] = fmaf(v.x, v.x, xx[r]); xx[r] = fmaf(v.y, v.y, xx[r]);
+                    xx[r] = fmaf(v.z, v.z, xx[r]); xx[r] = fmaf(v.w, v.w, xx[r]);
                 }
             }
         }
-        float a_mine = 0.f, x_mine = 0.f;
-#pragma unroll
-        for (int j = 0; j < RW; ++j) {
-            const float a = warp_sum(acc[j]);
-            const float b = (METRIC == VDB_METRIC_COSINE) ? warp_sum(xx[j]) : 0.f;
-            if (lane == j) { a_mine = a; x_mine = b; }
+        __syncwarp();                                                 // every lane is done reading the slot
+        // refill the slot before the reductions: the descriptor of item n + kRrSlots comes from the lane that holds it
+        // (current or prefetched block)
+        {
+            const int m = n + kRrSlots;
+            const int jm = m & 31;
+            const bool in_next = (m >> 5) != (n >> 5);
+            const uint32_t sx = in_next ? nx_l.x : it_l.x, sy = in_next ? nx_l.y : it_l.y;
+            const uint2 itn = make_uint2(__shfl_sync(0xffffffffu, sx, jm), __shfl_sync(0xffffffffu, sy, jm));
+            if (lane == 0 && m < mine) issue(itn, m);
         }
-        if (lane < RW && row0 + lane < N) {
-            const float score = (METRIC == VDB_METRIC_L2) ? sqrtf(a_mine) : -(a_mine / (sqrtf(x_mine) * qn));
-            rk[base + lane] = pack_key(score, (uint32_t)(row0 + lane));
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+            for (int r = 0; r < kBin; ++r) {
+                acc[r] += __shfl_xor_sync(0xffffffffu, acc[r], o);
+                if (METRIC == VDB_METRIC_COSINE) xx[r] += __shfl_xor_sync(0xffffffffu, xx[r], o);
+            }
+        }
+        float a_mine = 0.f, x_mine = 1.f;
+#pragma unroll
+        for (int r = 0; r < kBin; ++r)
+            if (lane == r) { a_mine = acc[r]; x_mine = xx[r]; }
+        if (lane < kBin) {
+            const int64_t row = (int64_t)it.y * kBin + lane;
+            u64 key = VDB_KEY_MAX;
+            if (row < N) {
+                const float score = (METRIC == VDB_METRIC_L2) ? sqrtf(a_mine) : -(a_mine / (sqrtf(x_mine) * sqrtf(qsq)));
+                key = pack_key(score, (uint32_t)row);
+            }
+            keys[(size_t)it.x * kBin + lane] = key;                   // it.x = q * kNBFinal + j
         }
     }
-    __syncthreads();
-    block_bitonic_sort(rk, C2);
-    if (tid == 0) {
-        int n = 0;
-        for (int i = 0; i < C2 && n < k; ++i, ++n) {
-            const u64 key = rk[i];
-            if (key == VDB_KEY_MAX) break;
-            const float sc = key_score(key);
-            out_d[(size_t)q * k + n] = (METRIC == VDB_METRIC_L2) ? sc : -sc;
-            const int64_t idx = (int64_t)key_index(key);
-            out_i[(size_t)q * k + n] = ids ? ids[idx] : idx;
+}
+
+// One warp per query: the k best keys of keep x kBin, outputs, certificate.
+template <int METRIC>
+__global__ void __launch_bounds__(256)
+tc_final_kernel(const u64* __restrict__ keys, const TcPostQuery* __restrict__ pq, int Q, int k, const int64_t* __restrict__ ids,
+                float* __restrict__ out_d, int64_t* __restrict__ out_i, int32_t* __restrict__ uncert) {
+    const int lane = threadIdx.x & 31;
+    const int q = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (q >= Q) return;
+    const TcPostQuery info = pq[q];
+    const int R = info.keep * kBin;
+    constexpr int PER = kNBFinal * kBin / 32;              // keys per lane (16)
+    u64 mine[PER];
+#pragma unroll
+    for (int i = 0; i < PER; ++i) {
+        const int s = i * 32 + lane;
+        mine[i] = s < R ? keys[(size_t)q * kNBFinal * kBin + s] : VDB_KEY_MAX;
+    }
+    u64 my_out = VDB_KEY_MAX;                               // lane r ends up with the r-th best key
+    u64 kth = VDB_KEY_MAX;
+    int got = 0;
+    for (int r = 0; r < k; ++r) {
+        u64 best = mine[0];
+#pragma unroll
+        for (int i = 1; i < PER; ++i) best = mine[i] < best ? mine[i] : best;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const u64 other = __shfl_xor_sync(0xffffffffu, best, o);
+            best = other < best ? other : best;
         }
-        const int got = n;
-        for (; n < k; ++n) {
-            out_d[(size_t)q * k + n] = (METRIC == VDB_METRIC_L2) ? INFINITY : -INFINITY;
-            out_i[(size_t)q * k + n] = -1;
+        if (best == VDB_KEY_MAX) break;
+#pragma unroll
+        for (int i = 0; i < PER; ++i) mine[i] = mine[i] == best ? VDB_KEY_MAX : mine[i];   // keys are unique (score, row)
+        if (lane == r) my_out = best;
+        kth = best;
+        ++got;
+    }
+    if (lane < k) {
+        if (my_out != VDB_KEY_MAX) {
+            const float sc = key_score(my_out);
+            out_d[(size_t)q * k + lane] = (METRIC == VDB_METRIC_L2) ? sc : -sc;
+            const int64_t idx = (int64_t)key_index(my_out);
+            out_i[(size_t)q * k + lane] = ids ? ids[idx] : idx;
+        } else {
+            out_d[(size_t)q * k + lane] = (METRIC == VDB_METRIC_L2) ? INFINITY : -INFINITY;
+            out_i[(size_t)q * k + lane] = -1;
         }
-        // ---- certificate
-        const float t_bound = tau_s;
+    }
+    if (lane == 0) {
         bool ok;
         if (got < k) {
-            ok = (t_bound == INFINITY);                              // fewer than k rows exist: all must have been reranked
+            ok = (info.tau_minus == INFINITY);                       // fewer than k rows exist: all must have been reranked
         } else if (METRIC == VDB_METRIC_L2) {
-            const float dk = key_score(rk[k - 1]);
-            ok = (t_bound - eps - slack) > dk * dk - qsq_s;
+            const float dk = key_score(kth);
+            ok = info.tau_minus > dk * dk - info.qsq;
         } else {
-            const float simk = -key_score(rk[k - 1]);
-            ok = (t_bound - eps - slack) > -simk * qn;
+            const float simk = -key_score(kth);
+            ok = info.tau_minus > -simk * sqrtf(info.qsq);
         }
         if (!ok) {
             const int slot = atomicAdd(uncert, 1);
@@ -722,7 +854,7 @@ static bool plan_tc(int Q, int64_t N, int D, int k, int metric, TcPlan* p) {
 }
 
 struct TcWorkspace {
-    size_t qbf16, partial, tau, rescan, rescan_bytes, total;
+    size_t qbf16, partial, tau, pq, items, keys, counters, rescan, rescan_bytes, total;
 };
 
 static TcWorkspace tc_workspace(const TcPlan& p, int Q, int64_t N, int D, int k) {
@@ -732,6 +864,10 @@ static TcWorkspace tc_workspace(const TcPlan& p, int Q, int64_t N, int D, int k)
     w.qbf16 = take((size_t)Q * p.Dp * 2);
     w.partial = take((size_t)Q * p.S * kGroups * kNBLMax * 8);
     w.tau = take((size_t)Q * 4);
+    w.pq = take((size_t)Q * sizeof(TcPostQuery));
+    w.items = take((size_t)Q * kNBFinal * sizeof(uint2));
+    w.keys = take((size_t)Q * kNBFinal * kBin * 8);
+    w.counters = take(256);
     w.rescan_bytes = exact_f32_subset_workspace(Q, N, D, k);      // fp32 rescan of uncertified queries
     w.rescan = take(w.rescan_bytes);
     w.total = off;
@@ -800,7 +936,8 @@ int vdb_exact_topk_tc(const float* q, int Q, const float* db, const void* mirror
     // per-list depth: lists of 8 are enough when there are many of them (L * 8 >= 4 * kNBFinal), debug bit 2 forces 16
     const int nbl = ((g_tc_flags & 4) || p.S * kGroups * 8 < 4 * kNBFinal) ? 16 : 8;
     uint32_t* gtau = reinterpret_cast<uint32_t*>(tau);            // per-query threshold exchange of the scan
-    tc_query_operand_kernel<<<sm_count() * 2, 256, 0, st>>>(q, qb, Q, D, p.Dp, metric, gtau, out_uncertified);
+    tc_query_operand_kernel<<<sm_count() * 2, 256, 0, st>>>(q, qb, Q, D, p.Dp, metric, gtau, out_uncertified,
+                                                            reinterpret_cast<int32_t*>(base + w.counters));
     CUtensorMap map_a, map_b;
     CUtensorMap map_a2, map_b2;
     int rc = make_map(&map_a, qb, Q, D, p.Dp, kBlockK, kTileM);
@@ -835,20 +972,35 @@ int vdb_exact_topk_tc(const float* q, int Q, const float* db, const void* mirror
     if ((g_tc_flags >> 12) & 0xFF) nbf = (g_tc_flags >> 12) & 0xFF;
     if (nbf > kNBFinal) nbf = kNBFinal;
     if (nbf < k) nbf = k;
-    const size_t post_smem = (size_t)(C + kNBFinal + kNBFinal * kBin) * 8 + (size_t)D * 4;
+    TcPostQuery* pq = reinterpret_cast<TcPostQuery*>(base + w.pq);
+    uint2* items = reinterpret_cast<uint2*>(base + w.items);
+    u64* keys = reinterpret_cast<u64*>(base + w.keys);
+    int32_t* item_count = reinterpret_cast<int32_t*>(base + w.counters);
     {
         ProfScope prof(kProfRerank, st);
+        const size_t sel_smem = (size_t)(C + kNBFinal) * 8;
+        VDB_CUDA(cudaFuncSetAttribute(tc_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sel_smem));
+        tc_select_kernel<<<Q, 128, sel_smem, st>>>(partial, L, nbl, nbf, C, q, D, k, metric, db_stats, (g_tc_flags & 16) ? 1 : 0,
+                                                  pq, items, item_count);
+        // one CTA per SM: as many warps (each with a two-slot ring of bin + query) as shared memory holds, at most 8
+        int rr_warps = (int)((size_t)(max_smem_optin() - 2048) / (kRrSlots * rr_slot_bytes(D)));
+        if (rr_warps > kRrMaxWarps) rr_warps = kRrMaxWarps;
+        VDB_REQUIRE(rr_warps >= 1, VDB_ERR_UNSUPPORTED, "D=%d: a rerank ring does not fit shared memory", D);
+        const size_t rr_smem = (size_t)rr_warps * kRrSlots * rr_slot_bytes(D);
+        const int rr_grid = sm_count();
+        const int rr_threads = 32 * rr_warps;
+        const int fin_blocks = (Q + 7) / 8;
         if (metric == VDB_METRIC_L2) {
-            VDB_CUDA(cudaFuncSetAttribute(tc_post_kernel<VDB_METRIC_L2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)post_smem));
-            tc_post_kernel<VDB_METRIC_L2><<<Q, 256, post_smem, st>>>(partial, L, nbl, nbf, C, N, q, db, ids, D, k, db_stats,
-                                                                    (g_tc_flags & 16) ? 1 : 0, out_d, out_i, out_uncertified);
+            VDB_CUDA(cudaFuncSetAttribute(tc_rerank_bins_kernel<VDB_METRIC_L2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rr_smem));
+            tc_rerank_bins_kernel<VDB_METRIC_L2><<<rr_grid, rr_threads, rr_smem, st>>>(items, item_count, q, db, N, D, pq, keys);
+            tc_final_kernel<VDB_METRIC_L2><<<fin_blocks, 256, 0, st>>>(keys, pq, Q, k, ids, out_d, out_i, out_uncertified);
         } else {
-            VDB_CUDA(cudaFuncSetAttribute(tc_post_kernel<VDB_METRIC_COSINE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)post_smem));
-            tc_post_kernel<VDB_METRIC_COSINE><<<Q, 256, post_smem, st>>>(partial, L, nbl, nbf, C, N, q, db, ids, D, k, db_stats,
-                                                                        (g_tc_flags & 16) ? 1 : 0, out_d, out_i, out_uncertified);
+            VDB_CUDA(cudaFuncSetAttribute(tc_rerank_bins_kernel<VDB_METRIC_COSINE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rr_smem));
+            tc_rerank_bins_kernel<VDB_METRIC_COSINE><<<rr_grid, rr_threads, rr_smem, st>>>(items, item_count, q, db, N, D, pq, keys);
+            tc_final_kernel<VDB_METRIC_COSINE><<<fin_blocks, 256, 0, st>>>(keys, pq, Q, k, ids, out_d, out_i, out_uncertified);
         }
     }
-    count_launch(3);
+    count_launch(5);
     VDB_CUDA(cudaGetLastError());
     // queries the certificate rejected: exact fp32 scan, driven by the device-side list (no host round trip)
     return exact_f32_subset(q, Q, db, ids, N, D, k, metric, out_uncertified + 1, out_uncertified, out_d, out_i,

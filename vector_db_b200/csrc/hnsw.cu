@@ -66,7 +66,7 @@ __device__ __forceinline__ float warp_l2(const float* __restrict__ qs, const flo
         const float4* r4 = reinterpret_cast<const float4*>(row);
         const float4* q4 = reinterpret_cast<const float4*>(qs);
         for (int c = lane; c < (D >> 2); c += 32) {
-            const float4 x = ld_stream_f4(r4 + c);
+            const float4 x = ld_gather_f4(r4 + c);
             const float4 qv = q4[c];
             float d0 = qv.x - x.x, d1 = qv.y - x.y, d2 = qv.z - x.z, d3 = qv.w - x.w;
             acc = fmaf(d0, d0, acc); acc = fmaf(d1, d1, acc); acc = fmaf(d2, d2, acc); acc = fmaf(d3, d3, acc);
@@ -87,8 +87,8 @@ __device__ __forceinline__ void warp_l2_x2(const float* __restrict__ qs, const f
         const float4* b4 = reinterpret_cast<const float4*>(row_b);
         const float4* q4 = reinterpret_cast<const float4*>(qs);
         for (int c = lane; c < (D >> 2); c += 32) {
-            const float4 xa = ld_stream_f4(a4 + c);             // read once: no L1 allocation (keeps adjacency / stack lines)
-            const float4 xb = ld_stream_f4(b4 + c);
+            const float4 xa = ld_gather_f4(a4 + c);             // read once: no L1 allocation (keeps adjacency / stack lines)
+            const float4 xb = ld_gather_f4(b4 + c);
             const float4 qv = q4[c];
             float d0 = qv.x - xa.x, d1 = qv.y - xa.y, d2 = qv.z - xa.z, d3 = qv.w - xa.w;
             acc_a = fmaf(d0, d0, acc_a); acc_a = fmaf(d1, d1, acc_a); acc_a = fmaf(d2, d2, acc_a); acc_a = fmaf(d3, d3, acc_a);
@@ -128,39 +128,50 @@ __device__ __forceinline__ int lower_bound_u64(const u64* sorted, int n, u64 key
     return lo;
 }
 
-// CTA-wide: dist of query to `node`, returned to every thread (one warp computes, broadcast via smem)
+// The traversal code below is written for a GROUP of NT threads working on one query with its own BeamMem: NT = 128
+// = the whole CTA (insert / wave-build kernels), NT = 32 = one warp (the search kernel: every warp runs its own query,
+// no CTA barrier anywhere).  group_sync<NT>() is the group's barrier, tid / warp are indices within the group.
+template <int NT>
+__device__ __forceinline__ void group_sync() {
+    if (NT == 32) __syncwarp(); else __syncthreads();
+}
+
+// group-wide: dist of query to `node`, returned to every thread (one warp computes, broadcast via smem)
+template <int NT>
 __device__ __forceinline__ float cta_dist_one(const Graph& g, BeamMem& m, int node) {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31, warp = (threadIdx.x % NT) >> 5;
     if (warp == 0) {
         float d = warp_l2(m.qs, g.db + (size_t)node * g.D, g.D, lane);
         if (lane == 0) m.newk[0] = pack_key(d, 0);
     }
-    __syncthreads();
+    group_sync<NT>();
     float d = key_score(m.newk[0]);
-    __syncthreads();
+    group_sync<NT>();
     return d;
 }
 
 // a5: strict-improvement hill climb on one upper level.  Returns the local minimum; *evals += work.
+template <int NT>
 __device__ int greedy_level(const Graph& g, BeamMem& m, int cur, int level, unsigned* evals) {
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    float cur_d = cta_dist_one(g, m, cur);
+    constexpr int kNW = NT / 32;
+    const int tid = threadIdx.x % NT, lane = tid & 31, warp = tid >> 5;
+    float cur_d = cta_dist_one<NT>(g, m, cur);
     *evals += 1;
     while (true) {
         int deg;
         const int32_t* nb = nbr_list(g, cur, level, &deg);
         if (tid == 0) m.scal[0] = 0;
-        __syncthreads();
+        group_sync<NT>();
         // keep list order: position p stays the tie-break ("first strictly smaller wins")
-        for (int p = tid; p < deg; p += kHnswThreads) {
+        for (int p = tid; p < deg; p += NT) {
             int r = __ldcg(nb + p);
             bool ok = r >= 0 && (g.alive == nullptr || bit_set(g.alive, r));
             m.todo[p] = ok ? r : -1;
             if (ok) atomicAdd(m.scal, 1);
         }
-        __syncthreads();
+        group_sync<NT>();
         *evals += (unsigned)m.scal[0];
-        for (int p = warp; p < deg; p += kHnswWarps) {
+        for (int p = warp; p < deg; p += kNW) {
             int r = m.todo[p];
             u64 key = VDB_KEY_MAX;
             if (r >= 0) {
@@ -169,13 +180,13 @@ __device__ int greedy_level(const Graph& g, BeamMem& m, int cur, int level, unsi
             }
             if (lane == 0) m.newk[p] = key;
         }
-        __syncthreads();
+        group_sync<NT>();
         // min over (d, position)
         u64 best = VDB_KEY_MAX;
         for (int p = 0; p < deg; ++p) { u64 kx = m.newk[p]; best = kx < best ? kx : best; }
         int next = cur;
         if (best != VDB_KEY_MAX && key_score(best) < cur_d) { cur_d = key_score(best); next = m.todo[key_index(best)]; }
-        __syncthreads();
+        group_sync<NT>();
         if (next == cur) return cur;
         cur = next;
     }
@@ -183,12 +194,14 @@ __device__ int greedy_level(const Graph& g, BeamMem& m, int cur, int level, unsi
 
 // a4: best-first beam on one level.  On return found[*which_found][0..return value) holds the
 // (dist,row) keys ascending.  `filter` gates results only.  stats[0] += evals, stats[1] += expansions.
+template <int NT>
 __device__ int beam_search(const Graph& g, BeamMem& m, int entry, int level, int ef, const uint32_t* filter,
                            int* which_found, unsigned* evals, unsigned* expansions) {
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    for (int i = tid; i < m.H; i += kHnswThreads) m.hash[i] = kEmpty;
-    __syncthreads();
-    const float d0 = cta_dist_one(g, m, entry);
+    constexpr int kNW = NT / 32;
+    const int tid = threadIdx.x % NT, lane = tid & 31, warp = tid >> 5;
+    for (int i = tid; i < m.H; i += NT) m.hash[i] = kEmpty;
+    group_sync<NT>();
+    const float d0 = cta_dist_one<NT>(g, m, entry);
     *evals += 1;
     int cc = 0, cf = 0;           // current buffers
     int ncand = 1, nfound = 0;
@@ -203,7 +216,7 @@ __device__ int beam_search(const Graph& g, BeamMem& m, int entry, int level, int
         nfound = 1;
     }
     unsigned nvisited = 1;
-    __syncthreads();
+    group_sync<NT>();
 
     while (ncand > 0) {
         const u64 top = m.cand[cc][0];
@@ -214,8 +227,8 @@ __device__ int beam_search(const Graph& g, BeamMem& m, int entry, int level, int
         int deg;
         const int32_t* nb = nbr_list(g, node, level, &deg);
         if (tid == 0) m.scal[0] = 0;
-        __syncthreads();
-        for (int p = tid; p < deg; p += kHnswThreads) {
+        group_sync<NT>();
+        for (int p = tid; p < deg; p += NT) {
             int r = __ldcg(nb + p);
             if (r >= 0 && visited_insert(m.hash, m.H, m.logH, (uint32_t)r)) {
                 if (g.alive == nullptr || bit_set(g.alive, r)) {     // tombstones: visited, never evaluated
@@ -226,11 +239,11 @@ __device__ int beam_search(const Graph& g, BeamMem& m, int entry, int level, int
                 }
             }
         }
-        __syncthreads();
+        group_sync<NT>();
         const int ntodo = m.scal[0];
         *evals += (unsigned)ntodo;
         nvisited += (unsigned)ntodo;
-        for (int i = 2 * warp; i < ntodo; i += 2 * kHnswWarps) {
+        for (int i = 2 * warp; i < ntodo; i += 2 * kNW) {
             const int r = m.todo[i];
             if (i + 1 < ntodo) {
                 const int r2 = m.todo[i + 1];
@@ -242,9 +255,9 @@ __device__ int beam_search(const Graph& g, BeamMem& m, int entry, int level, int
                 if (lane == 0) m.newk[i] = pack_key(d, (uint32_t)r);
             }
         }
-        __syncthreads();
+        group_sync<NT>();
         // rank sort of the new keys; ppass[i] = number of filter-passing keys before sorted slot i
-        for (int i = tid; i < ntodo; i += kHnswThreads) {
+        for (int i = tid; i < ntodo; i += NT) {
             const u64 mine = m.newk[i];
             int rank = 0, prank = 0;
             for (int j = 0; j < ntodo; ++j) {
@@ -257,7 +270,7 @@ __device__ int beam_search(const Graph& g, BeamMem& m, int entry, int level, int
             m.news[rank] = mine;
             m.ppass[rank] = prank;
         }
-        __syncthreads();
+        group_sync<NT>();
         int npass = ntodo;
         if (filter != nullptr) {
             npass = 0;
@@ -267,18 +280,18 @@ __device__ int beam_search(const Graph& g, BeamMem& m, int entry, int level, int
             }
         }
         if (tid == 0) m.ppass[ntodo] = npass;
-        __syncthreads();
+        group_sync<NT>();
 
         // ---- merge into found (keep the ef smallest)
         const u64* fsrc = m.found[cf];
         u64* fdst = m.found[cf ^ 1];
-        for (int i = tid; i < nfound; i += kHnswThreads) {
+        for (int i = tid; i < nfound; i += NT) {
             const u64 key = fsrc[i];
             const int lb = lower_bound_u64(m.news, ntodo, key);
             const int pos = i + m.ppass[lb];
             if (pos < ef) fdst[pos] = key;
         }
-        for (int i = tid; i < ntodo; i += kHnswThreads) {
+        for (int i = tid; i < ntodo; i += NT) {
             const u64 key = m.news[i];
             if (filter == nullptr || bit_set(filter, (int)key_index(key))) {
                 const int pos = m.ppass[i] + lower_bound_u64(fsrc, nfound, key);
@@ -287,7 +300,7 @@ __device__ int beam_search(const Graph& g, BeamMem& m, int entry, int level, int
         }
         int nfound_new = nfound + npass;
         if (nfound_new > ef) nfound_new = ef;
-        __syncthreads();
+        group_sync<NT>();
         cf ^= 1;
         nfound = nfound_new;
 
@@ -306,12 +319,12 @@ __device__ int beam_search(const Graph& g, BeamMem& m, int entry, int level, int
             keep_new = lower_bound_u64(m.news, ntodo, limit);
             if (keep_new < ntodo && m.news[keep_new] == limit) ++keep_new;
         }
-        for (int i = tid; i < keep_old; i += kHnswThreads) {
+        for (int i = tid; i < keep_old; i += NT) {
             const u64 key = csrc[i];
             const int pos = i + lower_bound_u64(m.news, keep_new, key);
             if (pos < m.CC) cdst[pos] = key;
         }
-        for (int i = tid; i < keep_new; i += kHnswThreads) {
+        for (int i = tid; i < keep_new; i += NT) {
             const u64 key = m.news[i];
             const int pos = i + lower_bound_u64(csrc, keep_old, key);
             if (pos < m.CC) cdst[pos] = key;
@@ -324,7 +337,7 @@ __device__ int beam_search(const Graph& g, BeamMem& m, int entry, int level, int
             ncand_new = m.CC;
             if (tid == 0) m.scal[1] |= 2;
         }
-        __syncthreads();
+        group_sync<NT>();
         cc ^= 1;
         ncand = ncand_new;
         if (nvisited + (unsigned)m.scal[2] > (unsigned)(m.H - (m.H >> 2))) {   // visited table above 75% load
@@ -332,7 +345,7 @@ __device__ int beam_search(const Graph& g, BeamMem& m, int entry, int level, int
             break;
         }
     }
-    __syncthreads();
+    group_sync<NT>();
     *which_found = cf;
     return nfound;
 }
@@ -384,8 +397,8 @@ hnsw_search_kernel(Graph g, const float* __restrict__ q, int Q, int32_t entry_ro
         int nfound = 0, wf = 0;
         if (entry_row >= 0) {
             int cur = entry_row;
-            for (int level = max_level; level >= 1; --level) cur = greedy_level(g, m, cur, level, &evals);
-            nfound = beam_search(g, m, cur, 0, ef, filter, &wf, &evals, &expansions);
+            for (int level = max_level; level >= 1; --level) cur = greedy_level<kHnswThreads>(g, m, cur, level, &evals);
+            nfound = beam_search<kHnswThreads>(g, m, cur, 0, ef, filter, &wf, &evals, &expansions);
             if (m.scal[1] && tid == 0) atomicOr(overflow_flag, m.scal[1]);
             if (out_status && tid == 0) out_status[qi] = m.scal[1];      // bit 0 visited table full, bit 1 frontier cut
         } else if (out_status && tid == 0) {
@@ -403,6 +416,51 @@ hnsw_search_kernel(Graph g, const float* __restrict__ q, int Q, int32_t entry_ro
             }
         }
         if (out_stats && tid == 0) { out_stats[2 * qi] = evals; out_stats[2 * qi + 1] = expansions; }
+    }
+}
+
+// The same search with ONE WARP per query (4 independent warps per CTA, no CTA barrier): the CTA-per-query form above
+// spends 19 % of its warp time at barriers and keeps loads in flight only ~60 % of the time (the four warps of a CTA walk
+// through hash / sort / merge phases together), which left the traversal at 5.5 TB/s of row gathers against the 7.2 TB/s a
+// plain random 3 KB gather reaches on this GPU (scripts/ubench/gather.cu).  A warp alone has nothing to wait for but its
+// own loads; every warp owns a BeamMem slice of shared memory and a visited table in global memory.
+__global__ void __launch_bounds__(kHnswThreads)
+hnsw_search_warp_kernel(Graph g, const float* __restrict__ q, int Q, int32_t entry_row, int max_level, int ef, int k,
+                        const uint32_t* __restrict__ filter, int CC, int NM, int H, uint32_t* global_hash, int warp_smem,
+                        float* __restrict__ out_d, int32_t* __restrict__ out_rows, uint32_t* __restrict__ out_stats,
+                        int32_t* __restrict__ out_status, int* __restrict__ overflow_flag) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int gw = (int)blockIdx.x * kHnswWarps + warp, nw = (int)gridDim.x * kHnswWarps;
+    BeamMem m;
+    carve(m, smem_raw + (size_t)warp * warp_smem, g.D, CC, ef, NM, H, global_hash + (size_t)gw * H);
+    for (int qi = gw; qi < Q; qi += nw) {
+        __syncwarp();
+        for (int t = lane; t < g.D; t += 32) m.qs[t] = q[(size_t)qi * g.D + t];
+        __syncwarp();
+        unsigned evals = 0, expansions = 0;
+        int nfound = 0, wf = 0;
+        if (entry_row >= 0) {
+            int cur = entry_row;
+            for (int level = max_level; level >= 1; --level) cur = greedy_level<32>(g, m, cur, level, &evals);
+            nfound = beam_search<32>(g, m, cur, 0, ef, filter, &wf, &evals, &expansions);
+            if (m.scal[1] && lane == 0) atomicOr(overflow_flag, m.scal[1]);
+            if (out_status && lane == 0) out_status[qi] = m.scal[1];     // bit 0 visited table full, bit 1 frontier cut
+        } else if (out_status && lane == 0) {
+            out_status[qi] = 0;
+        }
+        for (int i = lane; i < k; i += 32) {
+            size_t o = (size_t)qi * k + i;
+            if (i < nfound) {
+                u64 key = m.found[wf][i];
+                out_d[o] = key_score(key);
+                out_rows[o] = (int32_t)key_index(key);
+            } else {
+                out_d[o] = INFINITY;
+                out_rows[o] = -1;
+            }
+        }
+        if (out_stats && lane == 0) { out_stats[2 * qi] = evals; out_stats[2 * qi + 1] = expansions; }
     }
 }
 
@@ -445,10 +503,10 @@ hnsw_insert_kernel(Graph g, const int32_t* __restrict__ levels, int32_t first, i
         }
         unsigned evals = 0, expansions = 0;
         int cur = entry;
-        for (int level = top; level > lvl; --level) cur = greedy_level(g, m, cur, level, &evals);
+        for (int level = top; level > lvl; --level) cur = greedy_level<kHnswThreads>(g, m, cur, level, &evals);
         for (int level = (lvl < top ? lvl : top); level >= 0; --level) {
             int wf = 0;
-            const int nf = beam_search(g, m, cur, level, efc, nullptr, &wf, &evals, &expansions);
+            const int nf = beam_search<kHnswThreads>(g, m, cur, level, efc, nullptr, &wf, &evals, &expansions);
             if (m.scal[1] && tid == 0) atomicOr(overflow_flag, 1);
             const u64* found = m.found[wf];
             const int nsel = nf < M ? nf : M;
@@ -535,7 +593,7 @@ hnsw_build_search_kernel(Graph g, const int32_t* __restrict__ nodes, int count, 
         __syncthreads();
         unsigned evals = 0, expansions = 0;
         int cur = entry_row;
-        for (int l = max_level; l > level; --l) cur = greedy_level(g, m, cur, l, &evals);
+        for (int l = max_level; l > level; --l) cur = greedy_level<kHnswThreads>(g, m, cur, l, &evals);
         // `cur` may not be linked on this level yet (it is the node itself when the node also lives
         // on the level above): enter through its closest upper-level neighbour that is, else the seed
         int deg;
@@ -556,7 +614,7 @@ hnsw_build_search_kernel(Graph g, const int32_t* __restrict__ nodes, int count, 
             cur = pick;
         }
         int wf = 0;
-        const int nf = beam_search(g, m, cur, level, efc, nullptr, &wf, &evals, &expansions);
+        const int nf = beam_search<kHnswThreads>(g, m, cur, level, efc, nullptr, &wf, &evals, &expansions);
         if (m.scal[1] && tid == 0) atomicOr(overflow_flag, 1);
         const u64* found = m.found[wf];
         // the node itself can be reached (it is linked on the upper levels): skip it
@@ -623,6 +681,7 @@ hnsw_reverse_merge_kernel(int32_t* __restrict__ adj, float* __restrict__ adjd, i
 }
 
 static int g_hnsw_ctas_per_sm = 8;               // resident CTAs per SM the search grid is sized for (debug setter below)
+static int g_hnsw_mode = 0;                      // 0: one warp per query (default), 1: one CTA per query
 static int g_hnsw_smem_hash_limit = 48 * 1024;   // visited hash stays in shared memory only below this CTA footprint
 static int pick_hash_slots(int ef, int deg) {
     long long want = ((long long)(ef + 32) * deg * 5) / 4;
@@ -639,11 +698,12 @@ extern "C" {
 
 void vdb_debug_set_hnsw_smem_hash_limit(int bytes) { g_hnsw_smem_hash_limit = bytes; }
 void vdb_debug_set_hnsw_ctas_per_sm(int n) { g_hnsw_ctas_per_sm = n < 1 ? 1 : (n > 16 ? 16 : n); }
+void vdb_debug_set_hnsw_mode(int mode) { g_hnsw_mode = mode; }
 
 size_t vdb_hnsw_search_workspace(int Q, int ef, int deg0) {
     (void)Q;
     size_t h = (size_t)pick_hash_slots(ef, deg0) * 4;   // forced-retry variant may ask for 4x
-    return 256 + (size_t)sm_count() * 16 * h * 4;
+    return 256 + (size_t)sm_count() * 32 * h * 4;          // up to 32 traversals (warps or CTAs) resident per SM
 }
 
 int vdb_hnsw_search(const float* q, int Q, const float* db, int64_t N, int D, const int32_t* adj0, int deg0,
@@ -669,6 +729,29 @@ int vdb_hnsw_search(const float* q, int Q, const float* db, int64_t N, int D, co
     int H = hash_slots ? hash_slots : pick_hash_slots(ef, deg0);
     size_t smem_with = beam_smem_bytes(D, CC, ef, NM, H);
     size_t smem_without = beam_smem_bytes(D, CC, ef, NM, 0);
+    int* flag = static_cast<int*>(ws);
+    if (g_hnsw_mode == 0 && smem_without * kHnswWarps <= (size_t)max_smem_optin() - 1024) {
+        // one warp per query: 4 independent warps per CTA, visited tables in global memory
+        const size_t smem = smem_without * kHnswWarps;
+        VDB_CUDA(cudaFuncSetAttribute(hnsw_search_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        int per_sm = 1;
+        VDB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, hnsw_search_warp_kernel, kHnswThreads, smem));
+        if (per_sm < 1) per_sm = 1;
+        if (per_sm > g_hnsw_ctas_per_sm) per_sm = g_hnsw_ctas_per_sm;
+        int grid = sm_count() * per_sm;
+        const int want = (Q + kHnswWarps - 1) / kHnswWarps;
+        if (grid > want) grid = want;
+        const size_t need = 256 + (size_t)grid * kHnswWarps * H * 4;
+        VDB_REQUIRE(ws_bytes >= need, VDB_ERR_WORKSPACE, "workspace %zu < %zu", ws_bytes, need);
+        VDB_CUDA(cudaMemsetAsync(flag, 0, 4, st));
+        ProfScope prof(kProfHnswSearch, st);
+        hnsw_search_warp_kernel<<<grid, kHnswThreads, smem, st>>>(g, q, Q, entry_row, max_level, ef, k, filter, CC, NM, H,
+                                                                 reinterpret_cast<uint32_t*>(static_cast<char*>(ws) + 256),
+                                                                 (int)smem_without, out_d, out_rows, out_stats, out_status, flag);
+        count_launch(1);
+        VDB_CUDA(cudaGetLastError());
+        return VDB_OK;
+    }
     // a big shared-memory hash caps the CTAs per SM, and the traversal needs occupancy to hide gather latency
     const bool use_global = hash_slots != 0 || smem_with > (size_t)g_hnsw_smem_hash_limit;
     size_t smem = use_global ? smem_without : smem_with;
@@ -680,7 +763,6 @@ int vdb_hnsw_search(const float* q, int Q, const float* db, int64_t N, int D, co
     if (per_sm > g_hnsw_ctas_per_sm) per_sm = g_hnsw_ctas_per_sm;
     int grid = sm_count() * per_sm;
     if (grid > Q) grid = Q;
-    int* flag = static_cast<int*>(ws);
     uint32_t* ghash = nullptr;
     if (use_global) {
         size_t need = 256 + (size_t)grid * H * 4;

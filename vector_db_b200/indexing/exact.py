@@ -71,23 +71,22 @@ class ExactIndex:
         return ops.exact_topk_f32(q, st.vecs, k, self.metric, ids=st.ids, row_mask=mask, n_rows=st.n)
 
     def search(self, queries: np.ndarray, k: int, filter_ids=None) -> Tuple[np.ndarray, np.ndarray]:
-        """Host in / host out, one blocking call.  A large unfiltered batch is cut into 1024-query-aligned pieces that
-        go through the ``search_batches`` pipeline, so the call's own H2D / host staging / D2H copies run under the
-        scan of the neighbouring piece instead of in front of and behind one big scan (a 4096-query piece count of 2
-        keeps every piece a full wave of the tensor-core scan)."""
+        """Host in / host out, one blocking call: the queries go to pinned memory and on to the device in chunks (the
+        DMA of one chunk runs under the host copy of the next), the results come back through pinned buffers with one
+        synchronisation."""
         q_host = np.ascontiguousarray(queries, dtype=np.float32).reshape(-1, self.dim)
         nq = q_host.shape[0]
         dev = self.store.device
-        if filter_ids is None and nq >= 2048:
-            pieces = 2 if nq < 8192 else 4
-            step = (-(-nq // pieces) + 127) // 128 * 128
-            outs = list(self.search_batches((q_host[s:s + step] for s in range(0, nq, step)), k, depth=2))
-            return np.concatenate([o[0] for o in outs]), np.concatenate([o[1] for o in outs])
         if self._pin is None or self._pin.shape[0] < nq:
             self._pin = torch.empty((max(nq, 64), self.dim), dtype=torch.float32).pin_memory()
             self._pin_out = None
-        self._pin[:nq].copy_(torch.from_numpy(q_host))
-        q = self._pin[:nq].to(dev, non_blocking=True)
+        q = torch.empty((nq, self.dim), dtype=torch.float32, device=dev)
+        src = torch.from_numpy(q_host)
+        step = max(256, -(-nq // 4))
+        for s in range(0, nq, step):
+            e = min(nq, s + step)
+            self._pin[s:e].copy_(src[s:e])
+            q[s:e].copy_(self._pin[s:e], non_blocking=True)
         d, i = self.search_device(q, k, filter_ids)
         po = getattr(self, "_pin_out", None)
         if po is None or po[0].shape[0] < nq or po[0].shape[1] != k:

@@ -342,7 +342,7 @@ def hnsw_search(q: torch.Tensor, db: torch.Tensor, n_rows: int, adj0: torch.Tens
         while base < want:
             base *= 2
         hash_slots = base * 4 if hash_slots == 0 else hash_slots * 4
-        nbytes = 256 + 16 * torch.cuda.get_device_properties(dev).multi_processor_count * hash_slots * 4
+        nbytes = 256 + 32 * torch.cuda.get_device_properties(dev).multi_processor_count * hash_slots * 4
     raise _lib.VdbError("hnsw_search: visited table overflow persists")
 
 
