@@ -589,6 +589,14 @@ def path_staging(dev, peaks):
         for _ in range(3):
             ids, vecs = st.stage_to_device(dev)
             runs.append(dict(st.last_stage))
+        sweep = {}
+        for thr in (4, 8, 16, 32):
+            for chunk in (16384, 65536):
+                st._stage_ring = None
+                st.stage_to_device(dev, chunk_records=chunk, threads=thr)                  # first call allocates the ring
+                st.stage_to_device(dev, chunk_records=chunk, threads=thr)
+                sweep[f"threads={thr},chunk_records={chunk}"] = round(st.last_stage["gb_per_s"], 2)
+        st._stage_ring = None
         best = max(runs, key=lambda r_: r_["gb_per_s"])
         t0 = time.perf_counter()
         ids1, vecs1 = st.stage_to_device(dev, threads=1, depth=2)
@@ -601,7 +609,7 @@ def path_staging(dev, peaks):
                                        f"page-cache resident) -> HBM SoA"},
                 "metric": "GB/s", "value": best["gb_per_s"], "unit": "GB/s (file bytes / wall time)", "seconds": best["seconds"],
                 "threads": best["threads"], "ring_depth": best["depth"], "runs_gb_per_s": [round(r_["gb_per_s"], 2) for r_ in runs],
-                "single_thread_fill_gb_per_s": round(single["gb_per_s"], 2),
+                "single_thread_fill_gb_per_s": round(single["gb_per_s"], 2), "sweep_gb_per_s": sweep,
                 "pinned_h2d_gb_per_s": h2d_gbs, "frac_of_pinned_h2d": best["gb_per_s"] / h2d_gbs,
                 "parity": {"checked_rows": 64, "rows_equal": ok}}
     finally:

@@ -225,10 +225,8 @@ int vdb_hnsw_search(const float* q, int Q, const float* db, int64_t N, int D,
 
 /* bench/debug only: CTA shared-memory footprint above which the visited hash moves to global memory */
 void vdb_debug_set_hnsw_smem_hash_limit(int bytes);
-/* bench/debug only: resident CTAs per SM the search grid is sized for (default 8, at most 16) */
+/* bench/debug only: resident CTAs per SM the search grid is sized for (default 12, at most 16) */
 void vdb_debug_set_hnsw_ctas_per_sm(int n);
-/* bench/debug only: 0 = one warp per query (default), 1 = one CTA per query (the round-1 kernel, kept for A/B runs) */
-void vdb_debug_set_hnsw_mode(int mode);
 
 /* ---- a7 HNSW construction ----------------------------------------------------------------------
  * Sequential-semantics insert of rows first..first+count-1 (their vectors already in `db`, their

@@ -16,7 +16,8 @@ vec = idx._vectors
 entry_row, top = idx._read_state()
 lib = _lib.load()
 ref = None
-for cap in [int(a) for a in (sys.argv[1:] or ["8", "9", "10", "12", "16"])]:
+for spec in (sys.argv[1:] or ["c8", "c9", "c10", "c12", "c16"]):
+    cap = int(spec[1:])                                               # cN: N resident CTAs per SM
     lib.vdb_debug_set_hnsw_ctas_per_sm(cap)
     def step():
         return ops.hnsw_search(Qd, vec.vecs, vec.n, idx._adj0, idx._adj_up, idx._up_ptr_dev, entry_row, top, ef, K,
@@ -32,4 +33,4 @@ for cap in [int(a) for a in (sys.argv[1:] or ["8", "9", "10", "12", "16"])]:
     if ref is None:
         ref = out
     same = bool(torch.equal(out[1], ref[1]) and torch.equal(out[2], ref[2]))
-    print(f"ctas/SM cap {cap:2d}: kernel {ms / n:.3f} ms -> {Q / (ms / n) * 1e3:.0f} QPS  same_results={same}", flush=True)
+    print(f"{spec:>4s}: kernel {ms / n:.3f} ms -> {Q / (ms / n) * 1e3:.0f} QPS  same_results={same}", flush=True)

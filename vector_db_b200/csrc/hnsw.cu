@@ -128,9 +128,9 @@ __device__ __forceinline__ int lower_bound_u64(const u64* sorted, int n, u64 key
     return lo;
 }
 
-// The traversal code below is written for a GROUP of NT threads working on one query with its own BeamMem: NT = 128
-// = the whole CTA (insert / wave-build kernels), NT = 32 = one warp (the search kernel: every warp runs its own query,
-// no CTA barrier anywhere).  group_sync<NT>() is the group's barrier, tid / warp are indices within the group.
+// The traversal code below is written for a GROUP of NT threads working on one query with its own BeamMem: NT = 128 = the
+// whole CTA in every kernel of this file (NT = 32, one warp per query, was measured and dropped -- see hnsw_search_kernel).
+// group_sync<NT>() is the group's barrier, tid / warp are indices within the group.
 template <int NT>
 __device__ __forceinline__ void group_sync() {
     if (NT == 32) __syncwarp(); else __syncthreads();
@@ -380,7 +380,11 @@ __host__ __device__ __forceinline__ size_t beam_smem_bytes_dev(int D, int CC, in
 static size_t beam_smem_bytes(int D, int CC, int EF, int NM, int H_in_smem) {
     return beam_smem_bytes_dev(D, CC, EF, NM, H_in_smem);
 }
-__global__ void __launch_bounds__(kHnswThreads)
+// 12 resident CTAs per SM (40 registers): the traversal is bound by the row gathers it keeps in flight, and the number of
+// resident warps is what sets that -- 8 CTAs (56 registers): 40.2 ms per 10k queries at cfg 4, 9: 37.9, 10: 35.8, 12: 34.1,
+// 14-16 (32 registers): 33.7-34.1.  (One WARP per query, no CTA barrier at all, measured 66 ms: the per-query sort / merge
+// phases done by 32 lanes cost what the barriers saved.)
+__global__ void __launch_bounds__(kHnswThreads, 12)
 hnsw_search_kernel(Graph g, const float* __restrict__ q, int Q, int32_t entry_row, int max_level, int ef, int k,
                    const uint32_t* __restrict__ filter, int CC, int NM, int H, uint32_t* global_hash,
                    float* __restrict__ out_d, int32_t* __restrict__ out_rows, uint32_t* __restrict__ out_stats,
@@ -416,51 +420,6 @@ hnsw_search_kernel(Graph g, const float* __restrict__ q, int Q, int32_t entry_ro
             }
         }
         if (out_stats && tid == 0) { out_stats[2 * qi] = evals; out_stats[2 * qi + 1] = expansions; }
-    }
-}
-
-// The same search with ONE WARP per query (4 independent warps per CTA, no CTA barrier): the CTA-per-query form above
-// spends 19 % of its warp time at barriers and keeps loads in flight only ~60 % of the time (the four warps of a CTA walk
-// through hash / sort / merge phases together), which left the traversal at 5.5 TB/s of row gathers against the 7.2 TB/s a
-// plain random 3 KB gather reaches on this GPU (scripts/ubench/gather.cu).  A warp alone has nothing to wait for but its
-// own loads; every warp owns a BeamMem slice of shared memory and a visited table in global memory.
-__global__ void __launch_bounds__(kHnswThreads)
-hnsw_search_warp_kernel(Graph g, const float* __restrict__ q, int Q, int32_t entry_row, int max_level, int ef, int k,
-                        const uint32_t* __restrict__ filter, int CC, int NM, int H, uint32_t* global_hash, int warp_smem,
-                        float* __restrict__ out_d, int32_t* __restrict__ out_rows, uint32_t* __restrict__ out_stats,
-                        int32_t* __restrict__ out_status, int* __restrict__ overflow_flag) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int gw = (int)blockIdx.x * kHnswWarps + warp, nw = (int)gridDim.x * kHnswWarps;
-    BeamMem m;
-    carve(m, smem_raw + (size_t)warp * warp_smem, g.D, CC, ef, NM, H, global_hash + (size_t)gw * H);
-    for (int qi = gw; qi < Q; qi += nw) {
-        __syncwarp();
-        for (int t = lane; t < g.D; t += 32) m.qs[t] = q[(size_t)qi * g.D + t];
-        __syncwarp();
-        unsigned evals = 0, expansions = 0;
-        int nfound = 0, wf = 0;
-        if (entry_row >= 0) {
-            int cur = entry_row;
-            for (int level = max_level; level >= 1; --level) cur = greedy_level<32>(g, m, cur, level, &evals);
-            nfound = beam_search<32>(g, m, cur, 0, ef, filter, &wf, &evals, &expansions);
-            if (m.scal[1] && lane == 0) atomicOr(overflow_flag, m.scal[1]);
-            if (out_status && lane == 0) out_status[qi] = m.scal[1];     // bit 0 visited table full, bit 1 frontier cut
-        } else if (out_status && lane == 0) {
-            out_status[qi] = 0;
-        }
-        for (int i = lane; i < k; i += 32) {
-            size_t o = (size_t)qi * k + i;
-            if (i < nfound) {
-                u64 key = m.found[wf][i];
-                out_d[o] = key_score(key);
-                out_rows[o] = (int32_t)key_index(key);
-            } else {
-                out_d[o] = INFINITY;
-                out_rows[o] = -1;
-            }
-        }
-        if (out_stats && lane == 0) { out_stats[2 * qi] = evals; out_stats[2 * qi + 1] = expansions; }
     }
 }
 
@@ -680,8 +639,7 @@ hnsw_reverse_merge_kernel(int32_t* __restrict__ adj, float* __restrict__ adjd, i
     }
 }
 
-static int g_hnsw_ctas_per_sm = 8;               // resident CTAs per SM the search grid is sized for (debug setter below)
-static int g_hnsw_mode = 0;                      // 0: one warp per query (default), 1: one CTA per query
+static int g_hnsw_ctas_per_sm = 12;              // resident CTAs per SM the search grid is sized for (debug setter below)
 static int g_hnsw_smem_hash_limit = 48 * 1024;   // visited hash stays in shared memory only below this CTA footprint
 static int pick_hash_slots(int ef, int deg) {
     long long want = ((long long)(ef + 32) * deg * 5) / 4;
@@ -698,7 +656,6 @@ extern "C" {
 
 void vdb_debug_set_hnsw_smem_hash_limit(int bytes) { g_hnsw_smem_hash_limit = bytes; }
 void vdb_debug_set_hnsw_ctas_per_sm(int n) { g_hnsw_ctas_per_sm = n < 1 ? 1 : (n > 16 ? 16 : n); }
-void vdb_debug_set_hnsw_mode(int mode) { g_hnsw_mode = mode; }
 
 size_t vdb_hnsw_search_workspace(int Q, int ef, int deg0) {
     (void)Q;
@@ -730,28 +687,6 @@ int vdb_hnsw_search(const float* q, int Q, const float* db, int64_t N, int D, co
     size_t smem_with = beam_smem_bytes(D, CC, ef, NM, H);
     size_t smem_without = beam_smem_bytes(D, CC, ef, NM, 0);
     int* flag = static_cast<int*>(ws);
-    if (g_hnsw_mode == 0 && smem_without * kHnswWarps <= (size_t)max_smem_optin() - 1024) {
-        // one warp per query: 4 independent warps per CTA, visited tables in global memory
-        const size_t smem = smem_without * kHnswWarps;
-        VDB_CUDA(cudaFuncSetAttribute(hnsw_search_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        int per_sm = 1;
-        VDB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, hnsw_search_warp_kernel, kHnswThreads, smem));
-        if (per_sm < 1) per_sm = 1;
-        if (per_sm > g_hnsw_ctas_per_sm) per_sm = g_hnsw_ctas_per_sm;
-        int grid = sm_count() * per_sm;
-        const int want = (Q + kHnswWarps - 1) / kHnswWarps;
-        if (grid > want) grid = want;
-        const size_t need = 256 + (size_t)grid * kHnswWarps * H * 4;
-        VDB_REQUIRE(ws_bytes >= need, VDB_ERR_WORKSPACE, "workspace %zu < %zu", ws_bytes, need);
-        VDB_CUDA(cudaMemsetAsync(flag, 0, 4, st));
-        ProfScope prof(kProfHnswSearch, st);
-        hnsw_search_warp_kernel<<<grid, kHnswThreads, smem, st>>>(g, q, Q, entry_row, max_level, ef, k, filter, CC, NM, H,
-                                                                 reinterpret_cast<uint32_t*>(static_cast<char*>(ws) + 256),
-                                                                 (int)smem_without, out_d, out_rows, out_stats, out_status, flag);
-        count_launch(1);
-        VDB_CUDA(cudaGetLastError());
-        return VDB_OK;
-    }
     // a big shared-memory hash caps the CTAs per SM, and the traversal needs occupancy to hide gather latency
     const bool use_global = hash_slots != 0 || smem_with > (size_t)g_hnsw_smem_hash_limit;
     size_t smem = use_global ? smem_without : smem_with;
