@@ -591,7 +591,7 @@ def path_staging(dev, peaks):
             runs.append(dict(st.last_stage))
         sweep = {}
         for thr in (4, 8, 16, 32):
-            for chunk in (16384, 65536):
+            for chunk in (2048, 8192, 32768):
                 st._stage_ring = None
                 st.stage_to_device(dev, chunk_records=chunk, threads=thr)                  # first call allocates the ring
                 st.stage_to_device(dev, chunk_records=chunk, threads=thr)
@@ -599,7 +599,7 @@ def path_staging(dev, peaks):
         st._stage_ring = None
         best = max(runs, key=lambda r_: r_["gb_per_s"])
         t0 = time.perf_counter()
-        ids1, vecs1 = st.stage_to_device(dev, threads=1, depth=2)
+        ids1, vecs1 = st.stage_to_device(dev, threads=1, depth=2, chunk_records=65536)
         single = dict(st.last_stage)
         chk = np.random.default_rng(0).integers(0, n, 64)
         ok = bool(np.array_equal(vecs[torch.from_numpy(chk).to(dev)].cpu().numpy(), np.asarray(st.embeddings["embedding"][chk]))

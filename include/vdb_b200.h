@@ -62,14 +62,15 @@ int vdb_stage_aos_h2d(const void* host_records /*[host,pinned]*/, int64_t n, int
                       int64_t* ids /*[dev] n*/, float* vecs /*[dev] n*D*/, void* stream);
 
 /* The same upload from PAGEABLE memory -- the memmap of the reference's `.embeddings.npy` file itself
- * (storage.py:135-144): `threads` host threads copy record slices into a caller-owned ring of `depth` pinned buffers
- * of `buffer_bytes` each while the copy engine drains the previous buffers with the two strided DMA copies above.
- * Returns after the last copy has left the ring (the device arrays are then complete on `stream`). */
+ * (storage.py:135-144).  The records are cut into chunks of buffer_bytes; host worker t (of `threads`, each with its own
+ * CUDA stream) takes chunks t, t + threads, ...: memcpy out of the page cache into one of its pinned buffers, one
+ * contiguous DMA into the matching device buffer, a kernel that splits the id / embedding columns (a strided DMA of
+ * 8-byte rows is 5x slower than the contiguous copy).  `depth` buffers in each ring, at least two per worker (threads is
+ * cut to depth / 2).  Returns after every copy and kernel has finished; `stream` is made to wait for them. */
 int vdb_stage_aos_pageable_h2d(const void* records /*[host,pageable] n records*/, int64_t n, int D,
                                int64_t* ids /*[dev] n or NULL*/, float* vecs /*[dev] n*D*/,
                                void* pinned_ring /*[host,pinned] depth*buffer_bytes*/,
-                               void* device_ring /*[dev] depth*buffer_bytes: chunks land here by ONE contiguous DMA each
-                                  and a kernel splits the id / embedding columns (strided DMA of 8-byte rows is 5x slower)*/,
+                               void* device_ring /*[dev] depth*buffer_bytes*/,
                                size_t buffer_bytes, int depth, int threads, void* stream);
 
 /* Per-row squared norms and the bf16 mirror used by the tensor-core scan.

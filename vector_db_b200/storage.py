@@ -230,12 +230,13 @@ class MMapNodeStorage(NodeStorage):
             self.metadata.flush()
 
     # -- HBM staging ----------------------------------------------------------------------------
-    def stage_to_device(self, device=None, chunk_records: int = 65536, threads: Optional[int] = None, depth: int = 3
+    def stage_to_device(self, device=None, chunk_records: int = 8192, threads: Optional[int] = None, depth: Optional[int] = None
                         ) -> Tuple["torch.Tensor", "torch.Tensor"]:
         """Upload every valid record to HBM as SoA tensors ``(ids i64 [n], vecs f32 [n,dim])`` in slot
-        order.  Records travel memmap -> ring of ``depth`` pinned buffers, filled by ``threads`` host threads
-        (vdb_stage_aos_pageable_h2d) -> strided DMA that splits the id and embedding columns; invalid slots are
-        dropped on the device.  ``self.last_stage`` records bytes / seconds of the last upload."""
+        order.  ``threads`` host workers each take every ``threads``-th chunk of ``chunk_records`` records: memcpy out
+        of the memmap into a pinned buffer, one contiguous DMA, a kernel that splits the id and embedding columns
+        (vdb_stage_aos_pageable_h2d); ``depth`` buffers in all (default two per worker); invalid slots are dropped on
+        the device.  ``self.last_stage`` records bytes / seconds of the last upload."""
         import os
         import time
 
@@ -252,9 +253,14 @@ class MMapNodeStorage(NodeStorage):
             return ids, vecs
         rec = self.embeddings.dtype.itemsize
         chunk = max(1, min(chunk_records, hw))
-        depth = max(2, min(int(depth), 16))
         if threads is None:
-            threads = max(1, min(16, (os.cpu_count() or 2) // 2))
+            try:
+                cpus = len(os.sched_getaffinity(0))
+            except Exception:                                   # noqa: BLE001
+                cpus = os.cpu_count() or 2
+            threads = max(1, min(16, cpus))
+        threads = max(1, min(int(threads), 64))
+        depth = 2 * threads if depth is None else max(2, min(int(depth), 128))
         ring = getattr(self, "_stage_ring", None)
         if ring is None or ring.numel() < depth * chunk * rec:
             ring = self._stage_ring = torch.empty(depth * chunk * rec, dtype=torch.uint8).pin_memory()
