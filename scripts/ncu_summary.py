@@ -1,7 +1,9 @@
 #!/usr/bin/env python
 """Summarise an `ncu --set full` report into profiles/: key counters (JSON) + top stall lines (text).
 
-    python scripts/ncu_summary.py gpurun_out/prof_exact_tc.ncu-rep exact_tc r01
+    python scripts/ncu_summary.py gpurun_out/prof_exact_tc.ncu-rep exact_tc r01 [kernel-name-regex]
+
+With several captured launches (or a regex) the launch with the LONGEST duration among the matches is summarised.
 """
 import csv
 import io
@@ -12,10 +14,17 @@ import subprocess
 import sys
 
 rep, name, rnd = sys.argv[1], sys.argv[2], sys.argv[3]
+kfilter = ["--kernel-name", "regex:" + sys.argv[4]] if len(sys.argv) > 4 else []
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"] + kfilter, capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(raw)))
-hdr, units, vals = rows[0], rows[1], rows[2]
+hdr, units = rows[0], rows[1]
+_di = hdr.index("gpu__time_duration.sum")
+_launches = [r for r in rows[2:] if len(r) == len(hdr)]
+_pick = max(range(len(_launches)), key=lambda i: float(_launches[i][_di].replace(",", "") or 0))
+vals = _launches[_pick]
+_idcol = hdr.index("ID")
+kfilter_src = kfilter
 want = re.compile(
     r"^(Kernel Name|gpu__time_duration\.sum|dram__bytes_read\.sum|dram__bytes_write\.sum|dram__throughput\.avg\.pct_of_peak_sustained_elapsed|"
     r"lts__t_bytes\.sum|lts__throughput\.avg\.pct_of_peak_sustained_elapsed|l1tex__data_bank_conflicts_pipe_lsu_mem_shared\.sum|"
@@ -48,11 +57,15 @@ allsum = json.load(open(path)) if os.path.exists(path) else {}
 allsum[name] = summary
 json.dump(allsum, open(path, "w"), indent=1, sort_keys=True)
 
-src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
+# the source page holds one block per matching launch (a "Kernel Name" row, a header row, the SASS rows): take the picked one
+src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"] + kfilter, capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(src)))
-hdr = rows[1]
+starts = [i for i, r in enumerate(rows) if r and r[0] == "Kernel Name"]
+blk = starts[_pick] if _pick < len(starts) else starts[0]
+end = starts[starts.index(blk) + 1] if starts.index(blk) + 1 < len(starts) else len(rows)
+hdr = rows[blk + 1]
 ix = {h: i for i, h in enumerate(hdr)}
-data = [r for r in rows[2:] if len(r) == len(hdr)]
+data = [r for r in rows[blk + 2:end] if len(r) == len(hdr)]
 stall_cols = [h for h in hdr if h.startswith("stall_") and "Not Issued" not in h]
 tot = sum(int(r[ix["# Samples"]] or 0) for r in data)
 agg = {h: sum(int(r[ix[h]] or 0) for r in data) for h in stall_cols}
