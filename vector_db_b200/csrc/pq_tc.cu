@@ -39,7 +39,9 @@
 // their own next-step operands instead of a split warp (3.6 ms: fence.proxy.async per thread and step); two split
 // warps with the highest warp ids (2.96 ms); THREE epilogue groups rotating over the two accumulator stages (3.5 ms
 // at 128 registers; needs a full-barrier per (step mod 6), a barrier per stage aliases use u with u + 2); ambiguous
-// rows parked in shared memory and resolved once per tile (2.96 ms).
+// rows parked in shared memory and resolved once per tile (2.96 ms); r02: the tail of a step software-pipelined under
+// the next step's first TMEM load (2.89 ms at 145 registers -- the tail's FMA-pipe work does not reach the idle slots
+// of the ALU pipe, the other epilogue warp of the scheduler already fills what it can).
 //
 // Roofline: HBM, algorithmic bytes per vector = 4 D + m (rows read once, codes written once).
 #include <cuda.h>
@@ -352,57 +354,7 @@ pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         uint8_t* sCodesG = sCodes + (size_t)eg * kEtRows * m;
         int xs = eg % nxa;                             // own steps s = eg, eg + 2, ...: row slot s mod nxa
         int phase = 0;
-        float A[16], B[16];
-        // The TAIL of a step (norm, margin, the FMA-pipe margin test, the code store) runs one step late, between the issue
-        // of the next step's first TMEM load and its wait: the tail is FMA-pipe / SFU work with a long dependent chain, the
-        // load's latency was exposed at the top of every step, and the fold that follows owns the ALU pipe -- a warp now
-        // offers the scheduler both kinds of work at once.  A / B are dead once the tail has run, before the next fold
-        // writes them; the row slot of step s is released one step later (the ring has the slots).
-        auto tail = [&](const float4 xa, const float4 xb, int j, int slot) {
-            const float xs8[8] = {xa.x, xa.y, xa.z, xa.w, xb.x, xb.y, xb.z, xb.w};
-            float xx = 0.f;
-#pragma unroll
-            for (int t = 0; t < 8; ++t) xx = fmaf(xs8[t], xs8[t], xx);
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&xa_empty[slot]);   // this warp no longer reads the step's row slice
-            const float xn = sqrtf(xx) * 1.0000005f, cm_j = sCmax[j];
-            // rigorous candidate margin (see file header): operand split error + fp32 accumulation / reference rounding
-            const float thr = min16(B) + 5.2e-5f * xn * cm_j + 1e-5f * (xn + cm_j) * (xn + cm_j);
-            // Margin test on the FMA pipe (the fold owns the half-rate ALU pipe): u = sat((V - thr) * S) is
-            // exactly 1 for V > thr and 0 for V <= thr once S >= 2 / ulp(thr); acc = sum u * (1 + 32 i) then holds
-            // the count of minima outside the margin (low 5 bits) and the sum of their indices.
-            const uint32_t tb = __float_as_uint(thr), te = (tb >> 23) & 0xFFu;
-            const float S = __uint_as_float((279u - te) << 23), nts = -thr * S;
-            const float accA = gt_accumulate16(A, S, nts), accB = gt_accumulate16(B, S, nts);
-            const int ia = __float2int_rn(accA), ib = __float2int_rn(accB);
-            int code = 0;
-            if (te >= 27u && (ia & 31) == 15 && (ib & 31) == 15) {
-                code = (120 - (ia >> 5)) * 16 + 120 - (ib >> 5);      // the one index that is missing from each sum
-            } else if (const uint32_t mA = le_mask16(A, thr), mB = le_mask16(B, thr); mA && mB) {
-                // several candidates (a superset: the cross product of the two families): the reference's own
-                // arithmetic decides (pq.py:79-80), first minimum wins
-                float best = INFINITY;
-                const float* cbj = cb + (size_t)j * K * 8;
-                for (uint32_t ra = mA; ra; ra &= ra - 1) {
-                    const int c0 = (__ffs(ra) - 1) * 16;
-                    for (uint32_t rb = mB; rb; rb &= rb - 1) {
-                        const int c = c0 + __ffs(rb) - 1;
-                        if (c < K) {
-                            const float4* cp = reinterpret_cast<const float4*>(cbj + (size_t)c * 8);
-                            const float4 ca = __ldg(cp), cc = __ldg(cp + 1);
-                            float d[8] = {ca.x - xs8[0], ca.y - xs8[1], ca.z - xs8[2], ca.w - xs8[3],
-                                          cc.x - xs8[4], cc.y - xs8[5], cc.z - xs8[6], cc.w - xs8[7]};
-                            const float dist = sqrtf(np_sumsq<8>(d));
-                            if (dist < best) { best = dist; code = c; }
-                        }
-                    }
-                }
-            }
-            sCodesG[rt * m + j] = (uint8_t)code;
-        };
         for (int64_t pair = blockIdx.x; pair < pairs; pair += gridDim.x) {
-            float4 pxa = make_float4(0.f, 0.f, 0.f, 0.f), pxb = pxa;     // row slice of the step whose tail is pending
-            int pslot = 0;
             for (int j = 0; j < m; ++j) {
                 const uint32_t sx = smem_u32(sXa + (size_t)xs * kEtXaBytes) + (uint32_t)(rt * 32);
                 mbar_wait(&tmem_full[eg * 2], phase);  // columns 0..127 done => the step's operands were in shared memory too
@@ -410,12 +362,11 @@ pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                 // ONE pass over the scores.  Two 32-column register buffers: while one chunk is folded the next one's
                 // TMEM load is in flight (tcgen05.wait::ld waits for ALL outstanding loads, so exactly one is
                 // outstanding at every wait).
-                float va[32], vb[32];
-                tmem_ld_x32(taddr, va);
-                const float4 xa = lds128(sx), xb = lds128(sx + 16);     // issued here, consumed by this step's tail
-                if (j > 0) tail(pxa, pxb, j - 1, pslot);                // the previous step's tail, under the load
+                float va[32], vb[32], A[16], B[16];
 #pragma unroll
                 for (int i = 0; i < 16; ++i) B[i] = INFINITY;
+                tmem_ld_x32(taddr, va);
+                const float4 xa = lds128(sx), xb = lds128(sx + 16);     // issued here, consumed after the fold
                 tmem_ld_wait(va); tmem_ld_x32(taddr + 32u, vb); fold_chunk<0>(va, A, B);
                 tmem_ld_wait(vb); tmem_ld_x32(taddr + 64u, va); fold_chunk<1>(vb, A, B);
                 tmem_ld_wait(va); tmem_ld_x32(taddr + 96u, vb); fold_chunk<2>(va, A, B);
@@ -433,11 +384,49 @@ pq_encode_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                 tc_fence_before();
                 mbar_arrive(&tmem_empty[eg * 2 + 1]);          // columns 128..255 are in registers
                 fold_chunk<7>(vb, A, B);
-                pxa = xa; pxb = xb; pslot = xs;
+                const float xs8[8] = {xa.x, xa.y, xa.z, xa.w, xb.x, xb.y, xb.z, xb.w};
+                float xx = 0.f;
+#pragma unroll
+                for (int t = 0; t < 8; ++t) xx = fmaf(xs8[t], xs8[t], xx);
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&xa_empty[xs]);     // this warp no longer reads the step's row slice
+                const float xn = sqrtf(xx) * 1.0000005f, cm_j = sCmax[j];
+                // rigorous candidate margin (see file header): operand split error + fp32 accumulation / reference rounding
+                const float thr = min16(B) + 5.2e-5f * xn * cm_j + 1e-5f * (xn + cm_j) * (xn + cm_j);
+                // Margin test on the FMA pipe (the fold above owns the half-rate ALU pipe): u = sat((V - thr) * S) is
+                // exactly 1 for V > thr and 0 for V <= thr once S >= 2 / ulp(thr); acc = sum u * (1 + 32 i) then holds
+                // the count of minima outside the margin (low 5 bits) and the sum of their indices.
+                const uint32_t tb = __float_as_uint(thr), te = (tb >> 23) & 0xFFu;
+                const float S = __uint_as_float((279u - te) << 23), nts = -thr * S;
+                const float accA = gt_accumulate16(A, S, nts), accB = gt_accumulate16(B, S, nts);
+                const int ia = __float2int_rn(accA), ib = __float2int_rn(accB);
+                int code = 0;
+                if (te >= 27u && (ia & 31) == 15 && (ib & 31) == 15) {
+                    code = (120 - (ia >> 5)) * 16 + 120 - (ib >> 5);      // the one index that is missing from each sum
+                } else if (const uint32_t mA = le_mask16(A, thr), mB = le_mask16(B, thr); mA && mB) {
+                    // several candidates (a superset: the cross product of the two families): the reference's own
+                    // arithmetic decides (pq.py:79-80), first minimum wins
+                    float best = INFINITY;
+                    const float* cbj = cb + (size_t)j * K * 8;
+                    for (uint32_t ra = mA; ra; ra &= ra - 1) {
+                        const int c0 = (__ffs(ra) - 1) * 16;
+                        for (uint32_t rb = mB; rb; rb &= rb - 1) {
+                            const int c = c0 + __ffs(rb) - 1;
+                            if (c < K) {
+                                const float4* cp = reinterpret_cast<const float4*>(cbj + (size_t)c * 8);
+                                const float4 ca = __ldg(cp), cc = __ldg(cp + 1);
+                                float d[8] = {ca.x - xs8[0], ca.y - xs8[1], ca.z - xs8[2], ca.w - xs8[3],
+                                              cc.x - xs8[4], cc.y - xs8[5], cc.z - xs8[6], cc.w - xs8[7]};
+                                const float dist = sqrtf(np_sumsq<8>(d));
+                                if (dist < best) { best = dist; code = c; }
+                            }
+                        }
+                    }
+                }
+                sCodesG[rt * m + j] = (uint8_t)code;
                 xs += 2;
                 if (xs >= nxa) xs -= nxa;
             }
-            tail(pxa, pxb, m - 1, pslot);                       // the pair's last step
             // the tile's codes are one contiguous run of 128*m bytes in global memory
             named_bar_sync(1 + eg, 128);
             const int64_t row0 = (pair * 2 + eg) * kEtRows;
