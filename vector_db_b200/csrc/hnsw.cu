@@ -227,6 +227,16 @@ __device__ int beam_search(const Graph& g, BeamMem& m, int entry, int level, int
         int deg;
         const int32_t* nb = nbr_list(g, node, level, &deg);
         if (tid == 0) m.scal[0] = 0;
+        // the node expanded NEXT is most often the current runner-up: pull its adjacency row towards the SM while this
+        // expansion's distances are evaluated (the row's load heads the next expansion's critical path)
+        if (tid == 32 && ncand > 1) {
+            int d2;
+            const int32_t* nx = nbr_list(g, (int)key_index(m.cand[cc][1]), level, &d2);
+            if (d2 > 0) {
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(nx));
+                if (d2 > 32) asm volatile("prefetch.global.L2 [%0];" ::"l"(nx + 32));
+            }
+        }
         group_sync<NT>();
         for (int p = tid; p < deg; p += NT) {
             int r = __ldcg(nb + p);
