@@ -16,7 +16,7 @@ vec = idx._vectors
 entry_row, top = idx._read_state()
 lib = _lib.load()
 ref = None
-for spec in (sys.argv[1:] or ["c8", "c9", "c10", "c12", "c16"]):
+for spec in [a if a[0] == "c" else "c" + a for a in (sys.argv[1:] or ["c8", "c9", "c10", "c12", "c16"])]:
     cap = int(spec[1:])                                               # cN: N resident CTAs per SM
     lib.vdb_debug_set_hnsw_ctas_per_sm(cap)
     def step():

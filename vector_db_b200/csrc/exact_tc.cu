@@ -479,98 +479,133 @@ struct TcPostQuery {          // per query, written by tc_select_kernel
     int pad;
 };
 
-__global__ void __launch_bounds__(128)
+// ONE WARP per query (the CTA-per-query rank search of r01 was 12.5 k warp instructions per query, ALU-bound at 0.07 ms).
+// The kept bins need no order -- the rerank re-scores all of them -- so only c_k, the k-th smallest bin minimum, has to be
+// FOUND: k rounds of "smallest remaining score" (lane-strided scan of the query's L x NBL keys in shared memory, 32-bit
+// butterfly minimum, the lowest lane holding it marks one of its entries).  Then every key is tested against the cutoff
+// c_k + 2 eps + 4 slack in parallel and the survivors are compacted into the flat work list.
+//   tau = min( scores of the keys NOT kept, worst entry of every FULL list ): a bin that is not a candidate either is one
+//   of the keys not kept or was dropped from a full list, whose worst entry (kept or not) bounds it.
+// More than NB survivors (never seen on real data: the trim keeps ~20 bins): the extraction simply runs on to NB rounds.
+constexpr int kSelWarps = 4;
+__global__ void __launch_bounds__(32 * kSelWarps)
 tc_select_kernel(const u64* __restrict__ partial, int L, int NBL, int NB, int C, const float* __restrict__ qv, int D, int k,
-                 int metric, const float* __restrict__ stats, int no_trim, TcPostQuery* __restrict__ pq,
+                 int metric, const float* __restrict__ stats, int no_trim, int Q, TcPostQuery* __restrict__ pq,
                  uint2* __restrict__ items, int32_t* __restrict__ item_count) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    u64* buf = reinterpret_cast<u64*>(smem_raw);           // [C] merged list slots, then [kNBFinal] the best bins
-    u64* top = buf + C;
-    __shared__ unsigned tau_bits;          // ordered-float minimum over the full lists' worst entries
-    __shared__ float qsq_s, rsq_s;
-    __shared__ int keep_s, base_s;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int q = blockIdx.x, total = L * NBL;
-    if (tid == 0) tau_bits = f32_to_ordered(INFINITY);
-    for (int i = tid; i < NB; i += blockDim.x) top[i] = VDB_KEY_MAX;
-    __syncthreads();
-    if (warp == 3) {                                       // |q|^2 in the order rerank_f32_kernel uses, and |bf16(q) - q|^2
-        float a = 0.f, b = 0.f;
-        for (int t = lane; t < D; t += 32) {
-            const float v = qv[(size_t)q * D + t], r = bf16_residual(v);
-            a = fmaf(v, v, a);
-            b = fmaf(r, r, b);
-        }
-        a = warp_sum(a);
-        b = warp_sum(b);
-        if (lane == 0) { qsq_s = a; rsq_s = b; }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int q = (int)blockIdx.x * kSelWarps + warp;
+    if (q >= Q) return;
+    u64* buf = reinterpret_cast<u64*>(smem_raw) + (size_t)warp * C;       // [C] keys; entry i belongs to lane i % 32
+    const int total = L * NBL;                                             // <= C <= 1024: at most 32 entries per lane
+    float a = 0.f, b = 0.f;                                // |q|^2 in the order rerank_f32_kernel uses, and |bf16(q) - q|^2
+    for (int t = lane; t < D; t += 32) {
+        const float v = qv[(size_t)q * D + t], r = bf16_residual(v);
+        a = fmaf(v, v, a);
+        b = fmaf(r, r, b);
     }
-    for (int i = tid; i < C; i += blockDim.x) {
+    a = warp_sum(a);
+    b = warp_sum(b);
+    unsigned full_worst = f32_to_ordered(INFINITY);        // ordered-float minimum over the full lists' worst entries
+    for (int i = lane; i < C; i += 32) {
         u64 key = VDB_KEY_MAX;
         if (i < total) {
             key = partial[(size_t)q * total + i];
             if (key_index(key) == 0xFFFFFFFFu) key = VDB_KEY_MAX;                  // empty slot
-            else if ((i % NBL) == NBL - 1) atomicMin(&tau_bits, (unsigned)(key >> 32));   // worst entry of a full list
+            else if ((i % NBL) == NBL - 1) full_worst = min(full_worst, (unsigned)(key >> 32));
         }
         buf[i] = key;
     }
-    __syncthreads();
-    // The L lists arrive sorted by score, so a key's rank among all keys is its position in its own list plus, for
-    // every other list, the number of entries ahead of it -- a 5-probe binary search per list instead of a bitonic
-    // sort of all C keys.  Ties on the score are ordered by (list, position), which keeps the ranks unique.
-    for (int i = tid; i < total; i += blockDim.x) {
-        const u64 key = buf[i];
-        if (key == VDB_KEY_MAX) continue;
-        const unsigned sc = (unsigned)(key >> 32);
-        const int la = i / NBL;
-        int rank = i - la * NBL;
-        for (int l = 0; l < L; ++l) {
-            if (l == la) continue;
-            const u64* lst = buf + l * NBL;
-            const unsigned t = sc + (l < la ? 1u : 0u);            // entries with score < t are ahead (sc < 0xFFFFFFFF: a real key)
-            int pos = 0;
-            for (int h = NBL >> 1; h > 0; h >>= 1)
-                if ((unsigned)(lst[pos + h - 1] >> 32) < t) pos += h;
-            if ((unsigned)(lst[pos] >> 32) < t) ++pos;
-            rank += pos;
-        }
-        if (rank < NB) top[rank] = key;
-    }
-    __syncthreads();
-    // Trim: the k-th smallest bin minimum c_k bounds the k-th smallest coarse row score from above, so k rows have
-    // exact scores <= c_k + eps and no row of a bin whose minimum exceeds c_k + 2 eps can enter the top-k.  Those bins
-    // are not reranked; the first of them becomes the bound the certificate tests (a little extra slack keeps the
-    // certificate's own rounding allowance from rejecting the query).  keep = first j that is empty or (j >= k and
-    // above the cutoff): every thread tests one slot, the minimum wins.
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) full_worst = min(full_worst, __shfl_xor_sync(0xffffffffu, full_worst, o));
+    __syncwarp();
     float eps, slack;                                                // the certificate's allowance, also the trim's
-    tc_bound(metric, sqrtf(qsq_s) * 1.0001f, sqrtf(rsq_s) * 1.0001f, stats[0], stats[1], &eps, &slack);
-    if (tid == 0) keep_s = NB;
-    __syncthreads();
-    {
-        float cutoff = INFINITY;
-        if (!no_trim && k - 1 < NB && top[k - 1] != VDB_KEY_MAX) cutoff = key_score(top[k - 1]) + 2.f * eps + 4.f * slack;
-        if (tid < NB) {
-            const u64 key = top[tid];
-            if (key == VDB_KEY_MAX || (tid >= k && key_score(key) > cutoff)) atomicMin(&keep_s, tid);
+    tc_bound(metric, sqrtf(a) * 1.0001f, sqrtf(b) * 1.0001f, stats[0], stats[1], &eps, &slack);
+    // ---- rounds: the smallest remaining ordered score; `taken` = this lane's entries already extracted (bit t: entry lane + 32 t)
+    uint32_t taken = 0u;
+    unsigned last = 0xFFFFFFFFu;                                     // score of the last extracted key (ordered bits)
+    int n_ext = 0;
+    auto extract = [&]() -> bool {                                   // one round; false when nothing is left
+        unsigned best = 0xFFFFFFFFu;
+        int bt = -1;
+        for (int i = lane, t = 0; i < total; i += 32, ++t) {
+            const unsigned sc = (unsigned)(buf[i] >> 32);
+            if (!((taken >> t) & 1u) && sc < best) { best = sc; bt = t; }
         }
+        unsigned wbest = best;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) wbest = min(wbest, __shfl_xor_sync(0xffffffffu, wbest, o));
+        if (wbest == 0xFFFFFFFFu) return false;                      // only empty slots (score bits of VDB_KEY_MAX) are left
+        const unsigned owners = __ballot_sync(0xffffffffu, best == wbest && bt >= 0);
+        if (lane == __ffs(owners) - 1) taken |= 1u << bt;
+        last = wbest;
+        ++n_ext;
+        return true;
+    };
+    const int rounds = k < NB ? k : NB;
+    while (n_ext < rounds && extract()) {}
+    float cutoff = INFINITY;
+    if (!no_trim && n_ext == k) cutoff = ordered_to_f32(last) + 2.f * eps + 4.f * slack;
+    // ---- survivors: every key with score <= cutoff (the extracted k are among them)
+    auto count_kept = [&](unsigned cut_bits, bool use_taken) {
+        int c = 0;
+        for (int i = lane, t = 0; i < total; i += 32, ++t) {
+            const unsigned sc = (unsigned)(buf[i] >> 32);
+            const bool kept = use_taken ? ((taken >> t) & 1u) != 0u : (sc != 0xFFFFFFFFu && sc <= cut_bits);
+            c += kept ? 1 : 0;
+        }
+        return c;
+    };
+    unsigned cut_bits = cutoff == INFINITY ? 0xFFFFFFFEu : f32_to_ordered(cutoff);
+    bool by_mask = false;                                            // survivors named by `taken` instead of the cutoff
+    int mine = count_kept(cut_bits, false), keep = mine;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) keep += __shfl_xor_sync(0xffffffffu, keep, o);
+    if (keep > NB) {                                                 // rare: take exactly the NB smallest
+        while (n_ext < NB && extract()) {}
+        by_mask = true;
+        mine = count_kept(0u, true);
+        keep = n_ext;
     }
-    __syncthreads();
-    if (tid == 0) {
-        const int keep = keep_s;
-        float tau = ordered_to_f32(tau_bits);
-        if (top[NB - 1] != VDB_KEY_MAX) tau = fminf(tau, key_score(top[NB - 1]));
-        if (keep < NB && top[keep] != VDB_KEY_MAX) tau = fminf(tau, key_score(top[keep]));   // the first trimmed bin
-        base_s = keep > 0 ? atomicAdd(item_count, keep) : 0;
+    // tau: the smallest score that is not kept, and the full lists' worst entries
+    unsigned tmin = full_worst;
+    for (int i = lane, t = 0; i < total; i += 32, ++t) {
+        const unsigned sc = (unsigned)(buf[i] >> 32);
+        const bool kept = by_mask ? ((taken >> t) & 1u) != 0u : (sc != 0xFFFFFFFFu && sc <= cut_bits);
+        if (!kept) tmin = min(tmin, sc);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) tmin = min(tmin, __shfl_xor_sync(0xffffffffu, tmin, o));
+    const float tau = tmin == 0xFFFFFFFFu ? INFINITY : ordered_to_f32(tmin);
+    // ---- compaction into the flat work list: exclusive prefix of the per-lane counts
+    int pre = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, pre, o);
+        if (lane >= o) pre += v;
+    }
+    pre -= mine;
+    int base = 0;
+    if (lane == 0) {
+        base = keep > 0 ? atomicAdd(item_count, keep) : 0;
         TcPostQuery o;
         o.tau_minus = tau - eps - slack;
-        o.qsq = qsq_s;
+        o.qsq = a;
         o.keep = keep;
         o.pad = 0;
         pq[q] = o;
     }
-    __syncthreads();
-    for (int j = tid; j < keep_s; j += blockDim.x)
-        items[base_s + j] = make_uint2((uint32_t)q * (uint32_t)kNBFinal + (uint32_t)j, key_index(top[j]));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    int j = pre;
+    for (int i = lane, t = 0; i < total; i += 32, ++t) {
+        const u64 key = buf[i];
+        const unsigned sc = (unsigned)(key >> 32);
+        const bool kept = by_mask ? ((taken >> t) & 1u) != 0u : (sc != 0xFFFFFFFFu && sc <= cut_bits);
+        if (kept) {
+            items[base + j] = make_uint2((uint32_t)q * (uint32_t)kNBFinal + (uint32_t)j, key_index(key));
+            ++j;
+        }
+    }
 }
 
 constexpr int kRrMaxWarps = 8;             // warps per CTA, each with its own two-slot ring and its own work items
@@ -986,10 +1021,10 @@ int vdb_exact_topk_tc(const float* q, int Q, const float* db, const void* mirror
     int32_t* item_count = reinterpret_cast<int32_t*>(base + w.counters);
     {
         ProfScope prof(kProfRerank, st);
-        const size_t sel_smem = (size_t)(C + kNBFinal) * 8;
+        const size_t sel_smem = (size_t)kSelWarps * C * 8;
         VDB_CUDA(cudaFuncSetAttribute(tc_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sel_smem));
-        tc_select_kernel<<<Q, 128, sel_smem, st>>>(partial, L, nbl, nbf, C, q, D, k, metric, db_stats, (g_tc_flags & 16) ? 1 : 0,
-                                                  pq, items, item_count);
+        tc_select_kernel<<<(Q + kSelWarps - 1) / kSelWarps, 32 * kSelWarps, sel_smem, st>>>(
+            partial, L, nbl, nbf, C, q, D, k, metric, db_stats, (g_tc_flags & 16) ? 1 : 0, Q, pq, items, item_count);
         // one CTA per SM: as many warps (each with a two-slot ring of bin + query) as shared memory holds, at most 8
         int rr_warps = (int)((size_t)(max_smem_optin() - 2048) / (kRrSlots * rr_slot_bytes(D)));
         if (rr_warps > kRrMaxWarps) rr_warps = kRrMaxWarps;
