@@ -149,6 +149,32 @@ int vdb_exact_topk_tc(const float* q /*[dev] Q*D fp32*/, int Q,
                          those queries were re-scanned by the exact fp32 kernel inside this call (device-side list, no host
                          round trip), so out_d / out_i are exact for every query on return*/,
                       void* ws, size_t ws_bytes, void* stream);
+/* ---- f3: list-major IVF on the same tensor-core pipeline (src/vector_db/indexing/ivf.py:170-199 for a BATCH of queries) --------
+ * The query-major list scan (vdb_ivf_scan) reads every probed list once per query; at batch sizes of thousands the lists are
+ * shared, and the work is a set of small dense contractions: (queries probing list l) x (rows of list l).
+ *   lm_vecs / lm_ids: the rows in LIST-MAJOR order, every list padded to whole 256-row tiles (padding: id -1);
+ *   lm_mirror / lm_stats: vdb_tc_prepare_rows(L2) of the RESIDUALS row - centroid[list] in the same order (padding rows:
+ *     zero residual and a huge |x|^2 entry in the norm block) -- the query operand holds q - centroid[list] per pair, so the
+ *     accumulator is the squared distance and the bf16 error scales with the residual norms, not with |q||x|;
+ *   row_query[Qa]: the query of every row of the query operand -- one row per (query, probed list) PAIR, the pairs of a list
+ *     contiguous and padded to whole 128-row tiles (-1 = padding); pair_rows[Q][n_probe]: the operand row of a query's p-th
+ *     probe (-1 = that list is empty); unit_table[n_units][4] = (pair tile, first row tile, end row tile, 0): one unit per
+ *     pair tile of a non-empty list.
+ * The coarse pass keeps bin lists per pair; selection, trim, exact fp32 rerank and certificate then run per QUERY over the
+ * lists of all its pairs, exactly as in vdb_exact_topk_tc.  out_i = lm_ids[position] (or the list-major position when
+ * lm_ids is NULL), ordered by (distance, list-major position).  Queries the certificate rejects are LISTED in
+ * out_uncertified (count, then indices) and must be re-run by the caller through vdb_ivf_scan (a brute-force rescan would
+ * look at lists the query did not probe).  n_probe <= 32, k <= 16, D % 8 == 0, D <= 512. */
+size_t vdb_ivf_topk_tc_workspace(int Q, int64_t Qa, int64_t N, int D, int k, int n_units);
+int vdb_ivf_topk_tc(const float* q /*[dev] Q*D*/, int Q, const float* lm_vecs /*[dev] N*D*/, const void* lm_mirror,
+                    const float* lm_stats /*[dev] 2*/, const int64_t* lm_ids /*[dev] N or NULL*/, int64_t N /* padded rows */,
+                    int D, int k, int n_probe, const int32_t* pair_rows /*[dev] Q*n_probe*/,
+                    const int32_t* row_query /*[dev] Qa*/, const int32_t* row_list /*[dev] Qa: the pair's list*/,
+                    const float* centroids /*[dev] K*D*/, int64_t Qa, const int32_t* unit_table /*[dev] n_units*4*/,
+                    int n_units, const float* list_stats /*[dev] K*2 per-list (max |bf16 r|, max |bf16 r - r|) or NULL*/,
+                    float* out_d /*[dev] Q*k*/, int64_t* out_i /*[dev] Q*k*/,
+                    int32_t* out_uncertified /*[dev] Q+1*/, void* ws, size_t ws_bytes, void* stream);
+
 /* bench/debug only: bit 0 = skip the whole epilogue of the coarse pass, bit 1 = skip only its threshold
  * test and bin-list inserts (results are then invalid) */
 void vdb_debug_set_tc_flags(int flags);

@@ -228,3 +228,58 @@ def test_ivf_filter_ids_restricts_results(golden_dir):
     for qi in range(g["Q"].shape[0]):
         res, _, _ = IO.search(g["centroids"], lists, vec, g["Q"][qi], 3, 10)
         assert [r[1] for r in res] == [int(i) for i in I[qi] if i >= 0]
+
+
+def test_list_major_tensor_core_batch_search_matches_reference_run(golden_dir):
+    """The list-major tensor-core batch path (vdb_ivf_topk_tc, forced with batch_engine = "tc") on the reference-run
+    fixture: ids and distances of the reference's own IvfIndex.search at n_probe 1 / 3 / k, duplicate embeddings in list
+    order, and after delete()s -- lists far smaller than a 256-row tile, so padding rows and pair-tile padding dominate."""
+    g, idx = _golden_index(golden_dir)
+    idx.batch_engine = "tc"
+    k = int(g["k"])
+    for n_probe in (1, 3, k):
+        D, I = idx.search_batch(g["Q"], n_probe, 10)
+        np.testing.assert_array_equal(I, g[f"I{n_probe}"])
+        np.testing.assert_allclose(D, g[f"D{n_probe}"], rtol=1e-6, atol=1e-7)
+    D, I = idx.search_batch(g["Q"][:1], 3, 5)
+    assert I[0, :2].tolist() == [int(g["ids"][7]), int(g["ids"][40])] and D[0, 0] < 1e-6
+    for i in g["dead"]:
+        idx.delete(int(i))
+    D, I = idx.search_batch(g["Q"], 3, 10)
+    np.testing.assert_array_equal(I, g["Id"])
+    np.testing.assert_allclose(D, g["Dd"], rtol=1e-6, atol=1e-7)
+
+
+@pytest.mark.parametrize("n,dim,K,nq,n_probe,top_k,max_bad", [
+    (120_000, 64, 256, 700, 4, 10, 0.05), (120_000, 64, 256, 700, 16, 5, 0.05), (60_000, 128, 40, 300, 32, 10, None),
+    (50_000, 384, 512, 2100, 1, 10, None), (200_000, 128, 256, 1500, 8, 10, 0.01)])
+def test_list_major_tensor_core_batch_search_equals_query_major_scan(n, dim, K, nq, n_probe, top_k, max_bad):
+    """Same index, same queries: the tensor-core batch path must return what the query-major fp32 list scan returns --
+    ids equal, distances bit-equal (both re-score with the reference's arithmetic), candidates-enumerated counts equal.
+    ``max_bad``: largest share of queries the certificate may send back to the query-major scan (None: clustered rows
+    under 4 Lloyd rounds leave lists that merge several clusters, whose residuals are too wide for a bf16 coarse pass to
+    separate the k-th from the next neighbours -- still exact through the fallback, so only the results are checked);
+    the last case is unclustered Gaussian rows, where nothing should come back."""
+    from vector_db_b200.indexing import IvfIndex
+    rng = np.random.default_rng(n + K + n_probe)
+    if max_bad is not None and max_bad < 0.05:
+        X = rng.standard_normal((n, dim), dtype=np.float32)
+        Q = rng.standard_normal((nq, dim), dtype=np.float32)
+    else:
+        centres = rng.standard_normal((K, dim)).astype(np.float32) * 3
+        X = (centres[rng.integers(0, K, n)] + rng.standard_normal((n, dim))).astype(np.float32)
+        Q = (centres[rng.integers(0, K, nq)] + rng.standard_normal((nq, dim))).astype(np.float32)
+    X[5000] = X[17]                                                    # duplicate rows in one list: list order breaks the tie
+    Q[0] = X[17]
+    idx = IvfIndex(k=K)
+    idx.build_from_arrays(range(n), X, iters=4, init_rows=rng.choice(n, K, replace=False))
+    idx.batch_engine = "scan"
+    Ds, Is = idx.search_batch(Q, n_probe, top_k)
+    scanned = idx.last_scanned.copy()
+    idx.batch_engine = "tc"
+    Dt, It = idx.search_batch(Q, n_probe, top_k)
+    np.testing.assert_array_equal(It, Is)
+    np.testing.assert_array_equal(Dt, Ds)
+    np.testing.assert_array_equal(idx.last_scanned, scanned)
+    assert max_bad is None or idx.last_uncertified <= int(nq * max_bad)
+    assert Is[0, 0] == 17 and Ds[0, 0] == 0.0

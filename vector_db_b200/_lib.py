@@ -38,6 +38,8 @@ SIGNATURES = {
     "vdb_tc_prepare_rows": (_i, [_p, _i64, _i, _i, _p, _p, _p, _p]),
     "vdb_exact_topk_tc_workspace": (_sz, [_i, _i64, _i, _i, _i]),
     "vdb_exact_topk_tc": (_i, [_p, _i, _p, _p, _p, _p, _i64, _i, _i, _i, _p, _p, _p, _p, _sz, _p]),
+    "vdb_ivf_topk_tc_workspace": (_sz, [_i, _i64, _i64, _i, _i, _i]),
+    "vdb_ivf_topk_tc": (_i, [_p, _i, _p, _p, _p, _p, _i64, _i, _i, _i, _p, _p, _p, _p, _i64, _p, _i, _p, _p, _p, _p, _p, _sz, _p]),
     "vdb_debug_set_tc_flags": (None, [_i]),
     "vdb_pq_encode": (_i, [_p, _i64, _i, _i, _i, _p, _p, _p]),
     "vdb_pq_encode_tc_supported": (_i, [_i64, _i, _i, _i]),

@@ -145,13 +145,31 @@ __device__ __forceinline__ float tau_of_word(uint32_t w, int ui) {
     return ((w & 3u) == (uint32_t)(ui & 3)) ? ordered_to_f32(w & ~3u) : INFINITY;
 }
 
+// Work unit u -> (query tile mt, slice s, row tiles [t0, t1)).  Brute force: u = s * m_tiles + mt, slices of tiles_per_slice
+// row tiles.  LIST-MAJOR IVF (utab != nullptr): entry u of the table = (query tile, first row tile, end row tile) of one
+// (inverted list, 128-pair tile); one unit per pair tile, so s = 0 and S = 1.
+struct TcUnit { int mt, s, t0, t1; };
+__device__ __forceinline__ TcUnit tc_unit(int u, int m_tiles, int tiles_per_slice, int tiles_total, const int4* __restrict__ utab) {
+    TcUnit r;
+    if (utab) {
+        const int4 e = __ldg(utab + u);
+        r.mt = e.x; r.s = 0; r.t0 = e.y; r.t1 = e.z;
+    } else {
+        r.mt = u % m_tiles; r.s = u / m_tiles;
+        r.t0 = r.s * tiles_per_slice;
+        r.t1 = min(tiles_total, r.t0 + tiles_per_slice);
+    }
+    return r;
+}
+
 // flags: bit 0 = debug, skip the epilogue arithmetic (measures the TMA + MMA pipeline alone)
 template <int NBL>
 __global__ void __launch_bounds__(kTcThreads, 1)
 exact_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                 const __grid_constant__ CUtensorMap map_a2, const __grid_constant__ CUtensorMap map_b2,
                 int Q, int64_t N, int D, int has_norm, int num_kb, int stages, int m_tiles, int S,
-                int tiles_per_slice, int tiles_total, int flags, u64* __restrict__ partial, uint32_t* gtau) {
+                int tiles_per_slice, int tiles_total, int flags, u64* __restrict__ partial, uint32_t* gtau,
+                const int4* __restrict__ utab) {
     extern __shared__ __align__(1024) unsigned char smem[];   // 128B-swizzled operand tiles need 1024 B alignment
     if ((smem_u32(smem) & 1023u) != 0) __trap();
     const TcSmemLayout L = tc_layout(num_kb, stages, has_norm);
@@ -201,9 +219,8 @@ exact_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
         if (lane == 0) {
             int st = 0, ph = 0, ui = 0, ns = 0, nph = 0;
             for (int u = blockIdx.x; u < units; u += gridDim.x, ++ui) {
-                const int mt = u % m_tiles, s = u / m_tiles;
-                const int t0 = s * tiles_per_slice;
-                const int t1 = min(tiles_total, t0 + tiles_per_slice);
+                const TcUnit un = tc_unit(u, m_tiles, tiles_per_slice, tiles_total, utab);
+                const int mt = un.mt, t0 = un.t0, t1 = un.t1;
                 mbar_wait(a_empty, (ui & 1) ^ 1);                 // previous unit's MMAs are done with A
                 mbar_expect_tx(a_full, (uint32_t)(num_kb * kABytes + (has_norm ? kA2Bytes : 0)));
                 for (int kb = 0; kb < num_kb; ++kb)
@@ -232,9 +249,8 @@ exact_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
             const uint32_t idesc = make_idesc_bf16(kTileM, kTileN);
             int st = 0, ph = 0, as = 0, aph = 0, ui = 0, ns = 0, nph = 0;
             for (int u = blockIdx.x; u < units; u += gridDim.x, ++ui) {
-                const int s = u / m_tiles;
-                const int t0 = s * tiles_per_slice;
-                const int t1 = min(tiles_total, t0 + tiles_per_slice);
+                const TcUnit un = tc_unit(u, m_tiles, tiles_per_slice, tiles_total, utab);
+                const int t0 = un.t0, t1 = un.t1;
                 mbar_wait(a_full, ui & 1);
                 tc_fence_after();
                 for (int t = t0; t < t1; ++t) {
@@ -281,9 +297,8 @@ exact_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
         const volatile uint32_t* partner_tau = sTau + (eg ^ 1) * kTileM + row;
         int as = 0, aph = 0, ui = 0;
         for (int u = blockIdx.x; u < units; u += gridDim.x, ++ui) {
-            const int mt = u % m_tiles, s = u / m_tiles;
-            const int t0 = s * tiles_per_slice;
-            const int t1 = min(tiles_total, t0 + tiles_per_slice);
+            const TcUnit un = tc_unit(u, m_tiles, tiles_per_slice, tiles_total, utab);
+            const int mt = un.mt, s = un.s, t0 = un.t0, t1 = un.t1;
             list.reset();
             float pend_s = INFINITY;               // parked hit of this lane, not yet in the list
             uint32_t pend_b = 0xFFFFFFFFu;
@@ -366,27 +381,65 @@ exact_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
 // Query operand: bf16(q) padded to Dp columns; for L2 the three columns after D hold 1.0 so that
 // the MMA adds the (hi, mid, lo) bf16 split of |x|^2 stored in the same columns of the row mirror.
 // One warp per query row, four columns per lane and step (D % 8 == 0, Dp % 8 == 0): 128-bit loads, 64-bit stores.
+// List-major IVF (row_query != nullptr): operand row r is the (query, probed list) pair (row_query[r], row_list[r]) and holds
+// the RESIDUAL v = q - centroid[list] (the rows of the list-major mirror are residuals too: |v - r|^2 is the distance, and the
+// bf16 error scales with |v||r| instead of |q||x|); columns D..D+2 = 1 (x-norm split), D+3..D+5 = the 3-way bf16 split of
+// |v|^2, so the accumulator is the SQUARED DISTANCE, comparable across the pairs of a query.  qstat[r] = (|v|^2, |bf16(v)-v|^2).
 __global__ void __launch_bounds__(256)
 tc_query_operand_kernel(const float* __restrict__ q, __nv_bfloat16* __restrict__ y, int Q, int D, int Dp,
                         int metric, uint32_t* __restrict__ gtau, int32_t* __restrict__ uncert,
-                        int32_t* __restrict__ item_count) {
+                        int32_t* __restrict__ item_count, const int32_t* __restrict__ row_query,
+                        const int32_t* __restrict__ row_list, const float* __restrict__ centroids,
+                        float2* __restrict__ qstat) {
     if (blockIdx.x == 0 && threadIdx.x == 0) { uncert[0] = 0; item_count[0] = 0; }   // filled by the post-scan kernels
     const int lane = threadIdx.x & 31;
     const int r = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
     if (r >= Q) return;
     if (lane == 0) gtau[r] = 0xFF800000u;                          // the scan's per-query threshold exchange starts at +inf
-    const float4* src = reinterpret_cast<const float4*>(q + (size_t)r * D);
+    const int rq = row_query ? row_query[r] : r;
     uint2* dst = reinterpret_cast<uint2*>(y + (size_t)r * Dp);
-    for (int c4 = lane; c4 < (Dp >> 2); c4 += 32) {
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (c4 < (D >> 2)) v = src[c4];
-        else if (metric == VDB_METRIC_L2 && c4 == (D >> 2)) v = make_float4(1.f, 1.f, 1.f, 0.f);   // columns D, D+1, D+2
+    if (rq < 0) {                                                  // padding of a pair tile
+        for (int c4 = lane; c4 < (Dp >> 2); c4 += 32) dst[c4] = make_uint2(0u, 0u);
+        if (qstat && lane == 0) qstat[r] = make_float2(0.f, 0.f);
+        return;
+    }
+    const float4* src = reinterpret_cast<const float4*>(q + (size_t)rq * D);
+    const float4* cen = row_query ? reinterpret_cast<const float4*>(centroids + (size_t)row_list[r] * D) : nullptr;
+    float vsq = 0.f, rsq = 0.f;
+    for (int c4 = lane; c4 < (D >> 2); c4 += 32) {
+        float4 v = src[c4];
+        if (cen) { const float4 c = cen[c4]; v.x -= c.x; v.y -= c.y; v.z -= c.z; v.w -= c.w; }
         const __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
         uint2 pk;
         pk.x = *reinterpret_cast<const uint32_t*>(&lo);
         pk.y = *reinterpret_cast<const uint32_t*>(&hi);
         dst[c4] = pk;
+        if (cen) {
+            const float r0 = __low2float(lo) - v.x, r1 = __high2float(lo) - v.y, r2 = __low2float(hi) - v.z, r3 = __high2float(hi) - v.w;
+            vsq = fmaf(v.x, v.x, vsq); vsq = fmaf(v.y, v.y, vsq); vsq = fmaf(v.z, v.z, vsq); vsq = fmaf(v.w, v.w, vsq);
+            rsq = fmaf(r0, r0, rsq); rsq = fmaf(r1, r1, rsq); rsq = fmaf(r2, r2, rsq); rsq = fmaf(r3, r3, rsq);
+        }
     }
+    if (cen) { vsq = warp_sum(vsq); rsq = warp_sum(rsq); }
+    if (metric == VDB_METRIC_L2) {                                 // the 16-column norm block after the D data columns
+        for (int c4 = (D >> 2) + lane; c4 < (Dp >> 2); c4 += 32) {
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (c4 == (D >> 2)) {
+                v = make_float4(1.f, 1.f, 1.f, 0.f);               // columns D, D+1, D+2 against the split of |x|^2
+                if (cen) v.w = __bfloat162float(__float2bfloat16_rn(vsq));                      // column D+3: hi part of |v|^2
+            } else if (cen && c4 == (D >> 2) + 1) {
+                const float h = __bfloat162float(__float2bfloat16_rn(vsq));
+                const float m = __bfloat162float(__float2bfloat16_rn(vsq - h));
+                v = make_float4(m, __bfloat162float(__float2bfloat16_rn(vsq - h - m)), 0.f, 0.f);   // columns D+4, D+5
+            }
+            const __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+            uint2 pk;
+            pk.x = *reinterpret_cast<const uint32_t*>(&lo);
+            pk.y = *reinterpret_cast<const uint32_t*>(&hi);
+            dst[c4] = pk;
+        }
+    }
+    if (qstat && lane == 0) qstat[r] = make_float2(vsq, rsq);
 }
 
 // Row operand ("mirror"), one warp per row, built once per index mutation:
@@ -436,7 +489,9 @@ __global__ void tc_row_operand_kernel(const float* __restrict__ x, int64_t N, in
             const float r1 = acc - __bfloat162float(h);
             const __nv_bfloat16 m = __float2bfloat16_rn(r1);
             const __nv_bfloat16 l = __float2bfloat16_rn(r1 - __bfloat162float(m));
-            const __nv_bfloat16 v = lane == 0 ? h : (lane == 1 ? m : (lane == 2 ? l : __float2bfloat16_rn(0.f)));
+            // columns 3..5 hold 1.0: the list-major IVF query operand carries the split of |q - c|^2 there (zero for the
+            // brute-force scan), which turns the score into the squared distance itself
+            const __nv_bfloat16 v = lane == 0 ? h : (lane == 1 ? m : (lane == 2 ? l : __float2bfloat16_rn(lane < 6 ? 1.f : 0.f)));
             norms[r * 16 + (lane ^ ((int)((r >> 2) & 1) << 3))] = v;
         }
     }
@@ -491,36 +546,78 @@ constexpr int kSelWarps = 4;
 __global__ void __launch_bounds__(32 * kSelWarps)
 tc_select_kernel(const u64* __restrict__ partial, int L, int NBL, int NB, int C, const float* __restrict__ qv, int D, int k,
                  int metric, const float* __restrict__ stats, int no_trim, int Q, TcPostQuery* __restrict__ pq,
-                 uint2* __restrict__ items, int32_t* __restrict__ item_count) {
+                 uint2* __restrict__ items, int32_t* __restrict__ item_count, const int32_t* __restrict__ pair_rows, int P,
+                 const float2* __restrict__ qstat, const int32_t* __restrict__ row_list, const float2* __restrict__ list_stats) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int q = (int)blockIdx.x * kSelWarps + warp;
     if (q >= Q) return;
     u64* buf = reinterpret_cast<u64*>(smem_raw) + (size_t)warp * C;       // [C] keys; entry i belongs to lane i % 32
-    const int total = L * NBL;                                             // <= C <= 1024: at most 32 entries per lane
+    // brute force: the query's L lists are contiguous.  List-major IVF: operand row pair_rows[q][p] holds the lists of the
+    // query's p-th probed list (L lists each); -1 = the probed list is empty
+    const int per_row = L * NBL;
+    const int total = (pair_rows ? P : 1) * per_row;                       // <= C <= 1024: at most 32 entries per lane
     float a = 0.f, b = 0.f;                                // |q|^2 in the order rerank_f32_kernel uses, and |bf16(q) - q|^2
-    for (int t = lane; t < D; t += 32) {
-        const float v = qv[(size_t)q * D + t], r = bf16_residual(v);
-        a = fmaf(v, v, a);
-        b = fmaf(r, r, b);
+    float eps = 0.f, slack = 0.f;                          // the certificate's allowance, also the trim's
+    float eps_pair = 0.f;                                  // list-major IVF: lane p = allowance of the query's p-th pair
+    if (qstat) {
+        // list-major IVF: the operand rows are residuals q - centroid, one per probed list, and every probed list has its
+        // own row bounds (list_stats, else the global ones), so every PAIR has its own allowance eps_p.  The keys of pair p
+        // are lowered by eps_p when they are loaded: from there on every score is a LOWER BOUND of the bin's true minimum,
+        // and the certificate needs no further eps (a far, wide list no longer loosens the bound of the near ones).
+        for (int p = lane; p < P; p += 32) {
+            const int row = pair_rows[(size_t)q * P + p];
+            if (row >= 0) {
+                const float2 st = qstat[row];
+                float A = stats[0], B = stats[1];
+                if (list_stats) { const float2 ls = list_stats[row_list[row]]; A = fminf(A, ls.x); B = fminf(B, ls.y); }
+                float s;
+                tc_bound(metric, sqrtf(st.x) * 1.0001f, sqrtf(st.y) * 1.0001f, A, B, &eps_pair, &s);
+                slack = fmaxf(slack, s);
+            }
+        }
+        eps = eps_pair;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            eps = fmaxf(eps, __shfl_xor_sync(0xffffffffu, eps, o));
+            slack = fmaxf(slack, __shfl_xor_sync(0xffffffffu, slack, o));
+        }
+    } else {
+        for (int t = lane; t < D; t += 32) {
+            const float v = qv[(size_t)q * D + t], r = bf16_residual(v);
+            a = fmaf(v, v, a);
+            b = fmaf(r, r, b);
+        }
+        a = warp_sum(a);
+        b = warp_sum(b);
+        tc_bound(metric, sqrtf(a) * 1.0001f, sqrtf(b) * 1.0001f, stats[0], stats[1], &eps, &slack);
     }
-    a = warp_sum(a);
-    b = warp_sum(b);
     unsigned full_worst = f32_to_ordered(INFINITY);        // ordered-float minimum over the full lists' worst entries
     for (int i = lane; i < C; i += 32) {
         u64 key = VDB_KEY_MAX;
+        int pi = 0;
         if (i < total) {
-            key = partial[(size_t)q * total + i];
-            if (key_index(key) == 0xFFFFFFFFu) key = VDB_KEY_MAX;                  // empty slot
-            else if ((i % NBL) == NBL - 1) full_worst = min(full_worst, (unsigned)(key >> 32));
+            int64_t row = q;
+            int within = i;
+            if (pair_rows) {
+                pi = i / per_row;
+                within = i - pi * per_row;
+                row = pair_rows[(size_t)q * P + pi];
+            }
+            if (row >= 0) key = partial[(size_t)row * per_row + within];
+        }
+        const float ep = __shfl_sync(0xffffffffu, eps_pair, pi);                   // 0 in the brute-force scan
+        if (key_index(key) == 0xFFFFFFFFu) key = VDB_KEY_MAX;                      // empty slot
+        else {
+            if (pair_rows)
+                key = ((u64)f32_to_ordered(ordered_to_f32((unsigned)(key >> 32)) - ep) << 32) | (key & 0xFFFFFFFFull);
+            if ((i % NBL) == NBL - 1) full_worst = min(full_worst, (unsigned)(key >> 32));
         }
         buf[i] = key;
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) full_worst = min(full_worst, __shfl_xor_sync(0xffffffffu, full_worst, o));
     __syncwarp();
-    float eps, slack;                                                // the certificate's allowance, also the trim's
-    tc_bound(metric, sqrtf(a) * 1.0001f, sqrtf(b) * 1.0001f, stats[0], stats[1], &eps, &slack);
     // ---- rounds: the smallest remaining ordered score; `taken` = this lane's entries already extracted (bit t: entry lane + 32 t)
     uint32_t taken = 0u;
     unsigned last = 0xFFFFFFFFu;                                     // score of the last extracted key (ordered bits)
@@ -589,8 +686,8 @@ tc_select_kernel(const u64* __restrict__ partial, int L, int NBL, int NB, int C,
     if (lane == 0) {
         base = keep > 0 ? atomicAdd(item_count, keep) : 0;
         TcPostQuery o;
-        o.tau_minus = tau - eps - slack;
-        o.qsq = a;
+        o.tau_minus = qstat ? tau - slack : tau - eps - slack;       // IVF keys are lower bounds already
+        o.qsq = qstat ? 0.f : a;                                 // IVF scores are squared distances: nothing to subtract
         o.keep = keep;
         o.pad = 0;
         pq[q] = o;
@@ -897,25 +994,56 @@ static bool plan_tc(int Q, int64_t N, int D, int k, int metric, TcPlan* p) {
 }
 
 struct TcWorkspace {
-    size_t qbf16, partial, tau, pq, items, keys, counters, rescan, rescan_bytes, total;
+    size_t qbf16, partial, tau, qstat, pq, items, keys, counters, rescan, rescan_bytes, total;
 };
 
-static TcWorkspace tc_workspace(const TcPlan& p, int Q, int64_t N, int D, int k) {
+// Qa = rows of the query operand (= Q for the brute-force scan; pair-tile rows for list-major IVF, which has no fp32 rescan)
+static TcWorkspace tc_workspace(const TcPlan& p, int Q, int64_t Qa, int64_t N, int D, int k, bool rescan) {
     TcWorkspace w;
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
-    w.qbf16 = take((size_t)Q * p.Dp * 2);
-    w.partial = take((size_t)Q * p.S * kGroups * kNBLMax * 8);
-    w.tau = take((size_t)Q * 4);
+    w.qbf16 = take((size_t)Qa * p.Dp * 2);
+    w.partial = take((size_t)Qa * p.S * kGroups * kNBLMax * 8);
+    w.tau = take((size_t)Qa * 4);
+    w.qstat = take(rescan ? 0 : (size_t)Qa * 8);             // list-major IVF: (|v|^2, |bf16(v) - v|^2) per operand row
     w.pq = take((size_t)Q * sizeof(TcPostQuery));
     w.items = take((size_t)Q * kNBFinal * sizeof(uint2));
     w.keys = take((size_t)Q * kNBFinal * kBin * 8);
     w.counters = take(256);
-    w.rescan_bytes = exact_f32_subset_workspace(Q, N, D, k);      // fp32 rescan of uncertified queries
+    w.rescan_bytes = rescan ? exact_f32_subset_workspace(Q, N, D, k) : 0;      // fp32 rescan of uncertified queries
     w.rescan = take(w.rescan_bytes);
     w.total = off;
     return w;
 }
+
+// List-major IVF on the same pipeline (ivf.py:170-199 for a batch): the database operand is the list-major copy of the rows
+// (every list padded to whole 256-row tiles), the query operand holds one row per (query, probed list) pair, pairs of a
+// list padded to whole 128-row tiles, and a unit table names (pair tile, row tiles of its list).
+struct TcIvf {
+    int n_probe;                   // probed lists per query (<= 32)
+    const int32_t* pair_rows;      // [Q][n_probe] operand row of the query's p-th probe, -1 = empty list
+    const int32_t* row_query;      // [Qa] query of an operand row, -1 = padding
+    const int32_t* row_list;       // [Qa] inverted list of an operand row
+    const float* centroids;        // [K][D]: operand rows and mirror rows are residuals against the list's centroid
+    int64_t Qa;                    // operand rows (multiple of 128)
+    const int4* utab;              // [n_units] (pair tile, first row tile, end row tile, 0)
+    int n_units;
+    const float2* list_stats;      // [K] per list (max |bf16(x - c)|, max |bf16(x - c) - (x - c)|), or null: the global pair
+};
+
+static bool plan_tc_ivf(const TcIvf& v, int64_t N, int D, int k, TcPlan* p) {
+    if (!plan_tc((int)(v.Qa < (1 << 30) ? v.Qa : (1 << 30)), N, D, k, VDB_METRIC_L2, p)) return false;
+    p->m_tiles = v.n_units;        // units = m_tiles * S; tc_unit() reads the table instead of decoding u
+    p->S = 1;
+    p->tiles_per_slice = p->tiles_total;
+    const int sms = sm_count();
+    p->grid = v.n_units < sms ? v.n_units : sms;
+    return true;
+}
+
+static int tc_search_impl(const float* q, int Q, const float* db, const void* mirror, const float* db_stats,
+                          const int64_t* ids, int64_t N, int D, int k, int metric, float* out_d, int64_t* out_i,
+                          int32_t* out_uncertified, void* ws, size_t ws_bytes, void* stream, const TcIvf* ivf);
 
 }  // namespace vdb
 
@@ -953,20 +1081,55 @@ int vdb_tc_prepare_rows(const float* vecs, int64_t N, int D, int metric, float* 
 size_t vdb_exact_topk_tc_workspace(int Q, int64_t N, int D, int k, int metric) {
     TcPlan p;
     if (!plan_tc(Q, N, D, k, metric, &p)) return 0;
-    return tc_workspace(p, Q, N, D, k).total;
+    return tc_workspace(p, Q, Q, N, D, k, true).total;
 }
 
 int vdb_exact_topk_tc(const float* q, int Q, const float* db, const void* mirror, const float* db_stats,
                       const int64_t* ids, int64_t N, int D, int k, int metric, float* out_d,
                       int64_t* out_i, int32_t* out_uncertified, void* ws, size_t ws_bytes, void* stream) {
+    return tc_search_impl(q, Q, db, mirror, db_stats, ids, N, D, k, metric, out_d, out_i, out_uncertified, ws, ws_bytes,
+                          stream, nullptr);
+}
+
+size_t vdb_ivf_topk_tc_workspace(int Q, int64_t Qa, int64_t N, int D, int k, int n_units) {
+    TcIvf v{1, nullptr, nullptr, nullptr, nullptr, Qa, nullptr, n_units, nullptr};
+    TcPlan p;
+    if (Q <= 0 || Qa <= 0 || n_units <= 0 || !plan_tc_ivf(v, N, D, k, &p)) return 0;
+    return tc_workspace(p, Q, Qa, N, D, k, false).total;
+}
+
+int vdb_ivf_topk_tc(const float* q, int Q, const float* lm_vecs, const void* lm_mirror, const float* lm_stats,
+                    const int64_t* lm_ids, int64_t N, int D, int k, int n_probe, const int32_t* pair_rows,
+                    const int32_t* row_query, const int32_t* row_list, const float* centroids, int64_t Qa,
+                    const int32_t* unit_table, int n_units, const float* list_stats, float* out_d,
+                    int64_t* out_i, int32_t* out_uncertified, void* ws, size_t ws_bytes, void* stream) {
+    VDB_REQUIRE(n_probe > 0 && n_probe <= 32, VDB_ERR_UNSUPPORTED, "vdb_ivf_topk_tc: n_probe=%d (at most 32)", n_probe);
+    VDB_REQUIRE(pair_rows && row_query && row_list && centroids && unit_table && n_units > 0 && Qa > 0 && Qa % kTileM == 0 && N % kTileN == 0,
+                VDB_ERR_INVALID, "vdb_ivf_topk_tc: bad pair / unit tables (Qa=%lld, N=%lld, units=%d)", (long long)Qa,
+                (long long)N, n_units);
+    TcIvf v{n_probe, pair_rows, row_query, row_list, centroids, Qa, reinterpret_cast<const int4*>(unit_table), n_units,
+            reinterpret_cast<const float2*>(list_stats)};
+    return tc_search_impl(q, Q, lm_vecs, lm_mirror, lm_stats, lm_ids, N, D, k, VDB_METRIC_L2, out_d, out_i, out_uncertified,
+                          ws, ws_bytes, stream, &v);
+}
+
+}  // extern "C"
+
+namespace vdb {
+
+static int tc_search_impl(const float* q, int Q, const float* db, const void* mirror, const float* db_stats,
+                          const int64_t* ids, int64_t N, int D, int k, int metric, float* out_d, int64_t* out_i,
+                          int32_t* out_uncertified, void* ws, size_t ws_bytes, void* stream, const TcIvf* ivf) {
     VDB_REQUIRE(metric == VDB_METRIC_L2 || metric == VDB_METRIC_COSINE, VDB_ERR_INVALID, "unknown metric %d", metric);
     VDB_REQUIRE(Q > 0 && N > 0 && D > 0 && k > 0, VDB_ERR_INVALID, "vdb_exact_topk_tc: bad shape");
     VDB_REQUIRE(q && db && mirror && db_stats && out_d && out_i && out_uncertified && ws, VDB_ERR_INVALID,
                 "vdb_exact_topk_tc: null pointer");
     VDB_REQUIRE(N < (1ll << 31), VDB_ERR_UNSUPPORTED, "N too large for int32 candidate rows");
     TcPlan p;
-    VDB_REQUIRE(plan_tc(Q, N, D, k, metric, &p), VDB_ERR_UNSUPPORTED, "tensor-core scan does not support D=%d k=%d", D, k);
-    const TcWorkspace w = tc_workspace(p, Q, N, D, k);
+    VDB_REQUIRE(ivf ? plan_tc_ivf(*ivf, N, D, k, &p) : plan_tc(Q, N, D, k, metric, &p), VDB_ERR_UNSUPPORTED,
+                "tensor-core scan does not support D=%d k=%d", D, k);
+    const int64_t Qa = ivf ? ivf->Qa : Q;                            // rows of the query operand
+    const TcWorkspace w = tc_workspace(p, Q, Qa, N, D, k, ivf == nullptr);
     VDB_REQUIRE(ws_bytes >= w.total, VDB_ERR_WORKSPACE, "workspace %zu < %zu", ws_bytes, w.total);
     VDB_REQUIRE((reinterpret_cast<uintptr_t>(mirror) & 15) == 0 && (reinterpret_cast<uintptr_t>(ws) & 255) == 0,
                 VDB_ERR_INVALID, "operand mirror / workspace must be 16 / 256-byte aligned");
@@ -979,16 +1142,19 @@ int vdb_exact_topk_tc(const float* q, int Q, const float* db, const void* mirror
     // per-list depth: lists of 8 are enough when there are many of them (L * 8 >= 4 * kNBFinal), debug bit 2 forces 16
     const int nbl = ((g_tc_flags & 4) || p.S * kGroups * 8 < 4 * kNBFinal) ? 16 : 8;
     uint32_t* gtau = reinterpret_cast<uint32_t*>(tau);            // per-query threshold exchange of the scan
-    tc_query_operand_kernel<<<(Q + 7) / 8, 256, 0, st>>>(q, qb, Q, D, p.Dp, metric, gtau, out_uncertified,
-                                                            reinterpret_cast<int32_t*>(base + w.counters));
+    tc_query_operand_kernel<<<(unsigned)((Qa + 7) / 8), 256, 0, st>>>(q, qb, (int)Qa, D, p.Dp, metric, gtau, out_uncertified,
+                                                                     reinterpret_cast<int32_t*>(base + w.counters),
+                                                                     ivf ? ivf->row_query : nullptr, ivf ? ivf->row_list : nullptr,
+                                                                     ivf ? ivf->centroids : nullptr,
+                                                                     ivf ? reinterpret_cast<float2*>(base + w.qstat) : nullptr);
     CUtensorMap map_a, map_b;
     CUtensorMap map_a2, map_b2;
-    int rc = make_map(&map_a, qb, Q, D, p.Dp, kBlockK, kTileM);
+    int rc = make_map(&map_a, qb, Qa, D, p.Dp, kBlockK, kTileM);
     if (rc) return rc;
     rc = make_map(&map_b, mirror, N, D, D, kBlockK, kTileN);
     if (rc) return rc;
     // norm block (L2 only; cosine passes valid but unused maps): columns D..D+15 of the same operands
-    rc = make_map(&map_a2, qb, Q, p.Dp, p.Dp, 16, kTileM);
+    rc = make_map(&map_a2, qb, Qa, p.Dp, p.Dp, 16, kTileM);
     if (rc) return rc;
     // norm area viewed as lines of 4 rows (64 bf16 = 128 B): a 256-row tile is 64 line fetches, no swizzle (pre-applied)
     rc = make_map(&map_b2, p.has_norm ? static_cast<const void*>(static_cast<const __nv_bfloat16*>(mirror) + tc_norm_offset(N, D)) : mirror,
@@ -998,17 +1164,21 @@ int vdb_exact_topk_tc(const float* q, int Q, const float* db, const void* mirror
         ProfScope prof(kProfExactTC, st);
         if (nbl == 16) {
             VDB_CUDA(cudaFuncSetAttribute(exact_tc_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem));
-            exact_tc_kernel<16><<<p.grid, kTcThreads, p.smem, st>>>(map_a, map_b, map_a2, map_b2, Q, N, D, p.has_norm, p.num_kb, p.stages, p.m_tiles, p.S,
-                                                                   p.tiles_per_slice, p.tiles_total, g_tc_flags, partial, gtau);
+            exact_tc_kernel<16><<<p.grid, kTcThreads, p.smem, st>>>(map_a, map_b, map_a2, map_b2, (int)Qa, N, D, p.has_norm, p.num_kb, p.stages, p.m_tiles, p.S,
+                                                                   p.tiles_per_slice, p.tiles_total, g_tc_flags, partial, gtau,
+                                                                   ivf ? ivf->utab : nullptr);
         } else {
             VDB_CUDA(cudaFuncSetAttribute(exact_tc_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem));
-            exact_tc_kernel<8><<<p.grid, kTcThreads, p.smem, st>>>(map_a, map_b, map_a2, map_b2, Q, N, D, p.has_norm, p.num_kb, p.stages, p.m_tiles, p.S,
-                                                                  p.tiles_per_slice, p.tiles_total, g_tc_flags, partial, gtau);
+            exact_tc_kernel<8><<<p.grid, kTcThreads, p.smem, st>>>(map_a, map_b, map_a2, map_b2, (int)Qa, N, D, p.has_norm, p.num_kb, p.stages, p.m_tiles, p.S,
+                                                                  p.tiles_per_slice, p.tiles_total, g_tc_flags, partial, gtau,
+                                                                  ivf ? ivf->utab : nullptr);
         }
     }
     VDB_CUDA(cudaGetLastError());
-    const int L = p.S * kGroups;
-    const int C = next_pow2(L * nbl < 64 ? 64 : L * nbl);
+    const int L = p.S * kGroups;                                     // lists per operand row
+    const int lists = L * (ivf ? ivf->n_probe : 1);                  // lists the select kernel merges per query
+    const int C = next_pow2(lists * nbl < 64 ? 64 : lists * nbl);
+    VDB_REQUIRE(C <= 1024, VDB_ERR_UNSUPPORTED, "too many bin lists per query (%d x %d)", lists, nbl);
     // bins handed to the rerank per query (the post-scan kernel drops those that provably cannot matter);
     // debug bits 12..19 override the count, bit 4 disables the trimming
     int nbf = kNBFinal;
@@ -1024,7 +1194,10 @@ int vdb_exact_topk_tc(const float* q, int Q, const float* db, const void* mirror
         const size_t sel_smem = (size_t)kSelWarps * C * 8;
         VDB_CUDA(cudaFuncSetAttribute(tc_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sel_smem));
         tc_select_kernel<<<(Q + kSelWarps - 1) / kSelWarps, 32 * kSelWarps, sel_smem, st>>>(
-            partial, L, nbl, nbf, C, q, D, k, metric, db_stats, (g_tc_flags & 16) ? 1 : 0, Q, pq, items, item_count);
+            partial, L, nbl, nbf, C, q, D, k, metric, db_stats, (g_tc_flags & 16) ? 1 : 0, Q, pq, items, item_count,
+            ivf ? ivf->pair_rows : nullptr, ivf ? ivf->n_probe : 1,
+            ivf ? reinterpret_cast<const float2*>(base + w.qstat) : nullptr, ivf ? ivf->row_list : nullptr,
+            ivf ? ivf->list_stats : nullptr);
         // one CTA per SM: as many warps (each with a two-slot ring of bin + query) as shared memory holds, at most 8
         int rr_warps = (int)((size_t)(max_smem_optin() - 2048) / (kRrSlots * rr_slot_bytes(D)));
         if (rr_warps > kRrMaxWarps) rr_warps = kRrMaxWarps;
@@ -1045,9 +1218,12 @@ int vdb_exact_topk_tc(const float* q, int Q, const float* db, const void* mirror
     }
     count_launch(5);
     VDB_CUDA(cudaGetLastError());
+    // list-major IVF: a brute-force rescan would look at lists the query did not probe -- the caller re-runs the listed
+    // queries through vdb_ivf_scan
+    if (ivf) return VDB_OK;
     // queries the certificate rejected: exact fp32 scan, driven by the device-side list (no host round trip)
     return exact_f32_subset(q, Q, db, ids, N, D, k, metric, out_uncertified + 1, out_uncertified, out_d, out_i,
                             base + w.rescan, w.rescan_bytes, st);
 }
 
-}  // extern "C"
+}  // namespace vdb

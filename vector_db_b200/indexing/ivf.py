@@ -52,6 +52,9 @@ class IvfIndex:
         self._list_rows: Optional[torch.Tensor] = None
         self._csr_dirty = True
         self.last_scanned: Optional[np.ndarray] = None   # candidates enumerated per query by the last search
+        self.batch_engine = "auto"                       # "auto" | "tc" (list-major tensor-core batch search) | "scan"
+        self.last_uncertified = 0
+        self._lm = None
         if self.index_file and self.index_file.exists():
             self.load_index()
 
@@ -82,7 +85,116 @@ class IvfIndex:
             self._list_ptr = torch.from_numpy(ptr.astype(np.int32)).to(self._device)
             self._list_rows = torch.tensor(rows if rows else [0], dtype=torch.int32, device=self._device)
             self._csr_dirty = False
+            self._lm = None
         return self._list_ptr, self._list_rows
+
+    # ------------------------------------------------------------------ list-major copy for the tensor-core batch search
+    def _list_major(self) -> dict:
+        """Rows in list-major order, every list padded to whole 256-row tiles, with their L2 operand mirror
+        (vdb_ivf_topk_tc).  Built on first use after a change of the lists; costs one more copy of the rows in HBM."""
+        ptr, rows = self._csr()
+        lm = getattr(self, "_lm", None)
+        if lm is not None and lm["ptr"] is ptr:
+            return lm
+        dev, vec = self._device, self._vectors
+        ptr64 = ptr.long()
+        counts = ptr64[1:] - ptr64[:-1]
+        padded = (counts + 255) // 256 * 256
+        start = torch.zeros(self.k + 1, dtype=torch.int64, device=dev)
+        start[1:] = torch.cumsum(padded, 0)
+        n_pad = int(start[-1].item())
+        n = int(ptr64[-1].item())
+        lm_row = torch.full((max(n_pad, 256),), -1, dtype=torch.int64, device=dev)
+        if n:
+            list_of = torch.repeat_interleave(torch.arange(self.k, device=dev), counts)
+            pos = start[list_of] + (torch.arange(n, device=dev) - ptr64[list_of])
+            lm_row[pos] = rows[:n].long()
+        n_pad = lm_row.numel()
+        src = lm_row.clamp(min=0)
+        lm_vecs = vec.vecs[src].contiguous()
+        # the operand mirror holds RESIDUALS against the list's centroid (padding rows: zero, so the measured stats stay real)
+        lm_list = torch.searchsorted(start, torch.arange(n_pad, device=dev), right=True) - 1
+        res = lm_vecs - self._centroids_dev[lm_list.clamp(max=self.k - 1)]
+        res[lm_row < 0] = 0
+        mirror, _, stats = ops.tc_prepare_rows(res, "l2")
+        # per-list row bounds for the certificate (the global pair `stats` is the maximum over ALL lists: one wide list
+        # would loosen every query's allowance); 1.0001 covers the fp32 rounding of the norms computed here
+        rb = res.to(torch.bfloat16).to(torch.float32)
+        per_row = torch.stack([rb.norm(dim=1), (rb - res).norm(dim=1)], 1) * 1.0001
+        del res, rb
+        list_stats = torch.zeros((self.k, 2), dtype=torch.float32, device=dev)
+        list_stats.scatter_reduce_(0, lm_list.clamp(max=self.k - 1).unsqueeze(1).expand(-1, 2), per_row, "amax")
+        pad = (lm_row < 0).nonzero().squeeze(1)
+        if pad.numel():                                               # a padding row can never be selected: |x|^2 := 1e30
+            off = ops.tc_norm_offset(n_pad, vec.dim)
+            mirror[off + pad * 16 + (((pad >> 2) & 1) << 3)] = 1e30
+        lm_ids = torch.where(lm_row >= 0, vec.ids[src], torch.full_like(lm_row, -1))
+        self._lm = {"ptr": ptr, "vecs": lm_vecs, "mirror": mirror, "stats": stats, "list_stats": list_stats, "ids": lm_ids,
+                    "start": start,
+                    "counts": counts, "padded": padded}
+        return self._lm
+
+    def _search_list_major(self, q: torch.Tensor, probes: torch.Tensor, prefix: torch.Tensor, top_k: int):
+        """Batch search through the tensor cores: (query, probed list) pairs grouped by list, one small dense contraction per
+        list (vdb_ivf_topk_tc), selection / exact fp32 rerank / certificate per query; then the reference's stable order
+        (distance, enumeration sequence -- ivf.py:177-193) is restored among equal distances and queries the certificate
+        rejected are re-run through the query-major scan.  Returns (dist, ids) or None when the shape is not covered."""
+        lm = self._list_major()
+        dev = self._device
+        Q, n_probe = probes.shape
+        k2 = top_k + 1                # one extra result: a tie run that crosses the cut is SEEN and sent to the query-major scan
+        pl = probes.reshape(-1).long()                                # pair p = q * n_probe + rank -> list
+        live = lm["counts"][pl] > 0
+        order = torch.argsort(pl, stable=True)
+        order = order[live[order]]                                    # pairs with a non-empty list, grouped by list
+        if order.numel() == 0:
+            return None
+        lists_sorted = pl[order]
+        n_l = torch.bincount(lists_sorted, minlength=self.k)
+        mt_l = (n_l + 127) // 128
+        arow0 = torch.zeros(self.k + 1, dtype=torch.int64, device=dev)
+        arow0[1:] = torch.cumsum(mt_l * 128, 0)
+        grp0 = torch.zeros(self.k + 1, dtype=torch.int64, device=dev)
+        grp0[1:] = torch.cumsum(n_l, 0)
+        arow = arow0[lists_sorted] + (torch.arange(order.numel(), device=dev) - grp0[lists_sorted])
+        Qa = int(arow0[-1].item())
+        row_query = torch.full((Qa,), -1, dtype=torch.int32, device=dev)
+        row_query[arow] = (order // n_probe).to(torch.int32)
+        row_list = torch.zeros((Qa,), dtype=torch.int32, device=dev)
+        row_list[arow] = lists_sorted.to(torch.int32)
+        pair_rows = torch.full((Q * n_probe,), -1, dtype=torch.int32, device=dev)
+        pair_rows[order] = arow.to(torch.int32)
+        n_units = int(mt_l.sum().item())
+        ulist = torch.repeat_interleave(torch.arange(self.k, device=dev), mt_l)
+        u0 = torch.zeros(self.k + 1, dtype=torch.int64, device=dev)
+        u0[1:] = torch.cumsum(mt_l, 0)
+        utab = torch.zeros((n_units, 4), dtype=torch.int32, device=dev)
+        utab[:, 0] = (arow0[ulist] // 128 + (torch.arange(n_units, device=dev) - u0[ulist])).to(torch.int32)
+        utab[:, 1] = (lm["start"][ulist] // 256).to(torch.int32)
+        utab[:, 2] = ((lm["start"][ulist] + lm["padded"][ulist]) // 256).to(torch.int32)
+        d, pos, uncert = ops.ivf_topk_tc(q, lm["vecs"], lm["mirror"], lm["stats"], None, k2, n_probe, pair_rows, row_query,
+                                         row_list, self._centroids_dev, utab, lm["list_stats"])
+        # (distance, sequence) order: sequence = candidates enumerated before the row's list + position in the list
+        valid = pos >= 0
+        p0 = pos.clamp(min=0)
+        lst = torch.searchsorted(lm["start"], p0, right=True) - 1                     # list of every result
+        rank = (probes.long().unsqueeze(1) == lst.unsqueeze(2)).to(torch.int64).argmax(dim=2)   # its rank among the probes
+        seq = torch.gather(prefix.long(), 1, rank) + (p0 - lm["start"][lst])
+        key = (d.contiguous().view(torch.int32).long() << 32) | seq                    # d >= 0: its bits sort like the value
+        key = torch.where(valid, key, torch.full_like(key, torch.iinfo(torch.int64).max))
+        sel = torch.argsort(key, dim=1, stable=True)
+        d_sorted, valid_sorted = torch.gather(d, 1, sel), torch.gather(valid, 1, sel)
+        sel = sel[:, :top_k]
+        d = d_sorted[:, :top_k]
+        ids = torch.gather(torch.where(valid, lm["ids"][p0], torch.full_like(pos, -1)), 1, sel)
+        n_bad = int(uncert[0].item())
+        bad = torch.zeros((Q,), dtype=torch.bool, device=dev)
+        if n_bad:
+            bad[uncert[1:1 + n_bad].long()] = True
+        # equal distances on both sides of the cut: which of them the reference keeps depends on rows this call did not fetch
+        bad |= valid_sorted[:, top_k] & (d_sorted[:, top_k] == d_sorted[:, top_k - 1])
+        bad = bad.nonzero().squeeze(1)
+        return d, ids, (bad if bad.numel() else None)
 
     def _set_centroids(self, cent: torch.Tensor) -> None:
         self._centroids_dev = cent.contiguous()
@@ -232,6 +344,22 @@ class IvfIndex:
         if filter_ids is not None:
             flt = vec.bitmap_from_ids(filter_ids)
             alive = flt if alive is None else torch.bitwise_and(alive[:flt.numel()], flt)
+        Q = q.shape[0]
+        # the list-major pass costs ~1.3 ms of grouping before its first tile; the query-major scan streams the probed rows
+        # at 1-4.5 TB/s (L2-served): "auto" takes the tensor cores from ~8 GB of probed rows (and two probes) on
+        probed_bytes = Q * n_probe * (vec.n / max(self.k, 1)) * vec.dim * 4
+        worth = self.batch_engine == "tc" or (n_probe >= 2 and probed_bytes >= 8e9)
+        if (self.batch_engine != "scan" and filter_ids is None and alive is None and n_probe <= 32 and top_k <= 10
+                and vec.dim % 8 == 0 and vec.dim <= 512 and worth):
+            out = self._search_list_major(q, probes, prefix, top_k)
+            if out is not None:
+                d, ids, bad = out
+                if bad is not None:                                   # the certificate rejected these: query-major exact scan
+                    db, ib = ops.ivf_scan(q[bad], vec.vecs, ptr, rows, probes[bad], prefix[bad], top_k, ids=vec.ids)
+                    d[bad] = db
+                    ids[bad] = ib
+                self.last_uncertified = 0 if bad is None else int(bad.numel())
+                return d, ids, prefix[:, n_probe].long()
         return ops.ivf_scan(q, vec.vecs, ptr, rows, probes, prefix, top_k, alive=alive, ids=vec.ids, return_scanned=True)
 
     def search(self, query: np.ndarray, n_probe: int, top_k: int) -> List[Tuple[Node, float]]:

@@ -400,3 +400,35 @@ def exact_topk_tc(q: torch.Tensor, db: torch.Tensor, mirror: torch.Tensor, stats
     if return_uncertified:
         return out_d, out_i, uncert[0]
     return out_d, out_i
+
+
+def tc_norm_offset(n: int, d: int) -> int:
+    """Element offset of the packed norm block inside an L2 operand mirror of n rows (see tc_prepare_rows)."""
+    return int(load().vdb_tc_mirror_elems(int(n), int(d), METRIC_L2)) - ((int(n) + 3) & ~3) * 16
+
+
+def ivf_topk_tc(q: torch.Tensor, lm_vecs: torch.Tensor, lm_mirror: torch.Tensor, lm_stats: torch.Tensor,
+                lm_ids: Optional[torch.Tensor], k: int, n_probe: int, pair_rows: torch.Tensor, row_query: torch.Tensor,
+                row_list: torch.Tensor, centroids: torch.Tensor, unit_table: torch.Tensor,
+                list_stats: Optional[torch.Tensor] = None):
+    """List-major IVF search on the tensor-core pipeline (vdb_ivf_topk_tc).  ``list_stats`` f32 [K, 2]: per-list row bounds
+    (max |bf16(r)|, max |bf16(r) - r| over the list's residual rows r) that tighten the certificate.  Returns (dist f32 [Q,k], ids-or-positions i64
+    [Q,k], uncert i32 [Q+1] = count + indices of the queries the caller must re-run through ivf_scan)."""
+    q = _f32(q, "q")
+    Q, D = q.shape
+    N = lm_vecs.shape[0]
+    Qa = row_query.numel()
+    U = unit_table.shape[0]
+    dev = q.device
+    out_d = torch.empty((Q, k), dtype=torch.float32, device=dev)
+    out_i = torch.empty((Q, k), dtype=torch.int64, device=dev)
+    uncert = torch.empty((Q + 1,), dtype=torch.int32, device=dev)
+    lib = load()
+    nbytes = lib.vdb_ivf_topk_tc_workspace(Q, Qa, N, D, k, U)
+    if nbytes == 0:
+        raise ValueError(f"list-major IVF scan does not support Q={Q} N={N} D={D} k={k}")
+    ws = _ws("ivf_tc", nbytes, dev)
+    check(lib.vdb_ivf_topk_tc(ptr(q), Q, ptr(lm_vecs), ptr(lm_mirror), ptr(lm_stats), ptr(lm_ids), N, D, k, n_probe,
+                              ptr(pair_rows), ptr(row_query), ptr(row_list), ptr(_f32(centroids, "centroids")), Qa, ptr(unit_table), U,
+                              ptr(list_stats), ptr(out_d), ptr(out_i), ptr(uncert), ptr(ws), ws.numel(), _lib.stream_ptr(dev)))
+    return out_d, out_i, uncert
