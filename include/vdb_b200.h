@@ -194,6 +194,11 @@ int vdb_pq_encode_tc_supported(int64_t N, int D, int m, int K);
 size_t vdb_pq_encode_tc_workspace(int m);
 int vdb_pq_encode_tc(const float* x, int64_t N, int D, int m, int K, const float* codebooks, uint8_t* codes,
                      void* ws, size_t ws_bytes, void* stream);
+/* bench/debug only: 1 (default) = the f16-accumulator kernel, 0 = the fp32-accumulator kernel; counters of the last
+ * f16-accumulator call on workspace `ws`: out[0] = (row, sub-space) pairs the resolver warp decided, out[1] = of which
+ * with all-ones candidate masks, out[2] = pairs an epilogue lane resolved itself because the queue was full */
+void vdb_debug_set_pq_tc_mode(int mode);
+int vdb_debug_pq_tc_stats(const void* ws, int m, unsigned long long* out /*[host] 3*/, void* stream);
 
 /* ---- a12 PQ training (Lloyd iterations of scipy kmeans2 as called at pq.py:11) ------------------
  * One assignment + mean-update round for all m sub-spaces at once; an empty cluster keeps its

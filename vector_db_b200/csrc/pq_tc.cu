@@ -456,7 +456,27 @@ using namespace vdb;
 
 static size_t et_ws_operand(int m) { return (size_t)m * 256 * 8 * 4; }
 
+namespace vdb {
+int pq_encode_tc16_launch(const float* x, int64_t N, int D, int m, int K, const float* codebooks, uint8_t* codes, char* base,
+                          size_t operand_slab, size_t stats_off, cudaStream_t st);     // pq_tc16.cu
+}
+// 1 (default) = f16-accumulator kernel (pq_tc16.cu), 0 = the fp32-accumulator kernel of this file
+static int g_pq_tc_mode = 1;
+
 extern "C" {
+
+void vdb_debug_set_pq_tc_mode(int mode) { g_pq_tc_mode = mode; }
+
+// counters of the last f16-accumulator encode that used this workspace: out[0] = (row, sub-space) items the resolver warp
+// decided, out[1] = of which with all-ones masks (row out of f16 range), out[2] = pairs resolved by the epilogue lane itself
+// because the queue was full.  Synchronises the stream.
+int vdb_debug_pq_tc_stats(const void* ws, int m, unsigned long long* out, void* stream) {
+    VDB_REQUIRE(ws && out, VDB_ERR_INVALID, "vdb_debug_pq_tc_stats: null pointer");
+    const size_t off = 3 * et_ws_operand(m) + (((size_t)m * 4 + 255) & ~(size_t)255);
+    VDB_CUDA(cudaMemcpyAsync(out, static_cast<const char*>(ws) + off, 24, cudaMemcpyDeviceToHost, static_cast<cudaStream_t>(stream)));
+    VDB_CUDA(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
+    return VDB_OK;
+}
 
 int vdb_pq_encode_tc_supported(int64_t N, int D, int m, int K) {
     return (N > 0 && N < (1ll << 31) && m > 0 && D == 8 * m && K > 0 && K <= 256 && m <= 512) ? 1 : 0;
@@ -476,6 +496,9 @@ int vdb_pq_encode_tc(const float* x, int64_t N, int D, int m, int K, const float
                 VDB_ERR_INVALID, "rows / codebooks / workspace must be 16 / 16 / 256-byte aligned");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     char* base = static_cast<char*>(ws);
+    if (g_pq_tc_mode == 1)
+        return pq_encode_tc16_launch(x, N, D, m, K, codebooks, codes, base, et_ws_operand(m),
+                                     3 * et_ws_operand(m) + (((size_t)m * 4 + 255) & ~(size_t)255), st);
     uint32_t* opnd = reinterpret_cast<uint32_t*>(base);
     float* cmax = reinterpret_cast<float*>(base + 3 * et_ws_operand(m));
     pq_tc_operands_kernel<<<m, 256, 0, st>>>(codebooks, m, K, opnd, cmax);
