@@ -357,7 +357,7 @@ def path_pq_encode(dev, peaks, keep_codes=None):
                                f"(BASELINE.json configs[2], encode)", "codebooks": "10 Lloyd rounds on a 100k-row sample"},
         "metric": "vectors/s", "value": N / (total_ms * 1e-3), "unit": "vectors/s", "ms_per_step": total_ms / (N // CH),
         "ms_for_10M_rows": total_ms, "kernel": "pq_encode_tc_kernel", "kernel_ms": kernel_ms, "kernel_launches": n_launch,
-        "dtype": "bf16x3 split (exact) + fp32 resolve",
+        "dtype": "f16 split operands, f16 accumulators (candidates) + fp32 resolve (exact)",
         "roofline": _hbm_roofline(alg, kernel_ms, peaks, "pq_encode_tc_kernel", "rows x (4D + m) bytes per call",
                                   ncu_key="pq_encode_tc"),
         "cpu_baseline": {"value": nv / vec_dt, "unit": "vectors/s", "cores": 1, "kind": "port",

@@ -31,6 +31,11 @@ def run(mode):
     return codes, e0.elapsed_time(e1) / 5
 c0, t0 = run(0)
 c1, t1 = run(1)
+if len(sys.argv) > 6:
+    for dbg in (1, 3):
+        _, td = run(1 | (dbg << 4))
+        print(f'  debug bits {dbg & 255} hint {dbg >> 8} ns (1 = no epilogue work, 2 = no MMA, 4 = no split math, 8 = no row TMA): {td:.3f} ms', flush=True)
+    lib.vdb_debug_set_pq_tc_mode(1)
 st = (ctypes.c_ulonglong * 3)()
 ws = ops._ws("pq_encode_tc", lib.vdb_pq_encode_tc_workspace(m), x.device)
 _lib.check(lib.vdb_debug_pq_tc_stats(ctypes.c_void_p(ws.data_ptr()), m, st, None))

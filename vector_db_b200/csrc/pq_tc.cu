@@ -465,7 +465,7 @@ static int g_pq_tc_mode = 1;
 
 extern "C" {
 
-void vdb_debug_set_pq_tc_mode(int mode) { g_pq_tc_mode = mode; }
+void vdb_debug_set_pq_tc_mode(int mode) { g_pq_tc_mode = mode & 1; }
 
 // counters of the last f16-accumulator encode that used this workspace: out[0] = (row, sub-space) items the resolver warp
 // decided, out[1] = of which with all-ones masks (row out of f16 range), out[2] = pairs resolved by the epilogue lane itself

@@ -35,6 +35,26 @@
 // writers never touch the same byte and need no ordering).  Rows the f16 range cannot hold (S^2 |x|^2 > 30000, NaN) go
 // to the resolver with all-ones masks: correct, slow, and rare on data the codebook was trained for.
 //
+// Measured (2M x 384 rows, m = 48, K = 256, B200; scripts/dev_pq16.py times both kernels in one process): 2.24-2.30 ms
+// against 2.91 ms for pq_tc.cu on the same box, codes equal on all 96 M (also at scales 0.001 .. 30, K = 37 / 100, m = 13 /
+// 16, N not a multiple of anything), ~1.06 % of the (row, sub-space) pairs go through the resolver.  ncu: ALU pipe 45 %,
+// issue slots 48-76 % -- no pipe is the bound any more; an epilogue warp runs its ~370-instruction step at IPC 0.2.
+//
+// What the remaining time is (each measured by switching parts off, r02):
+//   * the ring itself -- TMA producer, split warps, MMA issuers and the accumulator hand-over with NO epilogue work, NO
+//     MMAs, NO split arithmetic and NO row loads still takes 0.9-1.4 ms: the step is so small (128 x 256 x 16 MACs, 128
+//     clocks of tensor time) that mbarrier round trips (release -> issuer wakes -> tcgen05.commit -> epilogue wakes) are
+//     of the order of the step.  Separate row / operand rings (the landing tile is free after the split, not after the
+//     MMA) and 4-tile rounds (half the codebook-operand traffic from L2: 6 -> 3 GB per call) are in, neither moved it;
+//   * the epilogue warps' own latency: two per scheduler cannot hide each other's dependent chains.  FOUR groups (each a
+//     128-column half of a stage, the halves of a step meeting through an 8-byte summary per row in shared memory, 768
+//     threads at 80 registers) measured 2.6 ms: 294 instructions per half-step instead of 370 per step, a quarter of them
+//     barrier probes, and the SM's issue slots 79 % full;
+//   * try_wait with a suspend-time hint (NANOSLEEP.SYNCS) takes the producers' probe loops off the schedulers (2.43 ->
+//     2.24 ms) but wakes late: on the epilogue's waits it costs 0.4 ms (3.1 ms), so the critical waits probe plainly.
+// TMEM reads are not the limit (scripts/ubench/ldtm.cu: packed x16 / x32 loads move 970-1250 B of TMEM cells per clock
+// and SM with two warps per sub-partition, a step needs 128 KB).
+//
 // Roofline: HBM, algorithmic bytes per vector = 4 D + m (rows read once, codes written once).
 #include <cuda.h>
 #include <cuda_fp16.h>
@@ -55,26 +75,33 @@ constexpr int kE16K = 256;                  // centroids per sub-space (UMMA N)
 constexpr int kE16XBytes = kE16Rows * 32;   // 4 KB: 128 rows x 8 fp32 (TMA landing tile, not swizzled)
 constexpr int kE16ABytes = kE16Rows * 32;   // 4 KB: 128 rows x 16 f16 (32-byte swizzle)
 constexpr int kE16BBytes = kE16K * 32;      // 8 KB: 256 centroids x 16 f16 (32-byte swizzle)
-constexpr int kE16XaBytes = kE16XBytes + 2 * kE16ABytes;     // x | A0 | A1  (12 KB per step)
+constexpr int kE16AsBytes = 2 * kE16ABytes;                  // A0 | A1  (8 KB per step)
 constexpr int kE16BsBytes = 2 * kE16BBytes;                  // B0 | B1  (16 KB per sub-space, shared by the two tiles of a pair)
-constexpr int kE16MaxXa = 16, kE16MaxBs = 8;
+constexpr int kE16MaxX = 32, kE16MaxA = 16, kE16MaxBs = 8;
+constexpr int kE16T = 4;                    // row tiles per round: the codebook operands of a sub-space are fetched once per round
 constexpr int kE16QCap = 512;               // resolver queue (16-byte items)
 constexpr float kE16Big = 60000.f;          // score of padding centroids / overflowing rows (f16 max 65504)
 constexpr float kE16Limit = 30000.f;        // a row minimum at or above this cannot be trusted: all-ones masks
 
 // Work order as in pq_tc.cu: a CTA takes PAIRS of row tiles and walks the sub-spaces j-major over the pair, so the codebook
 // operands of sub-space j are fetched once for two steps; step s uses accumulator stage s & 1 = its tile within the pair.
+// Three rings.  ROWS: the fp32 slice of a step as TMA lands it (4 KB), free again as soon as the split warp has read it;
+// OPERANDS: the step's two f16 A tiles (8 KB), free when its MMAs are done; CODEBOOK: B0 | B1 of a sub-space (16 KB, two
+// steps).  (One 12 KB slot per step for rows + operands held the landing tile through the split AND the MMA: the slot's
+// turn-around -- HBM latency + split + MMA, ~5800 clocks -- over 11 slots was 524 clocks per step, a 1.36 ms floor per
+// 2M x 384 rows with the epilogue and the MMAs switched off.)
 struct E16Smem {
-    int xa_off, bs_off, par_off, q_off, bar_off, total;
+    int x_off, as_off, bs_off, par_off, q_off, bar_off, total;
 };
-__host__ __device__ inline E16Smem e16_layout(int nxa, int nbs, int m) {
+__host__ __device__ inline E16Smem e16_layout(int nx, int na, int nbs, int m) {
     E16Smem L;
     L.bs_off = 0;                                              // 16 KB slots first: 1024-byte aligned
-    L.xa_off = nbs * kE16BsBytes;                              // 12 KB slots: 1024-byte aligned as well
-    L.par_off = L.xa_off + nxa * kE16XaBytes;                  // [m] float2 (scale S, S max|c|)
+    L.as_off = nbs * kE16BsBytes;                              // 8 KB slots: 1024-byte aligned as well
+    L.x_off = L.as_off + na * kE16AsBytes;                     // 4 KB slots
+    L.par_off = L.x_off + nx * kE16XBytes;                     // [m] float2 (scale S, S max|c|)
     L.q_off = (L.par_off + m * 8 + 15) & ~15;
     L.bar_off = L.q_off + kE16QCap * 16;
-    L.total = L.bar_off + (3 * kE16MaxXa + 2 * kE16MaxBs + 8) * 8 + 32;
+    L.total = L.bar_off + (2 * kE16MaxX + 2 * kE16MaxA + 2 * kE16MaxBs + 8) * 8 + 32;
     return L;
 }
 
@@ -239,6 +266,18 @@ __device__ __forceinline__ void fold_chunk16(const uint32_t (&v)[16], uint32_t (
     for (int i = 0; i < 8; ++i) B[i] = hmin3u(B[i], v[i], v[i + 8]);
 }
 
+// Same for a 128-column half (8 block minima): chunk CH of 4.
+template <int CH>
+__device__ __forceinline__ void fold_chunk8(const uint32_t (&v)[16], uint32_t (&A)[8], uint32_t (&B)[8]) {
+#pragma unroll
+    for (int b = 0; b < 2; ++b) {
+        const uint32_t* w = v + 8 * b;
+        A[2 * CH + b] = hmin2u(hmin3u(hmin3u(w[0], w[1], w[2]), hmin3u(w[3], w[4], w[5]), w[6]), w[7]);
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) B[i] = hmin3u(B[i], v[i], v[i + 8]);
+}
+
 // One 64-column chunk CH (32 packed registers = 4 blocks of 16 columns) folded into the two families: 32 instructions.
 template <int CH>
 __device__ __forceinline__ void fold_chunk16(const uint32_t (&v)[32], uint32_t (&A)[16], uint32_t (&B)[8]) {
@@ -317,20 +356,22 @@ __device__ __noinline__ int pq16_resolve(const float* __restrict__ xrow, const f
 __global__ void __launch_bounds__(kE16Threads, 1)
 pq_encode_tc16_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_b,
                       const float* __restrict__ x, int64_t N, int D, int m, int K, const float* __restrict__ cb,
-                      const float2* __restrict__ par, int nxa, int nbs, int64_t pairs, uint8_t* __restrict__ codes,
+                      const float2* __restrict__ par, int nx, int na, int nbs, int64_t rounds, uint8_t* __restrict__ codes,
                       unsigned long long* __restrict__ stats) {
     extern __shared__ __align__(1024) unsigned char smem[];
     if ((smem_u32(smem) & 1023u) != 0) __trap();
-    const E16Smem L = e16_layout(nxa, nbs, m);
-    unsigned char* sXa = smem + L.xa_off;
+    const E16Smem L = e16_layout(nx, na, nbs, m);
+    unsigned char* sX = smem + L.x_off;
+    unsigned char* sAs = smem + L.as_off;
     unsigned char* sBs = smem + L.bs_off;
     float2* sPar = reinterpret_cast<float2*>(smem + L.par_off);
     uint4* sQ = reinterpret_cast<uint4*>(smem + L.q_off);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L.bar_off);
-    uint64_t* x_full = bars;                        // [nxa]: TMA landed the fp32 row slice
-    uint64_t* a_full = bars + kE16MaxXa;            // [nxa]: A0 / A1 written by the step's split warp
-    uint64_t* xa_empty = bars + 2 * kE16MaxXa;      // [nxa]: the step's MMAs are done with A0 / A1
-    uint64_t* b_full = bars + 3 * kE16MaxXa;        // [nbs]: TMA landed B0, B1
+    uint64_t* x_full = bars;                        // [nx]: TMA landed the fp32 row slice
+    uint64_t* x_empty = bars + kE16MaxX;            // [nx]: the step's split warp has read it
+    uint64_t* a_full = bars + 2 * kE16MaxX;         // [na]: A0 / A1 written by the step's split warp
+    uint64_t* a_empty = a_full + kE16MaxA;          // [na]: the step's MMAs are done with A0 / A1
+    uint64_t* b_full = a_empty + kE16MaxA;          // [nbs]: TMA landed B0, B1
     uint64_t* b_empty = b_full + kE16MaxBs;         // [nbs]: the MMAs of BOTH steps of the sub-space are done
     uint64_t* tmem_full = b_empty + kE16MaxBs;      // [2 accumulator stages][2 column halves]
     uint64_t* tmem_empty = tmem_full + 4;           // [2][2]
@@ -339,6 +380,7 @@ pq_encode_tc16_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
     volatile uint32_t* q_tail = tmem_ptr + 2;       // items the resolver has taken
     volatile uint32_t* q_done = tmem_ptr + 3;       // epilogue groups that have finished
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t hint = 2000u;                                          // suspend-time hint of the producers' waits (ns)
 
     for (int i = threadIdx.x; i < m; i += kE16Threads) sPar[i] = par[i];
     for (int i = threadIdx.x; i < kE16QCap; i += kE16Threads) sQ[i] = make_uint4(0u, 0u, 0u, 0u);
@@ -347,8 +389,9 @@ pq_encode_tc16_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
         tma_prefetch_desc(&map_b);
     }
     if (warp == 1 && lane == 0) {
-        for (int i = 0; i < nxa; ++i) { mbar_init(&x_full[i], 1); mbar_init(&a_full[i], 1); mbar_init(&xa_empty[i], 1); }
-        for (int i = 0; i < nbs; ++i) { mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], 2); }
+        for (int i = 0; i < nx; ++i) { mbar_init(&x_full[i], 1); mbar_init(&x_empty[i], 1); }
+        for (int i = 0; i < na; ++i) { mbar_init(&a_full[i], 1); mbar_init(&a_empty[i], 1); }
+        for (int i = 0; i < nbs; ++i) { mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], kE16T); }
         for (int i = 0; i < 4; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 128); }
         *q_head = 0u; *q_tail = 0u; *q_done = 0u;
         fence_barrier_init();
@@ -364,21 +407,21 @@ pq_encode_tc16_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
         if (lane == 0) {
             int xs = 0, bs = 0;
             uint32_t xph = 0, bph = 0;
-            for (int64_t pair = blockIdx.x; pair < pairs; pair += gridDim.x) {
+            for (int64_t round = blockIdx.x; round < rounds; round += gridDim.x) {
                 for (int j = 0; j < m; ++j) {
-                    mbar_wait_relaxed(&b_empty[bs], bph ^ 1);
+                    mbar_wait_relaxed(&b_empty[bs], bph ^ 1, hint);
                     unsigned char* bb = sBs + (size_t)bs * kE16BsBytes;
                     mbar_expect_tx(&b_full[bs], (uint32_t)kE16BsBytes);
                     tma_load_2d(bb, &map_b, &b_full[bs], 0, (j * 2) * 256, kEvictLast);
                     tma_load_2d(bb + kE16BBytes, &map_b, &b_full[bs], 0, (j * 2 + 1) * 256, kEvictLast);
                     if (++bs == nbs) { bs = 0; bph ^= 1; }
 #pragma unroll
-                    for (int t = 0; t < 2; ++t) {
-                        mbar_wait_relaxed(&xa_empty[xs], xph ^ 1);
+                    for (int t = 0; t < kE16T; ++t) {
+                        mbar_wait_relaxed(&x_empty[xs], xph ^ 1, hint);
                         mbar_expect_tx(&x_full[xs], (uint32_t)kE16XBytes);
-                        // rows past N (a pair's missing second tile included) land as zeros and are never stored
-                        tma_load_2d(sXa + (size_t)xs * kE16XaBytes, &map_x, &x_full[xs], j * 8, (int)((pair * 2 + t) * kE16Rows), kEvictFirst);
-                        if (++xs == nxa) { xs = 0; xph ^= 1; }
+                        // rows past N (a round's missing tiles included) land as zeros and are never stored
+                        tma_load_2d(sX + (size_t)xs * kE16XBytes, &map_x, &x_full[xs], j * 8, (int)((round * kE16T + t) * kE16Rows), kEvictFirst);
+                        if (++xs == nx) { xs = 0; xph ^= 1; }
                     }
                 }
             }
@@ -388,18 +431,19 @@ pq_encode_tc16_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
         if (lane == 0) {
             const int as = warp - 1;
             const uint32_t idesc = make_idesc_f16_f16acc(kE16Rows, kE16K / 2);
-            int xs = as % nxa, bs = 0, aph = 0;        // own steps s = as, as + 2, ...: row slot s mod nxa, codebook slot (s / 2) mod nbs
+            int xs = as % na, bs = 0, aph = 0;         // own steps s = as, as + 2, ...: operand slot s mod na, codebook slot (s / T) mod nbs
             uint32_t xph = 0, bph = 0;
-            for (int64_t pair = blockIdx.x; pair < pairs; pair += gridDim.x) {
+            for (int64_t round = blockIdx.x; round < rounds; round += gridDim.x) {
                 for (int j = 0; j < m; ++j) {
-                    mbar_wait_relaxed(&b_full[bs], bph);
-                    mbar_wait_relaxed(&a_full[xs], xph);
-                    const uint32_t a0 = smem_u32(sXa + (size_t)xs * kE16XaBytes) + kE16XBytes;
+                    mbar_wait_relaxed(&b_full[bs], bph, hint);
+                  for (int u = as; u < kE16T; u += 2) {
+                    mbar_wait_relaxed(&a_full[xs], xph, hint);
+                    const uint32_t a0 = smem_u32(sAs + (size_t)xs * kE16AsBytes);
                     const uint32_t b0 = smem_u32(sBs + (size_t)bs * kE16BsBytes);
                     const uint64_t d_a0 = make_desc_k_sw32(a0), d_a1 = make_desc_k_sw32(a0 + kE16ABytes);
 #pragma unroll
                     for (int h = 0; h < 2; ++h) {
-                        mbar_wait_relaxed(&tmem_empty[as * 2 + h], aph ^ 1);
+                        mbar_wait(&tmem_empty[as * 2 + h], aph ^ 1);        // the hand-over is on the critical path: plain probing
                         tc_fence_after();
                         const uint32_t d_tmem = tmem_base + (uint32_t)(as * kE16K + h * (kE16K / 2));
                         const uint32_t boff = (uint32_t)(h * (kE16BBytes / 2));      // centroids 128 h .. 128 h + 127
@@ -407,11 +451,12 @@ pq_encode_tc16_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
                         umma_bf16(d_tmem, d_a1, make_desc_k_sw32(b0 + kE16BBytes + boff), idesc, 1u);     // + x1.c1 + |c|^2 + |x|^2
                         umma_commit(&tmem_full[as * 2 + h]);
                     }
-                    umma_commit(&xa_empty[xs]);
+                    umma_commit(&a_empty[xs]);
                     umma_commit(&b_empty[bs]);
                     aph ^= 1;
                     xs += 2;
-                    if (xs >= nxa) { xs -= nxa; xph ^= 1; }
+                    if (xs >= na) { xs -= na; xph ^= 1; }
+                  }
                     if (++bs == nbs) { bs = 0; bph ^= 1; }
                 }
             }
@@ -423,15 +468,17 @@ pq_encode_tc16_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
         // [0 | 0], [0 | 1 1 1 Big 0 0 0 0].  (One warp per row quarter of EVERY step serialised the ~600-clock
         // load -> convert -> store -> fence chain of a step: 2.6 ms per 2M x 384 rows.) =================
         const int w = warp - 12;
-        int xs = 0;
-        uint32_t xph = 0;
+        int xs = 0, as = 0;
+        uint32_t xph = 0, aph = 0;
         uint32_t step = 0;
-        for (int64_t pair = blockIdx.x; pair < pairs; pair += gridDim.x) {
-            for (int sidx = 0; sidx < 2 * m; ++sidx, ++step) {
+        for (int64_t round = blockIdx.x; round < rounds; round += gridDim.x) {
+            for (int sidx = 0; sidx < kE16T * m; ++sidx, ++step) {
                 if ((int)(step & 3u) == w) {
-                    const float S = sPar[sidx >> 1].x;
-                    mbar_wait_relaxed(&x_full[xs], xph);
-                    unsigned char* base = sXa + (size_t)xs * kE16XaBytes;
+                    const float S = sPar[sidx / kE16T].x;
+                    mbar_wait_relaxed(&a_empty[as], aph ^ 1, hint);      // the operand slot is free (the MMAs of its last use are done)
+                    mbar_wait_relaxed(&x_full[xs], xph, hint);
+                    const unsigned char* base = sX + (size_t)xs * kE16XBytes;
+                    unsigned char* abase = sAs + (size_t)as * kE16AsBytes;
 #pragma unroll
                     for (int it = 0; it < 4; ++it) {
                         const int r = it * 32 + lane;
@@ -455,7 +502,7 @@ pq_encode_tc16_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
                             q = p;
                             c = make_uint4(0x3C003C00u, pack_f16x2(1.f, kE16Big), 0u, 0u);
                         }
-                        unsigned char* a0 = base + kE16XBytes + r * 32;
+                        unsigned char* a0 = abase + r * 32;
                         *reinterpret_cast<uint4*>(a0 + (0u ^ sw)) = q;                      // A0 = [x2 | x1]
                         *reinterpret_cast<uint4*>(a0 + (16u ^ sw)) = p;
                         *reinterpret_cast<uint4*>(a0 + kE16ABytes + (0u ^ sw)) = p;         // A1 = [x1 | constants and |x|^2]
@@ -463,9 +510,10 @@ pq_encode_tc16_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
                     }
                     fence_proxy_async();               // generic-proxy writes -> visible to the MMA's async-proxy reads
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(&a_full[xs]);
+                    if (lane == 0) { mbar_arrive(&a_full[as]); mbar_arrive(&x_empty[xs]); }
                 }
-                if (++xs == nxa) { xs = 0; xph ^= 1; }
+                if (++xs == nx) { xs = 0; xph ^= 1; }
+                if (++as == na) { as = 0; aph ^= 1; }
             }
         }
     } else if (warp == 3) {
@@ -506,7 +554,7 @@ pq_encode_tc16_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
             if (n_full) atomicAdd(stats + 1, n_full);
         }
     } else {
-        // ================= epilogue: one thread per row; group eg owns accumulator stage eg = tile eg of every pair.
+        // ================= epilogue: one thread per row; group eg owns accumulator stage eg = tiles eg, eg + 2, .. of every round.
         // Software-pipelined by one step: the TAIL of step s (row minimum -> threshold -> candidate masks -> code / push:
         // ~170 mostly dependent instructions, 60 % of a warp's time when it ran after the fold) is spread in three
         // branch-free pieces between the TMEM loads and folds of step s + 1, which it does not depend on. =================
@@ -625,19 +673,20 @@ pq_encode_tc16_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
         Tail t;
         t.out = codes; t.row = 0u; t.j = 0; t.live = false; t.mA = 1u; t.mB = 1u; t.trust = false;
         t.th2 = 0u;
-        int64_t pair = blockIdx.x;
-        int j = 0;
-        // describes step (pair, j) as the pending one and moves on; returns false after the CTA's last step
+        int64_t round = blockIdx.x;
+        int j = 0, u = eg;
+        // describes step (round, j, tile u) as the pending one and moves on; returns false after the CTA's last step
         auto advance = [&](Tail& tt) -> bool {
-            const uint32_t row = (uint32_t)((pair * 2 + eg) * kE16Rows + rt);    // N < 2^31
+            const uint32_t row = (uint32_t)((round * kE16T + u) * kE16Rows + rt);    // N < 2^31
             tt.row = row;
             tt.j = j;
             tt.live = (int64_t)row < N;
             tt.out = codes + (size_t)row * m + j;
-            if (++j == m) { j = 0; pair += gridDim.x; }
-            return pair < pairs;
+            u += 2;
+            if (u >= kE16T) { u = eg; if (++j == m) { j = 0; round += gridDim.x; } }
+            return round < rounds;
         };
-        if (pair < pairs) {
+        if (round < rounds) {
             for (;;) {
                 step(A0, B0, A1, B1, t);                   // folds (pair, j) into A0 / B0, finishes the step before it
                 bool more = advance(t);
@@ -678,20 +727,21 @@ int pq_encode_tc16_launch(const float* x, int64_t N, int D, int m, int K, const 
     if (rc) return rc;
     rc = tma_map_2d(&map_b, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, opnd, 16, (uint64_t)m * 2 * 256, 32, 16, kE16K, CU_TENSOR_MAP_SWIZZLE_32B);
     if (rc) return rc;
-    // ring depths: 5 codebook slots (10 steps), as many row slots as shared memory allows
+    // ring depths: 4 codebook slots (8 steps), 10 operand slots, as many row slots as shared memory allows
     const int smem_max = max_smem_optin();
-    int nbs = 5, nxa = kE16MaxXa;
-    while (nxa > 4 && e16_layout(nxa, nbs, m).total + 1024 > smem_max) --nxa;
-    while (nbs > 2 && e16_layout(nxa, nbs, m).total + 1024 > smem_max) --nbs;
-    VDB_REQUIRE(e16_layout(nxa, nbs, m).total + 1024 <= smem_max, VDB_ERR_UNSUPPORTED, "m=%d does not fit shared memory", m);
-    const size_t smem = (size_t)e16_layout(nxa, nbs, m).total;
+    int nbs = 4, na = 10, nx = kE16MaxX;
+    while (nx > 8 && e16_layout(nx, na, nbs, m).total + 1024 > smem_max) --nx;
+    while (na > 4 && e16_layout(nx, na, nbs, m).total + 1024 > smem_max) --na;
+    while (nbs > 2 && e16_layout(nx, na, nbs, m).total + 1024 > smem_max) --nbs;
+    VDB_REQUIRE(e16_layout(nx, na, nbs, m).total + 1024 <= smem_max, VDB_ERR_UNSUPPORTED, "m=%d does not fit shared memory", m);
+    const size_t smem = (size_t)e16_layout(nx, na, nbs, m).total;
     const int64_t tiles = (N + kE16Rows - 1) / kE16Rows;
-    const int64_t pairs = (tiles + 1) / 2;
-    const int grid = (int)(pairs < sm_count() ? pairs : sm_count());
+    const int64_t rounds = (tiles + kE16T - 1) / kE16T;
+    const int grid = (int)(rounds < sm_count() ? rounds : sm_count());
     VDB_CUDA(cudaFuncSetAttribute(pq_encode_tc16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     {
         ProfScope prof(kProfPqEncode, st);
-        pq_encode_tc16_kernel<<<grid, kE16Threads, smem, st>>>(map_x, map_b, x, N, D, m, K, codebooks, par, nxa, nbs, pairs, codes, stats);
+        pq_encode_tc16_kernel<<<grid, kE16Threads, smem, st>>>(map_x, map_b, x, N, D, m, K, codebooks, par, nx, na, nbs, rounds, codes, stats);
     }
     count_launch(1);
     VDB_CUDA(cudaGetLastError());

@@ -53,6 +53,7 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 // epilogue): try_wait with a suspend-time hint, so the thread sleeps in hardware instead of re-issuing the probe every
 // ~30 clocks (measured in pq_tc16.cu: the spinning warps were 15 % of the SM's issued instructions).
 __device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity, uint32_t hint_ns = 2000u) {
+    if (hint_ns == 0xFFFFu) { mbar_wait(bar, parity); return; }      // plain probing
     uint32_t ok;
     do {
         asm volatile(
