@@ -185,3 +185,9 @@ def test_search_batches_streams_results_in_order_and_equal_to_search():
             np.testing.assert_array_equal(i, iw)
             np.testing.assert_array_equal(d, dw)
     assert list(idx.search_batches(iter([]), 10)) == []
+    # the blocking call takes pinned queries (tensor, or a numpy view of one) straight from the caller's buffer
+    pin = torch.from_numpy(batches[2]).pin_memory()
+    for src in (pin, pin.numpy()):
+        d, i = idx.search(src, 10)
+        np.testing.assert_array_equal(i, want[2][1])
+        np.testing.assert_array_equal(d, want[2][0])

@@ -459,13 +459,18 @@ static size_t et_ws_operand(int m) { return (size_t)m * 256 * 8 * 4; }
 namespace vdb {
 int pq_encode_tc16_launch(const float* x, int64_t N, int D, int m, int K, const float* codebooks, uint8_t* codes, char* base,
                           size_t operand_slab, size_t stats_off, cudaStream_t st);     // pq_tc16.cu
+extern int g_pq16_tiles, g_pq16_xhint;
 }
 // 1 (default) = f16-accumulator kernel (pq_tc16.cu), 0 = the fp32-accumulator kernel of this file
 static int g_pq_tc_mode = 1;
 
 extern "C" {
 
-void vdb_debug_set_pq_tc_mode(int mode) { g_pq_tc_mode = mode & 1; }
+void vdb_debug_set_pq_tc_mode(int mode) {      // bit 0: kernel; bits 4-7: row tiles per round (0 = keep); bit 8: row loads evict-first
+    g_pq_tc_mode = mode & 1;
+    if ((mode >> 4) & 15) vdb::g_pq16_tiles = ((mode >> 4) & 15) & ~1;
+    vdb::g_pq16_xhint = ((mode >> 8) & 1) ^ 1;      // bit 8 set: evict-first (the measured-worse setting)
+}
 
 // counters of the last f16-accumulator encode that used this workspace: out[0] = (row, sub-space) items the resolver warp
 // decided, out[1] = of which with all-ones masks (row out of f16 range), out[2] = pairs resolved by the epilogue lane itself

@@ -78,7 +78,6 @@ constexpr int kE16BBytes = kE16K * 32;      // 8 KB: 256 centroids x 16 f16 (32-
 constexpr int kE16AsBytes = 2 * kE16ABytes;                  // A0 | A1  (8 KB per step)
 constexpr int kE16BsBytes = 2 * kE16BBytes;                  // B0 | B1  (16 KB per sub-space, shared by the two tiles of a pair)
 constexpr int kE16MaxX = 32, kE16MaxA = 16, kE16MaxBs = 8;
-constexpr int kE16T = 4;                    // row tiles per round: the codebook operands of a sub-space are fetched once per round
 constexpr int kE16QCap = 512;               // resolver queue (16-byte items)
 constexpr float kE16Big = 60000.f;          // score of padding centroids / overflowing rows (f16 max 65504)
 constexpr float kE16Limit = 30000.f;        // a row minimum at or above this cannot be trusted: all-ones masks
@@ -357,7 +356,7 @@ __global__ void __launch_bounds__(kE16Threads, 1)
 pq_encode_tc16_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_b,
                       const float* __restrict__ x, int64_t N, int D, int m, int K, const float* __restrict__ cb,
                       const float2* __restrict__ par, int nx, int na, int nbs, int64_t rounds, uint8_t* __restrict__ codes,
-                      unsigned long long* __restrict__ stats) {
+                      unsigned long long* __restrict__ stats, int T, uint64_t x_hint) {
     extern __shared__ __align__(1024) unsigned char smem[];
     if ((smem_u32(smem) & 1023u) != 0) __trap();
     const E16Smem L = e16_layout(nx, na, nbs, m);
@@ -391,7 +390,7 @@ pq_encode_tc16_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
     if (warp == 1 && lane == 0) {
         for (int i = 0; i < nx; ++i) { mbar_init(&x_full[i], 1); mbar_init(&x_empty[i], 1); }
         for (int i = 0; i < na; ++i) { mbar_init(&a_full[i], 1); mbar_init(&a_empty[i], 1); }
-        for (int i = 0; i < nbs; ++i) { mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], kE16T); }
+        for (int i = 0; i < nbs; ++i) { mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], T); }
         for (int i = 0; i < 4; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 128); }
         *q_head = 0u; *q_tail = 0u; *q_done = 0u;
         fence_barrier_init();
@@ -415,12 +414,11 @@ pq_encode_tc16_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
                     tma_load_2d(bb, &map_b, &b_full[bs], 0, (j * 2) * 256, kEvictLast);
                     tma_load_2d(bb + kE16BBytes, &map_b, &b_full[bs], 0, (j * 2 + 1) * 256, kEvictLast);
                     if (++bs == nbs) { bs = 0; bph ^= 1; }
-#pragma unroll
-                    for (int t = 0; t < kE16T; ++t) {
+                    for (int t = 0; t < T; ++t) {
                         mbar_wait_relaxed(&x_empty[xs], xph ^ 1, hint);
                         mbar_expect_tx(&x_full[xs], (uint32_t)kE16XBytes);
                         // rows past N (a round's missing tiles included) land as zeros and are never stored
-                        tma_load_2d(sX + (size_t)xs * kE16XBytes, &map_x, &x_full[xs], j * 8, (int)((round * kE16T + t) * kE16Rows), kEvictFirst);
+                        tma_load_2d(sX + (size_t)xs * kE16XBytes, &map_x, &x_full[xs], j * 8, (int)((round * T + t) * kE16Rows), x_hint);
                         if (++xs == nx) { xs = 0; xph ^= 1; }
                     }
                 }
@@ -436,7 +434,7 @@ pq_encode_tc16_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
             for (int64_t round = blockIdx.x; round < rounds; round += gridDim.x) {
                 for (int j = 0; j < m; ++j) {
                     mbar_wait_relaxed(&b_full[bs], bph, hint);
-                  for (int u = as; u < kE16T; u += 2) {
+                  for (int u = as; u < T; u += 2) {
                     mbar_wait_relaxed(&a_full[xs], xph, hint);
                     const uint32_t a0 = smem_u32(sAs + (size_t)xs * kE16AsBytes);
                     const uint32_t b0 = smem_u32(sBs + (size_t)bs * kE16BsBytes);
@@ -472,9 +470,9 @@ pq_encode_tc16_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
         uint32_t xph = 0, aph = 0;
         uint32_t step = 0;
         for (int64_t round = blockIdx.x; round < rounds; round += gridDim.x) {
-            for (int sidx = 0; sidx < kE16T * m; ++sidx, ++step) {
+            for (int sidx = 0; sidx < T * m; ++sidx, ++step) {
                 if ((int)(step & 3u) == w) {
-                    const float S = sPar[sidx / kE16T].x;
+                    const float S = sPar[sidx / T].x;
                     mbar_wait_relaxed(&a_empty[as], aph ^ 1, hint);      // the operand slot is free (the MMAs of its last use are done)
                     mbar_wait_relaxed(&x_full[xs], xph, hint);
                     const unsigned char* base = sX + (size_t)xs * kE16XBytes;
@@ -677,13 +675,13 @@ pq_encode_tc16_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
         int j = 0, u = eg;
         // describes step (round, j, tile u) as the pending one and moves on; returns false after the CTA's last step
         auto advance = [&](Tail& tt) -> bool {
-            const uint32_t row = (uint32_t)((round * kE16T + u) * kE16Rows + rt);    // N < 2^31
+            const uint32_t row = (uint32_t)((round * T + u) * kE16Rows + rt);    // N < 2^31
             tt.row = row;
             tt.j = j;
             tt.live = (int64_t)row < N;
             tt.out = codes + (size_t)row * m + j;
             u += 2;
-            if (u >= kE16T) { u = eg; if (++j == m) { j = 0; round += gridDim.x; } }
+            if (u >= T) { u = eg; if (++j == m) { j = 0; round += gridDim.x; } }
             return round < rounds;
         };
         if (round < rounds) {
@@ -713,6 +711,11 @@ namespace vdb {
 
 // Workspace (shared with pq_tc.cu, vdb_pq_encode_tc_workspace): [0, 16 KB m) operands, [16 KB m, +8 m) par,
 // last 256 bytes: three 64-bit counters (items the resolver took, of which all-ones, items resolved in place: queue full).
+int g_pq16_tiles = 4;     // row tiles per round (even): the codebook operands of a sub-space are fetched once per round
+int g_pq16_xhint = 1;     // L2 hint of the row loads: 1 = evict normal, 0 = evict first (a 32-byte row slice shares its 64-byte DRAM
+                          // burst with the next sub-space's slice: evict-first lost it before its turn, 3.8 / 5.0 / 7.3 GB read per
+                          // 2M x 384 rows at 2 / 4 / 8 tiles per round against the algorithmic 3.07 GB; evict-normal reads 3.08 GB)
+
 int pq_encode_tc16_launch(const float* x, int64_t N, int D, int m, int K, const float* codebooks, uint8_t* codes, char* base,
                           size_t operand_slab, size_t stats_off, cudaStream_t st) {
     uint32_t* opnd = reinterpret_cast<uint32_t*>(base);
@@ -736,12 +739,13 @@ int pq_encode_tc16_launch(const float* x, int64_t N, int D, int m, int K, const 
     VDB_REQUIRE(e16_layout(nx, na, nbs, m).total + 1024 <= smem_max, VDB_ERR_UNSUPPORTED, "m=%d does not fit shared memory", m);
     const size_t smem = (size_t)e16_layout(nx, na, nbs, m).total;
     const int64_t tiles = (N + kE16Rows - 1) / kE16Rows;
-    const int64_t rounds = (tiles + kE16T - 1) / kE16T;
+    const int T = g_pq16_tiles;
+    const int64_t rounds = (tiles + T - 1) / T;
     const int grid = (int)(rounds < sm_count() ? rounds : sm_count());
     VDB_CUDA(cudaFuncSetAttribute(pq_encode_tc16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     {
         ProfScope prof(kProfPqEncode, st);
-        pq_encode_tc16_kernel<<<grid, kE16Threads, smem, st>>>(map_x, map_b, x, N, D, m, K, codebooks, par, nx, na, nbs, rounds, codes, stats);
+        pq_encode_tc16_kernel<<<grid, kE16Threads, smem, st>>>(map_x, map_b, x, N, D, m, K, codebooks, par, nx, na, nbs, rounds, codes, stats, T, g_pq16_xhint ? kEvictNormal : kEvictFirst);
     }
     count_launch(1);
     VDB_CUDA(cudaGetLastError());

@@ -71,22 +71,27 @@ class ExactIndex:
         return ops.exact_topk_f32(q, st.vecs, k, self.metric, ids=st.ids, row_mask=mask, n_rows=st.n)
 
     def search(self, queries: np.ndarray, k: int, filter_ids=None) -> Tuple[np.ndarray, np.ndarray]:
-        """Host in / host out, one blocking call: the queries go to pinned memory and on to the device in chunks (the
-        DMA of one chunk runs under the host copy of the next), the results come back through pinned buffers with one
-        synchronisation."""
-        q_host = np.ascontiguousarray(queries, dtype=np.float32).reshape(-1, self.dim)
-        nq = q_host.shape[0]
+        """Host in / host out, one blocking call.  Queries already in PINNED host memory (a pinned torch tensor, or a numpy
+        view of one) are copied to the device straight from there; pageable queries go through a pinned staging buffer in
+        chunks (the DMA of one chunk runs under the host copy of the next).  The results come back through pinned buffers
+        with one synchronisation."""
+        if isinstance(queries, torch.Tensor):
+            src = queries.detach().to(torch.float32).reshape(-1, self.dim).contiguous()
+        else:
+            src = torch.from_numpy(np.ascontiguousarray(queries, dtype=np.float32).reshape(-1, self.dim))
+        nq = src.shape[0]
         dev = self.store.device
-        if self._pin is None or self._pin.shape[0] < nq:
-            self._pin = torch.empty((max(nq, 64), self.dim), dtype=torch.float32).pin_memory()
-            self._pin_out = None
         q = torch.empty((nq, self.dim), dtype=torch.float32, device=dev)
-        src = torch.from_numpy(q_host)
-        step = max(256, -(-nq // 4))
-        for s in range(0, nq, step):
-            e = min(nq, s + step)
-            self._pin[s:e].copy_(src[s:e])
-            q[s:e].copy_(self._pin[s:e], non_blocking=True)
+        if src.is_pinned():
+            q.copy_(src, non_blocking=True)
+        else:
+            if self._pin is None or self._pin.shape[0] < nq:
+                self._pin = torch.empty((max(nq, 64), self.dim), dtype=torch.float32).pin_memory()
+            step = max(256, -(-nq // 4))
+            for s in range(0, nq, step):
+                e = min(nq, s + step)
+                self._pin[s:e].copy_(src[s:e])
+                q[s:e].copy_(self._pin[s:e], non_blocking=True)
         d, i = self.search_device(q, k, filter_ids)
         po = getattr(self, "_pin_out", None)
         if po is None or po[0].shape[0] < nq or po[0].shape[1] != k:
