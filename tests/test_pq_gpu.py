@@ -237,3 +237,34 @@ def test_pq_index_filter_ids(golden_dir):
     Dref, Iref = O.adc_scan_topk(g["codes"][keep], O.adc_lut(g["Y"][:8], cents), 10, ids=ids[keep])
     np.testing.assert_array_equal(I, Iref)
     np.testing.assert_array_equal(D, Dref)
+
+
+@pytest.mark.gpu
+def test_f16_accumulator_encode_equals_fp32_accumulator_kernel_and_handles_rows_outside_the_f16_range():
+    """The two tensor-core encoders (vdb_debug_set_pq_tc_mode 1 = f16 accumulators, the default; 0 = fp32 accumulators)
+    and the fp32 kernel agree code for code -- including rows whose scaled norm overflows f16 (resolver with all-ones
+    masks), rows of +-inf / NaN (numpy's argmin over all-NaN distances is 0), a single row, K = 1 and K = 2."""
+    from vector_db_b200 import _lib, ops
+    lib = _lib.load()
+    rng = np.random.default_rng(17)
+    try:
+        for n, m, K in ((7_000, 12, 256), (1, 5, 256), (300, 3, 1), (513, 7, 2)):
+            cb = rng.standard_normal((m, K, 8)).astype(np.float32)
+            X = rng.standard_normal((n, 8 * m)).astype(np.float32)
+            if n > 100:
+                X[3] *= 1e4                                   # far outside the codebook's range: S^2 |x|^2 > 30000
+                X[4] *= 1e18
+                X[5, :8] = np.nan
+                X[6, 8:16] = np.inf
+                X[7] = 0.0
+            got = {}
+            for mode in (1, 0):
+                lib.vdb_debug_set_pq_tc_mode(mode)
+                got[mode] = ops.pq_encode(_t(X), _t(cb), engine="tc").cpu().numpy()
+            f32 = ops.pq_encode(_t(X), _t(cb), engine="f32").cpu().numpy()
+            np.testing.assert_array_equal(got[1], f32)
+            np.testing.assert_array_equal(got[0], f32)
+            with np.errstate(all="ignore"):
+                np.testing.assert_array_equal(got[1][:64], O.pq_encode(X[:64], list(cb)))
+    finally:
+        lib.vdb_debug_set_pq_tc_mode(1)
