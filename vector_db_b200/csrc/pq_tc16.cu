@@ -69,7 +69,8 @@ namespace vdb {
 
 using namespace sm100;
 
-constexpr int kE16Threads = 512;            // warp 0 TMA, 1-2 MMA issuers (2: TMEM alloc), 3 resolver, 4-7 / 8-11 epilogue groups, 12-15 operand split
+constexpr int kE16Groups = 3;                // epilogue groups, taking the CTA's steps in turn (step s: group s mod 3, stage s & 1)
+constexpr int kE16Threads = 128 + 128 * kE16Groups + 128;   // warp 0 TMA, 1-2 MMA issuers (2: TMEM alloc), 3 resolver, then the epilogue groups, then 4 split warps
 constexpr int kE16Rows = 128;               // rows per tile (UMMA M)
 constexpr int kE16K = 256;                  // centroids per sub-space (UMMA N)
 constexpr int kE16XBytes = kE16Rows * 32;   // 4 KB: 128 rows x 8 fp32 (TMA landing tile, not swizzled)
@@ -77,7 +78,7 @@ constexpr int kE16ABytes = kE16Rows * 32;   // 4 KB: 128 rows x 16 f16 (32-byte 
 constexpr int kE16BBytes = kE16K * 32;      // 8 KB: 256 centroids x 16 f16 (32-byte swizzle)
 constexpr int kE16AsBytes = 2 * kE16ABytes;                  // A0 | A1  (8 KB per step)
 constexpr int kE16BsBytes = 2 * kE16BBytes;                  // B0 | B1  (16 KB per sub-space, shared by the two tiles of a pair)
-constexpr int kE16MaxX = 32, kE16MaxA = 16, kE16MaxBs = 8;
+constexpr int kE16MaxX = 32, kE16MaxA = 15, kE16MaxBs = 8;   // operand slots <= 15: see the full barriers' second use
 constexpr int kE16QCap = 512;               // resolver queue (16-byte items)
 constexpr float kE16Big = 60000.f;          // score of padding centroids / overflowing rows (f16 max 65504)
 constexpr float kE16Limit = 30000.f;        // a row minimum at or above this cannot be trusted: all-ones masks
@@ -100,7 +101,7 @@ __host__ __device__ inline E16Smem e16_layout(int nx, int na, int nbs, int m) {
     L.par_off = L.x_off + nx * kE16XBytes;                     // [m] float2 (scale S, S max|c|)
     L.q_off = (L.par_off + m * 8 + 15) & ~15;
     L.bar_off = L.q_off + kE16QCap * 16;
-    L.total = L.bar_off + (2 * kE16MaxX + 2 * kE16MaxA + 2 * kE16MaxBs + 8) * 8 + 32;
+    L.total = L.bar_off + (2 * kE16MaxX + 2 * kE16MaxA + 2 * kE16MaxBs + 20) * 8 + 32;
     return L;
 }
 
@@ -369,12 +370,19 @@ pq_encode_tc16_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
     uint64_t* x_full = bars;                        // [nx]: TMA landed the fp32 row slice
     uint64_t* x_empty = bars + kE16MaxX;            // [nx]: the step's split warp has read it
     uint64_t* a_full = bars + 2 * kE16MaxX;         // [na]: A0 / A1 written by the step's split warp
-    uint64_t* a_empty = a_full + kE16MaxA;          // [na]: the step's MMAs are done with A0 / A1
+    uint64_t* a_empty = a_full + kE16MaxA;          // (unused: the stage's full barrier of the step frees the slot)
     uint64_t* b_full = a_empty + kE16MaxA;          // [nbs]: TMA landed B0, B1
     uint64_t* b_empty = b_full + kE16MaxBs;         // [nbs]: the MMAs of BOTH steps of the sub-space are done
-    uint64_t* tmem_full = b_empty + kE16MaxBs;      // [2 accumulator stages][2 column halves]
-    uint64_t* tmem_empty = tmem_full + 4;           // [2][2]
-    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 4);
+    // EIGHT "full" barriers per stage, used by the stage's uses in turn.  A parity wait is only right when the barrier
+    // is at most one phase behind the awaited one.  With three groups taking the steps in turn, the group that waits for use
+    // u of a stage last consumed use u - 3 of it, so uses up to u - 3 have been produced -- but u - 1 and u - 2 (other
+    // groups' steps) may still be pending: with one barrier per stage the wait for use u then passes on the completion of
+    // use u - 2 (same parity).  With several barriers the same-parity predecessor is many uses back, long produced.  The
+    // same barrier tells the split warps that the step's operand slot is free again (na <= 15 steps later, before the
+    // barrier's next use 16 steps later can complete).
+    uint64_t* tmem_full = b_empty + kE16MaxBs;      // [2 accumulator stages][use & 7]
+    uint64_t* tmem_empty = tmem_full + 16;          // [2]
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 2);
     volatile uint32_t* q_head = tmem_ptr + 1;       // items pushed so far
     volatile uint32_t* q_tail = tmem_ptr + 2;       // items the resolver has taken
     volatile uint32_t* q_done = tmem_ptr + 3;       // epilogue groups that have finished
@@ -389,9 +397,10 @@ pq_encode_tc16_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
     }
     if (warp == 1 && lane == 0) {
         for (int i = 0; i < nx; ++i) { mbar_init(&x_full[i], 1); mbar_init(&x_empty[i], 1); }
-        for (int i = 0; i < na; ++i) { mbar_init(&a_full[i], 1); mbar_init(&a_empty[i], 1); }
-        for (int i = 0; i < nbs; ++i) { mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], T); }
-        for (int i = 0; i < 4; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 128); }
+        for (int i = 0; i < na; ++i) mbar_init(&a_full[i], 1);
+        for (int i = 0; i < nbs; ++i) { mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], 2); }
+        for (int i = 0; i < 16; ++i) mbar_init(&tmem_full[i], 1);
+        for (int i = 0; i < 2; ++i) mbar_init(&tmem_empty[i], 4);
         *q_head = 0u; *q_tail = 0u; *q_done = 0u;
         fence_barrier_init();
     }
@@ -428,7 +437,8 @@ pq_encode_tc16_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
         // ================= MMA issuers: warp 1 owns accumulator stage 0 (tile 0 of every pair), warp 2 stage 1 =================
         if (lane == 0) {
             const int as = warp - 1;
-            const uint32_t idesc = make_idesc_f16_f16acc(kE16Rows, kE16K / 2);
+            const uint32_t idesc = make_idesc_f16_f16acc(kE16Rows, kE16K);
+            uint32_t use = 0u;                         // own steps so far = use number of the stage
             int xs = as % na, bs = 0, aph = 0;         // own steps s = as, as + 2, ...: operand slot s mod na, codebook slot (s / T) mod nbs
             uint32_t xph = 0, bph = 0;
             for (int64_t round = blockIdx.x; round < rounds; round += gridDim.x) {
@@ -439,19 +449,20 @@ pq_encode_tc16_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
                     const uint32_t a0 = smem_u32(sAs + (size_t)xs * kE16AsBytes);
                     const uint32_t b0 = smem_u32(sBs + (size_t)bs * kE16BsBytes);
                     const uint64_t d_a0 = make_desc_k_sw32(a0), d_a1 = make_desc_k_sw32(a0 + kE16ABytes);
-#pragma unroll
-                    for (int h = 0; h < 2; ++h) {
-                        mbar_wait(&tmem_empty[as * 2 + h], aph ^ 1);        // the hand-over is on the critical path: plain probing
-                        tc_fence_after();
-                        const uint32_t d_tmem = tmem_base + (uint32_t)(as * kE16K + h * (kE16K / 2));
-                        const uint32_t boff = (uint32_t)(h * (kE16BBytes / 2));      // centroids 128 h .. 128 h + 127
-                        umma_bf16(d_tmem, d_a0, make_desc_k_sw32(b0 + boff), idesc, 0u);                  // x2.c1 + x1.c2 (small, first)
-                        umma_bf16(d_tmem, d_a1, make_desc_k_sw32(b0 + kE16BBytes + boff), idesc, 1u);     // + x1.c1 + |c|^2 + |x|^2
-                        umma_commit(&tmem_full[as * 2 + h]);
+                    // ONE hand-over per step: the issuing thread's own latency (every mbarrier probe, tcgen05.mma and
+                    // tcgen05.commit is a ~50-100 clock trip for a single thread) was the ring's floor with two 128-column
+                    // halves per step -- 13 such operations per step and issuer, ~500 clocks per step of the CTA
+                    mbar_wait(&tmem_empty[as], aph ^ 1);        // the hand-over is on the critical path: plain probing
+                    tc_fence_after();
+                    {
+                        const uint32_t d_tmem = tmem_base + (uint32_t)(as * kE16K);
+                        umma_bf16(d_tmem, d_a0, make_desc_k_sw32(b0), idesc, 0u);                      // x2.c1 + x1.c2 (small, first)
+                        umma_bf16(d_tmem, d_a1, make_desc_k_sw32(b0 + kE16BBytes), idesc, 1u);         // + x1.c1 + |c|^2 + |x|^2
+                        umma_commit(&tmem_full[as * 8 + (int)(use & 7u)]);     // also frees the step's operand slot (split warps)
                     }
-                    umma_commit(&a_empty[xs]);
-                    umma_commit(&b_empty[bs]);
+                    if (u + 2 >= T) umma_commit(&b_empty[bs]);                   // this issuer's last step on the sub-space
                     aph ^= 1;
+                    ++use;
                     xs += 2;
                     if (xs >= na) { xs -= na; xph ^= 1; }
                   }
@@ -459,13 +470,13 @@ pq_encode_tc16_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
                 }
             }
         }
-    } else if (warp >= 12) {
+    } else if (warp >= 4 + 4 * kE16Groups) {
         // ================= operand split: warp 12 + w converts steps s = w (mod 4), all 128 rows (four rows per lane, their
         // dependency chains interleave):  v = S x;  x1 = f16(v), x2 = f16(v - x1);  X = 3-way f16 split of |v|^2;
         // A0 row = [x2 | x1], A1 row = [x1 | 1 1 1 X1 X2 X3 0 0].  A row the f16 range cannot hold becomes
         // [0 | 0], [0 | 1 1 1 Big 0 0 0 0].  (One warp per row quarter of EVERY step serialised the ~600-clock
         // load -> convert -> store -> fence chain of a step: 2.6 ms per 2M x 384 rows.) =================
-        const int w = warp - 12;
+        const int w = warp - (4 + 4 * kE16Groups);
         int xs = 0, as = 0;
         uint32_t xph = 0, aph = 0;
         uint32_t step = 0;
@@ -473,7 +484,10 @@ pq_encode_tc16_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
             for (int sidx = 0; sidx < T * m; ++sidx, ++step) {
                 if ((int)(step & 3u) == w) {
                     const float S = sPar[sidx / T].x;
-                    mbar_wait_relaxed(&a_empty[as], aph ^ 1, hint);      // the operand slot is free (the MMAs of its last use are done)
+                    if (step >= (uint32_t)na) {                    // the operand slot is free: the MMAs of step - na are done
+                        const uint32_t prev = step - (uint32_t)na, puse = prev >> 1;
+                        mbar_wait_relaxed(&tmem_full[(prev & 1u) * 8u + (puse & 7u)], (puse >> 3) & 1u, hint);
+                    }
                     mbar_wait_relaxed(&x_full[xs], xph, hint);
                     const unsigned char* base = sX + (size_t)xs * kE16XBytes;
                     unsigned char* abase = sAs + (size_t)as * kE16AsBytes;
@@ -524,7 +538,7 @@ pq_encode_tc16_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
             const uint32_t avail = head - tail;
             // whole batches of 32 (a call of the resolve routine costs the same ~1000 warp instructions for 1 item or 32 --
             // polling for single items made this warp 24 % of the SM's issued instructions); the rest when both groups are done
-            if (avail < 32u && done != 2u) { __nanosleep(512); continue; }
+            if (avail < 32u && done != (uint32_t)kE16Groups) { __nanosleep(512); continue; }
             if (avail == 0u) break;                    // `done` was read BEFORE `head`: nothing can arrive after both groups finished
             const uint32_t n = avail < 32u ? avail : 32u;
             uint4 it = make_uint4(0u, 0u, 0u, 0u);
@@ -559,8 +573,7 @@ pq_encode_tc16_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
         const int eg = (warp - 4) >> 2;
         const int ew = warp & 3;
         const int rt = ew * 32 + lane;                 // row within the tile == TMEM lane
-        const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(eg * kE16K);
-        int phase = 0;
+        const uint32_t taddr0 = tmem_base + ((uint32_t)(ew * 32) << 16);
 
         struct Tail {                                  // state of the step whose tail is pending
             uint8_t* out;                              // its code byte
@@ -631,68 +644,50 @@ pq_encode_tc16_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
                 }
             }
         };
-        // one step: fold its 256 packed scores into (A, B) while the tail of the previous step (Ap, Bp, t) completes
-        auto step = [&](uint32_t (&A)[16], uint32_t (&B)[8], const uint32_t (&Ap)[16], const uint32_t (&Bp)[8], Tail& t) {
-            uint32_t va[16], vb[16];
+        // Group eg takes the CTA's steps s = eg, eg + 3, ...; step s lives in accumulator stage s & 1 (its use number s >> 1
+        // gives the barrier parity).  A group releases each half of the stage as soon as the half is in registers, so the
+        // stage is refilled for step s + 2 (another group's) while this group is still in its tail.
+        Tail t;
+        t.th2 = 0u; t.mA = t.mB = 1u; t.trust = false;
+        int64_t round = blockIdx.x;
+        int j = 0, u = eg;                             // step = (round, sub-space j, tile u of the round)
+        while (u >= T) { u -= T; ++j; }
+        while (j >= m) { j -= m; round += gridDim.x; }
+        for (uint32_t sidx = (uint32_t)eg; round < rounds; sidx += (uint32_t)kE16Groups) {
+            const int st = (int)(sidx & 1u);
+            const uint32_t use = sidx >> 1, ph = (use >> 3) & 1u;      // use number of the stage; its barrier serves every eighth use
+            const uint32_t ta = taddr0 + (uint32_t)(st * kE16K);
+            uint32_t va[16], vb[16], A[16], B[8];
 #pragma unroll
             for (int i = 0; i < 8; ++i) B[i] = kInf2;
-            mbar_wait(&tmem_full[eg * 2], phase);
+            mbar_wait(&tmem_full[st * 8 + (int)(use & 7u)], ph);
             tc_fence_after();
             // eight 32-column chunks, two 16-register buffers (tcgen05.wait::ld waits for ALL outstanding loads, so exactly
             // one is outstanding at every wait)
-            tmem_ld_x16_pack16(taddr, va);
-            tail1(Ap, t);
-            tmem_ld_wait_u(va); tmem_ld_x16_pack16(taddr + 32u, vb); fold_chunk16<0>(va, A, B);
-            tmem_ld_wait_u(vb); tmem_ld_x16_pack16(taddr + 64u, va); fold_chunk16<1>(vb, A, B);
-            tail2(Ap, Bp, t);
-            tmem_ld_wait_u(va); tmem_ld_x16_pack16(taddr + 96u, vb); fold_chunk16<2>(va, A, B);
+            tmem_ld_x16_pack16(ta, va);
+            tmem_ld_wait_u(va); tmem_ld_x16_pack16(ta + 32u, vb); fold_chunk16<0>(va, A, B);
+            tmem_ld_wait_u(vb); tmem_ld_x16_pack16(ta + 64u, va); fold_chunk16<1>(vb, A, B);
+            tmem_ld_wait_u(va); tmem_ld_x16_pack16(ta + 96u, vb); fold_chunk16<2>(va, A, B);
+            tmem_ld_wait_u(vb); tmem_ld_x16_pack16(ta + 128u, va); fold_chunk16<3>(vb, A, B);
+            tmem_ld_wait_u(va); tmem_ld_x16_pack16(ta + 160u, vb); fold_chunk16<4>(va, A, B);
+            tmem_ld_wait_u(vb); tmem_ld_x16_pack16(ta + 192u, va); fold_chunk16<5>(vb, A, B);
+            tmem_ld_wait_u(va); tmem_ld_x16_pack16(ta + 224u, vb); fold_chunk16<6>(va, A, B);
             tmem_ld_wait_u(vb);
             tc_fence_before();
-            mbar_arrive(&tmem_empty[eg * 2]);              // columns 0..127 are in registers
-            mbar_wait(&tmem_full[eg * 2 + 1], phase);
-            phase ^= 1;
-            tc_fence_after();
-            tmem_ld_x16_pack16(taddr + 128u, va); fold_chunk16<3>(vb, A, B);
-            tmem_ld_wait_u(va); tmem_ld_x16_pack16(taddr + 160u, vb); fold_chunk16<4>(va, A, B);
-            tmem_ld_wait_u(vb); tmem_ld_x16_pack16(taddr + 192u, va); fold_chunk16<5>(vb, A, B);
-            tmem_ld_wait_u(va); tmem_ld_x16_pack16(taddr + 224u, vb); fold_chunk16<6>(va, A, B);
-            tmem_ld_wait_u(vb);
-            tc_fence_before();
-            mbar_arrive(&tmem_empty[eg * 2 + 1]);          // columns 128..255 are in registers
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tmem_empty[st]);   // the step's 256 columns are in this warp's registers
             fold_chunk16<7>(vb, A, B);
-            tail3(t);
-        };
-
-        uint32_t A0[16], B0[8], A1[16], B1[8];
-#pragma unroll
-        for (int i = 0; i < 16; ++i) A1[i] = kInf2;
-#pragma unroll
-        for (int i = 0; i < 8; ++i) B1[i] = kInf2;
-        Tail t;
-        t.out = codes; t.row = 0u; t.j = 0; t.live = false; t.mA = 1u; t.mB = 1u; t.trust = false;
-        t.th2 = 0u;
-        int64_t round = blockIdx.x;
-        int j = 0, u = eg;
-        // describes step (round, j, tile u) as the pending one and moves on; returns false after the CTA's last step
-        auto advance = [&](Tail& tt) -> bool {
             const uint32_t row = (uint32_t)((round * T + u) * kE16Rows + rt);    // N < 2^31
-            tt.row = row;
-            tt.j = j;
-            tt.live = (int64_t)row < N;
-            tt.out = codes + (size_t)row * m + j;
-            u += 2;
-            if (u >= T) { u = eg; if (++j == m) { j = 0; round += gridDim.x; } }
-            return round < rounds;
-        };
-        if (round < rounds) {
-            for (;;) {
-                step(A0, B0, A1, B1, t);                   // folds (pair, j) into A0 / B0, finishes the step before it
-                bool more = advance(t);
-                if (!more) { tail1(A0, t); tail2(A0, B0, t); tail3(t); break; }
-                step(A1, B1, A0, B0, t);
-                more = advance(t);
-                if (!more) { tail1(A1, t); tail2(A1, B1, t); tail3(t); break; }
-            }
+            t.row = row;
+            t.j = j;
+            t.live = (int64_t)row < N;
+            t.out = codes + (size_t)row * m + j;
+            tail1(A, t);
+            tail2(A, B, t);
+            tail3(t);
+            u += kE16Groups;
+            while (u >= T) { u -= T; ++j; }
+            while (j >= m) { j -= m; round += gridDim.x; }
         }
         __threadfence_block();
         named_bar_sync(1 + eg, 128);
