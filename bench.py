@@ -356,10 +356,10 @@ def path_pq_encode(dev, peaks, keep_codes=None):
         "config": {"workload": f"PQ encode m={m} nbits=8, {N} x {D} fp32 rows in {N // CH} calls of {CH} rows "
                                f"(BASELINE.json configs[2], encode)", "codebooks": "10 Lloyd rounds on a 100k-row sample"},
         "metric": "vectors/s", "value": N / (total_ms * 1e-3), "unit": "vectors/s", "ms_per_step": total_ms / (N // CH),
-        "ms_for_10M_rows": total_ms, "kernel": "pq_encode_tc_kernel", "kernel_ms": kernel_ms, "kernel_launches": n_launch,
+        "ms_for_10M_rows": total_ms, "kernel": "pq_encode_tc16_kernel", "kernel_ms": kernel_ms, "kernel_launches": n_launch,
         "dtype": "f16 split operands, f16 accumulators (candidates) + fp32 resolve (exact)",
-        "roofline": _hbm_roofline(alg, kernel_ms, peaks, "pq_encode_tc_kernel", "rows x (4D + m) bytes per call",
-                                  ncu_key="pq_encode_tc"),
+        "roofline": _hbm_roofline(alg, kernel_ms, peaks, "pq_encode_tc16_kernel", "rows x (4D + m) bytes per call",
+                                  ncu_key="pq_encode_tc16"),
         "cpu_baseline": {"value": nv / vec_dt, "unit": "vectors/s", "cores": 1, "kind": "port",
                          "sample": f"oracle.pq_encode (vectorised numpy restatement) on {nv} rows, {vec_dt:.2f} s; the "
                                    f"reference's own per-row loop (oracle.pq_encode_loop, pq.py:82-89) on 200 rows: "

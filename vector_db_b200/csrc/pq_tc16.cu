@@ -35,25 +35,33 @@
 // writers never touch the same byte and need no ordering).  Rows the f16 range cannot hold (S^2 |x|^2 > 30000, NaN) go
 // to the resolver with all-ones masks: correct, slow, and rare on data the codebook was trained for.
 //
-// Measured (2M x 384 rows, m = 48, K = 256, B200; scripts/dev_pq16.py times both kernels in one process): 2.24-2.30 ms
-// against 2.91 ms for pq_tc.cu on the same box, codes equal on all 96 M (also at scales 0.001 .. 30, K = 37 / 100, m = 13 /
-// 16, N not a multiple of anything), ~1.06 % of the (row, sub-space) pairs go through the resolver.  ncu: ALU pipe 45 %,
-// issue slots 48-76 % -- no pipe is the bound any more; an epilogue warp runs its ~370-instruction step at IPC 0.2.
+// Measured (2M x 384 rows, m = 48, K = 256, B200; scripts/dev_pq16.py times both kernels in one process): 2.05 ms against
+// 2.91 ms for pq_tc.cu on the same box, codes equal on all 96 M (also at scales 0.001 .. 30, K = 5 / 37 / 100, m = 1 / 13 / 16, N
+// not a multiple of anything), ~1.06 % of the (row, sub-space) pairs go through the resolver, DRAM read 3.08 GB = the
+// algorithmic bytes.  ncu: no pipe is the bound (ALU ~45 %); the SM's issue slots are ~70 % full and an epilogue warp runs
+// its ~430-instruction step at IPC 0.15.
 //
-// What the remaining time is (each measured by switching parts off, r02):
-//   * the ring itself -- TMA producer, split warps, MMA issuers and the accumulator hand-over with NO epilogue work, NO
-//     MMAs, NO split arithmetic and NO row loads still takes 0.9-1.4 ms: the step is so small (128 x 256 x 16 MACs, 128
-//     clocks of tensor time) that mbarrier round trips (release -> issuer wakes -> tcgen05.commit -> epilogue wakes) are
-//     of the order of the step.  Separate row / operand rings (the landing tile is free after the split, not after the
-//     MMA) and 4-tile rounds (half the codebook-operand traffic from L2: 6 -> 3 GB per call) are in, neither moved it;
-//   * the epilogue warps' own latency: two per scheduler cannot hide each other's dependent chains.  FOUR groups (each a
-//     128-column half of a stage, the halves of a step meeting through an 8-byte summary per row in shared memory, 768
-//     threads at 80 registers) measured 2.6 ms: 294 instructions per half-step instead of 370 per step, a quarter of them
-//     barrier probes, and the SM's issue slots 79 % full;
-//   * try_wait with a suspend-time hint (NANOSLEEP.SYNCS) takes the producers' probe loops off the schedulers (2.43 ->
-//     2.24 ms) but wakes late: on the epilogue's waits it costs 0.4 ms (3.1 ms), so the critical waits probe plainly.
-// TMEM reads are not the limit (scripts/ubench/ldtm.cu: packed x16 / x32 loads move 970-1250 B of TMEM cells per clock
-// and SM with two warps per sub-partition, a step needs 128 KB).
+// How it got there, each step measured (r02):
+//   2.63 first version (two epilogue groups, one per stage; split = one warp per row quarter of every step)
+//   2.51 x16 TMEM loads instead of x32 (no spills in the loop), the resolver takes whole batches of 32
+//   2.43 the tail of step s software-pipelined into the folds of step s + 1
+//   2.24 producers wait with a suspend-time hint (their probe loops were 15 % of the issued instructions); packed compare
+//        (HSET2) instead of the saturating-FMA indicator
+//   2.15 THREE epilogue groups taking the steps in turn (step s: group s mod 3, stage s & 1), no software pipelining (96
+//        registers at 640 threads).  A parity wait is only right when the barrier is at most one phase behind: with one
+//        "full" barrier per stage the wait for use u passed on the completion of use u - 2 and the kernel dead-locked
+//        after a few rounds -- eight barriers per stage, used in turn
+//   2.05 ONE accumulator hand-over per step (two N = 256 MMAs, one commit) instead of two 128-column halves: every
+//        mbarrier probe / tcgen05.mma / tcgen05.commit is a ~50-100 clock trip for the single issuing thread
+// Measured and NOT kept: four groups, each a 128-column half of a stage, the halves of a step meeting through an 8-byte
+// summary per row in shared memory (2.6 ms: 294 instructions per half-step, a quarter of them barrier probes); four groups
+// in turn (2.24 ms: 80 registers, spills); hinted waits on the epilogue's own barriers (3.1 ms: late wake-ups); dropping the
+// per-step commits of the operand / codebook slots (no change -- the step's "full" barrier frees the operand slot now).
+// With the epilogue, the MMAs, the split arithmetic and the row loads all switched off the ring alone took 0.9-1.4 ms:
+// the step is 128 clocks of tensor time, so barrier round trips are of the order of the step.  Row slices are loaded
+// L2-evict-normal: a 32-byte slice shares its 64-byte DRAM burst with the next sub-space's slice, and evict-first lost
+// it before its turn (5.0 GB read instead of 3.08).  TMEM reads are not the limit (scripts/ubench/ldtm.cu: packed x16 /
+// x32 loads move 970-1250 B of TMEM cells per clock and SM with two warps per sub-partition, a step needs 128 KB).
 //
 // Roofline: HBM, algorithmic bytes per vector = 4 D + m (rows read once, codes written once).
 #include <cuda.h>
@@ -214,30 +222,7 @@ __device__ __forceinline__ uint32_t hadd2u(uint32_t a, uint32_t b) {
 }
 constexpr uint32_t kInf2 = 0x7C007C00u;     // (+inf, +inf)
 
-// 32 lanes x 64 consecutive f16 accumulator columns -> 32 registers of packed pairs (column 2i low, 2i+1 high)
-__device__ __forceinline__ void tmem_ld_x32_pack16(uint32_t taddr, uint32_t (&r)[32]) {
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x32.pack::16b.b32 "
-        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
-          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
-          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-        : "r"(taddr)
-        : "memory");
-}
-__device__ __forceinline__ void tmem_ld_wait_u(uint32_t (&r)[32]) {    // the loaded registers pass through the wait
-    asm volatile("tcgen05.wait::ld.sync.aligned;"
-                 : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]),
-                   "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15]),
-                   "+r"(r[16]), "+r"(r[17]), "+r"(r[18]), "+r"(r[19]), "+r"(r[20]), "+r"(r[21]), "+r"(r[22]), "+r"(r[23]),
-                   "+r"(r[24]), "+r"(r[25]), "+r"(r[26]), "+r"(r[27]), "+r"(r[28]), "+r"(r[29]), "+r"(r[30]), "+r"(r[31])
-                 :
-                 : "memory");
-}
-
-// 32 lanes x 32 consecutive f16 accumulator columns -> 16 registers of packed pairs
+// 32 lanes x 32 consecutive f16 accumulator columns -> 16 registers of packed pairs (column 2i low, 2i + 1 high)
 __device__ __forceinline__ void tmem_ld_x16_pack16(uint32_t taddr, uint32_t (&r)[16]) {
     asm volatile(
         "tcgen05.ld.sync.aligned.32x32b.x16.pack::16b.b32 "
@@ -264,30 +249,6 @@ __device__ __forceinline__ void fold_chunk16(const uint32_t (&v)[16], uint32_t (
     }
 #pragma unroll
     for (int i = 0; i < 8; ++i) B[i] = hmin3u(B[i], v[i], v[i + 8]);
-}
-
-// Same for a 128-column half (8 block minima): chunk CH of 4.
-template <int CH>
-__device__ __forceinline__ void fold_chunk8(const uint32_t (&v)[16], uint32_t (&A)[8], uint32_t (&B)[8]) {
-#pragma unroll
-    for (int b = 0; b < 2; ++b) {
-        const uint32_t* w = v + 8 * b;
-        A[2 * CH + b] = hmin2u(hmin3u(hmin3u(w[0], w[1], w[2]), hmin3u(w[3], w[4], w[5]), w[6]), w[7]);
-    }
-#pragma unroll
-    for (int i = 0; i < 8; ++i) B[i] = hmin3u(B[i], v[i], v[i + 8]);
-}
-
-// One 64-column chunk CH (32 packed registers = 4 blocks of 16 columns) folded into the two families: 32 instructions.
-template <int CH>
-__device__ __forceinline__ void fold_chunk16(const uint32_t (&v)[32], uint32_t (&A)[16], uint32_t (&B)[8]) {
-#pragma unroll
-    for (int b = 0; b < 4; ++b) {
-        const uint32_t* w = v + 8 * b;
-        A[4 * CH + b] = hmin2u(hmin3u(hmin3u(w[0], w[1], w[2]), hmin3u(w[3], w[4], w[5]), w[6]), w[7]);
-    }
-#pragma unroll
-    for (int i = 0; i < 8; ++i) B[i] = hmin3u(hmin3u(B[i], v[i], v[i + 8]), v[i + 16], v[i + 24]);
 }
 
 // The reference's own arithmetic over the candidates the masks name (pq.py:79-80): centroid 16 a + 2 i + p is a candidate
@@ -370,8 +331,7 @@ pq_encode_tc16_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
     uint64_t* x_full = bars;                        // [nx]: TMA landed the fp32 row slice
     uint64_t* x_empty = bars + kE16MaxX;            // [nx]: the step's split warp has read it
     uint64_t* a_full = bars + 2 * kE16MaxX;         // [na]: A0 / A1 written by the step's split warp
-    uint64_t* a_empty = a_full + kE16MaxA;          // (unused: the stage's full barrier of the step frees the slot)
-    uint64_t* b_full = a_empty + kE16MaxA;          // [nbs]: TMA landed B0, B1
+    uint64_t* b_full = a_full + 2 * kE16MaxA;       // [nbs]: TMA landed B0, B1  (the operand slot is freed by the step's full barrier)
     uint64_t* b_empty = b_full + kE16MaxBs;         // [nbs]: the MMAs of BOTH steps of the sub-space are done
     // EIGHT "full" barriers per stage, used by the stage's uses in turn.  A parity wait is only right when the barrier
     // is at most one phase behind the awaited one.  With three groups taking the steps in turn, the group that waits for use
@@ -566,10 +526,10 @@ pq_encode_tc16_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
             if (n_full) atomicAdd(stats + 1, n_full);
         }
     } else {
-        // ================= epilogue: one thread per row; group eg owns accumulator stage eg = tiles eg, eg + 2, .. of every round.
-        // Software-pipelined by one step: the TAIL of step s (row minimum -> threshold -> candidate masks -> code / push:
-        // ~170 mostly dependent instructions, 60 % of a warp's time when it ran after the fold) is spread in three
-        // branch-free pieces between the TMEM loads and folds of step s + 1, which it does not depend on. =================
+        // ================= epilogue: three groups of four warps, one thread per row; the groups take the CTA's steps in
+        // turn.  A step = fold the 256 packed scores (8 TMEM loads), release the stage, then the TAIL: row minimum ->
+        // threshold -> candidate masks -> code / push (~170 mostly dependent instructions; three warps per scheduler
+        // overlap one another's chains) =================
         const int eg = (warp - 4) >> 2;
         const int ew = warp & 3;
         const int rt = ew * 32 + lane;                 // row within the tile == TMEM lane
