@@ -38,8 +38,9 @@
 // Measured (2M x 384 rows, m = 48, K = 256, B200; scripts/dev_pq16.py times both kernels in one process): 2.05 ms against
 // 2.91 ms for pq_tc.cu on the same box, codes equal on all 96 M (also at scales 0.001 .. 30, K = 5 / 37 / 100, m = 1 / 13 / 16, N
 // not a multiple of anything), ~1.06 % of the (row, sub-space) pairs go through the resolver, DRAM read 3.08 GB = the
-// algorithmic bytes.  ncu: no pipe is the bound (ALU ~45 %); the SM's issue slots are ~70 % full and an epilogue warp runs
-// its ~430-instruction step at IPC 0.15.
+// algorithmic bytes.  ncu (profiles/r02_ncu_summary.json, pq_encode_tc16): ALU pipe 74 % busy, issue slots 70 %, tensor pipe
+// 37 % -- the 137 packed minima of a warp-step are a third of its ~430 instructions; the rest of the ALU load is the mask
+// arithmetic (HSET2, LOP3, POPC / FLO) and the split warps' conversions.
 //
 // How it got there, each step measured (r02):
 //   2.63 first version (two epilogue groups, one per stage; split = one warp per row quarter of every step)
