@@ -125,3 +125,25 @@ def test_exact_index_uses_tensor_cores_when_it_can():
     assert n == 1 and I[:, 0].tolist() == list(range(50)) and np.all(D[:, 0] == 0)
     Dref, Iref = O.exact_l2_topk(X, np.arange(30_000), X[:50], 10)
     np.testing.assert_array_equal(I, Iref)
+
+
+@pytest.mark.gpu
+def test_cta_pair_kernel_returns_the_single_cta_kernels_results():
+    """exact_tc2_kernel (tcgen05 cta_group::2, selected by debug bit 5) is kept although it measured slower: ids and
+    distances must equal the default kernel's, for an odd number of query tiles, a ragged last row tile and k = 1 / 10."""
+    import torch
+    from vector_db_b200 import _lib, ops
+    lib = _lib.load()
+    g = torch.Generator(device="cuda").manual_seed(3)
+    X = torch.randn((70_001, 192), device="cuda", generator=g)
+    mir, _, stats = ops.tc_prepare_rows(X, "cosine")
+    try:
+        for nq, k in ((700, 10), (129, 1), (4096, 10)):
+            q = torch.randn((nq, 192), device="cuda", generator=g)
+            lib.vdb_debug_set_tc_flags(0)
+            d0, i0 = ops.exact_topk_tc(q, X, mir, stats, k, "cosine")
+            lib.vdb_debug_set_tc_flags(32)
+            d1, i1 = ops.exact_topk_tc(q, X, mir, stats, k, "cosine")
+            assert torch.equal(i0, i1) and torch.equal(d0, d1)
+    finally:
+        lib.vdb_debug_set_tc_flags(0)
