@@ -56,7 +56,7 @@
 //        mbarrier probe / tcgen05.mma / tcgen05.commit is a ~50-100 clock trip for the single issuing thread
 // Measured and NOT kept: four groups, each a 128-column half of a stage, the halves of a step meeting through an 8-byte
 // summary per row in shared memory (2.6 ms: 294 instructions per half-step, a quarter of them barrier probes); four groups
-// in turn (2.24 ms: 80 registers, spills); hinted waits on the epilogue's own barriers (3.1 ms: late wake-ups); dropping the
+// in turn (2.24 ms: 80 registers, spills; with single-buffered TMEM loads to save registers 2.59 ms); hinted waits on the epilogue's own barriers (3.1 ms: late wake-ups); dropping the
 // per-step commits of the operand / codebook slots (no change -- the step's "full" barrier frees the operand slot now).
 // With the epilogue, the MMAs, the split arithmetic and the row loads all switched off the ring alone took 0.9-1.4 ms:
 // the step is 128 clocks of tensor time, so barrier round trips are of the order of the step.  Row slices are loaded
