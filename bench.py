@@ -553,6 +553,85 @@ def path_hnsw_search(dev, peaks):
     }
 
 
+def path_ivf_search(dev, peaks):
+    """SURVEY.md 8f rank 3 (widening beyond BASELINE.json): batched IVF search, 1M x 384, K = 1024 lists, 4096 queries, k = 10:
+    the list-major tensor-core engine (vdb_ivf_topk_tc) against the query-major fp32 list scan (vdb_ivf_scan); parity = the
+    reference's IvfIndex.search (oracle restatement of ivf.py:139-199) on the same centroids and lists."""
+    import torch
+
+    from oracle import ivf_oracle as IO
+    from vector_db_b200.indexing import IvfIndex
+    N, D, KL, Q = 1_000_000, 384, 1024, 4096
+    X = torch.randn((N, D), device=dev, generator=torch.Generator(device=dev).manual_seed(SEED_DB))
+    Qd = torch.randn((Q, D), device=dev, generator=torch.Generator(device=dev).manual_seed(SEED_Q))
+    X_host = X.cpu().numpy()
+    del X
+    idx = IvfIndex(k=KL, device=dev)
+    t0 = time.perf_counter()
+    idx.build_from_arrays(range(N), X_host, iters=10, init_rows=np.random.default_rng(SEED_DB).choice(N, KL, replace=False))
+    torch.cuda.synchronize()
+    build_s = time.perf_counter() - t0
+    rows = {}
+    for n_probe in (4, 16):
+        for engine in ("tc", "scan"):
+            idx.batch_engine = engine
+            (d, i, scanned), ms, _ = _timed(lambda: idx.search_device(Qd, n_probe, K), iters=5, warm=2)
+            rows[(n_probe, engine)] = (ms, d, i, float(scanned.float().mean().item()), idx.last_uncertified if engine == "tc" else 0)
+    n_probe = 4
+    ms_tc, d_tc, i_tc, cand, unc = rows[(n_probe, "tc")]
+    ms_sc, d_sc, i_sc, _, _ = rows[(n_probe, "scan")]
+    engines_equal = bool(torch.equal(i_tc, i_sc) and torch.equal(d_tc, d_sc)
+                         and torch.equal(rows[(16, "tc")][2], rows[(16, "scan")][2]))
+    idx.batch_engine = "tc"
+    Q_host = Qd.cpu().numpy()
+    idx.search_batch(Q_host, n_probe, K)
+    t0 = time.perf_counter()
+    for _ in range(3):
+        d_h, i_h = idx.search_batch(Q_host, n_probe, K)
+    e2e_dt = (time.perf_counter() - t0) / 3
+    # parity + CPU baseline: the reference's search on the same centroids / lists, 8 queries, 1 core
+    class _Rows:                                         # id -> embedding without a million-entry dict
+        def __getitem__(self, i):
+            return X_host[int(i)]
+
+        def __contains__(self, i):
+            return 0 <= int(i) < N
+
+    lists = idx.inverted_lists
+    n_or = 8
+    t0 = time.perf_counter()
+    same = 0
+    max_rel = 0.0
+    for j in range(n_or):
+        res, _, _ = IO.search(idx.centroids, lists, _Rows(), Q_host[j], n_probe, K)
+        ids_ref = [int(r[1]) for r in res]
+        same += int(ids_ref == [int(v) for v in i_h[j] if v >= 0])
+        dr = np.array([float(r[0]) for r in res], dtype=np.float64)
+        max_rel = max(max_rel, float(np.max(np.abs(d_h[j][:len(dr)] - dr) / np.maximum(dr, 1e-30))) if len(dr) else 0.0)
+    cpu_s = time.perf_counter() - t0
+    alg = Q * cand * (4 * D + 4)
+    return {
+        "config": {"workload": f"batched IVF search, {N} x {D} fp32, {KL} lists (upload + 10 Lloyd rounds, {build_s:.2f} s), {Q}-query batch, "
+                               f"n_probe={n_probe}, k={K} (SURVEY.md 8f rank 3; not a BASELINE.json config)",
+                   "engines_ms": {f"n_probe={p},{e}": round(v[0], 3) for (p, e), v in rows.items()},
+                   "candidates_per_query": cand, "uncertified_queries_rerun_through_the_scan": unc},
+        "metric": "queries/s", "value": Q / (ms_tc * 1e-3), "unit": "queries/s", "ms_per_step": ms_tc,
+        "kernel": "exact_tc_kernel (list-major units) + select / rerank / final", "kernel_ms": ms_tc, "dtype": "bf16 coarse + f32 rerank",
+        "query_major_scan_ms": ms_sc,
+        "roofline": dict(_hbm_roofline(alg, ms_tc, peaks, "ivf list-major step",
+                                       "candidates x (4D + 4) bytes per query (the query-major model of DESIGN.md 4.5) over the WHOLE "
+                                       "step incl. the host-side grouping; above 1 means lists shared by the batch are read once")),
+        "cpu_baseline": {"value": n_or / cpu_s, "unit": "queries/s", "cores": 1, "kind": "port",
+                         "sample": f"oracle.ivf_oracle.search (ivf.py:139-199 restated) on {n_or} queries, same lists, {cpu_s:.2f} s"},
+        "e2e": {"value": Q / e2e_dt, "unit": "queries/s", "h2d_bytes_per_step": int(Q * D * 4), "d2h_bytes_per_step": int(Q * K * 12),
+                "api": "IvfIndex.search_batch: numpy queries in, numpy (dist, ids) out"},
+        "parity": {"checked_queries": n_or, "ids_equal": bool(same == n_or), "identical_result_lists": same, "max_rel_err": max_rel,
+                   "tensor_core_engine_equals_list_scan_all_queries": engines_equal,
+                   "oracle": "the reference's IvfIndex.search restated (pinned to a reference run by tests/golden/ivf.npz), same "
+                             "centroids and lists"},
+    }
+
+
 def path_staging(dev, peaks):
     """Storage staging (north_star subsystem 1; storage.py:135-161,254-259): the reference's layer-1 memmap file
     ({i8 id, f4[D]} records, stride 8+4D) -> pinned ring -> strided DMA -> SoA in HBM."""
@@ -746,7 +825,7 @@ def path_sharded_adc(dev, peaks, rank, world, peer_ok):
     }
 
 
-PATHS = ("pq_encode", "adc_scan", "hnsw_search", "staging", "sharded_adc")
+PATHS = ("pq_encode", "adc_scan", "hnsw_search", "ivf_search", "staging", "sharded_adc")
 
 
 def run_paths(which, dev, peaks, rank, world):
@@ -776,6 +855,8 @@ def run_paths(which, dev, peaks, rank, world):
     torch.cuda.empty_cache()
     if single and "hnsw_search" in which:
         guarded("hnsw_search", lambda: path_hnsw_search(dev, peaks))
+    if single and "ivf_search" in which:
+        guarded("ivf_search", lambda: path_ivf_search(dev, peaks))
     if single and "staging" in which:
         guarded("staging", lambda: path_staging(dev, peaks))
     if "sharded_adc" in which:

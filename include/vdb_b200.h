@@ -171,9 +171,27 @@ int vdb_ivf_topk_tc(const float* q /*[dev] Q*D*/, int Q, const float* lm_vecs /*
                     int D, int k, int n_probe, const int32_t* pair_rows /*[dev] Q*n_probe*/,
                     const int32_t* row_query /*[dev] Qa*/, const int32_t* row_list /*[dev] Qa: the pair's list*/,
                     const float* centroids /*[dev] K*D*/, int64_t Qa, const int32_t* unit_table /*[dev] n_units*4*/,
-                    int n_units, const float* list_stats /*[dev] K*2 per-list (max |bf16 r|, max |bf16 r - r|) or NULL*/,
+                    int n_units, const int32_t* meta /*[dev] vdb_ivf_group_pairs' totals (then Qa / n_units are upper bounds) or NULL*/,
+                    const float* list_stats /*[dev] K*2 per-list (max |bf16 r|, max |bf16 r - r|) or NULL*/,
                     float* out_d /*[dev] Q*k*/, int64_t* out_i /*[dev] Q*k*/,
                     int32_t* out_uncertified /*[dev] Q+1*/, void* ws, size_t ws_bytes, void* stream);
+
+/* Device-side preparation / completion of vdb_ivf_topk_tc (no host round trip):
+ *   vdb_ivf_group_pairs: (query, probe) pairs grouped by list -> operand-row maps, unit table and meta = {operand rows, units};
+ *     list_tile_ptr [K+1] = first 256-row tile of every list in the list-major copy (empty lists have no tiles); Qa_max >=
+ *     (ceil(Q n_probe / 128) + min(K, Q n_probe)) * 128 rows, unit_table has Qa_max / 128 rows of 4 ints.
+ *   vdb_ivf_tc_finish: the k2 = top_k + 1 results of vdb_ivf_topk_tc (list-major positions) -> the reference's stable order
+ *     (distance, enumeration sequence; ivf.py:177-193), external ids, tie[q] = 1 when equal distances straddle the cut. */
+size_t vdb_ivf_group_workspace(int K);
+int vdb_ivf_group_pairs(const int32_t* probes /*[dev] Q*n_probe*/, int Q, int n_probe, const int32_t* list_tile_ptr /*[dev] K+1*/,
+                        int K, int64_t Qa_max, int32_t* row_query /*[dev] Qa_max*/, int32_t* row_list /*[dev] Qa_max*/,
+                        int32_t* pair_rows /*[dev] Q*n_probe*/, int32_t* unit_table /*[dev] Qa_max/128*4*/, int32_t* meta /*[dev] 2*/,
+                        void* ws, size_t ws_bytes, void* stream);
+int vdb_ivf_tc_finish(const float* d /*[dev] Q*k2*/, const int64_t* pos /*[dev] Q*k2*/, int Q, int k2, int top_k,
+                      const int32_t* probes /*[dev] Q*n_probe*/, const int32_t* prefix /*[dev] Q*(n_probe+1)*/, int n_probe,
+                      const int32_t* lm_list /*[dev] N: list of every list-major row*/, const int64_t* lm_start /*[dev] K*/,
+                      const int64_t* lm_ids /*[dev] N*/, float* out_d /*[dev] Q*top_k*/, int64_t* out_ids /*[dev] Q*top_k*/,
+                      int32_t* tie /*[dev] Q*/, void* stream);
 
 /* bench/debug only: bit 0 = skip the whole epilogue of the coarse pass, bit 1 = skip only its threshold
  * test and bin-list inserts (results are then invalid) */

@@ -169,7 +169,7 @@ exact_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                 const __grid_constant__ CUtensorMap map_a2, const __grid_constant__ CUtensorMap map_b2,
                 int Q, int64_t N, int D, int has_norm, int num_kb, int stages, int m_tiles, int S,
                 int tiles_per_slice, int tiles_total, int flags, u64* __restrict__ partial, uint32_t* gtau,
-                const int4* __restrict__ utab) {
+                const int4* __restrict__ utab, const int32_t* __restrict__ units_dev) {
     extern __shared__ __align__(1024) unsigned char smem[];   // 128B-swizzled operand tiles need 1024 B alignment
     if ((smem_u32(smem) & 1023u) != 0) __trap();
     const TcSmemLayout L = tc_layout(num_kb, stages, has_norm);
@@ -190,7 +190,7 @@ exact_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     uint32_t* sTau = reinterpret_cast<uint32_t*>(smem + L.tau_off);   // [group][row]
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int units = m_tiles * S;
+    const int units = units_dev ? __ldg(units_dev) : m_tiles * S;      // list-major IVF: the unit count may live on the device
     // UMMAs in the last k-block: columns past D are zero-filled by TMA, skip the all-zero K steps
     const int last_steps = (D - (num_kb - 1) * kBlockK + kUmmaK - 1) / kUmmaK;
 
@@ -1276,7 +1276,8 @@ struct TcIvf {
     const float* centroids;        // [K][D]: operand rows and mirror rows are residuals against the list's centroid
     int64_t Qa;                    // operand rows (multiple of 128)
     const int4* utab;              // [n_units] (pair tile, first row tile, end row tile, 0)
-    int n_units;
+    int n_units;                   // units, or their upper bound when units_dev is given
+    const int32_t* units_dev;      // device-side unit count (vdb_ivf_group_pairs' meta + 1), or null
     const float2* list_stats;      // [K] per list (max |bf16(x - c)|, max |bf16(x - c) - (x - c)|), or null: the global pair
 };
 
@@ -1341,7 +1342,7 @@ int vdb_exact_topk_tc(const float* q, int Q, const float* db, const void* mirror
 }
 
 size_t vdb_ivf_topk_tc_workspace(int Q, int64_t Qa, int64_t N, int D, int k, int n_units) {
-    TcIvf v{1, nullptr, nullptr, nullptr, nullptr, Qa, nullptr, n_units, nullptr};
+    TcIvf v{1, nullptr, nullptr, nullptr, nullptr, Qa, nullptr, n_units, nullptr, nullptr};
     TcPlan p;
     if (Q <= 0 || Qa <= 0 || n_units <= 0 || !plan_tc_ivf(v, N, D, k, &p)) return 0;
     return tc_workspace(p, Q, Qa, N, D, k, false).total;
@@ -1350,14 +1351,14 @@ size_t vdb_ivf_topk_tc_workspace(int Q, int64_t Qa, int64_t N, int D, int k, int
 int vdb_ivf_topk_tc(const float* q, int Q, const float* lm_vecs, const void* lm_mirror, const float* lm_stats,
                     const int64_t* lm_ids, int64_t N, int D, int k, int n_probe, const int32_t* pair_rows,
                     const int32_t* row_query, const int32_t* row_list, const float* centroids, int64_t Qa,
-                    const int32_t* unit_table, int n_units, const float* list_stats, float* out_d,
+                    const int32_t* unit_table, int n_units, const int32_t* meta, const float* list_stats, float* out_d,
                     int64_t* out_i, int32_t* out_uncertified, void* ws, size_t ws_bytes, void* stream) {
     VDB_REQUIRE(n_probe > 0 && n_probe <= 32, VDB_ERR_UNSUPPORTED, "vdb_ivf_topk_tc: n_probe=%d (at most 32)", n_probe);
     VDB_REQUIRE(pair_rows && row_query && row_list && centroids && unit_table && n_units > 0 && Qa > 0 && Qa % kTileM == 0 && N % kTileN == 0,
                 VDB_ERR_INVALID, "vdb_ivf_topk_tc: bad pair / unit tables (Qa=%lld, N=%lld, units=%d)", (long long)Qa,
                 (long long)N, n_units);
     TcIvf v{n_probe, pair_rows, row_query, row_list, centroids, Qa, reinterpret_cast<const int4*>(unit_table), n_units,
-            reinterpret_cast<const float2*>(list_stats)};
+            meta ? meta + 1 : nullptr, reinterpret_cast<const float2*>(list_stats)};
     return tc_search_impl(q, Q, lm_vecs, lm_mirror, lm_stats, lm_ids, N, D, k, VDB_METRIC_L2, out_d, out_i, out_uncertified,
                           ws, ws_bytes, stream, &v);
 }
@@ -1442,12 +1443,12 @@ static int tc_search_impl(const float* q, int Q, const float* db, const void* mi
             VDB_CUDA(cudaFuncSetAttribute(exact_tc_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem));
             exact_tc_kernel<16><<<p.grid, kTcThreads, p.smem, st>>>(map_a, map_b, map_a2, map_b2, (int)Qa, N, D, p.has_norm, p.num_kb, p.stages, p.m_tiles, p.S,
                                                                    p.tiles_per_slice, p.tiles_total, g_tc_flags, partial, gtau,
-                                                                   ivf ? ivf->utab : nullptr);
+                                                                   ivf ? ivf->utab : nullptr, ivf ? ivf->units_dev : nullptr);
         } else {
             VDB_CUDA(cudaFuncSetAttribute(exact_tc_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem));
             exact_tc_kernel<8><<<p.grid, kTcThreads, p.smem, st>>>(map_a, map_b, map_a2, map_b2, (int)Qa, N, D, p.has_norm, p.num_kb, p.stages, p.m_tiles, p.S,
                                                                   p.tiles_per_slice, p.tiles_total, g_tc_flags, partial, gtau,
-                                                                  ivf ? ivf->utab : nullptr);
+                                                                  ivf ? ivf->utab : nullptr, ivf ? ivf->units_dev : nullptr);
         }
     }
     VDB_CUDA(cudaGetLastError());

@@ -39,6 +39,7 @@ constexpr int kIvfMaxProbe = 8192;                         // probe prefix table
 constexpr int kIvfCdThreads = 128;      // centroids per CTA
 constexpr int kIvfCdQ = 4;              // queries per thread: one centroid element feeds four distances
 constexpr int kIvfCdChunk = 32;         // columns per shared-memory tile
+constexpr int kIvfCdStride = kIvfCdChunk + 4;   // tile row stride: 16-byte aligned rows, 128-bit reads of 8 consecutive rows hit 32 banks
 constexpr int kIvfCdMaxLeaves = 512;
 
 struct IvfLeaves {
@@ -72,7 +73,9 @@ __device__ void ivf_flatten_leaves(IvfLeaves* L, int n) {
 }
 
 // out[q][c] = np.linalg.norm(centroids[c] - query[q])  (ivf.py:109, :170).  CTA = 128 centroids x kIvfCdQ queries;
-// centroid columns go through a [128][33] shared tile (coalesced loads, conflict-free per-thread row reads).
+// centroid columns go through a [128][36] shared tile (coalesced loads, conflict-free per-thread 128-bit row reads); the
+// eight columns of a block are two 128-bit loads per operand row instead of eight scalar ones (the kernel was bound by its
+// shared-memory load instructions: 40 per 96 flops).
 __global__ void __launch_bounds__(kIvfCdThreads)
 ivf_centroid_dist_kernel(const float* __restrict__ q, int Q, int D, const float* __restrict__ cent, int K,
                          float* __restrict__ out) {
@@ -95,13 +98,14 @@ ivf_centroid_dist_kernel(const float* __restrict__ q, int Q, int D, const float*
             chunk_base = t & ~(kIvfCdChunk - 1);
             for (int r = warp; r < kIvfCdThreads; r += kIvfCdThreads / 32) {
                 const int c = c0 + r, col = chunk_base + lane;
-                tile[r * (kIvfCdChunk + 1) + lane] = (c < K && col < D) ? __ldg(cent + (size_t)c * D + col) : 0.f;
+                tile[r * kIvfCdStride + lane] = (c < K && col < D) ? __ldg(cent + (size_t)c * D + col) : 0.f;
             }
             __syncthreads();
         }
     };
     __syncthreads();
-    const float* mine = tile + tid * (kIvfCdChunk + 1);
+    const float* mine = tile + tid * kIvfCdStride;
+    const bool vec_ok = (D & 3) == 0;                                  // 128-bit shared loads of the query rows need 16-byte aligned rows
     float val[kIvfCdQ][12];                                            // post-order value stack (depth <= log2(D/64)+1)
     int nv = 0;
     for (int l = 0; l < leaves.n; ++l) {
@@ -125,12 +129,25 @@ ivf_centroid_dist_kernel(const float* __restrict__ q, int Q, int D, const float*
             for (int i = 0; i < main_end; i += 8) {
                 need(s + i);
                 const float* cp = mine + (s + i - chunk_base);
+                float cv8[8];
+                {
+                    const float4 a = *reinterpret_cast<const float4*>(cp), b = *reinterpret_cast<const float4*>(cp + 4);
+                    cv8[0] = a.x; cv8[1] = a.y; cv8[2] = a.z; cv8[3] = a.w; cv8[4] = b.x; cv8[5] = b.y; cv8[6] = b.z; cv8[7] = b.w;
+                }
 #pragma unroll
-                for (int t = 0; t < 8; ++t) {
-                    const float cv = cp[t];
+                for (int g = 0; g < kIvfCdQ; ++g) {
+                    float qv[8];
+                    const float* qp = qs + g * D + s + i;
+                    if (vec_ok) {
+                        const float4 a = *reinterpret_cast<const float4*>(qp), b = *reinterpret_cast<const float4*>(qp + 4);
+                        qv[0] = a.x; qv[1] = a.y; qv[2] = a.z; qv[3] = a.w; qv[4] = b.x; qv[5] = b.y; qv[6] = b.z; qv[7] = b.w;
+                    } else {
 #pragma unroll
-                    for (int g = 0; g < kIvfCdQ; ++g) {
-                        const float d = __fsub_rn(cv, qs[g * D + s + i + t]);
+                        for (int t = 0; t < 8; ++t) qv[t] = qp[t];
+                    }
+#pragma unroll
+                    for (int t = 0; t < 8; ++t) {
+                        const float d = __fsub_rn(cv8[t], qv[t]);
                         const float v = __fmul_rn(d, d);
                         r[g][t] = i == 0 ? v : __fadd_rn(r[g][t], v);
                     }
@@ -198,6 +215,51 @@ ivf_probe_kernel(const float* __restrict__ cdist, int K, int n_probe, int C, con
         }
         px[n_probe] = run;
     }
+}
+
+// The same selection for a BATCH with few probes (n_probe <= 32, K <= 4096): one WARP per query, the K keys in registers,
+// n_probe rounds of "smallest remaining (distance, centroid) key" -- the CTA-per-query BlockSelect above costs 0.36 ms for
+// 4096 queries x 1024 centroids, a quarter of a list-major batch search.
+constexpr int kIvfProbeWarpMaxK = 4096;
+template <int kPer>                                            // keys per lane: K <= 32 kPer
+__global__ void __launch_bounds__(256)
+ivf_probe_warp_kernel(const float* __restrict__ cdist, int Q, int K, int n_probe, const int32_t* __restrict__ list_ptr,
+                      int32_t* __restrict__ probes, int32_t* __restrict__ prefix) {
+    const int q = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
+    if (q >= Q) return;
+    uint32_t dk[kPer];                                         // ordered distance bits; the centroid index is t * 32 + lane
+    const float* src = cdist + (size_t)q * K;
+#pragma unroll
+    for (int t = 0; t < kPer; ++t) {
+        const int c = t * 32 + lane;
+        dk[t] = (c < K && t * 32 < K) ? f32_to_ordered(src[c]) : 0xFFFFFFFFu;
+    }
+    int run = 0;
+    for (int p = 0; p < n_probe; ++p) {
+        u64 best = VDB_KEY_MAX;
+#pragma unroll
+        for (int t = 0; t < kPer; ++t) {
+            const u64 k = ((u64)dk[t] << 32) | (uint32_t)(t * 32 + lane);
+            best = (dk[t] != 0xFFFFFFFFu && k < best) ? k : best;
+        }
+        u64 wbest = best;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const u64 other = __shfl_xor_sync(0xffffffffu, wbest, o);
+            wbest = other < wbest ? other : wbest;
+        }
+        const int c = (int)(uint32_t)(wbest & 0xFFFFFFFFull);
+        if ((c & 31) == lane) {                                // the owner retires it
+#pragma unroll
+            for (int t = 0; t < kPer; ++t) dk[t] = (t == (c >> 5)) ? 0xFFFFFFFFu : dk[t];
+        }
+        if (lane == 0) {
+            probes[(size_t)q * n_probe + p] = c;
+            if (prefix) prefix[(size_t)q * (n_probe + 1) + p] = run;
+        }
+        if (prefix) run += __ldg(list_ptr + c + 1) - __ldg(list_ptr + c);
+    }
+    if (prefix && lane == 0) prefix[(size_t)q * (n_probe + 1) + n_probe] = run;
 }
 
 __device__ __forceinline__ bool ivf_bit(const uint32_t* bm, int r) { return (bm[r >> 5] >> (r & 31)) & 1u; }
@@ -369,6 +431,127 @@ ivf_centroid_mean_kernel(const float* __restrict__ x, int D, const int32_t* __re
 static size_t ivf_al(size_t v) { return (v + 255) & ~(size_t)255; }
 static int ivf_chunk_min(int Q) { return Q >= 1024 ? 16384 : (Q >= 128 ? 2048 : 256); }
 
+// ---------------------------------------------------------------------------------------------------------------
+// List-major batch search (vdb_ivf_topk_tc): the grouping of the (query, probed list) pairs by list and the final ordering,
+// on the device -- as torch sorts / scatters around the scan they cost 1.9 ms of a 2.4 ms step with two size read-backs.
+//   ivf_group_count_kernel    pairs per (non-empty) list
+//   ivf_group_plan_kernel     one CTA: 128-row operand tiles per list -> first operand row of every list, the unit table
+//                             (pair tile, first row tile, end row tile) and the totals {operand rows, units}
+//   ivf_group_scatter_kernel  every pair takes the next operand row of its list (order inside a list is immaterial)
+//   ivf_tc_finish_kernel      one warp per query: list-major positions -> (distance, enumeration sequence) order of
+//                             ivf.py:177-193, external ids, and a flag when equal distances straddle the cut
+__global__ void ivf_group_count_kernel(const int32_t* __restrict__ probes, int P, const int32_t* __restrict__ tile_ptr,
+                                       int32_t* __restrict__ n_l) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P) return;
+    const int l = probes[p];
+    if (tile_ptr[l + 1] > tile_ptr[l]) atomicAdd(n_l + l, 1);
+}
+
+__global__ void __launch_bounds__(1024)
+ivf_group_plan_kernel(const int32_t* __restrict__ n_l, const int32_t* __restrict__ tile_ptr, int K, int32_t* __restrict__ arow0,
+                      int4* __restrict__ utab, int32_t* __restrict__ meta) {
+    __shared__ int warp_sums[32];
+    __shared__ int base_s;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) base_s = 0;
+    __syncthreads();
+    for (int l0 = 0; l0 < K; l0 += 1024) {
+        const int l = l0 + tid;
+        const int mt = l < K ? (n_l[l] + 127) >> 7 : 0;          // operand tiles of the list
+        int incl = mt;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        if (lane == 31) warp_sums[warp] = incl;
+        __syncthreads();
+        if (warp == 0) {
+            int w = warp_sums[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int v = __shfl_up_sync(0xffffffffu, w, o);
+                if (lane >= o) w += v;
+            }
+            warp_sums[lane] = w;
+        }
+        __syncthreads();
+        const int base = base_s;
+        const int excl = base + (warp ? warp_sums[warp - 1] : 0) + incl - mt;      // first unit of the list
+        if (l < K) {
+            arow0[l] = excl * 128;
+            for (int i = 0; i < mt; ++i) utab[excl + i] = make_int4(excl + i, tile_ptr[l], tile_ptr[l + 1], 0);
+        }
+        __syncthreads();
+        if (tid == 1023) base_s = base + warp_sums[31];
+        __syncthreads();
+    }
+    if (tid == 0) { meta[0] = base_s * 128; meta[1] = base_s; }
+}
+
+__global__ void ivf_group_scatter_kernel(const int32_t* __restrict__ probes, int P, int n_probe,
+                                         const int32_t* __restrict__ tile_ptr, const int32_t* __restrict__ arow0,
+                                         int32_t* __restrict__ cursor, int32_t* __restrict__ row_query,
+                                         int32_t* __restrict__ row_list, int32_t* __restrict__ pair_rows) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P) return;
+    const int l = probes[p];
+    int arow = -1;
+    if (tile_ptr[l + 1] > tile_ptr[l]) {
+        arow = arow0[l] + atomicAdd(cursor + l, 1);
+        row_query[arow] = p / n_probe;
+        row_list[arow] = l;
+    }
+    pair_rows[p] = arow;
+}
+
+// k2 <= 32 results per query (list-major positions, ascending distance); lane i owns result i
+__global__ void __launch_bounds__(256)
+ivf_tc_finish_kernel(const float* __restrict__ d, const int64_t* __restrict__ pos, int Q, int k2, int top_k,
+                     const int32_t* __restrict__ probes, const int32_t* __restrict__ prefix, int n_probe,
+                     const int32_t* __restrict__ lm_list, const int64_t* __restrict__ lm_start,
+                     const int64_t* __restrict__ lm_ids, float* __restrict__ out_d, int64_t* __restrict__ out_ids,
+                     int32_t* __restrict__ tie) {
+    const int q = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
+    if (q >= Q) return;
+    float dist = INFINITY;
+    int64_t id = -1;
+    u64 key = VDB_KEY_MAX;
+    if (lane < k2) {
+        const int64_t ps = pos[(size_t)q * k2 + lane];
+        if (ps >= 0) {
+            dist = d[(size_t)q * k2 + lane];
+            const int l = lm_list[ps];
+            int rank = 0;
+            for (int p = 0; p < n_probe; ++p)
+                if (probes[(size_t)q * n_probe + p] == l) { rank = p; break; }
+            const uint32_t seq = (uint32_t)(prefix[(size_t)q * (n_probe + 1) + rank] + (int)(ps - lm_start[l]));
+            key = ((u64)__float_as_uint(dist) << 32) | seq;               // dist >= 0: its bits order like the value
+            id = lm_ids[ps];
+        }
+    }
+    int r = 0;                                                              // rank of my key (keys are distinct)
+    for (int j = 0; j < 32; ++j) {
+        const u64 other = __shfl_sync(0xffffffffu, key, j);
+        r += (other < key) ? 1 : 0;
+    }
+    const bool valid = key != VDB_KEY_MAX;
+    if (valid && r < top_k) { out_d[(size_t)q * top_k + r] = dist; out_ids[(size_t)q * top_k + r] = id; }
+    // slots past the valid results
+    const int n_valid = __popc(__ballot_sync(0xffffffffu, valid));
+    if (lane >= n_valid && lane < top_k) { out_d[(size_t)q * top_k + lane] = INFINITY; out_ids[(size_t)q * top_k + lane] = -1; }
+    // equal distances on both sides of the cut: which of them the reference keeps depends on rows this call did not fetch
+    const unsigned at_cut = __ballot_sync(0xffffffffu, valid && r == top_k - 1);
+    const unsigned past = __ballot_sync(0xffffffffu, valid && r == top_k);
+    if (at_cut && past) {
+        const float da = __shfl_sync(0xffffffffu, dist, __ffs(at_cut) - 1), db = __shfl_sync(0xffffffffu, dist, __ffs(past) - 1);
+        if (lane == 0) tie[q] = (da == db) ? 1 : 0;
+    } else if (lane == 0) {
+        tie[q] = 0;
+    }
+}
+
 }  // namespace vdb
 
 using namespace vdb;
@@ -381,7 +564,7 @@ int vdb_ivf_centroid_dist(const float* q, int Q, int D, const float* centroids, 
     VDB_REQUIRE(q && centroids && out, VDB_ERR_INVALID, "vdb_ivf_centroid_dist: null pointer");
     VDB_REQUIRE(Q <= 65535 * kIvfCdQ, VDB_ERR_UNSUPPORTED, "Q=%d too large per call", Q);
     VDB_REQUIRE(D <= 8192, VDB_ERR_UNSUPPORTED, "D=%d > 8192", D);
-    const size_t smem = ((size_t)kIvfCdQ * D + (size_t)kIvfCdThreads * (kIvfCdChunk + 1)) * 4;
+    const size_t smem = ((size_t)kIvfCdQ * D + (size_t)kIvfCdThreads * kIvfCdStride) * 4;
     VDB_CUDA(cudaFuncSetAttribute(ivf_centroid_dist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid((K + kIvfCdThreads - 1) / kIvfCdThreads, (Q + kIvfCdQ - 1) / kIvfCdQ);
     ivf_centroid_dist_kernel<<<grid, kIvfCdThreads, smem, static_cast<cudaStream_t>(stream)>>>(q, Q, D, centroids, K, out);
@@ -397,6 +580,15 @@ int vdb_ivf_probe(const float* cdist, int Q, int K, int n_probe, const int32_t* 
     VDB_REQUIRE(n_probe <= kIvfMaxProbe, VDB_ERR_UNSUPPORTED, "n_probe=%d > %d", n_probe, kIvfMaxProbe);
     if (Q == 0) return VDB_OK;
     VDB_REQUIRE(cdist && probes && (!prefix || list_ptr), VDB_ERR_INVALID, "vdb_ivf_probe: null pointer");
+    if (n_probe <= 32 && K <= kIvfProbeWarpMaxK && K >= n_probe && Q >= 64) {
+        cudaStream_t st = static_cast<cudaStream_t>(stream);
+        if (K <= 1024) ivf_probe_warp_kernel<32><<<(Q + 7) / 8, 256, 0, st>>>(cdist, Q, K, n_probe, list_ptr, probes, prefix);
+        else if (K <= 2048) ivf_probe_warp_kernel<64><<<(Q + 7) / 8, 256, 0, st>>>(cdist, Q, K, n_probe, list_ptr, probes, prefix);
+        else ivf_probe_warp_kernel<128><<<(Q + 7) / 8, 256, 0, st>>>(cdist, Q, K, n_probe, list_ptr, probes, prefix);
+        count_launch(1);
+        VDB_CUDA(cudaGetLastError());
+        return VDB_OK;
+    }
     const int C = select_capacity(n_probe, 256);
     const size_t smem = (size_t)C * 8;
     VDB_CUDA(cudaFuncSetAttribute(ivf_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -451,6 +643,50 @@ int vdb_ivf_centroid_mean(const float* x, int D, const int32_t* list_ptr, const 
     VDB_REQUIRE(D > 0 && K > 0, VDB_ERR_INVALID, "vdb_ivf_centroid_mean: bad shape");
     VDB_REQUIRE(x && list_ptr && list_rows && centroids, VDB_ERR_INVALID, "vdb_ivf_centroid_mean: null pointer");
     ivf_centroid_mean_kernel<<<K, 128, 0, static_cast<cudaStream_t>(stream)>>>(x, D, list_ptr, list_rows, centroids);
+    count_launch(1);
+    VDB_CUDA(cudaGetLastError());
+    return VDB_OK;
+}
+
+size_t vdb_ivf_group_workspace(int K) { return ivf_al((size_t)K * 4) * 3 + 256; }
+
+int vdb_ivf_group_pairs(const int32_t* probes, int Q, int n_probe, const int32_t* list_tile_ptr, int K, int64_t Qa_max,
+                        int32_t* row_query, int32_t* row_list, int32_t* pair_rows, int32_t* unit_table, int32_t* meta,
+                        void* ws, size_t ws_bytes, void* stream) {
+    VDB_REQUIRE(Q > 0 && n_probe > 0 && K > 0 && Qa_max > 0 && Qa_max % 128 == 0, VDB_ERR_INVALID, "vdb_ivf_group_pairs: bad shape");
+    VDB_REQUIRE(probes && list_tile_ptr && row_query && row_list && pair_rows && unit_table && meta && ws, VDB_ERR_INVALID,
+                "vdb_ivf_group_pairs: null pointer");
+    VDB_REQUIRE(ws_bytes >= vdb_ivf_group_workspace(K), VDB_ERR_WORKSPACE, "workspace %zu < %zu", ws_bytes, vdb_ivf_group_workspace(K));
+    const int64_t P64 = (int64_t)Q * n_probe;
+    VDB_REQUIRE(P64 < (1ll << 30), VDB_ERR_UNSUPPORTED, "too many (query, probe) pairs");
+    // the worst case: every pair's list keeps a partly filled last tile
+    const int64_t need = ((P64 + 127) / 128 + (P64 < K ? P64 : K)) * 128;
+    VDB_REQUIRE(Qa_max >= need, VDB_ERR_INVALID, "Qa_max=%lld < %lld operand rows in the worst case", (long long)Qa_max, (long long)need);
+    const int P = (int)P64;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    char* base = static_cast<char*>(ws);
+    int32_t* n_l = reinterpret_cast<int32_t*>(base);
+    int32_t* arow0 = reinterpret_cast<int32_t*>(base + ivf_al((size_t)K * 4));
+    int32_t* cursor = reinterpret_cast<int32_t*>(base + 2 * ivf_al((size_t)K * 4));
+    VDB_CUDA(cudaMemsetAsync(n_l, 0, (size_t)K * 4, st));
+    VDB_CUDA(cudaMemsetAsync(cursor, 0, (size_t)K * 4, st));
+    VDB_CUDA(cudaMemsetAsync(row_query, 0xFF, (size_t)Qa_max * 4, st));      // -1: padding of the operand tiles
+    ivf_group_count_kernel<<<(P + 255) / 256, 256, 0, st>>>(probes, P, list_tile_ptr, n_l);
+    ivf_group_plan_kernel<<<1, 1024, 0, st>>>(n_l, list_tile_ptr, K, arow0, reinterpret_cast<int4*>(unit_table), meta);
+    ivf_group_scatter_kernel<<<(P + 255) / 256, 256, 0, st>>>(probes, P, n_probe, list_tile_ptr, arow0, cursor, row_query, row_list, pair_rows);
+    count_launch(3);
+    VDB_CUDA(cudaGetLastError());
+    return VDB_OK;
+}
+
+int vdb_ivf_tc_finish(const float* d, const int64_t* pos, int Q, int k2, int top_k, const int32_t* probes, const int32_t* prefix,
+                      int n_probe, const int32_t* lm_list, const int64_t* lm_start, const int64_t* lm_ids, float* out_d,
+                      int64_t* out_ids, int32_t* tie, void* stream) {
+    VDB_REQUIRE(Q > 0 && k2 > 0 && k2 <= 32 && top_k > 0 && top_k < k2 + 1 && n_probe > 0, VDB_ERR_INVALID, "vdb_ivf_tc_finish: bad shape");
+    VDB_REQUIRE(d && pos && probes && prefix && lm_list && lm_start && lm_ids && out_d && out_ids && tie, VDB_ERR_INVALID,
+                "vdb_ivf_tc_finish: null pointer");
+    ivf_tc_finish_kernel<<<(Q + 7) / 8, 256, 0, static_cast<cudaStream_t>(stream)>>>(d, pos, Q, k2, top_k, probes, prefix, n_probe, lm_list,
+                                                                                   lm_start, lm_ids, out_d, out_ids, tie);
     count_launch(1);
     VDB_CUDA(cudaGetLastError());
     return VDB_OK;

@@ -129,71 +129,33 @@ class IvfIndex:
             off = ops.tc_norm_offset(n_pad, vec.dim)
             mirror[off + pad * 16 + (((pad >> 2) & 1) << 3)] = 1e30
         lm_ids = torch.where(lm_row >= 0, vec.ids[src], torch.full_like(lm_row, -1))
+        tile_ptr = (start // 256).to(torch.int32).contiguous()          # first 256-row tile of every list (empty lists: none)
         self._lm = {"ptr": ptr, "vecs": lm_vecs, "mirror": mirror, "stats": stats, "list_stats": list_stats, "ids": lm_ids,
+                    "tile_ptr": tile_ptr, "list_of_row": lm_list.clamp(max=self.k - 1).to(torch.int32).contiguous(), "any_rows": n > 0,
                     "start": start,
                     "counts": counts, "padded": padded}
         return self._lm
 
     def _search_list_major(self, q: torch.Tensor, probes: torch.Tensor, prefix: torch.Tensor, top_k: int):
-        """Batch search through the tensor cores: (query, probed list) pairs grouped by list, one small dense contraction per
-        list (vdb_ivf_topk_tc), selection / exact fp32 rerank / certificate per query; then the reference's stable order
-        (distance, enumeration sequence -- ivf.py:177-193) is restored among equal distances and queries the certificate
-        rejected are re-run through the query-major scan.  Returns (dist, ids) or None when the shape is not covered."""
+        """Batch search through the tensor cores: (query, probed list) pairs grouped by list (vdb_ivf_group_pairs), one small
+        dense contraction per list (vdb_ivf_topk_tc), selection / exact fp32 rerank / certificate per query, then the
+        reference's stable order (distance, enumeration sequence -- ivf.py:177-193) among equal distances
+        (vdb_ivf_tc_finish) -- all on the device, one read-back (the list of queries to re-run).  Returns (dist, ids, bad):
+        ``bad`` = queries the certificate rejected or whose tie run crosses the cut; the caller re-runs them through the
+        query-major scan."""
         lm = self._list_major()
-        dev = self._device
         Q, n_probe = probes.shape
         k2 = top_k + 1                # one extra result: a tie run that crosses the cut is SEEN and sent to the query-major scan
-        pl = probes.reshape(-1).long()                                # pair p = q * n_probe + rank -> list
-        live = lm["counts"][pl] > 0
-        order = torch.argsort(pl, stable=True)
-        order = order[live[order]]                                    # pairs with a non-empty list, grouped by list
-        if order.numel() == 0:
+        if not bool(lm["any_rows"]):
             return None
-        lists_sorted = pl[order]
-        n_l = torch.bincount(lists_sorted, minlength=self.k)
-        mt_l = (n_l + 127) // 128
-        arow0 = torch.zeros(self.k + 1, dtype=torch.int64, device=dev)
-        arow0[1:] = torch.cumsum(mt_l * 128, 0)
-        grp0 = torch.zeros(self.k + 1, dtype=torch.int64, device=dev)
-        grp0[1:] = torch.cumsum(n_l, 0)
-        arow = arow0[lists_sorted] + (torch.arange(order.numel(), device=dev) - grp0[lists_sorted])
-        Qa = int(arow0[-1].item())
-        row_query = torch.full((Qa,), -1, dtype=torch.int32, device=dev)
-        row_query[arow] = (order // n_probe).to(torch.int32)
-        row_list = torch.zeros((Qa,), dtype=torch.int32, device=dev)
-        row_list[arow] = lists_sorted.to(torch.int32)
-        pair_rows = torch.full((Q * n_probe,), -1, dtype=torch.int32, device=dev)
-        pair_rows[order] = arow.to(torch.int32)
-        n_units = int(mt_l.sum().item())
-        ulist = torch.repeat_interleave(torch.arange(self.k, device=dev), mt_l)
-        u0 = torch.zeros(self.k + 1, dtype=torch.int64, device=dev)
-        u0[1:] = torch.cumsum(mt_l, 0)
-        utab = torch.zeros((n_units, 4), dtype=torch.int32, device=dev)
-        utab[:, 0] = (arow0[ulist] // 128 + (torch.arange(n_units, device=dev) - u0[ulist])).to(torch.int32)
-        utab[:, 1] = (lm["start"][ulist] // 256).to(torch.int32)
-        utab[:, 2] = ((lm["start"][ulist] + lm["padded"][ulist]) // 256).to(torch.int32)
+        row_query, row_list, pair_rows, utab, meta = ops.ivf_group_pairs(probes, lm["tile_ptr"])
         d, pos, uncert = ops.ivf_topk_tc(q, lm["vecs"], lm["mirror"], lm["stats"], None, k2, n_probe, pair_rows, row_query,
-                                         row_list, self._centroids_dev, utab, lm["list_stats"])
-        # (distance, sequence) order: sequence = candidates enumerated before the row's list + position in the list
-        valid = pos >= 0
-        p0 = pos.clamp(min=0)
-        lst = torch.searchsorted(lm["start"], p0, right=True) - 1                     # list of every result
-        rank = (probes.long().unsqueeze(1) == lst.unsqueeze(2)).to(torch.int64).argmax(dim=2)   # its rank among the probes
-        seq = torch.gather(prefix.long(), 1, rank) + (p0 - lm["start"][lst])
-        key = (d.contiguous().view(torch.int32).long() << 32) | seq                    # d >= 0: its bits sort like the value
-        key = torch.where(valid, key, torch.full_like(key, torch.iinfo(torch.int64).max))
-        sel = torch.argsort(key, dim=1, stable=True)
-        d_sorted, valid_sorted = torch.gather(d, 1, sel), torch.gather(valid, 1, sel)
-        sel = sel[:, :top_k]
-        d = d_sorted[:, :top_k]
-        ids = torch.gather(torch.where(valid, lm["ids"][p0], torch.full_like(pos, -1)), 1, sel)
-        n_bad = int(uncert[0].item())
-        bad = torch.zeros((Q,), dtype=torch.bool, device=dev)
-        if n_bad:
-            bad[uncert[1:1 + n_bad].long()] = True
-        # equal distances on both sides of the cut: which of them the reference keeps depends on rows this call did not fetch
-        bad |= valid_sorted[:, top_k] & (d_sorted[:, top_k] == d_sorted[:, top_k - 1])
-        bad = bad.nonzero().squeeze(1)
+                                         row_list, self._centroids_dev, utab, lm["list_stats"], meta=meta)
+        d, ids, tie = ops.ivf_tc_finish(d, pos, top_k, probes, prefix, lm["list_of_row"], lm["start"], lm["ids"])
+        # the ONE read-back: which queries go to the query-major scan (uncert = count + indices, tie = flag per query)
+        live = torch.arange(Q, device=q.device, dtype=torch.int32) < uncert[0]
+        tie.index_add_(0, torch.where(live, uncert[1:], torch.zeros_like(uncert[1:])).long(), live.to(torch.int32))
+        bad = (tie > 0).nonzero().squeeze(1)
         return d, ids, (bad if bad.numel() else None)
 
     def _set_centroids(self, cent: torch.Tensor) -> None:
@@ -345,10 +307,10 @@ class IvfIndex:
             flt = vec.bitmap_from_ids(filter_ids)
             alive = flt if alive is None else torch.bitwise_and(alive[:flt.numel()], flt)
         Q = q.shape[0]
-        # the list-major pass costs ~1.3 ms of grouping before its first tile; the query-major scan streams the probed rows
-        # at 1-4.5 TB/s (L2-served): "auto" takes the tensor cores from ~8 GB of probed rows (and two probes) on
+        # the list-major pass costs ~0.5 ms whatever the batch (grouping, operand rows, select / rerank / finish); the query-major
+        # scan streams the probed rows at 1-5 TB/s (L2-served): "auto" takes the tensor cores from ~3 GB of probed rows on
         probed_bytes = Q * n_probe * (vec.n / max(self.k, 1)) * vec.dim * 4
-        worth = self.batch_engine == "tc" or (n_probe >= 2 and probed_bytes >= 8e9)
+        worth = self.batch_engine == "tc" or (n_probe >= 2 and probed_bytes >= 3e9)
         if (self.batch_engine != "scan" and filter_ids is None and alive is None and n_probe <= 32 and top_k <= 10
                 and vec.dim % 8 == 0 and vec.dim <= 512 and worth):
             out = self._search_list_major(q, probes, prefix, top_k)

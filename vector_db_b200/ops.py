@@ -410,10 +410,11 @@ def tc_norm_offset(n: int, d: int) -> int:
 def ivf_topk_tc(q: torch.Tensor, lm_vecs: torch.Tensor, lm_mirror: torch.Tensor, lm_stats: torch.Tensor,
                 lm_ids: Optional[torch.Tensor], k: int, n_probe: int, pair_rows: torch.Tensor, row_query: torch.Tensor,
                 row_list: torch.Tensor, centroids: torch.Tensor, unit_table: torch.Tensor,
-                list_stats: Optional[torch.Tensor] = None):
+                list_stats: Optional[torch.Tensor] = None, meta: Optional[torch.Tensor] = None):
     """List-major IVF search on the tensor-core pipeline (vdb_ivf_topk_tc).  ``list_stats`` f32 [K, 2]: per-list row bounds
     (max |bf16(r)|, max |bf16(r) - r| over the list's residual rows r) that tighten the certificate.  Returns (dist f32 [Q,k], ids-or-positions i64
-    [Q,k], uncert i32 [Q+1] = count + indices of the queries the caller must re-run through ivf_scan)."""
+    [Q,k], uncert i32 [Q+1] = count + indices of the queries the caller must re-run through ivf_scan).  ``meta`` (from
+    ivf_group_pairs): the operand-row / unit counts live on the device and the tables are sized for the worst case."""
     q = _f32(q, "q")
     Q, D = q.shape
     N = lm_vecs.shape[0]
@@ -430,5 +431,38 @@ def ivf_topk_tc(q: torch.Tensor, lm_vecs: torch.Tensor, lm_mirror: torch.Tensor,
     ws = _ws("ivf_tc", nbytes, dev)
     check(lib.vdb_ivf_topk_tc(ptr(q), Q, ptr(lm_vecs), ptr(lm_mirror), ptr(lm_stats), ptr(lm_ids), N, D, k, n_probe,
                               ptr(pair_rows), ptr(row_query), ptr(row_list), ptr(_f32(centroids, "centroids")), Qa, ptr(unit_table), U,
-                              ptr(list_stats), ptr(out_d), ptr(out_i), ptr(uncert), ptr(ws), ws.numel(), _lib.stream_ptr(dev)))
+                              ptr(meta), ptr(list_stats), ptr(out_d), ptr(out_i), ptr(uncert), ptr(ws), ws.numel(), _lib.stream_ptr(dev)))
     return out_d, out_i, uncert
+
+
+def ivf_group_pairs(probes: torch.Tensor, list_tile_ptr: torch.Tensor):
+    """(query, probe) pairs grouped by list on the device (vdb_ivf_group_pairs) -> (row_query, row_list, pair_rows, unit_table,
+    meta), the tables sized for the worst case."""
+    Q, n_probe = probes.shape
+    K = list_tile_ptr.numel() - 1
+    P = Q * n_probe
+    qa_max = ((P + 127) // 128 + min(K, P)) * 128
+    dev = probes.device
+    row_query = torch.empty((qa_max,), dtype=torch.int32, device=dev)
+    row_list = torch.empty((qa_max,), dtype=torch.int32, device=dev)
+    pair_rows = torch.empty((P,), dtype=torch.int32, device=dev)
+    utab = torch.empty((qa_max // 128, 4), dtype=torch.int32, device=dev)
+    meta = torch.empty((2,), dtype=torch.int32, device=dev)
+    lib = load()
+    ws = _ws("ivf_group", lib.vdb_ivf_group_workspace(K), dev)
+    check(lib.vdb_ivf_group_pairs(ptr(probes), Q, n_probe, ptr(list_tile_ptr), K, qa_max, ptr(row_query), ptr(row_list), ptr(pair_rows),
+                                  ptr(utab), ptr(meta), ptr(ws), ws.numel(), _lib.stream_ptr(dev)))
+    return row_query, row_list, pair_rows, utab, meta
+
+
+def ivf_tc_finish(d: torch.Tensor, pos: torch.Tensor, top_k: int, probes: torch.Tensor, prefix: torch.Tensor, lm_list: torch.Tensor,
+                  lm_start: torch.Tensor, lm_ids: torch.Tensor):
+    """vdb_ivf_tc_finish: list-major positions -> (dist, ids) in the reference's stable order + tie flags (int32 [Q])."""
+    Q, k2 = d.shape
+    dev = d.device
+    out_d = torch.empty((Q, top_k), dtype=torch.float32, device=dev)
+    out_i = torch.empty((Q, top_k), dtype=torch.int64, device=dev)
+    tie = torch.empty((Q,), dtype=torch.int32, device=dev)
+    check(load().vdb_ivf_tc_finish(ptr(d), ptr(pos), Q, k2, top_k, ptr(probes), ptr(prefix), probes.shape[1], ptr(lm_list), ptr(lm_start),
+                                   ptr(lm_ids), ptr(out_d), ptr(out_i), ptr(tie), _lib.stream_ptr(dev)))
+    return out_d, out_i, tie
