@@ -182,6 +182,14 @@ int vdb_ivf_topk_tc(const float* q /*[dev] Q*D*/, int Q, const float* lm_vecs /*
  *     (ceil(Q n_probe / 128) + min(K, Q n_probe)) * 128 rows, unit_table has Qa_max / 128 rows of 4 ints.
  *   vdb_ivf_tc_finish: the k2 = top_k + 1 results of vdb_ivf_topk_tc (list-major positions) -> the reference's stable order
  *     (distance, enumeration sequence; ivf.py:177-193), external ids, tie[q] = 1 when equal distances straddle the cut. */
+/* Probe selection of a batch from the kc = n_probe + 4 (<= 16) nearest centroids per query returned by vdb_exact_topk_tc
+ * (L2, ids = NULL): the candidates are re-scored in numpy's summation order (ivf.py:170), queries whose n_probe-th candidate
+ * is not provably inside the candidate set are flagged and go through the full numpy-order kernels inside the call. */
+int vdb_ivf_probe_refine(const float* q /*[dev] Q*D*/, int Q, int D, const float* centroids /*[dev] K*D*/, int K,
+                         const float* cand_d /*[dev] Q*kc*/, const int64_t* cand_i /*[dev] Q*kc*/, int kc, int n_probe,
+                         const int32_t* list_ptr /*[dev] K+1 or NULL*/, int32_t* probes /*[dev] Q*n_probe*/,
+                         int32_t* prefix /*[dev] Q*(n_probe+1) or NULL*/, float* cdist_scratch /*[dev] Q*K*/,
+                         int32_t* flags /*[dev] Q*/, void* stream);
 size_t vdb_ivf_group_workspace(int K);
 int vdb_ivf_group_pairs(const int32_t* probes /*[dev] Q*n_probe*/, int Q, int n_probe, const int32_t* list_tile_ptr /*[dev] K+1*/,
                         int K, int64_t Qa_max, int32_t* row_query /*[dev] Qa_max*/, int32_t* row_list /*[dev] Qa_max*/,

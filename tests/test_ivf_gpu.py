@@ -283,3 +283,24 @@ def test_list_major_tensor_core_batch_search_equals_query_major_scan(n, dim, K, 
     np.testing.assert_array_equal(idx.last_scanned, scanned)
     assert max_bad is None or idx.last_uncertified <= int(nq * max_bad)
     assert Is[0, 0] == 17 and Ds[0, 0] == 0.0
+
+
+@pytest.mark.gpu
+def test_probe_selection_through_the_tensor_cores_equals_the_numpy_order_kernels():
+    """ops.ivf_probe_tc (n_probe + 4 nearest centroids from the tensor-core scan, re-scored in numpy's summation order, flagged
+    queries through the full kernels) must return the probes and prefix sums of ivf_probe(ivf_centroid_dist(...)) -- on
+    well-separated centroids (nothing flagged) and on centroids so close to one another that the certificate gives up."""
+    import torch
+    from vector_db_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(11)
+    for K, D, spread in ((1024, 384, 0.3), (300, 64, 1.0), (2048, 128, 1e-3)):
+        cent = torch.randn((K, D), device="cuda", generator=g) * spread
+        cent[7] = cent[3]                                           # duplicate centroid: the lower index must come first
+        q = torch.randn((2000, D), device="cuda", generator=g)
+        q[:50] = cent[torch.arange(50, device="cuda") % K] + 1e-4 * torch.randn((50, D), device="cuda", generator=g)
+        ptr = (torch.arange(K + 1, device="cuda", dtype=torch.int32) * 37).contiguous()
+        mirror, _, stats = ops.tc_prepare_rows(cent, "l2")
+        for n_probe in (1, 4, 8):
+            p0, x0 = ops.ivf_probe(ops.ivf_centroid_dist(q, cent), n_probe, ptr)
+            p1, x1, flags, _ = ops.ivf_probe_tc(q, cent, mirror, stats, n_probe, ptr)
+            assert torch.equal(p0, p1) and torch.equal(x0, x1), (K, D, spread, n_probe, int(flags.sum()))

@@ -40,6 +40,7 @@ SIGNATURES = {
     "vdb_exact_topk_tc": (_i, [_p, _i, _p, _p, _p, _p, _i64, _i, _i, _i, _p, _p, _p, _p, _sz, _p]),
     "vdb_ivf_topk_tc_workspace": (_sz, [_i, _i64, _i64, _i, _i, _i]),
     "vdb_ivf_topk_tc": (_i, [_p, _i, _p, _p, _p, _p, _i64, _i, _i, _i, _p, _p, _p, _p, _i64, _p, _i, _p, _p, _p, _p, _p, _p, _sz, _p]),
+    "vdb_ivf_probe_refine": (_i, [_p, _i, _i, _p, _i, _p, _p, _i, _i, _p, _p, _p, _p, _p, _p]),
     "vdb_ivf_group_workspace": (_sz, [_i]),
     "vdb_ivf_group_pairs": (_i, [_p, _i, _i, _p, _i, _i64, _p, _p, _p, _p, _p, _p, _sz, _p]),
     "vdb_ivf_tc_finish": (_i, [_p, _p, _i, _i, _i, _p, _p, _i, _p, _p, _p, _p, _p, _p, _p]),

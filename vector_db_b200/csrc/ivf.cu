@@ -78,7 +78,7 @@ __device__ void ivf_flatten_leaves(IvfLeaves* L, int n) {
 // shared-memory load instructions: 40 per 96 flops).
 __global__ void __launch_bounds__(kIvfCdThreads)
 ivf_centroid_dist_kernel(const float* __restrict__ q, int Q, int D, const float* __restrict__ cent, int K,
-                         float* __restrict__ out) {
+                         float* __restrict__ out, const int32_t* __restrict__ flags) {
     extern __shared__ __align__(16) float ivf_smem[];
     float* qs = ivf_smem;                                              // kIvfCdQ * D
     float* tile = qs + (size_t)kIvfCdQ * D;                            // 128 * 33
@@ -86,6 +86,11 @@ ivf_centroid_dist_kernel(const float* __restrict__ q, int Q, int D, const float*
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int c0 = blockIdx.x * kIvfCdThreads, q0 = blockIdx.y * kIvfCdQ;
     const int nq = min(kIvfCdQ, Q - q0);
+    if (flags) {                                                       // only the queries a cheaper pass could not settle
+        bool any = false;
+        for (int g = 0; g < nq; ++g) any = any || flags[q0 + g] != 0;
+        if (!any) return;
+    }
     for (int i = tid; i < kIvfCdQ * D; i += kIvfCdThreads) {
         const int g = i / D;
         qs[i] = g < nq ? q[(size_t)(q0 + g) * D + (i - g * D)] : 0.f;
@@ -224,9 +229,9 @@ constexpr int kIvfProbeWarpMaxK = 4096;
 template <int kPer>                                            // keys per lane: K <= 32 kPer
 __global__ void __launch_bounds__(256)
 ivf_probe_warp_kernel(const float* __restrict__ cdist, int Q, int K, int n_probe, const int32_t* __restrict__ list_ptr,
-                      int32_t* __restrict__ probes, int32_t* __restrict__ prefix) {
+                      int32_t* __restrict__ probes, int32_t* __restrict__ prefix, const int32_t* __restrict__ flags) {
     const int q = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
-    if (q >= Q) return;
+    if (q >= Q || (flags && flags[q] == 0)) return;
     uint32_t dk[kPer];                                         // ordered distance bits; the centroid index is t * 32 + lane
     const float* src = cdist + (size_t)q * K;
 #pragma unroll
@@ -260,6 +265,92 @@ ivf_probe_warp_kernel(const float* __restrict__ cdist, int Q, int K, int n_probe
         if (prefix) run += __ldg(list_ptr + c + 1) - __ldg(list_ptr + c);
     }
     if (prefix && lane == 0) prefix[(size_t)q * (n_probe + 1) + n_probe] = run;
+}
+
+// Probe selection through the tensor cores (batches, n_probe + 4 <= 16): vdb_exact_topk_tc gives the kc nearest centroids of
+// every query EXACTLY in the rerank's arithmetic r(.) (sequential fp32 direct differences); the probe set, however, must be
+// numpy's -- np.argsort of np.linalg.norm(centroids - q, axis=1), pairwise summation (ivf.py:170-171).  One thread per
+// (query, candidate) recomputes the candidate's distance n(.) in numpy's order; both are fp32 evaluations of the same
+// number, |n(c) - r(c)| <= eps r(c) with eps = D 2^-23 (generous).  Every centroid outside the candidates has r >= r_max,
+// hence n >= r_max (1 - eps): if the n_probe-th smallest n among the candidates is below that, numpy's n_probe nearest are
+// all candidates and their order by (n, index) is numpy's.  Otherwise the query is flagged and the full kernels decide.
+__device__ float ivf_np_dist_one(const float* __restrict__ c, const float* __restrict__ q, const IvfLeaves& L) {
+    float val[12];
+    int nv = 0;
+    for (int l = 0; l < L.n; ++l) {
+        const int s = (int)L.start[l] << 3, n = L.len[l];
+        float res;
+        if (n < 8) {
+            res = 0.f;
+            for (int t = 0; t < n; ++t) { const float d = __fsub_rn(c[s + t], q[s + t]); res = __fadd_rn(res, __fmul_rn(d, d)); }
+        } else {
+            float r[8];
+            const int main_end = n - (n % 8);
+            for (int i = 0; i < main_end; i += 8) {
+#pragma unroll
+                for (int t = 0; t < 8; ++t) {
+                    const float d = __fsub_rn(c[s + i + t], q[s + i + t]);
+                    const float v = __fmul_rn(d, d);
+                    r[t] = i == 0 ? v : __fadd_rn(r[t], v);
+                }
+            }
+            res = __fadd_rn(__fadd_rn(__fadd_rn(r[0], r[1]), __fadd_rn(r[2], r[3])), __fadd_rn(__fadd_rn(r[4], r[5]), __fadd_rn(r[6], r[7])));
+            for (int i = main_end; i < n; ++i) { const float d = __fsub_rn(c[s + i], q[s + i]); res = __fadd_rn(res, __fmul_rn(d, d)); }
+        }
+        val[nv++] = res;
+        for (int k = 0; k < (int)L.comb[l]; ++k) { val[nv - 2] = __fadd_rn(val[nv - 2], val[nv - 1]); --nv; }
+    }
+    return __fsqrt_rn(val[0]);
+}
+
+__global__ void __launch_bounds__(256)
+ivf_probe_refine_kernel(const float* __restrict__ q, int Q, int D, const float* __restrict__ cent, int K,
+                        const float* __restrict__ cand_d, const int64_t* __restrict__ cand_i, int kc, int n_probe,
+                        const int32_t* __restrict__ list_ptr, int32_t* __restrict__ probes, int32_t* __restrict__ prefix,
+                        int32_t* __restrict__ flags) {
+    __shared__ IvfLeaves leaves;
+    if (threadIdx.x == 0) ivf_flatten_leaves(&leaves, D);
+    __syncthreads();
+    const int qi = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
+    if (qi >= Q) return;
+    int c = -1;
+    float r = INFINITY, n = INFINITY;
+    if (lane < kc) {
+        const int64_t ci = cand_i[(size_t)qi * kc + lane];
+        if (ci >= 0 && ci < K) {
+            c = (int)ci;
+            r = cand_d[(size_t)qi * kc + lane];
+            n = ivf_np_dist_one(cent + (size_t)c * D, q + (size_t)qi * D, leaves);
+        }
+    }
+    const u64 key = c >= 0 ? pack_key(n, (uint32_t)c) : VDB_KEY_MAX;
+    int rank = 0;
+    float r_max = 0.f;
+    int n_valid = 0;
+    for (int j = 0; j < 32; ++j) {
+        const u64 other = __shfl_sync(0xffffffffu, key, j);
+        const float rj = __shfl_sync(0xffffffffu, r, j);
+        rank += (other < key) ? 1 : 0;
+        if (other != VDB_KEY_MAX) { r_max = fmaxf(r_max, rj); ++n_valid; }
+    }
+    // the n_probe-th smallest numpy-order distance among the candidates
+    const unsigned at = __ballot_sync(0xffffffffu, c >= 0 && rank == n_probe - 1);
+    const float n_p = at ? __shfl_sync(0xffffffffu, n, __ffs(at) - 1) : INFINITY;
+    const float eps = (float)D * 1.1920929e-7f;
+    const bool ok = n_valid >= n_probe && (n_valid >= K || n_p < r_max * (1.f - eps));
+    if (lane == 0) flags[qi] = ok ? 0 : 1;
+    if (!ok) return;
+    int run = 0;
+    for (int p = 0; p < n_probe; ++p) {
+        const unsigned own = __ballot_sync(0xffffffffu, c >= 0 && rank == p);
+        const int cp = __shfl_sync(0xffffffffu, c, __ffs(own) - 1);
+        if (lane == 0) {
+            probes[(size_t)qi * n_probe + p] = cp;
+            if (prefix) prefix[(size_t)qi * (n_probe + 1) + p] = run;
+        }
+        if (prefix) run += __ldg(list_ptr + cp + 1) - __ldg(list_ptr + cp);
+    }
+    if (prefix && lane == 0) prefix[(size_t)qi * (n_probe + 1) + n_probe] = run;
 }
 
 __device__ __forceinline__ bool ivf_bit(const uint32_t* bm, int r) { return (bm[r >> 5] >> (r & 31)) & 1u; }
@@ -440,12 +531,12 @@ static int ivf_chunk_min(int Q) { return Q >= 1024 ? 16384 : (Q >= 128 ? 2048 : 
 //   ivf_group_scatter_kernel  every pair takes the next operand row of its list (order inside a list is immaterial)
 //   ivf_tc_finish_kernel      one warp per query: list-major positions -> (distance, enumeration sequence) order of
 //                             ivf.py:177-193, external ids, and a flag when equal distances straddle the cut
-__global__ void ivf_group_count_kernel(const int32_t* __restrict__ probes, int P, const int32_t* __restrict__ tile_ptr,
+__global__ void ivf_group_count_kernel(const int32_t* __restrict__ probes, int P, const int32_t* __restrict__ tile_ptr, int K,
                                        int32_t* __restrict__ n_l) {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= P) return;
     const int l = probes[p];
-    if (tile_ptr[l + 1] > tile_ptr[l]) atomicAdd(n_l + l, 1);
+    if ((unsigned)l < (unsigned)K && tile_ptr[l + 1] > tile_ptr[l]) atomicAdd(n_l + l, 1);     // a list id out of range probes nothing
 }
 
 __global__ void __launch_bounds__(1024)
@@ -490,7 +581,7 @@ ivf_group_plan_kernel(const int32_t* __restrict__ n_l, const int32_t* __restrict
     if (tid == 0) { meta[0] = base_s * 128; meta[1] = base_s; }
 }
 
-__global__ void ivf_group_scatter_kernel(const int32_t* __restrict__ probes, int P, int n_probe,
+__global__ void ivf_group_scatter_kernel(const int32_t* __restrict__ probes, int P, int n_probe, int K,
                                          const int32_t* __restrict__ tile_ptr, const int32_t* __restrict__ arow0,
                                          int32_t* __restrict__ cursor, int32_t* __restrict__ row_query,
                                          int32_t* __restrict__ row_list, int32_t* __restrict__ pair_rows) {
@@ -498,7 +589,7 @@ __global__ void ivf_group_scatter_kernel(const int32_t* __restrict__ probes, int
     if (p >= P) return;
     const int l = probes[p];
     int arow = -1;
-    if (tile_ptr[l + 1] > tile_ptr[l]) {
+    if ((unsigned)l < (unsigned)K && tile_ptr[l + 1] > tile_ptr[l]) {
         arow = arow0[l] + atomicAdd(cursor + l, 1);
         row_query[arow] = p / n_probe;
         row_list[arow] = l;
@@ -567,7 +658,7 @@ int vdb_ivf_centroid_dist(const float* q, int Q, int D, const float* centroids, 
     const size_t smem = ((size_t)kIvfCdQ * D + (size_t)kIvfCdThreads * kIvfCdStride) * 4;
     VDB_CUDA(cudaFuncSetAttribute(ivf_centroid_dist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid((K + kIvfCdThreads - 1) / kIvfCdThreads, (Q + kIvfCdQ - 1) / kIvfCdQ);
-    ivf_centroid_dist_kernel<<<grid, kIvfCdThreads, smem, static_cast<cudaStream_t>(stream)>>>(q, Q, D, centroids, K, out);
+    ivf_centroid_dist_kernel<<<grid, kIvfCdThreads, smem, static_cast<cudaStream_t>(stream)>>>(q, Q, D, centroids, K, out, nullptr);
     count_launch(1);
     VDB_CUDA(cudaGetLastError());
     return VDB_OK;
@@ -582,9 +673,9 @@ int vdb_ivf_probe(const float* cdist, int Q, int K, int n_probe, const int32_t* 
     VDB_REQUIRE(cdist && probes && (!prefix || list_ptr), VDB_ERR_INVALID, "vdb_ivf_probe: null pointer");
     if (n_probe <= 32 && K <= kIvfProbeWarpMaxK && K >= n_probe && Q >= 64) {
         cudaStream_t st = static_cast<cudaStream_t>(stream);
-        if (K <= 1024) ivf_probe_warp_kernel<32><<<(Q + 7) / 8, 256, 0, st>>>(cdist, Q, K, n_probe, list_ptr, probes, prefix);
-        else if (K <= 2048) ivf_probe_warp_kernel<64><<<(Q + 7) / 8, 256, 0, st>>>(cdist, Q, K, n_probe, list_ptr, probes, prefix);
-        else ivf_probe_warp_kernel<128><<<(Q + 7) / 8, 256, 0, st>>>(cdist, Q, K, n_probe, list_ptr, probes, prefix);
+        if (K <= 1024) ivf_probe_warp_kernel<32><<<(Q + 7) / 8, 256, 0, st>>>(cdist, Q, K, n_probe, list_ptr, probes, prefix, nullptr);
+        else if (K <= 2048) ivf_probe_warp_kernel<64><<<(Q + 7) / 8, 256, 0, st>>>(cdist, Q, K, n_probe, list_ptr, probes, prefix, nullptr);
+        else ivf_probe_warp_kernel<128><<<(Q + 7) / 8, 256, 0, st>>>(cdist, Q, K, n_probe, list_ptr, probes, prefix, nullptr);
         count_launch(1);
         VDB_CUDA(cudaGetLastError());
         return VDB_OK;
@@ -648,6 +739,31 @@ int vdb_ivf_centroid_mean(const float* x, int D, const int32_t* list_ptr, const 
     return VDB_OK;
 }
 
+// Probes of a batch from the kc nearest centroids per query found by vdb_exact_topk_tc (cand_d / cand_i, L2, ids = NULL):
+// numpy-order re-check of the candidates (ivf_probe_refine_kernel), then the full numpy-order kernels for the flagged
+// queries only.  cdist_scratch: Q*K floats (written for flagged queries only); flags: Q ints.
+int vdb_ivf_probe_refine(const float* q, int Q, int D, const float* centroids, int K, const float* cand_d, const int64_t* cand_i,
+                         int kc, int n_probe, const int32_t* list_ptr, int32_t* probes, int32_t* prefix, float* cdist_scratch,
+                         int32_t* flags, void* stream) {
+    VDB_REQUIRE(Q > 0 && D > 0 && K > 0 && kc > 0 && kc <= 32 && n_probe >= 1 && n_probe <= kc && n_probe <= K, VDB_ERR_INVALID,
+                "vdb_ivf_probe_refine: bad shape (kc=%d n_probe=%d K=%d)", kc, n_probe, K);
+    VDB_REQUIRE(q && centroids && cand_d && cand_i && probes && cdist_scratch && flags && (!prefix || list_ptr), VDB_ERR_INVALID,
+                "vdb_ivf_probe_refine: null pointer");
+    VDB_REQUIRE(D <= 8192 && K <= kIvfProbeWarpMaxK && Q <= 65535 * kIvfCdQ, VDB_ERR_UNSUPPORTED, "vdb_ivf_probe_refine: D=%d K=%d Q=%d", D, K, Q);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    ivf_probe_refine_kernel<<<(Q + 7) / 8, 256, 0, st>>>(q, Q, D, centroids, K, cand_d, cand_i, kc, n_probe, list_ptr, probes, prefix, flags);
+    const size_t smem = ((size_t)kIvfCdQ * D + (size_t)kIvfCdThreads * kIvfCdStride) * 4;
+    VDB_CUDA(cudaFuncSetAttribute(ivf_centroid_dist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    dim3 grid((K + kIvfCdThreads - 1) / kIvfCdThreads, (Q + kIvfCdQ - 1) / kIvfCdQ);
+    ivf_centroid_dist_kernel<<<grid, kIvfCdThreads, smem, st>>>(q, Q, D, centroids, K, cdist_scratch, flags);
+    if (K <= 1024) ivf_probe_warp_kernel<32><<<(Q + 7) / 8, 256, 0, st>>>(cdist_scratch, Q, K, n_probe, list_ptr, probes, prefix, flags);
+    else if (K <= 2048) ivf_probe_warp_kernel<64><<<(Q + 7) / 8, 256, 0, st>>>(cdist_scratch, Q, K, n_probe, list_ptr, probes, prefix, flags);
+    else ivf_probe_warp_kernel<128><<<(Q + 7) / 8, 256, 0, st>>>(cdist_scratch, Q, K, n_probe, list_ptr, probes, prefix, flags);
+    count_launch(3);
+    VDB_CUDA(cudaGetLastError());
+    return VDB_OK;
+}
+
 size_t vdb_ivf_group_workspace(int K) { return ivf_al((size_t)K * 4) * 3 + 256; }
 
 int vdb_ivf_group_pairs(const int32_t* probes, int Q, int n_probe, const int32_t* list_tile_ptr, int K, int64_t Qa_max,
@@ -671,9 +787,9 @@ int vdb_ivf_group_pairs(const int32_t* probes, int Q, int n_probe, const int32_t
     VDB_CUDA(cudaMemsetAsync(n_l, 0, (size_t)K * 4, st));
     VDB_CUDA(cudaMemsetAsync(cursor, 0, (size_t)K * 4, st));
     VDB_CUDA(cudaMemsetAsync(row_query, 0xFF, (size_t)Qa_max * 4, st));      // -1: padding of the operand tiles
-    ivf_group_count_kernel<<<(P + 255) / 256, 256, 0, st>>>(probes, P, list_tile_ptr, n_l);
+    ivf_group_count_kernel<<<(P + 255) / 256, 256, 0, st>>>(probes, P, list_tile_ptr, K, n_l);
     ivf_group_plan_kernel<<<1, 1024, 0, st>>>(n_l, list_tile_ptr, K, arow0, reinterpret_cast<int4*>(unit_table), meta);
-    ivf_group_scatter_kernel<<<(P + 255) / 256, 256, 0, st>>>(probes, P, n_probe, list_tile_ptr, arow0, cursor, row_query, row_list, pair_rows);
+    ivf_group_scatter_kernel<<<(P + 255) / 256, 256, 0, st>>>(probes, P, n_probe, K, list_tile_ptr, arow0, cursor, row_query, row_list, pair_rows);
     count_launch(3);
     VDB_CUDA(cudaGetLastError());
     return VDB_OK;

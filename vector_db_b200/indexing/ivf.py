@@ -158,6 +158,32 @@ class IvfIndex:
         bad = (tie > 0).nonzero().squeeze(1)
         return d, ids, (bad if bad.numel() else None)
 
+    def _probe(self, q: torch.Tensor, n_probe: int, ptr: torch.Tensor):
+        """np.argsort(np.linalg.norm(centroids - q, axis=1))[:n_probe] per query (ivf.py:170-171) + candidate prefix sums.
+        Batches with few probes go through the tensor cores (candidates re-scored in numpy's order, ops.ivf_probe_tc)."""
+        cent = self._centroids_dev
+        Q, D = q.shape
+        K = cent.shape[0]
+        kc = n_probe + 4
+        if (Q >= 512 and kc <= 12 and 256 <= K <= 4096 and D % 8 == 0 and D <= 8192
+                and ops.tc_shape_supported(Q, K, D, kc, "l2")):
+            cm = getattr(self, "_cent_mirror", None)
+            if cm is None or cm["cent"] is not cent:
+                mirror, _, stats = ops.tc_prepare_rows(cent, "l2")
+                cm = self._cent_mirror = {"cent": cent, "mirror": mirror, "stats": stats, "use": None, "calls": 0}
+            # Whether the coarse pass can separate the probe boundary depends on the geometry (centroids of unclustered rows
+            # sit near the origin: all distances ~ |q|, the bf16 certificate fails and the scan's fp32 rescan costs more than
+            # the numpy-order kernels).  Decided by measurement: the first eligible batch (and every 256th) reads back how many
+            # queries needed the rescan / the fallback; above 2 % the tensor-core probing is switched off for this index.
+            if cm["use"] is not False:
+                probes, prefix, flags, n_unc = ops.ivf_probe_tc(q, cent, cm["mirror"], cm["stats"], n_probe, ptr)
+                if cm["use"] is None or cm["calls"] % 256 == 0:
+                    slow = int(n_unc.item()) + int(flags.sum().item())
+                    cm["use"] = slow * 50 <= Q
+                cm["calls"] += 1
+                return probes, prefix
+        return ops.ivf_probe(ops.ivf_centroid_dist(q, cent), n_probe, ptr)
+
     def _set_centroids(self, cent: torch.Tensor) -> None:
         self._centroids_dev = cent.contiguous()
         self.centroids = cent.cpu().numpy()
@@ -300,8 +326,7 @@ class IvfIndex:
         """Device in / device out: (dist, ids, candidates enumerated per query)."""
         ptr, rows = self._csr()
         vec = self._vectors
-        cdist = ops.ivf_centroid_dist(q, self._centroids_dev)
-        probes, prefix = ops.ivf_probe(cdist, n_probe, ptr)
+        probes, prefix = self._probe(q, n_probe, ptr)
         alive = vec.alive if vec.n_dead else None
         if filter_ids is not None:
             flt = vec.bitmap_from_ids(filter_ids)

@@ -186,6 +186,26 @@ def ivf_probe(cdist: torch.Tensor, n_probe: int, list_ptr: Optional[torch.Tensor
     return probes, prefix
 
 
+def ivf_probe_tc(q: torch.Tensor, centroids: torch.Tensor, cent_mirror: torch.Tensor, cent_stats: torch.Tensor, n_probe: int,
+                 list_ptr: Optional[torch.Tensor] = None):
+    """The same (probes, prefix) as ivf_probe(ivf_centroid_dist(q, centroids), n_probe, list_ptr) for a batch: the n_probe + 4
+    nearest centroids per query from the tensor-core scan, re-scored in numpy's order (vdb_ivf_probe_refine).  Also returns the
+    per-query fallback flags and the 0-dim device count of queries the scan's certificate sent through its fp32 rescan."""
+    q = _f32(q, "q")
+    Q, D = q.shape
+    K = centroids.shape[0]
+    kc = min(K, n_probe + 4)
+    cd, ci, n_unc = exact_topk_tc(q, centroids, cent_mirror, cent_stats, kc, "l2", return_uncertified=True)
+    dev = q.device
+    probes = torch.empty((Q, n_probe), dtype=torch.int32, device=dev)
+    prefix = torch.empty((Q, n_probe + 1), dtype=torch.int32, device=dev) if list_ptr is not None else None
+    scratch = _ws("ivf_cdist", Q * K * 4, dev)
+    flags = torch.empty((Q,), dtype=torch.int32, device=dev)
+    check(load().vdb_ivf_probe_refine(ptr(q), Q, D, ptr(_f32(centroids, "centroids")), K, ptr(cd), ptr(ci), kc, n_probe, ptr(list_ptr),
+                                      ptr(probes), ptr(prefix), ptr(scratch), ptr(flags), _lib.stream_ptr(dev)))
+    return probes, prefix, flags, n_unc
+
+
 def ivf_scan(q: torch.Tensor, db: torch.Tensor, list_ptr: torch.Tensor, list_rows: torch.Tensor, probes: torch.Tensor,
              prefix: torch.Tensor, k: int, alive: Optional[torch.Tensor] = None, ids: Optional[torch.Tensor] = None,
              return_scanned: bool = False):
@@ -352,6 +372,11 @@ def tc_supported(Q: int, N: int, D: int, k: int, metric=METRIC_L2) -> bool:
         return False          # tiny problems: the fp32 scan is already launch-bound (k-means assignment of many
                               # rows to a few hundred centroids is not tiny: 7.5 ms against 20-40 ms per 200k rows)
     return bool(load().vdb_exact_topk_tc_supported(int(Q), int(N), int(D), int(k), _metric(metric)))
+
+
+def tc_shape_supported(Q: int, N: int, D: int, k: int, metric=METRIC_L2) -> bool:
+    """vdb_exact_topk_tc_supported alone (tc_supported adds a "worth it" size rule)."""
+    return Q > 0 and N >= 256 and bool(load().vdb_exact_topk_tc_supported(int(Q), int(N), int(D), int(k), _metric(metric)))
 
 
 def tc_prepare_rows(vecs: torch.Tensor, metric=METRIC_L2):
