@@ -2,7 +2,8 @@
 """Benchmark of the search hot path (BASELINE.json metric: QPS @ recall@10 >= 0.95, 1M x 384, k = 10).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
-                    [--workload exact|pq_encode|adc_scan|hnsw_search|sharded_adc] [--paths all|none|a,b,...]
+                    [--workload exact|hnsw_small|pq_encode|adc_scan|hnsw_search|ivf_search|staging|sharded_adc]
+                    [--paths all|none|a,b,...]
 
 One "step" = one pass of the hot path over one batch of synthetic input.  The HEADLINE (default workload
 `exact`) is BASELINE.json configs[1]: exact brute-force cosine top-10 over 1M x 384 fp32 rows per GPU with a
@@ -12,9 +13,9 @@ GPU -- weak scaling.  `value` counts queries/s x 1M-row shards in BOTH arms (the
 N x 1M rows and multiplies by N as well), `queries_per_s_real` is the plain rate.
 
 Besides the headline the same JSON line carries `paths`: every other BASELINE.json config measured in the same
-run on rank 0 -- `pq_encode` (configs[2] encode, 10M x 384, m = 48), `adc_scan` (configs[2] scan, 10M x 48 codes,
+run on rank 0 -- `hnsw_small` (configs[0]: HNSW build + search on 10k x 384), `pq_encode` (configs[2] encode, 10M x 384, m = 48), `adc_scan` (configs[2] scan, 10M x 48 codes,
 Q = 1024, plus the shortlist + rerank point that reaches recall@10 >= 0.95), `hnsw_search` (configs[3], 1M x 768,
-M = 32, ef = 128), `staging` (the memmap -> HBM upload) at N = 1, and `sharded_adc` (configs[4], 100M x 128, m = 16,
+M = 32, ef = 128), `ivf_search` (batched IVF on the tensor cores), `staging` (the memmap -> HBM upload) at N = 1, and `sharded_adc` (configs[4], 100M x 128, m = 16,
 STRONG scaling: the same 100M codes at every N) at every N.  Each entry has kernel_ms (CUDA events), roofline,
 cpu_baseline (the oracle restatement timed in this run), e2e (host buffers through the host API) and parity
 (id EQUALITY against the oracle on a sample).  `--workload X` promotes one of them to the headline.
@@ -553,6 +554,77 @@ def path_hnsw_search(dev, peaks):
     }
 
 
+def path_hnsw_small(dev, peaks):
+    """BASELINE configs[0], the reference's own CPU-runnable case: HNSW M = 16, ef_construction = 200, ef_search = 64, build +
+    search on 10k random 384-d vectors, 100 queries, k = 10.  Build = the sequential-semantics insert kernel (the graph equals
+    the reference's link for link -- pinned on smaller reference-built graphs by tests/golden/hnsw_*.npz); parity of the search
+    = the reference's search (oracle restatement of hnsw.py:330-374) on the SAME graph."""
+    import random
+
+    import torch
+
+    from oracle.hnsw_oracle import search_arrays
+    from vector_db_b200.indexing import HNSW, ExactIndex
+    from vector_db_b200.types import Node
+    N, D, M, efc, ef, Q = 10_000, 384, 16, 200, 64, 100
+    rng = np.random.default_rng(SEED_DB)
+    X = rng.standard_normal((N, D), dtype=np.float32)
+    Qh = np.random.default_rng(SEED_Q).standard_normal((Q, D), dtype=np.float32)
+    idx = HNSW(M=M, ef_construction=efc, rng=random.Random(42), device=dev)
+    t0 = time.perf_counter()
+    idx.build_index([Node(id=i, embedding=X[i]) for i in range(N)])
+    torch.cuda.synchronize()
+    build_s = time.perf_counter() - t0
+    build_evals = idx.distance_evaluations()
+    idx.search_batch(Qh, K, ef=ef)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    reps = 20
+    for _ in range(reps):
+        d_h, i_h = idx.search_batch(Qh, K, ef=ef)
+    e2e_dt = (time.perf_counter() - t0) / reps
+    vec = idx._vectors
+    entry_row, top = idx._read_state()
+    from vector_db_b200 import ops
+    Qd = torch.from_numpy(Qh).to(dev)
+    (_, _, st), step_ms, prof = _timed(lambda: ops.hnsw_search(Qd, vec.vecs, vec.n, idx._adj0, idx._adj_up, idx._up_ptr_dev, entry_row,
+                                                             top, ef, K, want_stats=True, levels=idx._levels_dev),
+                                       iters=20, warm=3, slots=("hnsw_search",))
+    st_h = st.cpu().numpy().astype(np.int64)
+    adj0, adj_up, up_ptr, _, _ = idx._host_graph()
+    t0 = time.perf_counter()
+    same, ev_same, ref_rows = 0, 0, []
+    for j in range(Q):
+        res, ev = search_arrays(X, adj0, up_ptr, adj_up, entry_row, top, Qh[j], K, ef)
+        ref_rows.append([rr for _, rr in res] + [-1] * (K - len(res)))
+        same += int(ref_rows[-1] == i_h[j].tolist())
+        ev_same += int(ev == int(st_h[j, 0]))
+    cpu_s = time.perf_counter() - t0
+    ex = ExactIndex(D, "l2", device=dev)
+    ex.add(range(N), X)
+    _, truth = ex.search(Qh, K)
+    rec = float(np.mean([len(set(i_h[j]) & set(truth[j])) / K for j in range(Q)]))
+    return {
+        "config": {"workload": f"HNSW build + search, {N} x {D} fp32, M={M}, ef_construction={efc}, ef_search={ef}, {Q} queries, "
+                               f"k={K} (BASELINE.json configs[0])",
+                   "build": f"sequential-semantics insert kernel: {build_s:.1f} s = {N / build_s:.0f} inserts/s, "
+                            f"{build_evals} distance evaluations (the reference's Python build: ~52 inserts/s, BASELINE.md 2)"},
+        "metric": "queries/s", "value": Q / (step_ms * 1e-3), "unit": "queries/s", "ms_per_step": step_ms,
+        "kernel": "hnsw_search_kernel", "kernel_ms": prof["hnsw_search"][0], "dtype": "f32",
+        "build_seconds": build_s, "inserts_per_s": N / build_s,
+        "evals_per_query": float(st_h[:, 0].mean()), "recall_at_10_vs_exact": rec,
+        "roofline": None,
+        "cpu_baseline": {"value": Q / cpu_s, "unit": "queries/s", "cores": 1, "kind": "port",
+                         "sample": f"oracle.hnsw_oracle.search_arrays (hnsw.py:330-374 restated) on the {Q} queries, same graph, {cpu_s:.2f} s"},
+        "e2e": {"value": Q / e2e_dt, "unit": "queries/s", "h2d_bytes_per_step": int(Q * D * 4), "d2h_bytes_per_step": int(Q * K * 12),
+                "api": "HNSW.search_batch: numpy queries in, numpy (dist, ids) out"},
+        "parity": {"checked_queries": Q, "ids_equal": bool(same == Q), "identical_result_lists": same,
+                   "identical_eval_counts": ev_same,
+                   "oracle": "the reference's search restated, same graph; the graph itself is the reference's (insert kernel with "
+                             "sequential semantics, pinned by tests/golden/hnsw_*.npz and test_gpu_build_equals_reference_graph)"},
+    }
+
+
 def path_ivf_search(dev, peaks):
     """SURVEY.md 8f rank 3 (widening beyond BASELINE.json): batched IVF search, 1M x 384, K = 1024 lists, 4096 queries, k = 10:
     the list-major tensor-core engine (vdb_ivf_topk_tc) against the query-major fp32 list scan (vdb_ivf_scan); parity = the
@@ -825,7 +897,7 @@ def path_sharded_adc(dev, peaks, rank, world, peer_ok):
     }
 
 
-PATHS = ("pq_encode", "adc_scan", "hnsw_search", "ivf_search", "staging", "sharded_adc")
+PATHS = ("hnsw_small", "pq_encode", "adc_scan", "hnsw_search", "ivf_search", "staging", "sharded_adc")
 
 
 def run_paths(which, dev, peaks, rank, world):
@@ -847,6 +919,8 @@ def run_paths(which, dev, peaks, rank, world):
             out[name] = r
 
     single = rank == 0 and world == 1
+    if single and "hnsw_small" in which:
+        guarded("hnsw_small", lambda: path_hnsw_small(dev, peaks))
     if single and ("pq_encode" in which or "adc_scan" in which):
         guarded("pq_encode", lambda: path_pq_encode(dev, peaks, keep_codes=state))
     if single and "adc_scan" in which and "codes" in state:
