@@ -285,6 +285,7 @@ int vdb_hnsw_search(const float* q, int Q, const float* db, int64_t N, int D,
 void vdb_debug_set_hnsw_smem_hash_limit(int bytes);
 /* bench/debug only: resident CTAs per SM the search grid is sized for (default 12, at most 16) */
 void vdb_debug_set_hnsw_ctas_per_sm(int n);
+void vdb_debug_set_hnsw_insert_threads(int n);   /* 128 (default) | 256 | 512 threads of the sequential insert CTA */
 
 /* ---- a7 HNSW construction ----------------------------------------------------------------------
  * Sequential-semantics insert of rows first..first+count-1 (their vectors already in `db`, their

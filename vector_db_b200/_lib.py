@@ -62,6 +62,7 @@ SIGNATURES = {
                              _p, _p, _p, _p, _p, _sz, _p]),
     "vdb_debug_set_hnsw_smem_hash_limit": (None, [_i]),
     "vdb_debug_set_hnsw_ctas_per_sm": (None, [_i]),
+    "vdb_debug_set_hnsw_insert_threads": (None, [_i]),
     "vdb_hnsw_insert_workspace": (_sz, [_i, _i]),
     "vdb_hnsw_insert": (_i, [_p, _i64, _i, _p, _i, _p, _i, _p, _p, C.c_int32, C.c_int32, _i, _i, _p, _p,
                              _p, _sz, _p]),

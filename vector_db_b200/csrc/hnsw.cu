@@ -446,7 +446,10 @@ __device__ __forceinline__ int32_t* nbr_list_rw(const Graph& g, int node, int le
     return const_cast<int32_t*>(nbr_list(g, node, level, deg));
 }
 
-__global__ void __launch_bounds__(kHnswThreads)
+// NT threads: the insert is ONE CTA of serial steps (sequential semantics), so the only parallelism is inside a step --
+// rows evaluated per round (one warp each), rank sorts, list copies.
+template <int NT>
+__global__ void __launch_bounds__(NT)
 hnsw_insert_kernel(Graph g, const int32_t* __restrict__ levels, int32_t first, int32_t count, int M, int efc,
                    int32_t* __restrict__ state, int CC, int NM, int H, uint32_t* global_hash,
                    int* __restrict__ overflow_flag) {
@@ -462,7 +465,7 @@ hnsw_insert_kernel(Graph g, const int32_t* __restrict__ levels, int32_t first, i
         const int node = first + it;
         const int lvl = levels[node];
         __syncthreads();
-        for (int t = tid; t < g.D; t += kHnswThreads) m.qs[t] = g.db[(size_t)node * g.D + t];
+        for (int t = tid; t < g.D; t += NT) m.qs[t] = g.db[(size_t)node * g.D + t];
         const int entry = ((volatile int32_t*)state)[0], top = ((volatile int32_t*)state)[1];
         __syncthreads();
         if (entry < 0) {                       // first node: becomes the entry point, no links
@@ -472,16 +475,16 @@ hnsw_insert_kernel(Graph g, const int32_t* __restrict__ levels, int32_t first, i
         }
         unsigned evals = 0, expansions = 0;
         int cur = entry;
-        for (int level = top; level > lvl; --level) cur = greedy_level<kHnswThreads>(g, m, cur, level, &evals);
+        for (int level = top; level > lvl; --level) cur = greedy_level<NT>(g, m, cur, level, &evals);
         for (int level = (lvl < top ? lvl : top); level >= 0; --level) {
             int wf = 0;
-            const int nf = beam_search<kHnswThreads>(g, m, cur, level, efc, nullptr, &wf, &evals, &expansions);
+            const int nf = beam_search<NT>(g, m, cur, level, efc, nullptr, &wf, &evals, &expansions);
             if (m.scal[1] && tid == 0) atomicOr(overflow_flag, 1);
             const u64* found = m.found[wf];
             const int nsel = nf < M ? nf : M;
             int deg;
             int32_t* mine = nbr_list_rw(g, node, level, &deg);
-            for (int t = tid; t < deg; t += kHnswThreads) mine[t] = t < nsel ? (int32_t)key_index(found[t]) : -1;
+            for (int t = tid; t < deg; t += NT) mine[t] = t < nsel ? (int32_t)key_index(found[t]) : -1;
             __threadfence();
             __syncthreads();
             for (int sidx = 0; sidx < nsel; ++sidx) {
@@ -494,10 +497,10 @@ hnsw_insert_kernel(Graph g, const int32_t* __restrict__ levels, int32_t first, i
                     __syncthreads();
                 } else {
                     // truncate to the `cap` closest of (old links + new node), measured from nb
-                    for (int t = tid; t < g.D; t += kHnswThreads) qs2[t] = g.db[(size_t)nb * g.D + t];
+                    for (int t = tid; t < g.D; t += NT) qs2[t] = g.db[(size_t)nb * g.D + t];
                     __syncthreads();
                     if (tid == 0) m.scal[0] = 0;
-                    for (int c = warp; c <= cap; c += kHnswWarps) {
+                    for (int c = warp; c <= cap; c += (NT / 32)) {
                         const int other = c < cap ? __ldcg(lst + c) : node;
                         u64 key = VDB_KEY_MAX;
                         if (other >= 0 && (g.alive == nullptr || bit_set(g.alive, other))) {
@@ -511,7 +514,7 @@ hnsw_insert_kernel(Graph g, const int32_t* __restrict__ levels, int32_t first, i
                     int valid = 0;
                     for (int c = 0; c < n; ++c) valid += (m.newk[c] != VDB_KEY_MAX) ? 1 : 0;
                     evals += (unsigned)valid;
-                    for (int c = tid; c < n; c += kHnswThreads) {
+                    for (int c = tid; c < n; c += NT) {
                         const u64 me = m.newk[c];
                         if (me != VDB_KEY_MAX) {
                             int rank = 0;
@@ -521,7 +524,7 @@ hnsw_insert_kernel(Graph g, const int32_t* __restrict__ levels, int32_t first, i
                     }
                     __syncthreads();
                     const int keep = valid < cap ? valid : cap;
-                    for (int t = tid; t < cap; t += kHnswThreads) lst[t] = t < keep ? (int32_t)key_index(m.news[t]) : -1;
+                    for (int t = tid; t < cap; t += NT) lst[t] = t < keep ? (int32_t)key_index(m.news[t]) : -1;
                     __threadfence();
                     __syncthreads();
                 }
@@ -649,6 +652,7 @@ hnsw_reverse_merge_kernel(int32_t* __restrict__ adj, float* __restrict__ adjd, i
     }
 }
 
+static int g_hnsw_insert_threads = 256;          // threads of the single insert CTA (debug setter below)
 static int g_hnsw_ctas_per_sm = 12;              // resident CTAs per SM the search grid is sized for (debug setter below)
 static int g_hnsw_smem_hash_limit = 48 * 1024;   // visited hash stays in shared memory only below this CTA footprint
 static int pick_hash_slots(int ef, int deg) {
@@ -665,6 +669,7 @@ using namespace vdb;
 extern "C" {
 
 void vdb_debug_set_hnsw_smem_hash_limit(int bytes) { g_hnsw_smem_hash_limit = bytes; }
+void vdb_debug_set_hnsw_insert_threads(int n) { g_hnsw_insert_threads = (n == 256 || n == 512) ? n : (n == 128 ? 128 : 256); }
 void vdb_debug_set_hnsw_ctas_per_sm(int n) { g_hnsw_ctas_per_sm = n < 1 ? 1 : (n > 16 ? 16 : n); }
 
 size_t vdb_hnsw_search_workspace(int Q, int ef, int deg0) {
@@ -813,11 +818,20 @@ int vdb_hnsw_insert(const float* db, int64_t N, int D, int32_t* adj0, int deg0, 
         VDB_REQUIRE(ws_bytes >= 256 + (size_t)H * 4, VDB_ERR_WORKSPACE, "workspace too small");
         ghash = reinterpret_cast<uint32_t*>(static_cast<char*>(ws) + 256);
     }
-    VDB_CUDA(cudaFuncSetAttribute(hnsw_insert_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int nt = g_hnsw_insert_threads;
     // the overflow flag (first word of ws) is STICKY over the chunks of a build: the caller zeroes it once before
     // the first chunk and reads it once after the last (a per-call memset erased an overflow of an earlier chunk)
     ProfScope prof(kProfHnswInsert, st);
-    hnsw_insert_kernel<<<1, kHnswThreads, smem, st>>>(g, levels, first, count, M, efc, state, CC, NM, H, ghash, flag);
+    if (nt == 512) {
+        VDB_CUDA(cudaFuncSetAttribute(hnsw_insert_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        hnsw_insert_kernel<512><<<1, 512, smem, st>>>(g, levels, first, count, M, efc, state, CC, NM, H, ghash, flag);
+    } else if (nt == 256) {
+        VDB_CUDA(cudaFuncSetAttribute(hnsw_insert_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        hnsw_insert_kernel<256><<<1, 256, smem, st>>>(g, levels, first, count, M, efc, state, CC, NM, H, ghash, flag);
+    } else {
+        VDB_CUDA(cudaFuncSetAttribute(hnsw_insert_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        hnsw_insert_kernel<128><<<1, 128, smem, st>>>(g, levels, first, count, M, efc, state, CC, NM, H, ghash, flag);
+    }
     count_launch(1);
     VDB_CUDA(cudaGetLastError());
     return VDB_OK;
