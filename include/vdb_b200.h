@@ -253,6 +253,10 @@ size_t vdb_pq_adc_topk_workspace(int Q, int64_t N, int m, int R);
 int vdb_pq_adc_topk(const uint8_t* codes /*[dev] N*m*/, int64_t N, int m, const float* lut, int Q, int R,
                     const int64_t* ids, const uint32_t* row_mask /*[dev] nullable*/, float* out_d /*[dev] Q*R*/,
                     int64_t* out_i /*[dev] Q*R*/, void* ws, size_t ws_bytes, void* stream);
+/* Debug/A-B switch: 1 (default) = the threshold-collect pass runs on 16-bit lower-bound tables, eight queries per
+ * shared-memory lookup, and the collected rows are re-evaluated on the 32-bit tables (same result, bit for bit);
+ * 0 = the collect pass itself uses the 32-bit tables, four queries per lookup. */
+void vdb_debug_set_adc_coarse(int on);
 
 /* ---- a4/a5/a6 batched HNSW search -------------------------------------------------------------
  * One CTA per query: greedy descent on levels max_level..1 (hnsw.py:289-328, strict '<'), then the
@@ -285,7 +289,7 @@ int vdb_hnsw_search(const float* q, int Q, const float* db, int64_t N, int D,
 void vdb_debug_set_hnsw_smem_hash_limit(int bytes);
 /* bench/debug only: resident CTAs per SM the search grid is sized for (default 12, at most 16) */
 void vdb_debug_set_hnsw_ctas_per_sm(int n);
-void vdb_debug_set_hnsw_insert_threads(int n);   /* 128 (default) | 256 | 512 threads of the sequential insert CTA */
+void vdb_debug_set_hnsw_insert_threads(int n);   /* 128 | 256 (default) | 512 threads of the sequential insert CTA */
 
 /* ---- a7 HNSW construction ----------------------------------------------------------------------
  * Sequential-semantics insert of rows first..first+count-1 (their vectors already in `db`, their

@@ -268,3 +268,51 @@ def test_f16_accumulator_encode_equals_fp32_accumulator_kernel_and_handles_rows_
                 np.testing.assert_array_equal(got[1][:64], O.pq_encode(X[:64], list(cb)))
     finally:
         lib.vdb_debug_set_pq_tc_mode(1)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,m,q,R,kind", [(80_000, 48, 19, 10, "plain"), (80_000, 16, 9, 100, "tail"), (60_000, 7, 8, 10, "plain"),
+                                           (50_000, 64, 11, 10, "tail"), (80_000, 16, 13, 10, "dup"), (70_000, 24, 6, 900, "mask"),
+                                           (80_000, 48, 17, 10, "const")])
+def test_adc_collect_on_16bit_lower_bound_tables_equals_the_32bit_collect_and_the_oracle(n, m, q, R, kind):
+    """More than four queries: the collect pass tests rows against 15-bit lower-bound tables (eight queries per
+    shared-memory lookup, adc_coarse_collect_kernel) and re-evaluates the collected rows on the 32-bit tables.
+    Same (d_int, row) keys as the 32-bit collect, hence the oracle's result bit for bit -- on heavy-tailed tables
+    (entries clipped at the threshold budget), duplicates (buffer overflow -> device-side rescan), a row mask,
+    constant tables (every row ties), ragged query groups and m outside the unrolled cases (7; 64 -> four
+    queries per lookup)."""
+    from vector_db_b200 import _lib, ops
+    lib = _lib.load()
+    rng = np.random.default_rng(n + m + R + q)
+    codes = rng.integers(0, 256, (n, m)).astype(np.uint8)
+    lut = rng.random((q, m, 256), dtype=np.float32) * np.float32(3.0)
+    mask = None
+    kept = None
+    if kind == "tail":
+        lut[rng.random(lut.shape) < 0.01] *= np.float32(5000.0)
+    elif kind == "dup":
+        codes[rng.permutation(n)[: n // 2]] = codes[0]
+    elif kind == "const":
+        lut[:] = np.float32(1.25)
+        lut[1] = rng.random((m, 256), dtype=np.float32)
+    elif kind == "mask":
+        kept = np.flatnonzero(rng.random(n) < 0.6)
+        words = np.zeros((n + 31) // 32, dtype=np.uint32)
+        np.bitwise_or.at(words, kept >> 5, np.uint32(1) << (kept & 31).astype(np.uint32))
+        mask = _t(words.view(np.int32))
+    if kept is None:
+        Dref, Iref = O.adc_scan_topk(codes, lut, R)
+    else:
+        Dref, Iref = O.adc_scan_topk(codes[kept], lut, R, ids=kept)
+    out = {}
+    try:
+        for mode in (1, 0):
+            lib.vdb_debug_set_adc_coarse(mode)
+            D, I = ops.pq_adc_topk(_t(codes), _t(lut), R, row_mask=mask)
+            out[mode] = (D.cpu().numpy(), I.cpu().numpy())
+    finally:
+        lib.vdb_debug_set_adc_coarse(1)
+    np.testing.assert_array_equal(out[1][1], out[0][1])
+    np.testing.assert_array_equal(out[1][0], out[0][0])
+    np.testing.assert_array_equal(out[1][1], Iref)
+    np.testing.assert_array_equal(out[1][0], Dref)

@@ -258,6 +258,8 @@ struct AdcArgs {
     u64* cbuf;                  //   [Q][ccap] keys with d_int <= tau, unordered
     int32_t* ccnt;              //   [Q] number of keys found (may exceed ccap: overflow, handled by the caller)
     int ccap;
+    const uint16_t* lut16;      // coarse collect: per-query 15-bit lower-bound tables [Q][m][256]
+    const uint32_t* thr16;      //   per query 0x8000 + coarse threshold (0 = absent query)
 };
 
 // d_int of one row for the G queries of the group: 128-bit code loads, rotated conflict-free lookups.
@@ -418,6 +420,7 @@ struct AdcFinArgs {
     const u64* keys;            // [slot][L]
     int L, R, C;
     const int32_t* lens;        // optional per-query key count (collect buffers): count < R or > L flags the query
+    const int32_t* lens_valid;  // optional: how many of those keys are not VDB_KEY_MAX (coarse collect); < R flags the query
     const int32_t* expo;
     const int64_t* ids;
     float* out_d;
@@ -445,7 +448,7 @@ adc_finalize_kernel(const AdcFinArgs a) {
     int L = a.L;
     if (a.lens) {
         const int n = a.lens[q];
-        if (n < R || n > L) {       // too few rows under the threshold, or the buffer overflowed: exact rescan
+        if (n < R || n > L || (a.lens_valid && a.lens_valid[q] < R)) {   // too few rows under the threshold, or the buffer overflowed: exact rescan
             if (threadIdx.x == 0) a.bad[atomicAdd(a.bad_count, 1)] = q;
             return;
         }
@@ -484,6 +487,158 @@ adc_finalize_kernel(const AdcFinArgs a) {
             a.out_i[o] = a.ids ? a.ids[idx] : idx;
         }
     }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Coarse collect (r02).  The collect scan above is bound by the shared-memory pipe: one 128-bit lookup per code
+// byte serves FOUR queries.  The threshold test does not need 32-bit entries: with
+//     lut16[j][c] = min(lutq[j][c] - min_j, budget) >> s,   budget = tau - sum_j min_j,
+// the packed sum is a LOWER bound of the row's distance in units of 2^s above sum_j min_j, so
+//     d_int <= tau   ==>   sum_j lut16[j][code_j] <= budget >> s,
+// and a 128-bit lookup now serves EIGHT queries (two 16-bit fields per word, plain 32-bit adds: s is the
+// smallest shift that keeps every possible sum below 2^15, so no carry crosses a field and bit 15 is free
+// for the packed compare (0x8000 + thr) - sum).  Rows that pass are a superset of the rows the exact test
+// collects; `adc_exactify_kernel` then evaluates d_int of every collected row from the 32-bit tables (a few
+// hundred rows per query) and drops the ones above tau, after which the result is what the exact collect
+// would have produced -- same keys, same final selection, bit for bit.
+template <int MB, int W>
+__global__ void __launch_bounds__(kAdcThreads)
+adc_coarse_collect_kernel(const AdcArgs a) {
+    constexpr int G = 2 * W;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint32_t* lutS = reinterpret_cast<uint32_t*>(smem_raw);          // mb*256*8 slots of W words
+    const int m = a.m, S = a.S;
+    const int mb = (m + 7) >> 3;
+    const int tid = threadIdx.x;
+    const int rot = tid & 7;
+    const int groups = a.groups, units = S * groups;
+
+    for (int u = blockIdx.x; u < units; u += gridDim.x) {
+        const int s = u / groups, grp = u - s * groups;
+        const int q0 = grp * G;
+        const int nq = min(G, a.Q - q0);
+        __syncthreads();   // previous unit fully drained
+        for (int i = tid; i < mb * 2048; i += kAdcThreads) {
+            const int j = i >> 8, c = i & 255;
+            const uint32_t slot = (uint32_t)(((j >> 3) * 256 + c) * 8 + (j & 7));
+#pragma unroll
+            for (int w = 0; w < W; ++w) {
+                uint32_t lo = 0u, hi = 0u;
+                if (j < m) {
+                    if (2 * w < nq) lo = a.lut16[((size_t)(q0 + 2 * w) * m + j) * 256 + c];
+                    if (2 * w + 1 < nq) hi = a.lut16[((size_t)(q0 + 2 * w + 1) * m + j) * 256 + c];
+                }
+                lutS[(size_t)slot * W + w] = lo | (hi << 16);
+            }
+        }
+        uint32_t thr[W];
+#pragma unroll
+        for (int w = 0; w < W; ++w) {
+            const uint32_t lo = 2 * w < nq ? __ldg(a.thr16 + q0 + 2 * w) : 0u;
+            const uint32_t hi = 2 * w + 1 < nq ? __ldg(a.thr16 + q0 + 2 * w + 1) : 0u;
+            thr[w] = lo | (hi << 16);
+        }
+        __syncthreads();
+
+        const int64_t r_begin = (int64_t)s * a.slice_rows;
+        const int64_t r_end = min(a.N, r_begin + a.slice_rows);
+        for (int64_t rb = r_begin; rb < r_end; rb += kAdcThreads) {
+            const int64_t r = rb + tid;
+            bool live = r < r_end;
+            if (live && a.mask) live = (a.mask[r >> 5] >> (r & 31)) & 1u;
+            if (live) {
+                uint32_t acc[W];
+                adc_row<W, MB>(a.codes + r * m, m, mb, lutS, rot, acc);
+                uint32_t hit[W], any = 0u;
+#pragma unroll
+                for (int w = 0; w < W; ++w) { hit[w] = (thr[w] - acc[w]) & 0x80008000u; any |= hit[w]; }
+                if (any) {
+#pragma unroll
+                    for (int g = 0; g < G; ++g) {
+                        if (hit[g >> 1] & (g & 1 ? 0x80000000u : 0x8000u)) {
+                            const int p = atomicAdd(a.ccnt + q0 + g, 1);
+                            if ((unsigned)p < (unsigned)a.ccap) a.cbuf[(size_t)(q0 + g) * a.ccap + p] = (u64)(uint32_t)r;
+                        }
+                    }
+                }
+            }
+        }
+    }
+}
+
+// per query: 15-bit lower-bound tables and the packed threshold (see adc_coarse_collect_kernel).  One CTA per query.
+__global__ void __launch_bounds__(256)
+adc_coarse_lut_kernel(const uint32_t* __restrict__ lutq, int m, const uint32_t* __restrict__ tau,
+                      uint16_t* __restrict__ lut16, uint32_t* __restrict__ thr16) {
+    __shared__ uint32_t mn[256], rg[256];
+    __shared__ uint32_t s_budget;
+    __shared__ int s_shift;
+    const int q = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t* src = lutq + (size_t)q * m * 256;
+    for (int j = warp; j < m; j += 8) {
+        uint32_t lo = 0xFFFFFFFFu, hi = 0u;
+        for (int c = lane; c < 256; c += 32) { const uint32_t v = src[j * 256 + c]; lo = min(lo, v); hi = max(hi, v); }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+            hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+        }
+        if (lane == 0) { mn[j] = lo; rg[j] = hi - lo; }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t off = 0u;                               // m <= 255 entries <= 2^23: fits
+        for (int j = 0; j < m; ++j) off += mn[j];
+        const uint32_t t = tau[q];
+        const uint32_t budget = t >= off ? t - off : 0u;     // t < off cannot happen for a tau taken from a row; 0 keeps a superset
+        int sh = 0;
+        for (; sh < 32; ++sh) {
+            uint32_t tot = 0u;
+            for (int j = 0; j < m; ++j) tot += min(rg[j], budget) >> sh;
+            if (tot <= 32767u) break;
+        }
+        s_budget = budget; s_shift = sh;
+        const uint32_t tc = sh < 32 ? budget >> sh : 0u;
+        thr16[q] = 0x8000u + min(tc, 32767u);
+    }
+    __syncthreads();
+    const uint32_t budget = s_budget;
+    const int sh = s_shift;
+    uint16_t* dst = lut16 + (size_t)q * m * 256;
+    for (int i = threadIdx.x; i < m * 256; i += 256) {
+        const uint32_t v = min(src[i] - mn[i >> 8], budget);
+        dst[i] = (uint16_t)(sh < 32 ? v >> sh : 0u);
+    }
+}
+
+// collected rows -> exact keys: d_int from the 32-bit tables; rows above tau become VDB_KEY_MAX.  One CTA per query.
+__global__ void __launch_bounds__(256)
+adc_exactify_kernel(const uint8_t* __restrict__ codes, int m, const uint32_t* __restrict__ lutq,
+                    const uint32_t* __restrict__ tau, u64* __restrict__ cbuf, const int32_t* __restrict__ ccnt, int ccap,
+                    int32_t* __restrict__ cvalid) {
+    __shared__ int valid;
+    const int q = blockIdx.x;
+    const int n = ccnt[q];
+    if (threadIdx.x == 0) valid = 0;
+    __syncthreads();
+    if (n <= ccap) {
+        const uint32_t t = tau[q];
+        const uint32_t* lq = lutq + (size_t)q * m * 256;
+        u64* buf = cbuf + (size_t)q * ccap;
+        int mine = 0;
+        for (int p = threadIdx.x; p < n; p += 256) {
+            const uint32_t r = (uint32_t)buf[p];
+            const uint8_t* pr = codes + (size_t)r * m;
+            uint32_t d = 0u;
+            for (int j = 0; j < m; ++j) d += __ldg(lq + j * 256 + __ldg(pr + j));
+            const bool ok = d <= t;
+            buf[p] = ok ? (((u64)d << 32) | (u64)r) : VDB_KEY_MAX;
+            mine += ok ? 1 : 0;
+        }
+        if (mine) atomicAdd(&valid, mine);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) cvalid[q] = valid;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -755,7 +910,30 @@ struct AdcCollectPlan {
     int cap, Rs;
     AdcPlan sample, collect, rescan;
     size_t off_tau, off_cnt, off_bad, off_badn, off_cbuf, off_partial, total;   // after lutq + expo
+    bool coarse;                // 16-bit lower-bound collect (adc_coarse_collect_kernel) available for this shape
+    AdcPlan cscan;              //   its unit plan; G = queries per group = 2 * W
+    int W;
+    size_t off_lut16, off_thr16, off_valid;
 };
+
+static int g_adc_coarse = 1;    // debug switch (vdb_debug_set_adc_coarse): 0 = always the 32-bit collect
+
+static bool plan_adc_coarse_scan(int Q, int64_t N, int m, AdcPlan* p, int* W_out) {
+    const int mb = (m + 7) / 8;
+    const size_t smem_max = (size_t)max_smem_optin() - 64;
+    const int ws[3] = {4, 2, 1};
+    for (int t = 0; t < 3; ++t) {
+        const int W = ws[t];
+        const size_t smem = (size_t)mb * 2048 * W * 4;
+        if (smem > smem_max) continue;
+        p->G = 2 * W; p->C = 0; p->smem = smem;
+        p->groups = (Q + p->G - 1) / p->G;
+        plan_adc_slices(p, N, m, 1ll << 30, smem_max);
+        *W_out = W;
+        return true;
+    }
+    return false;
+}
 
 static bool plan_adc_collect_scan(int Q, int64_t N, int m, AdcPlan* p) {
     const int mb = (m + 7) / 8;
@@ -779,9 +957,13 @@ static bool plan_adc_collect(int Q, int64_t N, int m, int R, AdcCollectPlan* c) 
     c->use = false;
     double T;
     // relative spread of the collected count: sigma = 1/sqrt(Rs); T (1 - 4.5 sigma) >= R and cap >= T (1 + 6 sigma)
-    if (R <= 100) { c->Rs = 32; T = 512.0; c->cap = 2048; }              // sigma 18%
-    else if (R <= 512) { c->Rs = 64; T = 4.0 * R; c->cap = 8 * R; }      // sigma 12.5%
-    else { c->Rs = 128; T = 1.8 * R; c->cap = 4 * R; }                   // sigma 8.8%
+    // r02: the sample pass runs the 32-bit running selection over N / stride rows, 1/16 of the scan at T = 512; since the
+    // collect pass went to 16-bit tables (half the time per row) T is 4x larger -- collected rows cost next to nothing
+    // (one atomic + 48 table reads in adc_exactify_kernel each), sample rows cost a full lookup pass.  cap also
+    // covers the 16-bit tables' looser test (+20..40% rows).
+    if (R <= 100) { c->Rs = 32; T = 2048.0; c->cap = 8192; }                                  // sigma 18%
+    else if (R <= 512) { c->Rs = 64; T = R < 512 ? 2048.0 : 4.0 * R; c->cap = 3 * (int)T; }  // sigma 12.5%
+    else { c->Rs = 128; T = 3.0 * R; c->cap = 8 * R; }                                        // sigma 8.8%
     c->stride = (int64_t)(T / c->Rs);
     if (c->stride < 1) c->stride = 1;
     c->n_sample = N / c->stride;
@@ -798,9 +980,38 @@ static bool plan_adc_collect(int Q, int64_t N, int m, int R, AdcCollectPlan* c) 
     c->off_partial = o;
     const size_t ps = (size_t)Q * c->sample.S * c->Rs * 8, pr = (size_t)Q * c->rescan.S * R * 8;
     o += al256(ps > pr ? ps : pr);
+    c->coarse = Q > 4 && plan_adc_coarse_scan(Q, N, m, &c->cscan, &c->W);
+    c->off_lut16 = o; o += al256((size_t)Q * m * 256 * 2);
+    c->off_thr16 = o; o += al256((size_t)Q * 4);
+    c->off_valid = o; o += al256((size_t)Q * 4);
     c->total = o;
     c->use = true;
     return true;
+}
+
+template <int W>
+static int launch_adc_coarse(const AdcPlan& p, const AdcArgs& a, cudaStream_t st) {
+#define VDB_ADCC_CASE(MBV)                                                                                      \
+    {                                                                                                           \
+        auto kern = adc_coarse_collect_kernel<MBV, W>;                                                          \
+        VDB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem));         \
+        kern<<<p.grid, kAdcThreads, p.smem, st>>>(a);                                                           \
+    }
+    const int m = a.m;
+    const bool aligned16 = (reinterpret_cast<uintptr_t>(a.codes) & 15) == 0;
+    const bool aligned8 = (reinterpret_cast<uintptr_t>(a.codes) & 7) == 0;
+    if (aligned16 && m == 16) VDB_ADCC_CASE(2)
+    else if (aligned16 && m == 32) VDB_ADCC_CASE(4)
+    else if (aligned16 && m == 48) VDB_ADCC_CASE(6)
+    else if (aligned16 && m == 64) VDB_ADCC_CASE(8)
+    else if (aligned16 && m == 96) VDB_ADCC_CASE(12)
+    else if (aligned8 && m == 8) VDB_ADCC_CASE(1)
+    else if (aligned8 && m == 24) VDB_ADCC_CASE(3)
+    else VDB_ADCC_CASE(0)
+#undef VDB_ADCC_CASE
+    count_launch(1);
+    VDB_CUDA(cudaGetLastError());
+    return VDB_OK;
 }
 
 static size_t adc_lutq_bytes(int Q, int m) { return (((size_t)Q * m * 256 * 4) + 255) & ~(size_t)255; }
@@ -909,6 +1120,8 @@ int vdb_pq_lut(const float* q, int Q, int D, int m, int K, const float* codebook
     return VDB_OK;
 }
 
+void vdb_debug_set_adc_coarse(int on) { g_adc_coarse = on ? 1 : 0; }
+
 size_t vdb_pq_adc_topk_workspace(int Q, int64_t N, int m, int R) {
     if (Q <= 0 || R <= 0 || m <= 0) return 0;
     AdcCollectPlan c;
@@ -966,6 +1179,7 @@ int vdb_pq_adc_topk(const uint8_t* codes, int64_t N, int m, const float* lut, in
     int32_t* badn = reinterpret_cast<int32_t*>(w + c.off_badn);
     u64* cbuf = reinterpret_cast<u64*>(w + c.off_cbuf);
     u64* partial = reinterpret_cast<u64*>(w + c.off_partial);
+    int32_t* cvalid = nullptr;                                             // set by the coarse collect
     VDB_CUDA(cudaMemsetAsync(ccnt, 0, c.off_cbuf - c.off_cnt, st));       // counters, flagged list and its length
     {
         ProfScope prof(kProfAdcScan, st);
@@ -980,19 +1194,34 @@ int vdb_pq_adc_topk(const uint8_t* codes, int64_t N, int m, const float* lut, in
         if ((rc = launch_adc_finalize(fs, Q, st))) return rc;
         // (B) collect
         AdcArgs b = a;
-        b.C = 0; b.slice_rows = c.collect.slice_rows; b.S = c.collect.S; b.groups = c.collect.groups;
         b.tau = tau; b.cbuf = cbuf; b.ccnt = ccnt; b.ccap = c.cap;
-        if ((rc = launch_adc_g<1>(c.collect, b, st))) return rc;
+        if (c.coarse && g_adc_coarse) {
+            uint16_t* lut16 = reinterpret_cast<uint16_t*>(w + c.off_lut16);
+            uint32_t* thr16 = reinterpret_cast<uint32_t*>(w + c.off_thr16);
+            cvalid = reinterpret_cast<int32_t*>(w + c.off_valid);
+            adc_coarse_lut_kernel<<<Q, 256, 0, st>>>(lutq, m, tau, lut16, thr16);
+            b.C = 0; b.slice_rows = c.cscan.slice_rows; b.S = c.cscan.S; b.groups = c.cscan.groups;
+            b.lut16 = lut16; b.thr16 = thr16;
+            rc = c.W == 4 ? launch_adc_coarse<4>(c.cscan, b, st)
+                          : (c.W == 2 ? launch_adc_coarse<2>(c.cscan, b, st) : launch_adc_coarse<1>(c.cscan, b, st));
+            if (rc) return rc;
+            adc_exactify_kernel<<<Q, 256, 0, st>>>(codes, m, lutq, tau, cbuf, ccnt, c.cap, cvalid);
+            count_launch(2);
+            VDB_CUDA(cudaGetLastError());
+        } else {
+            b.C = 0; b.slice_rows = c.collect.slice_rows; b.S = c.collect.S; b.groups = c.collect.groups;
+            if ((rc = launch_adc_g<1>(c.collect, b, st))) return rc;
+        }
     }
     ProfScope prof(kProfFinalize, st);
     // (C) exact top-R of the collected keys; queries outside [R, cap] go to the flagged list
-    f.keys = cbuf; f.L = c.cap; f.lens = ccnt; f.C = select_capacity(R, 256); f.bad = bad; f.bad_count = badn;
+    f.keys = cbuf; f.L = c.cap; f.lens = ccnt; f.lens_valid = cvalid; f.C = select_capacity(R, 256); f.bad = bad; f.bad_count = badn;
     if ((rc = launch_adc_finalize(f, Q, st))) return rc;
     // (D, E) flagged queries: running-selection scan + merge, driven by the device-side list
     a.C = c.rescan.C; a.slice_rows = c.rescan.slice_rows; a.S = c.rescan.S; a.groups = c.rescan.groups;
     a.partial = partial; a.qsel = bad; a.qcount = badn;
     if ((rc = launch_adc_g<0>(c.rescan, a, st))) return rc;
-    f.keys = partial; f.L = c.rescan.S * R; f.lens = nullptr; f.bad = nullptr; f.bad_count = nullptr;
+    f.keys = partial; f.L = c.rescan.S * R; f.lens = nullptr; f.lens_valid = nullptr; f.bad = nullptr; f.bad_count = nullptr;
     f.qsel = bad; f.qcount = badn;
     return launch_adc_finalize(f, Q, st);
 }
