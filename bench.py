@@ -886,10 +886,13 @@ def path_sharded_adc(dev, peaks, rank, world, peer_ok):
                                f"(seed = 50000 + chunk), encoded shard-side, dropped",
                    "rows_per_gpu": n_local, "exchange": "one packed NCCL all-gather (122,880 B per rank) + merge kernel" if world > 1 else "none"},
         "metric": "queries/s", "value": Q / (ms_step * 1e-3), "unit": "queries/s", "scaling": "strong", "n_gpus": world,
-        "ms_per_step": ms_step, "kernel": "adc_scan_kernel", "kernel_ms": kernel_ms, "kernel_ms_is": "max over ranks",
+        "ms_per_step": ms_step, "kernel": "adc_coarse_collect_kernel", "kernel_ms": kernel_ms,
+        "kernel_ms_is": "scan phase (threshold sample + collect on 16-bit tables + re-evaluation), max over ranks",
         "encode_ms_per_shard": enc_max, "encode_vectors_per_s_per_gpu": n_local / (enc_max * 1e-3),
-        "roofline": _hbm_roofline(alg, kernel_ms, peaks, "adc_scan_kernel", "per GPU: Q x rows_per_gpu x m code bytes",
-                                  ncu_key="adc_scan"),
+        "roofline": _hbm_roofline(alg, kernel_ms, peaks, "adc_coarse_collect_kernel",
+                                  "per GPU: Q x rows_per_gpu x m code bytes (per-query code stream; eight queries share a "
+                                  "pass over the codes, so the figure exceeds the HBM peak -- shared-memory-pipe bound)",
+                                  ncu_key="adc_coarse"),
         "cpu_baseline": {"value": npar / cpu_total_s, "unit": "queries/s", "cores": thr, "kind": "port",
                          "sample": f"oracle.adc_scan_topk, {npar} queries x all {N_TOTAL} rows (sum over shards of the "
                                    f"per-shard time, {thr} threads each), {cpu_total_s:.2f} s"},

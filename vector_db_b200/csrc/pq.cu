@@ -370,14 +370,28 @@ adc_scan_kernel(const AdcArgs a) {
 
         const int64_t r_begin = (int64_t)s * a.slice_rows;
         const int64_t r_end = min(a.N, r_begin + a.slice_rows);
+        // the next batch's code bytes are requested before this batch's lookups: MODE 0 has a barrier per batch, so the
+        // load latency (a DRAM sector per row on the strided sample pass) is otherwise exposed once per batch
+        // (MB >= 3 only: the small tables of m = 16 leave three CTAs per SM, whose warps hide the latency themselves, and
+        // the extra registers cost more than the prefetch gains there)
+        constexpr bool kPre = MB >= 3;
+        uint32_t wn[MB > 0 ? 2 * MB : 2];
+        if (kPre && r_begin + tid < r_end) adc_load_codes<MB>(a.codes + (r_begin + tid) * a.row_stride * m, wn);
         for (int64_t rb = r_begin; rb < r_end; rb += kAdcThreads) {
             const int64_t r = rb + tid;
             int nearly_full = 0;
             bool live = r < r_end;
             if (live && a.mask) { const int64_t pr = r * a.row_stride; live = (a.mask[pr >> 5] >> (pr & 31)) & 1u; }
+            uint32_t w[MB > 0 ? 2 * MB : 2];
+            if (kPre) {
+#pragma unroll
+                for (int i = 0; i < 2 * MB; ++i) w[i] = wn[i];
+                if (r + kAdcThreads < r_end) adc_load_codes<MB>(a.codes + (r + kAdcThreads) * a.row_stride * m, wn);
+            }
             if (live) {
                 uint32_t acc[G];
-                adc_row<G, MB>(a.codes + r * a.row_stride * m, m, mb, lutS, rot, acc);
+                if (kPre) adc_sum_codes<G, MB>(w, lutS, rot, acc);
+                else adc_row<G, MB>(a.codes + r * a.row_stride * m, m, mb, lutS, rot, acc);
 #pragma unroll
                 for (int g = 0; g < G; ++g) {
                     if (g < nq) {
@@ -542,13 +556,23 @@ adc_coarse_collect_kernel(const AdcArgs a) {
 
         const int64_t r_begin = (int64_t)s * a.slice_rows;
         const int64_t r_end = min(a.N, r_begin + a.slice_rows);
+        constexpr bool kPre = MB >= 3;             // next batch's code bytes in flight during this batch's lookups
+        uint32_t wn[MB > 0 ? 2 * MB : 2];
+        if (kPre && r_begin + tid < r_end) adc_load_codes<MB>(a.codes + (r_begin + tid) * m, wn);
         for (int64_t rb = r_begin; rb < r_end; rb += kAdcThreads) {
             const int64_t r = rb + tid;
             bool live = r < r_end;
             if (live && a.mask) live = (a.mask[r >> 5] >> (r & 31)) & 1u;
+            uint32_t cw[MB > 0 ? 2 * MB : 2];
+            if (kPre) {
+#pragma unroll
+                for (int i = 0; i < 2 * MB; ++i) cw[i] = wn[i];
+                if (r + kAdcThreads < r_end) adc_load_codes<MB>(a.codes + (r + kAdcThreads) * m, wn);
+            }
             if (live) {
                 uint32_t acc[W];
-                adc_row<W, MB>(a.codes + r * m, m, mb, lutS, rot, acc);
+                if (kPre) adc_sum_codes<W, MB>(cw, lutS, rot, acc);
+                else adc_row<W, MB>(a.codes + r * m, m, mb, lutS, rot, acc);
                 uint32_t hit[W], any = 0u;
 #pragma unroll
                 for (int w = 0; w < W; ++w) { hit[w] = (thr[w] - acc[w]) & 0x80008000u; any |= hit[w]; }
