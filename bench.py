@@ -427,11 +427,17 @@ def path_adc_scan(dev, peaks, state):
     out = {
         "config": {"workload": f"PQ ADC scan top-{K}, {N} x {m} uint8 codes, {Q}-query batch (BASELINE.json configs[2], scan)"},
         "metric": "queries/s", "value": Q / (step_ms * 1e-3), "unit": "queries/s", "ms_per_step": step_ms,
-        "kernel": "adc_scan_kernel", "kernel_ms": kernel_ms, "dtype": "u8 codes, fixed-point i32 sums",
-        "roofline": _hbm_roofline(alg, kernel_ms, peaks, "adc_scan_kernel",
-                                  "per-query code stream: Q x N x m code bytes (SURVEY.md 8d); four queries share one "
-                                  "pass over the codes, so DRAM traffic is far below it -- the kernel is LDS-pipe bound",
-                                  ncu_key="adc_scan"),
+        "kernel": "adc_coarse_collect_kernel", "kernel_ms": kernel_ms,
+        "kernel_ms_is": "the whole scan phase: threshold sample + 16-bit tables + collect kernel + re-evaluation of the "
+                        "collected rows on the 32-bit tables (the collect kernel is ~90% of it)",
+        "dtype": "u8 codes, fixed-point i32 sums",
+        "roofline": _hbm_roofline(alg, kernel_ms, peaks, "adc_coarse_collect_kernel",
+                                  "per-query code stream: Q x N x m code bytes (SURVEY.md 8d); EIGHT queries share one pass "
+                                  "over the codes (one 128-bit shared-memory lookup per code byte returns eight 16-bit "
+                                  "lower-bound entries), so the figure exceeds the HBM peak and DRAM traffic is far below "
+                                  "it -- the physical bound is the shared-memory pipe (ncu: l1tex throughput 98.6% of peak, "
+                                  "profiles/r02_ncu_summary.json adc_coarse)",
+                                  ncu_key="adc_coarse"),
         "cpu_baseline": {"value": npar / cpu_s, "unit": "queries/s", "cores": thr, "kind": "port",
                          "sample": f"oracle.adc_scan_topk, {npar} queries x {N} rows (row chunks on {thr} threads), {cpu_s:.2f} s"},
         "e2e": {"value": Q / e2e_dt, "unit": "queries/s", "h2d_bytes_per_step": int(Q_pin.numel() * 4),
@@ -891,8 +897,9 @@ def path_sharded_adc(dev, peaks, rank, world, peer_ok):
         "encode_ms_per_shard": enc_max, "encode_vectors_per_s_per_gpu": n_local / (enc_max * 1e-3),
         "roofline": _hbm_roofline(alg, kernel_ms, peaks, "adc_coarse_collect_kernel",
                                   "per GPU: Q x rows_per_gpu x m code bytes (per-query code stream; eight queries share a "
-                                  "pass over the codes, so the figure exceeds the HBM peak -- shared-memory-pipe bound)",
-                                  ncu_key="adc_coarse"),
+                                  "pass over the codes, so the figure exceeds the HBM peak -- shared-memory-pipe bound: ncu "
+                                  "l1tex data-pipe wavefronts at 97% of peak, profiles/r02_ncu_summary.json adc_coarse_m16)",
+                                  ncu_key="adc_coarse_m16"),
         "cpu_baseline": {"value": npar / cpu_total_s, "unit": "queries/s", "cores": thr, "kind": "port",
                          "sample": f"oracle.adc_scan_topk, {npar} queries x all {N_TOTAL} rows (sum over shards of the "
                                    f"per-shard time, {thr} threads each), {cpu_total_s:.2f} s"},

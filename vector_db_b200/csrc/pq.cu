@@ -654,6 +654,7 @@ adc_exactify_kernel(const uint8_t* __restrict__ codes, int m, const uint32_t* __
             const uint32_t r = (uint32_t)buf[p];
             const uint8_t* pr = codes + (size_t)r * m;
             uint32_t d = 0u;
+#pragma unroll 8
             for (int j = 0; j < m; ++j) d += __ldg(lq + j * 256 + __ldg(pr + j));
             const bool ok = d <= t;
             buf[p] = ok ? (((u64)d << 32) | (u64)r) : VDB_KEY_MAX;
@@ -987,7 +988,7 @@ static bool plan_adc_collect(int Q, int64_t N, int m, int R, AdcCollectPlan* c) 
     // covers the 16-bit tables' looser test (+20..40% rows).
     if (R <= 100) { c->Rs = 32; T = 2048.0; c->cap = 8192; }                                  // sigma 18%
     else if (R <= 512) { c->Rs = 64; T = R < 512 ? 2048.0 : 4.0 * R; c->cap = 3 * (int)T; }  // sigma 12.5%
-    else { c->Rs = 128; T = 3.0 * R; c->cap = 8 * R; }                                        // sigma 8.8%
+    else { c->Rs = 128; T = 1.8 * R; c->cap = 5 * R; }                                        // sigma 8.8%; large R: collected rows are no longer free
     c->stride = (int64_t)(T / c->Rs);
     if (c->stride < 1) c->stride = 1;
     c->n_sample = N / c->stride;
