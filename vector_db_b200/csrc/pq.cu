@@ -988,7 +988,8 @@ static bool plan_adc_collect(int Q, int64_t N, int m, int R, AdcCollectPlan* c) 
     // covers the 16-bit tables' looser test (+20..40% rows).
     if (R <= 100) { c->Rs = 32; T = 2048.0; c->cap = 8192; }                                  // sigma 18%
     else if (R <= 512) { c->Rs = 64; T = R < 512 ? 2048.0 : 4.0 * R; c->cap = 3 * (int)T; }  // sigma 12.5%
-    else { c->Rs = 128; T = 1.8 * R; c->cap = 5 * R; }                                        // sigma 8.8%; large R: collected rows are no longer free
+    else if (R <= 2048) { c->Rs = 128; T = 3.0 * R; c->cap = 8 * R; }                         // sigma 8.8%
+    else { c->Rs = 128; T = 1.8 * R; c->cap = 5 * R; }       // large R: the final selection over the collected keys dominates, keep them few
     c->stride = (int64_t)(T / c->Rs);
     if (c->stride < 1) c->stride = 1;
     c->n_sample = N / c->stride;
