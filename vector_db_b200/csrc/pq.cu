@@ -258,7 +258,7 @@ struct AdcArgs {
     u64* cbuf;                  //   [Q][ccap] keys with d_int <= tau, unordered
     int32_t* ccnt;              //   [Q] number of keys found (may exceed ccap: overflow, handled by the caller)
     int ccap;
-    const uint16_t* lut16;      // coarse collect: per-query 15-bit lower-bound tables [Q][m][256]
+    const uint16_t* lut16;      // coarse collect: 15-bit lower-bound tables, [group][slot][G] in the shared-memory order
     const uint32_t* thr16;      //   per query 0x8000 + coarse threshold (0 = absent query)
 };
 
@@ -352,12 +352,17 @@ adc_scan_kernel(const AdcArgs a) {
         for (int g = 0; g < G; ++g) qid[g] = g < nq ? (a.qsel ? __ldg(a.qsel + q0 + g) : q0 + g) : 0;
         __syncthreads();   // previous unit fully drained
         // stage the group's LUTs into the rotated-slot layout
+        // in SLOT order (i = ((j/8)*256 + c)*8 + j%8): consecutive lanes write consecutive G-word slots, one vector store
+        // each (the (j, c)-ordered loop of r01 put a whole warp on one bank: 32 wavefronts per store, and its dependent
+        // global loads were not overlapped -- 200 us per unit, most of the sample pass at 1M rows)
+#pragma unroll 4
         for (int i = tid; i < mb * 2048; i += kAdcThreads) {
-            const int j = i >> 8, c = i & 255;
-            const uint32_t slot = (uint32_t)(((j >> 3) * 256 + c) * 8 + (j & 7));
+            const int j = ((i >> 11) << 3) | (i & 7), c = (i >> 3) & 255;
+            typename LutVec<G>::type v;
+            uint32_t* pv = reinterpret_cast<uint32_t*>(&v);
 #pragma unroll
-            for (int g = 0; g < G; ++g)
-                lutS[(size_t)slot * G + g] = (g < nq && j < m) ? a.lutq[((size_t)qid[g] * m + j) * 256 + c] : 0u;
+            for (int g = 0; g < G; ++g) pv[g] = (g < nq && j < m) ? __ldg(a.lutq + ((size_t)qid[g] * m + j) * 256 + c) : 0u;
+            *reinterpret_cast<typename LutVec<G>::type*>(lutS + (size_t)i * G) = v;
         }
         if (MODE == 0) {
             for (int i = tid; i < G * C; i += kAdcThreads) sel_buf[i] = VDB_KEY_MAX;
@@ -532,18 +537,14 @@ adc_coarse_collect_kernel(const AdcArgs a) {
         const int q0 = grp * G;
         const int nq = min(G, a.Q - q0);
         __syncthreads();   // previous unit fully drained
-        for (int i = tid; i < mb * 2048; i += kAdcThreads) {
-            const int j = i >> 8, c = i & 255;
-            const uint32_t slot = (uint32_t)(((j >> 3) * 256 + c) * 8 + (j & 7));
-#pragma unroll
-            for (int w = 0; w < W; ++w) {
-                uint32_t lo = 0u, hi = 0u;
-                if (j < m) {
-                    if (2 * w < nq) lo = a.lut16[((size_t)(q0 + 2 * w) * m + j) * 256 + c];
-                    if (2 * w + 1 < nq) hi = a.lut16[((size_t)(q0 + 2 * w + 1) * m + j) * 256 + c];
-                }
-                lutS[(size_t)slot * W + w] = lo | (hi << 16);
-            }
+        {
+            // adc_coarse_lut_kernel wrote the group's table in the shared-memory layout already (rotated slots, the 2W
+            // queries' 16-bit entries side by side, zeros for padded sub-spaces and absent queries): staging is a copy
+            const uint4* src = reinterpret_cast<const uint4*>(a.lut16 + (size_t)grp * mb * 2048 * G);
+            uint4* dst = reinterpret_cast<uint4*>(lutS);
+            const int n16 = mb * 2048 * W / 4;
+#pragma unroll 8
+            for (int i = tid; i < n16; i += kAdcThreads) dst[i] = __ldg(src + i);
         }
         uint32_t thr[W];
 #pragma unroll
@@ -590,48 +591,67 @@ adc_coarse_collect_kernel(const AdcArgs a) {
     }
 }
 
-// per query: 15-bit lower-bound tables and the packed threshold (see adc_coarse_collect_kernel).  One CTA per query.
+// 15-bit lower-bound tables and the packed thresholds (see adc_coarse_collect_kernel).  One CTA per group of G <= 8
+// queries; the group's table leaves in the collect kernel's shared-memory order -- slot ((j/8)*256 + c)*8 + j%8, the
+// G queries' 16-bit entries side by side, zeros for padded sub-spaces and absent queries -- so staging it is a copy.
 __global__ void __launch_bounds__(256)
-adc_coarse_lut_kernel(const uint32_t* __restrict__ lutq, int m, const uint32_t* __restrict__ tau,
-                      uint16_t* __restrict__ lut16, uint32_t* __restrict__ thr16) {
-    __shared__ uint32_t mn[256], rg[256];
-    __shared__ uint32_t s_budget;
-    __shared__ int s_shift;
-    const int q = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint32_t* src = lutq + (size_t)q * m * 256;
-    for (int j = warp; j < m; j += 8) {
+adc_coarse_lut_kernel(const uint32_t* __restrict__ lutq, int m, int Q, const uint32_t* __restrict__ tau,
+                      uint16_t* __restrict__ lut16, uint32_t* __restrict__ thr16, int G) {
+    __shared__ uint32_t mn[8][256], rg[8][256];
+    __shared__ uint32_t s_budget[8];
+    __shared__ int s_shift[8];
+    const int grp = blockIdx.x, q0 = grp * G, nq = min(G, Q - q0);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int p = warp; p < nq * m; p += 8) {                 // (query, sub-space) pairs: min and range of the 256 entries
+        const int e = p / m, j = p - e * m;
+        const uint32_t* src = lutq + ((size_t)(q0 + e) * m + j) * 256;
         uint32_t lo = 0xFFFFFFFFu, hi = 0u;
-        for (int c = lane; c < 256; c += 32) { const uint32_t v = src[j * 256 + c]; lo = min(lo, v); hi = max(hi, v); }
+        for (int c = lane; c < 256; c += 32) { const uint32_t v = __ldg(src + c); lo = min(lo, v); hi = max(hi, v); }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o));
             hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o));
         }
-        if (lane == 0) { mn[j] = lo; rg[j] = hi - lo; }
+        if (lane == 0) { mn[e][j] = lo; rg[e][j] = hi - lo; }
     }
     __syncthreads();
-    if (threadIdx.x == 0) {
-        uint32_t off = 0u;                               // m <= 255 entries <= 2^23: fits
-        for (int j = 0; j < m; ++j) off += mn[j];
-        const uint32_t t = tau[q];
+    if (warp < nq) {                                         // warp e: budget and shift of query e
+        const int e = warp;
+        uint32_t off = 0u;                                   // m <= 255 entries <= 2^23: fits
+        for (int j = lane; j < m; j += 32) off += mn[e][j];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) off += __shfl_xor_sync(0xffffffffu, off, o);
+        const uint32_t t = __ldg(tau + q0 + e);
         const uint32_t budget = t >= off ? t - off : 0u;     // t < off cannot happen for a tau taken from a row; 0 keeps a superset
         int sh = 0;
-        for (; sh < 32; ++sh) {
+        for (; sh < 32; ++sh) {                              // smallest shift that keeps every possible sum below 2^15
             uint32_t tot = 0u;
-            for (int j = 0; j < m; ++j) tot += min(rg[j], budget) >> sh;
+            for (int j = lane; j < m; j += 32) tot += min(rg[e][j], budget) >> sh;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
             if (tot <= 32767u) break;
         }
-        s_budget = budget; s_shift = sh;
-        const uint32_t tc = sh < 32 ? budget >> sh : 0u;
-        thr16[q] = 0x8000u + min(tc, 32767u);
+        if (lane == 0) {
+            s_budget[e] = budget; s_shift[e] = sh;
+            const uint32_t tc = sh < 32 ? budget >> sh : 0u;
+            thr16[q0 + e] = 0x8000u + min(tc, 32767u);
+        }
     }
     __syncthreads();
-    const uint32_t budget = s_budget;
-    const int sh = s_shift;
-    uint16_t* dst = lut16 + (size_t)q * m * 256;
-    for (int i = threadIdx.x; i < m * 256; i += 256) {
-        const uint32_t v = min(src[i] - mn[i >> 8], budget);
-        dst[i] = (uint16_t)(sh < 32 ? v >> sh : 0u);
+    const int mb = (m + 7) >> 3;
+    uint16_t* dst = lut16 + (size_t)grp * mb * 2048 * G;
+    for (int i = threadIdx.x; i < mb * 2048; i += 256) {     // slot order: consecutive threads write consecutive slots
+        const int j = ((i >> 11) << 3) | (i & 7), c = (i >> 3) & 255;
+        uint32_t w[4] = {0u, 0u, 0u, 0u};
+        if (j < m) {
+            for (int e = 0; e < nq; ++e) {
+                const uint32_t v = min(__ldg(lutq + ((size_t)(q0 + e) * m + j) * 256 + c) - mn[e][j], s_budget[e]);
+                const uint32_t x = s_shift[e] < 32 ? v >> s_shift[e] : 0u;
+                w[e >> 1] |= x << (16 * (e & 1));
+            }
+        }
+        uint32_t* d32 = reinterpret_cast<uint32_t*>(dst + (size_t)i * G);
+        for (int k = 0; k < G / 2; ++k) d32[k] = w[k];
     }
 }
 
@@ -938,7 +958,7 @@ struct AdcCollectPlan {
     bool coarse;                // 16-bit lower-bound collect (adc_coarse_collect_kernel) available for this shape
     AdcPlan cscan;              //   its unit plan; G = queries per group = 2 * W
     int W;
-    size_t off_lut16, off_thr16, off_valid;
+    size_t off_lut16, off_thr16, off_valid, lut16_bytes;
 };
 
 static int g_adc_coarse = 1;    // debug switch (vdb_debug_set_adc_coarse): 0 = always the 32-bit collect
@@ -1007,7 +1027,8 @@ static bool plan_adc_collect(int Q, int64_t N, int m, int R, AdcCollectPlan* c) 
     const size_t ps = (size_t)Q * c->sample.S * c->Rs * 8, pr = (size_t)Q * c->rescan.S * R * 8;
     o += al256(ps > pr ? ps : pr);
     c->coarse = Q > 4 && plan_adc_coarse_scan(Q, N, m, &c->cscan, &c->W);
-    c->off_lut16 = o; o += al256((size_t)Q * m * 256 * 2);
+    c->lut16_bytes = c->coarse ? (size_t)c->cscan.groups * ((m + 7) / 8) * 2048 * c->cscan.G * 2 : 0;   // [group][slot][G] u16
+    c->off_lut16 = o; o += al256(c->lut16_bytes);
     c->off_thr16 = o; o += al256((size_t)Q * 4);
     c->off_valid = o; o += al256((size_t)Q * 4);
     c->total = o;
@@ -1225,7 +1246,7 @@ int vdb_pq_adc_topk(const uint8_t* codes, int64_t N, int m, const float* lut, in
             uint16_t* lut16 = reinterpret_cast<uint16_t*>(w + c.off_lut16);
             uint32_t* thr16 = reinterpret_cast<uint32_t*>(w + c.off_thr16);
             cvalid = reinterpret_cast<int32_t*>(w + c.off_valid);
-            adc_coarse_lut_kernel<<<Q, 256, 0, st>>>(lutq, m, tau, lut16, thr16);
+            adc_coarse_lut_kernel<<<c.cscan.groups, 256, 0, st>>>(lutq, m, Q, tau, lut16, thr16, c.cscan.G);
             b.C = 0; b.slice_rows = c.cscan.slice_rows; b.S = c.cscan.S; b.groups = c.cscan.groups;
             b.lut16 = lut16; b.thr16 = thr16;
             rc = c.W == 4 ? launch_adc_coarse<4>(c.cscan, b, st)
