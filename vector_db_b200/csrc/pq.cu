@@ -1006,9 +1006,11 @@ static bool plan_adc_collect(int Q, int64_t N, int m, int R, AdcCollectPlan* c) 
     // collect pass went to 16-bit tables (half the time per row) T is 4x larger -- collected rows cost next to nothing
     // (one atomic + 48 table reads in adc_exactify_kernel each), sample rows cost a full lookup pass.  cap also
     // covers the 16-bit tables' looser test (+20..40% rows).
-    if (R <= 100) { c->Rs = 32; T = 2048.0; c->cap = 8192; }                                  // sigma 18%
-    else if (R <= 512) { c->Rs = 64; T = R < 512 ? 2048.0 : 4.0 * R; c->cap = 3 * (int)T; }  // sigma 12.5%
-    else if (R <= 2048) { c->Rs = 128; T = 3.0 * R; c->cap = 8 * R; }                         // sigma 8.8%
+    // R <= 100: T is 20x R or more, so the sample may be small -- Rs = 16 (count / T ~ Gamma(16)/16: P(count > cap / 1.4
+    // = 2.9 T) ~ 1e-8 per query, P(count < R) far below that) halves the sample pass
+    if (R <= 100) { c->Rs = 16; T = 2048.0; c->cap = 8192; }                                  // sigma 25%
+    else if (R <= 512) { c->Rs = 32; T = R < 512 ? 2048.0 : 4.0 * R; c->cap = 3 * (int)T; }  // sigma 18%: T >= 4R, cap / 1.3 = 2.3 T
+    else if (R <= 2048) { c->Rs = 64; T = 3.0 * R; c->cap = 8 * R; }                          // sigma 12.5%: cap / 1.3 = 2.05 T (8 sigma)
     else { c->Rs = 128; T = 1.8 * R; c->cap = 5 * R; }       // large R: the final selection over the collected keys dominates, keep them few
     c->stride = (int64_t)(T / c->Rs);
     if (c->stride < 1) c->stride = 1;
