@@ -125,6 +125,39 @@ def _graph_rows(o):
     return np.array(sorted(rows), dtype=np.int64)
 
 
+def test_adc_lower_bound_tables_never_drop_a_row_under_the_threshold():
+    """The collect pass of the ADC scan tests rows against 15-bit lower-bound tables (eight queries per shared-memory
+    lookup) and re-evaluates the rows that pass.  What makes that exact: a row with d_int <= tau always passes, and no
+    sum of table entries reaches 2^15 (two 16-bit fields share a word; bit 15 carries the packed compare).  Checked
+    on the restatement of the table construction for plain, heavy-tailed and constant tables, thresholds from the
+    5e-4 quantile up to "collect everything"."""
+    rng = np.random.default_rng(99)
+    n, m = 20000, 24
+    codes = rng.integers(0, 256, (n, m))
+    for kind in ("plain", "tail", "const", "wide"):
+        lut = rng.random((6, m, 256)).astype(np.float32) * np.float32(3.0)
+        if kind == "tail":
+            lut[rng.random(lut.shape) < 0.01] *= np.float32(5000.0)
+        elif kind == "const":
+            lut[:] = np.float32(0.75)
+        lutq, _ = O.adc_quantize_lut(lut)
+        d = np.zeros((6, n), dtype=np.int64)
+        for j in range(m):
+            d += lutq[:, j, codes[:, j]]
+        tau = np.sort(d, axis=1)[:, 10] if kind != "wide" else np.full(6, 0xFFFFFFFF, dtype=np.int64)
+        tau[0] = d[0].min()                                   # the tightest useful threshold
+        lut16, thr, off, shift = O.adc_coarse_tables(lutq, tau)
+        assert lut16.min() >= 0 and int(lut16.max(axis=2).sum(axis=1).max()) <= 32767
+        cs = np.zeros((6, n), dtype=np.int64)
+        for j in range(m):
+            cs += lut16[:, j, codes[:, j]]
+        assert np.all((cs << shift[:, None]) + off[:, None] <= d)              # a lower bound of every row's distance
+        passed = cs <= thr[:, None]
+        assert np.all(passed[d <= tau[:, None]])                                # no row under the threshold is dropped
+        if kind == "plain":                                                     # and the filter is worth having
+            assert passed.sum(axis=1).max() < 40
+
+
 def test_hnsw_oracle_reproduces_reference_graph_and_search(golden_dir):
     for name in ("hnsw_small.npz", "hnsw_medium.npz"):
         g = _load(golden_dir, name)
