@@ -257,6 +257,11 @@ int vdb_pq_adc_topk(const uint8_t* codes /*[dev] N*m*/, int64_t N, int m, const 
  * shared-memory lookup, and the collected rows are re-evaluated on the 32-bit tables (same result, bit for bit);
  * 0 = the collect pass itself uses the 32-bit tables, four queries per lookup. */
 void vdb_debug_set_adc_coarse(int on);
+/* Test hook: the 15-bit tables of that collect pass for given fixed-point tables lutq [Q][m][256] and thresholds tau [Q]
+ * (all device pointers).  lut16: [ceil(Q/G)][ceil(m/8) * 2048 slots][G] u16 with slot = ((j/8)*256 + c)*8 + j%8;
+ * thr16[q] = 0x8000 + threshold.  G = queries per lookup group (2, 4 or 8). */
+int vdb_debug_adc_coarse_tables(const uint32_t* lutq, int m, int Q, const uint32_t* tau, uint16_t* lut16, uint32_t* thr16,
+                                int G, void* stream);
 
 /* ---- a4/a5/a6 batched HNSW search -------------------------------------------------------------
  * One CTA per query: greedy descent on levels max_level..1 (hnsw.py:289-328, strict '<'), then the

@@ -316,3 +316,36 @@ def test_adc_collect_on_16bit_lower_bound_tables_equals_the_32bit_collect_and_th
     np.testing.assert_array_equal(out[1][0], out[0][0])
     np.testing.assert_array_equal(out[1][1], Iref)
     np.testing.assert_array_equal(out[1][0], Dref)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("m,q,G,kind", [(48, 19, 8, "plain"), (16, 8, 8, "tail"), (7, 5, 8, "plain"), (64, 6, 4, "tail"), (24, 3, 2, "wide")])
+def test_adc_lower_bound_tables_equal_the_restatement(m, q, G, kind):
+    """adc_coarse_lut_kernel == oracle.adc_coarse_tables, entry for entry (the CPU suite proves on the restatement that
+    these tables never drop a row under the threshold)."""
+    from vector_db_b200 import _lib
+    from vector_db_b200._lib import check, ptr
+    lib = _lib.load()
+    rng = np.random.default_rng(m * 100 + q)
+    lut = rng.random((q, m, 256)).astype(np.float32) * np.float32(3.0)
+    if kind == "tail":
+        lut[rng.random(lut.shape) < 0.01] *= np.float32(5000.0)
+    lutq, _ = O.adc_quantize_lut(lut)
+    off = lutq.min(axis=2).sum(axis=1)
+    tau = off + rng.integers(1, 1 << 22, q) if kind != "wide" else np.full(q, 0xFFFFFFFF, dtype=np.int64)
+    ref16, thr, _, _ = O.adc_coarse_tables(lutq, tau)
+    mb = (m + 7) // 8
+    groups = (q + G - 1) // G
+    out16 = torch.full((groups, mb * 2048, G), -1, dtype=torch.int16, device="cuda")
+    thr16 = torch.zeros(q, dtype=torch.int32, device="cuda")
+    check(lib.vdb_debug_adc_coarse_tables(ptr(_t(lutq.astype(np.uint32).view(np.int32))), m, q,
+                                          ptr(_t(tau.astype(np.uint32).view(np.int32))), ptr(out16), ptr(thr16), G,
+                                          _lib.stream_ptr(out16.device)))
+    got = out16.cpu().numpy().view(np.uint16).astype(np.int64)
+    np.testing.assert_array_equal(thr16.cpu().numpy().astype(np.int64), 0x8000 + thr)
+    want = np.zeros((groups, mb * 2048, G), dtype=np.int64)        # padded sub-spaces and absent queries read 0
+    j, c = np.meshgrid(np.arange(m), np.arange(256), indexing="ij")
+    slot = ((j >> 3) * 256 + c) * 8 + (j & 7)
+    for qi in range(q):
+        want[qi // G, slot, qi % G] = ref16[qi]
+    np.testing.assert_array_equal(got, want)

@@ -51,6 +51,7 @@ SIGNATURES = {
     "vdb_pq_encode_tc": (_i, [_p, _i64, _i, _i, _i, _p, _p, _p, _sz, _p]),
     "vdb_debug_set_pq_tc_mode": (None, [_i]),
     "vdb_debug_set_adc_coarse": (None, [_i]),
+    "vdb_debug_adc_coarse_tables": (_i, [_p, _i, _i, _p, _p, _p, _i, _p]),
     "vdb_debug_pq_tc_stats": (_i, [_p, _i, _p, _p]),
     "vdb_pq_kmeans_workspace": (_sz, [_i, _i, _i]),
     "vdb_pq_kmeans_step": (_i, [_p, _i64, _i, _i, _i, _p, _p, _p, _sz, _p]),

@@ -1171,6 +1171,17 @@ int vdb_pq_lut(const float* q, int Q, int D, int m, int K, const float* codebook
 
 void vdb_debug_set_adc_coarse(int on) { g_adc_coarse = on ? 1 : 0; }
 
+// test hook: the collect pass's 15-bit tables for given 32-bit tables and thresholds (adc_coarse_lut_kernel as the scan
+// launches it).  lut16 is [ceil(Q/G)][ceil8(m)/8 * 2048 slots][G] u16, slot = ((j/8)*256 + c)*8 + j%8; thr16 = 0x8000 + thr.
+int vdb_debug_adc_coarse_tables(const uint32_t* lutq, int m, int Q, const uint32_t* tau, uint16_t* lut16, uint32_t* thr16,
+                                int G, void* stream) {
+    VDB_REQUIRE(lutq && tau && lut16 && thr16 && Q > 0 && m > 0 && m <= 255 && (G == 2 || G == 4 || G == 8), VDB_ERR_INVALID,
+                "vdb_debug_adc_coarse_tables: bad arguments");
+    adc_coarse_lut_kernel<<<(Q + G - 1) / G, 256, 0, static_cast<cudaStream_t>(stream)>>>(lutq, m, Q, tau, lut16, thr16, G);
+    VDB_CUDA(cudaGetLastError());
+    return VDB_OK;
+}
+
 size_t vdb_pq_adc_topk_workspace(int Q, int64_t N, int m, int R) {
     if (Q <= 0 || R <= 0 || m <= 0) return 0;
     AdcCollectPlan c;
